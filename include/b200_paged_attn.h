@@ -1,0 +1,129 @@
+/*
+ * b200_paged_attn.h — C ABI of libb200attn.so: the B200-native (sm_100a) replacement for the
+ * reference's paged-attention hot path.  Plain pointers and sizes only; every pointer named
+ * "device" is a CUDA device pointer, `stream` is a cudaStream_t passed as void*.
+ *
+ * What each entry point replaces in the reference (paths relative to the reference root):
+ *   b200_paged_attention   <- ggml_cuda_flash_attn_ext            ggml/src/ggml-cuda/fattn.cu:244
+ *                             (launch_fattn, fattn-common.cuh:675-836; CPU twin
+ *                              ggml_compute_forward_flash_attn_ext_f16, ggml-cpu/ggml-cpu.c:12219)
+ *   b200_kv_write          <- ggml_cuda_cpy for the KV store       ggml/src/ggml-cuda/cpy.cu:510-584
+ *                             (graph nodes built at src/llama-graph.cpp:1375-1397) and the fork's
+ *                             BlockKVCache::writeToCache            
+ *   b200_block_copy        <- per-move ggml_cpy / cudaMemcpyAsync  cpy.cu:544-547,
+ *                             src/llama-context.cpp:653-711 (defrag moves) and the fork's
+ *                             BlockKVCache::copyBlocks
+ *   b200_flash_attn_ext / b200_cpy / b200_supports_op (b200_ggml_abi.h) take the ggml op node itself.
+ *
+ * All functions return B200_OK (0 == GGML_STATUS_SUCCESS) or a negative b200_status; they never
+ * throw, never synchronise the stream and never allocate device memory, so they are CUDA-graph
+ * capturable (SURVEY.md §8b "Threading").  There is no CPU fallback: without a CUDA device every
+ * compute entry returns B200_ERR_CUDA.
+ */
+#ifndef B200_PAGED_ATTN_H
+#define B200_PAGED_ATTN_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_API __attribute__((visibility("default")))
+
+typedef enum {
+    B200_OK              =  0,   /* GGML_STATUS_SUCCESS */
+    B200_ERR_FAILED      = -1,   /* GGML_STATUS_FAILED */
+    B200_ERR_ALLOC       = -2,   /* GGML_STATUS_ALLOC_FAILED: workspace too small */
+    B200_ERR_UNSUPPORTED = -3,   /* shape / type outside b200_supports_* */
+    B200_ERR_INVALID     = -4,   /* malformed descriptor (NULL pointer, misaligned, ...) */
+    B200_ERR_CUDA        = -5    /* CUDA runtime error; see b200_last_error() */
+} b200_status;
+
+/* ggml type ids accepted for K/V (ggml/include/ggml.h:351-389) */
+enum { B200_TYPE_F32 = 0, B200_TYPE_F16 = 1, B200_TYPE_Q4_0 = 2, B200_TYPE_Q8_0 = 8 };
+
+/* kernel selection, for tests and ablation; AUTO in production */
+enum { B200_KERNEL_AUTO = 0, B200_KERNEL_GENERIC = 1, B200_KERNEL_STREAMK = 2 };
+
+/*
+ * Attention descriptor.  Tensor meaning follows ggml_flash_attn_ext (ggml/include/ggml.h:1794-1807):
+ *   q   F32  [d, n_q, n_head]    element (i, t, h) at q + t*nbq1 + h*nbq2 (+ i*4)
+ *   k,v type [d, n_cells, n_head_kv]  cell c, head g row at k + c*nbk1 + g*nbk2   (flat llama.cpp cache)
+ *   dst F32  [d, n_head, n_q]    contiguous
+ * Two addressing modes:
+ *   dense  (block_table == NULL): cells [0, n_kv) all scanned, optional F16 mask [n_kv, >= n_q]
+ *          with -inf hiding cells — identical semantics to the reference op.
+ *   paged  (block_table != NULL): query row t belongs to sequence q_seq[t] (or t when NULL) and sees
+ *          positions [0, min(seq_lens[s], q_pos[t]+1)); position p lives in cell
+ *          block_table[s*bt_stride + p/block_size]*block_size + p%block_size.  No mask is read.
+ */
+typedef struct b200_attn_desc {
+    int32_t n_q, n_head, n_head_kv, head_dim;
+    int32_t type_k, type_v;
+    const void *q;   int64_t nbq1, nbq2;      /* device */
+    const void *k;   int64_t nbk1, nbk2;      /* device */
+    const void *v;   int64_t nbv1, nbv2;      /* device */
+    void       *dst;                          /* device */
+    float scale, max_bias, logit_softcap;
+
+    int64_t     n_kv;                         /* dense: cells to scan; paged: cells in the pool (bounds) */
+    const void *mask; int64_t nb_mask1;       /* device F16, dense mode only, may be NULL */
+
+    const int32_t *block_table; int64_t bt_stride;   /* device */
+    const int32_t *seq_lens;                          /* device [n_seqs] */
+    int32_t        n_seqs, block_size;
+    const int32_t *q_seq;                             /* device [n_q] or NULL */
+    const int32_t *q_pos;                             /* device [n_q] or NULL */
+    int64_t        max_seq_len;   /* host-known upper bound on seq_lens (0: bt_stride*block_size) */
+    int64_t        total_tokens;  /* host-known sum of seq_lens, a scheduling hint only (0: unknown) */
+
+    void   *workspace; size_t workspace_bytes;        /* device scratch, see b200_paged_attention_workspace */
+    int32_t kernel;                                   /* B200_KERNEL_* */
+    int32_t reserved;
+} b200_attn_desc;
+
+B200_API size_t b200_paged_attention_workspace(const b200_attn_desc *d);
+B200_API int    b200_paged_attention(const b200_attn_desc *d, void *stream);
+B200_API int    b200_supports_attention(const b200_attn_desc *d);   /* 1 / 0 */
+
+/*
+ * Slot-mapped KV write with fused F32 -> {F16,Q8_0,Q4_0,F32} conversion.  K and V in one launch.
+ *   k_src,v_src F32 [n_tokens][n_head_kv*head_dim], row strides src_nb1 bytes (either may be NULL)
+ *   slot_mapping device int32 [n_tokens]: destination cell; negative or >= n_cells -> token skipped
+ *   cache cell c, head g at cache + c*nb_token + g*nb_head
+ * Quantisation is bit-exact with quantize_row_q8_0_ref / quantize_row_q4_0_ref
+ * (ggml/src/ggml-quants.c:194-216, :31-66) and ggml_fp32_to_fp16_row (ggml/src/ggml.c:387).
+ */
+typedef struct b200_kv_write_desc {
+    const float *k_src; const float *v_src; int64_t src_nb1;
+    int64_t n_tokens;
+    const int32_t *slot_mapping;
+    void *k_cache; void *v_cache;
+    int32_t type_k, type_v, n_head_kv, head_dim;
+    int64_t nbk_token, nbk_head, nbv_token, nbv_head;
+    int64_t n_cells;
+} b200_kv_write_desc;
+
+B200_API int b200_kv_write(const b200_kv_write_desc *d, void *stream);
+
+/*
+ * Batched block copy (copy-on-write, defrag moves, swap-in): for every cache in caches[0..n_caches)
+ * (HOST array of device base pointers, e.g. k_l[il], v_l[il] of all layers) copy block pairs[i][0] to
+ * pairs[i][1]; a block is block_bytes contiguous bytes (multiple of 16).  One launch.  No block may
+ * be both a source and a destination in one call.
+ */
+B200_API int b200_block_copy(void *const *caches, int32_t n_caches, int64_t block_bytes, int64_t n_blocks,
+                             const int32_t *pairs /* device [n_pairs][2] */, int64_t n_pairs, void *stream);
+
+/* diagnostics */
+B200_API const char *b200_last_error(void);
+B200_API const char *b200_version(void);
+B200_API int         b200_device_sm_count(void);
+B200_API int64_t     b200_launch_count(void);      /* kernels launched by this library so far */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

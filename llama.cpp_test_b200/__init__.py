@@ -1,0 +1,173 @@
+"""llama.cpp_test_b200 — test/bench driver bindings for libb200attn.so.
+
+The product is the C-ABI shared library (include/b200_paged_attn.h, b200_ggml_abi.h, b200_host.h) built from
+csrc/ (hand-written sm_100a CUDA) and host/ (C++ block managers mirroring the reference's
+BlockManager / BlockKVCache / llama_kv_cache interfaces).  This Python module only binds it with ctypes
+so pytest and bench.py can drive it with torch-allocated device buffers; torch is plumbing (memory,
+streams, NCCL), never the compute path.  There is NO fallback: if the library is missing, importing
+raises; if no GPU is present, compute calls return B200_ERR_CUDA and the wrappers raise.
+
+The directory name contains a dot, so import it with `load()` from __graft_entry__ / tests/conftest.py
+(importlib by path) under the module name `llama_cpp_test_b200`.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200attn.so")
+
+TYPE_F32, TYPE_F16, TYPE_Q4_0, TYPE_Q8_0 = 0, 1, 2, 8
+TYPE_NAMES = {TYPE_F32: "f32", TYPE_F16: "f16", TYPE_Q4_0: "q4_0", TYPE_Q8_0: "q8_0"}
+KERNEL_AUTO, KERNEL_GENERIC, KERNEL_STREAMK = 0, 1, 2
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} not found: build it with `make -C {os.path.join(_HERE, 'csrc')}` "
+        "(or __graft_entry__.build()); this package has no fallback path")
+
+lib = C.CDLL(LIB_PATH)
+
+
+class AttnDesc(C.Structure):
+    """struct b200_attn_desc (include/b200_paged_attn.h)"""
+    _fields_ = [
+        ("n_q", C.c_int32), ("n_head", C.c_int32), ("n_head_kv", C.c_int32), ("head_dim", C.c_int32),
+        ("type_k", C.c_int32), ("type_v", C.c_int32),
+        ("q", C.c_void_p), ("nbq1", C.c_int64), ("nbq2", C.c_int64),
+        ("k", C.c_void_p), ("nbk1", C.c_int64), ("nbk2", C.c_int64),
+        ("v", C.c_void_p), ("nbv1", C.c_int64), ("nbv2", C.c_int64),
+        ("dst", C.c_void_p),
+        ("scale", C.c_float), ("max_bias", C.c_float), ("logit_softcap", C.c_float),
+        ("n_kv", C.c_int64),
+        ("mask", C.c_void_p), ("nb_mask1", C.c_int64),
+        ("block_table", C.c_void_p), ("bt_stride", C.c_int64),
+        ("seq_lens", C.c_void_p),
+        ("n_seqs", C.c_int32), ("block_size", C.c_int32),
+        ("q_seq", C.c_void_p), ("q_pos", C.c_void_p),
+        ("max_seq_len", C.c_int64), ("total_tokens", C.c_int64),
+        ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
+        ("kernel", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+class KVWriteDesc(C.Structure):
+    """struct b200_kv_write_desc"""
+    _fields_ = [
+        ("k_src", C.c_void_p), ("v_src", C.c_void_p), ("src_nb1", C.c_int64),
+        ("n_tokens", C.c_int64),
+        ("slot_mapping", C.c_void_p),
+        ("k_cache", C.c_void_p), ("v_cache", C.c_void_p),
+        ("type_k", C.c_int32), ("type_v", C.c_int32), ("n_head_kv", C.c_int32), ("head_dim", C.c_int32),
+        ("nbk_token", C.c_int64), ("nbk_head", C.c_int64), ("nbv_token", C.c_int64), ("nbv_head", C.c_int64),
+        ("n_cells", C.c_int64),
+    ]
+
+
+class GgmlTensor(C.Structure):
+    """struct b200_ggml_tensor == the reference's struct ggml_tensor (include/b200_ggml_abi.h)"""
+    pass
+
+
+GgmlTensor._fields_ = [
+    ("type", C.c_int32), ("buffer", C.c_void_p),
+    ("ne", C.c_int64 * 4), ("nb", C.c_size_t * 4),
+    ("op", C.c_int32), ("op_params", C.c_int32 * 16), ("flags", C.c_int32),
+    ("src", C.POINTER(GgmlTensor) * 10),
+    ("view_src", C.POINTER(GgmlTensor)), ("view_offs", C.c_size_t),
+    ("data", C.c_void_p), ("name", C.c_char * 64), ("extra", C.c_void_p), ("padding", C.c_char * 8),
+]
+
+GGML_OP_CPY, GGML_OP_FLASH_ATTN_EXT, GGML_TYPE_I32 = 32, 62, 26
+
+# every symbol the headers declare (tests/test_abi.py checks the .so exports exactly these)
+EXPORTS = {
+    "b200_paged_attn.h": [
+        "b200_paged_attention_workspace", "b200_paged_attention", "b200_supports_attention", "b200_kv_write",
+        "b200_block_copy", "b200_last_error", "b200_version", "b200_device_sm_count", "b200_launch_count"],
+    "b200_ggml_abi.h": ["b200_flash_attn_ext_workspace", "b200_flash_attn_ext", "b200_cpy", "b200_supports_op"],
+    "b200_host.h": [
+        "b200_bm_create", "b200_bm_destroy", "b200_bm_allocate", "b200_bm_free", "b200_bm_evict", "b200_bm_status",
+        "b200_fork_trace", "b200_pc_create", "b200_pc_destroy", "b200_pc_append", "b200_pc_seq_cp", "b200_pc_seq_rm",
+        "b200_pc_seq_keep", "b200_pc_clear", "b200_pc_seq_len", "b200_pc_n_free", "b200_pc_ref_count", "b200_pc_export"],
+}
+
+lib.b200_paged_attention_workspace.restype = C.c_size_t
+lib.b200_paged_attention_workspace.argtypes = [C.POINTER(AttnDesc)]
+lib.b200_paged_attention.restype = C.c_int
+lib.b200_paged_attention.argtypes = [C.POINTER(AttnDesc), C.c_void_p]
+lib.b200_supports_attention.restype = C.c_int
+lib.b200_supports_attention.argtypes = [C.POINTER(AttnDesc)]
+lib.b200_kv_write.restype = C.c_int
+lib.b200_kv_write.argtypes = [C.POINTER(KVWriteDesc), C.c_void_p]
+lib.b200_block_copy.restype = C.c_int
+lib.b200_block_copy.argtypes = [C.POINTER(C.c_void_p), C.c_int32, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]
+lib.b200_last_error.restype = C.c_char_p
+lib.b200_version.restype = C.c_char_p
+lib.b200_device_sm_count.restype = C.c_int
+lib.b200_launch_count.restype = C.c_int64
+lib.b200_flash_attn_ext_workspace.restype = C.c_size_t
+lib.b200_flash_attn_ext_workspace.argtypes = [C.POINTER(GgmlTensor)]
+lib.b200_flash_attn_ext.restype = C.c_int
+lib.b200_flash_attn_ext.argtypes = [C.POINTER(GgmlTensor), C.c_void_p, C.c_size_t, C.c_void_p]
+lib.b200_cpy.restype = C.c_int
+lib.b200_cpy.argtypes = [C.POINTER(GgmlTensor), C.POINTER(GgmlTensor), C.c_void_p]
+lib.b200_supports_op.restype = C.c_int
+lib.b200_supports_op.argtypes = [C.POINTER(GgmlTensor)]
+
+lib.b200_bm_create.restype = C.c_void_p
+lib.b200_bm_create.argtypes = [C.c_int64]
+lib.b200_bm_destroy.argtypes = [C.c_void_p]
+lib.b200_bm_allocate.restype = C.c_int32
+lib.b200_bm_allocate.argtypes = [C.c_void_p]
+lib.b200_bm_free.argtypes = [C.c_void_p, C.c_int32]
+lib.b200_bm_evict.restype = C.c_int32
+lib.b200_bm_evict.argtypes = [C.c_void_p]
+lib.b200_bm_status.restype = C.c_int64
+lib.b200_bm_status.argtypes = [C.c_void_p, C.POINTER(C.c_uint8), C.c_int64]
+lib.b200_fork_trace.argtypes = [C.c_int]
+lib.b200_pc_create.restype = C.c_void_p
+lib.b200_pc_create.argtypes = [C.c_int64, C.c_int32]
+lib.b200_pc_destroy.argtypes = [C.c_void_p]
+lib.b200_pc_append.restype = C.c_int64
+lib.b200_pc_append.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int64]
+lib.b200_pc_seq_cp.restype = C.c_int32
+lib.b200_pc_seq_cp.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int64, C.c_int64]
+lib.b200_pc_seq_rm.restype = C.c_int32
+lib.b200_pc_seq_rm.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_int64]
+lib.b200_pc_seq_keep.argtypes = [C.c_void_p, C.c_int32]
+lib.b200_pc_clear.argtypes = [C.c_void_p]
+lib.b200_pc_seq_len.restype = C.c_int64
+lib.b200_pc_seq_len.argtypes = [C.c_void_p, C.c_int32]
+lib.b200_pc_n_free.restype = C.c_int64
+lib.b200_pc_n_free.argtypes = [C.c_void_p]
+lib.b200_pc_ref_count.restype = C.c_int32
+lib.b200_pc_ref_count.argtypes = [C.c_void_p, C.c_int64]
+lib.b200_pc_export.restype = C.c_int32
+lib.b200_pc_export.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_int64, C.POINTER(C.c_int32), C.c_int64, C.POINTER(C.c_int32)]
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise B200Error(f"{what}: status {rc}: {lib.b200_last_error().decode(errors='replace')}")
+
+
+def row_bytes(type_id: int, n: int) -> int:
+    """ggml_row_size for the KV types (ggml/src/ggml.c:1169)"""
+    if type_id == TYPE_F32:
+        return n * 4
+    if type_id == TYPE_F16:
+        return n * 2
+    if type_id == TYPE_Q8_0:
+        return n // 32 * 34
+    if type_id == TYPE_Q4_0:
+        return n // 32 * 18
+    raise ValueError(f"unsupported type {type_id}")
+
+
+from .driver import *  # noqa: E402,F401,F403  (torch-tensor helpers and host-class wrappers)

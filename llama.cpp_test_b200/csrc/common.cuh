@@ -1,0 +1,86 @@
+// common.cuh — shared device helpers for the sm_100a paged-attention kernels.
+#pragma once
+
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "b200_paged_attn.h"
+
+namespace b200 {
+
+constexpr int QK       = 32;   // elements per quant block (QK4_0 == QK8_0, ggml/src/ggml-common.h:161,203)
+constexpr int Q8_BYTES = 34;   // block_q8_0: half d + 32 int8
+constexpr int Q4_BYTES = 18;   // block_q4_0: half d + 16 nibble bytes
+
+__host__ __device__ constexpr int64_t row_bytes(int type, int64_t n) {
+    return type == B200_TYPE_F32  ? n*4
+         : type == B200_TYPE_F16  ? n*2
+         : type == B200_TYPE_Q8_0 ? (n/QK)*Q8_BYTES
+         : type == B200_TYPE_Q4_0 ? (n/QK)*Q4_BYTES : 0;
+}
+
+__host__ __device__ constexpr bool type_ok(int type) {
+    return type == B200_TYPE_F32 || type == B200_TYPE_F16 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_0;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+__device__ __forceinline__ uint32_t ld_u16(const void *p) { return *reinterpret_cast<const uint16_t *>(p); }
+__device__ __forceinline__ float    h2f(uint32_t bits)    { return __half2float(__ushort_as_half((unsigned short) bits)); }
+
+// Load N (2 or 4 or 8) consecutive elements e0..e0+N-1 of one head row of `TYPE` as floats.
+// e0 is a multiple of N, so the group never straddles a quant block (N <= 8 divides 16 and 32).
+// Dequantisation follows dequantize_row_q8_0 / dequantize_row_q4_0 (ggml/src/ggml-quants.c:349-362,
+// :255-273): y = q*d with d the block's half scale; Q4_0 element j<16 is the low nibble of qs[j],
+// element j>=16 the high nibble of qs[j-16], both minus 8.
+template <int TYPE, int N>
+__device__ __forceinline__ void load_row_elems(const char *row, int e0, float (&out)[N]) {
+    if constexpr (TYPE == B200_TYPE_F32) {
+        const float *p = reinterpret_cast<const float *>(row) + e0;
+#pragma unroll
+        for (int i = 0; i < N; ++i) out[i] = p[i];
+    } else if constexpr (TYPE == B200_TYPE_F16) {
+        const __half2 *p = reinterpret_cast<const __half2 *>(row + 2*e0);
+#pragma unroll
+        for (int i = 0; i < N/2; ++i) { const float2 f = __half22float2(p[i]); out[2*i] = f.x; out[2*i+1] = f.y; }
+    } else if constexpr (TYPE == B200_TYPE_Q8_0) {
+        const char *blk = row + (e0/QK)*Q8_BYTES;
+        const float d = h2f(ld_u16(blk));
+        const char *qs = blk + 2 + (e0 % QK);            // 2-byte aligned
+#pragma unroll
+        for (int i = 0; i < N/2; ++i) {
+            const uint32_t w = ld_u16(qs + 2*i);
+            out[2*i]   = (float) (int8_t) (w & 0xff) * d;
+            out[2*i+1] = (float) (int8_t) (w >> 8)   * d;
+        }
+    } else {                                             // Q4_0
+        const char *blk = row + (e0/QK)*Q4_BYTES;
+        const float d = h2f(ld_u16(blk));
+        const int j = e0 % QK;
+        const char *qs = blk + 2 + (j & 15);
+        const int sh = (j & 16) ? 4 : 0;
+#pragma unroll
+        for (int i = 0; i < N/2; ++i) {
+            const uint32_t w = ld_u16(qs + 2*i);
+            out[2*i]   = (float) ((int) ((w >> sh)       & 0xf) - 8) * d;
+            out[2*i+1] = (float) ((int) ((w >> (8 + sh)) & 0xf) - 8) * d;
+        }
+    }
+}
+
+// process-wide bookkeeping (defined in shim.cu)
+void set_error(const char *fmt, ...);
+void count_launch(int n = 1);
+bool check_launch(const char *what);
+
+} // namespace b200

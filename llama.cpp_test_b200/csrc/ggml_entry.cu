@@ -1,0 +1,147 @@
+// ggml_entry.cu — entry points taking the reference's op node (include/b200_ggml_abi.h).
+// Lowers a GGML_OP_FLASH_ATTN_EXT / GGML_OP_CPY node to the plain descriptors of b200_paged_attn.h,
+// reading the node exactly as launch_fattn does (ggml/src/ggml-cuda/fattn-common.cuh:683-700, :782-815)
+// and as ggml_cuda_cpy does (ggml/src/ggml-cuda/cpy.cu:510-584).
+#include "common.cuh"
+#include "b200_ggml_abi.h"
+
+#include <cstring>
+
+namespace b200 {
+
+static_assert(sizeof(b200_ggml_tensor) == 336, "ggml_tensor mirror out of sync with ggml/include/ggml.h:578-610");
+
+int launch_kv_write(const b200_kv_write_desc &d, cudaStream_t stream);
+
+static int64_t nelements(const b200_ggml_tensor *t) { return t->ne[0]*t->ne[1]*t->ne[2]*t->ne[3]; }
+
+static bool is_contiguous(const b200_ggml_tensor *t) {
+    if (!type_ok(t->type)) return false;
+    const int64_t blck = (t->type == B200_TYPE_Q8_0 || t->type == B200_TYPE_Q4_0) ? QK : 1;
+    if (t->ne[0] % blck) return false;
+    size_t nb = (size_t) row_bytes(t->type, blck);
+    if (t->nb[0] != nb) return false;
+    nb = (size_t) row_bytes(t->type, t->ne[0]);
+    for (int i = 1; i < B200_GGML_MAX_DIMS; ++i) {
+        if (t->ne[i] != 1 && t->nb[i] != nb) return false;
+        nb *= (size_t) t->ne[i];
+    }
+    return true;
+}
+
+static bool node_to_desc(const b200_ggml_tensor *dst, b200_attn_desc &d) {
+    if (!dst || dst->op != B200_GGML_OP_FLASH_ATTN_EXT) { set_error("flash_attn_ext: not a FLASH_ATTN_EXT node"); return false; }
+    const b200_ggml_tensor *Q = dst->src[0], *K = dst->src[1], *V = dst->src[2], *M = dst->src[3];
+    if (!Q || !K || !V) { set_error("flash_attn_ext: missing q/k/v source"); return false; }
+    // asserts of launch_fattn (fattn-common.cuh:691-700) and of the CPU op (ggml-cpu.c:12242-12261)
+    if (Q->type != B200_TYPE_F32 || dst->type != B200_TYPE_F32) { set_error("flash_attn_ext: q and dst must be F32"); return false; }
+    if (Q->ne[3] != 1 || K->ne[3] != 1 || V->ne[3] != 1) { set_error("flash_attn_ext: batch dim (ne3) must be 1"); return false; }
+    if (Q->nb[0] != 4 || K->ne[0] != Q->ne[0] || V->ne[0] != Q->ne[0]) { set_error("flash_attn_ext: head size mismatch / q rows not contiguous"); return false; }
+    if (M && (M->type != B200_TYPE_F16 || M->ne[1] < Q->ne[1] || M->ne[0] != K->ne[1])) { set_error("flash_attn_ext: mask must be F16 [n_kv, >= n_q]"); return false; }
+    if (dst->ne[0] != Q->ne[0] || dst->ne[1] != Q->ne[2] || dst->ne[2] != Q->ne[1] || !is_contiguous(dst)) { set_error("flash_attn_ext: dst must be contiguous [d, n_head, n_q]"); return false; }
+    memset(&d, 0, sizeof(d));
+    d.head_dim = (int32_t) Q->ne[0]; d.n_q = (int32_t) Q->ne[1]; d.n_head = (int32_t) Q->ne[2];
+    d.n_head_kv = (int32_t) K->ne[2];
+    d.type_k = K->type; d.type_v = V->type;
+    d.q = Q->data; d.nbq1 = (int64_t) Q->nb[1]; d.nbq2 = (int64_t) Q->nb[2];
+    d.k = K->data; d.nbk1 = (int64_t) K->nb[1]; d.nbk2 = (int64_t) K->nb[2];
+    d.v = V->data; d.nbv1 = (int64_t) V->nb[1]; d.nbv2 = (int64_t) V->nb[2];
+    d.dst = dst->data;
+    memcpy(&d.scale,         &dst->op_params[0], 4);
+    memcpy(&d.max_bias,      &dst->op_params[1], 4);
+    memcpy(&d.logit_softcap, &dst->op_params[2], 4);
+    d.n_kv = K->ne[1];
+    const b200_ggml_tensor *BT = dst->src[4];
+    if (BT) {                                                     // paged extension
+        const b200_ggml_tensor *SL = dst->src[5], *QS = dst->src[6], *QP = dst->src[7];
+        if (BT->type != B200_GGML_TYPE_I32 || !SL || SL->type != B200_GGML_TYPE_I32) { set_error("flash_attn_ext: block_table/seq_lens must be I32"); return false; }
+        if ((QS && QS->type != B200_GGML_TYPE_I32) || (QP && QP->type != B200_GGML_TYPE_I32)) { set_error("flash_attn_ext: q_seq/q_pos must be I32"); return false; }
+        d.block_table = static_cast<const int32_t *>(BT->data);
+        d.bt_stride   = (int64_t) (BT->nb[1]/4);
+        d.n_seqs      = (int32_t) BT->ne[1];
+        d.seq_lens    = static_cast<const int32_t *>(SL->data);
+        d.q_seq       = QS ? static_cast<const int32_t *>(QS->data) : nullptr;
+        d.q_pos       = QP ? static_cast<const int32_t *>(QP->data) : nullptr;
+        d.block_size  = dst->op_params[4];
+        memcpy(&d.max_seq_len, &dst->op_params[5], 8);
+    } else if (M) {
+        d.mask = M->data; d.nb_mask1 = (int64_t) M->nb[1];
+    }
+    return true;
+}
+
+__global__ void __launch_bounds__(256) copy16_kernel(const uint4 *src, uint4 *dst, int64_t n16) {
+    for (int64_t i = (int64_t) blockIdx.x*256 + threadIdx.x; i < n16; i += (int64_t) gridDim.x*256) dst[i] = src[i];
+}
+__global__ void __launch_bounds__(256) copy1_kernel(const char *src, char *dst, int64_t n) {
+    for (int64_t i = (int64_t) blockIdx.x*256 + threadIdx.x; i < n; i += (int64_t) gridDim.x*256) dst[i] = src[i];
+}
+
+} // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+B200_API size_t b200_flash_attn_ext_workspace(const struct b200_ggml_tensor *dst) {
+    b200_attn_desc d;
+    if (!node_to_desc(dst, d)) return 0;
+    return b200_paged_attention_workspace(&d);
+}
+
+B200_API int b200_flash_attn_ext(const struct b200_ggml_tensor *dst, void *workspace, size_t workspace_bytes, void *stream) {
+    b200_attn_desc d;
+    if (!node_to_desc(dst, d)) return B200_ERR_INVALID;
+    d.workspace = workspace; d.workspace_bytes = workspace_bytes;
+    return b200_paged_attention(&d, stream);
+}
+
+B200_API int b200_cpy(const struct b200_ggml_tensor *src0, struct b200_ggml_tensor *src1, void *stream) {
+    if (!src0 || !src1) { set_error("cpy: NULL tensor"); return B200_ERR_INVALID; }
+    if (nelements(src0) != nelements(src1)) { set_error("cpy: element counts differ"); return B200_ERR_INVALID; }   // ggml.c:2953
+    if (!is_contiguous(src0) || !is_contiguous(src1)) { set_error("cpy: only contiguous tensors are taken"); return B200_ERR_UNSUPPORTED; }
+    const int64_t n = nelements(src0);
+    if (n == 0) return B200_OK;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (src0->type == src1->type) {                                // block move: bytes
+        const int64_t bytes = row_bytes(src0->type, n);
+        const int grid = (int) ((bytes/16 + 255)/256 < 148*8 ? ((bytes/16 + 255)/256 > 0 ? (bytes/16 + 255)/256 : 1) : 148*8);
+        if (((((uintptr_t) src0->data) | ((uintptr_t) src1->data) | (uintptr_t) bytes) & 15) == 0)
+            copy16_kernel<<<grid, 256, 0, st>>>(static_cast<const uint4 *>(src0->data), static_cast<uint4 *>(src1->data), bytes/16);
+        else
+            copy1_kernel<<<grid, 256, 0, st>>>(static_cast<const char *>(src0->data), static_cast<char *>(src1->data), bytes);
+        count_launch();
+        return check_launch("cpy") ? B200_OK : B200_ERR_CUDA;
+    }
+    if (src0->type != B200_TYPE_F32) { set_error("cpy: source must be F32 or the destination type"); return B200_ERR_UNSUPPORTED; }
+    // KV store: treat as rows of `row` elements written to consecutive cells of a one-head cache
+    int64_t row = src0->ne[0];
+    if (row % QK || row > 8192) { set_error("cpy: row of %lld elements not supported", (long long) row); return B200_ERR_UNSUPPORTED; }
+    b200_kv_write_desc w;
+    memset(&w, 0, sizeof(w));
+    w.k_src = static_cast<const float *>(src0->data); w.src_nb1 = row*4;
+    w.n_tokens = n/row;
+    w.k_cache = src1->data; w.type_k = src1->type; w.type_v = src1->type;
+    w.n_head_kv = 1; w.head_dim = (int32_t) row;
+    w.nbk_token = row_bytes(src1->type, row); w.nbk_head = w.nbk_token;
+    w.n_cells = w.n_tokens;
+    return b200_kv_write(&w, stream);
+}
+
+B200_API int b200_supports_op(const struct b200_ggml_tensor *op) {
+    if (!op) return 0;
+    if (op->op == B200_GGML_OP_FLASH_ATTN_EXT) {
+        b200_attn_desc d;
+        if (!node_to_desc(op, d)) return 0;
+        return b200_supports_attention(&d);
+    }
+    if (op->op == B200_GGML_OP_CPY || op->op == B200_GGML_OP_DUP || op->op == B200_GGML_OP_CONT) {
+        const b200_ggml_tensor *s0 = op->src[0], *s1 = op->op == B200_GGML_OP_CPY ? op->src[1] : op;
+        if (!s0 || !s1 || !is_contiguous(s0) || !is_contiguous(s1)) return 0;
+        if (s0->type == s1->type) return 1;
+        return s0->type == B200_TYPE_F32 && s0->ne[0] % QK == 0 && s0->ne[0] <= 8192 ? 1 : 0;
+    }
+    return 0;
+}
+
+} // extern "C"

@@ -1,0 +1,208 @@
+// kv_write.cu — slot-mapped KV-cache write with fused F32 -> {F32,F16,Q8_0,Q4_0} conversion, and the
+// batched block copy used for copy-on-write / defrag moves.
+//
+// Replaces (reference paths): ggml_cuda_cpy + cpy_f32_f16 / cpy_f32_q<cpy_blck_f32_q8_0|q4_0>
+// (ggml/src/ggml-cuda/cpy.cu:34-127, :290-402, :510-584) as scheduled by build_attn
+// (src/llama-graph.cpp:1375-1397), and the per-move cudaMemcpyAsync of defrag (cpy.cu:544-547,
+// src/llama-context.cpp:653-711).  The reference launches ONE single-thread CTA per 32-element quant
+// block (cpy.cu:372-381); here one CTA owns one token row, 8 lanes cooperate on each quant block with
+// shuffles, the converted row is staged in shared memory and leaves the SM as coalesced 16-byte stores.
+//
+// Bit-exactness: arithmetic is the IEEE sequence of quantize_row_q8_0_ref / quantize_row_q4_0_ref
+// (ggml/src/ggml-quants.c:194-216, :31-66) with explicit _rn intrinsics so nvcc cannot contract
+// x*id + 8.5f into an FMA; half conversion is RNE like ggml_fp32_to_fp16_row (ggml/src/ggml.c:387).
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int KVW_THREADS = 256;
+
+// 8-lane group reductions (lanes of a group are contiguous and 8-aligned)
+__device__ __forceinline__ float group8_max(float v) {
+    v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 1));
+    v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 2));
+    v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 4));
+    return v;
+}
+
+// first element (in index order) with the largest |v|: quantize_row_q4_0_ref keeps `max` of the
+// first strictly-greater amax (ggml-quants.c:42-48), so ties resolve to the lower index.
+__device__ __forceinline__ void group8_absmax_first(float &amax, float &vmax, int lane) {
+#pragma unroll
+    for (int o = 1; o <= 4; o <<= 1) {
+        const float oa = __shfl_xor_sync(0xffffffffu, amax, o);
+        const float ov = __shfl_xor_sync(0xffffffffu, vmax, o);
+        const bool partner_is_lower = ((lane ^ o) < lane);
+        // lo = lower lane's candidate, hi = higher lane's; result = (lo.amax < hi.amax) ? hi : lo
+        const float lo_a = partner_is_lower ? oa : amax, hi_a = partner_is_lower ? amax : oa;
+        const float lo_v = partner_is_lower ? ov : vmax, hi_v = partner_is_lower ? vmax : ov;
+        const bool take_hi = lo_a < hi_a;
+        amax = take_hi ? hi_a : lo_a;
+        vmax = take_hi ? hi_v : lo_v;
+    }
+}
+
+// Convert 4 consecutive floats (element index e0 = 4*i of the token row) into the staged row.
+template <int TYPE>
+__device__ __forceinline__ void convert4(const float4 x, int e0, char *stage, int lane, bool active) {
+    if constexpr (TYPE == B200_TYPE_F32) {
+        if (!active) return;
+        *reinterpret_cast<float4 *>(stage + 4*e0) = x;
+    } else if constexpr (TYPE == B200_TYPE_F16) {
+        if (!active) return;
+        const __half2 a = __floats2half2_rn(x.x, x.y), b = __floats2half2_rn(x.z, x.w);
+        uint2 w;
+        w.x = *reinterpret_cast<const uint32_t *>(&a);
+        w.y = *reinterpret_cast<const uint32_t *>(&b);
+        *reinterpret_cast<uint2 *>(stage + 2*e0) = w;
+    } else if constexpr (TYPE == B200_TYPE_Q8_0) {
+        // ggml-quants.c:199-214
+        float amax = fmaxf(fmaxf(fabsf(x.x), fabsf(x.y)), fmaxf(fabsf(x.z), fabsf(x.w)));
+        amax = group8_max(amax);
+        const float d  = __fdiv_rn(amax, 127.0f);
+        const float id = d ? __fdiv_rn(1.0f, d) : 0.0f;
+        const int q0 = (int) roundf(__fmul_rn(x.x, id)), q1 = (int) roundf(__fmul_rn(x.y, id));
+        const int q2 = (int) roundf(__fmul_rn(x.z, id)), q3 = (int) roundf(__fmul_rn(x.w, id));
+        if (!active) return;
+        char *blk = stage + (e0/QK)*Q8_BYTES;
+        uint16_t *qs = reinterpret_cast<uint16_t *>(blk + 2 + (e0 % QK));      // 2-byte aligned
+        qs[0] = (uint16_t) ((q0 & 0xff) | ((q1 & 0xff) << 8));
+        qs[1] = (uint16_t) ((q2 & 0xff) | ((q3 & 0xff) << 8));
+        if ((lane & 7) == 0) *reinterpret_cast<__half *>(blk) = __float2half_rn(d);
+    } else {                                                                   // Q4_0, ggml-quants.c:38-64
+        float amax = 0.0f, vmax = 0.0f;
+        if (amax < fabsf(x.x)) { amax = fabsf(x.x); vmax = x.x; }
+        if (amax < fabsf(x.y)) { amax = fabsf(x.y); vmax = x.y; }
+        if (amax < fabsf(x.z)) { amax = fabsf(x.z); vmax = x.z; }
+        if (amax < fabsf(x.w)) { amax = fabsf(x.w); vmax = x.w; }
+        group8_absmax_first(amax, vmax, lane);
+        const float d  = __fdiv_rn(vmax, -8.0f);
+        const float id = d ? __fdiv_rn(1.0f, d) : 0.0f;
+        auto q4 = [&](float v) -> uint32_t {
+            const int t = (int) (int8_t) (int) __fadd_rn(__fmul_rn(v, id), 8.5f);   // (int8_t)(x0 + 8.5f)
+            return (uint32_t) (t < 15 ? t : 15) & 0xffu;                            // MIN(15, .)
+        };
+        // 4 codes, one per byte lane of a 32-bit word
+        uint32_t mine = q4(x.x) | (q4(x.y) << 8) | (q4(x.z) << 16) | (q4(x.w) << 24);
+        const uint32_t theirs = __shfl_xor_sync(0xffffffffu, mine, 4);
+        if (!active) return;
+        char *blk = stage + (e0/QK)*Q4_BYTES;
+        const int t = lane & 7;
+        if (t < 4) {            // elements 4t..4t+3 are the low nibbles of qs[4t..4t+3]; partner holds +16
+            const uint32_t w = (mine & 0x0f0f0f0fu) | ((theirs & 0x0f0f0f0fu) << 4);
+            uint16_t *qs = reinterpret_cast<uint16_t *>(blk + 2 + 4*t);
+            qs[0] = (uint16_t) (w & 0xffffu);
+            qs[1] = (uint16_t) (w >> 16);
+        }
+        if (t == 0) *reinterpret_cast<__half *>(blk) = __float2half_rn(d);
+    }
+}
+
+template <int TYPE>
+__device__ void write_row(const float *src, char *cache, int64_t cell, int n_head_kv, int head_dim,
+                          int64_t nb_token, int64_t nb_head, char *stage) {
+    const int row_elems = n_head_kv*head_dim;
+    const int lane = threadIdx.x & 31;
+    // uniform trip count for the whole CTA: lanes past the row still take part in the shuffles
+    for (int base = 0; base < row_elems; base += 4*KVW_THREADS) {
+        const int e0 = base + 4*threadIdx.x;
+        const bool active = e0 < row_elems;
+        const float4 x = active ? *reinterpret_cast<const float4 *>(src + e0) : make_float4(0.f, 0.f, 0.f, 0.f);
+        convert4<TYPE>(x, e0, stage, lane, active);
+    }
+    __syncthreads();
+    const int64_t head_bytes = row_bytes(TYPE, head_dim);
+    char *dst = cache + cell*nb_token;
+    if (nb_head == head_bytes && (((uintptr_t) dst | (uintptr_t) (head_bytes*n_head_kv)) & 15) == 0) {
+        const int n16 = (int) (head_bytes*n_head_kv/16);
+        for (int i = threadIdx.x; i < n16; i += KVW_THREADS)
+            reinterpret_cast<uint4 *>(dst)[i] = reinterpret_cast<const uint4 *>(stage)[i];
+    } else {                                   // arbitrary head stride / alignment: 2-byte units
+        const int per_head = (int) (head_bytes/2);
+        for (int i = threadIdx.x; i < per_head*n_head_kv; i += KVW_THREADS) {
+            const int h = i / per_head, o = i - h*per_head;
+            reinterpret_cast<uint16_t *>(dst + h*nb_head)[o] = reinterpret_cast<const uint16_t *>(stage)[i];
+        }
+    }
+}
+
+// grid (n_tokens, 2): y == 0 writes K, y == 1 writes V
+__global__ void __launch_bounds__(KVW_THREADS)
+kv_write_kernel(const b200_kv_write_desc p) {
+    extern __shared__ __align__(16) char stage[];
+    const int64_t t = blockIdx.x;
+    const int64_t cell = p.slot_mapping ? (int64_t) p.slot_mapping[t] : t;
+    if (cell < 0 || cell >= p.n_cells) return;                       // writeToCache skips invalid slots
+    const bool is_v = blockIdx.y == 1;
+    const float *src = is_v ? p.v_src : p.k_src;
+    if (src == nullptr) return;
+    src = reinterpret_cast<const float *>(reinterpret_cast<const char *>(src) + t*p.src_nb1);
+    char *cache = static_cast<char *>(is_v ? p.v_cache : p.k_cache);
+    const int type = is_v ? p.type_v : p.type_k;
+    const int64_t nbt = is_v ? p.nbv_token : p.nbk_token, nbh = is_v ? p.nbv_head : p.nbk_head;
+    switch (type) {
+        case B200_TYPE_F32:  write_row<B200_TYPE_F32 >(src, cache, cell, p.n_head_kv, p.head_dim, nbt, nbh, stage); break;
+        case B200_TYPE_F16:  write_row<B200_TYPE_F16 >(src, cache, cell, p.n_head_kv, p.head_dim, nbt, nbh, stage); break;
+        case B200_TYPE_Q8_0: write_row<B200_TYPE_Q8_0>(src, cache, cell, p.n_head_kv, p.head_dim, nbt, nbh, stage); break;
+        default:             write_row<B200_TYPE_Q4_0>(src, cache, cell, p.n_head_kv, p.head_dim, nbt, nbh, stage); break;
+    }
+}
+
+int launch_kv_write(const b200_kv_write_desc &d, cudaStream_t stream) {
+    if (d.n_tokens == 0) return B200_OK;
+    const int64_t row_elems = (int64_t) d.n_head_kv*d.head_dim;
+    const int64_t sk = row_bytes(d.type_k, row_elems), sv = row_bytes(d.type_v, row_elems);
+    const size_t smem = (size_t) (sk > sv ? sk : sv);
+    if (smem > 48*1024) { set_error("kv_write: token row of %lld bytes exceeds 48 KiB staging", (long long) smem); return B200_ERR_UNSUPPORTED; }
+    const dim3 grid((unsigned) d.n_tokens, 2);
+    kv_write_kernel<<<grid, KVW_THREADS, smem, stream>>>(d);
+    count_launch();
+    return check_launch("kv_write") ? B200_OK : B200_ERR_CUDA;
+}
+
+// ---------------------------------------------------------------------------------------------
+// batched block copy: grid (n_pairs, n_caches); each CTA streams one block with 16-byte accesses
+// ---------------------------------------------------------------------------------------------
+constexpr int BC_MAX_CACHES = 128;
+struct block_copy_args {
+    char   *caches[BC_MAX_CACHES];
+    int64_t block_bytes, n_blocks;
+    const int32_t *pairs;
+};
+
+__global__ void __launch_bounds__(256)
+block_copy_kernel(const __grid_constant__ block_copy_args a) {
+    const int32_t s = a.pairs[2*blockIdx.x], d = a.pairs[2*blockIdx.x + 1];
+    if (s == d || s < 0 || d < 0 || s >= a.n_blocks || d >= a.n_blocks) return;
+    char *base = a.caches[blockIdx.y];
+    const uint4 *src = reinterpret_cast<const uint4 *>(base + (int64_t) s*a.block_bytes);
+    uint4       *dst = reinterpret_cast<uint4 *>(base + (int64_t) d*a.block_bytes);
+    const int n16 = (int) (a.block_bytes/16);
+    int i = threadIdx.x;
+    for (; i + 3*256 < n16; i += 4*256) {                            // 4 independent 16-byte loads in flight
+        const uint4 v0 = src[i], v1 = src[i + 256], v2 = src[i + 512], v3 = src[i + 768];
+        dst[i] = v0; dst[i + 256] = v1; dst[i + 512] = v2; dst[i + 768] = v3;
+    }
+    for (; i < n16; i += 256) dst[i] = src[i];
+}
+
+int launch_block_copy(void *const *caches, int n_caches, int64_t block_bytes, int64_t n_blocks,
+                      const int32_t *pairs, int64_t n_pairs, cudaStream_t stream) {
+    if (n_pairs == 0 || n_caches == 0) return B200_OK;
+    if (block_bytes <= 0 || (block_bytes & 15)) { set_error("block_copy: block_bytes %lld not a multiple of 16", (long long) block_bytes); return B200_ERR_INVALID; }
+    for (int c0 = 0; c0 < n_caches; c0 += BC_MAX_CACHES) {
+        block_copy_args a;
+        const int n = n_caches - c0 < BC_MAX_CACHES ? n_caches - c0 : BC_MAX_CACHES;
+        for (int i = 0; i < n; ++i) {
+            a.caches[i] = static_cast<char *>(caches[c0 + i]);
+            if (((uintptr_t) a.caches[i]) & 15) { set_error("block_copy: cache %d not 16-byte aligned", c0 + i); return B200_ERR_INVALID; }
+        }
+        a.block_bytes = block_bytes; a.n_blocks = n_blocks; a.pairs = pairs;
+        block_copy_kernel<<<dim3((unsigned) n_pairs, (unsigned) n), 256, 0, stream>>>(a);
+        count_launch();
+        if (!check_launch("block_copy")) return B200_ERR_CUDA;
+    }
+    return B200_OK;
+}
+
+} // namespace b200

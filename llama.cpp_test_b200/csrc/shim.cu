@@ -1,0 +1,138 @@
+// shim.cu — the C ABI of libb200attn.so (include/b200_paged_attn.h): validation, dispatch, bookkeeping.
+// No CPU fallback anywhere: every compute entry launches CUDA kernels or returns an error.
+#include "common.cuh"
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+namespace b200 {
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+void set_error(const char *fmt, ...) {
+    va_list ap; va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+bool check_launch(const char *what) {
+    const cudaError_t e = cudaPeekAtLastError();
+    if (e != cudaSuccess) { set_error("%s: %s", what, cudaGetErrorString(e)); (void) cudaGetLastError(); return false; }
+    return true;
+}
+
+// kernels (kv_write.cu, attn_generic.cu, attn_streamk.cu)
+int    launch_kv_write(const b200_kv_write_desc &d, cudaStream_t stream);
+int    launch_block_copy(void *const *caches, int n_caches, int64_t block_bytes, int64_t n_blocks,
+                         const int32_t *pairs, int64_t n_pairs, cudaStream_t stream);
+bool   generic_supports(const b200_attn_desc &d);
+size_t generic_workspace(const b200_attn_desc &d);
+int    launch_attn_generic(const b200_attn_desc &d, cudaStream_t st);
+bool   streamk_supports(const b200_attn_desc &d);
+size_t streamk_workspace(const b200_attn_desc &d);
+int    launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st);
+
+static bool have_device() {
+    static int state = -1;                       // -1 unknown, 0 none, 1 ok
+    if (state < 0) {
+        int n = 0;
+        const cudaError_t e = cudaGetDeviceCount(&n);
+        state = (e == cudaSuccess && n > 0) ? 1 : 0;
+        if (!state) { (void) cudaGetLastError(); }
+    }
+    if (!state) set_error("no CUDA device: libb200attn has no CPU fallback");
+    return state == 1;
+}
+
+static int validate_attn(const b200_attn_desc *d) {
+    if (!d) { set_error("attention: NULL descriptor"); return B200_ERR_INVALID; }
+    if (!d->q || !d->k || !d->v || !d->dst) { set_error("attention: NULL tensor pointer"); return B200_ERR_INVALID; }
+    if (d->n_q < 0 || d->n_head <= 0 || d->n_head_kv <= 0 || d->head_dim <= 0) { set_error("attention: bad shape"); return B200_ERR_INVALID; }
+    if (d->n_head % d->n_head_kv) { set_error("attention: n_head %d not a multiple of n_head_kv %d", d->n_head, d->n_head_kv); return B200_ERR_INVALID; }
+    if (d->block_table) {
+        if (!d->seq_lens || d->n_seqs <= 0 || d->block_size <= 0 || d->bt_stride <= 0) { set_error("attention: paged mode needs seq_lens, n_seqs, block_size, bt_stride"); return B200_ERR_INVALID; }
+        if (!d->q_seq && d->n_q > d->n_seqs) { set_error("attention: n_q %d > n_seqs %d without q_seq", d->n_q, d->n_seqs); return B200_ERR_INVALID; }
+        if (d->max_bias != 0.0f) { set_error("attention: ALiBi needs the dense mask (paged mode carries no positions bias)"); return B200_ERR_UNSUPPORTED; }
+    } else if (d->n_kv < 0) { set_error("attention: negative n_kv"); return B200_ERR_INVALID; }
+    return B200_OK;
+}
+
+static int pick_kernel(const b200_attn_desc &d) {
+    if (d.kernel == B200_KERNEL_GENERIC) return B200_KERNEL_GENERIC;
+    if (d.kernel == B200_KERNEL_STREAMK) return B200_KERNEL_STREAMK;
+    return streamk_supports(d) ? B200_KERNEL_STREAMK : B200_KERNEL_GENERIC;
+}
+
+} // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+B200_API const char *b200_last_error(void) { return g_err; }
+B200_API const char *b200_version(void)    { return "b200attn 0.1 (sm_100a)"; }
+B200_API int64_t     b200_launch_count(void) { return g_launches.load(); }
+
+B200_API int b200_device_sm_count(void) {
+    if (!have_device()) return 0;
+    int dev = 0, n = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    return n;
+}
+
+B200_API int b200_supports_attention(const b200_attn_desc *d) {
+    if (validate_attn(d) != B200_OK) return 0;
+    if (d->kernel == B200_KERNEL_STREAMK) return streamk_supports(*d) ? 1 : 0;
+    return (generic_supports(*d) || streamk_supports(*d)) ? 1 : 0;
+}
+
+B200_API size_t b200_paged_attention_workspace(const b200_attn_desc *d) {
+    if (validate_attn(d) != B200_OK) return 0;
+    size_t a = generic_supports(*d) ? generic_workspace(*d) : 0;
+    size_t b = streamk_supports(*d) ? streamk_workspace(*d) : 0;
+    if (d->kernel == B200_KERNEL_GENERIC) b = 0;
+    if (d->kernel == B200_KERNEL_STREAMK) a = 0;
+    return a > b ? a : b;
+}
+
+B200_API int b200_paged_attention(const b200_attn_desc *d, void *stream) {
+    const int rc = validate_attn(d);
+    if (rc != B200_OK) return rc;
+    if (!have_device()) return B200_ERR_CUDA;
+    if (d->n_q == 0) return B200_OK;
+    const int k = pick_kernel(*d);
+    if (k == B200_KERNEL_STREAMK) {
+        if (!streamk_supports(*d)) { set_error("attention: stream-K kernel does not take this shape"); return B200_ERR_UNSUPPORTED; }
+        return launch_attn_streamk(*d, static_cast<cudaStream_t>(stream));
+    }
+    if (!generic_supports(*d)) {
+        set_error("attention: unsupported shape/type (head_dim %d, type_k %d, type_v %d)", d->head_dim, d->type_k, d->type_v);
+        return B200_ERR_UNSUPPORTED;
+    }
+    return launch_attn_generic(*d, static_cast<cudaStream_t>(stream));
+}
+
+B200_API int b200_kv_write(const b200_kv_write_desc *d, void *stream) {
+    if (!d) { set_error("kv_write: NULL descriptor"); return B200_ERR_INVALID; }
+    if (d->n_tokens < 0 || d->n_head_kv <= 0 || d->head_dim <= 0) { set_error("kv_write: bad shape"); return B200_ERR_INVALID; }
+    if ((d->k_src && !d->k_cache) || (d->v_src && !d->v_cache)) { set_error("kv_write: source without cache"); return B200_ERR_INVALID; }
+    if (!type_ok(d->type_k) || !type_ok(d->type_v)) { set_error("kv_write: unsupported cache type %d/%d", d->type_k, d->type_v); return B200_ERR_UNSUPPORTED; }
+    if (d->head_dim % QK) { set_error("kv_write: head_dim %d not a multiple of 32", d->head_dim); return B200_ERR_UNSUPPORTED; }
+    if ((d->src_nb1 & 15) || ((uintptr_t) d->k_src & 15) || ((uintptr_t) d->v_src & 15)) { set_error("kv_write: source rows must be 16-byte aligned"); return B200_ERR_INVALID; }
+    if ((d->nbk_token | d->nbk_head | d->nbv_token | d->nbv_head | (int64_t) (uintptr_t) d->k_cache | (int64_t) (uintptr_t) d->v_cache) & 1) { set_error("kv_write: cache strides must be even"); return B200_ERR_INVALID; }
+    if (!have_device()) return B200_ERR_CUDA;
+    return launch_kv_write(*d, static_cast<cudaStream_t>(stream));
+}
+
+B200_API int b200_block_copy(void *const *caches, int32_t n_caches, int64_t block_bytes, int64_t n_blocks,
+                             const int32_t *pairs, int64_t n_pairs, void *stream) {
+    if (n_caches < 0 || n_pairs < 0 || (n_caches > 0 && !caches) || (n_pairs > 0 && !pairs)) { set_error("block_copy: bad arguments"); return B200_ERR_INVALID; }
+    if (!have_device()) return B200_ERR_CUDA;
+    return launch_block_copy(caches, n_caches, block_bytes, n_blocks, pairs, n_pairs, static_cast<cudaStream_t>(stream));
+}
+
+} // extern "C"

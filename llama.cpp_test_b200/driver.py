@@ -1,0 +1,226 @@
+"""driver.py — thin helpers that hand torch device buffers to the C ABI, plus ctypes wrappers of the
+host-side block managers.  No arithmetic happens here."""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+from . import (AttnDesc, KVWriteDesc, KERNEL_AUTO, TYPE_F16, TYPE_F32, TYPE_Q4_0, TYPE_Q8_0,  # noqa: F401
+               check, lib, row_bytes)
+
+__all__ = ["KVLayout", "AttnCall", "paged_attention", "dense_attention", "kv_write", "block_copy",
+           "BlockManager", "PagedKVCache", "current_stream"]
+
+
+def current_stream() -> int:
+    import torch
+    return torch.cuda.current_stream().cuda_stream
+
+
+@dataclass(frozen=True)
+class KVLayout:
+    """The flat llama.cpp cache (src/llama-kv-cache.cpp:100-101) seen as blocks of `block_size` cells:
+    cell c, kv-head g at  c*token_bytes + g*head_bytes ; block b = cells [b*block_size, (b+1)*block_size)."""
+    type_id: int
+    n_head_kv: int
+    head_dim: int
+    block_size: int
+    n_blocks: int
+
+    @property
+    def head_bytes(self) -> int:
+        return row_bytes(self.type_id, self.head_dim)
+
+    @property
+    def token_bytes(self) -> int:
+        return self.head_bytes * self.n_head_kv
+
+    @property
+    def block_bytes(self) -> int:
+        return self.token_bytes * self.block_size
+
+    @property
+    def n_cells(self) -> int:
+        return self.n_blocks * self.block_size
+
+    @property
+    def total_bytes(self) -> int:
+        return self.n_cells * self.token_bytes
+
+    def alloc(self, device="cuda"):
+        import torch
+        return torch.zeros(self.total_bytes, dtype=torch.uint8, device=device)
+
+
+def _ptr(t) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+class AttnCall:
+    """A prepared b200_paged_attention call (descriptor + workspace), reusable across launches."""
+
+    def __init__(self, q, k_cache, v_cache, layout_k: KVLayout, out, scale: float, *, layout_v: KVLayout | None = None,
+                 block_table=None, seq_lens=None, q_seq=None, q_pos=None, mask=None, n_kv: int | None = None,
+                 max_seq_len: int = 0, total_tokens: int = 0, softcap: float = 0.0, max_bias: float = 0.0,
+                 kernel: int = KERNEL_AUTO):
+        import torch
+        layout_v = layout_v or layout_k
+        assert q.dtype == torch.float32 and q.dim() == 3 and q.is_contiguous()
+        assert out.dtype == torch.float32 and out.is_contiguous() and out.shape == q.shape
+        n_q, n_head, d = q.shape
+        desc = AttnDesc()
+        desc.n_q, desc.n_head, desc.n_head_kv, desc.head_dim = n_q, n_head, layout_k.n_head_kv, d
+        desc.type_k, desc.type_v = layout_k.type_id, layout_v.type_id
+        desc.q, desc.nbq1, desc.nbq2 = q.data_ptr(), n_head * d * 4, d * 4       # [d, n_q, n_head] permuted view
+        desc.k, desc.nbk1, desc.nbk2 = k_cache.data_ptr(), layout_k.token_bytes, layout_k.head_bytes
+        desc.v, desc.nbv1, desc.nbv2 = v_cache.data_ptr(), layout_v.token_bytes, layout_v.head_bytes
+        desc.dst = out.data_ptr()
+        desc.scale, desc.max_bias, desc.logit_softcap = scale, max_bias, softcap
+        desc.n_kv = layout_k.n_cells if n_kv is None else n_kv
+        if block_table is not None:
+            assert block_table.dtype == torch.int32 and block_table.dim() == 2 and block_table.stride(1) == 1
+            assert seq_lens is not None and seq_lens.dtype == torch.int32
+            desc.block_table, desc.bt_stride = block_table.data_ptr(), block_table.stride(0)
+            desc.seq_lens, desc.n_seqs, desc.block_size = seq_lens.data_ptr(), block_table.shape[0], layout_k.block_size
+            desc.q_seq, desc.q_pos = _ptr(q_seq), _ptr(q_pos)
+            desc.max_seq_len, desc.total_tokens = max_seq_len, total_tokens
+        elif mask is not None:
+            assert mask.dtype == torch.float16 and mask.dim() == 2 and mask.stride(1) == 1
+            desc.mask, desc.nb_mask1 = mask.data_ptr(), mask.stride(0) * 2
+        desc.kernel = kernel
+        self.desc = desc
+        ws = lib.b200_paged_attention_workspace(C.byref(desc))
+        self.workspace = torch.empty(max(ws, 16), dtype=torch.uint8, device=q.device)
+        desc.workspace, desc.workspace_bytes = self.workspace.data_ptr(), self.workspace.numel()
+        self._keep = (q, k_cache, v_cache, out, block_table, seq_lens, q_seq, q_pos, mask)
+
+    def supported(self) -> bool:
+        return bool(lib.b200_supports_attention(C.byref(self.desc)))
+
+    def run(self, stream: int | None = None) -> None:
+        check(lib.b200_paged_attention(C.byref(self.desc), C.c_void_p(current_stream() if stream is None else stream)),
+              "b200_paged_attention")
+
+
+def paged_attention(q, k_cache, v_cache, layout: KVLayout, block_table, seq_lens, scale: float, **kw):
+    """q F32 [n_q, n_head, d] -> out F32 [n_q, n_head, d] through the block table."""
+    import torch
+    out = kw.pop("out", None)
+    if out is None:
+        out = torch.empty_like(q)
+    AttnCall(q, k_cache, v_cache, layout, out, scale, block_table=block_table, seq_lens=seq_lens, **kw).run()
+    return out
+
+
+def dense_attention(q, k_cache, v_cache, layout: KVLayout, n_kv: int, mask, scale: float, **kw):
+    """reference-semantics mode: flat cache cells [0, n_kv) + F16 mask [>=n_q, n_kv]."""
+    import torch
+    out = kw.pop("out", None)
+    if out is None:
+        out = torch.empty_like(q)
+    AttnCall(q, k_cache, v_cache, layout, out, scale, mask=mask, n_kv=n_kv, **kw).run()
+    return out
+
+
+def kv_write(k_src, v_src, slot_mapping, k_cache, v_cache, layout_k: KVLayout, layout_v: KVLayout | None = None,
+             stream: int | None = None) -> None:
+    """k_src/v_src F32 [n_tokens, n_head_kv*head_dim] -> typed cache cells slot_mapping[t]."""
+    layout_v = layout_v or layout_k
+    src = k_src if k_src is not None else v_src
+    d = KVWriteDesc()
+    d.k_src, d.v_src, d.src_nb1 = _ptr(k_src), _ptr(v_src), src.stride(0) * 4
+    d.n_tokens = src.shape[0]
+    d.slot_mapping = _ptr(slot_mapping)
+    d.k_cache, d.v_cache = _ptr(k_cache), _ptr(v_cache)
+    d.type_k, d.type_v, d.n_head_kv, d.head_dim = layout_k.type_id, layout_v.type_id, layout_k.n_head_kv, layout_k.head_dim
+    d.nbk_token, d.nbk_head = layout_k.token_bytes, layout_k.head_bytes
+    d.nbv_token, d.nbv_head = layout_v.token_bytes, layout_v.head_bytes
+    d.n_cells = layout_k.n_cells
+    check(lib.b200_kv_write(C.byref(d), C.c_void_p(current_stream() if stream is None else stream)), "b200_kv_write")
+
+
+def block_copy(caches, block_bytes: int, n_blocks: int, pairs, stream: int | None = None) -> None:
+    """caches: list of device byte tensors sharing one block geometry; pairs: int32 device tensor [n, 2]."""
+    arr = (C.c_void_p * len(caches))(*[c.data_ptr() for c in caches])
+    check(lib.b200_block_copy(arr, len(caches), block_bytes, n_blocks, C.c_void_p(pairs.data_ptr()), pairs.shape[0],
+                              C.c_void_p(current_stream() if stream is None else stream)), "b200_block_copy")
+
+
+class BlockManager:
+    """the fork's BlockManager through the C ABI (include/b200_host.h)"""
+
+    def __init__(self, num_blocks: int):
+        self._h = lib.b200_bm_create(num_blocks)
+        self.num_blocks = num_blocks
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib.b200_bm_destroy(self._h)
+            self._h = None
+
+    def allocateBlock(self) -> int:
+        return lib.b200_bm_allocate(self._h)
+
+    def freeBlock(self, i: int) -> None:
+        lib.b200_bm_free(self._h, i)
+
+    def evictBlock(self) -> int:
+        return lib.b200_bm_evict(self._h)
+
+    def getBlockStatus(self) -> list[bool]:
+        buf = (C.c_uint8 * max(self.num_blocks, 1))()
+        n = lib.b200_bm_status(self._h, buf, self.num_blocks)
+        return [bool(buf[i]) for i in range(n)]
+
+
+class PagedKVCache:
+    """PagedKVCache through the C ABI"""
+
+    def __init__(self, n_blocks: int, block_size: int):
+        self._h = lib.b200_pc_create(n_blocks, block_size)
+        self.n_blocks, self.block_size = n_blocks, block_size
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib.b200_pc_destroy(self._h)
+            self._h = None
+
+    def append(self, seq: int, n_new: int):
+        """-> (slot_mapping list, cow_pairs list of (src,dst)) or None when out of blocks"""
+        slots = (C.c_int32 * max(n_new, 1))()
+        cow = (C.c_int32 * 2)()
+        n = lib.b200_pc_append(self._h, seq, n_new, slots, cow, 1)
+        if n < 0:
+            return None
+        return [slots[i] for i in range(n_new)], [(cow[2 * i], cow[2 * i + 1]) for i in range(n)]
+
+    def seq_cp(self, src: int, dst: int, p0: int = 0, p1: int = -1) -> bool:
+        return bool(lib.b200_pc_seq_cp(self._h, src, dst, p0, p1))
+
+    def seq_rm(self, seq: int, p0: int = 0, p1: int = -1) -> bool:
+        return bool(lib.b200_pc_seq_rm(self._h, seq, p0, p1))
+
+    def seq_keep(self, seq: int) -> None:
+        lib.b200_pc_seq_keep(self._h, seq)
+
+    def clear(self) -> None:
+        lib.b200_pc_clear(self._h)
+
+    def seq_len(self, seq: int) -> int:
+        return lib.b200_pc_seq_len(self._h, seq)
+
+    def n_free(self) -> int:
+        return lib.b200_pc_n_free(self._h)
+
+    def ref_count(self, block: int) -> int:
+        return lib.b200_pc_ref_count(self._h, block)
+
+    def export(self, seqs: list[int], stride: int):
+        """-> (block_table rows as list of lists, seq_lens list) or None if stride too small"""
+        n = len(seqs)
+        ids = (C.c_int32 * max(n, 1))(*seqs)
+        bt = (C.c_int32 * max(n * stride, 1))()
+        lens = (C.c_int32 * max(n, 1))()
+        if not lib.b200_pc_export(self._h, ids, n, bt, stride, lens):
+            return None
+        return [[bt[i * stride + j] for j in range(stride)] for i in range(n)], [lens[i] for i in range(n)]

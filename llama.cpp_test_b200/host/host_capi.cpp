@@ -1,0 +1,53 @@
+// host_capi.cpp — C ABI wrappers (include/b200_host.h) over the host classes.
+#include "b200_host.h"
+#include "block_manager.h"
+#include "paged_kv_cache.h"
+
+#include <new>
+#include <vector>
+
+struct b200_block_manager { BlockManager impl; explicit b200_block_manager(size_t n) : impl(n) {} };
+struct b200_paged_cache   { PagedKVCache impl; b200_paged_cache(int64_t n, int bs) : impl(n, bs) {} };
+
+extern "C" {
+
+B200_API b200_block_manager *b200_bm_create(int64_t n) { return n < 0 ? nullptr : new (std::nothrow) b200_block_manager((size_t) n); }
+B200_API void    b200_bm_destroy(b200_block_manager *bm) { delete bm; }
+B200_API int32_t b200_bm_allocate(b200_block_manager *bm) { return bm->impl.allocateBlock(); }
+B200_API void    b200_bm_free(b200_block_manager *bm, int32_t i) { bm->impl.freeBlock(i); }
+B200_API int32_t b200_bm_evict(b200_block_manager *bm) { return bm->impl.evictBlock(); }
+B200_API int64_t b200_bm_status(const b200_block_manager *bm, uint8_t *out, int64_t cap) {
+    const std::vector<bool> s = bm->impl.getBlockStatus();
+    for (int64_t i = 0; i < (int64_t) s.size() && i < cap; ++i) out[i] = s[(size_t) i] ? 1 : 0;
+    return (int64_t) s.size();
+}
+B200_API void b200_fork_trace(int enabled) { g_b200_fork_trace = enabled != 0; }
+
+B200_API b200_paged_cache *b200_pc_create(int64_t n_blocks, int32_t block_size) {
+    return (n_blocks < 0 || block_size <= 0) ? nullptr : new (std::nothrow) b200_paged_cache(n_blocks, block_size);
+}
+B200_API void b200_pc_destroy(b200_paged_cache *pc) { delete pc; }
+
+B200_API int64_t b200_pc_append(b200_paged_cache *pc, int32_t seq, int64_t n_new, int32_t *slot_mapping,
+                                int32_t *cow_pairs, int64_t cow_cap) {
+    if (cow_cap < 1 && n_new > 0) return -2;             // one append emits at most one pair
+    std::vector<int32_t> slots;
+    std::vector<std::pair<int32_t, int32_t>> cow;
+    if (!pc->impl.append(seq, n_new, slots, cow)) return -1;
+    for (size_t i = 0; i < slots.size(); ++i) slot_mapping[i] = slots[i];
+    for (size_t i = 0; i < cow.size(); ++i) { cow_pairs[2*i] = cow[i].first; cow_pairs[2*i + 1] = cow[i].second; }
+    return (int64_t) cow.size();
+}
+B200_API int32_t b200_pc_seq_cp(b200_paged_cache *pc, int32_t s, int32_t d, int64_t p0, int64_t p1) { return pc->impl.seq_cp(s, d, p0, p1) ? 1 : 0; }
+B200_API int32_t b200_pc_seq_rm(b200_paged_cache *pc, int32_t s, int64_t p0, int64_t p1) { return pc->impl.seq_rm(s, p0, p1) ? 1 : 0; }
+B200_API void    b200_pc_seq_keep(b200_paged_cache *pc, int32_t s) { pc->impl.seq_keep(s); }
+B200_API void    b200_pc_clear(b200_paged_cache *pc) { pc->impl.clear(); }
+B200_API int64_t b200_pc_seq_len(const b200_paged_cache *pc, int32_t s) { return pc->impl.seq_len(s); }
+B200_API int64_t b200_pc_n_free(const b200_paged_cache *pc) { return pc->impl.n_free(); }
+B200_API int32_t b200_pc_ref_count(const b200_paged_cache *pc, int64_t b) { return pc->impl.ref_count(b); }
+B200_API int32_t b200_pc_export(const b200_paged_cache *pc, const int32_t *seqs, int64_t n,
+                                int32_t *bt, int64_t stride, int32_t *lens) {
+    return pc->impl.export_tables(seqs, n, bt, stride, lens) ? 1 : 0;
+}
+
+} // extern "C"

@@ -1,0 +1,131 @@
+// paged_kv_cache.cpp — see src/paged_kv_cache.h
+#include "paged_kv_cache.h"
+
+#include <algorithm>
+
+PagedKVCache::PagedKVCache(int64_t n_blocks, int block_size)
+    : block_size_(block_size > 0 ? block_size : 1), ref_((size_t) (n_blocks > 0 ? n_blocks : 0), 0), n_free_(n_blocks > 0 ? n_blocks : 0) {
+    for (int32_t b = 0; b < (int32_t) ref_.size(); ++b) free_.push(b);
+}
+
+int PagedKVCache::ref_count(int64_t block) const {
+    return (block < 0 || block >= (int64_t) ref_.size()) ? -1 : ref_[(size_t) block];
+}
+
+int32_t PagedKVCache::alloc_block() {
+    if (free_.empty()) return -1;
+    const int32_t b = free_.top(); free_.pop();
+    ref_[(size_t) b] = 1; --n_free_;
+    return b;
+}
+
+void PagedKVCache::unref(int32_t b) {
+    if (--ref_[(size_t) b] == 0) { free_.push(b); ++n_free_; }
+}
+
+void PagedKVCache::release(Seq & s, int64_t keep_tokens) {
+    const int64_t keep_blocks = (keep_tokens + block_size_ - 1)/block_size_;
+    while ((int64_t) s.blocks.size() > keep_blocks) { unref(s.blocks.back()); s.blocks.pop_back(); }
+    s.len = std::min(s.len, keep_tokens);
+}
+
+bool PagedKVCache::append(seq_id seq, int64_t n_new, std::vector<int32_t> & slot_mapping,
+                          std::vector<std::pair<int32_t, int32_t>> & cow_pairs) {
+    if (n_new < 0) return false;
+    auto it = seqs_.find(seq);
+    const int64_t len = it == seqs_.end() ? 0 : it->second.len;
+    const int64_t have = it == seqs_.end() ? 0 : (int64_t) it->second.blocks.size();
+    const int64_t off  = len % block_size_;
+    const bool tail_shared = n_new > 0 && off != 0 && ref_[(size_t) it->second.blocks.back()] > 1;
+    const int64_t need_blocks = (len + n_new + block_size_ - 1)/block_size_ - have;
+    if (need_blocks + (tail_shared ? 1 : 0) > n_free_) return false;          // all-or-nothing
+    if (n_new == 0) { if (it == seqs_.end()) seqs_[seq]; return true; }
+    Seq & s = seqs_[seq];
+    if (tail_shared) {                                                         // copy-on-write
+        const int32_t old = s.blocks.back();
+        const int32_t nb  = alloc_block();
+        cow_pairs.emplace_back(old, nb);
+        s.blocks.back() = nb;
+        unref(old);
+    }
+    for (int64_t i = 0; i < need_blocks; ++i) s.blocks.push_back(alloc_block());
+    for (int64_t p = len; p < len + n_new; ++p)
+        slot_mapping.push_back((int32_t) ((int64_t) s.blocks[(size_t) (p/block_size_)]*block_size_ + p % block_size_));
+    s.len = len + n_new;
+    return true;
+}
+
+bool PagedKVCache::seq_cp(seq_id src, seq_id dst, int64_t p0, int64_t p1) {
+    if (p0 > 0) return false;
+    auto it = seqs_.find(src);
+    if (it == seqs_.end()) return false;
+    if (src == dst) return true;                                               // llama-kv-cache.cpp:245-247
+    const int64_t n = (p1 < 0 || p1 > it->second.len) ? it->second.len : p1;
+    const int64_t nb = (n + block_size_ - 1)/block_size_;
+    std::vector<int32_t> shared(it->second.blocks.begin(), it->second.blocks.begin() + nb);
+    for (int32_t b : shared) ++ref_[(size_t) b];
+    auto jt = seqs_.find(dst);
+    if (jt != seqs_.end()) release(jt->second, 0);
+    Seq & d = seqs_[dst];
+    d.blocks.swap(shared);
+    d.len = n;
+    return true;
+}
+
+bool PagedKVCache::seq_rm(seq_id seq, int64_t p0, int64_t p1) {
+    if (seq < 0) {
+        bool ok = true;
+        std::vector<seq_id> ids;
+        for (auto & kv : seqs_) ids.push_back(kv.first);
+        for (seq_id s : ids) ok = seq_rm(s, p0, p1) && ok;
+        return ok;
+    }
+    auto it = seqs_.find(seq);
+    if (it == seqs_.end()) return true;
+    if (p0 < 0) p0 = 0;
+    const int64_t len = it->second.len;
+    if (p1 >= 0 && p1 < len) return p0 >= p1;                                  // middle range: only the empty one
+    release(it->second, std::min(p0, len));
+    if (it->second.len == 0) seqs_.erase(it);
+    return true;
+}
+
+void PagedKVCache::seq_keep(seq_id seq) {
+    std::vector<seq_id> ids;
+    for (auto & kv : seqs_) if (kv.first != seq) ids.push_back(kv.first);
+    for (seq_id s : ids) seq_rm(s, 0, -1);
+}
+
+void PagedKVCache::clear() {
+    seqs_.clear();
+    std::fill(ref_.begin(), ref_.end(), 0);
+    free_ = decltype(free_)();
+    for (int32_t b = 0; b < (int32_t) ref_.size(); ++b) free_.push(b);
+    n_free_ = (int64_t) ref_.size();
+}
+
+int64_t PagedKVCache::seq_len(seq_id seq) const {
+    auto it = seqs_.find(seq);
+    return it == seqs_.end() ? 0 : it->second.len;
+}
+
+const std::vector<int32_t> * PagedKVCache::blocks_of(seq_id seq) const {
+    auto it = seqs_.find(seq);
+    return it == seqs_.end() ? nullptr : &it->second.blocks;
+}
+
+bool PagedKVCache::export_tables(const seq_id * seqs, int64_t n, int32_t * block_table, int64_t stride, int32_t * seq_lens) const {
+    for (int64_t i = 0; i < n; ++i) {
+        auto it = seqs_.find(seqs[i]);
+        int32_t * row = block_table + i*stride;
+        int64_t nb = 0;
+        if (it != seqs_.end()) {
+            nb = (int64_t) it->second.blocks.size();
+            if (nb > stride) return false;
+            std::copy(it->second.blocks.begin(), it->second.blocks.end(), row);
+        }
+        std::fill(row + nb, row + stride, 0);
+        if (seq_lens) seq_lens[i] = it == seqs_.end() ? 0 : (int32_t) it->second.len;
+    }
+    return true;
+}

@@ -1,0 +1,67 @@
+// paged_kv_cache.h — token-granular block manager for the device-resident paged KV cache.
+//
+// This is the bookkeeping half of the reference's llama_kv_cache_unified (src/llama-kv-cache.h:63-178:
+// find_slot .cpp:453-672, seq_cp :244-293, seq_rm :173-242, seq_keep :295-325, clear) re-expressed over
+// fixed-size blocks in the fork's vocabulary (BlockManager first-fit allocation), extended
+// with what north_star asks for and the reference lacks: per-sequence block tables, reference counts and
+// copy-on-write.  The reference shares prefix cells by inserting the new seq_id into each cell's set
+// (seq_cp is metadata-only); here seq_cp shares whole blocks by bumping ref-counts, and the first append
+// into a shared, partially filled tail block emits a (src,dst) copy pair for b200_block_copy.
+//
+// Cell numbering is the flat llama.cpp cache's: cell = block*block_size + offset, so slot_mapping entries
+// index the same k_l/v_l tensors (src/llama-kv-cache.cpp:100-101) the ggml views address.
+#pragma once
+#include <cstdint>
+#include <map>
+#include <queue>
+#include <utility>
+#include <vector>
+
+class PagedKVCache {
+public:
+    typedef int32_t seq_id;
+
+    PagedKVCache(int64_t n_blocks, int block_size);
+
+    int     block_size() const { return block_size_; }
+    int64_t n_blocks()   const { return (int64_t) ref_.size(); }
+    int64_t n_free()     const { return n_free_; }
+    int     ref_count(int64_t block) const;
+
+    // Reserve room for n_new tokens at the end of `seq` (created if absent).  Appends n_new cell indices to
+    // slot_mapping and any copy-on-write (src_block, dst_block) pairs to cow_pairs.  All-or-nothing: on
+    // exhaustion nothing changes and false is returned (llama_decode's "no KV slot", src/llama-context.cpp:1302).
+    bool append(seq_id seq, int64_t n_new, std::vector<int32_t> & slot_mapping,
+                std::vector<std::pair<int32_t, int32_t>> & cow_pairs);
+
+    // llama_kv_self_seq_cp semantics restricted to prefixes (p0 <= 0): dst becomes positions [0, p1) of src,
+    // sharing blocks.  p1 < 0 means "to the end".  Returns false for p0 > 0 or unknown src.
+    bool seq_cp(seq_id src, seq_id dst, int64_t p0, int64_t p1);
+    // llama_kv_self_seq_rm: whole sequence (p0 <= 0, p1 < 0 or >= len) or tail truncation (p1 < 0 or >= len);
+    // removing a middle range returns false like the recurrent cache does.  seq < 0 matches every sequence.
+    bool seq_rm(seq_id seq, int64_t p0, int64_t p1);
+    void seq_keep(seq_id seq);
+    void clear();
+
+    bool    has_seq(seq_id seq) const { return seqs_.count(seq) != 0; }
+    int64_t seq_len(seq_id seq) const;                 // tokens cached (seq_pos_max + 1), 0 if absent
+    int64_t n_seqs() const { return (int64_t) seqs_.size(); }
+    const std::vector<int32_t> * blocks_of(seq_id seq) const;
+
+    // Export rows of the device block table / seq_lens for the given sequences (row i <-> seqs[i]);
+    // unused entries are filled with 0 (a valid block, never dereferenced past seq_len).
+    // Returns false if a row would not fit in `stride` entries.
+    bool export_tables(const seq_id * seqs, int64_t n, int32_t * block_table, int64_t stride, int32_t * seq_lens) const;
+
+private:
+    struct Seq { std::vector<int32_t> blocks; int64_t len = 0; };
+    int32_t alloc_block();                  // lowest free index (BlockManager::allocateBlock policy), -1 if none
+    void    unref(int32_t b);
+    void    release(Seq & s, int64_t keep_tokens);
+
+    int                  block_size_;
+    std::vector<int32_t> ref_;
+    std::priority_queue<int32_t, std::vector<int32_t>, std::greater<int32_t>> free_;
+    int64_t              n_free_;
+    std::map<seq_id, Seq> seqs_;
+};
