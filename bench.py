@@ -1,0 +1,315 @@
+#!/usr/bin/env python
+"""bench.py — paged-attn decode KV-read GB/s (BASELINE.json metric) on BASELINE config 2.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--kv-type q8_0|q4_0|f16] [--impl b200|reference]
+
+Workload ("config2_llama3_8b_<type>"): Llama-3-8B attention shape (32 q / 8 kv heads, d = 128, 32 layers), 64
+sequences with context lengths ~ U{512..8192} (seed 7 + rank), 16-token blocks scattered by a random
+permutation, Q8_0 (default) / Q4_0 / F16 KV cache, synthetic U(-1,1) data.  One STEP = one decode step of the
+hot path = the attention op of all 32 layers, each over its own KV cache (19 GB of Q8_0 KV per GPU, far
+beyond the 126 MB L2, so no flush is needed between iterations).
+
+  value       whole-job KV GB/s with everything resident in HBM (CUDA-graph replay of the 32 layer ops)
+  e2e         same metric through the C ABI the way a host uses it per step: pinned-host Q / new K,V rows /
+              block table / seq_lens copied H2D, b200_kv_write + b200_paged_attention per layer, outputs D2H
+  roofline    op-level achieved GB/s = algorithmic KV bytes / CUDA-event time, vs MEASURED_PEAKS.json
+  cpu_baseline the reference's own ggml CPU FLASH_ATTN_EXT (oracle/_ref) on one layer-op of the same workload
+
+Multi-GPU (torchrun, one rank per GPU): sequences shard across ranks with no data-path collective
+(SURVEY.md §8e partitioning A), each rank runs the same per-GPU workload => "scaling": "weak"; time is the
+max over ranks of the CUDA-event time.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+TYPES = {"f16": 1, "q4_0": 2, "q8_0": 8}
+N_HEAD, N_HEAD_KV, D, BS, N_LAYER, N_SEQS = 32, 8, 128, 16, 32, 64
+
+
+def row_bytes(t, n):
+    return {1: n * 2, 8: n // 32 * 34, 2: n // 32 * 18}[t]
+
+
+def ctx_lens(rank):
+    return np.random.default_rng(7 + rank).integers(512, 8193, size=N_SEQS).astype(np.int32)
+
+
+def block_tables(lens, seed=42):
+    nb = (lens.astype(np.int64) + BS - 1) // BS
+    ids = np.random.default_rng(seed).permutation(int(nb.sum())).astype(np.int32)
+    bt = np.zeros((len(lens), int(nb.max())), dtype=np.int32)
+    slot = np.empty(int(lens.sum()), dtype=np.int32)
+    o = ob = 0
+    for s, n in enumerate(lens):
+        n = int(n); b = int(nb[s])
+        bt[s, :b] = ids[ob:ob + b]; ob += b
+        p = np.arange(n); slot[o:o + n] = bt[s, p // BS] * BS + p % BS; o += n
+    return bt, slot, int(nb.sum())
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)"""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        self.stop_flag = True
+        sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows for i in range(4) if len(r) >= 6 and r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def reference_arm(args, rank, world):
+    """the reference's own CPU implementation of the path (oracle/_ref: ggml FLASH_ATTN_EXT on the flat cache with
+    the dense F16 mask, SURVEY.md §8d "CPU baseline timing"), all host threads, one layer-op per step"""
+    if rank != 0:
+        return
+    from oracle.loader import Oracle, Ref
+    t = TYPES[args.kv_type]
+    sample, value, cores, kind, ms = cpu_layer_op(t, args.steps, args.warmup)
+    line = {"impl": "reference", "metric": "paged-attn decode KV-read GB/s", "value": value, "unit": "GB/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": args.kv_type, "data": "synthetic",
+            "config": {"workload": f"config2_llama3_8b_{args.kv_type}", "n_seqs": N_SEQS, "ctx": "U{512..8192} seed 7",
+                       "block_size": BS, "n_head": N_HEAD, "n_head_kv": N_HEAD_KV, "head_dim": D},
+            "cpu_baseline": {"value": value, "unit": "GB/s", "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": value, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def cpu_layer_op(t, steps, warmup):
+    """time one layer-op of the rank-0 workload on the host cores; returns (sample, GB/s, cores, kind, ms)"""
+    from oracle.loader import Oracle, Ref
+    from workloads import make_workload
+    orc, ref = Oracle(), Ref.load()
+    lens = ctx_lens(0)
+    w = make_workload(orc, lens, N_HEAD, N_HEAD_KV, D, t, seed=1234, spare_blocks=0)
+    kv_bytes = w.kv_bytes()
+    if ref is not None:
+        mask = w.dense_mask()
+        n_iter = max(1, warmup + steps)
+        _, us = ref.attention(0, w.q, w.k_cache, w.v_cache, t, t, N_HEAD_KV, w.n_cells, mask, w.scale, n_iter=n_iter)
+        kind, cores = "reference", ref.n_threads
+        sample = (f"one layer-op of the full workload (1/{N_LAYER} of a step): ggml CPU GGML_OP_FLASH_ATTN_EXT, flat cache "
+                  f"of {w.n_cells} cells + dense F16 mask, {cores} threads, isa {ref.isa}, best of {n_iter}")
+    else:
+        t0 = time.perf_counter()
+        rows = np.argsort(lens)[:4]
+        orc.attention(w.q[rows], w.k_cache, w.v_cache, t, t, N_HEAD_KV, w.scale, block_table=w.block_table[rows],
+                      seq_lens=lens[rows], block_size=BS)
+        us = (time.perf_counter() - t0) * 1e6
+        kv_bytes = int(lens[rows].sum()) * N_HEAD_KV * 2 * row_bytes(t, D)
+        kind, cores = "port", 1
+        sample = "oracle port (scalar C), the 4 shortest sequences of one layer-op"
+    return sample, kv_bytes / us / 1e3, cores, kind, us / 1e3
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--kv-type", default="q8_0", choices=list(TYPES))
+    ap.add_argument("--kernel", type=int, default=0, help="0 auto, 1 generic, 2 stream-K")
+    ap.add_argument("--layers", type=int, default=N_LAYER)
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        return reference_arm(args, rank, world)
+    args.warmup = max(args.warmup, 3)
+
+    import torch
+    import torch.distributed as dist
+    from __graft_entry__ import load
+    pkg = load()
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    t = TYPES[args.kv_type]
+    n_layer = args.layers
+    lens = ctx_lens(rank)
+    bt_h, slot_h, n_blocks = block_tables(lens)
+    total = int(lens.sum())
+    lay = pkg.KVLayout(t, N_HEAD_KV, D, BS, n_blocks + 8)
+    kv_bytes_op = total * N_HEAD_KV * 2 * row_bytes(t, D)
+    scale = float(1.0 / np.sqrt(D))
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+    # ---- resident state: per-layer KV caches filled through the product's own kv_write kernel
+    gen = torch.Generator(device="cuda"); gen.manual_seed(1234 + rank)
+    slot_d, bt_d, sl_d = dev(slot_h), dev(bt_h), dev(lens)
+    kcs, vcs = [], []
+    for _ in range(n_layer):
+        kc, vc = lay.alloc(), lay.alloc()
+        ks = torch.rand((total, N_HEAD_KV * D), generator=gen, device="cuda") * 2 - 1
+        vs = torch.rand((total, N_HEAD_KV * D), generator=gen, device="cuda") * 2 - 1
+        pkg.kv_write(ks, vs, slot_d, kc, vc, lay)
+        kcs.append(kc); vcs.append(vc)
+    del ks, vs
+    q_d = torch.rand((n_layer, N_SEQS, N_HEAD, D), generator=gen, device="cuda") * 2 - 1
+    out_d = torch.empty_like(q_d)
+    calls = [pkg.AttnCall(q_d[l], kcs[l], vcs[l], lay, out_d[l], scale, block_table=bt_d, seq_lens=sl_d,
+                          max_seq_len=int(lens.max()), total_tokens=total, kernel=args.kernel) for l in range(n_layer)]
+    torch.cuda.synchronize()
+
+    def step_resident():
+        for c in calls:
+            c.run()
+
+    l0 = pkg.lib.b200_launch_count(); step_resident(); launches_per_step = pkg.lib.b200_launch_count() - l0
+    graph = None
+    if not args.no_graph:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            step_resident()
+        torch.cuda.current_stream().wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            step_resident()
+    run_step = graph.replay if graph is not None else step_resident
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    sampler = ClockSampler(local); sampler.start()
+    ms_total = timed(run_step, args.steps, args.warmup)
+    clocks = sampler.summary()
+    ms_step = ms_total / args.steps
+    bytes_step_rank = kv_bytes_op * n_layer
+    # every rank holds the same amount of work (weak scaling); whole-job bytes = sum over ranks
+    tot = torch.tensor([float(bytes_step_rank), float(N_SEQS)], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tot)
+    value = tot[0].item() / (ms_step * 1e-3) / 1e9
+    tok_s = tot[1].item() / (ms_step * 1e-3)
+
+    # ---- end to end through the C ABI with HOST buffers (per step: H2D inputs, kv_write + attention, D2H outputs)
+    q_h = torch.rand((n_layer, N_SEQS, N_HEAD, D)).pin_memory()
+    knew_h = (torch.rand((n_layer, N_SEQS, N_HEAD_KV * D)) * 2 - 1).pin_memory()
+    vnew_h = (torch.rand((n_layer, N_SEQS, N_HEAD_KV * D)) * 2 - 1).pin_memory()
+    bt_hp, sl_hp = torch.from_numpy(bt_h).pin_memory(), torch.from_numpy(lens).pin_memory()
+    # the step's new token of each sequence overwrites its last cached position (cache stays the same size)
+    last = np.cumsum(lens.astype(np.int64)) - 1
+    slot_new_h = torch.from_numpy(slot_h[last].copy()).pin_memory()
+    out_h = torch.empty((n_layer, N_SEQS, N_HEAD, D)).pin_memory()
+    knew_d, vnew_d = torch.empty_like(knew_h, device="cuda"), torch.empty_like(vnew_h, device="cuda")
+    slot_new_d = torch.empty_like(slot_new_h, device="cuda")
+    h2d = q_h.numel() * 4 + knew_h.numel() * 4 + vnew_h.numel() * 4 + bt_hp.numel() * 4 + sl_hp.numel() * 4 + slot_new_h.numel() * 4
+    d2h = out_h.numel() * 4
+
+    def step_e2e():
+        q_d.copy_(q_h, non_blocking=True); knew_d.copy_(knew_h, non_blocking=True); vnew_d.copy_(vnew_h, non_blocking=True)
+        bt_d.copy_(bt_hp, non_blocking=True); sl_d.copy_(sl_hp, non_blocking=True); slot_new_d.copy_(slot_new_h, non_blocking=True)
+        for l in range(n_layer):
+            pkg.kv_write(knew_d[l], vnew_d[l], slot_new_d, kcs[l], vcs[l], lay)
+            calls[l].run()
+        out_h.copy_(out_d, non_blocking=True)
+        torch.cuda.current_stream().synchronize()      # the host reads the step's result
+
+    e2e_steps = max(3, args.steps // 2)
+    ms_e2e = timed(step_e2e, e2e_steps, 3) / e2e_steps
+    e2e_value = tot[0].item() / (ms_e2e * 1e-3) / 1e9
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        achieved = kv_bytes_op / (ms_step / n_layer * 1e-3) / 1e9         # per-GPU, per op
+        which = "stream-K" if (args.kernel != 1 and _uses_streamk(pkg, calls[0])) else "generic"
+        line = {
+            "metric": "paged-attn decode KV-read GB/s", "value": round(value, 2), "unit": "GB/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": args.kv_type, "data": "synthetic",
+            "config": {"workload": f"config2_llama3_8b_{args.kv_type}", "n_seqs_per_gpu": N_SEQS, "ctx": "U{512..8192} seed 7+rank",
+                       "block_size": BS, "n_head": N_HEAD, "n_head_kv": N_HEAD_KV, "head_dim": D, "n_layer": n_layer,
+                       "kv_bytes_per_step_per_gpu": bytes_step_rank, "l2_flush": "inputs (per-layer KV caches, "
+                       f"{bytes_step_rank / 1e9:.1f} GB per step) are far larger than the 126 MB L2", "cuda_graph": graph is not None,
+                       "kernel": which, "parallelism": f"sequence-batch sharding x{world}, no collective"},
+            "decode_tok_s": round(tok_s, 1), "pct_hbm_nominal_8TBs": round(100 * achieved / 8000.0, 2),
+            "gpu_launches": int(launches_per_step * args.steps),
+            "e2e": {"value": round(e2e_value, 2), "unit": "GB/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "ms_per_step": round(ms_e2e, 4)},
+            "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+                         "traffic": None, "peak_source": peak_src, "kernel": f"paged attention op ({which}), one layer",
+                         "algorithmic_bytes_per_launch": kv_bytes_op},
+            "clocks": clocks,
+        }
+        if not args.no_cpu_baseline:
+            sample, v, cores, kind, _ = cpu_layer_op(t, 3, 1)
+            line["cpu_baseline"] = {"value": round(v, 3), "unit": "GB/s", "cores": cores, "kind": kind, "sample": sample}
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def _uses_streamk(pkg, call):
+    import ctypes as C
+    d = pkg.AttnDesc.from_buffer_copy(call.desc)
+    d.kernel = pkg.KERNEL_STREAMK
+    return bool(pkg.lib.b200_supports_attention(C.byref(d)))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,317 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI, against the CPU oracle on the same
+seeded inputs.  Bars (north_star): KV write / block copy / block tables bit-exact; attention max relative
+error <= 2e-3 for F16 KV and <= 1e-2 for Q8_0/Q4_0 against the F32 CPU result, where the relative error
+of an element is |out-ref| / max(|ref|, rms(ref row)) (oracle.max_rel_err); NMSE <= 5e-4 is the
+reference's own bar (tests/test-backend-ops.cpp:3216-3218)."""
+import numpy as np
+import pytest
+
+from workloads import F16, F32, Q4_0, Q8_0, make_workload, mixed_ctx, oracle_attention, row_bytes
+
+pytestmark = pytest.mark.gpu
+
+TOL = {F32: 2e-3, F16: 2e-3, Q8_0: 1e-2, Q4_0: 1e-2}
+TYPES = [F16, Q8_0, Q4_0]
+
+
+def _dev(torch, a, dtype=None):
+    t = torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    return t if dtype is None else t.to(dtype)
+
+
+def _run_paged(pkg, torch, w, kernel=0, hints=True):
+    lay_k = pkg.KVLayout(w.type_k, w.n_head_kv, w.d, w.block_size, w.n_blocks)
+    lay_v = pkg.KVLayout(w.type_v, w.n_head_kv, w.d, w.block_size, w.n_blocks)
+    q = _dev(torch, w.q)
+    kc, vc = _dev(torch, w.k_cache.reshape(-1)), _dev(torch, w.v_cache.reshape(-1))
+    bt, sl = _dev(torch, w.block_table), _dev(torch, w.seq_lens)
+    qs = None if w.q_seq is None else _dev(torch, w.q_seq)
+    qp = None if w.q_pos is None else _dev(torch, w.q_pos)
+    out = torch.full_like(q, float("nan"))
+    call = pkg.AttnCall(q, kc, vc, lay_k, out, w.scale, layout_v=lay_v, block_table=bt, seq_lens=sl, q_seq=qs, q_pos=qp,
+                        max_seq_len=int(w.seq_lens.max()) if hints else 0,
+                        total_tokens=int(w.seq_lens.sum()) if hints else 0, kernel=kernel)
+    if not call.supported():
+        pytest.skip("kernel does not take this shape")
+    before = pkg.lib.b200_launch_count()
+    call.run()
+    torch.cuda.synchronize()
+    assert pkg.lib.b200_launch_count() > before, "no CUDA kernel was launched"
+    return out.cpu().numpy()
+
+
+# ---------------------------------------------------------------- KV write / block copy: bit-exact
+
+@pytest.mark.parametrize("t", [F32, F16, Q8_0, Q4_0])
+@pytest.mark.parametrize("shape", [(8, 128), (2, 64), (1, 32)])
+def test_kv_write_bit_exact(pkg, oracle, cuda, t, shape):
+    import torch
+    n_head_kv, d = shape
+    rng = np.random.default_rng(100 + t)
+    n_tokens, n_cells = 300, 512
+    src_k = rng.uniform(-1, 1, (n_tokens, n_head_kv * d)).astype(np.float32)
+    src_v = rng.standard_normal((n_tokens, n_head_kv * d)).astype(np.float32) * 3
+    src_k[0, :32] = 0.0
+    src_k[1, :32] = -0.75
+    src_k[2, :32] = np.linspace(-1, 1, 32); src_k[2, 31] = -1.0
+    src_k[3, 5] = 6.0e4
+    slot = rng.permutation(n_cells)[:n_tokens].astype(np.int32)
+    slot[7] = -1                      # skipped (writeToCache ignores invalid slots)
+    slot[9] = n_cells + 3             # out of range: skipped
+    lay = pkg.KVLayout(t, n_head_kv, d, 16, n_cells // 16)
+    kc = torch.full((lay.total_bytes,), 0x5a, dtype=torch.uint8, device=cuda)
+    vc = torch.full((lay.total_bytes,), 0x5a, dtype=torch.uint8, device=cuda)
+    pkg.kv_write(_dev(torch, src_k), _dev(torch, src_v), _dev(torch, slot), kc, vc, lay)
+    torch.cuda.synchronize()
+    for src, dev in ((src_k, kc), (src_v, vc)):
+        want = np.full((n_cells, lay.token_bytes), 0x5a, dtype=np.uint8)
+        oracle.kv_write(src, slot, want, t, n_head_kv, d, lay.token_bytes, lay.head_bytes, n_cells)
+        got = dev.cpu().numpy().reshape(n_cells, lay.token_bytes)
+        assert np.array_equal(got, want), f"{int((got != want).sum())} bytes differ"
+
+
+def test_kv_write_mixed_types_and_strided_heads(pkg, oracle, cuda):
+    """type_k != type_v (-ctk q8_0 -ctv f16) and a head stride wider than the row (generic store path)"""
+    import torch
+    n_head_kv, d, n_tokens, n_cells = 4, 128, 40, 64
+    rng = np.random.default_rng(5)
+    src = rng.uniform(-1, 1, (n_tokens, n_head_kv * d)).astype(np.float32)
+    slot = rng.permutation(n_cells)[:n_tokens].astype(np.int32)
+    d_ = pkg.KVWriteDesc()
+    nbh_k, nbh_v = row_bytes(Q8_0, d) + 6, row_bytes(F16, d)
+    nbt_k, nbt_v = nbh_k * n_head_kv + 10, nbh_v * n_head_kv
+    kc = torch.zeros(n_cells * nbt_k, dtype=torch.uint8, device=cuda)
+    vc = torch.zeros(n_cells * nbt_v, dtype=torch.uint8, device=cuda)
+    s, sm = _dev(torch, src), _dev(torch, slot)
+    d_.k_src = d_.v_src = s.data_ptr(); d_.src_nb1 = src.strides[0]; d_.n_tokens = n_tokens
+    d_.slot_mapping = sm.data_ptr(); d_.k_cache, d_.v_cache = kc.data_ptr(), vc.data_ptr()
+    d_.type_k, d_.type_v, d_.n_head_kv, d_.head_dim = Q8_0, F16, n_head_kv, d
+    d_.nbk_token, d_.nbk_head, d_.nbv_token, d_.nbv_head, d_.n_cells = nbt_k, nbh_k, nbt_v, nbh_v, n_cells
+    import ctypes as C
+    pkg.check(pkg.lib.b200_kv_write(C.byref(d_), C.c_void_p(pkg.current_stream())), "kv_write")
+    torch.cuda.synchronize()
+    wk = np.zeros(n_cells * nbt_k, dtype=np.uint8); wv = np.zeros(n_cells * nbt_v, dtype=np.uint8)
+    oracle.kv_write(src, slot, wk, Q8_0, n_head_kv, d, nbt_k, nbh_k, n_cells)
+    oracle.kv_write(src, slot, wv, F16, n_head_kv, d, nbt_v, nbh_v, n_cells)
+    assert np.array_equal(kc.cpu().numpy(), wk) and np.array_equal(vc.cpu().numpy(), wv)
+
+
+@pytest.mark.parametrize("t", TYPES)
+def test_block_copy_bit_exact(pkg, oracle, cuda, t):
+    import torch
+    lay = pkg.KVLayout(t, 8, 128, 16, 40)
+    rng = np.random.default_rng(t)
+    caches = [rng.integers(0, 256, lay.total_bytes, dtype=np.uint8) for _ in range(5)]
+    pairs = np.array([[3, 20], [4, 21], [39, 0], [7, 7], [11, 30]], dtype=np.int32)
+    dev = [_dev(torch, c) for c in caches]
+    pkg.block_copy(dev, lay.block_bytes, lay.n_blocks, _dev(torch, pairs))
+    torch.cuda.synchronize()
+    for c, d in zip(caches, dev):
+        want = c.copy()
+        oracle.block_copy(want, lay.block_bytes, lay.n_blocks, pairs)
+        assert np.array_equal(d.cpu().numpy(), want)
+
+
+# ---------------------------------------------------------------- attention vs the F32 CPU result
+
+DECODE_CASES = [
+    # seq_lens, n_head, n_head_kv, d
+    ([1, 15, 16, 17, 100, 333], 32, 8, 128),        # ragged, block-edge lengths
+    ([1024] * 8, 32, 8, 128),                        # BASELINE config 1 shape
+    ([700, 64, 2049], 64, 8, 128),                   # 70B GQA ratio 8
+    ([129, 40], 8, 8, 128),                          # MHA (ratio 1): CUDA-core single-query path
+    ([77, 300], 12, 4, 64),                          # d = 64, ratio 3
+]
+
+
+@pytest.mark.parametrize("kernel", [1, 2], ids=["generic", "streamk"])
+@pytest.mark.parametrize("t", TYPES)
+@pytest.mark.parametrize("case", DECODE_CASES, ids=lambda c: f"{len(c[0])}x{max(c[0])}_h{c[1]}_{c[2]}_d{c[3]}")
+def test_paged_decode(pkg, oracle, cuda, case, t, kernel):
+    import torch
+    seq_lens, n_head, n_head_kv, d = case
+    w = make_workload(oracle, seq_lens, n_head, n_head_kv, d, t, seed=1234 + t)
+    got = _run_paged(pkg, torch, w, kernel)
+    want = oracle_attention(oracle, w)
+    assert not np.isnan(got).any()
+    err, nm = oracle.max_rel_err(want, got), oracle.nmse(want, got)
+    assert err <= TOL[t], f"max rel err {err:.3e} (nmse {nm:.3e})"
+    assert nm <= 5e-4
+
+
+@pytest.mark.parametrize("kernel", [1, 2], ids=["generic", "streamk"])
+@pytest.mark.parametrize("dist", ["uniform", "normal"])
+def test_paged_decode_mixed_types_and_normal_inputs(pkg, oracle, cuda, dist, kernel):
+    import torch
+    w = make_workload(oracle, [513, 90, 1200], 32, 8, 128, Q8_0, F16, seed=77, dist=dist)
+    got = _run_paged(pkg, torch, w, kernel)
+    want = oracle_attention(oracle, w)
+    assert oracle.max_rel_err(want, got) <= 1e-2
+
+
+@pytest.mark.parametrize("kernel", [1, 2], ids=["generic", "streamk"])
+@pytest.mark.parametrize("t", TYPES)
+def test_chunked_prefill_rows(pkg, oracle, cuda, t, kernel):
+    """multi-token rows: each query sees positions <= its own (causal through q_pos), two sequences interleaved"""
+    import torch
+    seq_lens = [90, 41]
+    rows = [(0, p) for p in range(58, 90)] + [(1, p) for p in range(30, 41)] + [(0, 0), (1, 0)]
+    w = make_workload(oracle, seq_lens, 8, 2, 128, t, seed=9, q_rows=rows)
+    got = _run_paged(pkg, torch, w, kernel)
+    want = oracle_attention(oracle, w)
+    assert oracle.max_rel_err(want, got) <= TOL[t]
+
+
+def test_without_host_hints(pkg, oracle, cuda):
+    """max_seq_len / total_tokens are only scheduling hints: results must not depend on them"""
+    import torch
+    w = make_workload(oracle, [300, 5, 1000], 32, 8, 128, Q4_0, seed=3)
+    a = _run_paged(pkg, torch, w, 0, hints=True)
+    b = _run_paged(pkg, torch, w, 0, hints=False)
+    want = oracle_attention(oracle, w)
+    assert oracle.max_rel_err(want, a) <= 1e-2 and oracle.max_rel_err(want, b) <= 1e-2
+
+
+@pytest.mark.parametrize("t", TYPES)
+def test_dense_mask_mode_matches_reference_semantics(pkg, oracle, cuda, t):
+    """block_table == NULL: flat cache + F16 mask, finite mask values added, -inf cells skipped"""
+    import torch
+    rng = np.random.default_rng(21)
+    n_q, n_head, n_head_kv, d, n_kv = 5, 16, 4, 128, 512
+    q = rng.uniform(-1, 1, (n_q, n_head, d)).astype(np.float32)
+    kf = rng.uniform(-1, 1, (n_kv * n_head_kv, d)).astype(np.float32)
+    vf = rng.uniform(-1, 1, (n_kv * n_head_kv, d)).astype(np.float32)
+    k = oracle.from_float(t, kf).reshape(-1); v = oracle.from_float(t, vf).reshape(-1)
+    mask = rng.uniform(-1, 1, (64, n_kv)).astype(np.float16)
+    mask[:, 400:] = -np.inf
+    mask[2, 10:200] = -np.inf
+    lay = pkg.KVLayout(t, n_head_kv, d, 16, n_kv // 16)
+    for softcap in (0.0, 10.0):
+        got = pkg.dense_attention(_dev(torch, q), _dev(torch, k), _dev(torch, v), lay, n_kv, _dev(torch, mask), 0.0884,
+                                  softcap=softcap).cpu().numpy()
+        want = oracle.attention(q, k, v, t, t, n_head_kv, 0.0884, mask=mask, n_kv=n_kv, softcap=softcap)
+        assert oracle.max_rel_err(want, got) <= TOL[t]
+
+
+def test_dense_alibi(pkg, oracle, cuda):
+    import torch
+    rng = np.random.default_rng(22)
+    n_q, n_head, n_head_kv, d, n_kv = 3, 8, 8, 128, 256
+    q = rng.uniform(-1, 1, (n_q, n_head, d)).astype(np.float32)
+    k = oracle.from_float(F16, rng.uniform(-1, 1, (n_kv * n_head_kv, d)).astype(np.float32)).reshape(-1)
+    v = oracle.from_float(F16, rng.uniform(-1, 1, (n_kv * n_head_kv, d)).astype(np.float32)).reshape(-1)
+    mask = rng.uniform(-1, 1, (64, n_kv)).astype(np.float16)
+    lay = pkg.KVLayout(F16, n_head_kv, d, 16, n_kv // 16)
+    got = pkg.dense_attention(_dev(torch, q), _dev(torch, k), _dev(torch, v), lay, n_kv, _dev(torch, mask), 0.0884,
+                              max_bias=8.0).cpu().numpy()
+    want = oracle.attention(q, k, v, F16, F16, n_head_kv, 0.0884, mask=mask, n_kv=n_kv, max_bias=8.0)
+    assert oracle.max_rel_err(want, got) <= 2e-3
+
+
+# ---------------------------------------------------------------- end to end: write -> fork/CoW -> attend
+
+@pytest.mark.parametrize("t", TYPES)
+def test_write_fork_cow_attend(pkg, oracle, cuda, t):
+    """config 3 in miniature: chunked prefill into the paged cache through PagedKVCache + b200_kv_write, fork a
+    shared prefix at a non-block-aligned point, append to both branches (copy-on-write through b200_block_copy),
+    attend; cache bytes must equal the oracle's replay bit for bit and outputs meet the tolerance."""
+    import torch
+    n_head, n_head_kv, d, bs, n_blocks = 8, 2, 128, 16, 64
+    lay = pkg.KVLayout(t, n_head_kv, d, bs, n_blocks)
+    pc = pkg.PagedKVCache(n_blocks, bs)
+    rng = np.random.default_rng(31)
+    kc, vc = lay.alloc(), lay.alloc()
+    hk = np.zeros((lay.n_cells, lay.token_bytes), dtype=np.uint8); hv = hk.copy()
+
+    def write(seq, n):
+        slots, cow = pc.append(seq, n)
+        if cow:
+            pairs = np.asarray(cow, dtype=np.int32)
+            pkg.block_copy([kc, vc], lay.block_bytes, n_blocks, _dev(torch, pairs))
+            oracle.block_copy(hk, lay.block_bytes, n_blocks, pairs); oracle.block_copy(hv, lay.block_bytes, n_blocks, pairs)
+        ks = rng.uniform(-1, 1, (n, n_head_kv * d)).astype(np.float32)
+        vs = rng.uniform(-1, 1, (n, n_head_kv * d)).astype(np.float32)
+        sm = np.asarray(slots, dtype=np.int32)
+        pkg.kv_write(_dev(torch, ks), _dev(torch, vs), _dev(torch, sm), kc, vc, lay)
+        oracle.kv_write(ks, sm, hk, t, n_head_kv, d, lay.token_bytes, lay.head_bytes, lay.n_cells)
+        oracle.kv_write(vs, sm, hv, t, n_head_kv, d, lay.token_bytes, lay.head_bytes, lay.n_cells)
+        return cow
+
+    for chunk in (32, 32, 36):                       # 100-token prompt in chunks
+        assert write(0, chunk) == []
+    assert pc.seq_cp(0, 1, 0, 90)                    # fork at token 90: block 5 (tokens 80..95) is shared, partly
+    assert pc.ref_count(pc.export([0], 8)[0][0][5]) == 2
+    cow1 = write(1, 7)                               # branch appends -> copy-on-write of the shared tail block
+    assert len(cow1) == 1
+    cow0 = write(0, 3)                               # parent's tail block (block 6) was never shared
+    assert cow0 == []
+    torch.cuda.synchronize()
+    assert np.array_equal(kc.cpu().numpy().reshape(hk.shape), hk)
+    assert np.array_equal(vc.cpu().numpy().reshape(hv.shape), hv)
+    (bt, lens) = pc.export([0, 1], 8)
+    assert lens == [103, 97]
+    q = rng.uniform(-1, 1, (2, n_head, d)).astype(np.float32)
+    btn, sln = np.asarray(bt, dtype=np.int32), np.asarray(lens, dtype=np.int32)
+    got = pkg.paged_attention(_dev(torch, q), kc, vc, lay, _dev(torch, btn), _dev(torch, sln), 0.0884).cpu().numpy()
+    want = oracle.attention(q, hk, hv, t, t, n_head_kv, 0.0884, block_table=btn, seq_lens=sln, block_size=bs)
+    assert oracle.max_rel_err(want, got) <= TOL[t]
+
+
+# ---------------------------------------------------------------- full-size properties (no oracle needed)
+
+@pytest.mark.parametrize("t", [Q8_0, Q4_0])
+def test_full_size_properties_config2(pkg, oracle, cuda, t):
+    """BASELINE config 2 at full size (64 seqs x U{512..8192}): (a) output is invariant under a re-permutation
+    of physical blocks, (b) the two kernels agree, (c) sampled rows meet the oracle tolerance,
+    (d) V == const gives exactly that const (softmax weights sum to 1)."""
+    import torch
+    lens = mixed_ctx()
+    n_head, n_head_kv, d, bs = 32, 8, 128, 16
+    rng = np.random.default_rng(8)
+    total = int(lens.sum())
+    nb = int(((lens + bs - 1) // bs).sum())
+    lay = pkg.KVLayout(t, n_head_kv, d, bs, nb)
+    kc, vc = lay.alloc(), lay.alloc()
+
+    def build(perm_seed):
+        ids = np.random.default_rng(perm_seed).permutation(nb).astype(np.int32)
+        bt = np.zeros((len(lens), int(((lens + bs - 1) // bs).max())), dtype=np.int32)
+        slot = np.empty(total, dtype=np.int32); o = 0; ob = 0
+        for s, n in enumerate(lens):
+            n = int(n); b = (n + bs - 1) // bs
+            bt[s, :b] = ids[ob:ob + b]; ob += b
+            p = np.arange(n); slot[o:o + n] = bt[s, p // bs] * bs + p % bs; o += n
+        return bt, slot
+
+    gen = torch.Generator(device="cuda"); gen.manual_seed(5)
+    ks = torch.rand((total, n_head_kv * d), generator=gen, device=cuda) * 2 - 1
+    vs = torch.rand((total, n_head_kv * d), generator=gen, device=cuda) * 2 - 1
+    q = torch.rand((len(lens), n_head, d), generator=gen, device=cuda) * 2 - 1
+    sl = _dev(torch, lens)
+    outs = []
+    for seed in (1, 2):
+        bt, slot = build(seed)
+        pkg.kv_write(ks, vs, _dev(torch, slot), kc, vc, lay)
+        for kernel in (1, 2):
+            out = torch.empty_like(q)
+            call = pkg.AttnCall(q, kc, vc, lay, out, 0.0884, block_table=_dev(torch, bt), seq_lens=sl,
+                                max_seq_len=int(lens.max()), total_tokens=total, kernel=kernel)
+            if not call.supported():
+                continue
+            call.run(); torch.cuda.synchronize()
+            outs.append(out.cpu().numpy())
+    for o in outs[1:]:
+        assert oracle.max_rel_err(outs[0], o) <= 1e-3
+    # sampled rows against the oracle (3 shortest sequences keep the CPU time in seconds)
+    bt, slot = build(2)
+    rows = np.argsort(lens)[:3]
+    hk, hv = kc.cpu().numpy().reshape(lay.n_cells, -1), vc.cpu().numpy().reshape(lay.n_cells, -1)
+    want = oracle.attention(q.cpu().numpy()[rows], hk, hv, t, t, n_head_kv, 0.0884, block_table=bt[rows],
+                            seq_lens=lens[rows], block_size=bs)
+    assert oracle.max_rel_err(want, outs[-1][rows]) <= TOL[t]
+    # constant V
+    pkg.kv_write(None, torch.full_like(vs, 0.5), _dev(torch, slot), None, vc, lay)
+    out = pkg.paged_attention(q, kc, vc, lay, _dev(torch, bt), sl, 0.0884, max_seq_len=int(lens.max()), total_tokens=total)
+    torch.cuda.synchronize()
+    c = oracle.to_float(t, oracle.from_float(t, np.full((1, d), 0.5, dtype=np.float32)), d)[0, 0]
+    assert np.abs(out.cpu().numpy() - c).max() <= 2e-3 * abs(c)
