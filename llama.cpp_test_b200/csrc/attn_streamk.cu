@@ -19,24 +19,31 @@
 //   * sk_plan_kernel   1 CTA: tiles per row (16 tokens each) from the DEVICE seq_lens / q_pos, prefix sums,
 //                      chunk = ceil(total / n_items): item i owns global tiles [i*chunk, (i+1)*chunk).  An item
 //                      crossing a row boundary yields one segment per row; segment slots are contiguous per row.
-//   * sk_main_kernel   every WARP is an independent worker for (item, kv head): it streams its K/V tiles with a
-//                      private 16-byte cp.async ring (no CTA barrier in the loop), gathers through the block table,
-//                      places each tile in shared memory as [16-byte chunk][token][16 B] so that ldmatrix (F16)
-//                      and the fragment loads of the quantised types are bank-conflict free, dequantises in
-//                      registers straight into mma A fragments, and keeps the online softmax in registers
-//                      (warp-shuffle max/sum).  The 8 warps of a CTA take the 8 kv heads of the same tokens, so a
-//                      CTA consumes whole contiguous token rows of the flat llama.cpp cache.
+//   * sk_main_kernel   every WARP is an independent worker for (item, kv head): it streams its K/V tiles through a
+//                      private ring of TMA tensor-map boxes completed on its own mbarriers (no CTA barrier in the
+//                      loop; the first version used 16-byte cp.async and stalled on the LSU queues, see
+//                      profiles/r1c_*), gathered through the block table: one box = the 16 cells of a tile x one
+//                      head row.  F16 boxes are 3-D {128 B, 16 cells, 2 halves} with the 128-byte swizzle so that
+//                      ldmatrix is bank-conflict free; Q8_0 / Q4_0 boxes are 2-D {144 | 80 B, 16 cells}, whose row
+//                      pitch makes the fragment-order 32-bit loads conflict free.  Quantised tiles are
+//                      dequantised in registers straight into mma A fragments (byte -> half by OR-ing the
+//                      exponent of 1024; K scales applied to the FP32 scores per 32-element block, V scales
+//                      fused into one HFMA2 per register).  Online softmax lives in registers (warp-shuffle
+//                      max/sum).  The 8 warps of a CTA take the 8 kv heads of the same tokens, so a CTA consumes
+//                      whole contiguous token rows of the flat llama.cpp cache.
 //   * sk_combine_kernel merges the segments of rows that were split (rows with one segment are written
 //                      directly by the main kernel).
 #include "common.cuh"
+#include <cuda.h>
 #include <math.h>
+#include <type_traits>
+#include <climits>
 
 namespace b200 {
 
-constexpr int SK_WARPS  = 8;
-constexpr int SK_D      = 128;
-constexpr int SK_TILE   = 16;          // tokens per tile
-constexpr int SK_STAGES = 3;
+constexpr int SK_WARPS = 8;
+constexpr int SK_D     = 128;
+constexpr int SK_TILE  = 16;           // tokens per tile
 
 struct sk_args {
     b200_attn_desc d;
@@ -50,21 +57,48 @@ struct sk_args {
 };
 
 // ------------------------------------------------------------------------------------------------
-// type traits for D = 128: bytes of one head row and the most 16-byte chunks a (mis-aligned) row can span
+// per-type tile geometry for D = 128.  WIN = bytes of one token row of the shared-memory tile.
 // ------------------------------------------------------------------------------------------------
 template <int T> struct sk_type;
-template <> struct sk_type<B200_TYPE_F16>  { static constexpr int HEAD_BYTES = 256; static constexpr int NCH = 16; };
-template <> struct sk_type<B200_TYPE_Q8_0> { static constexpr int HEAD_BYTES = 136; static constexpr int NCH = 9;  };
-template <> struct sk_type<B200_TYPE_Q4_0> { static constexpr int HEAD_BYTES = 72;  static constexpr int NCH = 5;  };
-template <int T> constexpr int sk_tile_bytes() { return sk_type<T>::NCH*SK_TILE*16; }
+template <> struct sk_type<B200_TYPE_F16>  { static constexpr int HEAD_BYTES = 256, WIN = 256, TILE = 4096, BLK = 0;  };
+template <> struct sk_type<B200_TYPE_Q8_0> { static constexpr int HEAD_BYTES = 136, WIN = 144, TILE = 2304, BLK = 34; };
+template <> struct sk_type<B200_TYPE_Q4_0> { static constexpr int HEAD_BYTES = 72,  WIN = 80,  TILE = 1280, BLK = 18; };
+
+template <int TK, int TV>
+struct sk_smem {
+    static constexpr bool ANY16 = TK == B200_TYPE_F16 || TV == B200_TYPE_F16;
+    static constexpr int KT = sk_type<TK>::TILE, VT = sk_type<TV>::TILE;
+    static constexpr bool KFIRST = TK == B200_TYPE_F16 || TV != B200_TYPE_F16;     // F16 tiles need 1024-byte alignment
+    static constexpr int KOFF = KFIRST ? 0 : VT, VOFF = KFIRST ? KT : 0;
+    static constexpr int ALIGN = ANY16 ? 1024 : 128;
+    static constexpr int STAGE = (KT + VT + ALIGN - 1)/ALIGN*ALIGN;
+    static constexpr int STAGES = STAGE <= 2560 ? 4 : 3;
+    static constexpr int WARP = STAGE*STAGES;
+    static constexpr int BAR_BYTES = 1024;                                        // mbarriers, keeps tiles 1024-aligned
+    static constexpr int CTA = BAR_BYTES + WARP*SK_WARPS + 16;                    // +16: funnel loads may touch 4 bytes past a row
+    static constexpr int CTAS_PER_SM = 2*(CTA + 1024) <= 233472 ? 2 : 1;
+};
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
 
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src, int src_bytes) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" :: "r"(dst), "l"(src), "r"(src_bytes) : "memory");
+__device__ __forceinline__ void mbar_init(uint32_t bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" :: "n"(N) : "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile("{\n .reg .pred p;\nSK_WAIT_%=:\n mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n @p bra SK_DONE_%=;\n bra SK_WAIT_%=;\nSK_DONE_%=:\n}"
+                 :: "r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *tm, int c0, int c1, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 :: "r"(dst), "l"(tm), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *tm, int c0, int c1, int c2, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 :: "r"(dst), "l"(tm), "r"(c0), "r"(c1), "r"(c2), "r"(bar) : "memory");
+}
 
 __device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
     asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];\n"
@@ -89,9 +123,25 @@ __device__ __forceinline__ uint32_t pack_h2(float lo, float hi) {
     const __half2 h = __floats2half2_rn(lo, hi);
     return *reinterpret_cast<const uint32_t *>(&h);
 }
+__device__ __forceinline__ float2 unpack_h2(uint32_t v) { return __half22float2(*reinterpret_cast<const __half2 *>(&v)); }
+__device__ __forceinline__ uint32_t hfma2_u(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d; asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d;
+}
+__device__ __forceinline__ uint32_t hmul2_u(uint32_t a, uint32_t b) {
+    uint32_t d; asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b)); return d;
+}
 __device__ __forceinline__ float ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ uint32_t lds32(uint32_t addr) { uint32_t v; asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
+__device__ __forceinline__ void sts128_zero(uint32_t addr) { asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" :: "r"(addr), "r"(0) : "memory"); }
+__device__ __forceinline__ float h16f(uint32_t bits) { return __half2float(__ushort_as_half((unsigned short) bits)); }
 
+// int8 / nibble -> half by OR-ing the exponent of 1024 (0x6400): half(0x6400 | u) == 1024 + u exactly.
+// Q8_0 bytes are first biased to unsigned (xor 0x80): value = 1152 + q.  Pairs are (byte0, byte2) and (byte1, byte3).
+__device__ __forceinline__ uint32_t q8_e02(uint32_t w) { return (w & 0x00ff00ffu) ^ 0x64806480u; }
+__device__ __forceinline__ uint32_t q8_e13(uint32_t w) { return ((w >> 8) & 0x00ff00ffu) ^ 0x64806480u; }
+// Q4_0: low nibbles give 1024 + n, high nibbles 1024 + 16 n
+__device__ __forceinline__ uint32_t q4_lo(uint32_t w) { return (w & 0x000f000fu) | 0x64006400u; }
+__device__ __forceinline__ uint32_t q4_hi(uint32_t w) { return (w & 0x00f000f0u) | 0x64006400u; }
 // ------------------------------------------------------------------------------------------------
 // plan: tiles per row, prefix sums, chunk, segment slots.  One CTA of 1024 threads.
 // ------------------------------------------------------------------------------------------------
@@ -161,90 +211,232 @@ sk_plan_kernel(const __grid_constant__ sk_args a) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// tile copy: 16 tokens x NCH 16-byte chunks of one head row -> smem [chunk][token][16 B]
-// lane handles tokens (lane&7) and (lane&7)+8; quarter-warps write 128 contiguous bytes (no bank conflict)
-// and read 64 contiguous bytes per token from HBM/L2.
+// Q as the B operand of S^T = K.Q^T  (lane = 4n + t holds column n = query head, contraction slots of t)
 // ------------------------------------------------------------------------------------------------
-template <int NCH>
-__device__ __forceinline__ void sk_copy_tile(uint32_t dst, const char *row0, const char *row1, bool ok0, bool ok1,
-                                             int nch, int last_bytes, int lane) {
-    constexpr int ITERS = 2*((NCH + 3)/4);
-    const int tq = lane & 7, cq = lane >> 3;
-#pragma unroll
-    for (int it = 0; it < ITERS; ++it) {
-        const int half = it & 1, chunk = cq + 4*(it >> 1);
-        if (chunk < nch) {
-            const char *row = half ? row1 : row0;
-            const bool ok = half ? ok1 : ok0;
-            const int bytes = ok ? (chunk == nch - 1 ? last_bytes : 16) : 0;
-            cp_async16(dst + chunk*(SK_TILE*16) + (tq + 8*half)*16, row + chunk*16, bytes);
-        }
-    }
-}
-
-// ------------------------------------------------------------------------------------------------
-// per-type fragment producers
-// ------------------------------------------------------------------------------------------------
-// Q as the B operand of S^T = K.Q^T.  For F16 K the contraction index is d in natural order:
-// k-step s, lane (n = lane>>2, t = lane&3): b0 = Q[n][16s+2t, +1], b1 = Q[n][16s+2t+8, +9].
-struct sk_qfrag_f16 {
+// F16 K: contraction index = d in natural order.  k-step s: b0 = Q[n][16s+2t, +1], b1 = Q[n][16s+2t+8, +9].
+// Quantised K: 32-element block `blk` feeds k-steps 2blk (elements 0..15 of the block) and 2blk+1 (16..31); the
+// byte->half expansion pairs (byte0, byte2) / (byte1, byte3) of the lane's word, so b0 = Q[e0], Q[e0+2] and
+// b1 = Q[e0+1], Q[e0+3] with e0 = 32blk + 16hi + 4t.  Q4_0 high nibbles arrive as 1024 + 16n: their Q is /16.
+// cb[blk][c] = the constant the biased integers add to column 2t+c of block blk (removed from the FP32 scores).
+template <int TK>
+struct sk_qfrag {
+    static constexpr bool QUANT = TK != B200_TYPE_F16;
     uint32_t b[8][2];
+    float    cb[QUANT ? 4 : 1][2];
+
     __device__ __forceinline__ void load(const float *qrow, bool live, float qscale, int lane) {
         const int t = lane & 3;
+        if constexpr (!QUANT) {
 #pragma unroll
-        for (int s = 0; s < 8; ++s) {
-            float2 x = make_float2(0.f, 0.f), y = make_float2(0.f, 0.f);
-            if (live) {
-                x = *reinterpret_cast<const float2 *>(qrow + 16*s + 2*t);
-                y = *reinterpret_cast<const float2 *>(qrow + 16*s + 2*t + 8);
+            for (int s = 0; s < 8; ++s) {
+                float2 x = make_float2(0.f, 0.f), y = make_float2(0.f, 0.f);
+                if (live) {
+                    x = *reinterpret_cast<const float2 *>(qrow + 16*s + 2*t);
+                    y = *reinterpret_cast<const float2 *>(qrow + 16*s + 2*t + 8);
+                }
+                b[s][0] = pack_h2(x.x*qscale, x.y*qscale);
+                b[s][1] = pack_h2(y.x*qscale, y.y*qscale);
             }
-            b[s][0] = pack_h2(x.x*qscale, x.y*qscale);
-            b[s][1] = pack_h2(y.x*qscale, y.y*qscale);
+        } else {
+#pragma unroll
+            for (int ks = 0; ks < 8; ++ks) {
+                const int hi = ks & 1;
+                float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (live) x = *reinterpret_cast<const float4 *>(qrow + 32*(ks >> 1) + 16*hi + 4*t);
+                const float sc = (TK == B200_TYPE_Q4_0 && hi) ? qscale*0.0625f : qscale;
+                b[ks][0] = pack_h2(x.x*sc, x.z*sc);
+                b[ks][1] = pack_h2(x.y*sc, x.w*sc);
+            }
+#pragma unroll
+            for (int blk = 0; blk < 4; ++blk) {
+                const float2 a0 = unpack_h2(b[2*blk][0]), a1 = unpack_h2(b[2*blk][1]);
+                const float2 c0 = unpack_h2(b[2*blk + 1][0]), c1 = unpack_h2(b[2*blk + 1][1]);
+                const float slo = (a0.x + a0.y) + (a1.x + a1.y), shi = (c0.x + c0.y) + (c1.x + c1.y);
+                float v = TK == B200_TYPE_Q8_0 ? 1152.0f*(slo + shi)                         // sum (1152 + q) Q
+                                               : 1024.0f*(slo + shi) + 8.0f*(slo + 16.0f*shi);   // sum (1024 + s n) Q/s, and the -8
+                v += __shfl_xor_sync(0xffffffffu, v, 1);
+                v += __shfl_xor_sync(0xffffffffu, v, 2);
+                cb[blk][0] = __shfl_sync(0xffffffffu, v, 8*t);
+                cb[blk][1] = __shfl_sync(0xffffffffu, v, 8*t + 4);
+            }
         }
     }
 };
 
-// S^T tile (16 tokens x 8 heads) for an F16 K tile at smem address kb
-__device__ __forceinline__ void sk_qk_f16(float (&S)[4], uint32_t kb, const sk_qfrag_f16 &q, int lane) {
-    const uint32_t base = kb + (lane >> 4)*(SK_TILE*16) + ((lane & 7) + 8*((lane >> 3) & 1))*16;
+// ------------------------------------------------------------------------------------------------
+// S^T tile (16 tokens x 8 heads), FP32, log2 domain
+// ------------------------------------------------------------------------------------------------
+// F16 tile: [2 halves][16 tokens][128 B], 16-byte pieces XOR-swizzled with (token & 7) (TMA SWIZZLE_128B)
+__device__ __forceinline__ void sk_qk_f16(float (&S)[4], uint32_t kb, const sk_qfrag<B200_TYPE_F16> &q, int lane) {
+    const int tau = (lane & 7) + 8*((lane >> 3) & 1);
+    const uint32_t base = kb + tau*128;
+    const uint32_t y = ((tau & 7) << 4) ^ ((lane >> 4) << 4);
+    float S2[4] = {0.f, 0.f, 0.f, 0.f};                      // two independent accumulation chains
 #pragma unroll
-    for (int s = 0; s < 8; ++s) {
-        uint32_t a[4];
-        ldmatrix_x4(a, base + 2*s*(SK_TILE*16));
-        mma_16816(S, a, q.b[s][0], q.b[s][1]);
+    for (int s = 0; s < 8; s += 2) {
+        uint32_t a[4], b[4];
+        ldmatrix_x4(a, base + (s >> 2)*2048 + ((((2*s) & 7) << 4) ^ y));
+        ldmatrix_x4(b, base + ((s + 1) >> 2)*2048 + ((((2*(s + 1)) & 7) << 4) ^ y));
+        mma_16816(S,  a, q.b[s][0],     q.b[s][1]);
+        mma_16816(S2, b, q.b[s + 1][0], q.b[s + 1][1]);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) S[j] += S2[j];
+}
+
+// fetch 4 bytes at byte offset `off` of a row; off % 4 is 0 (ALIGNED) or 2 (funnel of two words)
+template <bool ALIGNED>
+__device__ __forceinline__ uint32_t sk_ld4(uint32_t row, int off) {
+    if constexpr (ALIGNED) return lds32(row + off);
+    else return __byte_perm(lds32(row + off - 2), lds32(row + off + 2), 0x5432);
+}
+
+// Quantised tile: [16 tokens][WIN bytes]; the head row starts `mis` (0 or 8) bytes into each token row.
+// Even blocks: scale in the low half of its word, quants 2 bytes off word alignment; odd blocks: high half, aligned.
+template <int TK>
+__device__ __forceinline__ void sk_qk_quant(float (&S)[4], uint32_t kb, int mis, const sk_qfrag<TK> &q, int lane) {
+    constexpr int WIN = sk_type<TK>::WIN, BLK = sk_type<TK>::BLK;
+    const int g = lane >> 2, t = lane & 3;
+    const uint32_t row0 = kb + g*WIN + mis, row1 = row0 + 8*WIN;
+#pragma unroll
+    for (int blk = 0; blk < 4; ++blk) {
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        const int o = BLK*blk + 2 + 4*t;
+        if constexpr (TK == B200_TYPE_Q8_0) {
+            uint32_t A0, A1, B0, B1;
+            if (blk & 1) { A0 = sk_ld4<true >(row0, o); A1 = sk_ld4<true >(row1, o); B0 = sk_ld4<true >(row0, o + 16); B1 = sk_ld4<true >(row1, o + 16); }
+            else         { A0 = sk_ld4<false>(row0, o); A1 = sk_ld4<false>(row1, o); B0 = sk_ld4<false>(row0, o + 16); B1 = sk_ld4<false>(row1, o + 16); }
+            const uint32_t a[4] = {q8_e02(A0), q8_e02(A1), q8_e13(A0), q8_e13(A1)};
+            const uint32_t c[4] = {q8_e02(B0), q8_e02(B1), q8_e13(B0), q8_e13(B1)};
+            mma_16816(acc, a, q.b[2*blk][0],     q.b[2*blk][1]);
+            mma_16816(acc, c, q.b[2*blk + 1][0], q.b[2*blk + 1][1]);
+        } else {
+            uint32_t W0, W1;
+            if (blk & 1) { W0 = sk_ld4<true >(row0, o); W1 = sk_ld4<true >(row1, o); }
+            else         { W0 = sk_ld4<false>(row0, o); W1 = sk_ld4<false>(row1, o); }
+            const uint32_t Y0 = W0 >> 8, Y1 = W1 >> 8;
+            const uint32_t a[4] = {q4_lo(W0), q4_lo(W1), q4_lo(Y0), q4_lo(Y1)};
+            const uint32_t c[4] = {q4_hi(W0), q4_hi(W1), q4_hi(Y0), q4_hi(Y1)};
+            mma_16816(acc, a, q.b[2*blk][0],     q.b[2*blk][1]);
+            mma_16816(acc, c, q.b[2*blk + 1][0], q.b[2*blk + 1][1]);
+        }
+        const int so = (BLK*blk) & ~3;                        // mis % 4 == 0
+        const uint32_t s0 = lds32(row0 + so), s1 = lds32(row1 + so);
+        const float d0 = h16f((blk & 1) ? s0 >> 16 : s0 & 0xffffu), d1 = h16f((blk & 1) ? s1 >> 16 : s1 & 0xffffu);
+        S[0] = fmaf(d0, acc[0] - q.cb[blk][0], S[0]);
+        S[1] = fmaf(d0, acc[1] - q.cb[blk][1], S[1]);
+        S[2] = fmaf(d1, acc[2] - q.cb[blk][0], S[2]);
+        S[3] = fmaf(d1, acc[3] - q.cb[blk][1], S[3]);
     }
 }
 
-// O^T += V^T . P^T for an F16 V tile; m-tile mu covers d = 16mu .. 16mu+15 in natural order
+// ------------------------------------------------------------------------------------------------
+// O^T += V^T . P^T ; 8 m-tiles of 16 d-rows.  OW = extra accumulators of sum_tok P*d_blk (quantised V only):
+// the A operand holds (128 + q) d for Q8_0 and n d for Q4_0 (the -1024 d of the exponent trick is exact in half,
+// the -128 d / -8 d is not), so 128 W / 8 W is subtracted once per segment in sk_store.
+// ------------------------------------------------------------------------------------------------
+template <int TV> struct sk_vacc { static constexpr int NW = TV == B200_TYPE_F16 ? 1 : TV == B200_TYPE_Q8_0 ? 4 : 2; };
+
 __device__ __forceinline__ void sk_pv_f16(float (&O)[8][4], uint32_t vb, uint32_t p0, uint32_t p1, int lane) {
-    const uint32_t base = vb + ((lane >> 3) & 1)*(SK_TILE*16) + ((lane & 7) + 8*(lane >> 4))*16;
+    const int tau = (lane & 7) + 8*(lane >> 4);
+    const uint32_t base = vb + tau*128;
+    const uint32_t y = ((tau & 7) << 4) ^ (((lane >> 3) & 1) << 4);
 #pragma unroll
     for (int mu = 0; mu < 8; ++mu) {
         uint32_t a[4];
-        ldmatrix_x4_trans(a, base + 2*mu*(SK_TILE*16));
+        ldmatrix_x4_trans(a, base + (mu >> 2)*2048 + ((((2*mu) & 7) << 4) ^ y));
         mma_16816(O[mu], a, p0, p1);
     }
 }
 
+template <int TV>
+__device__ __forceinline__ void sk_pv_quant(float (&O)[8][4], float (&OW)[sk_vacc<TV>::NW][4], uint32_t vb, int mis,
+                                            uint32_t p0, uint32_t p1, int lane) {
+    constexpr int WIN = sk_type<TV>::WIN, BLK = sk_type<TV>::BLK;
+    const int g = lane >> 2, t = lane & 3;
+    const uint32_t r0 = vb + 2*t*WIN + mis, r1 = r0 + WIN, r2 = r0 + 8*WIN, r3 = r2 + WIN;   // tokens 2t, 2t+1, 2t+8, 2t+9
+    constexpr uint32_t M1024 = 0xE400E400u;                  // half2(-1024)
+    if constexpr (TV == B200_TYPE_Q8_0) {
+#pragma unroll
+        for (int blk = 0; blk < 4; ++blk) {
+            const int so = (BLK*blk) & ~3;
+            const uint32_t sel = (blk & 1) ? 0x7632 : 0x5410;
+            const uint32_t sp01 = __byte_perm(lds32(r0 + so), lds32(r1 + so), sel);           // (d[2t], d[2t+1])
+            const uint32_t sp23 = __byte_perm(lds32(r2 + so), lds32(r3 + so), sel);
+            const uint32_t of01 = hmul2_u(sp01, M1024), of23 = hmul2_u(sp23, M1024);
+            const int o = BLK*blk + 2 + 4*g;
+            uint32_t W0, W1, W2, W3;
+            if (blk & 1) { W0 = sk_ld4<true >(r0, o); W1 = sk_ld4<true >(r1, o); W2 = sk_ld4<true >(r2, o); W3 = sk_ld4<true >(r3, o); }
+            else         { W0 = sk_ld4<false>(r0, o); W1 = sk_ld4<false>(r1, o); W2 = sk_ld4<false>(r2, o); W3 = sk_ld4<false>(r3, o); }
+            const uint32_t x01l = __byte_perm(W0, W1, 0x5410), x01h = __byte_perm(W0, W1, 0x7632);
+            const uint32_t x23l = __byte_perm(W2, W3, 0x5410), x23h = __byte_perm(W2, W3, 0x7632);
+            const uint32_t a[4] = {hfma2_u(q8_e02(x01l), sp01, of01), hfma2_u(q8_e13(x01l), sp01, of01),
+                                   hfma2_u(q8_e02(x23l), sp23, of23), hfma2_u(q8_e13(x23l), sp23, of23)};
+            const uint32_t c[4] = {hfma2_u(q8_e02(x01h), sp01, of01), hfma2_u(q8_e13(x01h), sp01, of01),
+                                   hfma2_u(q8_e02(x23h), sp23, of23), hfma2_u(q8_e13(x23h), sp23, of23)};
+            mma_16816(O[2*blk],     a, p0, p1);
+            mma_16816(O[2*blk + 1], c, p0, p1);
+            const uint32_t w[4] = {sp01, 0u, sp23, 0u};
+            mma_16816(OW[blk], w, p0, p1);
+        }
+    } else {
+        constexpr uint32_t R16 = 0x2C002C00u, M64 = 0xD400D400u;   // half2(1/16), half2(-64)
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int odd = g >> 2, bb = 2*k + odd, wq = g & 3;      // this lane's block of the pair (2k, 2k+1)
+            const int so = (BLK*bb) & ~3;
+            const uint32_t sel = odd ? 0x7632 : 0x5410;
+            const uint32_t sp01 = __byte_perm(lds32(r0 + so), lds32(r1 + so), sel);
+            const uint32_t sp23 = __byte_perm(lds32(r2 + so), lds32(r3 + so), sel);
+            const uint32_t sq01 = hmul2_u(sp01, R16), sq23 = hmul2_u(sp23, R16);
+            const uint32_t ol01 = hmul2_u(sp01, M1024), ol23 = hmul2_u(sp23, M1024);
+            const uint32_t oh01 = hmul2_u(sp01, M64), oh23 = hmul2_u(sp23, M64);
+            const int o = BLK*bb + 2 + 4*wq, oa = o & ~3;
+            const uint32_t fsel = odd ? 0x3210 : 0x5432;              // odd blocks are word aligned
+            const uint32_t W0 = __byte_perm(lds32(r0 + oa), lds32(r0 + oa + 4), fsel);
+            const uint32_t W1 = __byte_perm(lds32(r1 + oa), lds32(r1 + oa + 4), fsel);
+            const uint32_t W2 = __byte_perm(lds32(r2 + oa), lds32(r2 + oa + 4), fsel);
+            const uint32_t W3 = __byte_perm(lds32(r3 + oa), lds32(r3 + oa + 4), fsel);
+#pragma unroll
+            for (int hb = 0; hb < 2; ++hb) {                           // bytes (0,1) then (2,3) of the word
+                const uint32_t x01 = __byte_perm(W0, W1, hb ? 0x7632 : 0x5410), x23 = __byte_perm(W2, W3, hb ? 0x7632 : 0x5410);
+                const uint32_t y01 = x01 >> 8, y23 = x23 >> 8;
+                const uint32_t a[4] = {hfma2_u(q4_lo(x01), sp01, ol01), hfma2_u(q4_lo(y01), sp01, ol01),
+                                       hfma2_u(q4_lo(x23), sp23, ol23), hfma2_u(q4_lo(y23), sp23, ol23)};
+                const uint32_t c[4] = {hfma2_u(q4_hi(x01), sq01, oh01), hfma2_u(q4_hi(y01), sq01, oh01),
+                                       hfma2_u(q4_hi(x23), sq23, oh23), hfma2_u(q4_hi(y23), sq23, oh23)};
+                mma_16816(O[4*k + 2*hb],     a, p0, p1);
+                mma_16816(O[4*k + 2*hb + 1], c, p0, p1);
+            }
+            const uint32_t w[4] = {sp01, 0u, sp23, 0u};
+            mma_16816(OW[k], w, p0, p1);
+        }
+    }
+}
+
+// d index of accumulator row (m-tile mt, half h: 0 = row g, 1 = row g+8) and the OW entry that corrects it
+template <int TV>
+__device__ __forceinline__ int sk_row_d(int mt, int h, int g) {
+    if constexpr (TV == B200_TYPE_F16)       return 16*mt + g + 8*h;
+    else if constexpr (TV == B200_TYPE_Q8_0) return 32*(mt >> 1) + 4*g + 2*(mt & 1) + h;
+    else { const int bb = 2*(mt >> 2) + (g >> 2); return 32*bb + 4*(g & 3) + 16*(mt & 1) + 2*((mt >> 1) & 1) + h; }
+}
+template <int TV> __device__ __forceinline__ int sk_row_w(int mt) {
+    if constexpr (TV == B200_TYPE_Q8_0) return mt >> 1; else if constexpr (TV == B200_TYPE_Q4_0) return mt >> 2; else return 0;
+}
 // ------------------------------------------------------------------------------------------------
 // main kernel
 // ------------------------------------------------------------------------------------------------
 template <int TK, int TV>
-struct sk_smem {
-    static constexpr int KB = sk_tile_bytes<TK>();
-    static constexpr int VB = sk_tile_bytes<TV>();
-    static constexpr int STAGE = KB + VB;
-    static constexpr int WARP = STAGE*SK_STAGES;
-    static constexpr int CTA = WARP*SK_WARPS;
-};
-
-template <int TK, int TV>
-__global__ void __launch_bounds__(32*SK_WARPS)
-sk_main_kernel(const __grid_constant__ sk_args a) {
-    extern __shared__ __align__(128) char sk_dyn[];
+__global__ void __launch_bounds__(32*SK_WARPS, sk_smem<TK, TV>::CTAS_PER_SM)
+sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV) {
+    extern __shared__ __align__(1024) char sk_dyn[];
     using SM = sk_smem<TK, TV>;
+    constexpr int STAGES = SM::STAGES, NW = sk_vacc<TV>::NW;
     const b200_attn_desc &p = a.d;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int lane = threadIdx.x & 31;
+    asm volatile("mov.b32 %0, %0;" : "+r"(lane));             // pin in a register: ptxas otherwise re-reads SR_TID in the loop
+    const int warp = threadIdx.x >> 5;
     const int g = lane >> 2, t = lane & 3;
 
     const int wid  = blockIdx.x*SK_WARPS + warp;
@@ -260,17 +452,25 @@ sk_main_kernel(const __grid_constant__ sk_args a) {
     while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (P[mid] <= g0) lo = mid; else hi = mid; }
     int row = lo;
 
-    const uint32_t smem0 = smem_u32(sk_dyn) + warp*SM::WARP;
+    uint32_t smem0 = smem_u32(sk_dyn) + SM::BAR_BYTES + warp*SM::WARP;
+    uint32_t bar0  = smem_u32(sk_dyn) + warp*STAGES*8;
+    asm volatile("mov.b32 %0, %0;" : "+r"(smem0));
+    asm volatile("mov.b32 %0, %0;" : "+r"(bar0));
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(bar0 + 8*s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
 
-    // head-row placement inside the 16-byte chunk grid (quantised rows are only 8-byte aligned)
+    // head-row placement: quantised rows are only 8-byte aligned, the TMA box starts `mis` bytes earlier
     const int64_t koff = (int64_t) kvh*p.nbk2, voff = (int64_t) kvh*p.nbv2;
-    const int kmis = (int) (koff & 15), vmis = (int) (voff & 15);
-    const int knch = (kmis + sk_type<TK>::HEAD_BYTES + 15) >> 4, vnch = (vmis + sk_type<TV>::HEAD_BYTES + 15) >> 4;
-    const int klast = kmis + sk_type<TK>::HEAD_BYTES - 16*(knch - 1), vlast = vmis + sk_type<TV>::HEAD_BYTES - 16*(vnch - 1);
-    const char *kbase = static_cast<const char *>(p.k) + koff - kmis;
-    const char *vbase = static_cast<const char *>(p.v) + voff - vmis;
-    const int bs = p.block_size;
-    const bool tile_in_block = (bs % SK_TILE) == 0;
+    const int kmis = TK == B200_TYPE_F16 ? 0 : (int) (koff & 15), vmis = TV == B200_TYPE_F16 ? 0 : (int) (voff & 15);
+    const int kc = TK == B200_TYPE_F16 ? (int) (koff >> 7) : (int) (koff - kmis);     // TMA coordinate of the head row
+    const int vc = TV == B200_TYPE_F16 ? (int) (voff >> 7) : (int) (voff - vmis);
+    const int bs = p.block_size, tpb = bs/SK_TILE;                                    // tiles per block (bs % 16 == 0)
+    const int n_blk = p.bt_stride < INT32_MAX ? (int) p.bt_stride : INT32_MAX;
+    uint32_t it = 0;                                                                  // tiles consumed by this warp so far
 
     while (g0 < g1) {
         const int pb = P[row], pe = P[row + 1];
@@ -283,7 +483,7 @@ sk_main_kernel(const __grid_constant__ sk_args a) {
         const bool single = (FS[row + 1] - FS[row]) == 1;
 
         // ---- Q fragments (this kv head's query heads in the 8 mma columns)
-        sk_qfrag_f16 qf;
+        sk_qfrag<TK> qf;
         {
             const bool live = g < a.gqa;
             const float *qrow = reinterpret_cast<const float *>(static_cast<const char *>(p.q) + (int64_t) row*p.nbq1
@@ -291,47 +491,67 @@ sk_main_kernel(const __grid_constant__ sk_args a) {
             qf.load(qrow, live, a.qscale, lane);
         }
 
-        float O[8][4];
+        float O[8][4], OW[NW][4];
 #pragma unroll
         for (int mu = 0; mu < 8; ++mu) { O[mu][0] = O[mu][1] = O[mu][2] = O[mu][3] = 0.f; }
+#pragma unroll
+        for (int w = 0; w < NW; ++w) { OW[w][0] = OW[w][1] = OW[w][2] = OW[w][3] = 0.f; }
         float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;   // columns 2t, 2t+1
 
-        auto issue = [&](int tile, int slot) {
-            const int pos0 = tile*SK_TILE + (lane & 7), pos1 = pos0 + 8;
-            const bool ok0 = pos0 < n_vis, ok1 = pos1 < n_vis;
-            int64_t c0 = 0, c1 = 0;
-            if (tile_in_block) {
-                const int tp = tile*SK_TILE;
-                const int64_t cb = (int64_t) bt[tp/bs]*bs + tp % bs;     // same address for the whole warp
-                c0 = cb + (lane & 7); c1 = c0 + 8;
-            } else {
-                if (ok0) c0 = (int64_t) bt[pos0/bs]*bs + pos0 % bs;
-                if (ok1) c1 = (int64_t) bt[pos1/bs]*bs + pos1 % bs;
+        // block-table window: lane l holds entry win_base + l; the next window is fetched 32 blocks ahead, so the
+        // gather never waits on a global load inside the tile loop
+        int b_cur = t0/tpb, o_cur = t0 - b_cur*tpb, win_base = b_cur;
+        int win      = win_base + lane      < n_blk ? bt[win_base + lane]      : 0;
+        int win_next = win_base + 32 + lane < n_blk ? bt[win_base + 32 + lane] : 0;
+
+        auto issue = [&](uint32_t n) {                      // all lanes (shuffle); lane 0 talks to the TMA unit
+            if (b_cur - win_base >= 32) {
+                win_base += 32; win = win_next;
+                win_next = win_base + 32 + lane < n_blk ? bt[win_base + 32 + lane] : 0;
             }
-            const uint32_t sb = smem0 + slot*SM::STAGE;
-            sk_copy_tile<sk_type<TK>::NCH>(sb,          kbase + c0*p.nbk1, kbase + c1*p.nbk1, ok0, ok1, knch, klast, lane);
-            sk_copy_tile<sk_type<TV>::NCH>(sb + SM::KB, vbase + c0*p.nbv1, vbase + c1*p.nbv1, ok0, ok1, vnch, vlast, lane);
+            const int blk = __shfl_sync(0xffffffffu, win, b_cur - win_base);
+            const int cell = blk*bs + o_cur*SK_TILE;
+            if (++o_cur == tpb) { o_cur = 0; ++b_cur; }
+            if (lane == 0) {
+                const uint32_t slot = n % STAGES, bar = bar0 + 8*slot, sb = smem0 + slot*SM::STAGE;
+                mbar_expect_tx(bar, SM::KT + SM::VT);
+                if constexpr (TK == B200_TYPE_F16) tma_load_3d(sb + SM::KOFF, &tmK, 0, cell, kc, bar);
+                else                               tma_load_2d(sb + SM::KOFF, &tmK, kc, cell, bar);
+                if constexpr (TV == B200_TYPE_F16) tma_load_3d(sb + SM::VOFF, &tmV, 0, cell, vc, bar);
+                else                               tma_load_2d(sb + SM::VOFF, &tmV, vc, cell, bar);
+            }
         };
 
         const int nt = t1 - t0;
 #pragma unroll
-        for (int s = 0; s < SK_STAGES - 1; ++s) { if (s < nt) issue(t0 + s, s); cp_async_commit(); }
+        for (int s = 0; s < STAGES - 1; ++s) { if (s < nt) issue(it + s); }
 
-        for (int i = 0; i < nt; ++i) {
-            cp_async_wait<SK_STAGES - 2>();
-            __syncwarp();
-            if (i + SK_STAGES - 1 < nt) issue(t0 + i + SK_STAGES - 1, (i + SK_STAGES - 1) % SK_STAGES);
-            cp_async_commit();
+        for (int i = 0; i < nt; ++i, ++it) {
+            __syncwarp();                                    // every lane is done with the slot about to be refilled
+            if (i + STAGES - 1 < nt) issue(it + STAGES - 1);
+            const uint32_t slot = it % STAGES;
+            mbar_wait(bar0 + 8*slot, (it / STAGES) & 1);
+            const uint32_t sb = smem0 + slot*SM::STAGE, kb = sb + SM::KOFF, vb = sb + SM::VOFF;
 
-            const uint32_t sb = smem0 + (i % SK_STAGES)*SM::STAGE;
+            const int tok0 = (t0 + i)*SK_TILE;
+            if (tok0 + SK_TILE > n_vis) {                    // tail tile: cells past n_vis hold stale bytes; 0 * NaN must not reach O
+                constexpr int VW = sk_type<TV>::WIN;
+                for (int tau = n_vis - tok0; tau < SK_TILE; ++tau) {
+                    if constexpr (TV == B200_TYPE_F16) { if (lane < 16) sts128_zero(vb + ((lane >> 3)*16 + tau)*128 + (lane & 7)*16); }
+                    else                               { if (lane < VW/16) sts128_zero(vb + tau*VW + lane*16); }
+                }
+                __syncwarp();
+            }
+
             float S[4] = {0.f, 0.f, 0.f, 0.f};
-            sk_qk_f16(S, sb, qf, lane);
+            if constexpr (TK == B200_TYPE_F16) sk_qk_f16(S, kb, qf, lane);
+            else                               sk_qk_quant<TK>(S, kb, kmis, qf, lane);
 
             if (p.logit_softcap != 0.0f) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) S[j] = a.cap_log2e*tanhf(S[j]);
             }
-            const int tok = (t0 + i)*SK_TILE + g;
+            const int tok = tok0 + g;
             if (tok >= n_vis)     { S[0] = -INFINITY; S[1] = -INFINITY; }
             if (tok + 8 >= n_vis) { S[2] = -INFINITY; S[3] = -INFINITY; }
 
@@ -341,7 +561,7 @@ sk_main_kernel(const __grid_constant__ sk_args a) {
                 x0 = fmaxf(x0, __shfl_xor_sync(0xffffffffu, x0, o));
                 x1 = fmaxf(x1, __shfl_xor_sync(0xffffffffu, x1, o));
             }
-            const float n0 = fmaxf(m0, x0), n1 = fmaxf(m1, x1);      // finite: token t0*16 of a tile is always visible
+            const float n0 = fmaxf(m0, x0), n1 = fmaxf(m1, x1);      // finite: the first token of a tile is always visible
             const float al0 = ex2(m0 - n0), al1 = ex2(m1 - n1);
             m0 = n0; m1 = n1;
             const float p00 = ex2(S[0] - n0), p01 = ex2(S[1] - n1), p10 = ex2(S[2] - n0), p11 = ex2(S[3] - n1);
@@ -350,42 +570,46 @@ sk_main_kernel(const __grid_constant__ sk_args a) {
             if (__any_sync(0xffffffffu, al0 != 1.0f || al1 != 1.0f)) {
 #pragma unroll
                 for (int mu = 0; mu < 8; ++mu) { O[mu][0] *= al0; O[mu][1] *= al1; O[mu][2] *= al0; O[mu][3] *= al1; }
+                if constexpr (TV != B200_TYPE_F16) {
+#pragma unroll
+                    for (int w = 0; w < NW; ++w) { OW[w][0] *= al0; OW[w][1] *= al1; }
+                }
             }
             const uint32_t pt0 = movmatrix_trans(pack_h2(p00, p01));
             const uint32_t pt1 = movmatrix_trans(pack_h2(p10, p11));
-            sk_pv_f16(O, sb + SM::KB, pt0, pt1, lane);
+            if constexpr (TV == B200_TYPE_F16) sk_pv_f16(O, vb, pt0, pt1, lane);
+            else                               sk_pv_quant<TV>(O, OW, vb, vmis, pt0, pt1, lane);
         }
-        cp_async_wait<0>();
-        __syncwarp();
 
-        // ---- segment epilogue: row sums over the 8 token groups, then output or partial
+        // ---- segment epilogue
+        if constexpr (TV != B200_TYPE_F16) {                 // remove the 128 d (Q8_0) / 8 d (Q4_0) the A operand carried
+            constexpr float C = TV == B200_TYPE_Q8_0 ? 128.0f : 8.0f;
 #pragma unroll
-        for (int o = 4; o < 32; o <<= 1) {
+            for (int mu = 0; mu < 8; ++mu) {
+                const int w = sk_row_w<TV>(mu);
+                O[mu][0] -= C*OW[w][0]; O[mu][1] -= C*OW[w][1]; O[mu][2] -= C*OW[w][0]; O[mu][3] -= C*OW[w][1];
+            }
+        }
+#pragma unroll
+        for (int o = 4; o < 32; o <<= 1) {                   // row sums over the 8 token groups
             l0 += __shfl_xor_sync(0xffffffffu, l0, o);
             l1 += __shfl_xor_sync(0xffffffffu, l1, o);
         }
         const int h0 = kvh*a.gqa + 2*t;                          // query heads of columns 2t, 2t+1
         const bool w0 = 2*t < a.gqa, w1 = 2*t + 1 < a.gqa;
-        if (single) {
-            float *o0 = static_cast<float *>(p.dst) + ((int64_t) row*p.n_head + h0)*SK_D;
-            const float i0 = 1.0f/l0, i1 = 1.0f/l1;
+        float *o0 = single ? static_cast<float *>(p.dst) + ((int64_t) row*p.n_head + h0)*SK_D
+                           : a.part_o + ((int64_t) seg*p.n_head + h0)*SK_D;
+        const float i0 = single ? 1.0f/l0 : 1.0f, i1 = single ? 1.0f/l1 : 1.0f;
 #pragma unroll
-            for (int mu = 0; mu < 8; ++mu) {
-                if (w0) { o0[16*mu + g] = O[mu][0]*i0; o0[16*mu + g + 8] = O[mu][2]*i0; }
-                if (w1) { o0[SK_D + 16*mu + g] = O[mu][1]*i1; o0[SK_D + 16*mu + g + 8] = O[mu][3]*i1; }
-            }
-        } else {
-            float *o0 = a.part_o + ((int64_t) seg*p.n_head + h0)*SK_D;
-#pragma unroll
-            for (int mu = 0; mu < 8; ++mu) {
-                if (w0) { o0[16*mu + g] = O[mu][0]; o0[16*mu + g + 8] = O[mu][2]; }
-                if (w1) { o0[SK_D + 16*mu + g] = O[mu][1]; o0[SK_D + 16*mu + g + 8] = O[mu][3]; }
-            }
-            if (g == 0) {
-                float *ml = a.part_ml + ((int64_t) seg*p.n_head + h0)*2;
-                if (w0) { ml[0] = m0; ml[1] = l0; }
-                if (w1) { ml[2] = m1; ml[3] = l1; }
-            }
+        for (int mu = 0; mu < 8; ++mu) {
+            const int da = sk_row_d<TV>(mu, 0, g), db = sk_row_d<TV>(mu, 1, g);
+            if (w0) { o0[da] = O[mu][0]*i0; o0[db] = O[mu][2]*i0; }
+            if (w1) { o0[SK_D + da] = O[mu][1]*i1; o0[SK_D + db] = O[mu][3]*i1; }
+        }
+        if (!single && g == 0) {
+            float *ml = a.part_ml + ((int64_t) seg*p.n_head + h0)*2;
+            if (w0) { ml[0] = m0; ml[1] = l0; }
+            if (w1) { ml[2] = m1; ml[3] = l1; }
         }
         g0 = pb + t1;
         ++row;
@@ -427,33 +651,36 @@ static int sk_sm_count() {
     return n;
 }
 
-static bool sk_type_ok(int t) { return t == B200_TYPE_F16; }
+static bool sk_type_ok(int t) { return t == B200_TYPE_F16 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_0; }
 
 bool streamk_supports(const b200_attn_desc &d) {
     if (!d.block_table || d.head_dim != SK_D || d.max_bias != 0.0f) return false;
     if (!sk_type_ok(d.type_k) || !sk_type_ok(d.type_v)) return false;
     const int gqa = d.n_head/d.n_head_kv;
     if (gqa < 1 || gqa > 8) return false;
+    if (d.block_size % SK_TILE || d.n_kv < SK_TILE) return false;                          // one TMA box = 16 consecutive cells
     if (((uintptr_t) d.k | (uintptr_t) d.v | (uint64_t) d.nbk1 | (uint64_t) d.nbv1) & 15) return false;
-    const int ka = d.type_k == B200_TYPE_F16 ? 15 : 7, va = d.type_v == B200_TYPE_F16 ? 15 : 7;
-    if ((d.nbk2 & ka) || (d.nbv2 & va)) return false;
-    if (((uintptr_t) d.q | (uint64_t) d.nbq1 | (uint64_t) d.nbq2) & 7) return false;      // float2 loads of Q
+    if ((d.nbk2 & (d.type_k == B200_TYPE_F16 ? 127 : 7)) || (d.nbv2 & (d.type_v == B200_TYPE_F16 ? 127 : 7))) return false;
+    if (d.nbk1 <= 0 || d.nbv1 <= 0 || d.nbk2 <= 0 || d.nbv2 <= 0) return false;
+    if ((int64_t) d.n_head_kv*d.nbk2 > d.nbk1 || (int64_t) d.n_head_kv*d.nbv2 > d.nbv1) return false;   // heads inside the token row
+    if (d.n_kv*(d.nbk1 > d.nbv1 ? d.nbk1 : d.nbv1) >= (1LL << 40) || d.n_kv >= (1LL << 31)) return false;
+    if (((uintptr_t) d.q | (uint64_t) d.nbq1 | (uint64_t) d.nbq2) & 15) return false;      // float4 loads of Q
     if ((uintptr_t) d.dst & 15) return false;
     return true;
 }
 
-template <int TK, int TV> static int sk_ctas_per_sm() {
-    const int by_smem = (227*1024)/(sk_smem<TK, TV>::CTA + 1024);
-    return by_smem < 1 ? 1 : (by_smem > 2 ? 2 : by_smem);
-}
-
-static int sk_ctas_per_sm_rt(int tk, int tv) {
-    (void) tk; (void) tv;
-    return sk_ctas_per_sm<B200_TYPE_F16, B200_TYPE_F16>();
+template <typename F> static auto sk_dispatch(int tk, int tv, F &&f) {
+#define SK_CASE(K, V) if (tk == K && tv == V) return f(std::integral_constant<int, K>{}, std::integral_constant<int, V>{});
+    SK_CASE(B200_TYPE_F16,  B200_TYPE_F16)  SK_CASE(B200_TYPE_F16,  B200_TYPE_Q8_0) SK_CASE(B200_TYPE_F16,  B200_TYPE_Q4_0)
+    SK_CASE(B200_TYPE_Q8_0, B200_TYPE_F16)  SK_CASE(B200_TYPE_Q8_0, B200_TYPE_Q8_0) SK_CASE(B200_TYPE_Q8_0, B200_TYPE_Q4_0)
+    SK_CASE(B200_TYPE_Q4_0, B200_TYPE_F16)  SK_CASE(B200_TYPE_Q4_0, B200_TYPE_Q8_0)
+#undef SK_CASE
+    return f(std::integral_constant<int, B200_TYPE_Q4_0>{}, std::integral_constant<int, B200_TYPE_Q4_0>{});
 }
 
 static int sk_items(const b200_attn_desc &d) {
-    const int64_t warps = (int64_t) sk_sm_count()*sk_ctas_per_sm_rt(d.type_k, d.type_v)*SK_WARPS;
+    const int cps = sk_dispatch(d.type_k, d.type_v, [](auto k, auto v) { return sk_smem<decltype(k)::value, decltype(v)::value>::CTAS_PER_SM; });
+    const int64_t warps = (int64_t) sk_sm_count()*cps*SK_WARPS;
     int64_t items = warps/d.n_head_kv;
     if (items < 1) items = 1;
     // no more items than 4-tile pieces of the (host-estimated) work: tiny problems stay in few warps
@@ -473,8 +700,49 @@ size_t streamk_workspace(const b200_attn_desc &d) {
          + max_segs*d.n_head*SK_D*sizeof(float);
 }
 
+typedef CUresult (*sk_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                 const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static sk_encode_fn sk_encoder() {
+    static sk_encode_fn fn = nullptr;
+    if (!fn) {
+        void *ptr = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<sk_encode_fn>(ptr);
+        else (void) cudaGetLastError();
+    }
+    return fn;
+}
+
+// One box = the 16 cells of a tile x one head row (see the file header).  The flat cache is cell-major:
+// cell c at base + c*nb1, head h at + h*nb2.
+static bool sk_make_map(CUtensorMap *tm, int type, const void *base, int64_t nb1, int64_t nb2, int n_head_kv, int64_t n_cells) {
+    sk_encode_fn enc = sk_encoder();
+    if (!enc) { set_error("stream-K: cuTensorMapEncodeTiled not available from the driver"); return false; }
+    const cuuint32_t ones[3] = {1, 1, 1};
+    CUresult r;
+    if (type == B200_TYPE_F16) {
+        const cuuint64_t dims[3]    = {64, (cuuint64_t) n_cells, (cuuint64_t) (((int64_t) (n_head_kv - 1)*nb2 + 256)/128)};
+        const cuuint64_t strides[2] = {(cuuint64_t) nb1, 128};
+        const cuuint32_t box[3]     = {64, SK_TILE, 2};
+        r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void *>(base), dims, strides, box, ones,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    } else {
+        const int hb = type == B200_TYPE_Q8_0 ? 136 : 72, win = type == B200_TYPE_Q8_0 ? 144 : 80;
+        const cuuint64_t dims[2]    = {(cuuint64_t) ((int64_t) (n_head_kv - 1)*nb2 + hb), (cuuint64_t) n_cells};
+        const cuuint64_t strides[1] = {(cuuint64_t) nb1};
+        const cuuint32_t box[2]     = {(cuuint32_t) win, SK_TILE};
+        r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(base), dims, strides, box, ones,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    }
+    if (r != CUDA_SUCCESS) { set_error("stream-K: cuTensorMapEncodeTiled failed with %d", (int) r); return false; }
+    return true;
+}
+
 template <int TK, int TV>
-static int sk_launch(const sk_args &a, cudaStream_t st) {
+static int sk_launch(const sk_args &a, const CUtensorMap &tmK, const CUtensorMap &tmV, cudaStream_t st) {
     using SM = sk_smem<TK, TV>;
     static bool configured = false;
     if (!configured) {
@@ -484,7 +752,7 @@ static int sk_launch(const sk_args &a, cudaStream_t st) {
     }
     const int64_t warps = (int64_t) a.n_items*a.d.n_head_kv;
     const unsigned grid = (unsigned) ((warps + SK_WARPS - 1)/SK_WARPS);
-    sk_main_kernel<TK, TV><<<grid, 32*SK_WARPS, SM::CTA, st>>>(a);
+    sk_main_kernel<TK, TV><<<grid, 32*SK_WARPS, SM::CTA, st>>>(a, tmK, tmV);
     return B200_OK;
 }
 
@@ -509,10 +777,14 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st) {
     if (d.logit_softcap != 0.0f) { a.qscale = d.scale/d.logit_softcap; a.cap_log2e = d.logit_softcap*log2e; }
     else                         { a.qscale = d.scale*log2e;           a.cap_log2e = 0.0f; }
 
+    alignas(64) CUtensorMap tmK, tmV;
+    if (!sk_make_map(&tmK, d.type_k, d.k, d.nbk1, d.nbk2, d.n_head_kv, d.n_kv)) return B200_ERR_CUDA;
+    if (!sk_make_map(&tmV, d.type_v, d.v, d.nbv1, d.nbv2, d.n_head_kv, d.n_kv)) return B200_ERR_CUDA;
+
     sk_plan_kernel<<<1, 1024, 0, st>>>(a);
     count_launch();
     if (!check_launch("sk_plan")) return B200_ERR_CUDA;
-    const int rc = sk_launch<B200_TYPE_F16, B200_TYPE_F16>(a, st);
+    const int rc = sk_dispatch(d.type_k, d.type_v, [&](auto k, auto v) { return sk_launch<decltype(k)::value, decltype(v)::value>(a, tmK, tmV, st); });
     if (rc != B200_OK) return rc;
     count_launch();
     if (!check_launch("sk_main")) return B200_ERR_CUDA;
