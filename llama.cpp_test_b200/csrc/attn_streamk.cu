@@ -136,12 +136,27 @@ __device__ __forceinline__ void sts128_zero(uint32_t addr) { asm volatile("st.sh
 __device__ __forceinline__ float h16f(uint32_t bits) { return __half2float(__ushort_as_half((unsigned short) bits)); }
 
 // int8 / nibble -> half by OR-ing the exponent of 1024 (0x6400): half(0x6400 | u) == 1024 + u exactly.
-// Q8_0 bytes are first biased to unsigned (xor 0x80): value = 1152 + q.  Pairs are (byte0, byte2) and (byte1, byte3).
-__device__ __forceinline__ uint32_t q8_e02(uint32_t w) { return (w & 0x00ff00ffu) ^ 0x64806480u; }
-__device__ __forceinline__ uint32_t q8_e13(uint32_t w) { return ((w >> 8) & 0x00ff00ffu) ^ 0x64806480u; }
-// Q4_0: low nibbles give 1024 + n, high nibbles 1024 + 16 n
-__device__ __forceinline__ uint32_t q4_lo(uint32_t w) { return (w & 0x000f000fu) | 0x64006400u; }
-__device__ __forceinline__ uint32_t q4_hi(uint32_t w) { return (w & 0x00f000f0u) | 0x64006400u; }
+// Q8_0: the word is biased to unsigned first (xor 0x80 per byte, one LOP3 per 4 elements), then one PRMT per
+// register pair drops 0x64 above bytes (0, 2) / (1, 3): value = 1152 + q.  k64 is 0x64646464 held in a register.
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+    uint32_t d; asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel)); return d;
+}
+__device__ __forceinline__ uint32_t q8_bias(uint32_t w) { return w ^ 0x80808080u; }
+__device__ __forceinline__ uint32_t q8_e02(uint32_t wb, uint32_t k64) { return prmt(wb, k64, 0x4240); }   // (b0, 0x64, b2, 0x64)
+__device__ __forceinline__ uint32_t q8_e13(uint32_t wb, uint32_t k64) { return prmt(wb, k64, 0x4341); }   // (b1, 0x64, b3, 0x64)
+// Q4_0: (w & mask) | 0x64006400 as ONE three-input LOP3 (mask in a register): low nibbles give 1024 + n,
+// high nibbles 1024 + 16 n
+__device__ __forceinline__ uint32_t lop3_and_or(uint32_t a, uint32_t m, uint32_t c) {
+    uint32_t d; asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(d) : "r"(a), "r"(m), "r"(c)); return d;
+}
+__device__ __forceinline__ uint32_t q4_lo(uint32_t w, uint32_t mlo) { return lop3_and_or(w, mlo, 0x64006400u); }
+__device__ __forceinline__ uint32_t q4_hi(uint32_t w, uint32_t mhi) { return lop3_and_or(w, mhi, 0x64006400u); }
+__device__ __forceinline__ uint32_t hadd2_u(uint32_t a, uint32_t b) {
+    uint32_t d; asm("add.rn.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b)); return d;
+}
+// a constant the optimiser cannot fold back into immediates (keeps it in one register across the loop)
+__device__ __forceinline__ uint32_t sk_opaque(uint32_t v) { asm volatile("mov.b32 %0, %0;" : "+r"(v)); return v; }
+
 // ------------------------------------------------------------------------------------------------
 // plan: tiles per row, prefix sums, chunk, segment slots.  One CTA of 1024 threads.
 // ------------------------------------------------------------------------------------------------
@@ -294,7 +309,7 @@ __device__ __forceinline__ uint32_t sk_ld4(uint32_t row, int off) {
 // Quantised tile: [16 tokens][WIN bytes]; the head row starts `mis` (0 or 8) bytes into each token row.
 // Even blocks: scale in the low half of its word, quants 2 bytes off word alignment; odd blocks: high half, aligned.
 template <int TK>
-__device__ __forceinline__ void sk_qk_quant(float (&S)[4], uint32_t kb, int mis, const sk_qfrag<TK> &q, int lane) {
+__device__ __forceinline__ void sk_qk_quant(float (&S)[4], uint32_t kb, int mis, const sk_qfrag<TK> &q, uint2 kc, int lane) {
     constexpr int WIN = sk_type<TK>::WIN, BLK = sk_type<TK>::BLK;
     const int g = lane >> 2, t = lane & 3;
     const uint32_t row0 = kb + g*WIN + mis, row1 = row0 + 8*WIN;
@@ -306,8 +321,9 @@ __device__ __forceinline__ void sk_qk_quant(float (&S)[4], uint32_t kb, int mis,
             uint32_t A0, A1, B0, B1;
             if (blk & 1) { A0 = sk_ld4<true >(row0, o); A1 = sk_ld4<true >(row1, o); B0 = sk_ld4<true >(row0, o + 16); B1 = sk_ld4<true >(row1, o + 16); }
             else         { A0 = sk_ld4<false>(row0, o); A1 = sk_ld4<false>(row1, o); B0 = sk_ld4<false>(row0, o + 16); B1 = sk_ld4<false>(row1, o + 16); }
-            const uint32_t a[4] = {q8_e02(A0), q8_e02(A1), q8_e13(A0), q8_e13(A1)};
-            const uint32_t c[4] = {q8_e02(B0), q8_e02(B1), q8_e13(B0), q8_e13(B1)};
+            A0 = q8_bias(A0); A1 = q8_bias(A1); B0 = q8_bias(B0); B1 = q8_bias(B1);
+            const uint32_t a[4] = {q8_e02(A0, kc.x), q8_e02(A1, kc.x), q8_e13(A0, kc.x), q8_e13(A1, kc.x)};
+            const uint32_t c[4] = {q8_e02(B0, kc.x), q8_e02(B1, kc.x), q8_e13(B0, kc.x), q8_e13(B1, kc.x)};
             mma_16816(acc, a, q.b[2*blk][0],     q.b[2*blk][1]);
             mma_16816(acc, c, q.b[2*blk + 1][0], q.b[2*blk + 1][1]);
         } else {
@@ -315,8 +331,8 @@ __device__ __forceinline__ void sk_qk_quant(float (&S)[4], uint32_t kb, int mis,
             if (blk & 1) { W0 = sk_ld4<true >(row0, o); W1 = sk_ld4<true >(row1, o); }
             else         { W0 = sk_ld4<false>(row0, o); W1 = sk_ld4<false>(row1, o); }
             const uint32_t Y0 = W0 >> 8, Y1 = W1 >> 8;
-            const uint32_t a[4] = {q4_lo(W0), q4_lo(W1), q4_lo(Y0), q4_lo(Y1)};
-            const uint32_t c[4] = {q4_hi(W0), q4_hi(W1), q4_hi(Y0), q4_hi(Y1)};
+            const uint32_t a[4] = {q4_lo(W0, kc.x), q4_lo(W1, kc.x), q4_lo(Y0, kc.x), q4_lo(Y1, kc.x)};
+            const uint32_t c[4] = {q4_hi(W0, kc.y), q4_hi(W1, kc.y), q4_hi(Y0, kc.y), q4_hi(Y1, kc.y)};
             mma_16816(acc, a, q.b[2*blk][0],     q.b[2*blk][1]);
             mma_16816(acc, c, q.b[2*blk + 1][0], q.b[2*blk + 1][1]);
         }
@@ -331,12 +347,11 @@ __device__ __forceinline__ void sk_qk_quant(float (&S)[4], uint32_t kb, int mis,
 }
 
 // ------------------------------------------------------------------------------------------------
-// O^T += V^T . P^T ; 8 m-tiles of 16 d-rows.  OW = extra accumulators of sum_tok P*d_blk (quantised V only):
-// the A operand holds (128 + q) d for Q8_0 and n d for Q4_0 (the -1024 d of the exponent trick is exact in half,
-// the -128 d / -8 d is not), so 128 W / 8 W is subtracted once per segment in sk_store.
+// O^T += V^T . P^T ; 8 m-tiles of 16 d-rows.  Quantised V: the biased integer of the exponent trick is brought
+// back to the exact signed integer with one half2 add (1152 + q -> q, 1024 + n -> n - 8, 1024 + 16 n -> n - 8 by
+// one fma with 1/16), then scaled by the token pair's block scales: one rounding, like dequantize_row_*
+// (ggml/src/ggml-quants.c:255-273, :349-362) followed by a half conversion.
 // ------------------------------------------------------------------------------------------------
-template <int TV> struct sk_vacc { static constexpr int NW = TV == B200_TYPE_F16 ? 1 : TV == B200_TYPE_Q8_0 ? 4 : 2; };
-
 __device__ __forceinline__ void sk_pv_f16(float (&O)[8][4], uint32_t vb, uint32_t p0, uint32_t p1, int lane) {
     const int tau = (lane & 7) + 8*(lane >> 4);
     const uint32_t base = vb + tau*128;
@@ -350,66 +365,60 @@ __device__ __forceinline__ void sk_pv_f16(float (&O)[8][4], uint32_t vb, uint32_
 }
 
 template <int TV>
-__device__ __forceinline__ void sk_pv_quant(float (&O)[8][4], float (&OW)[sk_vacc<TV>::NW][4], uint32_t vb, int mis,
-                                            uint32_t p0, uint32_t p1, int lane) {
+__device__ __forceinline__ void sk_pv_quant(float (&O)[8][4], uint32_t vb, int mis, uint32_t p0, uint32_t p1, uint2 kc, int lane) {
     constexpr int WIN = sk_type<TV>::WIN, BLK = sk_type<TV>::BLK;
     const int g = lane >> 2, t = lane & 3;
     const uint32_t r0 = vb + 2*t*WIN + mis, r1 = r0 + WIN, r2 = r0 + 8*WIN, r3 = r2 + WIN;   // tokens 2t, 2t+1, 2t+8, 2t+9
-    constexpr uint32_t M1024 = 0xE400E400u;                  // half2(-1024)
     if constexpr (TV == B200_TYPE_Q8_0) {
+        constexpr uint32_t M1152 = 0xE480E480u;              // half2(-1152)
 #pragma unroll
         for (int blk = 0; blk < 4; ++blk) {
             const int so = (BLK*blk) & ~3;
             const uint32_t sel = (blk & 1) ? 0x7632 : 0x5410;
-            const uint32_t sp01 = __byte_perm(lds32(r0 + so), lds32(r1 + so), sel);           // (d[2t], d[2t+1])
-            const uint32_t sp23 = __byte_perm(lds32(r2 + so), lds32(r3 + so), sel);
-            const uint32_t of01 = hmul2_u(sp01, M1024), of23 = hmul2_u(sp23, M1024);
+            const uint32_t sp01 = prmt(lds32(r0 + so), lds32(r1 + so), sel);                  // (d[2t], d[2t+1])
+            const uint32_t sp23 = prmt(lds32(r2 + so), lds32(r3 + so), sel);
             const int o = BLK*blk + 2 + 4*g;
             uint32_t W0, W1, W2, W3;
             if (blk & 1) { W0 = sk_ld4<true >(r0, o); W1 = sk_ld4<true >(r1, o); W2 = sk_ld4<true >(r2, o); W3 = sk_ld4<true >(r3, o); }
             else         { W0 = sk_ld4<false>(r0, o); W1 = sk_ld4<false>(r1, o); W2 = sk_ld4<false>(r2, o); W3 = sk_ld4<false>(r3, o); }
-            const uint32_t x01l = __byte_perm(W0, W1, 0x5410), x01h = __byte_perm(W0, W1, 0x7632);
-            const uint32_t x23l = __byte_perm(W2, W3, 0x5410), x23h = __byte_perm(W2, W3, 0x7632);
-            const uint32_t a[4] = {hfma2_u(q8_e02(x01l), sp01, of01), hfma2_u(q8_e13(x01l), sp01, of01),
-                                   hfma2_u(q8_e02(x23l), sp23, of23), hfma2_u(q8_e13(x23l), sp23, of23)};
-            const uint32_t c[4] = {hfma2_u(q8_e02(x01h), sp01, of01), hfma2_u(q8_e13(x01h), sp01, of01),
-                                   hfma2_u(q8_e02(x23h), sp23, of23), hfma2_u(q8_e13(x23h), sp23, of23)};
+            const uint32_t x01l = q8_bias(prmt(W0, W1, 0x5410)), x01h = q8_bias(prmt(W0, W1, 0x7632));
+            const uint32_t x23l = q8_bias(prmt(W2, W3, 0x5410)), x23h = q8_bias(prmt(W2, W3, 0x7632));
+            auto deq = [&](uint32_t e, uint32_t sp) { return hmul2_u(hadd2_u(e, M1152), sp); };
+            const uint32_t a[4] = {deq(q8_e02(x01l, kc.x), sp01), deq(q8_e13(x01l, kc.x), sp01),
+                                   deq(q8_e02(x23l, kc.x), sp23), deq(q8_e13(x23l, kc.x), sp23)};
+            const uint32_t c[4] = {deq(q8_e02(x01h, kc.x), sp01), deq(q8_e13(x01h, kc.x), sp01),
+                                   deq(q8_e02(x23h, kc.x), sp23), deq(q8_e13(x23h, kc.x), sp23)};
             mma_16816(O[2*blk],     a, p0, p1);
             mma_16816(O[2*blk + 1], c, p0, p1);
-            const uint32_t w[4] = {sp01, 0u, sp23, 0u};
-            mma_16816(OW[blk], w, p0, p1);
         }
     } else {
-        constexpr uint32_t R16 = 0x2C002C00u, M64 = 0xD400D400u;   // half2(1/16), half2(-64)
+        constexpr uint32_t M1032 = 0xE408E408u, R16 = 0x2C002C00u, M72 = 0xD480D480u;   // half2(-1032), (1/16), (-72)
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
             const int odd = g >> 2, bb = 2*k + odd, wq = g & 3;      // this lane's block of the pair (2k, 2k+1)
             const int so = (BLK*bb) & ~3;
             const uint32_t sel = odd ? 0x7632 : 0x5410;
-            const uint32_t sp01 = __byte_perm(lds32(r0 + so), lds32(r1 + so), sel);
-            const uint32_t sp23 = __byte_perm(lds32(r2 + so), lds32(r3 + so), sel);
-            const uint32_t sq01 = hmul2_u(sp01, R16), sq23 = hmul2_u(sp23, R16);
-            const uint32_t ol01 = hmul2_u(sp01, M1024), ol23 = hmul2_u(sp23, M1024);
-            const uint32_t oh01 = hmul2_u(sp01, M64), oh23 = hmul2_u(sp23, M64);
+            const uint32_t sp01 = prmt(lds32(r0 + so), lds32(r1 + so), sel);
+            const uint32_t sp23 = prmt(lds32(r2 + so), lds32(r3 + so), sel);
             const int o = BLK*bb + 2 + 4*wq, oa = o & ~3;
             const uint32_t fsel = odd ? 0x3210 : 0x5432;              // odd blocks are word aligned
-            const uint32_t W0 = __byte_perm(lds32(r0 + oa), lds32(r0 + oa + 4), fsel);
-            const uint32_t W1 = __byte_perm(lds32(r1 + oa), lds32(r1 + oa + 4), fsel);
-            const uint32_t W2 = __byte_perm(lds32(r2 + oa), lds32(r2 + oa + 4), fsel);
-            const uint32_t W3 = __byte_perm(lds32(r3 + oa), lds32(r3 + oa + 4), fsel);
+            const uint32_t W0 = prmt(lds32(r0 + oa), lds32(r0 + oa + 4), fsel);
+            const uint32_t W1 = prmt(lds32(r1 + oa), lds32(r1 + oa + 4), fsel);
+            const uint32_t W2 = prmt(lds32(r2 + oa), lds32(r2 + oa + 4), fsel);
+            const uint32_t W3 = prmt(lds32(r3 + oa), lds32(r3 + oa + 4), fsel);
+            auto dlo = [&](uint32_t e, uint32_t sp) { return hmul2_u(hadd2_u(e, M1032), sp); };          // (1024 + n) - 1032
+            auto dhi = [&](uint32_t e, uint32_t sp) { return hmul2_u(hfma2_u(e, R16, M72), sp); };       // (1024 + 16 n)/16 - 72
 #pragma unroll
             for (int hb = 0; hb < 2; ++hb) {                           // bytes (0,1) then (2,3) of the word
-                const uint32_t x01 = __byte_perm(W0, W1, hb ? 0x7632 : 0x5410), x23 = __byte_perm(W2, W3, hb ? 0x7632 : 0x5410);
+                const uint32_t x01 = prmt(W0, W1, hb ? 0x7632 : 0x5410), x23 = prmt(W2, W3, hb ? 0x7632 : 0x5410);
                 const uint32_t y01 = x01 >> 8, y23 = x23 >> 8;
-                const uint32_t a[4] = {hfma2_u(q4_lo(x01), sp01, ol01), hfma2_u(q4_lo(y01), sp01, ol01),
-                                       hfma2_u(q4_lo(x23), sp23, ol23), hfma2_u(q4_lo(y23), sp23, ol23)};
-                const uint32_t c[4] = {hfma2_u(q4_hi(x01), sq01, oh01), hfma2_u(q4_hi(y01), sq01, oh01),
-                                       hfma2_u(q4_hi(x23), sq23, oh23), hfma2_u(q4_hi(y23), sq23, oh23)};
+                const uint32_t a[4] = {dlo(q4_lo(x01, kc.x), sp01), dlo(q4_lo(y01, kc.x), sp01),
+                                       dlo(q4_lo(x23, kc.x), sp23), dlo(q4_lo(y23, kc.x), sp23)};
+                const uint32_t c[4] = {dhi(q4_hi(x01, kc.y), sp01), dhi(q4_hi(y01, kc.y), sp01),
+                                       dhi(q4_hi(x23, kc.y), sp23), dhi(q4_hi(y23, kc.y), sp23)};
                 mma_16816(O[4*k + 2*hb],     a, p0, p1);
                 mma_16816(O[4*k + 2*hb + 1], c, p0, p1);
             }
-            const uint32_t w[4] = {sp01, 0u, sp23, 0u};
-            mma_16816(OW[k], w, p0, p1);
         }
     }
 }
@@ -421,9 +430,6 @@ __device__ __forceinline__ int sk_row_d(int mt, int h, int g) {
     else if constexpr (TV == B200_TYPE_Q8_0) return 32*(mt >> 1) + 4*g + 2*(mt & 1) + h;
     else { const int bb = 2*(mt >> 2) + (g >> 2); return 32*bb + 4*(g & 3) + 16*(mt & 1) + 2*((mt >> 1) & 1) + h; }
 }
-template <int TV> __device__ __forceinline__ int sk_row_w(int mt) {
-    if constexpr (TV == B200_TYPE_Q8_0) return mt >> 1; else if constexpr (TV == B200_TYPE_Q4_0) return mt >> 2; else return 0;
-}
 // ------------------------------------------------------------------------------------------------
 // main kernel
 // ------------------------------------------------------------------------------------------------
@@ -432,7 +438,7 @@ __global__ void __launch_bounds__(32*SK_WARPS, sk_smem<TK, TV>::CTAS_PER_SM)
 sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV) {
     extern __shared__ __align__(1024) char sk_dyn[];
     using SM = sk_smem<TK, TV>;
-    constexpr int STAGES = SM::STAGES, NW = sk_vacc<TV>::NW;
+    constexpr int STAGES = SM::STAGES;
     const b200_attn_desc &p = a.d;
     int lane = threadIdx.x & 31;
     asm volatile("mov.b32 %0, %0;" : "+r"(lane));             // pin in a register: ptxas otherwise re-reads SR_TID in the loop
@@ -471,6 +477,9 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
     const int bs = p.block_size, tpb = bs/SK_TILE;                                    // tiles per block (bs % 16 == 0)
     const int n_blk = p.bt_stride < INT32_MAX ? (int) p.bt_stride : INT32_MAX;
     uint32_t it = 0;                                                                  // tiles consumed by this warp so far
+    // expansion constants, one register each: Q8_0 {0x64646464}, Q4_0 {low-nibble mask, high-nibble mask}
+    const uint2 kcon = make_uint2(sk_opaque(TK == B200_TYPE_Q8_0 ? 0x64646464u : 0x000f000fu), sk_opaque(0x00f000f0u));
+    const uint2 vcon = TK == TV ? kcon : make_uint2(sk_opaque(TV == B200_TYPE_Q8_0 ? 0x64646464u : 0x000f000fu), sk_opaque(0x00f000f0u));
 
     while (g0 < g1) {
         const int pb = P[row], pe = P[row + 1];
@@ -491,11 +500,9 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
             qf.load(qrow, live, a.qscale, lane);
         }
 
-        float O[8][4], OW[NW][4];
+        float O[8][4];
 #pragma unroll
         for (int mu = 0; mu < 8; ++mu) { O[mu][0] = O[mu][1] = O[mu][2] = O[mu][3] = 0.f; }
-#pragma unroll
-        for (int w = 0; w < NW; ++w) { OW[w][0] = OW[w][1] = OW[w][2] = OW[w][3] = 0.f; }
         float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;   // columns 2t, 2t+1
 
         // block-table window: lane l holds entry win_base + l; the next window is fetched 32 blocks ahead, so the
@@ -545,7 +552,7 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
 
             float S[4] = {0.f, 0.f, 0.f, 0.f};
             if constexpr (TK == B200_TYPE_F16) sk_qk_f16(S, kb, qf, lane);
-            else                               sk_qk_quant<TK>(S, kb, kmis, qf, lane);
+            else                               sk_qk_quant<TK>(S, kb, kmis, qf, kcon, lane);
 
             if (p.logit_softcap != 0.0f) {
 #pragma unroll
@@ -570,26 +577,14 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
             if (__any_sync(0xffffffffu, al0 != 1.0f || al1 != 1.0f)) {
 #pragma unroll
                 for (int mu = 0; mu < 8; ++mu) { O[mu][0] *= al0; O[mu][1] *= al1; O[mu][2] *= al0; O[mu][3] *= al1; }
-                if constexpr (TV != B200_TYPE_F16) {
-#pragma unroll
-                    for (int w = 0; w < NW; ++w) { OW[w][0] *= al0; OW[w][1] *= al1; }
-                }
             }
             const uint32_t pt0 = movmatrix_trans(pack_h2(p00, p01));
             const uint32_t pt1 = movmatrix_trans(pack_h2(p10, p11));
             if constexpr (TV == B200_TYPE_F16) sk_pv_f16(O, vb, pt0, pt1, lane);
-            else                               sk_pv_quant<TV>(O, OW, vb, vmis, pt0, pt1, lane);
+            else                               sk_pv_quant<TV>(O, vb, vmis, pt0, pt1, vcon, lane);
         }
 
         // ---- segment epilogue
-        if constexpr (TV != B200_TYPE_F16) {                 // remove the 128 d (Q8_0) / 8 d (Q4_0) the A operand carried
-            constexpr float C = TV == B200_TYPE_Q8_0 ? 128.0f : 8.0f;
-#pragma unroll
-            for (int mu = 0; mu < 8; ++mu) {
-                const int w = sk_row_w<TV>(mu);
-                O[mu][0] -= C*OW[w][0]; O[mu][1] -= C*OW[w][1]; O[mu][2] -= C*OW[w][0]; O[mu][3] -= C*OW[w][1];
-            }
-        }
 #pragma unroll
         for (int o = 4; o < 32; o <<= 1) {                   // row sums over the 8 token groups
             l0 += __shfl_xor_sync(0xffffffffu, l0, o);

@@ -300,8 +300,10 @@ def test_full_size_properties_config2(pkg, oracle, cuda, t):
                 continue
             call.run(); torch.cuda.synchronize()
             outs.append(out.cpu().numpy())
+    # generic (FP32 CUDA cores) vs stream-K (half-precision mma operands, FP32 accumulation): the half rounding of
+    # Q, P and the dequantised V is ~2.4e-4 rms per element, so kernel-to-kernel agreement is bounded by the F16 bar
     for o in outs[1:]:
-        assert oracle.max_rel_err(outs[0], o) <= 1e-3
+        assert oracle.max_rel_err(outs[0], o) <= 2e-3
     # sampled rows against the oracle (3 shortest sequences keep the CPU time in seconds)
     bt, slot = build(2)
     rows = np.argsort(lens)[:3]
