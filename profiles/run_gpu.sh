@@ -1,0 +1,20 @@
+#!/bin/bash
+# profiles/run_gpu.sh TAG — the round's standard GPU pass (run under gpurun): parity tests, bench lines for the
+# three KV types + the reference arm, the ncu launch list and one --set full capture of the dominant kernel.
+TAG=${1:-rX}
+O=gpurun_out
+mkdir -p $O
+python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest.log 2>&1; echo "pytest rc=$?" >> $O/${TAG}_pytest.log
+tail -3 $O/${TAG}_pytest.log
+python -c "import __graft_entry__ as g; g.smoke()" > $O/${TAG}_smoke.log 2>&1; tail -1 $O/${TAG}_smoke.log
+for T in q8_0 f16 q4_0; do
+  python bench.py --kv-type $T > $O/${TAG}_bench_$T.log 2>&1; tail -c 600 $O/${TAG}_bench_$T.log; echo
+done
+python bench.py --impl reference --steps 3 --warmup 1 > $O/${TAG}_bench_reference.log 2>&1; tail -c 400 $O/${TAG}_bench_reference.log; echo
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches.csv \
+    python bench.py --layers 4 --steps 2 --warmup 3 --no-graph --no-cpu-baseline > $O/${TAG}_ncu_list.log 2>&1
+for T in q8_0 q4_0 f16; do
+  ncu --set full --clock-control none --import-source on -k regex:sk_main -s 4 -c 1 -o $O/${TAG}_sk_$T -f \
+    python bench.py --kv-type $T --layers 2 --steps 2 --warmup 3 --no-graph --no-cpu-baseline > $O/${TAG}_ncu_$T.log 2>&1
+done
+ls -la $O | tail -15
