@@ -1,23 +1,25 @@
 #!/usr/bin/env python
-"""bench.py — paged-attn decode KV-read GB/s (BASELINE.json metric) on BASELINE config 2.
+"""bench.py — paged-attn decode KV-read GB/s (BASELINE.json metric); default workload = BASELINE config 2.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--kv-type q8_0|q4_0|f16] [--impl b200|reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload config2|config1|config4] [--kv-type q8_0|q4_0|f16]
+                  [--impl b200|reference]
 
-Workload ("config2_llama3_8b_<type>"): Llama-3-8B attention shape (32 q / 8 kv heads, d = 128, 32 layers), 64
-sequences with context lengths ~ U{512..8192} (seed 7 + rank), 16-token blocks scattered by a random
-permutation, Q8_0 (default) / Q4_0 / F16 KV cache, synthetic U(-1,1) data.  One STEP = one decode step of the
-hot path = the attention op of all 32 layers, each over its own KV cache (19 GB of Q8_0 KV per GPU, far
-beyond the 126 MB L2, so no flush is needed between iterations).
+Workloads (all synthetic U(-1,1) data, 16-token blocks scattered by a seeded random permutation):
+  config2  (default; the configuration the metric is quoted on) Llama-3-8B attention shape (32 q / 8 kv heads,
+           d = 128, 32 layers), 64 sequences with context ~ U{512..8192} (seed 7 + rank), Q8_0 (default) / Q4_0 /
+           F16 KV.  Multi-GPU: sequence-batch sharding, every rank holds its own 64 sequences => "weak".
+  config1  same shape, 8 sequences x 1024 context, F16 (the reference's CPU-runnable case; latency-bound).
+  config4  Llama-3-70B shape (64 q / 8 kv heads), 32 sequences x 32768 context, F16, 8 layers resident;
+           KV heads sharded over the ranks + ONE NCCL all-gather of the outputs per layer => "strong".
+One STEP = one decode step of the hot path = the attention op of every layer, each over its own KV cache (GBs per
+step, far beyond the 126 MB L2, so no flush is needed between iterations).
 
-  value       whole-job KV GB/s with everything resident in HBM (CUDA-graph replay of the 32 layer ops)
-  e2e         same metric through the C ABI the way a host uses it per step: pinned-host Q / new K,V rows /
-              block table / seq_lens copied H2D, b200_kv_write + b200_paged_attention per layer, outputs D2H
-  roofline    op-level achieved GB/s = algorithmic KV bytes / CUDA-event time, vs MEASURED_PEAKS.json
-  cpu_baseline the reference's own ggml CPU FLASH_ATTN_EXT (oracle/_ref) on one layer-op of the same workload
-
-Multi-GPU (torchrun, one rank per GPU): sequences shard across ranks with no data-path collective
-(SURVEY.md §8e partitioning A), each rank runs the same per-GPU workload => "scaling": "weak"; time is the
-max over ranks of the CUDA-event time.
+  value        whole-job KV GB/s with everything resident in HBM (CUDA-graph replay when no collective is inside)
+  e2e          same metric through the C ABI the way a host uses it per step: pinned-host Q / new K,V rows / block
+               table / seq_lens copied H2D (copy stream, overlapped layer by layer), b200_kv_write +
+               b200_paged_attention per layer, outputs D2H, host waits for the last byte
+  roofline     op-level achieved GB/s = algorithmic KV bytes of one layer-op / CUDA-event time, vs MEASURED_PEAKS.json
+  cpu_baseline the reference's own ggml CPU FLASH_ATTN_EXT (oracle/_ref) on a bounded sample of the same workload
 """
 from __future__ import annotations
 
@@ -36,15 +38,26 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 TYPES = {"f16": 1, "q4_0": 2, "q8_0": 8}
-N_HEAD, N_HEAD_KV, D, BS, N_LAYER, N_SEQS = 32, 8, 128, 16, 32, 64
+D, BS = 128, 16
+WORKLOADS = {
+    "config2": dict(n_head=32, n_head_kv=8, n_layer=32, n_seqs=64, ctx="U{512..8192} seed 7+rank", shard="sequences",
+                    scaling="weak", kv_type="q8_0", steps=100),
+    "config1": dict(n_head=32, n_head_kv=8, n_layer=32, n_seqs=8, ctx="1024", shard="sequences", scaling="weak",
+                    kv_type="f16", steps=500),
+    "config4": dict(n_head=64, n_head_kv=8, n_layer=8, n_seqs=32, ctx="32768", shard="heads", scaling="strong",
+                    kv_type="f16", steps=50),
+}
 
 
 def row_bytes(t, n):
     return {1: n * 2, 8: n // 32 * 34, 2: n // 32 * 18}[t]
 
 
-def ctx_lens(rank):
-    return np.random.default_rng(7 + rank).integers(512, 8193, size=N_SEQS).astype(np.int32)
+def ctx_lens(workload, rank):
+    w = WORKLOADS[workload]
+    if workload == "config2":
+        return np.random.default_rng(7 + rank).integers(512, 8193, size=w["n_seqs"]).astype(np.int32)
+    return np.full(w["n_seqs"], int(w["ctx"]), dtype=np.int32)
 
 
 def block_tables(lens, seed=42):
@@ -66,6 +79,17 @@ def peaks():
         with open(p) as f:
             return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic(kv_type):
+    """dram bytes read+written by the dominant kernel for one layer-op of config 2, from the committed
+    `ncu --set full` capture (profiles/traffic.json, written by profiles/summarize.py) — None if absent"""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(p) as f:
+            return json.load(f).get(kv_type)
+    except Exception:
+        return None
 
 
 class ClockSampler(threading.Thread):
@@ -98,67 +122,90 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(self.rows)}
 
 
+
+
+def cpu_sample(workload):
+    """the bounded slice of the workload the CPU arm times: (ctx lens, n_head, n_head_kv, description)"""
+    w = WORKLOADS[workload]
+    lens = ctx_lens(workload, 0)
+    if workload == "config4":          # 4 of the 32 sequences, 1 of the 8 kv heads (with its 8 query heads)
+        return lens[:4], w["n_head"] // w["n_head_kv"], 1, "4 of 32 sequences x 1 of 8 kv heads of one layer-op"
+    return lens, w["n_head"], w["n_head_kv"], f"one layer-op of the full workload (1/{w['n_layer']} of a step)"
+
+
+def cpu_layer_op(workload, t, steps, warmup):
+    """time the reference CPU implementation on the sample; returns (sample, GB/s, cores, kind, ms per op)"""
+    from oracle.loader import Oracle, Ref
+    from workloads import make_workload
+    orc, ref = Oracle(), Ref.load()
+    lens, n_head, n_head_kv, what = cpu_sample(workload)
+    w = make_workload(orc, lens, n_head, n_head_kv, D, t, seed=1234, spare_blocks=0)
+    kv_bytes = w.kv_bytes()
+    if ref is not None:
+        mask = w.dense_mask()
+        n_iter = max(1, warmup + steps)
+        _, us = ref.attention(0, w.q, w.k_cache, w.v_cache, t, t, n_head_kv, w.n_cells, mask, w.scale, n_iter=n_iter)
+        kind, cores = "reference", ref.n_threads
+        sample = (f"{what}: ggml CPU GGML_OP_FLASH_ATTN_EXT, flat cache of {w.n_cells} cells + dense F16 mask, "
+                  f"{cores} threads, isa {ref.isa}, best of {n_iter}")
+    else:
+        t0 = time.perf_counter()
+        rows = np.argsort(lens)[:4]
+        orc.attention(w.q[rows], w.k_cache, w.v_cache, t, t, n_head_kv, w.scale, block_table=w.block_table[rows],
+                      seq_lens=lens[rows], block_size=BS)
+        us = (time.perf_counter() - t0) * 1e6
+        kv_bytes = int(lens[rows].sum()) * n_head_kv * 2 * row_bytes(t, D)
+        kind, cores = "port", 1
+        sample = f"oracle port (scalar C), the 4 shortest sequences of: {what}"
+    return sample, kv_bytes / us / 1e3, cores, kind, us / 1e3
+
+
+def workload_config(workload, kv_type, world):
+    w = WORKLOADS[workload]
+    return {"workload": f"{workload}_{'llama3_70b' if w['n_head'] == 64 else 'llama3_8b'}_{kv_type}", "n_seqs": w["n_seqs"],
+            "ctx": w["ctx"], "block_size": BS, "n_head": w["n_head"], "n_head_kv": w["n_head_kv"], "head_dim": D,
+            "parallelism": (f"sequence-batch sharding x{world}, no collective" if w["shard"] == "sequences"
+                            else f"KV-head sharding x{world} + one NCCL all-gather of the outputs per layer")}
+
+
 def reference_arm(args, rank, world):
     """the reference's own CPU implementation of the path (oracle/_ref: ggml FLASH_ATTN_EXT on the flat cache with
-    the dense F16 mask, SURVEY.md §8d "CPU baseline timing"), all host threads, one layer-op per step"""
+    the dense F16 mask, SURVEY.md §8d "CPU baseline timing"), all host threads, one bounded sample per step"""
     if rank != 0:
         return
-    from oracle.loader import Oracle, Ref
     t = TYPES[args.kv_type]
-    sample, value, cores, kind, ms = cpu_layer_op(t, args.steps, args.warmup)
+    sample, value, cores, kind, ms = cpu_layer_op(args.workload, t, args.steps, args.warmup)
     line = {"impl": "reference", "metric": "paged-attn decode KV-read GB/s", "value": value, "unit": "GB/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": args.kv_type, "data": "synthetic",
-            "config": {"workload": f"config2_llama3_8b_{args.kv_type}", "n_seqs": N_SEQS, "ctx": "U{512..8192} seed 7",
-                       "block_size": BS, "n_head": N_HEAD, "n_head_kv": N_HEAD_KV, "head_dim": D},
+            "scaling": WORKLOADS[args.workload]["scaling"], "vs_baseline": None, "dtype": args.kv_type, "data": "synthetic",
+            "config": workload_config(args.workload, args.kv_type, world),
             "cpu_baseline": {"value": value, "unit": "GB/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
 
-def cpu_layer_op(t, steps, warmup):
-    """time one layer-op of the rank-0 workload on the host cores; returns (sample, GB/s, cores, kind, ms)"""
-    from oracle.loader import Oracle, Ref
-    from workloads import make_workload
-    orc, ref = Oracle(), Ref.load()
-    lens = ctx_lens(0)
-    w = make_workload(orc, lens, N_HEAD, N_HEAD_KV, D, t, seed=1234, spare_blocks=0)
-    kv_bytes = w.kv_bytes()
-    if ref is not None:
-        mask = w.dense_mask()
-        n_iter = max(1, warmup + steps)
-        _, us = ref.attention(0, w.q, w.k_cache, w.v_cache, t, t, N_HEAD_KV, w.n_cells, mask, w.scale, n_iter=n_iter)
-        kind, cores = "reference", ref.n_threads
-        sample = (f"one layer-op of the full workload (1/{N_LAYER} of a step): ggml CPU GGML_OP_FLASH_ATTN_EXT, flat cache "
-                  f"of {w.n_cells} cells + dense F16 mask, {cores} threads, isa {ref.isa}, best of {n_iter}")
-    else:
-        t0 = time.perf_counter()
-        rows = np.argsort(lens)[:4]
-        orc.attention(w.q[rows], w.k_cache, w.v_cache, t, t, N_HEAD_KV, w.scale, block_table=w.block_table[rows],
-                      seq_lens=lens[rows], block_size=BS)
-        us = (time.perf_counter() - t0) * 1e6
-        kv_bytes = int(lens[rows].sum()) * N_HEAD_KV * 2 * row_bytes(t, D)
-        kind, cores = "port", 1
-        sample = "oracle port (scalar C), the 4 shortest sequences of one layer-op"
-    return sample, kv_bytes / us / 1e3, cores, kind, us / 1e3
-
-
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=0, help="timed steps (0: the workload's default)")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--kv-type", default="q8_0", choices=list(TYPES))
+    ap.add_argument("--workload", default="config2", choices=list(WORKLOADS))
+    ap.add_argument("--kv-type", default=None, choices=list(TYPES))
     ap.add_argument("--kernel", type=int, default=0, help="0 auto, 1 generic, 2 stream-K")
-    ap.add_argument("--layers", type=int, default=N_LAYER)
+    ap.add_argument("--layers", type=int, default=0)
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the end-to-end leg")
     args = ap.parse_args()
+    W = WORKLOADS[args.workload]
+    args.kv_type = args.kv_type or W["kv_type"]
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
     if args.impl == "reference":
+        args.steps = args.steps or 3
         return reference_arm(args, rank, world)
+    args.steps = args.steps or W["steps"]
     args.warmup = max(args.warmup, 3)
 
     import torch
@@ -170,12 +217,17 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     t = TYPES[args.kv_type]
-    n_layer = args.layers
-    lens = ctx_lens(rank)
+    n_layer = args.layers or W["n_layer"]
+    n_seqs = W["n_seqs"]
+    by_heads = W["shard"] == "heads"
+    sh = pkg.head_shard(rank if by_heads else 0, world if by_heads else 1, W["n_head"], W["n_head_kv"])
+    n_head, n_head_kv = sh.n_head, sh.n_head_kv              # what THIS rank computes
+    collective = by_heads and world > 1
+    lens = ctx_lens(args.workload, rank)
     bt_h, slot_h, n_blocks = block_tables(lens)
     total = int(lens.sum())
-    lay = pkg.KVLayout(t, N_HEAD_KV, D, BS, n_blocks + 8)
-    kv_bytes_op = total * N_HEAD_KV * 2 * row_bytes(t, D)
+    lay = pkg.KVLayout(t, n_head_kv, D, BS, n_blocks + 8)
+    kv_bytes_op = total * n_head_kv * 2 * row_bytes(t, D)    # algorithmic bytes of one layer-op on this rank
     scale = float(1.0 / np.sqrt(D))
     dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
 
@@ -183,26 +235,35 @@ def main():
     gen = torch.Generator(device="cuda"); gen.manual_seed(1234 + rank)
     slot_d, bt_d, sl_d = dev(slot_h), dev(bt_h), dev(lens)
     kcs, vcs = [], []
+    CH = 65536
     for _ in range(n_layer):
         kc, vc = lay.alloc(), lay.alloc()
-        ks = torch.rand((total, N_HEAD_KV * D), generator=gen, device="cuda") * 2 - 1
-        vs = torch.rand((total, N_HEAD_KV * D), generator=gen, device="cuda") * 2 - 1
-        pkg.kv_write(ks, vs, slot_d, kc, vc, lay)
+        for o in range(0, total, CH):
+            n = min(CH, total - o)
+            ks = torch.rand((n, n_head_kv * D), generator=gen, device="cuda") * 2 - 1
+            vs = torch.rand((n, n_head_kv * D), generator=gen, device="cuda") * 2 - 1
+            pkg.kv_write(ks, vs, slot_d[o:o + n], kc, vc, lay)
         kcs.append(kc); vcs.append(vc)
     del ks, vs
-    q_d = torch.rand((n_layer, N_SEQS, N_HEAD, D), generator=gen, device="cuda") * 2 - 1
+    q_d = torch.rand((n_layer, n_seqs, n_head, D), generator=gen, device="cuda") * 2 - 1
     out_d = torch.empty_like(q_d)
+    gathered = torch.empty((n_layer, world, n_seqs, n_head, D), device="cuda") if collective else None
     calls = [pkg.AttnCall(q_d[l], kcs[l], vcs[l], lay, out_d[l], scale, block_table=bt_d, seq_lens=sl_d,
                           max_seq_len=int(lens.max()), total_tokens=total, kernel=args.kernel) for l in range(n_layer)]
     torch.cuda.synchronize()
 
+    def layer_op(l):
+        calls[l].run()
+        if collective:
+            pkg.gather_head_outputs(out_d[l], gathered[l])
+
     def step_resident():
-        for c in calls:
-            c.run()
+        for l in range(n_layer):
+            layer_op(l)
 
     l0 = pkg.lib.b200_launch_count(); step_resident(); launches_per_step = pkg.lib.b200_launch_count() - l0
     graph = None
-    if not args.no_graph:
+    if not args.no_graph and not collective:
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
@@ -236,67 +297,86 @@ def main():
 
     sampler = ClockSampler(local); sampler.start()
     ms_total = timed(run_step, args.steps, args.warmup)
-    clocks = sampler.summary()
     ms_step = ms_total / args.steps
     bytes_step_rank = kv_bytes_op * n_layer
-    # every rank holds the same amount of work (weak scaling); whole-job bytes = sum over ranks
-    tot = torch.tensor([float(bytes_step_rank), float(N_SEQS)], device="cuda", dtype=torch.float64)
+    # whole-job bytes = sum over ranks (weak: every rank holds its own sequences; strong: its own kv heads)
+    tot = torch.tensor([float(bytes_step_rank), float(n_seqs)], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(tot)
     value = tot[0].item() / (ms_step * 1e-3) / 1e9
-    tok_s = tot[1].item() / (ms_step * 1e-3)
+    tok_s = (tot[1].item() if not by_heads else float(n_seqs)) / (ms_step * 1e-3)
 
-    # ---- end to end through the C ABI with HOST buffers (per step: H2D inputs, kv_write + attention, D2H outputs)
-    q_h = torch.rand((n_layer, N_SEQS, N_HEAD, D)).pin_memory()
-    knew_h = (torch.rand((n_layer, N_SEQS, N_HEAD_KV * D)) * 2 - 1).pin_memory()
-    vnew_h = (torch.rand((n_layer, N_SEQS, N_HEAD_KV * D)) * 2 - 1).pin_memory()
-    bt_hp, sl_hp = torch.from_numpy(bt_h).pin_memory(), torch.from_numpy(lens).pin_memory()
-    # the step's new token of each sequence overwrites its last cached position (cache stays the same size)
-    last = np.cumsum(lens.astype(np.int64)) - 1
-    slot_new_h = torch.from_numpy(slot_h[last].copy()).pin_memory()
-    out_h = torch.empty((n_layer, N_SEQS, N_HEAD, D)).pin_memory()
-    knew_d, vnew_d = torch.empty_like(knew_h, device="cuda"), torch.empty_like(vnew_h, device="cuda")
-    slot_new_d = torch.empty_like(slot_new_h, device="cuda")
-    h2d = q_h.numel() * 4 + knew_h.numel() * 4 + vnew_h.numel() * 4 + bt_hp.numel() * 4 + sl_hp.numel() * 4 + slot_new_h.numel() * 4
-    d2h = out_h.numel() * 4
+    # ---- end to end through the C ABI with HOST buffers: per step, H2D of the step's inputs (copy stream, layer by
+    # layer, overlapped with compute), kv_write + attention (+ all-gather) per layer, D2H of every layer's output
+    e2e = None
+    if not args.no_e2e:
+        res_d = gathered if collective else out_d
+        q_h = (torch.rand((n_layer, n_seqs, n_head, D)) * 2 - 1).pin_memory()
+        knew_h = (torch.rand((n_layer, n_seqs, n_head_kv * D)) * 2 - 1).pin_memory()
+        vnew_h = (torch.rand((n_layer, n_seqs, n_head_kv * D)) * 2 - 1).pin_memory()
+        bt_hp, sl_hp = torch.from_numpy(bt_h).pin_memory(), torch.from_numpy(lens).pin_memory()
+        # the step's new token of each sequence overwrites its last cached position (cache stays the same size)
+        last = np.cumsum(lens.astype(np.int64)) - 1
+        slot_new_h = torch.from_numpy(slot_h[last].copy()).pin_memory()
+        out_h = torch.empty(tuple(res_d.shape)).pin_memory()
+        knew_d, vnew_d = torch.empty_like(knew_h, device="cuda"), torch.empty_like(vnew_h, device="cuda")
+        slot_new_d = torch.empty_like(slot_new_h, device="cuda")
+        h2d = 4 * (q_h.numel() + knew_h.numel() + vnew_h.numel() + bt_hp.numel() + sl_hp.numel() + slot_new_h.numel())
+        d2h = 4 * out_h.numel()
+        s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+        ev_in = [torch.cuda.Event() for _ in range(n_layer)]
+        ev_c = [torch.cuda.Event() for _ in range(n_layer)]
 
-    def step_e2e():
-        q_d.copy_(q_h, non_blocking=True); knew_d.copy_(knew_h, non_blocking=True); vnew_d.copy_(vnew_h, non_blocking=True)
-        bt_d.copy_(bt_hp, non_blocking=True); sl_d.copy_(sl_hp, non_blocking=True); slot_new_d.copy_(slot_new_h, non_blocking=True)
-        for l in range(n_layer):
-            pkg.kv_write(knew_d[l], vnew_d[l], slot_new_d, kcs[l], vcs[l], lay)
-            calls[l].run()
-        out_h.copy_(out_d, non_blocking=True)
-        torch.cuda.current_stream().synchronize()      # the host reads the step's result
+        def step_e2e():
+            cur = torch.cuda.current_stream()
+            s_in.wait_stream(cur)
+            with torch.cuda.stream(s_in):
+                bt_d.copy_(bt_hp, non_blocking=True); sl_d.copy_(sl_hp, non_blocking=True)
+                slot_new_d.copy_(slot_new_h, non_blocking=True)
+                for l in range(n_layer):
+                    q_d[l].copy_(q_h[l], non_blocking=True)
+                    knew_d[l].copy_(knew_h[l], non_blocking=True); vnew_d[l].copy_(vnew_h[l], non_blocking=True)
+                    ev_in[l].record(s_in)
+            for l in range(n_layer):
+                cur.wait_event(ev_in[l])
+                pkg.kv_write(knew_d[l], vnew_d[l], slot_new_d, kcs[l], vcs[l], lay)
+                layer_op(l)
+                ev_c[l].record(cur)
+                s_out.wait_event(ev_c[l])
+                with torch.cuda.stream(s_out):
+                    out_h[l].copy_(res_d[l], non_blocking=True)
+            s_out.synchronize()                              # the host holds the step's result
 
-    e2e_steps = max(3, args.steps // 2)
-    ms_e2e = timed(step_e2e, e2e_steps, 3) / e2e_steps
-    e2e_value = tot[0].item() / (ms_e2e * 1e-3) / 1e9
+        e2e_steps = max(3, args.steps // 2)
+        ms_e2e = timed(step_e2e, e2e_steps, 3) / e2e_steps
+        e2e = {"value": round(tot[0].item() / (ms_e2e * 1e-3) / 1e9, 2), "unit": "GB/s", "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": round(ms_e2e, 4)}
+    clocks = sampler.summary()
 
     if rank == 0:
         peak, peak_src = peaks()
-        achieved = kv_bytes_op / (ms_step / n_layer * 1e-3) / 1e9         # per-GPU, per op
+        achieved = kv_bytes_op / (ms_step / n_layer * 1e-3) / 1e9         # per GPU, per layer-op
         which = "stream-K" if (args.kernel != 1 and _uses_streamk(pkg, calls[0])) else "generic"
+        cfg = workload_config(args.workload, args.kv_type, world)
+        cfg.update({"n_layer": n_layer, "n_head_per_gpu": n_head, "n_head_kv_per_gpu": n_head_kv,
+                    "kv_bytes_per_step_per_gpu": bytes_step_rank, "cuda_graph": graph is not None, "kernel": which,
+                    "l2_flush": f"inputs (per-layer KV caches, {bytes_step_rank / 1e9:.1f} GB per step per GPU) are far larger than the 126 MB L2"})
         line = {
             "metric": "paged-attn decode KV-read GB/s", "value": round(value, 2), "unit": "GB/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4), "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": args.kv_type, "data": "synthetic",
-            "config": {"workload": f"config2_llama3_8b_{args.kv_type}", "n_seqs_per_gpu": N_SEQS, "ctx": "U{512..8192} seed 7+rank",
-                       "block_size": BS, "n_head": N_HEAD, "n_head_kv": N_HEAD_KV, "head_dim": D, "n_layer": n_layer,
-                       "kv_bytes_per_step_per_gpu": bytes_step_rank, "l2_flush": "inputs (per-layer KV caches, "
-                       f"{bytes_step_rank / 1e9:.1f} GB per step) are far larger than the 126 MB L2", "cuda_graph": graph is not None,
-                       "kernel": which, "parallelism": f"sequence-batch sharding x{world}, no collective"},
+            "scaling": W["scaling"], "vs_baseline": None, "dtype": args.kv_type, "data": "synthetic", "config": cfg,
             "decode_tok_s": round(tok_s, 1), "pct_hbm_nominal_8TBs": round(100 * achieved / 8000.0, 2),
             "gpu_launches": int(launches_per_step * args.steps),
-            "e2e": {"value": round(e2e_value, 2), "unit": "GB/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "ms_per_step": round(ms_e2e, 4)},
             "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                         "traffic": None, "peak_source": peak_src, "kernel": f"paged attention op ({which}), one layer",
+                         "traffic": ncu_traffic(args.kv_type) if args.workload == "config2" else None, "peak_source": peak_src,
+                         "kernel": f"paged attention op ({which}: plan + main + combine), one layer",
                          "algorithmic_bytes_per_launch": kv_bytes_op},
             "clocks": clocks,
         }
+        if e2e is not None:
+            line["e2e"] = e2e
         if not args.no_cpu_baseline:
-            sample, v, cores, kind, _ = cpu_layer_op(t, 3, 1)
+            sample, v, cores, kind, _ = cpu_layer_op(args.workload, t, 3, 1)
             line["cpu_baseline"] = {"value": round(v, 3), "unit": "GB/s", "cores": cores, "kind": kind, "sample": sample}
         print(json.dumps(line))
     if world > 1:

@@ -171,3 +171,4 @@ def row_bytes(type_id: int, n: int) -> int:
 
 
 from .driver import *  # noqa: E402,F401,F403  (torch-tensor helpers and host-class wrappers)
+from .sharding import *  # noqa: E402,F401,F403  (multi-GPU partitioning + the one all-gather)
