@@ -54,6 +54,7 @@ struct sk_args {
     float *part_o;                      // [max_segs][n_head][D]
     float  qscale;                      // scale*log2(e), or scale/softcap when softcap != 0
     float  cap_log2e;                   // softcap*log2(e)
+    uint32_t k65536;                    // 65536, read from the constant bank so ptxas keeps pack16 an IMAD (FMA pipe)
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -71,8 +72,11 @@ struct sk_smem {
     static constexpr bool KFIRST = TK == B200_TYPE_F16 || TV != B200_TYPE_F16;     // F16 tiles need 1024-byte alignment
     static constexpr int KOFF = KFIRST ? 0 : VT, VOFF = KFIRST ? KT : 0;
     static constexpr int ALIGN = ANY16 ? 1024 : 128;
-    static constexpr int STAGE = (KT + VT + ALIGN - 1)/ALIGN*ALIGN;
-    static constexpr int STAGES = STAGE <= 2560 ? 4 : 3;
+    static constexpr int STAGE = (KT + VT + ALIGN - 1)/ALIGN*ALIGN;                // one 16-token tile: K box + V box
+    // quantised K and V: TWO tiles per loop iteration share one softmax step (the loop is instruction-issue
+    // bound, profiles/r1f_*), so the ring must hold the 2 being consumed + at least 1 in flight
+    static constexpr int NSUB = ANY16 ? 1 : 2;
+    static constexpr int STAGES = ANY16 ? (STAGE <= 2560 ? 4 : 3) : (STAGE <= 2560 ? 5 : 3);
     static constexpr int WARP = STAGE*STAGES;
     static constexpr int BAR_BYTES = 1024;                                        // mbarriers, keeps tiles 1024-aligned
     static constexpr int CTA = BAR_BYTES + WARP*SK_WARPS + 16;                    // +16: funnel loads may touch 4 bytes past a row
@@ -132,6 +136,7 @@ __device__ __forceinline__ uint32_t hmul2_u(uint32_t a, uint32_t b) {
 }
 __device__ __forceinline__ float ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ uint32_t lds32(uint32_t addr) { uint32_t v; asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
+__device__ __forceinline__ uint32_t lds16(uint32_t addr) { uint32_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
 __device__ __forceinline__ void sts128_zero(uint32_t addr) { asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" :: "r"(addr), "r"(0) : "memory"); }
 __device__ __forceinline__ float h16f(uint32_t bits) { return __half2float(__ushort_as_half((unsigned short) bits)); }
 
@@ -336,9 +341,7 @@ __device__ __forceinline__ void sk_qk_quant(float (&S)[4], uint32_t kb, int mis,
             mma_16816(acc, a, q.b[2*blk][0],     q.b[2*blk][1]);
             mma_16816(acc, c, q.b[2*blk + 1][0], q.b[2*blk + 1][1]);
         }
-        const int so = (BLK*blk) & ~3;                        // mis % 4 == 0
-        const uint32_t s0 = lds32(row0 + so), s1 = lds32(row1 + so);
-        const float d0 = h16f((blk & 1) ? s0 >> 16 : s0 & 0xffffu), d1 = h16f((blk & 1) ? s1 >> 16 : s1 & 0xffffu);
+        const float d0 = h16f(lds16(row0 + BLK*blk)), d1 = h16f(lds16(row1 + BLK*blk));
         S[0] = fmaf(d0, acc[0] - q.cb[blk][0], S[0]);
         S[1] = fmaf(d0, acc[1] - q.cb[blk][1], S[1]);
         S[2] = fmaf(d1, acc[2] - q.cb[blk][0], S[2]);
@@ -347,10 +350,16 @@ __device__ __forceinline__ void sk_qk_quant(float (&S)[4], uint32_t kb, int mis,
 }
 
 // ------------------------------------------------------------------------------------------------
-// O^T += V^T . P^T ; 8 m-tiles of 16 d-rows.  Quantised V: the biased integer of the exponent trick is brought
-// back to the exact signed integer with one half2 add (1152 + q -> q, 1024 + n -> n - 8, 1024 + 16 n -> n - 8 by
-// one fma with 1/16), then scaled by the token pair's block scales: one rounding, like dequantize_row_*
-// (ggml/src/ggml-quants.c:255-273, :349-362) followed by a half conversion.
+// O^T += V^T . P^T ; 8 m-tiles of 16 d-rows.
+// Quantised V costs NO per-element arithmetic beyond the byte/nibble -> half expansion:
+//   * the block scale d[token][blk] is folded into the B operand: b = P * d (one HMUL2 per register and block, the
+//     16 rows of an m-tile all belong to ONE 32-element block, so the scale depends on (token, block) only);
+//   * the bias of the exponent trick (1152 + q for Q8_0; (1024 + 16 n)/16 = 64 + n for Q4_0, whose b carries an
+//     extra 1/16) is removed on the tensor core: one more MMA per m-tile with A = -1152 everywhere adds
+//     -1152 * sum_tok b = -(bias) * sum_tok P d to the accumulator BEFORE the data MMA, so the accumulator only
+//     ever strays from the true value by one tile's bias (FP32 error ~1e-7 relative; the tensor pipe was 18 %
+//     busy, profiles/r1f_sk_q4_0_ncu_full.txt).  Result: sum_tok (q | n - 8) * d * P, i.e. dequantize_row_*
+//     (ggml/src/ggml-quants.c:255-273, :349-362) times P with P*d rounded to half once.
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void sk_pv_f16(float (&O)[8][4], uint32_t vb, uint32_t p0, uint32_t p1, int lane) {
     const int tau = (lane & 7) + 8*(lane >> 4);
@@ -364,71 +373,62 @@ __device__ __forceinline__ void sk_pv_f16(float (&O)[8][4], uint32_t vb, uint32_
     }
 }
 
+// (hi << 16) | lo for lo < 65536, as an integer multiply-add: runs on the FMA pipe, which this kernel leaves
+// half idle, instead of a PRMT on the ALU pipe, which bounds it (profiles/r1h_*)
+// k65536 must be an opaque register: with an immediate ptxas strength-reduces the multiply back to LEA (ALU pipe)
+__device__ __forceinline__ uint32_t pack16(uint32_t lo, uint32_t hi, uint32_t k65536) {
+    uint32_t d; asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(hi), "r"(k65536), "r"(lo)); return d;
+}
+
 template <int TV>
-__device__ __forceinline__ void sk_pv_quant(float (&O)[8][4], uint32_t vb, int mis, uint32_t p0, uint32_t p1, uint2 kc, int lane) {
+__device__ __forceinline__ void sk_pv_quant(float (&O)[8][4], uint32_t vb, int mis, uint32_t p0, uint32_t p1, uint2 kc, uint32_t k64k, int lane) {
     constexpr int WIN = sk_type<TV>::WIN, BLK = sk_type<TV>::BLK;
     const int g = lane >> 2, t = lane & 3;
     const uint32_t r0 = vb + 2*t*WIN + mis, r1 = r0 + WIN, r2 = r0 + 8*WIN, r3 = r2 + WIN;   // tokens 2t, 2t+1, 2t+8, 2t+9
-    if constexpr (TV == B200_TYPE_Q8_0) {
-        constexpr uint32_t M1152 = 0xE480E480u;              // half2(-1152)
+    const uint32_t NEG = sk_opaque(0xE480E480u);             // half2(-1152): Q8_0 bias, and Q4_0 high nibbles (72 * 16)
+    const uint32_t neg[4] = {NEG, NEG, NEG, NEG};
 #pragma unroll
-        for (int blk = 0; blk < 4; ++blk) {
-            const int so = (BLK*blk) & ~3;
-            const uint32_t sel = (blk & 1) ? 0x7632 : 0x5410;
-            const uint32_t sp01 = prmt(lds32(r0 + so), lds32(r1 + so), sel);                  // (d[2t], d[2t+1])
-            const uint32_t sp23 = prmt(lds32(r2 + so), lds32(r3 + so), sel);
+    for (int blk = 0; blk < 4; ++blk) {
+        const int so = BLK*blk;                              // block scale: 2-byte aligned
+        const uint32_t b0 = hmul2_u(p0, pack16(lds16(r0 + so), lds16(r1 + so), k64k));              // P * (d[2t], d[2t+1])
+        const uint32_t b1 = hmul2_u(p1, pack16(lds16(r2 + so), lds16(r3 + so), k64k));
+        uint32_t a[4], c[4];
+        if constexpr (TV == B200_TYPE_Q8_0) {                // lane g: bytes 4g..4g+3 of the block -> d = 32 blk + 4g + {0,1 | 2,3}
             const int o = BLK*blk + 2 + 4*g;
             uint32_t W0, W1, W2, W3;
             if (blk & 1) { W0 = sk_ld4<true >(r0, o); W1 = sk_ld4<true >(r1, o); W2 = sk_ld4<true >(r2, o); W3 = sk_ld4<true >(r3, o); }
             else         { W0 = sk_ld4<false>(r0, o); W1 = sk_ld4<false>(r1, o); W2 = sk_ld4<false>(r2, o); W3 = sk_ld4<false>(r3, o); }
             const uint32_t x01l = q8_bias(prmt(W0, W1, 0x5410)), x01h = q8_bias(prmt(W0, W1, 0x7632));
             const uint32_t x23l = q8_bias(prmt(W2, W3, 0x5410)), x23h = q8_bias(prmt(W2, W3, 0x7632));
-            auto deq = [&](uint32_t e, uint32_t sp) { return hmul2_u(hadd2_u(e, M1152), sp); };
-            const uint32_t a[4] = {deq(q8_e02(x01l, kc.x), sp01), deq(q8_e13(x01l, kc.x), sp01),
-                                   deq(q8_e02(x23l, kc.x), sp23), deq(q8_e13(x23l, kc.x), sp23)};
-            const uint32_t c[4] = {deq(q8_e02(x01h, kc.x), sp01), deq(q8_e13(x01h, kc.x), sp01),
-                                   deq(q8_e02(x23h, kc.x), sp23), deq(q8_e13(x23h, kc.x), sp23)};
-            mma_16816(O[2*blk],     a, p0, p1);
-            mma_16816(O[2*blk + 1], c, p0, p1);
-        }
-    } else {
-        constexpr uint32_t M1032 = 0xE408E408u, R16 = 0x2C002C00u, M72 = 0xD480D480u;   // half2(-1032), (1/16), (-72)
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            const int odd = g >> 2, bb = 2*k + odd, wq = g & 3;      // this lane's block of the pair (2k, 2k+1)
-            const int so = (BLK*bb) & ~3;
-            const uint32_t sel = odd ? 0x7632 : 0x5410;
-            const uint32_t sp01 = prmt(lds32(r0 + so), lds32(r1 + so), sel);
-            const uint32_t sp23 = prmt(lds32(r2 + so), lds32(r3 + so), sel);
-            const int o = BLK*bb + 2 + 4*wq, oa = o & ~3;
-            const uint32_t fsel = odd ? 0x3210 : 0x5432;              // odd blocks are word aligned
-            const uint32_t W0 = prmt(lds32(r0 + oa), lds32(r0 + oa + 4), fsel);
-            const uint32_t W1 = prmt(lds32(r1 + oa), lds32(r1 + oa + 4), fsel);
-            const uint32_t W2 = prmt(lds32(r2 + oa), lds32(r2 + oa + 4), fsel);
-            const uint32_t W3 = prmt(lds32(r3 + oa), lds32(r3 + oa + 4), fsel);
-            auto dlo = [&](uint32_t e, uint32_t sp) { return hmul2_u(hadd2_u(e, M1032), sp); };          // (1024 + n) - 1032
-            auto dhi = [&](uint32_t e, uint32_t sp) { return hmul2_u(hfma2_u(e, R16, M72), sp); };       // (1024 + 16 n)/16 - 72
-#pragma unroll
-            for (int hb = 0; hb < 2; ++hb) {                           // bytes (0,1) then (2,3) of the word
-                const uint32_t x01 = prmt(W0, W1, hb ? 0x7632 : 0x5410), x23 = prmt(W2, W3, hb ? 0x7632 : 0x5410);
-                const uint32_t y01 = x01 >> 8, y23 = x23 >> 8;
-                const uint32_t a[4] = {dlo(q4_lo(x01, kc.x), sp01), dlo(q4_lo(y01, kc.x), sp01),
-                                       dlo(q4_lo(x23, kc.x), sp23), dlo(q4_lo(y23, kc.x), sp23)};
-                const uint32_t c[4] = {dhi(q4_hi(x01, kc.y), sp01), dhi(q4_hi(y01, kc.y), sp01),
-                                       dhi(q4_hi(x23, kc.y), sp23), dhi(q4_hi(y23, kc.y), sp23)};
-                mma_16816(O[4*k + 2*hb],     a, p0, p1);
-                mma_16816(O[4*k + 2*hb + 1], c, p0, p1);
-            }
+            a[0] = q8_e02(x01l, kc.x); a[1] = q8_e13(x01l, kc.x); a[2] = q8_e02(x23l, kc.x); a[3] = q8_e13(x23l, kc.x);
+            c[0] = q8_e02(x01h, kc.x); c[1] = q8_e13(x01h, kc.x); c[2] = q8_e02(x23h, kc.x); c[3] = q8_e13(x23h, kc.x);
+            mma_16816(O[2*blk],     neg, b0, b1);
+            mma_16816(O[2*blk + 1], neg, b0, b1);
+            mma_16816(O[2*blk],     a,   b0, b1);
+            mma_16816(O[2*blk + 1], c,   b0, b1);
+        } else {                                             // lane g: bytes 2g, 2g+1 -> d = 32 blk + 2g + {0,1} (low), + 16 (high nibbles)
+            const int o = BLK*blk + 2 + 2*g;
+            const uint32_t x01 = pack16(lds16(r0 + o), lds16(r1 + o), k64k), x23 = pack16(lds16(r2 + o), lds16(r3 + o), k64k);
+            const uint32_t y01 = x01 >> 8, y23 = x23 >> 8;
+            a[0] = q4_lo(x01, kc.x); a[1] = q4_lo(y01, kc.x); a[2] = q4_lo(x23, kc.x); a[3] = q4_lo(y23, kc.x);   // 1024 + n
+            c[0] = q4_hi(x01, kc.y); c[1] = q4_hi(y01, kc.y); c[2] = q4_hi(x23, kc.y); c[3] = q4_hi(y23, kc.y);   // 1024 + 16 n
+            const uint32_t NEGLO = 0xE408E408u;              // half2(-1032)
+            const uint32_t neglo[4] = {NEGLO, NEGLO, NEGLO, NEGLO};
+            const uint32_t h0 = hmul2_u(b0, 0x2C002C00u), h1 = hmul2_u(b1, 0x2C002C00u);      // * 1/16 (exact)
+            mma_16816(O[2*blk],     neglo, b0, b1);
+            mma_16816(O[2*blk + 1], neg,   h0, h1);
+            mma_16816(O[2*blk],     a,     b0, b1);
+            mma_16816(O[2*blk + 1], c,     h0, h1);
         }
     }
 }
 
-// d index of accumulator row (m-tile mt, half h: 0 = row g, 1 = row g+8) and the OW entry that corrects it
+// d index of accumulator row (m-tile mt, half h: 0 = row g, 1 = row g+8)
 template <int TV>
 __device__ __forceinline__ int sk_row_d(int mt, int h, int g) {
     if constexpr (TV == B200_TYPE_F16)       return 16*mt + g + 8*h;
     else if constexpr (TV == B200_TYPE_Q8_0) return 32*(mt >> 1) + 4*g + 2*(mt & 1) + h;
-    else { const int bb = 2*(mt >> 2) + (g >> 2); return 32*bb + 4*(g & 3) + 16*(mt & 1) + 2*((mt >> 1) & 1) + h; }
+    else                                     return 32*(mt >> 1) + 16*(mt & 1) + 2*g + h;
 }
 // ------------------------------------------------------------------------------------------------
 // main kernel
@@ -476,10 +476,14 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
     const int vc = TV == B200_TYPE_F16 ? (int) (voff >> 7) : (int) (voff - vmis);
     const int bs = p.block_size, tpb = bs/SK_TILE;                                    // tiles per block (bs % 16 == 0)
     const int n_blk = p.bt_stride < INT32_MAX ? (int) p.bt_stride : INT32_MAX;
-    uint32_t it = 0;                                                                  // tiles consumed by this warp so far
+    constexpr int NSUB = SM::NSUB;
+    int cs = 0, is = 0;                 // ring slots of the next tile to consume / to issue (equal at row boundaries)
+    uint32_t cph = 0;                   // phase parity of the consume slot's current use
     // expansion constants, one register each: Q8_0 {0x64646464}, Q4_0 {low-nibble mask, high-nibble mask}
     const uint2 kcon = make_uint2(sk_opaque(TK == B200_TYPE_Q8_0 ? 0x64646464u : 0x000f000fu), sk_opaque(0x00f000f0u));
     const uint2 vcon = TK == TV ? kcon : make_uint2(sk_opaque(TV == B200_TYPE_Q8_0 ? 0x64646464u : 0x000f000fu), sk_opaque(0x00f000f0u));
+
+    const uint32_t k64k = a.k65536;
 
     while (g0 < g1) {
         const int pb = P[row], pe = P[row + 1];
@@ -511,7 +515,7 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
         int win      = win_base + lane      < n_blk ? bt[win_base + lane]      : 0;
         int win_next = win_base + 32 + lane < n_blk ? bt[win_base + 32 + lane] : 0;
 
-        auto issue = [&](uint32_t n) {                      // all lanes (shuffle); lane 0 talks to the TMA unit
+        auto issue = [&]() {                                // all lanes (shuffle); lane 0 talks to the TMA unit
             if (b_cur - win_base >= 32) {
                 win_base += 32; win = win_next;
                 win_next = win_base + 32 + lane < n_blk ? bt[win_base + 32 + lane] : 0;
@@ -520,68 +524,90 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
             const int cell = blk*bs + o_cur*SK_TILE;
             if (++o_cur == tpb) { o_cur = 0; ++b_cur; }
             if (lane == 0) {
-                const uint32_t slot = n % STAGES, bar = bar0 + 8*slot, sb = smem0 + slot*SM::STAGE;
+                const uint32_t bar = bar0 + 8*is, sb = smem0 + is*SM::STAGE;
                 mbar_expect_tx(bar, SM::KT + SM::VT);
                 if constexpr (TK == B200_TYPE_F16) tma_load_3d(sb + SM::KOFF, &tmK, 0, cell, kc, bar);
                 else                               tma_load_2d(sb + SM::KOFF, &tmK, kc, cell, bar);
                 if constexpr (TV == B200_TYPE_F16) tma_load_3d(sb + SM::VOFF, &tmV, 0, cell, vc, bar);
                 else                               tma_load_2d(sb + SM::VOFF, &tmV, vc, cell, bar);
             }
+            if (++is == STAGES) is = 0;
         };
 
         const int nt = t1 - t0;
+        int issued = 0;
 #pragma unroll
-        for (int s = 0; s < STAGES - 1; ++s) { if (s < nt) issue(it + s); }
+        for (int s = 0; s < STAGES - NSUB; ++s) { if (issued < nt) { issue(); ++issued; } }
 
-        for (int i = 0; i < nt; ++i, ++it) {
-            __syncwarp();                                    // every lane is done with the slot about to be refilled
-            if (i + STAGES - 1 < nt) issue(it + STAGES - 1);
-            const uint32_t slot = it % STAGES;
-            mbar_wait(bar0 + 8*slot, (it / STAGES) & 1);
-            const uint32_t sb = smem0 + slot*SM::STAGE, kb = sb + SM::KOFF, vb = sb + SM::VOFF;
+        for (int i = 0; i < nt; i += NSUB) {
+            __syncwarp();                                    // every lane is done with the slots about to be refilled
+#pragma unroll
+            for (int u = 0; u < NSUB; ++u) { if (issued < nt) { issue(); ++issued; } }
+            const int nsub = min(NSUB, nt - i);              // tiles of this iteration (warp-uniform)
 
-            const int tok0 = (t0 + i)*SK_TILE;
-            if (tok0 + SK_TILE > n_vis) {                    // tail tile: cells past n_vis hold stale bytes; 0 * NaN must not reach O
-                constexpr int VW = sk_type<TV>::WIN;
-                for (int tau = n_vis - tok0; tau < SK_TILE; ++tau) {
-                    if constexpr (TV == B200_TYPE_F16) { if (lane < 16) sts128_zero(vb + ((lane >> 3)*16 + tau)*128 + (lane & 7)*16); }
-                    else                               { if (lane < VW/16) sts128_zero(vb + tau*VW + lane*16); }
+            float S[NSUB][4];
+            uint32_t vbs[NSUB];
+#pragma unroll
+            for (int u = 0; u < NSUB; ++u) {
+                S[u][0] = S[u][1] = S[u][2] = S[u][3] = -INFINITY;
+                if (u < nsub) {
+                    mbar_wait(bar0 + 8*cs, cph);
+                    const uint32_t sb = smem0 + cs*SM::STAGE, kb = sb + SM::KOFF, vb = sb + SM::VOFF;
+                    vbs[u] = vb;
+                    if (++cs == STAGES) { cs = 0; cph ^= 1; }
+                    const int tok0 = (t0 + i + u)*SK_TILE;
+                    if (tok0 + SK_TILE > n_vis) {            // tail tile: cells past n_vis hold stale bytes; 0 * NaN must not reach O
+                        constexpr int VW = sk_type<TV>::WIN;
+                        for (int tau = n_vis - tok0; tau < SK_TILE; ++tau) {
+                            if constexpr (TV == B200_TYPE_F16) { if (lane < 16) sts128_zero(vb + ((lane >> 3)*16 + tau)*128 + (lane & 7)*16); }
+                            else                               { if (lane < VW/16) sts128_zero(vb + tau*VW + lane*16); }
+                        }
+                        __syncwarp();
+                    }
+                    float A[4] = {0.f, 0.f, 0.f, 0.f};
+                    if constexpr (TK == B200_TYPE_F16) sk_qk_f16(A, kb, qf, lane);
+                    else                               sk_qk_quant<TK>(A, kb, kmis, qf, kcon, lane);
+                    if (p.logit_softcap != 0.0f) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) A[j] = a.cap_log2e*tanhf(A[j]);
+                    }
+                    S[u][0] = A[0]; S[u][1] = A[1]; S[u][2] = A[2]; S[u][3] = A[3];
+                    if (tok0 + SK_TILE > n_vis) {            // warp-uniform: only a row's last tile masks
+                        const int tok = tok0 + g;
+                        if (tok >= n_vis)     { S[u][0] = -INFINITY; S[u][1] = -INFINITY; }
+                        if (tok + 8 >= n_vis) { S[u][2] = -INFINITY; S[u][3] = -INFINITY; }
+                    }
                 }
-                __syncwarp();
             }
 
-            float S[4] = {0.f, 0.f, 0.f, 0.f};
-            if constexpr (TK == B200_TYPE_F16) sk_qk_f16(S, kb, qf, lane);
-            else                               sk_qk_quant<TK>(S, kb, kmis, qf, kcon, lane);
-
-            if (p.logit_softcap != 0.0f) {
+            float x0 = fmaxf(S[0][0], S[0][2]), x1 = fmaxf(S[0][1], S[0][3]);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) S[j] = a.cap_log2e*tanhf(S[j]);
-            }
-            const int tok = tok0 + g;
-            if (tok >= n_vis)     { S[0] = -INFINITY; S[1] = -INFINITY; }
-            if (tok + 8 >= n_vis) { S[2] = -INFINITY; S[3] = -INFINITY; }
-
-            float x0 = fmaxf(S[0], S[2]), x1 = fmaxf(S[1], S[3]);
+            for (int u = 1; u < NSUB; ++u) { x0 = fmaxf(x0, fmaxf(S[u][0], S[u][2])); x1 = fmaxf(x1, fmaxf(S[u][1], S[u][3])); }
 #pragma unroll
             for (int o = 4; o < 32; o <<= 1) {
                 x0 = fmaxf(x0, __shfl_xor_sync(0xffffffffu, x0, o));
                 x1 = fmaxf(x1, __shfl_xor_sync(0xffffffffu, x1, o));
             }
-            const float n0 = fmaxf(m0, x0), n1 = fmaxf(m1, x1);      // finite: the first token of a tile is always visible
+            const float n0 = fmaxf(m0, x0), n1 = fmaxf(m1, x1);      // finite: the first token of the first tile is always visible
             const float al0 = ex2(m0 - n0), al1 = ex2(m1 - n1);
             m0 = n0; m1 = n1;
-            const float p00 = ex2(S[0] - n0), p01 = ex2(S[1] - n1), p10 = ex2(S[2] - n0), p11 = ex2(S[3] - n1);
-            l0 = l0*al0 + p00 + p10;
-            l1 = l1*al1 + p01 + p11;
+            l0 *= al0; l1 *= al1;
             if (__any_sync(0xffffffffu, al0 != 1.0f || al1 != 1.0f)) {
 #pragma unroll
                 for (int mu = 0; mu < 8; ++mu) { O[mu][0] *= al0; O[mu][1] *= al1; O[mu][2] *= al0; O[mu][3] *= al1; }
             }
-            const uint32_t pt0 = movmatrix_trans(pack_h2(p00, p01));
-            const uint32_t pt1 = movmatrix_trans(pack_h2(p10, p11));
-            if constexpr (TV == B200_TYPE_F16) sk_pv_f16(O, vb, pt0, pt1, lane);
-            else                               sk_pv_quant<TV>(O, vb, vmis, pt0, pt1, vcon, lane);
+#pragma unroll
+            for (int u = 0; u < NSUB; ++u) {
+                if (u < nsub) {
+                    const float p00 = ex2(S[u][0] - n0), p01 = ex2(S[u][1] - n1), p10 = ex2(S[u][2] - n0), p11 = ex2(S[u][3] - n1);
+                    l0 += p00 + p10;
+                    l1 += p01 + p11;
+                    const uint32_t pt0 = movmatrix_trans(pack_h2(p00, p01));
+                    const uint32_t pt1 = movmatrix_trans(pack_h2(p10, p11));
+                    if constexpr (TV == B200_TYPE_F16) sk_pv_f16(O, vbs[u], pt0, pt1, lane);
+                    else                               sk_pv_quant<TV>(O, vbs[u], vmis, pt0, pt1, vcon, k64k, lane);
+                }
+            }
         }
 
         // ---- segment epilogue
@@ -760,6 +786,7 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st) {
     sk_args a;
     a.d = d;
     a.gqa = d.n_head/d.n_head_kv;
+    a.k65536 = 65536u;
     a.n_items = sk_items(d);
     const size_t max_segs = (size_t) a.n_items + d.n_q;
     char *ws = static_cast<char *>(d.workspace);
