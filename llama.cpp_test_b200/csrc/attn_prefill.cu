@@ -1,0 +1,509 @@
+// attn_prefill.cu — chunked-prefill paged attention on the 5th-generation tensor cores (tcgen05 + TMEM).
+//
+// Replaces flash_attn_ext_f16 (the mma.sync tile kernel, ggml/src/ggml-cuda/fattn-mma-f16.cuh:804-936) for the
+// many-query case: 512-token chunks appended into the paged cache (BASELINE config 3).  Semantics are those of
+// ggml_compute_forward_flash_attn_ext_f16 (ggml/src/ggml-cpu/ggml-cpu.c:12219-12432) restricted to what a block
+// table expresses: query row t of sequence s sees positions [0, min(seq_lens[s], q_pos[t]+1)); the causal limit is
+// applied in-kernel, no dense mask is read (the reference fills and reads an [n_kv, n_q] F16 mask,
+// src/llama-graph.cpp:403-477).
+//
+// Work item = (row tile, kv head).  A row tile is up to 128/gqa consecutive query rows of ONE sequence (found on
+// the device by pf_plan_kernel from q_seq, so any row order is legal); with the gqa query heads of the kv head
+// that is M = 128 MMA rows, TMEM lane r = token r/gqa, head r%gqa.  K/V of the sequence stream ONCE per work item
+// through a 2-stage ring of 64-token tiles (per-row stream-K decode would re-read them once per query row).
+//
+// CTA = 6 warps, 2 CTAs per SM so one CTA's softmax overlaps the other's MMAs:
+//   warps 0-3  softmax: thread r owns accumulator row r (TMEM lane r): tcgen05.ld S -> causal mask -> running max
+//              (lazy: the reference point only moves when the max grows by > 2^8, so O is rarely rescaled) -> exp2
+//              -> P as F16 into shared memory in the UMMA K-major 128B-swizzle layout; final O * 1/l -> dst
+//   warp 4     one thread issues tcgen05.mma: S[128x64] = Q K^T (8 x K16, A and B from shared memory, K-major),
+//              O[128x128] += P V (4 x K16, V as the MN-major B operand straight from its row-major cache layout);
+//              S is double-buffered in TMEM so QK^T of tile j+1 runs under the softmax of tile j
+//   warp 5     one thread gathers K/V through the block table with TMA: one box = 16 cells x 64 halves of one head
+//              (128-byte swizzle), 16 boxes per 64-token stage
+// TMEM: 256 columns per CTA (S0 64, S1 64, O 128).  Shared: Q 32 KB + 2 x (K 16 + V 16) + P 16 = 112 KB.
+#include "common.cuh"
+#include <cuda.h>
+#include <math.h>
+#include <climits>
+
+namespace b200 {
+
+constexpr int PF_ROWS    = 128;          // MMA rows per work item
+constexpr int PF_BN      = 64;           // kv tokens per tile
+constexpr int PF_D       = 128;
+constexpr int PF_THREADS = 192;
+constexpr int PF_SQ      = 0;            // [2 d-halves][128 rows][128 B]
+constexpr int PF_SKV     = 32768;        // stage s at + s*32768: K [2][64][128 B] then V [2][64][128 B]
+constexpr int PF_SP      = 98304;        // [128 rows][128 B]
+constexpr int PF_SBAR    = 114688;
+constexpr int PF_SMEM    = PF_SBAR + 128;
+
+enum { PF_FULLK = 0, PF_FULLV = 2, PF_EMPTY = 4, PF_SFULL = 6, PF_PFULL = 8, PF_ODONE = 9, PF_NBAR = 10 };
+
+struct pf_args {
+    b200_attn_desc d;
+    int    gqa, tok_per_tile;            // tok_per_tile = 128/gqa
+    int   *plan;                         // [0] n_tiles, [1] work counter, [2..] tile_row0[n_q], then tile_rows[n_q]
+    float  qscale;                       // scale*log2(e)
+};
+
+__device__ __forceinline__ uint32_t pf_smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void pf_mbar_init(uint32_t bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void pf_mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void pf_mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void pf_mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile("{\n .reg .pred p;\nPF_WAIT_%=:\n mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n @p bra PF_DONE_%=;\n bra PF_WAIT_%=;\nPF_DONE_%=:\n}"
+                 :: "r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void pf_tma_2d(uint32_t dst, const CUtensorMap *tm, int c0, int c1, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 :: "r"(dst), "l"(tm), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void pf_fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void pf_tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void pf_tc_fence_after()  { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// shared-memory matrix descriptor, 128-byte swizzle (cute/arch/mma_sm100_desc.hpp SmemDescriptor: start >> 4 at
+// [0,14), LBO >> 4 at [16,30), SBO >> 4 at [32,46), version 1 at [46,48), layout SWIZZLE_128B = 2 at [61,64))
+__device__ __forceinline__ uint64_t pf_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    return (uint64_t) ((addr & 0x3FFFFu) >> 4) | ((uint64_t) (lbo_bytes >> 4) << 16) | ((uint64_t) (sbo_bytes >> 4) << 32)
+         | (1ull << 46) | (2ull << 61);
+}
+// instruction descriptor, kind::f16: D F32 (bit 4), A/B F16, b_major at 16, N >> 3 at [17,23), M >> 4 at [24,29)
+__host__ __device__ constexpr uint32_t pf_idesc(int m, int n, int b_mn_major) {
+    return (1u << 4) | ((uint32_t) b_mn_major << 16) | ((uint32_t) (n >> 3) << 17) | ((uint32_t) (m >> 4) << 24);
+}
+__device__ __forceinline__ void pf_mma(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
+                 :: "r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void pf_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
+}
+
+#define PF_R32(v, o) "=r"(v[o+0]), "=r"(v[o+1]), "=r"(v[o+2]), "=r"(v[o+3]), "=r"(v[o+4]), "=r"(v[o+5]), "=r"(v[o+6]), "=r"(v[o+7]), \
+                     "=r"(v[o+8]), "=r"(v[o+9]), "=r"(v[o+10]), "=r"(v[o+11]), "=r"(v[o+12]), "=r"(v[o+13]), "=r"(v[o+14]), "=r"(v[o+15]), \
+                     "=r"(v[o+16]), "=r"(v[o+17]), "=r"(v[o+18]), "=r"(v[o+19]), "=r"(v[o+20]), "=r"(v[o+21]), "=r"(v[o+22]), "=r"(v[o+23]), \
+                     "=r"(v[o+24]), "=r"(v[o+25]), "=r"(v[o+26]), "=r"(v[o+27]), "=r"(v[o+28]), "=r"(v[o+29]), "=r"(v[o+30]), "=r"(v[o+31])
+#define PF_W32(v, o) "r"(v[o+0]), "r"(v[o+1]), "r"(v[o+2]), "r"(v[o+3]), "r"(v[o+4]), "r"(v[o+5]), "r"(v[o+6]), "r"(v[o+7]), \
+                     "r"(v[o+8]), "r"(v[o+9]), "r"(v[o+10]), "r"(v[o+11]), "r"(v[o+12]), "r"(v[o+13]), "r"(v[o+14]), "r"(v[o+15]), \
+                     "r"(v[o+16]), "r"(v[o+17]), "r"(v[o+18]), "r"(v[o+19]), "r"(v[o+20]), "r"(v[o+21]), "r"(v[o+22]), "r"(v[o+23]), \
+                     "r"(v[o+24]), "r"(v[o+25]), "r"(v[o+26]), "r"(v[o+27]), "r"(v[o+28]), "r"(v[o+29]), "r"(v[o+30]), "r"(v[o+31])
+#define PF_LIST32 "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}"
+#define PF_LIST32S "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32}"
+
+// 32 consecutive FP32 columns of this thread's TMEM lane (warp w touches lanes 32*(w%4)..+31)
+__device__ __forceinline__ void pf_tmem_ld32(uint32_t taddr, uint32_t (&v)[64], int o) {
+    if (o == 0) asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 " PF_LIST32 ", [%32];" : PF_R32(v, 0)  : "r"(taddr) : "memory");
+    else        asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 " PF_LIST32 ", [%32];" : PF_R32(v, 32) : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void pf_tmem_st32(uint32_t taddr, const uint32_t (&v)[64], int o) {
+    if (o == 0) asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], " PF_LIST32S ";" :: "r"(taddr), PF_W32(v, 0)  : "memory");
+    else        asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], " PF_LIST32S ";" :: "r"(taddr), PF_W32(v, 32) : "memory");
+}
+__device__ __forceinline__ void pf_tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void pf_tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ float pf_ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ uint32_t pf_pack_h2(float lo, float hi) {
+    const __half2 h = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t *>(&h);
+}
+// byte offset of 16-byte chunk c (0..7) of row r inside a [rows][128 B] tile with the 128-byte swizzle
+__device__ __forceinline__ uint32_t pf_swz(int r, int c) { return (uint32_t) ((r >> 3)*1024 + (r & 7)*128 + ((c ^ (r & 7)) << 4)); }
+__device__ __forceinline__ void pf_sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" :: "r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------------
+// plan: cut the query rows into tiles of <= tok_per_tile consecutive rows of one sequence.  One CTA.
+// ------------------------------------------------------------------------------------------------
+template <bool MAX>
+__device__ __forceinline__ int pf_block_scan_incl(int v, int *s_warp) {      // inclusive scan over the CTA (sum or max)
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    int x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x = MAX ? max(x, y) : x + y; }
+    if (lane == 31) s_warp[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+        int w = lane < nw ? s_warp[lane] : 0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w = MAX ? max(w, y) : w + y; }
+        s_warp[lane] = w;
+    }
+    __syncthreads();
+    if (warp) x = MAX ? max(x, s_warp[warp - 1]) : x + s_warp[warp - 1];
+    __syncthreads();
+    return x;
+}
+
+__global__ void __launch_bounds__(1024)
+pf_plan_kernel(const __grid_constant__ pf_args a) {
+    __shared__ int s_warp[32];
+    const b200_attn_desc &p = a.d;
+    int *row0 = a.plan + 2, *rows = row0 + p.n_q;
+    int carry_start = 0, carry_tiles = 0;                    // run start of the last row seen, tiles so far
+    for (int r0 = 0; r0 < p.n_q; r0 += 1024) {
+        const int r = r0 + threadIdx.x;
+        int boundary = 0;
+        if (r < p.n_q) {
+            const int s = p.q_seq ? p.q_seq[r] : r;
+            boundary = r == 0 || s != (p.q_seq ? p.q_seq[r - 1] : r - 1);
+        }
+        int start = pf_block_scan_incl<true>(boundary ? r : 0, s_warp);
+        start = max(start, carry_start);
+        const int is_tile = r < p.n_q && (boundary || (r - start) % a.tok_per_tile == 0);
+        const int idx = carry_tiles + pf_block_scan_incl<false>(is_tile, s_warp) - 1;
+        if (is_tile) row0[idx] = r;
+        __shared__ int s_carry[2];
+        if (threadIdx.x == 1023) { s_carry[0] = start; s_carry[1] = idx + 1; }
+        __syncthreads();
+        carry_start = s_carry[0]; carry_tiles = s_carry[1];
+        __syncthreads();
+    }
+    const int n_tiles = carry_tiles;
+    __threadfence_block();
+    __syncthreads();
+    for (int t = threadIdx.x; t < n_tiles; t += 1024) rows[t] = (t + 1 < n_tiles ? row0[t + 1] : p.n_q) - row0[t];
+    if (threadIdx.x == 0) { a.plan[0] = n_tiles; a.plan[1] = 0; }
+}
+
+// ------------------------------------------------------------------------------------------------
+// main kernel
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(PF_THREADS, 2)
+pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV) {
+    extern __shared__ __align__(1024) char pf_dyn[];
+    const b200_attn_desc &p = a.d;
+    const uint32_t sbase = pf_smem_u32(pf_dyn);
+    const uint32_t sQ = sbase + PF_SQ, sKV = sbase + PF_SKV, sP = sbase + PF_SP, sBar = sbase + PF_SBAR;
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(pf_dyn + PF_SBAR + 96);
+    volatile int      *work_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 100);
+    volatile int      *nvis_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 104);   // [4] per-warp max n_vis
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < PF_NBAR; ++i) pf_mbar_init(sBar + 8*i, i == PF_PFULL ? 128 : 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) {                                         // 256 TMEM columns: S0 | S1 | O
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" :: "r"(sBar + 96) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    pf_tc_fence_before();
+    __syncthreads();
+    pf_tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t tS = tmem, tO = tmem + 128;
+
+    const int gqa = a.gqa, bs = p.block_size;
+    const int n_blk = p.bt_stride < INT32_MAX ? (int) p.bt_stride : INT32_MAX;
+    const int *tile_row0 = a.plan + 2, *tile_rows = tile_row0 + p.n_q;
+    uint32_t G = 0;                                          // kv tiles processed by this CTA so far (same in every role)
+
+    for (;;) {
+        if (threadIdx.x == 0) *work_slot = atomicAdd(&a.plan[1], 1);
+        __syncthreads();
+        const int w = *work_slot;
+        const int n_tiles = a.plan[0];
+        if (w >= n_tiles*p.n_head_kv) break;
+        const int tile = n_tiles - 1 - w/p.n_head_kv, kvh = w % p.n_head_kv;      // later rows (longer contexts) first
+        const int row0 = tile_row0[tile], nrows = tile_rows[tile];
+        const int seq = p.q_seq ? p.q_seq[row0] : row0;
+        int seq_len = p.seq_lens[seq];
+        { const int64_t cap = (int64_t) n_blk*bs; if (seq_len > cap) seq_len = (int) cap; if (seq_len < 0) seq_len = 0; }
+        const int32_t *bt = p.block_table + (int64_t) seq*p.bt_stride;
+
+        // ---- softmax warps: this thread's row, its Q row -> F16 * scale*log2(e) -> shared (UMMA K-major, 128B swizzle)
+        int n_vis = 0;
+        const int r = threadIdx.x, tl = r/gqa, hg = r - tl*gqa;
+        if (warp < 4) {
+            const bool live = tl < nrows;
+            if (live) {
+                n_vis = seq_len;
+                if (p.q_pos) { const int lim = p.q_pos[row0 + tl] + 1; n_vis = lim < n_vis ? lim : n_vis; }
+                if (n_vis < 0) n_vis = 0;
+            }
+            const float *qrow = reinterpret_cast<const float *>(static_cast<const char *>(p.q) + (int64_t) (row0 + (live ? tl : 0))*p.nbq1
+                                                                 + (int64_t) (kvh*gqa + hg)*p.nbq2);
+#pragma unroll 4
+            for (int c = 0; c < 16; ++c) {
+                float4 x = make_float4(0.f, 0.f, 0.f, 0.f), y = x;
+                if (live) { x = *reinterpret_cast<const float4 *>(qrow + 8*c); y = *reinterpret_cast<const float4 *>(qrow + 8*c + 4); }
+                pf_sts128(sQ + (c >> 3)*16384 + pf_swz(r, c & 7), pf_pack_h2(x.x*a.qscale, x.y*a.qscale), pf_pack_h2(x.z*a.qscale, x.w*a.qscale),
+                          pf_pack_h2(y.x*a.qscale, y.y*a.qscale), pf_pack_h2(y.z*a.qscale, y.w*a.qscale));
+            }
+            const int wmax = __reduce_max_sync(0xffffffffu, n_vis);
+            if (lane == 0) nvis_slot[warp] = wmax;
+            pf_fence_async_smem();
+        }
+        __syncthreads();
+        const int nvis_max = max(max(nvis_slot[0], nvis_slot[1]), max(nvis_slot[2], nvis_slot[3]));
+        const int nkt = (nvis_max + PF_BN - 1)/PF_BN;
+
+        if (warp == 5) {
+            // ================= TMA producer =================
+            if (lane == 0) {
+                const int kc0 = (int) ((int64_t) kvh*p.nbk2/2), vc0 = (int) ((int64_t) kvh*p.nbv2/2);   // element coordinate of the head row
+                // block-table entries of the NEXT tile are fetched before waiting for a free stage, so the gather
+                // never adds a global-load latency to the TMA latency
+                auto cells_of = [&](int j, int (&cell)[4]) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int tok = j*PF_BN + 16*i, bi = tok/bs;
+                        cell[i] = (bi < n_blk ? bt[bi] : 0)*bs + (tok - bi*bs);
+                    }
+                };
+                int cur[4], nxt[4];
+                if (nkt > 0) cells_of(0, cur);
+                for (int j = 0; j < nkt; ++j) {
+                    const uint32_t g = G + j, st = g & 1;
+                    if (j + 1 < nkt) cells_of(j + 1, nxt);
+                    pf_mbar_wait(sBar + 8*(PF_EMPTY + st), ((g >> 1) & 1) ^ 1);
+                    const uint32_t sk = sKV + st*32768, sv = sk + 16384;
+                    const uint32_t bk = sBar + 8*(PF_FULLK + st), bv = sBar + 8*(PF_FULLV + st);
+                    pf_mbar_expect_tx(bk, 16384);
+                    pf_mbar_expect_tx(bv, 16384);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        pf_tma_2d(sk + 2048*i,        &tmK, kc0,      cur[i], bk);
+                        pf_tma_2d(sk + 8192 + 2048*i, &tmK, kc0 + 64, cur[i], bk);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        pf_tma_2d(sv + 2048*i,        &tmV, vc0,      cur[i], bv);
+                        pf_tma_2d(sv + 8192 + 2048*i, &tmV, vc0 + 64, cur[i], bv);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) cur[i] = nxt[i];
+                }
+            }
+        } else if (warp == 4) {
+            // ================= MMA issuer =================
+            if (lane == 0) {
+                constexpr uint32_t ID_QK = pf_idesc(PF_ROWS, PF_BN, 0), ID_PV = pf_idesc(PF_ROWS, PF_D, 1);
+                auto issue_qk = [&](uint32_t g) {
+                    const uint32_t st = g & 1, sk = sKV + st*32768;
+                    pf_mbar_wait(sBar + 8*(PF_FULLK + st), (g >> 1) & 1);
+                    pf_tc_fence_after();
+#pragma unroll
+                    for (int ks = 0; ks < 8; ++ks) {
+                        const uint64_t da = pf_desc(sQ + (ks >> 2)*16384 + (ks & 3)*32, 16, 1024);
+                        const uint64_t db = pf_desc(sk + (ks >> 2)*8192  + (ks & 3)*32, 16, 1024);
+                        pf_mma(tS + (g & 1)*64, da, db, ID_QK, ks > 0);
+                    }
+                    pf_commit(sBar + 8*(PF_SFULL + (g & 1)));
+                };
+                if (nkt > 0) issue_qk(G);
+                for (int j = 0; j < nkt; ++j) {
+                    const uint32_t g = G + j, st = g & 1, sv = sKV + st*32768 + 16384;
+                    if (j + 1 < nkt) issue_qk(g + 1);
+                    pf_mbar_wait(sBar + 8*PF_PFULL, g & 1);
+                    pf_mbar_wait(sBar + 8*(PF_FULLV + st), (g >> 1) & 1);
+                    pf_tc_fence_after();
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) {
+                        const uint64_t da = pf_desc(sP + ks*32, 16, 1024);
+                        const uint64_t db = pf_desc(sv + ks*2048, 8192, 1024);      // MN-major: LBO = next 64 d, SBO = next 8 tokens
+                        pf_mma(tO, da, db, ID_PV, (j > 0) || (ks > 0));
+                    }
+                    pf_commit(sBar + 8*(PF_EMPTY + st));
+                    pf_commit(sBar + 8*PF_ODONE);
+                }
+            }
+        } else {
+            // ================= softmax =================
+            const uint32_t lane_base = (uint32_t) (32*warp) << 16;
+            float m_run = -INFINITY, l_run = 0.f;
+            int nvis_min = __reduce_min_sync(0xffffffffu, n_vis);
+            uint32_t v[64];
+            for (int j = 0; j < nkt; ++j) {
+                const uint32_t g = G + j, st = g & 1;
+                pf_mbar_wait(sBar + 8*(PF_SFULL + (g & 1)), (g >> 1) & 1);
+                pf_tc_fence_after();
+                pf_tmem_ld32(tS + (g & 1)*64 + lane_base,      v, 0);
+                pf_tmem_ld32(tS + (g & 1)*64 + lane_base + 32, v, 32);
+                pf_tmem_wait_ld();
+                const int tok0 = j*PF_BN;
+                float mx = -INFINITY;
+                if (tok0 + PF_BN > nvis_min) {               // warp-uniform: only tiles that cross some row's limit mask
+#pragma unroll
+                    for (int c = 0; c < 64; ++c) { if (tok0 + c >= n_vis) v[c] = 0xff800000u; }
+                }
+#pragma unroll
+                for (int c = 0; c < 64; ++c) mx = fmaxf(mx, __uint_as_float(v[c]));
+                // lazy running max: move the reference point only when the max grew by more than 2^8
+                const bool grow = mx > m_run + 8.0f;
+                float alpha = 1.0f;
+                if (grow) { alpha = pf_ex2(m_run - mx); m_run = mx; }         // m_run == -inf: alpha = 0
+                const float msub = m_run == -INFINITY ? 0.0f : m_run;
+                float sum = 0.f;
+                uint32_t pk[32];
+#pragma unroll
+                for (int c = 0; c < 32; ++c) {
+                    const float p0 = pf_ex2(__uint_as_float(v[2*c]) - msub), p1 = pf_ex2(__uint_as_float(v[2*c + 1]) - msub);
+                    sum += p0 + p1;
+                    pk[c] = pf_pack_h2(p0, p1);
+                }
+                l_run = l_run*alpha + sum;
+                if (j > 0) {                                 // P buffer and O are free once PV of the previous tile retired
+                    pf_mbar_wait(sBar + 8*PF_ODONE, (g - 1) & 1);
+                    pf_tc_fence_after();
+                    if (__any_sync(0xffffffffu, grow)) {
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            pf_tmem_ld32(tO + lane_base + 64*h,      v, 0);
+                            pf_tmem_ld32(tO + lane_base + 64*h + 32, v, 32);
+                            pf_tmem_wait_ld();
+#pragma unroll
+                            for (int c = 0; c < 64; ++c) v[c] = __float_as_uint(__uint_as_float(v[c])*alpha);
+                            pf_tmem_st32(tO + lane_base + 64*h,      v, 0);
+                            pf_tmem_st32(tO + lane_base + 64*h + 32, v, 32);
+                        }
+                        pf_tmem_wait_st();
+                    }
+                }
+#pragma unroll
+                for (int c = 0; c < 8; ++c) pf_sts128(sP + pf_swz(r, c), pk[4*c], pk[4*c + 1], pk[4*c + 2], pk[4*c + 3]);
+                if (tok0 + PF_BN > seq_len) {                // cells past seq_len hold stale bytes: 0 * NaN must not reach O
+                    pf_mbar_wait(sBar + 8*(PF_FULLV + st), (g >> 1) & 1);
+                    const uint32_t sv = sKV + st*32768 + 16384;
+                    for (int idx = threadIdx.x; idx < 64*16; idx += 128) {
+                        const int tok = idx >> 4, c = idx & 15;
+                        if (tok0 + tok >= seq_len) pf_sts128(sv + (c >> 3)*8192 + pf_swz(tok, c & 7), 0u, 0u, 0u, 0u);
+                    }
+                }
+                pf_fence_async_smem();
+                pf_tc_fence_before();
+                pf_mbar_arrive(sBar + 8*PF_PFULL);
+            }
+            // ---- epilogue: O / l -> dst[row][head][d]
+            const bool live = tl < nrows;
+            float *out = static_cast<float *>(p.dst) + ((int64_t) (row0 + (live ? tl : 0))*p.n_head + kvh*gqa + hg)*PF_D;
+            if (nkt > 0) {
+                pf_mbar_wait(sBar + 8*PF_ODONE, (G + nkt - 1) & 1);
+                pf_tc_fence_after();
+                const float inv = 1.0f/l_run;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    pf_tmem_ld32(tO + lane_base + 64*h,      v, 0);
+                    pf_tmem_ld32(tO + lane_base + 64*h + 32, v, 32);
+                    pf_tmem_wait_ld();
+                    if (live) {
+#pragma unroll
+                        for (int c = 0; c < 64; c += 4)
+                            *reinterpret_cast<float4 *>(out + 64*h + c) = make_float4(__uint_as_float(v[c])*inv, __uint_as_float(v[c + 1])*inv,
+                                                                                      __uint_as_float(v[c + 2])*inv, __uint_as_float(v[c + 3])*inv);
+                    }
+                }
+            } else if (live) {
+                const float nan = __int_as_float(0x7fc00000);                     // no visible cell: 0/0 like the reference (ggml-cpu.c:12418)
+                for (int c = 0; c < PF_D; c += 4) *reinterpret_cast<float4 *>(out + c) = make_float4(nan, nan, nan, nan);
+            }
+            pf_tc_fence_before();
+        }
+        G += nkt;
+        __syncthreads();                                     // O, Q and the S buffers are free for the next work item
+    }
+
+    pf_tc_fence_before();
+    __syncthreads();
+    if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" :: "r"(tmem) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+typedef CUresult (*pf_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                 const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static pf_encode_fn pf_encoder() {
+    static pf_encode_fn fn = nullptr;
+    if (!fn) {
+        void *ptr = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<pf_encode_fn>(ptr);
+        else (void) cudaGetLastError();
+    }
+    return fn;
+}
+
+bool prefill_supports(const b200_attn_desc &d) {
+    if (!d.block_table || !d.seq_lens || d.head_dim != PF_D || d.max_bias != 0.0f || d.logit_softcap != 0.0f) return false;
+    if (d.type_k != B200_TYPE_F16 || d.type_v != B200_TYPE_F16) return false;
+    const int gqa = d.n_head/d.n_head_kv;
+    if (gqa < 1 || gqa > PF_ROWS || PF_ROWS % gqa) return false;
+    if (d.block_size % 16 || d.n_kv < 16) return false;                                   // one TMA box = 16 consecutive cells
+    if (((uintptr_t) d.k | (uintptr_t) d.v | (uint64_t) d.nbk1 | (uint64_t) d.nbv1 | (uint64_t) d.nbk2 | (uint64_t) d.nbv2) & 15) return false;
+    if (d.nbk1 <= 0 || d.nbv1 <= 0 || d.nbk2 <= 0 || d.nbv2 <= 0) return false;
+    if ((int64_t) (d.n_head_kv - 1)*d.nbk2 + 256 > d.nbk1 || (int64_t) (d.n_head_kv - 1)*d.nbv2 + 256 > d.nbv1) return false;
+    if (d.n_kv >= (1LL << 31) || d.n_kv*(d.nbk1 > d.nbv1 ? d.nbk1 : d.nbv1) >= (1LL << 40)) return false;
+    if (((uintptr_t) d.q | (uint64_t) d.nbq1 | (uint64_t) d.nbq2 | (uintptr_t) d.dst) & 15) return false;
+    return true;
+}
+
+size_t prefill_workspace(const b200_attn_desc &d) { return (2 + 2*(size_t) d.n_q)*sizeof(int) + 256; }
+
+static bool pf_make_map(CUtensorMap *tm, const void *base, int64_t nb1, int64_t nb2, int n_head_kv, int64_t n_cells) {
+    pf_encode_fn enc = pf_encoder();
+    if (!enc) { set_error("prefill: cuTensorMapEncodeTiled not available from the driver"); return false; }
+    const cuuint64_t dims[2]    = {(cuuint64_t) (((int64_t) (n_head_kv - 1)*nb2 + 256)/2), (cuuint64_t) n_cells};
+    const cuuint64_t strides[1] = {(cuuint64_t) nb1};
+    const cuuint32_t box[2]     = {64, 16};
+    const cuuint32_t ones[2]    = {1, 1};
+    const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(base), dims, strides, box, ones,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("prefill: cuTensorMapEncodeTiled failed with %d", (int) r); return false; }
+    return true;
+}
+
+int launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st) {
+    const size_t need = prefill_workspace(d);
+    if (d.workspace == nullptr || d.workspace_bytes < need) {
+        set_error("attention: workspace of %zu bytes needed, %zu given", need, d.workspace_bytes);
+        return B200_ERR_ALLOC;
+    }
+    static bool configured = false;
+    if (!configured) {
+        const cudaError_t e = cudaFuncSetAttribute(pf_main_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PF_SMEM);
+        if (e != cudaSuccess) { set_error("prefill: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return B200_ERR_CUDA; }
+        configured = true;
+    }
+    pf_args a;
+    a.d = d;
+    a.gqa = d.n_head/d.n_head_kv;
+    a.tok_per_tile = PF_ROWS/a.gqa;
+    a.plan = reinterpret_cast<int *>(d.workspace);
+    a.qscale = d.scale*1.4426950408889634f;
+    alignas(64) CUtensorMap tmK, tmV;
+    if (!pf_make_map(&tmK, d.k, d.nbk1, d.nbk2, d.n_head_kv, d.n_kv)) return B200_ERR_CUDA;
+    if (!pf_make_map(&tmV, d.v, d.nbv1, d.nbv2, d.n_head_kv, d.n_kv)) return B200_ERR_CUDA;
+
+    pf_plan_kernel<<<1, 1024, 0, st>>>(a);
+    count_launch();
+    if (!check_launch("pf_plan")) return B200_ERR_CUDA;
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) sms = 148;
+    int64_t grid = (int64_t) d.n_q*d.n_head_kv;              // upper bound on work items (one row per tile)
+    if (grid > 2*sms) grid = 2*sms;
+    pf_main_kernel<<<(unsigned) grid, PF_THREADS, PF_SMEM, st>>>(a, tmK, tmV);
+    count_launch();
+    if (!check_launch("pf_main")) return B200_ERR_CUDA;
+    return B200_OK;
+}
+
+} // namespace b200

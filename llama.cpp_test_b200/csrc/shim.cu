@@ -34,6 +34,9 @@ int    launch_attn_generic(const b200_attn_desc &d, cudaStream_t st);
 bool   streamk_supports(const b200_attn_desc &d);
 size_t streamk_workspace(const b200_attn_desc &d);
 int    launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st);
+bool   prefill_supports(const b200_attn_desc &d);
+size_t prefill_workspace(const b200_attn_desc &d);
+int    launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st);
 
 static bool have_device() {
     static int state = -1;                       // -1 unknown, 0 none, 1 ok
@@ -63,6 +66,9 @@ static int validate_attn(const b200_attn_desc *d) {
 static int pick_kernel(const b200_attn_desc &d) {
     if (d.kernel == B200_KERNEL_GENERIC) return B200_KERNEL_GENERIC;
     if (d.kernel == B200_KERNEL_STREAMK) return B200_KERNEL_STREAMK;
+    if (d.kernel == B200_KERNEL_PREFILL) return B200_KERNEL_PREFILL;
+    // many causal query rows per sequence: the tcgen05 tile kernel reads K/V once per 128/gqa rows instead of once per row
+    if (d.q_pos && d.n_q >= 128 && prefill_supports(d)) return B200_KERNEL_PREFILL;
     return streamk_supports(d) ? B200_KERNEL_STREAMK : B200_KERNEL_GENERIC;
 }
 
@@ -87,16 +93,21 @@ B200_API int b200_device_sm_count(void) {
 B200_API int b200_supports_attention(const b200_attn_desc *d) {
     if (validate_attn(d) != B200_OK) return 0;
     if (d->kernel == B200_KERNEL_STREAMK) return streamk_supports(*d) ? 1 : 0;
-    return (generic_supports(*d) || streamk_supports(*d)) ? 1 : 0;
+    if (d->kernel == B200_KERNEL_PREFILL) return prefill_supports(*d) ? 1 : 0;
+    if (d->kernel == B200_KERNEL_GENERIC) return generic_supports(*d) ? 1 : 0;
+    return (generic_supports(*d) || streamk_supports(*d) || prefill_supports(*d)) ? 1 : 0;
 }
 
 B200_API size_t b200_paged_attention_workspace(const b200_attn_desc *d) {
     if (validate_attn(d) != B200_OK) return 0;
     size_t a = generic_supports(*d) ? generic_workspace(*d) : 0;
     size_t b = streamk_supports(*d) ? streamk_workspace(*d) : 0;
-    if (d->kernel == B200_KERNEL_GENERIC) b = 0;
-    if (d->kernel == B200_KERNEL_STREAMK) a = 0;
-    return a > b ? a : b;
+    size_t c = prefill_supports(*d) ? prefill_workspace(*d) : 0;
+    if (d->kernel == B200_KERNEL_GENERIC) b = c = 0;
+    if (d->kernel == B200_KERNEL_STREAMK) a = c = 0;
+    if (d->kernel == B200_KERNEL_PREFILL) a = b = 0;
+    if (b > a) a = b;
+    return a > c ? a : c;
 }
 
 B200_API int b200_paged_attention(const b200_attn_desc *d, void *stream) {
@@ -105,6 +116,10 @@ B200_API int b200_paged_attention(const b200_attn_desc *d, void *stream) {
     if (!have_device()) return B200_ERR_CUDA;
     if (d->n_q == 0) return B200_OK;
     const int k = pick_kernel(*d);
+    if (k == B200_KERNEL_PREFILL) {
+        if (!prefill_supports(*d)) { set_error("attention: prefill tile kernel does not take this shape"); return B200_ERR_UNSUPPORTED; }
+        return launch_attn_prefill(*d, static_cast<cudaStream_t>(stream));
+    }
     if (k == B200_KERNEL_STREAMK) {
         if (!streamk_supports(*d)) { set_error("attention: stream-K kernel does not take this shape"); return B200_ERR_UNSUPPORTED; }
         return launch_attn_streamk(*d, static_cast<cudaStream_t>(stream));
