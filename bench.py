@@ -11,6 +11,8 @@ Workloads (all synthetic U(-1,1) data, 16-token blocks scattered by a seeded ran
   config1  same shape, 8 sequences x 1024 context, F16 (the reference's CPU-runnable case; latency-bound).
   config4  Llama-3-70B shape (64 q / 8 kv heads), 32 sequences x 32768 context, F16, 8 layers resident;
            KV heads sharded over the ranks + ONE NCCL all-gather of the outputs per layer => "strong".
+  config3  chunked prefill: 8 sequences, each appending a 512-token chunk at position 3584 (4096 causal query rows per
+           layer-op): slot-mapped KV write of the chunk + tile attention; metric = attention TFLOP/s (tensor roofline).
 One STEP = one decode step of the hot path = the attention op of every layer, each over its own KV cache (GBs per
 step, far beyond the 126 MB L2, so no flush is needed between iterations).
 
@@ -44,6 +46,8 @@ WORKLOADS = {
                     scaling="weak", kv_type="q8_0", steps=100),
     "config1": dict(n_head=32, n_head_kv=8, n_layer=32, n_seqs=8, ctx="1024", shard="sequences", scaling="weak",
                     kv_type="f16", steps=500),
+    "config3": dict(n_head=32, n_head_kv=8, n_layer=32, n_seqs=8, ctx="4096 (chunk of 512 appended at 3584)", shard="sequences",
+                    scaling="weak", kv_type="f16", steps=20),
     "config4": dict(n_head=64, n_head_kv=8, n_layer=8, n_seqs=32, ctx="32768", shard="heads", scaling="strong",
                     kv_type="f16", steps=50),
 }
@@ -57,7 +61,7 @@ def ctx_lens(workload, rank):
     w = WORKLOADS[workload]
     if workload == "config2":
         return np.random.default_rng(7 + rank).integers(512, 8193, size=w["n_seqs"]).astype(np.int32)
-    return np.full(w["n_seqs"], int(w["ctx"]), dtype=np.int32)
+    return np.full(w["n_seqs"], int(w["ctx"].split()[0]), dtype=np.int32)
 
 
 def block_tables(lens, seed=42):
@@ -205,6 +209,8 @@ def main():
     if args.impl == "reference":
         args.steps = args.steps or 3
         return reference_arm(args, rank, world)
+    if args.workload == "config3":
+        return run_config3(args, rank, world, local)
     args.steps = args.steps or W["steps"]
     args.warmup = max(args.warmup, 3)
 
@@ -382,6 +388,136 @@ def main():
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def run_config3(args, rank, world, local):
+    """chunked prefill (BASELINE config 3): per layer, slot-mapped write of the 8 x 512 new rows then causal tile
+    attention of those 4096 query rows over their sequences' 4096-token paged contexts"""
+    import torch
+    import torch.distributed as dist
+    from __graft_entry__ import load
+    pkg = load()
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    W = WORKLOADS["config3"]
+    t = TYPES[args.kv_type]
+    n_layer, n_seqs, n_head, n_head_kv = args.layers or W["n_layer"], W["n_seqs"], W["n_head"], W["n_head_kv"]
+    steps = args.steps or W["steps"]
+    CHUNK, P0 = 512, 3584
+    lens = ctx_lens("config3", rank)
+    bt_h, slot_h, n_blocks = block_tables(lens)
+    total = int(lens.sum())
+    lay = pkg.KVLayout(t, n_head_kv, D, BS, n_blocks + 8)
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    gen = torch.Generator(device="cuda"); gen.manual_seed(4321 + rank)
+    slot_d, bt_d, sl_d = dev(slot_h), dev(bt_h), dev(lens)
+    starts = np.concatenate([[0], np.cumsum(lens.astype(np.int64))[:-1]])
+    rows_seq = np.repeat(np.arange(n_seqs, dtype=np.int32), CHUNK)
+    rows_pos = np.tile(np.arange(P0, P0 + CHUNK, dtype=np.int32), n_seqs)
+    slot_chunk = dev(slot_h[(starts[rows_seq] + rows_pos).astype(np.int64)])
+    qs_d, qp_d = dev(rows_seq), dev(rows_pos)
+    n_q = n_seqs * CHUNK
+    kcs, vcs = [], []
+    for _ in range(n_layer):
+        kc, vc = lay.alloc(), lay.alloc()
+        for o in range(0, total, 16384):
+            n = min(16384, total - o)
+            ks = torch.rand((n, n_head_kv * D), generator=gen, device="cuda") * 2 - 1
+            vs = torch.rand((n, n_head_kv * D), generator=gen, device="cuda") * 2 - 1
+            pkg.kv_write(ks, vs, slot_d[o:o + n], kc, vc, lay)
+        kcs.append(kc); vcs.append(vc)
+    knew = torch.rand((n_q, n_head_kv * D), generator=gen, device="cuda") * 2 - 1
+    vnew = torch.rand((n_q, n_head_kv * D), generator=gen, device="cuda") * 2 - 1
+    q_d = torch.rand((n_q, n_head, D), generator=gen, device="cuda") * 2 - 1        # one Q / out buffer shared by the layers
+    out_d = torch.empty_like(q_d)
+    scale = float(1.0 / np.sqrt(D))
+    calls = [pkg.AttnCall(q_d, kcs[l], vcs[l], lay, out_d, scale, block_table=bt_d, seq_lens=sl_d, q_seq=qs_d, q_pos=qp_d,
+                          max_seq_len=int(lens.max()), total_tokens=total, kernel=args.kernel) for l in range(n_layer)]
+    torch.cuda.synchronize()
+
+    def writes():
+        for l in range(n_layer):
+            pkg.kv_write(knew, vnew, slot_chunk, kcs[l], vcs[l], lay)
+
+    def attns():
+        for c in calls:
+            c.run()
+
+    def step():
+        for l in range(n_layer):
+            pkg.kv_write(knew, vnew, slot_chunk, kcs[l], vcs[l], lay)
+            calls[l].run()
+
+    def graphed(fn):
+        if args.no_graph:
+            return fn
+        side = torch.cuda.Stream(); side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            fn()
+        torch.cuda.current_stream().wait_stream(side)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            fn()
+        return g.replay
+
+    l0 = pkg.lib.b200_launch_count(); step(); launches = pkg.lib.b200_launch_count() - l0
+
+    def timed(fn, n):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ms = torch.tensor([e0.elapsed_time(e1) / n], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    sampler = ClockSampler(local); sampler.start()
+    ms_step = timed(graphed(step), steps)
+    ms_attn = timed(graphed(attns), steps)
+    ms_write = timed(graphed(writes), steps)
+    clocks = sampler.summary()
+    vis = float(sum(min(int(lens[s]), P0 + i + 1) for s in range(n_seqs) for i in range(CHUNK)))
+    flops_op = 4.0 * n_head * D * vis                                   # QK^T + PV over the visible (causal) cells
+    write_bytes_op = n_q * n_head_kv * D * (4 + row_bytes(t, D) / D) * 2   # F32 rows in, typed rows out, K and V
+    if rank == 0:
+        tf_attn = flops_op * n_layer / (ms_attn * 1e-3) / 1e12
+        tf_step = flops_op * n_layer * world / (ms_step * 1e-3) / 1e12
+        peak = 1640.5
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                peak = float(json.load(f)["bf16_tflops"])
+        except Exception:
+            pass
+        cfg = workload_config("config3", args.kv_type, world)
+        cfg.update({"n_layer": n_layer, "chunk": CHUNK, "chunk_start": P0, "query_rows_per_layer_op": n_q, "cuda_graph": not args.no_graph,
+                    "kernel": "tcgen05 tile kernel (plan + main)" if args.kernel in (0, 3) else f"kernel {args.kernel}",
+                    "l2_flush": f"per-layer KV caches ({2 * lay.total_bytes * n_layer / 1e9:.1f} GB per step) exceed the 126 MB L2"})
+        line = {"metric": "chunked-prefill paged attention TFLOP/s (KV write + attention per layer)", "value": round(tf_step, 2),
+                "unit": "TFLOP/s", "n_gpus": world, "steps": steps, "warmup": 3, "ms_per_step": round(ms_step, 4),
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16 (fp32 accumulate)", "data": "synthetic",
+                "config": cfg, "prefill_tok_s": round(n_q * world / (ms_step * 1e-3) / n_layer, 1),
+                "attention_only": {"ms_per_step": round(ms_attn, 4), "tflops_per_gpu": round(tf_attn, 2)},
+                "kv_write_only": {"ms_per_step": round(ms_write, 4), "gbs_per_gpu": round(write_bytes_op * n_layer / (ms_write * 1e-3) / 1e9, 1),
+                                  "algorithmic_bytes_per_launch": int(write_bytes_op)},
+                "gpu_launches": int(launches * steps),
+                "roofline": {"bound": "tensor", "achieved": round(tf_attn, 2), "peak": peak, "unit": "TFLOP/s", "frac": round(tf_attn / peak, 4),
+                             "traffic": None, "peak_source": "measured (MEASURED_PEAKS.json bf16_tflops, burst)",
+                             "kernel": "pf_main_kernel, one layer", "algorithmic_flops_per_launch": flops_op},
+                "clocks": clocks}
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier(); dist.destroy_process_group()
 
 
 def _uses_streamk(pkg, call):

@@ -39,7 +39,7 @@ constexpr int PF_SP      = 98304;        // [128 rows][128 B]
 constexpr int PF_SBAR    = 114688;
 constexpr int PF_SMEM    = PF_SBAR + 128;
 
-enum { PF_FULLK = 0, PF_FULLV = 2, PF_EMPTY = 4, PF_SFULL = 6, PF_PFULL = 8, PF_ODONE = 9, PF_NBAR = 10 };
+enum { PF_FULLK = 0, PF_FULLV = 2, PF_EMPTYK = 4, PF_EMPTYV = 6, PF_SFULL = 8, PF_PFULL = 10, PF_ODONE = 11, PF_NBAR = 12 };
 
 struct pf_args {
     b200_attn_desc d;
@@ -66,6 +66,14 @@ __device__ __forceinline__ void pf_mbar_wait(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void pf_tma_2d(uint32_t dst, const CUtensorMap *tm, int c0, int c1, uint32_t bar) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
                  :: "r"(dst), "l"(tm), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+// both d-halves of one 16-cell block, issued by ONE elected lane of a converged warp: with elect.sync ptxas knows a
+// single thread runs the copies and emits plain UTMALDG (an `if (lane == 0)` costs an 11-instruction vote loop each)
+__device__ __forceinline__ void pf_tma_pair_elect(uint32_t dst, const CUtensorMap *tm, int c0, int cell, uint32_t bar) {
+    asm volatile("{\n .reg .pred p;\n .reg .b32 d1, c1;\n elect.sync _|p, 0xffffffff;\n add.u32 d1, %0, 8192;\n add.s32 c1, %2, 64;\n"
+                 " @p cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];\n"
+                 " @p cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [d1], [%1, {c1, %3}], [%4];\n}"
+                 :: "r"(dst), "l"(tm), "r"(c0), "r"(cell), "r"(bar) : "memory");
 }
 __device__ __forceinline__ void pf_fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void pf_tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -252,40 +260,49 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
 
         if (warp == 5) {
             // ================= TMA producer =================
-            if (lane == 0) {
-                const int kc0 = (int) ((int64_t) kvh*p.nbk2/2), vc0 = (int) ((int64_t) kvh*p.nbv2/2);   // element coordinate of the head row
-                // block-table entries of the NEXT tile are fetched before waiting for a free stage, so the gather
-                // never adds a global-load latency to the TMA latency
-                auto cells_of = [&](int j, int (&cell)[4]) {
+            // K and V have their own 2-stage rings: a K stage is free as soon as QK^T of its tile retired, long before
+            // the V stage (after PV), and K runs one tile ahead of V — the order the MMA warp consumes them in.
+            // Lane l holds block-table entry win_base + l; the next 32 entries are fetched one window ahead, so the
+            // gather never waits on a global load (the whole warp takes part, lane 0 talks to the TMA unit).
+            const int kc0 = (int) ((int64_t) kvh*p.nbk2/2), vc0 = (int) ((int64_t) kvh*p.nbv2/2);   // element coordinate of the head row
+            int win_base = 0;
+            int win      = lane < n_blk ? bt[lane] : 0;
+            int win_next = 32 + lane < n_blk ? bt[32 + lane] : 0;
+            const int tpb = bs/16;                           // 16-cell boxes per block
+            int b_cur = 0, o_cur = 0;
+            int cell[4], vcell[4] = {0, 0, 0, 0};
+            for (int t = 0; t <= nkt; ++t) {
+                if (t < nkt) {
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
-                        const int tok = j*PF_BN + 16*i, bi = tok/bs;
-                        cell[i] = (bi < n_blk ? bt[bi] : 0)*bs + (tok - bi*bs);
+                        if (b_cur - win_base >= 32) {
+                            win_base += 32; win = win_next;
+                            win_next = win_base + 32 + lane < n_blk ? bt[win_base + 32 + lane] : 0;
+                        }
+                        cell[i] = __shfl_sync(0xffffffffu, win, b_cur - win_base)*bs + o_cur*16;
+                        if (++o_cur == tpb) { o_cur = 0; ++b_cur; }
                     }
-                };
-                int cur[4], nxt[4];
-                if (nkt > 0) cells_of(0, cur);
-                for (int j = 0; j < nkt; ++j) {
-                    const uint32_t g = G + j, st = g & 1;
-                    if (j + 1 < nkt) cells_of(j + 1, nxt);
-                    pf_mbar_wait(sBar + 8*(PF_EMPTY + st), ((g >> 1) & 1) ^ 1);
-                    const uint32_t sk = sKV + st*32768, sv = sk + 16384;
-                    const uint32_t bk = sBar + 8*(PF_FULLK + st), bv = sBar + 8*(PF_FULLV + st);
-                    pf_mbar_expect_tx(bk, 16384);
-                    pf_mbar_expect_tx(bv, 16384);
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        pf_tma_2d(sk + 2048*i,        &tmK, kc0,      cur[i], bk);
-                        pf_tma_2d(sk + 8192 + 2048*i, &tmK, kc0 + 64, cur[i], bk);
+                    const uint32_t g = G + t, st = g & 1, sk = sKV + st*32768, bk = sBar + 8*(PF_FULLK + st);
+                    if (lane == 0) {
+                        pf_mbar_wait(sBar + 8*(PF_EMPTYK + st), ((g >> 1) & 1) ^ 1);
+                        pf_mbar_expect_tx(bk, 16384);
                     }
+                    __syncwarp();
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        pf_tma_2d(sv + 2048*i,        &tmV, vc0,      cur[i], bv);
-                        pf_tma_2d(sv + 8192 + 2048*i, &tmV, vc0 + 64, cur[i], bv);
-                    }
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) cur[i] = nxt[i];
+                    for (int i = 0; i < 4; ++i) pf_tma_pair_elect(sk + 2048*i, &tmK, kc0, cell[i], bk);
                 }
+                if (t > 0) {
+                    const uint32_t g = G + t - 1, st = g & 1, sv = sKV + st*32768 + 16384, bv = sBar + 8*(PF_FULLV + st);
+                    if (lane == 0) {
+                        pf_mbar_wait(sBar + 8*(PF_EMPTYV + st), ((g >> 1) & 1) ^ 1);
+                        pf_mbar_expect_tx(bv, 16384);
+                    }
+                    __syncwarp();
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) pf_tma_pair_elect(sv + 2048*i, &tmV, vc0, vcell[i], bv);
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) vcell[i] = cell[i];
             }
         } else if (warp == 4) {
             // ================= MMA issuer =================
@@ -301,6 +318,7 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                         const uint64_t db = pf_desc(sk + (ks >> 2)*8192  + (ks & 3)*32, 16, 1024);
                         pf_mma(tS + (g & 1)*64, da, db, ID_QK, ks > 0);
                     }
+                    pf_commit(sBar + 8*(PF_EMPTYK + st));
                     pf_commit(sBar + 8*(PF_SFULL + (g & 1)));
                 };
                 if (nkt > 0) issue_qk(G);
@@ -316,7 +334,7 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                         const uint64_t db = pf_desc(sv + ks*2048, 8192, 1024);      // MN-major: LBO = next 64 d, SBO = next 8 tokens
                         pf_mma(tO, da, db, ID_PV, (j > 0) || (ks > 0));
                     }
-                    pf_commit(sBar + 8*(PF_EMPTY + st));
+                    pf_commit(sBar + 8*(PF_EMPTYV + st));
                     pf_commit(sBar + 8*PF_ODONE);
                 }
             }

@@ -1,3 +1,3 @@
-timeout 180 python -m pytest tests/test_gpu_prefill.py -x -q 2>&1 | tail -25
-echo "rc=$?"
-nvidia-smi --query-gpu=name,memory.used --format=csv,noheader
+timeout 240 python -m pytest tests/test_gpu_prefill.py -x -q 2>&1 | tail -4
+timeout 300 python bench.py --workload config3 --layers 8 --steps 10 2>&1 | tail -1 | python -c "
+import sys,json; d=json.loads(sys.stdin.read()); print(d['value'], d['attention_only'], d['kv_write_only'], d['clocks'])"
