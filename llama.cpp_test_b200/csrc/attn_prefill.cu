@@ -89,12 +89,13 @@ __device__ __forceinline__ uint64_t pf_desc(uint32_t addr, uint32_t lbo_bytes, u
 __host__ __device__ constexpr uint32_t pf_idesc(int m, int n, int b_mn_major) {
     return (1u << 4) | ((uint32_t) b_mn_major << 16) | ((uint32_t) (n >> 3) << 17) | ((uint32_t) (m >> 4) << 24);
 }
+// issued by ONE elected lane of a converged warp (elect.sync lets ptxas emit the uniform-datapath instruction directly)
 __device__ __forceinline__ void pf_mma(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile("{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
+    asm volatile("{\n .reg .pred p, e;\n elect.sync _|e, 0xffffffff;\n setp.ne.b32 p, %4, 0;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
                  :: "r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void pf_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
+    asm volatile("{\n .reg .pred e;\n elect.sync _|e, 0xffffffff;\n @e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n}" :: "r"(bar) : "memory");
 }
 
 #define PF_R32(v, o) "=r"(v[o+0]), "=r"(v[o+1]), "=r"(v[o+2]), "=r"(v[o+3]), "=r"(v[o+4]), "=r"(v[o+5]), "=r"(v[o+6]), "=r"(v[o+7]), \
@@ -305,38 +306,36 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                 for (int i = 0; i < 4; ++i) vcell[i] = cell[i];
             }
         } else if (warp == 4) {
-            // ================= MMA issuer =================
-            if (lane == 0) {
-                constexpr uint32_t ID_QK = pf_idesc(PF_ROWS, PF_BN, 0), ID_PV = pf_idesc(PF_ROWS, PF_D, 1);
-                auto issue_qk = [&](uint32_t g) {
-                    const uint32_t st = g & 1, sk = sKV + st*32768;
-                    pf_mbar_wait(sBar + 8*(PF_FULLK + st), (g >> 1) & 1);
-                    pf_tc_fence_after();
+            // ================= MMA issuer =================  (whole warp converged; one elected lane issues)
+            constexpr uint32_t ID_QK = pf_idesc(PF_ROWS, PF_BN, 0), ID_PV = pf_idesc(PF_ROWS, PF_D, 1);
+            auto issue_qk = [&](uint32_t g) {
+                const uint32_t st = g & 1, sk = sKV + st*32768;
+                pf_mbar_wait(sBar + 8*(PF_FULLK + st), (g >> 1) & 1);
+                pf_tc_fence_after();
 #pragma unroll
-                    for (int ks = 0; ks < 8; ++ks) {
-                        const uint64_t da = pf_desc(sQ + (ks >> 2)*16384 + (ks & 3)*32, 16, 1024);
-                        const uint64_t db = pf_desc(sk + (ks >> 2)*8192  + (ks & 3)*32, 16, 1024);
-                        pf_mma(tS + (g & 1)*64, da, db, ID_QK, ks > 0);
-                    }
-                    pf_commit(sBar + 8*(PF_EMPTYK + st));
-                    pf_commit(sBar + 8*(PF_SFULL + (g & 1)));
-                };
-                if (nkt > 0) issue_qk(G);
-                for (int j = 0; j < nkt; ++j) {
-                    const uint32_t g = G + j, st = g & 1, sv = sKV + st*32768 + 16384;
-                    if (j + 1 < nkt) issue_qk(g + 1);
-                    pf_mbar_wait(sBar + 8*PF_PFULL, g & 1);
-                    pf_mbar_wait(sBar + 8*(PF_FULLV + st), (g >> 1) & 1);
-                    pf_tc_fence_after();
-#pragma unroll
-                    for (int ks = 0; ks < 4; ++ks) {
-                        const uint64_t da = pf_desc(sP + ks*32, 16, 1024);
-                        const uint64_t db = pf_desc(sv + ks*2048, 8192, 1024);      // MN-major: LBO = next 64 d, SBO = next 8 tokens
-                        pf_mma(tO, da, db, ID_PV, (j > 0) || (ks > 0));
-                    }
-                    pf_commit(sBar + 8*(PF_EMPTYV + st));
-                    pf_commit(sBar + 8*PF_ODONE);
+                for (int ks = 0; ks < 8; ++ks) {
+                    const uint64_t da = pf_desc(sQ + (ks >> 2)*16384 + (ks & 3)*32, 16, 1024);
+                    const uint64_t db = pf_desc(sk + (ks >> 2)*8192  + (ks & 3)*32, 16, 1024);
+                    pf_mma(tS + (g & 1)*64, da, db, ID_QK, ks > 0);
                 }
+                pf_commit(sBar + 8*(PF_EMPTYK + st));
+                pf_commit(sBar + 8*(PF_SFULL + (g & 1)));
+            };
+            if (nkt > 0) issue_qk(G);
+            for (int j = 0; j < nkt; ++j) {
+                const uint32_t g = G + j, st = g & 1, sv = sKV + st*32768 + 16384;
+                if (j + 1 < nkt) issue_qk(g + 1);
+                pf_mbar_wait(sBar + 8*PF_PFULL, g & 1);
+                pf_mbar_wait(sBar + 8*(PF_FULLV + st), (g >> 1) & 1);
+                pf_tc_fence_after();
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {
+                    const uint64_t da = pf_desc(sP + ks*32, 16, 1024);
+                    const uint64_t db = pf_desc(sv + ks*2048, 8192, 1024);      // MN-major: LBO = next 64 d, SBO = next 8 tokens
+                    pf_mma(tO, da, db, ID_PV, (j > 0) || (ks > 0));
+                }
+                pf_commit(sBar + 8*(PF_EMPTYV + st));
+                pf_commit(sBar + 8*PF_ODONE);
             }
         } else {
             // ================= softmax =================
