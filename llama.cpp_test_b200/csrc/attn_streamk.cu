@@ -104,6 +104,32 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *tm,
                  :: "r"(dst), "l"(tm), "r"(c0), "r"(c1), "r"(c2), "r"(bar) : "memory");
 }
 
+// One tile's K box + V box and their expect_tx, issued by ONE elected lane of the converged warp.  With elect.sync
+// ptxas knows a single thread runs the copies and emits plain UTMALDG; `if (lane == 0)` costs an 11-instruction
+// vote loop per copy (profiles/r1i_*: the issue path was 16 % of the decode loop's instructions).
+template <bool K3D, bool V3D>
+__device__ __forceinline__ void sk_issue_elect(uint32_t bar, uint32_t bytes, uint32_t dk, const CUtensorMap *tmK, int kc,
+                                               uint32_t dv, const CUtensorMap *tmV, int vc, int cell) {
+    asm volatile("{\n .reg .pred p;\n elect.sync _|p, 0xffffffff;\n"
+                 " @p mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n}" :: "r"(bar), "r"(bytes) : "memory");
+    if constexpr (K3D)
+        asm volatile("{\n .reg .pred p;\n elect.sync _|p, 0xffffffff;\n"
+                     " @p cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];\n}"
+                     :: "r"(dk), "l"(tmK), "r"(0), "r"(cell), "r"(kc), "r"(bar) : "memory");
+    else
+        asm volatile("{\n .reg .pred p;\n elect.sync _|p, 0xffffffff;\n"
+                     " @p cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];\n}"
+                     :: "r"(dk), "l"(tmK), "r"(kc), "r"(cell), "r"(bar) : "memory");
+    if constexpr (V3D)
+        asm volatile("{\n .reg .pred p;\n elect.sync _|p, 0xffffffff;\n"
+                     " @p cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];\n}"
+                     :: "r"(dv), "l"(tmV), "r"(0), "r"(cell), "r"(vc), "r"(bar) : "memory");
+    else
+        asm volatile("{\n .reg .pred p;\n elect.sync _|p, 0xffffffff;\n"
+                     " @p cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];\n}"
+                     :: "r"(dv), "l"(tmV), "r"(vc), "r"(cell), "r"(bar) : "memory");
+}
+
 __device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
     asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];\n"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
@@ -523,13 +549,10 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
             const int blk = __shfl_sync(0xffffffffu, win, b_cur - win_base);
             const int cell = blk*bs + o_cur*SK_TILE;
             if (++o_cur == tpb) { o_cur = 0; ++b_cur; }
-            if (lane == 0) {
+            {
                 const uint32_t bar = bar0 + 8*is, sb = smem0 + is*SM::STAGE;
-                mbar_expect_tx(bar, SM::KT + SM::VT);
-                if constexpr (TK == B200_TYPE_F16) tma_load_3d(sb + SM::KOFF, &tmK, 0, cell, kc, bar);
-                else                               tma_load_2d(sb + SM::KOFF, &tmK, kc, cell, bar);
-                if constexpr (TV == B200_TYPE_F16) tma_load_3d(sb + SM::VOFF, &tmV, 0, cell, vc, bar);
-                else                               tma_load_2d(sb + SM::VOFF, &tmV, vc, cell, bar);
+                sk_issue_elect<TK == B200_TYPE_F16, TV == B200_TYPE_F16>(bar, SM::KT + SM::VT, sb + SM::KOFF, &tmK, kc,
+                                                                        sb + SM::VOFF, &tmV, vc, cell);
             }
             if (++is == STAGES) is = 0;
         };
