@@ -18,8 +18,8 @@ step, far beyond the 126 MB L2, so no flush is needed between iterations).
 
   value        whole-job KV GB/s with everything resident in HBM (CUDA-graph replay when no collective is inside)
   e2e          same metric through the C ABI the way a host uses it per step: pinned-host Q / new K,V rows / block
-               table / seq_lens copied H2D (copy stream, overlapped layer by layer), b200_kv_write +
-               b200_paged_attention per layer, outputs D2H, host waits for the last byte
+               table / seq_lens copied H2D (copy stream, overlapped group by group), one b200_decode_step call
+               (b200_kv_write + b200_paged_attention per layer) per group of 8 layers, outputs D2H, host waits for the last byte
   roofline     op-level achieved GB/s = algorithmic KV bytes of one layer-op / CUDA-event time, vs MEASURED_PEAKS.json
   cpu_baseline the reference's own ggml CPU FLASH_ATTN_EXT (oracle/_ref) on a bounded sample of the same workload
 """
@@ -330,8 +330,16 @@ def main():
         h2d = 4 * (q_h.numel() + knew_h.numel() + vnew_h.numel() + bt_hp.numel() + sl_hp.numel() + slot_new_h.numel())
         d2h = 4 * out_h.numel()
         s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
-        ev_in = [torch.cuda.Event() for _ in range(n_layer)]
-        ev_c = [torch.cuda.Event() for _ in range(n_layer)]
+        # layers go through the C ABI in groups: one b200_decode_step call (kv_write + attention per layer) per group,
+        # its inputs copied H2D on the copy stream while the previous group computes, its outputs D2H while the next does
+        GL = 1 if collective else 8
+        groups = [(a0, min(a0 + GL, n_layer)) for a0 in range(0, n_layer, GL)]
+        ev_in = [torch.cuda.Event() for _ in groups]
+        ev_c = [torch.cuda.Event() for _ in groups]
+        group_calls = None
+        if not collective:
+            group_calls = [pkg.StepCall(calls[a0:a1], [pkg.kv_write_desc(knew_d[l], vnew_d[l], slot_new_d, kcs[l], vcs[l], lay)
+                                                        for l in range(a0, a1)]) for a0, a1 in groups]
 
         def step_e2e():
             cur = torch.cuda.current_stream()
@@ -339,18 +347,22 @@ def main():
             with torch.cuda.stream(s_in):
                 bt_d.copy_(bt_hp, non_blocking=True); sl_d.copy_(sl_hp, non_blocking=True)
                 slot_new_d.copy_(slot_new_h, non_blocking=True)
-                for l in range(n_layer):
-                    q_d[l].copy_(q_h[l], non_blocking=True)
-                    knew_d[l].copy_(knew_h[l], non_blocking=True); vnew_d[l].copy_(vnew_h[l], non_blocking=True)
-                    ev_in[l].record(s_in)
-            for l in range(n_layer):
-                cur.wait_event(ev_in[l])
-                pkg.kv_write(knew_d[l], vnew_d[l], slot_new_d, kcs[l], vcs[l], lay)
-                layer_op(l)
-                ev_c[l].record(cur)
-                s_out.wait_event(ev_c[l])
+                for gi, (a0, a1) in enumerate(groups):
+                    q_d[a0:a1].copy_(q_h[a0:a1], non_blocking=True)
+                    knew_d[a0:a1].copy_(knew_h[a0:a1], non_blocking=True); vnew_d[a0:a1].copy_(vnew_h[a0:a1], non_blocking=True)
+                    ev_in[gi].record(s_in)
+            for gi, (a0, a1) in enumerate(groups):
+                cur.wait_event(ev_in[gi])
+                if group_calls is not None:
+                    group_calls[gi].run()
+                else:
+                    for l in range(a0, a1):
+                        pkg.kv_write(knew_d[l], vnew_d[l], slot_new_d, kcs[l], vcs[l], lay)
+                        layer_op(l)
+                ev_c[gi].record(cur)
+                s_out.wait_event(ev_c[gi])
                 with torch.cuda.stream(s_out):
-                    out_h[l].copy_(res_d[l], non_blocking=True)
+                    out_h[a0:a1].copy_(res_d[a0:a1], non_blocking=True)
             s_out.synchronize()                              # the host holds the step's result
 
         e2e_steps = max(3, args.steps // 2)

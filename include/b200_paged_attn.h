@@ -117,6 +117,15 @@ B200_API int b200_kv_write(const b200_kv_write_desc *d, void *stream);
 B200_API int b200_block_copy(void *const *caches, int32_t n_caches, int64_t block_bytes, int64_t n_blocks,
                              const int32_t *pairs /* device [n_pairs][2] */, int64_t n_pairs, void *stream);
 
+/*
+ * One decode/prefill step over several layers in ONE call: for l in [0, n_layers): b200_kv_write(&writes[l]) (skipped
+ * when writes == NULL) then b200_paged_attention(&attns[l]), all on `stream`.  This is the loop
+ * llama_context::decode runs through ggml_backend_sched for the attention part of every layer
+ * (src/llama-context.cpp:1291-1353); batching it removes the per-call host overhead of an FFI host.
+ * Stops at the first failing layer and returns its status.
+ */
+B200_API int b200_decode_step(const b200_kv_write_desc *writes, const b200_attn_desc *attns, int32_t n_layers, void *stream);
+
 /* diagnostics */
 B200_API const char *b200_last_error(void);
 B200_API const char *b200_version(void);

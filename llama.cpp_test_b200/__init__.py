@@ -85,7 +85,7 @@ GGML_OP_CPY, GGML_OP_FLASH_ATTN_EXT, GGML_TYPE_I32 = 32, 62, 26
 EXPORTS = {
     "b200_paged_attn.h": [
         "b200_paged_attention_workspace", "b200_paged_attention", "b200_supports_attention", "b200_kv_write",
-        "b200_block_copy", "b200_last_error", "b200_version", "b200_device_sm_count", "b200_launch_count"],
+        "b200_block_copy", "b200_decode_step", "b200_last_error", "b200_version", "b200_device_sm_count", "b200_launch_count"],
     "b200_ggml_abi.h": ["b200_flash_attn_ext_workspace", "b200_flash_attn_ext", "b200_cpy", "b200_supports_op"],
     "b200_host.h": [
         "b200_bm_create", "b200_bm_destroy", "b200_bm_allocate", "b200_bm_free", "b200_bm_evict", "b200_bm_status",
@@ -103,6 +103,8 @@ lib.b200_kv_write.restype = C.c_int
 lib.b200_kv_write.argtypes = [C.POINTER(KVWriteDesc), C.c_void_p]
 lib.b200_block_copy.restype = C.c_int
 lib.b200_block_copy.argtypes = [C.POINTER(C.c_void_p), C.c_int32, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]
+lib.b200_decode_step.restype = C.c_int
+lib.b200_decode_step.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]
 lib.b200_last_error.restype = C.c_char_p
 lib.b200_version.restype = C.c_char_p
 lib.b200_device_sm_count.restype = C.c_int

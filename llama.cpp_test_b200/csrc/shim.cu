@@ -143,6 +143,16 @@ B200_API int b200_kv_write(const b200_kv_write_desc *d, void *stream) {
     return launch_kv_write(*d, static_cast<cudaStream_t>(stream));
 }
 
+B200_API int b200_decode_step(const b200_kv_write_desc *writes, const b200_attn_desc *attns, int32_t n_layers, void *stream) {
+    if (n_layers < 0 || (n_layers > 0 && !attns)) { set_error("decode_step: bad arguments"); return B200_ERR_INVALID; }
+    for (int32_t l = 0; l < n_layers; ++l) {
+        if (writes) { const int rc = b200_kv_write(&writes[l], stream); if (rc != B200_OK) return rc; }
+        const int rc = b200_paged_attention(&attns[l], stream);
+        if (rc != B200_OK) return rc;
+    }
+    return B200_OK;
+}
+
 B200_API int b200_block_copy(void *const *caches, int32_t n_caches, int64_t block_bytes, int64_t n_blocks,
                              const int32_t *pairs, int64_t n_pairs, void *stream) {
     if (n_caches < 0 || n_pairs < 0 || (n_caches > 0 && !caches) || (n_pairs > 0 && !pairs)) { set_error("block_copy: bad arguments"); return B200_ERR_INVALID; }

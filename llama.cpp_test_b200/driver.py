@@ -8,7 +8,7 @@ from dataclasses import dataclass
 from . import (AttnDesc, KVWriteDesc, KERNEL_AUTO, TYPE_F16, TYPE_F32, TYPE_Q4_0, TYPE_Q8_0,  # noqa: F401
                check, lib, row_bytes)
 
-__all__ = ["KVLayout", "AttnCall", "paged_attention", "dense_attention", "kv_write", "block_copy",
+__all__ = ["KVLayout", "AttnCall", "StepCall", "kv_write_desc", "paged_attention", "dense_attention", "kv_write", "block_copy",
            "BlockManager", "PagedKVCache", "current_stream"]
 
 
@@ -120,6 +120,36 @@ def dense_attention(q, k_cache, v_cache, layout: KVLayout, n_kv: int, mask, scal
         out = torch.empty_like(q)
     AttnCall(q, k_cache, v_cache, layout, out, scale, mask=mask, n_kv=n_kv, **kw).run()
     return out
+
+
+class StepCall:
+    """b200_decode_step over a fixed list of layers: descriptor arrays are built once, one FFI call per step."""
+
+    def __init__(self, attn_calls, write_descs=None):
+        n = len(attn_calls)
+        self.n = n
+        self.attns = (AttnDesc * n)(*[c.desc for c in attn_calls])
+        self.writes = None if write_descs is None else (KVWriteDesc * n)(*write_descs)
+        self._keep = (attn_calls, write_descs)
+
+    def run(self, stream: int | None = None) -> None:
+        check(lib.b200_decode_step(None if self.writes is None else C.cast(self.writes, C.c_void_p), C.cast(self.attns, C.c_void_p),
+                                   self.n, C.c_void_p(current_stream() if stream is None else stream)), "b200_decode_step")
+
+
+def kv_write_desc(k_src, v_src, slot_mapping, k_cache, v_cache, layout_k: KVLayout, layout_v: KVLayout | None = None) -> KVWriteDesc:
+    layout_v = layout_v or layout_k
+    src = k_src if k_src is not None else v_src
+    d = KVWriteDesc()
+    d.k_src, d.v_src, d.src_nb1 = _ptr(k_src), _ptr(v_src), src.stride(0) * 4
+    d.n_tokens = src.shape[0]
+    d.slot_mapping = _ptr(slot_mapping)
+    d.k_cache, d.v_cache = _ptr(k_cache), _ptr(v_cache)
+    d.type_k, d.type_v, d.n_head_kv, d.head_dim = layout_k.type_id, layout_v.type_id, layout_k.n_head_kv, layout_k.head_dim
+    d.nbk_token, d.nbk_head = layout_k.token_bytes, layout_k.head_bytes
+    d.nbv_token, d.nbv_head = layout_v.token_bytes, layout_v.head_bytes
+    d.n_cells = layout_k.n_cells
+    return d
 
 
 def kv_write(k_src, v_src, slot_mapping, k_cache, v_cache, layout_k: KVLayout, layout_v: KVLayout | None = None,
