@@ -562,41 +562,55 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
 #pragma unroll
         for (int s = 0; s < STAGES - NSUB; ++s) { if (issued < nt) { issue(); ++issued; } }
 
-        for (int i = 0; i < nt; i += NSUB) {
-            __syncwarp();                                    // every lane is done with the slots about to be refilled
-#pragma unroll
-            for (int u = 0; u < NSUB; ++u) { if (issued < nt) { issue(); ++issued; } }
-            const int nsub = min(NSUB, nt - i);              // tiles of this iteration (warp-uniform)
-
-            float S[NSUB][4];
-            uint32_t vbs[NSUB];
+        // One loop iteration = NSUB tiles sharing one softmax step.  FULL iterations (all tiles complete and inside the
+        // row's visible range, no softcap) run branch-free between the barrier waits and the rescale vote, so the
+        // independent dequantise -> MMA chains of the tiles interleave; the row's last iteration takes the general path.
+        auto body = [&](auto full_c, int i) {
+            constexpr bool FULL = decltype(full_c)::value;
+            const int nsub = FULL ? NSUB : min(NSUB, nt - i);        // tiles of this iteration (warp-uniform)
+            uint32_t kbs[NSUB], vbs[NSUB];
 #pragma unroll
             for (int u = 0; u < NSUB; ++u) {
-                S[u][0] = S[u][1] = S[u][2] = S[u][3] = -INFINITY;
-                if (u < nsub) {
+                kbs[u] = vbs[u] = 0;
+                if (FULL || u < nsub) {
                     mbar_wait(bar0 + 8*cs, cph);
-                    const uint32_t sb = smem0 + cs*SM::STAGE, kb = sb + SM::KOFF, vb = sb + SM::VOFF;
-                    vbs[u] = vb;
+                    const uint32_t sb = smem0 + cs*SM::STAGE;
+                    kbs[u] = sb + SM::KOFF; vbs[u] = sb + SM::VOFF;
                     if (++cs == STAGES) { cs = 0; cph ^= 1; }
+                }
+            }
+            if constexpr (!FULL) {
+#pragma unroll
+                for (int u = 0; u < NSUB; ++u) {
                     const int tok0 = (t0 + i + u)*SK_TILE;
-                    if (tok0 + SK_TILE > n_vis) {            // tail tile: cells past n_vis hold stale bytes; 0 * NaN must not reach O
+                    if (u < nsub && tok0 + SK_TILE > n_vis) {     // tail tile: cells past n_vis hold stale bytes; 0 * NaN must not reach O
                         constexpr int VW = sk_type<TV>::WIN;
                         for (int tau = n_vis - tok0; tau < SK_TILE; ++tau) {
-                            if constexpr (TV == B200_TYPE_F16) { if (lane < 16) sts128_zero(vb + ((lane >> 3)*16 + tau)*128 + (lane & 7)*16); }
-                            else                               { if (lane < VW/16) sts128_zero(vb + tau*VW + lane*16); }
+                            if constexpr (TV == B200_TYPE_F16) { if (lane < 16) sts128_zero(vbs[u] + ((lane >> 3)*16 + tau)*128 + (lane & 7)*16); }
+                            else                               { if (lane < VW/16) sts128_zero(vbs[u] + tau*VW + lane*16); }
                         }
-                        __syncwarp();
                     }
-                    float A[4] = {0.f, 0.f, 0.f, 0.f};
-                    if constexpr (TK == B200_TYPE_F16) sk_qk_f16(A, kb, qf, lane);
-                    else                               sk_qk_quant<TK>(A, kb, kmis, qf, kcon, lane);
-                    if (p.logit_softcap != 0.0f) {
+                }
+                __syncwarp();
+            }
+
+            float S[NSUB][4];
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) A[j] = a.cap_log2e*tanhf(A[j]);
+            for (int u = 0; u < NSUB; ++u) {
+                S[u][0] = S[u][1] = S[u][2] = S[u][3] = FULL ? 0.f : -INFINITY;
+                if (FULL || u < nsub) {
+                    float A[4] = {0.f, 0.f, 0.f, 0.f};
+                    if constexpr (TK == B200_TYPE_F16) sk_qk_f16(A, kbs[u], qf, lane);
+                    else                               sk_qk_quant<TK>(A, kbs[u], kmis, qf, kcon, lane);
+                    if constexpr (!FULL) {
+                        if (p.logit_softcap != 0.0f) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) A[j] = a.cap_log2e*tanhf(A[j]);
+                        }
                     }
                     S[u][0] = A[0]; S[u][1] = A[1]; S[u][2] = A[2]; S[u][3] = A[3];
-                    if (tok0 + SK_TILE > n_vis) {            // warp-uniform: only a row's last tile masks
-                        const int tok = tok0 + g;
+                    if constexpr (!FULL) {
+                        const int tok = (t0 + i + u)*SK_TILE + g;
                         if (tok >= n_vis)     { S[u][0] = -INFINITY; S[u][1] = -INFINITY; }
                         if (tok + 8 >= n_vis) { S[u][2] = -INFINITY; S[u][3] = -INFINITY; }
                     }
@@ -621,7 +635,7 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
             }
 #pragma unroll
             for (int u = 0; u < NSUB; ++u) {
-                if (u < nsub) {
+                if (FULL || u < nsub) {
                     const float p00 = ex2(S[u][0] - n0), p01 = ex2(S[u][1] - n1), p10 = ex2(S[u][2] - n0), p11 = ex2(S[u][3] - n1);
                     l0 += p00 + p10;
                     l1 += p01 + p11;
@@ -631,6 +645,15 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
                     else                               sk_pv_quant<TV>(O, vbs[u], vmis, pt0, pt1, vcon, k64k, lane);
                 }
             }
+        };
+
+        const bool no_cap = p.logit_softcap == 0.0f;
+        for (int i = 0; i < nt; i += NSUB) {
+            __syncwarp();                                    // every lane is done with the slots about to be refilled
+#pragma unroll
+            for (int u = 0; u < NSUB; ++u) { if (issued < nt) { issue(); ++issued; } }
+            if (no_cap && i + NSUB <= nt && (t0 + i + NSUB)*SK_TILE <= n_vis) body(std::true_type{}, i);
+            else                                                              body(std::false_type{}, i);
         }
 
         // ---- segment epilogue
