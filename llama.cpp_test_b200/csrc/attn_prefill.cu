@@ -46,6 +46,12 @@ struct pf_args {
     int    gqa, tok_per_tile;            // tok_per_tile = 128/gqa
     int   *plan;                         // [0] n_tiles, [1] work counter, [2..] tile_row0[n_q], then tile_rows[n_q]
     float  qscale;                       // scale*log2(e)
+    // quantised caches: the sequences' cells are expanded once per call to a dense F16 scratch (sequence s at cells
+    // seq_off[s] .. + pad64(seq_len)), and the tile kernel reads that instead of the paged cache (seq_off == NULL: paged)
+    int    *seq_off;                     // [n_seqs + 1]
+    __half *k16, *v16;                   // [scratch_cells][n_head_kv][128]
+    int64_t scratch_cells;
+    int64_t cap;                         // upper bound applied to every seq_lens entry (block-table capacity, or max_seq_len)
 };
 
 __device__ __forceinline__ uint32_t pf_smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
@@ -184,6 +190,89 @@ pf_plan_kernel(const __grid_constant__ pf_args a) {
     __syncthreads();
     for (int t = threadIdx.x; t < n_tiles; t += 1024) rows[t] = (t + 1 < n_tiles ? row0[t + 1] : p.n_q) - row0[t];
     if (threadIdx.x == 0) { a.plan[0] = n_tiles; a.plan[1] = 0; }
+    if (a.seq_off) {
+        const int64_t cap = a.cap;
+        int carry = 0;
+        for (int s0 = 0; s0 < p.n_seqs; s0 += 1024) {
+            const int sq = s0 + threadIdx.x;
+            int n = 0;
+            if (sq < p.n_seqs) { int64_t l = p.seq_lens[sq]; l = l < 0 ? 0 : (l > cap ? cap : l); n = (int) ((l + PF_BN - 1)/PF_BN*PF_BN); }
+            const int incl = pf_block_scan_incl<false>(n, s_warp);
+            if (sq < p.n_seqs) a.seq_off[sq] = carry + incl - n;
+            __shared__ int s_tot;
+            if (threadIdx.x == 1023) s_tot = incl;
+            __syncthreads();
+            carry += s_tot;
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) a.seq_off[p.n_seqs] = carry;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// quantised caches: expand the sequences' cells to the dense F16 scratch.  One CTA = 16 scratch cells.
+// y = q*d (dequantize_row_q8_0 / dequantize_row_q4_0, ggml/src/ggml-quants.c:349-362, :255-273) rounded to half;
+// cells past seq_len (up to the 64-cell padding) are written as zeros.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pf_dequant_block(int type, const char *row, int blk, __half *out) {
+    uint4 w[4];
+    __half2 *h = reinterpret_cast<__half2 *>(w);
+    if (type == B200_TYPE_F16) {
+        const uint4 *src = reinterpret_cast<const uint4 *>(row + 64*blk);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) w[i] = src[i];
+    } else if (type == B200_TYPE_Q8_0) {
+        const char *b = row + Q8_BYTES*blk;
+        const float d = h2f(ld_u16(b));
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const uint32_t x = ld_u16(b + 2 + 2*i);
+            h[i] = __floats2half2_rn((float) (int8_t) (x & 0xff)*d, (float) (int8_t) (x >> 8)*d);
+        }
+    } else {
+        const char *b = row + Q4_BYTES*blk;
+        const float d = h2f(ld_u16(b));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t x = ld_u16(b + 2 + 2*i);                        // qs[2i], qs[2i+1]
+            h[i]     = __floats2half2_rn((float) ((int) (x & 0xf) - 8)*d,        (float) ((int) ((x >> 8) & 0xf) - 8)*d);
+            h[8 + i] = __floats2half2_rn((float) ((int) ((x >> 4) & 0xf) - 8)*d, (float) ((int) (x >> 12) - 8)*d);
+        }
+    }
+    uint4 *dst = reinterpret_cast<uint4 *>(out);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dst[i] = w[i];
+}
+
+__global__ void __launch_bounds__(256)
+pf_dequant_kernel(const __grid_constant__ pf_args a) {
+    const b200_attn_desc &p = a.d;
+    const int total = a.seq_off[p.n_seqs];
+    for (int64_t c0 = (int64_t) blockIdx.x*16; c0 < total; c0 += (int64_t) gridDim.x*16) {
+        int lo = 0, hi = p.n_seqs;                           // sequence owning scratch cell c0: last s with seq_off[s] <= c0
+        while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (a.seq_off[mid] <= c0) lo = mid; else hi = mid; }
+        const int sq = lo, p0 = (int) (c0 - a.seq_off[sq]);
+        int64_t seq_len = p.seq_lens[sq];
+        seq_len = seq_len < 0 ? 0 : (seq_len > a.cap ? a.cap : seq_len);
+        const int32_t *bt = p.block_table + (int64_t) sq*p.bt_stride;
+        const int units = 16*p.n_head_kv*4;                  // (cell, head, 32-element block)
+        for (int u = threadIdx.x; u < 2*units; u += blockDim.x) {
+            const bool is_v = u >= units;
+            const int uu = is_v ? u - units : u;
+            const int blk = uu & 3, head = (uu >> 2) % p.n_head_kv, i = (uu >> 2)/p.n_head_kv;
+            const int pos = p0 + i;
+            __half *out = (is_v ? a.v16 : a.k16) + ((c0 + i)*p.n_head_kv + head)*PF_D + 32*blk;
+            if (pos < seq_len) {
+                const int64_t cell = (int64_t) bt[pos/p.block_size]*p.block_size + pos % p.block_size;
+                const char *row = static_cast<const char *>(is_v ? p.v : p.k) + cell*(is_v ? p.nbv1 : p.nbk1) + (int64_t) head*(is_v ? p.nbv2 : p.nbk2);
+                pf_dequant_block(is_v ? p.type_v : p.type_k, row, blk, out);
+            } else {
+                uint4 *dst = reinterpret_cast<uint4 *>(out);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) dst[k] = make_uint4(0u, 0u, 0u, 0u);
+            }
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -229,7 +318,8 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
         const int row0 = tile_row0[tile], nrows = tile_rows[tile];
         const int seq = p.q_seq ? p.q_seq[row0] : row0;
         int seq_len = p.seq_lens[seq];
-        { const int64_t cap = (int64_t) n_blk*bs; if (seq_len > cap) seq_len = (int) cap; if (seq_len < 0) seq_len = 0; }
+        if (seq_len > a.cap) seq_len = (int) a.cap;
+        if (seq_len < 0) seq_len = 0;
         const int32_t *bt = p.block_table + (int64_t) seq*p.bt_stride;
 
         // ---- softmax warps: this thread's row, its Q row -> F16 * scale*log2(e) -> shared (UMMA K-major, 128B swizzle)
@@ -265,7 +355,8 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
             // the V stage (after PV), and K runs one tile ahead of V — the order the MMA warp consumes them in.
             // Lane l holds block-table entry win_base + l; the next 32 entries are fetched one window ahead, so the
             // gather never waits on a global load (the whole warp takes part, lane 0 talks to the TMA unit).
-            const int kc0 = (int) ((int64_t) kvh*p.nbk2/2), vc0 = (int) ((int64_t) kvh*p.nbv2/2);   // element coordinate of the head row
+            const int dense_base = a.seq_off ? a.seq_off[seq] : -1;       // F16 scratch of a quantised cache: cells are sequence-local
+            const int kc0 = a.seq_off ? kvh*PF_D : (int) ((int64_t) kvh*p.nbk2/2), vc0 = a.seq_off ? kvh*PF_D : (int) ((int64_t) kvh*p.nbv2/2);
             int win_base = 0;
             int win      = lane < n_blk ? bt[lane] : 0;
             int win_next = 32 + lane < n_blk ? bt[32 + lane] : 0;
@@ -282,6 +373,7 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                         }
                         cell[i] = __shfl_sync(0xffffffffu, win, b_cur - win_base)*bs + o_cur*16;
                         if (++o_cur == tpb) { o_cur = 0; ++b_cur; }
+                        if (dense_base >= 0) cell[i] = dense_base + t*PF_BN + 16*i;
                     }
                     const uint32_t g = G + t, st = g & 1, sk = sKV + st*32768, bk = sBar + 8*(PF_FULLK + st);
                     if (lane == 0) {
@@ -456,21 +548,46 @@ static pf_encode_fn pf_encoder() {
     return fn;
 }
 
+static bool pf_type_ok(int t) { return t == B200_TYPE_F16 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_0; }
+static bool pf_needs_scratch(const b200_attn_desc &d) { return d.type_k != B200_TYPE_F16 || d.type_v != B200_TYPE_F16; }
+
+// cells of the F16 scratch: every sequence padded to a multiple of 64 cells.  Sized from host-known bounds only
+// (total_tokens is a scheduling hint and is not trusted for memory safety).
+static int64_t pf_scratch_cells(const b200_attn_desc &d) {
+    int64_t cap = d.bt_stride*d.block_size;
+    if (d.max_seq_len > 0 && d.max_seq_len < cap) cap = d.max_seq_len;
+    return (int64_t) d.n_seqs*((cap + PF_BN - 1)/PF_BN*PF_BN);
+}
+constexpr int64_t PF_SCRATCH_MAX = 1LL << 30;                // bytes per tensor; beyond that the per-row kernel takes the call
+
 bool prefill_supports(const b200_attn_desc &d) {
     if (!d.block_table || !d.seq_lens || d.head_dim != PF_D || d.max_bias != 0.0f || d.logit_softcap != 0.0f) return false;
-    if (d.type_k != B200_TYPE_F16 || d.type_v != B200_TYPE_F16) return false;
+    if (!pf_type_ok(d.type_k) || !pf_type_ok(d.type_v)) return false;
     const int gqa = d.n_head/d.n_head_kv;
     if (gqa < 1 || gqa > PF_ROWS || PF_ROWS % gqa) return false;
     if (d.block_size % 16 || d.n_kv < 16) return false;                                   // one TMA box = 16 consecutive cells
-    if (((uintptr_t) d.k | (uintptr_t) d.v | (uint64_t) d.nbk1 | (uint64_t) d.nbv1 | (uint64_t) d.nbk2 | (uint64_t) d.nbv2) & 15) return false;
     if (d.nbk1 <= 0 || d.nbv1 <= 0 || d.nbk2 <= 0 || d.nbv2 <= 0) return false;
+    if (((uintptr_t) d.q | (uint64_t) d.nbq1 | (uint64_t) d.nbq2 | (uintptr_t) d.dst) & 15) return false;
+    if (pf_needs_scratch(d)) {
+        if (((uintptr_t) d.k | (uintptr_t) d.v | (uint64_t) d.nbk1 | (uint64_t) d.nbv1 | (uint64_t) d.nbk2 | (uint64_t) d.nbv2) & 1) return false;
+        const int64_t cells = pf_scratch_cells(d);
+        if (cells <= 0 || cells >= (1LL << 31) || cells*d.n_head_kv*PF_D*2 > PF_SCRATCH_MAX) return false;
+        return true;
+    }
+    if (((uintptr_t) d.k | (uintptr_t) d.v | (uint64_t) d.nbk1 | (uint64_t) d.nbv1 | (uint64_t) d.nbk2 | (uint64_t) d.nbv2) & 15) return false;
     if ((int64_t) (d.n_head_kv - 1)*d.nbk2 + 256 > d.nbk1 || (int64_t) (d.n_head_kv - 1)*d.nbv2 + 256 > d.nbv1) return false;
     if (d.n_kv >= (1LL << 31) || d.n_kv*(d.nbk1 > d.nbv1 ? d.nbk1 : d.nbv1) >= (1LL << 40)) return false;
-    if (((uintptr_t) d.q | (uint64_t) d.nbq1 | (uint64_t) d.nbq2 | (uintptr_t) d.dst) & 15) return false;
     return true;
 }
 
-size_t prefill_workspace(const b200_attn_desc &d) { return (2 + 2*(size_t) d.n_q)*sizeof(int) + 256; }
+static size_t pf_align(size_t x) { return (x + 1023) & ~(size_t) 1023; }
+static size_t pf_plan_bytes(const b200_attn_desc &d) { return pf_align((2 + 2*(size_t) d.n_q + (size_t) d.n_seqs + 1)*sizeof(int)); }
+
+size_t prefill_workspace(const b200_attn_desc &d) {
+    size_t n = pf_plan_bytes(d);
+    if (pf_needs_scratch(d)) n += 2*pf_align((size_t) pf_scratch_cells(d)*d.n_head_kv*PF_D*2);
+    return n;
+}
 
 static bool pf_make_map(CUtensorMap *tm, const void *base, int64_t nb1, int64_t nb2, int n_head_kv, int64_t n_cells) {
     pf_encode_fn enc = pf_encoder();
@@ -504,9 +621,26 @@ int launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st) {
     a.tok_per_tile = PF_ROWS/a.gqa;
     a.plan = reinterpret_cast<int *>(d.workspace);
     a.qscale = d.scale*1.4426950408889634f;
+    const bool scratch = pf_needs_scratch(d);
+    a.cap = d.bt_stride*d.block_size;
+    if (scratch && d.max_seq_len > 0 && d.max_seq_len < a.cap) a.cap = d.max_seq_len;
+    a.seq_off = nullptr; a.k16 = a.v16 = nullptr; a.scratch_cells = 0;
+    if (scratch) {
+        char *ws = static_cast<char *>(d.workspace);
+        a.seq_off = a.plan + 2 + 2*(size_t) d.n_q;
+        a.scratch_cells = pf_scratch_cells(d);
+        const size_t tb = pf_align((size_t) a.scratch_cells*d.n_head_kv*PF_D*2);
+        a.k16 = reinterpret_cast<__half *>(ws + pf_plan_bytes(d));
+        a.v16 = reinterpret_cast<__half *>(ws + pf_plan_bytes(d) + tb);
+    }
     alignas(64) CUtensorMap tmK, tmV;
-    if (!pf_make_map(&tmK, d.k, d.nbk1, d.nbk2, d.n_head_kv, d.n_kv)) return B200_ERR_CUDA;
-    if (!pf_make_map(&tmV, d.v, d.nbv1, d.nbv2, d.n_head_kv, d.n_kv)) return B200_ERR_CUDA;
+    if (scratch) {
+        if (!pf_make_map(&tmK, a.k16, (int64_t) d.n_head_kv*256, 256, d.n_head_kv, a.scratch_cells)) return B200_ERR_CUDA;
+        if (!pf_make_map(&tmV, a.v16, (int64_t) d.n_head_kv*256, 256, d.n_head_kv, a.scratch_cells)) return B200_ERR_CUDA;
+    } else {
+        if (!pf_make_map(&tmK, d.k, d.nbk1, d.nbk2, d.n_head_kv, d.n_kv)) return B200_ERR_CUDA;
+        if (!pf_make_map(&tmV, d.v, d.nbv1, d.nbv2, d.n_head_kv, d.n_kv)) return B200_ERR_CUDA;
+    }
 
     pf_plan_kernel<<<1, 1024, 0, st>>>(a);
     count_launch();
@@ -515,6 +649,14 @@ int launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st) {
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (sms <= 0) sms = 148;
+    if (scratch) {
+        int64_t g = a.scratch_cells/16;
+        if (g > 8*sms) g = 8*sms;
+        if (g < 1) g = 1;
+        pf_dequant_kernel<<<(unsigned) g, 256, 0, st>>>(a);
+        count_launch();
+        if (!check_launch("pf_dequant")) return B200_ERR_CUDA;
+    }
     int64_t grid = (int64_t) d.n_q*d.n_head_kv;              // upper bound on work items (one row per tile)
     if (grid > 2*sms) grid = 2*sms;
     pf_main_kernel<<<(unsigned) grid, PF_THREADS, PF_SMEM, st>>>(a, tmK, tmV);

@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 
 from test_gpu_parity import TOL, _run_paged
-from workloads import F16, make_workload, oracle_attention
+from workloads import F16, Q4_0, Q8_0, make_workload, oracle_attention
 
 pytestmark = pytest.mark.gpu
 PREFILL = 3
@@ -40,6 +40,21 @@ def test_prefill_tile_kernel(pkg, oracle, cuda, name):
     assert not np.isnan(got).any()
     err, nm = oracle.max_rel_err(want, got), oracle.nmse(want, got)
     assert err <= TOL[F16], f"max rel err {err:.3e} (nmse {nm:.3e})"
+    assert nm <= 5e-4
+
+
+@pytest.mark.parametrize("tk,tv", [(Q8_0, Q8_0), (Q4_0, Q4_0), (Q8_0, F16), (F16, Q4_0)], ids=["q8", "q4", "q8k_f16v", "f16k_q4v"])
+@pytest.mark.parametrize("name", ["two_seqs_ragged", "chunk512_ctx2k", "block32", "gqa8_70b"])
+def test_prefill_quantised_cache(pkg, oracle, cuda, name, tk, tv):
+    """quantised caches: sequences expanded once to the F16 scratch, then the same tile kernel"""
+    import torch
+    seq_lens, n_head, n_head_kv, rows, bs = CASES[name]
+    w = make_workload(oracle, seq_lens, n_head, n_head_kv, 128, tk, tv, seed=32, q_rows=rows, block_size=bs)
+    got = _run_paged(pkg, torch, w, PREFILL)
+    want = oracle_attention(oracle, w)
+    assert not np.isnan(got).any()
+    err, nm = oracle.max_rel_err(want, got), oracle.nmse(want, got)
+    assert err <= max(TOL[tk], TOL[tv]), f"max rel err {err:.3e} (nmse {nm:.3e})"
     assert nm <= 5e-4
 
 
