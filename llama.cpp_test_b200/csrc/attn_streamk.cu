@@ -224,6 +224,7 @@ __device__ __forceinline__ int sk_block_scan(int v, int *s_warp, int *total) {
 __global__ void __launch_bounds__(1024)
 sk_plan_kernel(const __grid_constant__ sk_args a) {
     __shared__ int s_warp[32];
+    pdl_prologue();
     const b200_attn_desc &p = a.d;
     int *P = a.plan + 4, *FS = P + (p.n_q + 1);
     int carry = 0;
@@ -470,6 +471,7 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
     asm volatile("mov.b32 %0, %0;" : "+r"(lane));             // pin in a register: ptxas otherwise re-reads SR_TID in the loop
     const int warp = threadIdx.x >> 5;
     const int g = lane >> 2, t = lane & 3;
+    pdl_prologue();
 
     const int wid  = blockIdx.x*SK_WARPS + warp;
     const int item = wid / p.n_head_kv, kvh = wid - item*p.n_head_kv;
@@ -687,6 +689,7 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
 __global__ void __launch_bounds__(128)
 sk_combine_kernel(const __grid_constant__ sk_args a) {
     const b200_attn_desc &p = a.d;
+    pdl_prologue();
     const int lane = threadIdx.x & 31;
     const int64_t idx = (int64_t) blockIdx.x*4 + (threadIdx.x >> 5);
     if (idx >= (int64_t) p.n_q*p.n_head) return;
@@ -819,7 +822,7 @@ static int sk_launch(const sk_args &a, const CUtensorMap &tmK, const CUtensorMap
     }
     const int64_t warps = (int64_t) a.n_items*a.d.n_head_kv;
     const unsigned grid = (unsigned) ((warps + SK_WARPS - 1)/SK_WARPS);
-    sk_main_kernel<TK, TV><<<grid, 32*SK_WARPS, SM::CTA, st>>>(a, tmK, tmV);
+    launch_pdl(sk_main_kernel<TK, TV>, dim3(grid), dim3(32*SK_WARPS), SM::CTA, st, a, tmK, tmV);
     return B200_OK;
 }
 
@@ -849,7 +852,7 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st) {
     if (!sk_make_map(&tmK, d.type_k, d.k, d.nbk1, d.nbk2, d.n_head_kv, d.n_kv)) return B200_ERR_CUDA;
     if (!sk_make_map(&tmV, d.type_v, d.v, d.nbv1, d.nbv2, d.n_head_kv, d.n_kv)) return B200_ERR_CUDA;
 
-    sk_plan_kernel<<<1, 1024, 0, st>>>(a);
+    launch_pdl(sk_plan_kernel, dim3(1), dim3(1024), 0, st, a);
     count_launch();
     if (!check_launch("sk_plan")) return B200_ERR_CUDA;
     const int rc = sk_dispatch(d.type_k, d.type_v, [&](auto k, auto v) { return sk_launch<decltype(k)::value, decltype(v)::value>(a, tmK, tmV, st); });
@@ -857,7 +860,7 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st) {
     count_launch();
     if (!check_launch("sk_main")) return B200_ERR_CUDA;
     const int64_t pairs = (int64_t) d.n_q*d.n_head;
-    sk_combine_kernel<<<(unsigned) ((pairs + 3)/4), 128, 0, st>>>(a);
+    launch_pdl(sk_combine_kernel, dim3((unsigned) ((pairs + 3)/4)), dim3(128), 0, st, a);
     count_launch();
     if (!check_launch("sk_combine")) return B200_ERR_CUDA;
     return B200_OK;

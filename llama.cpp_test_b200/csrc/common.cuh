@@ -4,6 +4,7 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <utility>
 
 #include "b200_paged_attn.h"
 
@@ -76,6 +77,28 @@ __device__ __forceinline__ void load_row_elems(const char *row, int e0, float (&
             out[2*i+1] = (float) ((int) ((w >> (8 + sh)) & 0xf) - 8) * d;
         }
     }
+}
+
+// Programmatic dependent launch: every kernel of the decode chain (kv_write -> plan -> main -> combine -> next layer's
+// kv_write ...) lets its successor be scheduled at once (launch_dependents) and waits for its predecessor's memory
+// before touching global memory (wait), so launch latency and CTA ramp-up hide under the predecessor's tail instead of
+// adding ~1-2 us per kernel boundary to a 20 us layer-op (config 1).  Without the launch attribute both are no-ops.
+__device__ __forceinline__ void pdl_prologue() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+bool pdl_enabled();                       // shim.cu: false when B200_NO_PDL=1
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args &&...args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(std::forward<Args>(args))...);
 }
 
 // process-wide bookkeeping (defined in shim.cu)

@@ -130,6 +130,7 @@ __device__ void write_row(const float *src, char *cache, int64_t cell, int n_hea
 __global__ void __launch_bounds__(KVW_THREADS)
 kv_write_kernel(const b200_kv_write_desc p) {
     extern __shared__ __align__(16) char stage[];
+    pdl_prologue();
     const int64_t t = blockIdx.x;
     const int64_t cell = p.slot_mapping ? (int64_t) p.slot_mapping[t] : t;
     if (cell < 0 || cell >= p.n_cells) return;                       // writeToCache skips invalid slots
@@ -155,7 +156,7 @@ int launch_kv_write(const b200_kv_write_desc &d, cudaStream_t stream) {
     const size_t smem = (size_t) (sk > sv ? sk : sv);
     if (smem > 48*1024) { set_error("kv_write: token row of %lld bytes exceeds 48 KiB staging", (long long) smem); return B200_ERR_UNSUPPORTED; }
     const dim3 grid((unsigned) d.n_tokens, 2);
-    kv_write_kernel<<<grid, KVW_THREADS, smem, stream>>>(d);
+    launch_pdl(kv_write_kernel, grid, dim3(KVW_THREADS), smem, stream, d);
     count_launch();
     return check_launch("kv_write") ? B200_OK : B200_ERR_CUDA;
 }

@@ -6,6 +6,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 
 namespace b200 {
 
@@ -16,6 +17,11 @@ void set_error(const char *fmt, ...) {
     va_list ap; va_start(ap, fmt);
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
+}
+bool pdl_enabled() {
+    static int on = -1;
+    if (on < 0) { const char *e = getenv("B200_NO_PDL"); on = (e && e[0] == '1') ? 0 : 1; }
+    return on == 1;
 }
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 bool check_launch(const char *what) {

@@ -10,6 +10,9 @@ python -c "import __graft_entry__ as g; g.smoke()" > $O/${TAG}_smoke.log 2>&1; t
 for T in q8_0 f16 q4_0; do
   python bench.py --kv-type $T > $O/${TAG}_bench_$T.log 2>&1; tail -c 600 $O/${TAG}_bench_$T.log; echo
 done
+for WL in config1 config3 config4; do
+  python bench.py --workload $WL --no-cpu-baseline > $O/${TAG}_bench_$WL.log 2>&1; tail -c 400 $O/${TAG}_bench_$WL.log; echo
+done
 python bench.py --impl reference --steps 3 --warmup 1 > $O/${TAG}_bench_reference.log 2>&1; tail -c 400 $O/${TAG}_bench_reference.log; echo
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches.csv \
     python bench.py --layers 4 --steps 2 --warmup 3 --no-graph --no-cpu-baseline > $O/${TAG}_ncu_list.log 2>&1
@@ -17,4 +20,8 @@ for T in q8_0 q4_0 f16; do
   ncu --set full --clock-control none --import-source on -k regex:sk_main -s 4 -c 1 -o $O/${TAG}_sk_$T -f \
     python bench.py --kv-type $T --layers 2 --steps 2 --warmup 3 --no-graph --no-cpu-baseline > $O/${TAG}_ncu_$T.log 2>&1
 done
+ncu --set full --clock-control none --import-source on -k regex:pf_main -s 2 -c 1 -o $O/${TAG}_pf -f \
+    python bench.py --workload config3 --layers 2 --steps 2 --no-graph > $O/${TAG}_ncu_pf.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $O/${TAG}_launches_config3.csv \
+    python bench.py --workload config3 --layers 2 --steps 2 --no-graph > $O/${TAG}_ncu_list3.log 2>&1
 ls -la $O | tail -15

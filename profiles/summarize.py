@@ -32,5 +32,25 @@ def main(path):
                 print(f"{k} = {r[i]} {units[i]}")
 
 
+def traffic(path):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the (single) profiled launch, in bytes"""
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = [r for r in csv.reader(out.splitlines()) if r]
+    start = next(i for i, r in enumerate(rows) if r and r[0] == "ID")
+    hdr, units, r = rows[start], rows[start + 1], rows[start + 2]
+    mul = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    tot = 0.0
+    for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+        i = hdr.index(k)
+        tot += float(r[i]) * mul[units[i]]
+    return int(tot)
+
+
 if __name__ == "__main__":
-    main(sys.argv[1])
+    if sys.argv[1] == "--traffic":            # summarize.py --traffic out.json q8_0=a.ncu-rep q4_0=b.ncu-rep ...
+        import json
+        res = {kv.split("=")[0]: traffic(kv.split("=")[1]) for kv in sys.argv[3:]}
+        json.dump(res, open(sys.argv[2], "w"), indent=1)
+        print(res)
+    else:
+        main(sys.argv[1])
