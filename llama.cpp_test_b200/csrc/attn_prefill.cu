@@ -21,7 +21,8 @@
 //              S is double-buffered in TMEM so QK^T of tile j+1 runs under the softmax of tile j
 //   warp 5     one thread gathers K/V through the block table with TMA: one box = 16 cells x 64 halves of one head
 //              (128-byte swizzle), 16 boxes per 64-token stage
-// TMEM: 256 columns per CTA (S0 64, S1 64, O 128).  Shared: Q 32 KB + 2 x (K 16 + V 16) + P 16 = 112 KB.
+// TMEM: 256 columns per CTA (S0 64, S1 64, O 128; P overwrites the first 32 columns of its S buffer as packed F16 and
+// is the A operand of PV straight from TMEM).  Shared: Q 32 KB + K 3 x 16 KB + V 2 x 16 KB = 112 KB.
 #include "common.cuh"
 #include <cuda.h>
 #include <math.h>
@@ -34,12 +35,13 @@ constexpr int PF_BN      = 64;           // kv tokens per tile
 constexpr int PF_D       = 128;
 constexpr int PF_THREADS = 192;
 constexpr int PF_SQ      = 0;            // [2 d-halves][128 rows][128 B]
-constexpr int PF_SKV     = 32768;        // stage s at + s*32768: K [2][64][128 B] then V [2][64][128 B]
-constexpr int PF_SP      = 98304;        // [128 rows][128 B]
+constexpr int PF_KST     = 3;            // K ring stages (a K stage is free once QK^T of its tile retired)
+constexpr int PF_SK      = 32768;        // K stage s at + s*16384: [2 d-halves][64 tokens][128 B]
+constexpr int PF_SV      = 81920;        // V stage s (2 stages) at + s*16384, same layout
 constexpr int PF_SBAR    = 114688;
-constexpr int PF_SMEM    = PF_SBAR + 128;
+constexpr int PF_SMEM    = PF_SBAR + 160;
 
-enum { PF_FULLK = 0, PF_FULLV = 2, PF_EMPTYK = 4, PF_EMPTYV = 6, PF_SFULL = 8, PF_PFULL = 10, PF_ODONE = 11, PF_NBAR = 12 };
+enum { PF_FULLK = 0, PF_FULLV = 3, PF_EMPTYK = 5, PF_EMPTYV = 8, PF_SFULL = 10, PF_PFULL = 12, PF_ODONE = 13, PF_NBAR = 14 };
 
 struct pf_args {
     b200_attn_desc d;
@@ -100,6 +102,11 @@ __device__ __forceinline__ void pf_mma(uint32_t d_tmem, uint64_t a_desc, uint64_
     asm volatile("{\n .reg .pred p, e;\n elect.sync _|e, 0xffffffff;\n setp.ne.b32 p, %4, 0;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
                  :: "r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// A operand from TMEM (P: lane = row, 2 halves per 32-bit column, 8 columns per K16 step)
+__device__ __forceinline__ void pf_mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n .reg .pred p, e;\n elect.sync _|e, 0xffffffff;\n setp.ne.b32 p, %4, 0;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n}"
+                 :: "r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
 __device__ __forceinline__ void pf_commit(uint32_t bar) {
     asm volatile("{\n .reg .pred e;\n elect.sync _|e, 0xffffffff;\n @e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n}" :: "r"(bar) : "memory");
 }
@@ -123,6 +130,9 @@ __device__ __forceinline__ void pf_tmem_ld32(uint32_t taddr, uint32_t (&v)[64], 
 __device__ __forceinline__ void pf_tmem_st32(uint32_t taddr, const uint32_t (&v)[64], int o) {
     if (o == 0) asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], " PF_LIST32S ";" :: "r"(taddr), PF_W32(v, 0)  : "memory");
     else        asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], " PF_LIST32S ";" :: "r"(taddr), PF_W32(v, 32) : "memory");
+}
+__device__ __forceinline__ void pf_tmem_st32p(uint32_t taddr, const uint32_t (&v)[32]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], " PF_LIST32S ";" :: "r"(taddr), PF_W32(v, 0) : "memory");
 }
 __device__ __forceinline__ void pf_tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void pf_tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
@@ -283,10 +293,10 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
     extern __shared__ __align__(1024) char pf_dyn[];
     const b200_attn_desc &p = a.d;
     const uint32_t sbase = pf_smem_u32(pf_dyn);
-    const uint32_t sQ = sbase + PF_SQ, sKV = sbase + PF_SKV, sP = sbase + PF_SP, sBar = sbase + PF_SBAR;
-    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(pf_dyn + PF_SBAR + 96);
-    volatile int      *work_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 100);
-    volatile int      *nvis_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 104);   // [4] per-warp max n_vis
+    const uint32_t sQ = sbase + PF_SQ, sK = sbase + PF_SK, sV = sbase + PF_SV, sBar = sbase + PF_SBAR;
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(pf_dyn + PF_SBAR + 112);
+    volatile int      *work_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 116);
+    volatile int      *nvis_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 120);   // [4] per-warp max n_vis
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
@@ -294,7 +304,7 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 4) {                                         // 256 TMEM columns: S0 | S1 | O
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" :: "r"(sBar + 96) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" :: "r"(sBar + 112) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     pf_tc_fence_before();
@@ -375,9 +385,9 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                         if (++o_cur == tpb) { o_cur = 0; ++b_cur; }
                         if (dense_base >= 0) cell[i] = dense_base + t*PF_BN + 16*i;
                     }
-                    const uint32_t g = G + t, st = g & 1, sk = sKV + st*32768, bk = sBar + 8*(PF_FULLK + st);
+                    const uint32_t g = G + t, st = g % PF_KST, sk = sK + st*16384, bk = sBar + 8*(PF_FULLK + st);
                     if (lane == 0) {
-                        pf_mbar_wait(sBar + 8*(PF_EMPTYK + st), ((g >> 1) & 1) ^ 1);
+                        pf_mbar_wait(sBar + 8*(PF_EMPTYK + st), ((g / PF_KST) & 1) ^ 1);
                         pf_mbar_expect_tx(bk, 16384);
                     }
                     __syncwarp();
@@ -385,7 +395,7 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                     for (int i = 0; i < 4; ++i) pf_tma_pair_elect(sk + 2048*i, &tmK, kc0, cell[i], bk);
                 }
                 if (t > 0) {
-                    const uint32_t g = G + t - 1, st = g & 1, sv = sKV + st*32768 + 16384, bv = sBar + 8*(PF_FULLV + st);
+                    const uint32_t g = G + t - 1, st = g & 1, sv = sV + st*16384, bv = sBar + 8*(PF_FULLV + st);
                     if (lane == 0) {
                         pf_mbar_wait(sBar + 8*(PF_EMPTYV + st), ((g >> 1) & 1) ^ 1);
                         pf_mbar_expect_tx(bv, 16384);
@@ -401,8 +411,8 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
             // ================= MMA issuer =================  (whole warp converged; one elected lane issues)
             constexpr uint32_t ID_QK = pf_idesc(PF_ROWS, PF_BN, 0), ID_PV = pf_idesc(PF_ROWS, PF_D, 1);
             auto issue_qk = [&](uint32_t g) {
-                const uint32_t st = g & 1, sk = sKV + st*32768;
-                pf_mbar_wait(sBar + 8*(PF_FULLK + st), (g >> 1) & 1);
+                const uint32_t st = g % PF_KST, sk = sK + st*16384;
+                pf_mbar_wait(sBar + 8*(PF_FULLK + st), (g / PF_KST) & 1);
                 pf_tc_fence_after();
 #pragma unroll
                 for (int ks = 0; ks < 8; ++ks) {
@@ -415,16 +425,15 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
             };
             if (nkt > 0) issue_qk(G);
             for (int j = 0; j < nkt; ++j) {
-                const uint32_t g = G + j, st = g & 1, sv = sKV + st*32768 + 16384;
+                const uint32_t g = G + j, st = g & 1, sv = sV + st*16384;
                 if (j + 1 < nkt) issue_qk(g + 1);
                 pf_mbar_wait(sBar + 8*PF_PFULL, g & 1);
                 pf_mbar_wait(sBar + 8*(PF_FULLV + st), (g >> 1) & 1);
                 pf_tc_fence_after();
 #pragma unroll
                 for (int ks = 0; ks < 4; ++ks) {
-                    const uint64_t da = pf_desc(sP + ks*32, 16, 1024);
                     const uint64_t db = pf_desc(sv + ks*2048, 8192, 1024);      // MN-major: LBO = next 64 d, SBO = next 8 tokens
-                    pf_mma(tO, da, db, ID_PV, (j > 0) || (ks > 0));
+                    pf_mma_ts(tO, tS + (g & 1)*64 + ks*8, db, ID_PV, (j > 0) || (ks > 0));
                 }
                 pf_commit(sBar + 8*(PF_EMPTYV + st));
                 pf_commit(sBar + 8*PF_ODONE);
@@ -464,34 +473,33 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                     pk[c] = pf_pack_h2(p0, p1);
                 }
                 l_run = l_run*alpha + sum;
-                if (j > 0) {                                 // P buffer and O are free once PV of the previous tile retired
+                if (j > 0 && __any_sync(0xffffffffu, grow)) {  // rare: rescale O once PV of the previous tile retired
                     pf_mbar_wait(sBar + 8*PF_ODONE, (g - 1) & 1);
                     pf_tc_fence_after();
-                    if (__any_sync(0xffffffffu, grow)) {
 #pragma unroll
-                        for (int h = 0; h < 2; ++h) {
-                            pf_tmem_ld32(tO + lane_base + 64*h,      v, 0);
-                            pf_tmem_ld32(tO + lane_base + 64*h + 32, v, 32);
-                            pf_tmem_wait_ld();
+                    for (int h = 0; h < 2; ++h) {
+                        pf_tmem_ld32(tO + lane_base + 64*h,      v, 0);
+                        pf_tmem_ld32(tO + lane_base + 64*h + 32, v, 32);
+                        pf_tmem_wait_ld();
 #pragma unroll
-                            for (int c = 0; c < 64; ++c) v[c] = __float_as_uint(__uint_as_float(v[c])*alpha);
-                            pf_tmem_st32(tO + lane_base + 64*h,      v, 0);
-                            pf_tmem_st32(tO + lane_base + 64*h + 32, v, 32);
-                        }
-                        pf_tmem_wait_st();
+                        for (int c = 0; c < 64; ++c) v[c] = __float_as_uint(__uint_as_float(v[c])*alpha);
+                        pf_tmem_st32(tO + lane_base + 64*h,      v, 0);
+                        pf_tmem_st32(tO + lane_base + 64*h + 32, v, 32);
                     }
                 }
-#pragma unroll
-                for (int c = 0; c < 8; ++c) pf_sts128(sP + pf_swz(r, c), pk[4*c], pk[4*c + 1], pk[4*c + 2], pk[4*c + 3]);
+                // P (packed F16) over the first 32 columns of this tile's S buffer: S was read into registers above, and
+                // the next QK^T into this buffer is issued after PV of this tile (tcgen05.mma executes in issue order)
+                pf_tmem_st32p(tS + (g & 1)*64 + lane_base, pk);
+                pf_tmem_wait_st();
                 if (tok0 + PF_BN > seq_len) {                // cells past seq_len hold stale bytes: 0 * NaN must not reach O
                     pf_mbar_wait(sBar + 8*(PF_FULLV + st), (g >> 1) & 1);
-                    const uint32_t sv = sKV + st*32768 + 16384;
+                    const uint32_t sv = sV + st*16384;
                     for (int idx = threadIdx.x; idx < 64*16; idx += 128) {
                         const int tok = idx >> 4, c = idx & 15;
                         if (tok0 + tok >= seq_len) pf_sts128(sv + (c >> 3)*8192 + pf_swz(tok, c & 7), 0u, 0u, 0u, 0u);
                     }
+                    pf_fence_async_smem();
                 }
-                pf_fence_async_smem();
                 pf_tc_fence_before();
                 pf_mbar_arrive(sBar + 8*PF_PFULL);
             }
