@@ -7,22 +7,23 @@
 // applied in-kernel, no dense mask is read (the reference fills and reads an [n_kv, n_q] F16 mask,
 // src/llama-graph.cpp:403-477).
 //
-// Work item = (row tile, kv head).  A row tile is up to 128/gqa consecutive query rows of ONE sequence (found on
+// Work item = (row tile, kv head).  A row tile is up to 256/gqa consecutive query rows of ONE sequence (found on
 // the device by pf_plan_kernel from q_seq, so any row order is legal); with the gqa query heads of the kv head
-// that is M = 128 MMA rows, TMEM lane r = token r/gqa, head r%gqa.  K/V of the sequence stream ONCE per work item
+// that is 2 x (M = 128) MMA rows, row R = token R/gqa, head R%gqa, group R/128, TMEM lane R%128.  K/V of the sequence stream ONCE per work item
 // through a 2-stage ring of 64-token tiles (per-row stream-K decode would re-read them once per query row).
 //
-// CTA = 6 warps, 2 CTAs per SM so one CTA's softmax overlaps the other's MMAs:
-//   warps 0-3  softmax: thread r owns accumulator row r (TMEM lane r): tcgen05.ld S -> causal mask -> running max
+// CTA = 10 warps, one CTA per SM, TWO 128-row groups per work item (256 rows = 256/gqa tokens) sharing every K/V tile:
+// K/V cross L2 -> shared memory once per 256 rows, and the tensor pipe works on one group while the other's softmax runs.
+//   warps 0-7  softmax (4 per group): thread r owns accumulator row r of its group (TMEM lane r): tcgen05.ld S -> causal mask -> running max
 //              (lazy: the reference point only moves when the max grows by > 2^8, so O is rarely rescaled) -> exp2
 //              -> P as F16 into shared memory in the UMMA K-major 128B-swizzle layout; final O * 1/l -> dst
-//   warp 4     one thread issues tcgen05.mma: S[128x64] = Q K^T (8 x K16, A and B from shared memory, K-major),
+//   warp 8     one thread issues tcgen05.mma: S[128x64] = Q K^T (8 x K16, A and B from shared memory, K-major),
 //              O[128x128] += P V (4 x K16, V as the MN-major B operand straight from its row-major cache layout);
 //              S is double-buffered in TMEM so QK^T of tile j+1 runs under the softmax of tile j
-//   warp 5     one thread gathers K/V through the block table with TMA: one box = 16 cells x 64 halves of one head
+//   warp 9     one thread gathers K/V through the block table with TMA: one box = 16 cells x 64 halves of one head
 //              (128-byte swizzle), 16 boxes per 64-token stage
-// TMEM: 256 columns per CTA (S0 64, S1 64, O 128; P overwrites the first 32 columns of its S buffer as packed F16 and
-// is the A operand of PV straight from TMEM).  Shared: Q 32 KB + K 3 x 16 KB + V 2 x 16 KB = 112 KB.
+// TMEM: all 512 columns (per group S0 64, S1 64, O 128; P overwrites the first 32 columns of its S buffer as packed F16 and
+// is the A operand of PV straight from TMEM).  Shared: Q 2 x 32 KB + K 4 x 16 KB + V 3 x 16 KB = 176 KB.
 #include "common.cuh"
 #include <cuda.h>
 #include <math.h>
@@ -30,18 +31,20 @@
 
 namespace b200 {
 
-constexpr int PF_ROWS    = 128;          // MMA rows per work item
+constexpr int PF_ROWS    = 128;          // MMA rows per group; a work item is two groups (256 rows)
 constexpr int PF_BN      = 64;           // kv tokens per tile
 constexpr int PF_D       = 128;
-constexpr int PF_THREADS = 192;
+constexpr int PF_THREADS = 320;          // 8 softmax warps (4 per group) + MMA warp + TMA warp
+constexpr int PF_MMA_WARP = 8, PF_TMA_WARP = 9;
 constexpr int PF_SQ      = 0;            // [2 d-halves][128 rows][128 B]
-constexpr int PF_KST     = 3;            // K ring stages (a K stage is free once QK^T of its tile retired)
-constexpr int PF_SK      = 32768;        // K stage s at + s*16384: [2 d-halves][64 tokens][128 B]
-constexpr int PF_SV      = 81920;        // V stage s (2 stages) at + s*16384, same layout
-constexpr int PF_SBAR    = 114688;
-constexpr int PF_SMEM    = PF_SBAR + 160;
+constexpr int PF_KST     = 4, PF_VST = 3; // ring stages (a K stage is free once QK^T of its tile retired, V after PV)
+constexpr int PF_SK      = 65536;        // after Q [2 groups][2 d-halves][128 rows][128 B]; K stage s at + s*16384: [2 d-halves][64 tokens][128 B]
+constexpr int PF_SV      = PF_SK + PF_KST*16384;   // V stage s at + s*16384, same layout
+constexpr int PF_SBAR    = PF_SV + PF_VST*16384;
+constexpr int PF_SMEM    = PF_SBAR + 256;
 
-enum { PF_FULLK = 0, PF_FULLV = 3, PF_EMPTYK = 5, PF_EMPTYV = 8, PF_SFULL = 10, PF_PFULL = 12, PF_ODONE = 13, PF_NBAR = 14 };
+// mbarriers: SFULL[group][S buffer], PFULL[group][P buffer] (128 arrivals; the softmax may be a tile ahead of the MMA warp), ODONE[group]
+enum { PF_FULLK = 0, PF_FULLV = 4, PF_EMPTYK = 7, PF_EMPTYV = 11, PF_SFULL = 14, PF_PFULL = 18, PF_ODONE = 22, PF_NBAR = 24 };
 
 struct pf_args {
     b200_attn_desc d;
@@ -102,6 +105,30 @@ __device__ __forceinline__ void pf_mma(uint32_t d_tmem, uint64_t a_desc, uint64_
     asm volatile("{\n .reg .pred p, e;\n elect.sync _|e, 0xffffffff;\n setp.ne.b32 p, %4, 0;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
                  :: "r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// The 8 K16 steps of one S = Q K^T tile in ONE elected block: the descriptors of step ks are the step-0 descriptors plus
+// constants (32 B per step inside a 64-element swizzle atom, then the second d-half: +16 KB for Q, +8 KB for K), so the
+// issuing warp spends ~25 instructions per tile instead of ~12 per MMA (it was the critical path, profiles/r1o_*).
+__device__ __forceinline__ void pf_qk_block(uint32_t d_tmem, uint64_t a0, uint64_t b0, uint32_t idesc) {
+    asm volatile("{\n .reg .pred e, z;\n .reg .b64 a, b;\n elect.sync _|e, 0xffffffff;\n setp.ne.b32 z, 0, 0;\n"
+                 " @e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, z;\n setp.eq.b32 z, 0, 0;\n"
+                 " add.u64 a, %1, 2;\n add.u64 b, %2, 2;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, z;\n"
+                 " add.u64 a, %1, 4;\n add.u64 b, %2, 4;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, z;\n"
+                 " add.u64 a, %1, 6;\n add.u64 b, %2, 6;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, z;\n"
+                 " add.u64 a, %1, 1024;\n add.u64 b, %2, 512;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, z;\n"
+                 " add.u64 a, %1, 1026;\n add.u64 b, %2, 514;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, z;\n"
+                 " add.u64 a, %1, 1028;\n add.u64 b, %2, 516;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, z;\n"
+                 " add.u64 a, %1, 1030;\n add.u64 b, %2, 518;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, z;\n}"
+                 :: "r"(d_tmem), "l"(a0), "l"(b0), "r"(idesc) : "memory");
+}
+// The 4 K16 steps of one O += P V tile: P from TMEM (8 columns per step), V descriptor + 2 KB (16 tokens) per step
+__device__ __forceinline__ void pf_pv_block(uint32_t d_tmem, uint32_t p_tmem, uint64_t b0, uint32_t idesc, uint32_t acc_first) {
+    asm volatile("{\n .reg .pred e, z;\n .reg .b64 b;\n .reg .b32 t;\n elect.sync _|e, 0xffffffff;\n setp.ne.b32 z, %4, 0;\n"
+                 " @e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, z;\n setp.eq.b32 z, 0, 0;\n"
+                 " add.u32 t, %1, 8;\n add.u64 b, %2, 128;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], [t], b, %3, z;\n"
+                 " add.u32 t, %1, 16;\n add.u64 b, %2, 256;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], [t], b, %3, z;\n"
+                 " add.u32 t, %1, 24;\n add.u64 b, %2, 384;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], [t], b, %3, z;\n}"
+                 :: "r"(d_tmem), "r"(p_tmem), "l"(b0), "r"(idesc), "r"(acc_first) : "memory");
+}
 // A operand from TMEM (P: lane = row, 2 halves per 32-bit column, 8 columns per K16 step)
 __device__ __forceinline__ void pf_mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
     asm volatile("{\n .reg .pred p, e;\n elect.sync _|e, 0xffffffff;\n setp.ne.b32 p, %4, 0;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n}"
@@ -138,6 +165,14 @@ __device__ __forceinline__ void pf_tmem_wait_ld() { asm volatile("tcgen05.wait::
 __device__ __forceinline__ void pf_tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 __device__ __forceinline__ float pf_ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+
+// sm_100 packed-pair F32 add and 3-input max: the softmax warps are bound by instruction issue (2 warps per scheduler,
+// ~300 dependent instructions per kv tile), so halving the subtract / row-sum / row-max instruction counts is what pays
+__device__ __forceinline__ void pf_add2(float &d0, float &d1, float a0, float a1, float b0, float b1) {
+    asm("{\n .reg .b64 a, b, d;\n mov.b64 a, {%2, %3};\n mov.b64 b, {%4, %5};\n add.rn.f32x2 d, a, b;\n mov.b64 {%0, %1}, d;\n}"
+        : "=f"(d0), "=f"(d1) : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
+}
+__device__ __forceinline__ float pf_max3(float a, float b, float c) { float d; asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c)); return d; }
 __device__ __forceinline__ uint32_t pf_pack_h2(float lo, float hi) {
     const __half2 h = __floats2half2_rn(lo, hi);
     return *reinterpret_cast<const uint32_t *>(&h);
@@ -286,37 +321,41 @@ pf_dequant_kernel(const __grid_constant__ pf_args a) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// main kernel
+// main kernel: one CTA per SM, TWO 128-row groups (A = rows 0..127, B = 128..255 of a 256-row work item) share every
+// K/V tile, so K/V cross L2 -> shared memory once per 256 rows, and the tensor pipe works on one group while the
+// other group's softmax warps run (the S/P/O of the groups live in disjoint TMEM columns).
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(PF_THREADS, 2)
+__global__ void __launch_bounds__(PF_THREADS, 1)
 pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV) {
     extern __shared__ __align__(1024) char pf_dyn[];
     const b200_attn_desc &p = a.d;
     const uint32_t sbase = pf_smem_u32(pf_dyn);
     const uint32_t sQ = sbase + PF_SQ, sK = sbase + PF_SK, sV = sbase + PF_SV, sBar = sbase + PF_SBAR;
-    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(pf_dyn + PF_SBAR + 112);
-    volatile int      *work_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 116);
-    volatile int      *nvis_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 120);   // [4] per-warp max n_vis
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(pf_dyn + PF_SBAR + 208);
+    volatile int      *work_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 212);
+    volatile int      *nvis_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 216);   // [8] per-warp max n_vis
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    pdl_prologue();
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < PF_NBAR; ++i) pf_mbar_init(sBar + 8*i, i == PF_PFULL ? 128 : 1);
+        for (int i = 0; i < PF_NBAR; ++i) pf_mbar_init(sBar + 8*i, (i >= PF_PFULL && i < PF_PFULL + 4) ? 128 : 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 4) {                                         // 256 TMEM columns: S0 | S1 | O
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" :: "r"(sBar + 112) : "memory");
+    if (warp == PF_MMA_WARP) {                               // all 512 TMEM columns: per group S0 | S1 | O
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" :: "r"(sBar + 208) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     pf_tc_fence_before();
     __syncthreads();
     pf_tc_fence_after();
     const uint32_t tmem = *tmem_slot;
-    const uint32_t tS = tmem, tO = tmem + 128;
 
     const int gqa = a.gqa, bs = p.block_size;
     const int n_blk = p.bt_stride < INT32_MAX ? (int) p.bt_stride : INT32_MAX;
     const int *tile_row0 = a.plan + 2, *tile_rows = tile_row0 + p.n_q;
-    uint32_t G = 0;                                          // kv tiles processed by this CTA so far (same in every role)
+    const int tokA = PF_ROWS/gqa;                            // tokens of group A (= of group B)
+    uint32_t G = 0;                                          // kv tiles processed by this CTA so far (same in every role): K/V rings
+    uint32_t GB = 0;                                         // ... by work items that used group B: group B's barriers and S buffers
 
     for (;;) {
         if (threadIdx.x == 0) *work_slot = atomicAdd(&a.plan[1], 1);
@@ -326,6 +365,7 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
         if (w >= n_tiles*p.n_head_kv) break;
         const int tile = n_tiles - 1 - w/p.n_head_kv, kvh = w % p.n_head_kv;      // later rows (longer contexts) first
         const int row0 = tile_row0[tile], nrows = tile_rows[tile];
+        const bool useB = nrows > tokA;                      // group B has live rows
         const int seq = p.q_seq ? p.q_seq[row0] : row0;
         int seq_len = p.seq_lens[seq];
         if (seq_len > a.cap) seq_len = (int) a.cap;
@@ -334,37 +374,41 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
 
         // ---- softmax warps: this thread's row, its Q row -> F16 * scale*log2(e) -> shared (UMMA K-major, 128B swizzle)
         int n_vis = 0;
-        const int r = threadIdx.x, tl = r/gqa, hg = r - tl*gqa;
-        if (warp < 4) {
+        const int R = threadIdx.x, grp = (R >> 7) & 1, r = R & 127, tl = R/gqa, hg = R - tl*gqa;
+        if (warp < 8) {
             const bool live = tl < nrows;
             if (live) {
                 n_vis = seq_len;
                 if (p.q_pos) { const int lim = p.q_pos[row0 + tl] + 1; n_vis = lim < n_vis ? lim : n_vis; }
                 if (n_vis < 0) n_vis = 0;
             }
-            const float *qrow = reinterpret_cast<const float *>(static_cast<const char *>(p.q) + (int64_t) (row0 + (live ? tl : 0))*p.nbq1
-                                                                 + (int64_t) (kvh*gqa + hg)*p.nbq2);
+            if (grp == 0 || useB) {
+                const float *qrow = reinterpret_cast<const float *>(static_cast<const char *>(p.q) + (int64_t) (row0 + (live ? tl : 0))*p.nbq1
+                                                                     + (int64_t) (kvh*gqa + hg)*p.nbq2);
 #pragma unroll 4
-            for (int c = 0; c < 16; ++c) {
-                float4 x = make_float4(0.f, 0.f, 0.f, 0.f), y = x;
-                if (live) { x = *reinterpret_cast<const float4 *>(qrow + 8*c); y = *reinterpret_cast<const float4 *>(qrow + 8*c + 4); }
-                pf_sts128(sQ + (c >> 3)*16384 + pf_swz(r, c & 7), pf_pack_h2(x.x*a.qscale, x.y*a.qscale), pf_pack_h2(x.z*a.qscale, x.w*a.qscale),
-                          pf_pack_h2(y.x*a.qscale, y.y*a.qscale), pf_pack_h2(y.z*a.qscale, y.w*a.qscale));
+                for (int c = 0; c < 16; ++c) {
+                    float4 x = make_float4(0.f, 0.f, 0.f, 0.f), y = x;
+                    if (live) { x = *reinterpret_cast<const float4 *>(qrow + 8*c); y = *reinterpret_cast<const float4 *>(qrow + 8*c + 4); }
+                    pf_sts128(sQ + grp*32768 + (c >> 3)*16384 + pf_swz(r, c & 7), pf_pack_h2(x.x*a.qscale, x.y*a.qscale),
+                              pf_pack_h2(x.z*a.qscale, x.w*a.qscale), pf_pack_h2(y.x*a.qscale, y.y*a.qscale), pf_pack_h2(y.z*a.qscale, y.w*a.qscale));
+                }
             }
             const int wmax = __reduce_max_sync(0xffffffffu, n_vis);
             if (lane == 0) nvis_slot[warp] = wmax;
             pf_fence_async_smem();
         }
         __syncthreads();
-        const int nvis_max = max(max(nvis_slot[0], nvis_slot[1]), max(nvis_slot[2], nvis_slot[3]));
+        int nvis_max = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) nvis_max = max(nvis_max, nvis_slot[i]);
         const int nkt = (nvis_max + PF_BN - 1)/PF_BN;
 
-        if (warp == 5) {
+        if (warp == PF_TMA_WARP) {
             // ================= TMA producer =================
-            // K and V have their own 2-stage rings: a K stage is free as soon as QK^T of its tile retired, long before
-            // the V stage (after PV), and K runs one tile ahead of V — the order the MMA warp consumes them in.
-            // Lane l holds block-table entry win_base + l; the next 32 entries are fetched one window ahead, so the
-            // gather never waits on a global load (the whole warp takes part, lane 0 talks to the TMA unit).
+            // K (4 stages) and V (3 stages) have their own rings: a K stage is free as soon as QK^T of its tile retired,
+            // and K runs one tile ahead of V — the order the MMA warp consumes them in.  Lane l holds block-table entry
+            // win_base + l; the next 32 entries are fetched one window ahead, so the gather never waits on a global load
+            // (the whole warp takes part, one elected lane talks to the TMA unit).
             const int dense_base = a.seq_off ? a.seq_off[seq] : -1;       // F16 scratch of a quantised cache: cells are sequence-local
             const int kc0 = a.seq_off ? kvh*PF_D : (int) ((int64_t) kvh*p.nbk2/2), vc0 = a.seq_off ? kvh*PF_D : (int) ((int64_t) kvh*p.nbv2/2);
             int win_base = 0;
@@ -395,9 +439,9 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                     for (int i = 0; i < 4; ++i) pf_tma_pair_elect(sk + 2048*i, &tmK, kc0, cell[i], bk);
                 }
                 if (t > 0) {
-                    const uint32_t g = G + t - 1, st = g & 1, sv = sV + st*16384, bv = sBar + 8*(PF_FULLV + st);
+                    const uint32_t g = G + t - 1, st = g % PF_VST, sv = sV + st*16384, bv = sBar + 8*(PF_FULLV + st);
                     if (lane == 0) {
-                        pf_mbar_wait(sBar + 8*(PF_EMPTYV + st), ((g >> 1) & 1) ^ 1);
+                        pf_mbar_wait(sBar + 8*(PF_EMPTYV + st), ((g / PF_VST) & 1) ^ 1);
                         pf_mbar_expect_tx(bv, 16384);
                     }
                     __syncwarp();
@@ -407,46 +451,55 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
 #pragma unroll
                 for (int i = 0; i < 4; ++i) vcell[i] = cell[i];
             }
-        } else if (warp == 4) {
+        } else if (warp == PF_MMA_WARP) {
             // ================= MMA issuer =================  (whole warp converged; one elected lane issues)
+            // Issue order per kv tile j:  wait P_A(j), PV_A(j) | QK_B(j+1) | wait P_B(j), PV_B(j) | QK_A(j+2): while one
+            // group's softmax works, the tensor pipe runs the other group's MMAs.
             constexpr uint32_t ID_QK = pf_idesc(PF_ROWS, PF_BN, 0), ID_PV = pf_idesc(PF_ROWS, PF_D, 1);
-            auto issue_qk = [&](uint32_t g) {
-                const uint32_t st = g % PF_KST, sk = sK + st*16384;
-                pf_mbar_wait(sBar + 8*(PF_FULLK + st), (g / PF_KST) & 1);
-                pf_tc_fence_after();
-#pragma unroll
-                for (int ks = 0; ks < 8; ++ks) {
-                    const uint64_t da = pf_desc(sQ + (ks >> 2)*16384 + (ks & 3)*32, 16, 1024);
-                    const uint64_t db = pf_desc(sk + (ks >> 2)*8192  + (ks & 3)*32, 16, 1024);
-                    pf_mma(tS + (g & 1)*64, da, db, ID_QK, ks > 0);
-                }
-                pf_commit(sBar + 8*(PF_EMPTYK + st));
-                pf_commit(sBar + 8*(PF_SFULL + (g & 1)));
+            const int ngrp = useB ? 2 : 1;
+            auto issue_qk = [&](int gr, int j) {             // S_gr(j) = Q_gr K(j)^T
+                const uint32_t g = G + j, gg = gr ? GB + j : g, st = g % PF_KST, sk = sK + st*16384;
+                if (gr == 0) { pf_mbar_wait(sBar + 8*(PF_FULLK + st), (g / PF_KST) & 1); pf_tc_fence_after(); }
+                pf_qk_block(tmem + gr*256 + (gg & 1)*64, pf_desc(sQ + gr*32768, 16, 1024), pf_desc(sk, 16, 1024), ID_QK);
+                pf_commit(sBar + 8*(PF_SFULL + 2*gr + (gg & 1)));
+                if (gr == ngrp - 1) pf_commit(sBar + 8*(PF_EMPTYK + st));       // last reader of the K stage
             };
-            if (nkt > 0) issue_qk(G);
-            for (int j = 0; j < nkt; ++j) {
-                const uint32_t g = G + j, st = g & 1, sv = sV + st*16384;
-                if (j + 1 < nkt) issue_qk(g + 1);
-                pf_mbar_wait(sBar + 8*PF_PFULL, g & 1);
-                pf_mbar_wait(sBar + 8*(PF_FULLV + st), (g >> 1) & 1);
+            auto issue_pv = [&](int gr, int j) {             // O_gr += P_gr(j) V(j)
+                const uint32_t g = G + j, gg = gr ? GB + j : g, st = g % PF_VST, sv = sV + st*16384;
+                pf_mbar_wait(sBar + 8*(PF_PFULL + 2*gr + (gg & 1)), (gg >> 1) & 1);   // one barrier per P buffer: softmax may run a tile ahead
+                if (gr == 0) pf_mbar_wait(sBar + 8*(PF_FULLV + st), (g / PF_VST) & 1);
                 pf_tc_fence_after();
-#pragma unroll
-                for (int ks = 0; ks < 4; ++ks) {
-                    const uint64_t db = pf_desc(sv + ks*2048, 8192, 1024);      // MN-major: LBO = next 64 d, SBO = next 8 tokens
-                    pf_mma_ts(tO, tS + (g & 1)*64 + ks*8, db, ID_PV, (j > 0) || (ks > 0));
+                // V as the MN-major B operand: LBO = next 64 d (8 KB), SBO = next 8 tokens (1 KB)
+                pf_pv_block(tmem + gr*256 + 128, tmem + gr*256 + (gg & 1)*64, pf_desc(sv, 8192, 1024), ID_PV, j > 0);
+                pf_commit(sBar + 8*(PF_ODONE + gr));
+                if (gr == ngrp - 1) pf_commit(sBar + 8*(PF_EMPTYV + st));       // last reader of the V stage
+            };
+            // tcgen05.mma is only ordered against an earlier one with the same accumulator and shape, so before S_gr(t)
+            // overwrites the buffer P_gr(t-2) sits in, PV_gr(t-2) must have retired (ODONE).  Group A's QK^T runs two
+            // tiles ahead and group B's one: neither group's next S ever queues behind the other group's softmax, and
+            // every ODONE wait has another group's MMA block in flight behind it.
+            auto wait_pv = [&](int gr, int j) { pf_mbar_wait(sBar + 8*(PF_ODONE + gr), ((gr ? GB : G) + j) & 1); };
+            if (nkt > 0) { issue_qk(0, 0); if (useB) issue_qk(1, 0); }
+            if (nkt > 1) issue_qk(0, 1);
+            for (int j = 0; j < nkt; ++j) {
+                issue_pv(0, j);
+                if (useB) {
+                    if (j + 1 < nkt) { if (j > 0) wait_pv(1, j - 1); issue_qk(1, j + 1); }
+                    issue_pv(1, j);
                 }
-                pf_commit(sBar + 8*(PF_EMPTYV + st));
-                pf_commit(sBar + 8*PF_ODONE);
+                if (j + 2 < nkt) { wait_pv(0, j); issue_qk(0, j + 2); }
             }
-        } else {
-            // ================= softmax =================
-            const uint32_t lane_base = (uint32_t) (32*warp) << 16;
+        } else if (grp == 0 || useB) {
+            // ================= softmax (group grp) =================
+            const uint32_t lane_base = (uint32_t) (32*(warp & 3)) << 16;
+            const uint32_t tS = tmem + grp*256, tO = tS + 128;
             float m_run = -INFINITY, l_run = 0.f;
             int nvis_min = __reduce_min_sync(0xffffffffu, n_vis);
             uint32_t v[64];
+            const uint32_t Gg = grp ? GB : G;                // this group's tile counter (barrier parities, S buffer)
             for (int j = 0; j < nkt; ++j) {
-                const uint32_t g = G + j, st = g & 1;
-                pf_mbar_wait(sBar + 8*(PF_SFULL + (g & 1)), (g >> 1) & 1);
+                const uint32_t g = Gg + j, gkv = G + j;
+                pf_mbar_wait(sBar + 8*(PF_SFULL + 2*grp + (g & 1)), (g >> 1) & 1);
                 pf_tc_fence_after();
                 pf_tmem_ld32(tS + (g & 1)*64 + lane_base,      v, 0);
                 pf_tmem_ld32(tS + (g & 1)*64 + lane_base + 32, v, 32);
@@ -458,23 +511,26 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                     for (int c = 0; c < 64; ++c) { if (tok0 + c >= n_vis) v[c] = 0xff800000u; }
                 }
 #pragma unroll
-                for (int c = 0; c < 64; ++c) mx = fmaxf(mx, __uint_as_float(v[c]));
+                for (int c = 0; c < 64; c += 2) mx = pf_max3(mx, __uint_as_float(v[c]), __uint_as_float(v[c + 1]));
                 // lazy running max: move the reference point only when the max grew by more than 2^8
                 const bool grow = mx > m_run + 8.0f;
                 float alpha = 1.0f;
                 if (grow) { alpha = pf_ex2(m_run - mx); m_run = mx; }         // m_run == -inf: alpha = 0
-                const float msub = m_run == -INFINITY ? 0.0f : m_run;
-                float sum = 0.f;
+                const float nsub = m_run == -INFINITY ? 0.0f : -m_run;
+                float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
                 uint32_t pk[32];
 #pragma unroll
                 for (int c = 0; c < 32; ++c) {
-                    const float p0 = pf_ex2(__uint_as_float(v[2*c]) - msub), p1 = pf_ex2(__uint_as_float(v[2*c + 1]) - msub);
-                    sum += p0 + p1;
+                    float x0, x1;
+                    pf_add2(x0, x1, __uint_as_float(v[2*c]), __uint_as_float(v[2*c + 1]), nsub, nsub);
+                    const float p0 = pf_ex2(x0), p1 = pf_ex2(x1);
+                    if (c & 1) pf_add2(sum2, sum3, sum2, sum3, p0, p1); else pf_add2(sum0, sum1, sum0, sum1, p0, p1);
                     pk[c] = pf_pack_h2(p0, p1);
                 }
-                l_run = l_run*alpha + sum;
+                pf_add2(sum0, sum1, sum0, sum1, sum2, sum3);
+                l_run = l_run*alpha + (sum0 + sum1);
                 if (j > 0 && __any_sync(0xffffffffu, grow)) {  // rare: rescale O once PV of the previous tile retired
-                    pf_mbar_wait(sBar + 8*PF_ODONE, (g - 1) & 1);
+                    pf_mbar_wait(sBar + 8*(PF_ODONE + grp), (g - 1) & 1);
                     pf_tc_fence_after();
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
@@ -492,22 +548,22 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                 pf_tmem_st32p(tS + (g & 1)*64 + lane_base, pk);
                 pf_tmem_wait_st();
                 if (tok0 + PF_BN > seq_len) {                // cells past seq_len hold stale bytes: 0 * NaN must not reach O
-                    pf_mbar_wait(sBar + 8*(PF_FULLV + st), (g >> 1) & 1);
-                    const uint32_t sv = sV + st*16384;
-                    for (int idx = threadIdx.x; idx < 64*16; idx += 128) {
+                    const uint32_t st = gkv % PF_VST, sv = sV + st*16384;
+                    pf_mbar_wait(sBar + 8*(PF_FULLV + st), (gkv / PF_VST) & 1);
+                    for (int idx = r; idx < 64*16; idx += 128) {  // each group clears every stale row itself (idempotent)
                         const int tok = idx >> 4, c = idx & 15;
                         if (tok0 + tok >= seq_len) pf_sts128(sv + (c >> 3)*8192 + pf_swz(tok, c & 7), 0u, 0u, 0u, 0u);
                     }
                     pf_fence_async_smem();
                 }
                 pf_tc_fence_before();
-                pf_mbar_arrive(sBar + 8*PF_PFULL);
+                pf_mbar_arrive(sBar + 8*(PF_PFULL + 2*grp + (g & 1)));
             }
             // ---- epilogue: O / l -> dst[row][head][d]
             const bool live = tl < nrows;
             float *out = static_cast<float *>(p.dst) + ((int64_t) (row0 + (live ? tl : 0))*p.n_head + kvh*gqa + hg)*PF_D;
             if (nkt > 0) {
-                pf_mbar_wait(sBar + 8*PF_ODONE, (G + nkt - 1) & 1);
+                pf_mbar_wait(sBar + 8*(PF_ODONE + grp), (Gg + nkt - 1) & 1);
                 pf_tc_fence_after();
                 const float inv = 1.0f/l_run;
 #pragma unroll
@@ -529,12 +585,13 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
             pf_tc_fence_before();
         }
         G += nkt;
+        if (useB) GB += nkt;
         __syncthreads();                                     // O, Q and the S buffers are free for the next work item
     }
 
     pf_tc_fence_before();
     __syncthreads();
-    if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" :: "r"(tmem) : "memory");
+    if (warp == PF_MMA_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(tmem) : "memory");
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -626,7 +683,7 @@ int launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st) {
     pf_args a;
     a.d = d;
     a.gqa = d.n_head/d.n_head_kv;
-    a.tok_per_tile = PF_ROWS/a.gqa;
+    a.tok_per_tile = 2*PF_ROWS/a.gqa;
     a.plan = reinterpret_cast<int *>(d.workspace);
     a.qscale = d.scale*1.4426950408889634f;
     const bool scratch = pf_needs_scratch(d);
@@ -666,7 +723,7 @@ int launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st) {
         if (!check_launch("pf_dequant")) return B200_ERR_CUDA;
     }
     int64_t grid = (int64_t) d.n_q*d.n_head_kv;              // upper bound on work items (one row per tile)
-    if (grid > 2*sms) grid = 2*sms;
+    if (grid > sms) grid = sms;
     pf_main_kernel<<<(unsigned) grid, PF_THREADS, PF_SMEM, st>>>(a, tmK, tmV);
     count_launch();
     if (!check_launch("pf_main")) return B200_ERR_CUDA;
