@@ -24,6 +24,9 @@
 //              (128-byte swizzle), 16 boxes per 64-token stage
 // TMEM: all 512 columns (per group S0 64, S1 64, O 128; P overwrites the first 32 columns of its S buffer as packed F16 and
 // is the A operand of PV straight from TMEM).  Shared: Q 2 x 32 KB + K 4 x 16 KB + V 3 x 16 KB = 176 KB.
+#ifdef PF_TIMELINE
+#include <cstdio>
+#endif
 #include "common.cuh"
 #include <cuda.h>
 #include <math.h>
@@ -57,7 +60,16 @@ struct pf_args {
     __half *k16, *v16;                   // [scratch_cells][n_head_kv][128]
     int64_t scratch_cells;
     int64_t cap;                         // upper bound applied to every seq_lens entry (block-table capacity, or max_seq_len)
+#ifdef PF_TIMELINE
+    long long *dbg;                      // debug builds only: clock64 stamps of CTA 0's first work item, [3 warps][64 tiles][8]
+#endif
 };
+
+#ifdef PF_TIMELINE
+#define PF_T(w, j, k) do { if (blockIdx.x == 0 && first_item && (threadIdx.x & 31) == 0 && (j) < 64) a.dbg[((w)*64 + (j))*8 + (k)] = clock64(); } while (0)
+#else
+#define PF_T(w, j, k) do { } while (0)
+#endif
 
 __device__ __forceinline__ uint32_t pf_smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
 
@@ -166,13 +178,14 @@ __device__ __forceinline__ void pf_tmem_wait_st() { asm volatile("tcgen05.wait::
 
 __device__ __forceinline__ float pf_ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
-// sm_100 packed-pair F32 add and 3-input max: the softmax warps are bound by instruction issue (2 warps per scheduler,
-// ~300 dependent instructions per kv tile), so halving the subtract / row-sum / row-max instruction counts is what pays
+// sm_100 packed-pair F32 add (FADD2): halves the subtract and row-sum instruction counts of the softmax warps.
+// Measured and NOT used (profiles/r1p_microbench.txt): 3-input max (FMNMX3 issues at the XU rate, 8 cycles per warp),
+// and a polynomial exp2 on the FMA pipe for a share of the columns (every variant was slower: the tile period is set by
+// the tensor pipe, ~1240 of ~1350 cycles, not by the 1024 XU cycles).
 __device__ __forceinline__ void pf_add2(float &d0, float &d1, float a0, float a1, float b0, float b1) {
     asm("{\n .reg .b64 a, b, d;\n mov.b64 a, {%2, %3};\n mov.b64 b, {%4, %5};\n add.rn.f32x2 d, a, b;\n mov.b64 {%0, %1}, d;\n}"
         : "=f"(d0), "=f"(d1) : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
 }
-__device__ __forceinline__ float pf_max3(float a, float b, float c) { float d; asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c)); return d; }
 __device__ __forceinline__ uint32_t pf_pack_h2(float lo, float hi) {
     const __half2 h = __floats2half2_rn(lo, hi);
     return *reinterpret_cast<const uint32_t *>(&h);
@@ -366,6 +379,9 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
         const int tile = n_tiles - 1 - w/p.n_head_kv, kvh = w % p.n_head_kv;      // later rows (longer contexts) first
         const int row0 = tile_row0[tile], nrows = tile_rows[tile];
         const bool useB = nrows > tokA;                      // group B has live rows
+#ifdef PF_TIMELINE
+        const bool first_item = G == 0;
+#endif
         const int seq = p.q_seq ? p.q_seq[row0] : row0;
         int seq_len = p.seq_lens[seq];
         if (seq_len > a.cap) seq_len = (int) a.cap;
@@ -482,12 +498,17 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
             if (nkt > 0) { issue_qk(0, 0); if (useB) issue_qk(1, 0); }
             if (nkt > 1) issue_qk(0, 1);
             for (int j = 0; j < nkt; ++j) {
+                PF_T(2, j, 0);
                 issue_pv(0, j);
+                PF_T(2, j, 1);
                 if (useB) {
-                    if (j + 1 < nkt) { if (j > 0) wait_pv(1, j - 1); issue_qk(1, j + 1); }
+                    if (j + 1 < nkt) { if (j > 0) wait_pv(1, j - 1); PF_T(2, j, 2); issue_qk(1, j + 1); }
+                    PF_T(2, j, 3);
                     issue_pv(1, j);
+                    PF_T(2, j, 4);
                 }
-                if (j + 2 < nkt) { wait_pv(0, j); issue_qk(0, j + 2); }
+                if (j + 2 < nkt) { wait_pv(0, j); PF_T(2, j, 5); issue_qk(0, j + 2); }
+                PF_T(2, j, 6);
             }
         } else if (grp == 0 || useB) {
             // ================= softmax (group grp) =================
@@ -499,24 +520,29 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
             const uint32_t Gg = grp ? GB : G;                // this group's tile counter (barrier parities, S buffer)
             for (int j = 0; j < nkt; ++j) {
                 const uint32_t g = Gg + j, gkv = G + j;
+                PF_T(grp, j, 0);
                 pf_mbar_wait(sBar + 8*(PF_SFULL + 2*grp + (g & 1)), (g >> 1) & 1);
+                PF_T(grp, j, 1);
                 pf_tc_fence_after();
                 pf_tmem_ld32(tS + (g & 1)*64 + lane_base,      v, 0);
                 pf_tmem_ld32(tS + (g & 1)*64 + lane_base + 32, v, 32);
                 pf_tmem_wait_ld();
+                PF_T(grp, j, 2);
                 const int tok0 = j*PF_BN;
-                float mx = -INFINITY;
+                float mx = -INFINITY, mx2 = -INFINITY;
                 if (tok0 + PF_BN > nvis_min) {               // warp-uniform: only tiles that cross some row's limit mask
 #pragma unroll
                     for (int c = 0; c < 64; ++c) { if (tok0 + c >= n_vis) v[c] = 0xff800000u; }
                 }
 #pragma unroll
-                for (int c = 0; c < 64; c += 2) mx = pf_max3(mx, __uint_as_float(v[c]), __uint_as_float(v[c + 1]));
+                for (int c = 0; c < 64; c += 2) { mx = fmaxf(mx, __uint_as_float(v[c])); mx2 = fmaxf(mx2, __uint_as_float(v[c + 1])); }
+                mx = fmaxf(mx, mx2);
                 // lazy running max: move the reference point only when the max grew by more than 2^8
                 const bool grow = mx > m_run + 8.0f;
                 float alpha = 1.0f;
                 if (grow) { alpha = pf_ex2(m_run - mx); m_run = mx; }         // m_run == -inf: alpha = 0
                 const float nsub = m_run == -INFINITY ? 0.0f : -m_run;
+                PF_T(grp, j, 3);
                 float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
                 uint32_t pk[32];
 #pragma unroll
@@ -545,8 +571,10 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                 }
                 // P (packed F16) over the first 32 columns of this tile's S buffer: S was read into registers above, and
                 // the next QK^T into this buffer is issued after PV of this tile (tcgen05.mma executes in issue order)
+                PF_T(grp, j, 4);
                 pf_tmem_st32p(tS + (g & 1)*64 + lane_base, pk);
                 pf_tmem_wait_st();
+                PF_T(grp, j, 5);
                 if (tok0 + PF_BN > seq_len) {                // cells past seq_len hold stale bytes: 0 * NaN must not reach O
                     const uint32_t st = gkv % PF_VST, sv = sV + st*16384;
                     pf_mbar_wait(sBar + 8*(PF_FULLV + st), (gkv / PF_VST) & 1);
@@ -558,6 +586,7 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                 }
                 pf_tc_fence_before();
                 pf_mbar_arrive(sBar + 8*(PF_PFULL + 2*grp + (g & 1)));
+                PF_T(grp, j, 6);
             }
             // ---- epilogue: O / l -> dst[row][head][d]
             const bool live = tl < nrows;
@@ -724,7 +753,28 @@ int launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st) {
     }
     int64_t grid = (int64_t) d.n_q*d.n_head_kv;              // upper bound on work items (one row per tile)
     if (grid > sms) grid = sms;
+#ifdef PF_TIMELINE
+    cudaMalloc(&a.dbg, 3*64*8*sizeof(long long)); cudaMemset(a.dbg, 0, 3*64*8*sizeof(long long));
+#endif
     pf_main_kernel<<<(unsigned) grid, PF_THREADS, PF_SMEM, st>>>(a, tmK, tmV);
+#ifdef PF_TIMELINE
+    {
+        static int dumped = 0;
+        cudaStreamSynchronize(st);
+        if (dumped++ == 3) {
+            static long long h[3*64*8];
+            cudaMemcpy(h, a.dbg, sizeof(h), cudaMemcpyDeviceToHost);
+            long long t0 = h[(2*64 + 0)*8 + 0];
+            for (int w = 0; w < 3; ++w)
+                for (int j = 0; j < 64; ++j) {
+                    fprintf(stderr, "TL w%d j%02d", w, j);
+                    for (int k = 0; k < 7; ++k) fprintf(stderr, " %6lld", h[(w*64 + j)*8 + k] ? h[(w*64 + j)*8 + k] - t0 : -1);
+                    fprintf(stderr, "\n");
+                }
+        }
+        cudaFree(a.dbg);
+    }
+#endif
     count_launch();
     if (!check_launch("pf_main")) return B200_ERR_CUDA;
     return B200_OK;
