@@ -44,6 +44,45 @@ B200_API int32_t b200_pc_ref_count(const b200_paged_cache *pc, int64_t block);
 B200_API int32_t b200_pc_export(const b200_paged_cache *pc, const int32_t *seqs, int64_t n,
                                 int32_t *block_table, int64_t stride, int32_t *seq_lens);   /* 1 ok / 0 stride too small */
 
+/* cell index of every cached position of `seq` in position order; returns the count, -1 for an unknown sequence,
+ * -(count)-1 when cap is too small */
+B200_API int64_t b200_pc_slots_of(const b200_paged_cache *pc, int32_t seq, int32_t *cells, int64_t cap);
+/* block compaction (reference defrag_prepare, src/llama-kv-cache.cpp:711-846, at block granularity): writes up to
+ * min(cap, max_moves) (src_block, dst_block) pairs for b200_block_copy and rewrites the block tables; returns the
+ * number of moves.  max_moves < 0: as many as cap allows. */
+B200_API int64_t b200_pc_defrag(b200_paged_cache *pc, int32_t *moves /* [cap][2] */, int64_t cap, int64_t max_moves);
+
+/*
+ * KV session state of ONE sequence in the reference's stream format (llama_kv_cache_unified::state_write / state_read
+ * with seq_id >= 0 and flash-attention caches, src/llama-kv-cache.cpp:848-1240; users: llama_state_seq_get_data /
+ * llama_state_seq_set_data, examples/save-load-state).  Rows are token-ordered: gather them from the blocks with
+ * b200_kv_rows_gather, restore them with b200_kv_rows_scatter (b200_paged_attn.h).
+ *   k_rows / v_rows  host [n_layer][n_cells][size_row] bytes
+ *   type_k / type_v  ggml_type ids (== B200_TYPE_*), size_row = ggml_row_size(type, n_embd_gqa)
+ */
+enum {
+    B200_STATE_ERR_TRUNCATED    = -1,   /* stream shorter than its own header says */
+    B200_STATE_ERR_SEQ_AGNOSTIC = -2,   /* a cell carries seq ids (whole-cache stream, not a sequence stream)   :1024 */
+    B200_STATE_ERR_POSITIONS    = -3,   /* positions are not 0..n-1 (outside the block-table model)                  */
+    B200_STATE_ERR_LAYERS       = -4,   /* mismatched layer count                                               :1112 */
+    B200_STATE_ERR_VTRANS       = -5,   /* incompatible V transposition                                         :1120 */
+    B200_STATE_ERR_TYPE         = -6,   /* mismatched key / value type                                     :1132,:1160 */
+    B200_STATE_ERR_ROW_SIZE     = -7    /* mismatched key / value row size                                 :1141,:1169 */
+};
+B200_API int64_t b200_kv_state_seq_size(int64_t n_cells, int32_t n_layer, int64_t k_size_row, int64_t v_size_row);
+/* returns bytes written; -(bytes needed) when out is NULL or cap too small; -1 on bad arguments */
+B200_API int64_t b200_kv_state_seq_write(uint8_t *out, int64_t cap, int64_t n_cells, int32_t n_layer,
+                                         int32_t type_k, int64_t k_size_row, int32_t type_v, int64_t v_size_row,
+                                         const uint8_t *k_rows, const uint8_t *v_rows);
+/* validates a stream against the cache's shape; returns 0 or a B200_STATE_ERR_*; k_off/v_off [n_layer] receive the
+ * byte offsets of each layer's rows inside `data` (either may be NULL) */
+B200_API int32_t b200_kv_state_seq_parse(const uint8_t *data, int64_t size, int32_t n_layer,
+                                         int32_t type_k, int64_t k_size_row, int32_t type_v, int64_t v_size_row,
+                                         int64_t *n_cells, int64_t *k_off, int64_t *v_off);
+/* state_read_meta for one sequence: drop `seq`, reserve n_cells tokens, slot_mapping[n_cells] = their cells.
+ * Returns n_cells, or -1 when the pool has no room (the sequence is gone either way, as in the reference). */
+B200_API int64_t b200_pc_restore_seq(b200_paged_cache *pc, int32_t seq, int64_t n_cells, int32_t *slot_mapping);
+
 #ifdef __cplusplus
 }
 #endif

@@ -118,6 +118,21 @@ B200_API int b200_block_copy(void *const *caches, int32_t n_caches, int64_t bloc
                              const int32_t *pairs /* device [n_pairs][2] */, int64_t n_pairs, void *stream);
 
 /*
+ * Token-ordered rows <-> scattered cells, for KV session state on the paged layout.  The reference reads / writes
+ * whole cell ranges of k_l[il] / v_l[il] with ggml_backend_tensor_get / _set (io.write_tensor,
+ * src/llama-kv-cache.cpp:940-946; state_read_data :1147-1150); with blocks the rows of a sequence are scattered, so:
+ *   gather : staging[c][i][0..row_bytes) = caches[c] + slots[i]*nb_token   for every cache c (all layers in one launch)
+ *   scatter: the inverse
+ * caches is a HOST array of device base pointers; slots is a DEVICE int32 [n_rows] (PagedKVCache::slots_of /
+ * b200_pc_restore_seq); staging is DEVICE [n_caches][n_rows][row_bytes].  row_bytes, nb_token, pointers: multiples
+ * of 16.  Rows whose slot is negative or >= n_cells are skipped.
+ */
+B200_API int b200_kv_rows_gather(void *const *caches, int32_t n_caches, int64_t nb_token, int64_t row_bytes, int64_t n_cells,
+                                 const int32_t *slots, int64_t n_rows, void *staging, void *stream);
+B200_API int b200_kv_rows_scatter(void *const *caches, int32_t n_caches, int64_t nb_token, int64_t row_bytes, int64_t n_cells,
+                                  const int32_t *slots, int64_t n_rows, const void *staging, void *stream);
+
+/*
  * One decode/prefill step over several layers in ONE call: for l in [0, n_layers): b200_kv_write(&writes[l]) (skipped
  * when writes == NULL) then b200_paged_attention(&attns[l]), all on `stream`.  This is the loop
  * llama_context::decode runs through ggml_backend_sched for the attention part of every layer

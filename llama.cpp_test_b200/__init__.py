@@ -85,12 +85,14 @@ GGML_OP_CPY, GGML_OP_FLASH_ATTN_EXT, GGML_TYPE_I32 = 32, 62, 26
 EXPORTS = {
     "b200_paged_attn.h": [
         "b200_paged_attention_workspace", "b200_paged_attention", "b200_supports_attention", "b200_kv_write",
-        "b200_block_copy", "b200_decode_step", "b200_last_error", "b200_version", "b200_device_sm_count", "b200_launch_count"],
+        "b200_block_copy", "b200_kv_rows_gather", "b200_kv_rows_scatter", "b200_decode_step", "b200_last_error", "b200_version", "b200_device_sm_count", "b200_launch_count"],
     "b200_ggml_abi.h": ["b200_flash_attn_ext_workspace", "b200_flash_attn_ext", "b200_cpy", "b200_supports_op"],
     "b200_host.h": [
         "b200_bm_create", "b200_bm_destroy", "b200_bm_allocate", "b200_bm_free", "b200_bm_evict", "b200_bm_status",
         "b200_fork_trace", "b200_pc_create", "b200_pc_destroy", "b200_pc_append", "b200_pc_seq_cp", "b200_pc_seq_rm",
-        "b200_pc_seq_keep", "b200_pc_clear", "b200_pc_seq_len", "b200_pc_n_free", "b200_pc_ref_count", "b200_pc_export"],
+        "b200_pc_seq_keep", "b200_pc_clear", "b200_pc_seq_len", "b200_pc_n_free", "b200_pc_ref_count", "b200_pc_export",
+        "b200_pc_slots_of", "b200_pc_defrag", "b200_pc_restore_seq", "b200_kv_state_seq_size", "b200_kv_state_seq_write",
+        "b200_kv_state_seq_parse"],
 }
 
 lib.b200_paged_attention_workspace.restype = C.c_size_t
@@ -103,6 +105,10 @@ lib.b200_kv_write.restype = C.c_int
 lib.b200_kv_write.argtypes = [C.POINTER(KVWriteDesc), C.c_void_p]
 lib.b200_block_copy.restype = C.c_int
 lib.b200_block_copy.argtypes = [C.POINTER(C.c_void_p), C.c_int32, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]
+lib.b200_kv_rows_gather.restype = C.c_int
+lib.b200_kv_rows_gather.argtypes = [C.POINTER(C.c_void_p), C.c_int32, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+lib.b200_kv_rows_scatter.restype = C.c_int
+lib.b200_kv_rows_scatter.argtypes = lib.b200_kv_rows_gather.argtypes
 lib.b200_decode_step.restype = C.c_int
 lib.b200_decode_step.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]
 lib.b200_last_error.restype = C.c_char_p
@@ -148,6 +154,23 @@ lib.b200_pc_ref_count.restype = C.c_int32
 lib.b200_pc_ref_count.argtypes = [C.c_void_p, C.c_int64]
 lib.b200_pc_export.restype = C.c_int32
 lib.b200_pc_export.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_int64, C.POINTER(C.c_int32), C.c_int64, C.POINTER(C.c_int32)]
+lib.b200_pc_slots_of.restype = C.c_int64
+lib.b200_pc_slots_of.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.c_int64]
+lib.b200_pc_defrag.restype = C.c_int64
+lib.b200_pc_defrag.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_int64, C.c_int64]
+lib.b200_pc_restore_seq.restype = C.c_int64
+lib.b200_pc_restore_seq.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.POINTER(C.c_int32)]
+lib.b200_kv_state_seq_size.restype = C.c_int64
+lib.b200_kv_state_seq_size.argtypes = [C.c_int64, C.c_int32, C.c_int64, C.c_int64]
+lib.b200_kv_state_seq_write.restype = C.c_int64
+lib.b200_kv_state_seq_write.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_int64,
+                                        C.c_void_p, C.c_void_p]
+lib.b200_kv_state_seq_parse.restype = C.c_int32
+lib.b200_kv_state_seq_parse.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_int64,
+                                        C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+STATE_ERRORS = {-1: "truncated stream", -2: "invalid seq_id-agnostic kv cell", -3: "positions are not 0..n-1",
+                -4: "mismatched layer count", -5: "incompatible V transposition", -6: "mismatched key/value type",
+                -7: "mismatched key/value row size"}
 
 
 class B200Error(RuntimeError):

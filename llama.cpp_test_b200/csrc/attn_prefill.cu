@@ -9,21 +9,22 @@
 //
 // Work item = (row tile, kv head).  A row tile is up to 256/gqa consecutive query rows of ONE sequence (found on
 // the device by pf_plan_kernel from q_seq, so any row order is legal); with the gqa query heads of the kv head
-// that is 2 x (M = 128) MMA rows, row R = token R/gqa, head R%gqa, group R/128, TMEM lane R%128.  K/V of the sequence stream ONCE per work item
-// through a 2-stage ring of 64-token tiles (per-row stream-K decode would re-read them once per query row).
+// that is 2 x (M = 128) MMA rows: row R = token R/gqa, head R%gqa, group R/128, TMEM lane R%128.  K/V of the
+// sequence stream ONCE per work item in 64-token tiles (per-row stream-K would re-read them once per query row).
 //
-// CTA = 10 warps, one CTA per SM, TWO 128-row groups per work item (256 rows = 256/gqa tokens) sharing every K/V tile:
-// K/V cross L2 -> shared memory once per 256 rows, and the tensor pipe works on one group while the other's softmax runs.
-//   warps 0-7  softmax (4 per group): thread r owns accumulator row r of its group (TMEM lane r): tcgen05.ld S -> causal mask -> running max
-//              (lazy: the reference point only moves when the max grows by > 2^8, so O is rarely rescaled) -> exp2
-//              -> P as F16 into shared memory in the UMMA K-major 128B-swizzle layout; final O * 1/l -> dst
-//   warp 8     one thread issues tcgen05.mma: S[128x64] = Q K^T (8 x K16, A and B from shared memory, K-major),
-//              O[128x128] += P V (4 x K16, V as the MN-major B operand straight from its row-major cache layout);
-//              S is double-buffered in TMEM so QK^T of tile j+1 runs under the softmax of tile j
-//   warp 9     one thread gathers K/V through the block table with TMA: one box = 16 cells x 64 halves of one head
-//              (128-byte swizzle), 16 boxes per 64-token stage
-// TMEM: all 512 columns (per group S0 64, S1 64, O 128; P overwrites the first 32 columns of its S buffer as packed F16 and
-// is the A operand of PV straight from TMEM).  Shared: Q 2 x 32 KB + K 4 x 16 KB + V 3 x 16 KB = 176 KB.
+// CTA = 10 warps, one CTA per SM; the two 128-row groups share every K/V tile, so K/V cross L2 -> shared memory
+// once per 256 rows and the tensor pipe works on one group while the other's softmax runs.
+//   warps 0-7  softmax (4 per group): thread r owns accumulator row r of its group (TMEM lane r): tcgen05.ld S ->
+//              causal mask -> running max (lazy: the reference point only moves when the max grows by > 2^8, so O
+//              is rarely rescaled) -> exp2 -> P as packed F16 over the first 32 columns of its S buffer
+//              (tcgen05.st); final O * 1/l -> dst
+//   warp 8     issues tcgen05.mma: S[128x64] = Q K^T (8 x K16, A and B from shared memory, K-major),
+//              O[128x128] += P V (4 x K16, P from TMEM, V as the MN-major B operand straight from its row-major
+//              cache layout); S is double-buffered per group; order per kv tile: PV_A(j) QK_B(j+1) PV_B(j) QK_A(j+2)
+//   warp 9     gathers K/V through the block table with TMA: one box = 16 cells x 64 halves of one head
+//              (128-byte swizzle), 8 boxes per 64-token stage; K ring 4 stages, V ring 3
+// TMEM: all 512 columns (per group S0 64, S1 64, O 128).  Shared: Q 2 x 32 KB + K 4 x 16 KB + V 3 x 16 KB = 176 KB.
+// What bounds it is measured in profiles/r1p_microbench.txt (QK^T from shared memory: 384 cycles per block).
 #ifdef PF_TIMELINE
 #include <cstdio>
 #endif

@@ -206,4 +206,52 @@ int launch_block_copy(void *const *caches, int n_caches, int64_t block_bytes, in
     return B200_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// token-ordered rows <-> scattered cells (session state save / load on the paged layout)
+// ------------------------------------------------------------------------------------------------
+struct kv_rows_args {
+    char   *caches[BC_MAX_CACHES];
+    char   *staging;                 // [n_caches of this launch][n_rows][row_bytes]
+    int64_t nb_token, row_bytes, n_cells, n_rows;
+    const int32_t *slots;            // [n_rows] cell of row i; out of range: row skipped
+};
+
+template <bool SCATTER>
+__global__ void __launch_bounds__(128)
+kv_rows_kernel(const __grid_constant__ kv_rows_args a) {
+    const int64_t n16 = a.row_bytes/16;
+    char *base = a.caches[blockIdx.y], *stage = a.staging + (int64_t) blockIdx.y*a.n_rows*a.row_bytes;
+    for (int64_t r = blockIdx.x; r < a.n_rows; r += gridDim.x) {
+        const int32_t c = a.slots[r];
+        if (c < 0 || c >= a.n_cells) continue;
+        uint4 *cell = reinterpret_cast<uint4 *>(base + (int64_t) c*a.nb_token), *row = reinterpret_cast<uint4 *>(stage + r*a.row_bytes);
+        for (int64_t i = threadIdx.x; i < n16; i += 128) { if (SCATTER) cell[i] = row[i]; else row[i] = cell[i]; }
+    }
+}
+
+int launch_kv_rows(bool scatter, void *const *caches, int n_caches, int64_t nb_token, int64_t row_bytes, int64_t n_cells,
+                   const int32_t *slots, int64_t n_rows, void *staging, cudaStream_t stream) {
+    if (n_rows == 0 || n_caches == 0) return B200_OK;
+    if (row_bytes <= 0 || (row_bytes & 15) || (nb_token & 15) || nb_token < row_bytes || (((uintptr_t) staging) & 15)) {
+        set_error("kv_rows: row_bytes %lld / nb_token %lld / staging must be multiples of 16 with row_bytes <= nb_token", (long long) row_bytes, (long long) nb_token);
+        return B200_ERR_INVALID;
+    }
+    const unsigned gx = (unsigned) (n_rows < 148*32 ? n_rows : 148*32);
+    for (int c0 = 0; c0 < n_caches; c0 += BC_MAX_CACHES) {
+        kv_rows_args a;
+        const int n = n_caches - c0 < BC_MAX_CACHES ? n_caches - c0 : BC_MAX_CACHES;
+        for (int i = 0; i < n; ++i) {
+            a.caches[i] = static_cast<char *>(caches[c0 + i]);
+            if (((uintptr_t) a.caches[i]) & 15) { set_error("kv_rows: cache %d not 16-byte aligned", c0 + i); return B200_ERR_INVALID; }
+        }
+        a.staging = static_cast<char *>(staging) + (int64_t) c0*n_rows*row_bytes;
+        a.nb_token = nb_token; a.row_bytes = row_bytes; a.n_cells = n_cells; a.n_rows = n_rows; a.slots = slots;
+        if (scatter) kv_rows_kernel<true><<<dim3(gx, (unsigned) n), 128, 0, stream>>>(a);
+        else         kv_rows_kernel<false><<<dim3(gx, (unsigned) n), 128, 0, stream>>>(a);
+        count_launch();
+        if (!check_launch("kv_rows")) return B200_ERR_CUDA;
+    }
+    return B200_OK;
+}
+
 } // namespace b200

@@ -34,6 +34,8 @@ bool check_launch(const char *what) {
 int    launch_kv_write(const b200_kv_write_desc &d, cudaStream_t stream);
 int    launch_block_copy(void *const *caches, int n_caches, int64_t block_bytes, int64_t n_blocks,
                          const int32_t *pairs, int64_t n_pairs, cudaStream_t stream);
+int    launch_kv_rows(bool scatter, void *const *caches, int n_caches, int64_t nb_token, int64_t row_bytes, int64_t n_cells,
+                      const int32_t *slots, int64_t n_rows, void *staging, cudaStream_t stream);
 bool   generic_supports(const b200_attn_desc &d);
 size_t generic_workspace(const b200_attn_desc &d);
 int    launch_attn_generic(const b200_attn_desc &d, cudaStream_t st);
@@ -164,6 +166,20 @@ B200_API int b200_block_copy(void *const *caches, int32_t n_caches, int64_t bloc
     if (n_caches < 0 || n_pairs < 0 || (n_caches > 0 && !caches) || (n_pairs > 0 && !pairs)) { set_error("block_copy: bad arguments"); return B200_ERR_INVALID; }
     if (!have_device()) return B200_ERR_CUDA;
     return launch_block_copy(caches, n_caches, block_bytes, n_blocks, pairs, n_pairs, static_cast<cudaStream_t>(stream));
+}
+
+B200_API int b200_kv_rows_gather(void *const *caches, int32_t n_caches, int64_t nb_token, int64_t row_bytes, int64_t n_cells,
+                                 const int32_t *slots, int64_t n_rows, void *staging, void *stream) {
+    if (n_caches < 0 || n_rows < 0 || (n_caches > 0 && !caches) || (n_rows > 0 && (!slots || !staging))) { set_error("kv_rows_gather: bad arguments"); return B200_ERR_INVALID; }
+    if (!have_device()) return B200_ERR_CUDA;
+    return launch_kv_rows(false, caches, n_caches, nb_token, row_bytes, n_cells, slots, n_rows, staging, static_cast<cudaStream_t>(stream));
+}
+
+B200_API int b200_kv_rows_scatter(void *const *caches, int32_t n_caches, int64_t nb_token, int64_t row_bytes, int64_t n_cells,
+                                  const int32_t *slots, int64_t n_rows, const void *staging, void *stream) {
+    if (n_caches < 0 || n_rows < 0 || (n_caches > 0 && !caches) || (n_rows > 0 && (!slots || !staging))) { set_error("kv_rows_scatter: bad arguments"); return B200_ERR_INVALID; }
+    if (!have_device()) return B200_ERR_CUDA;
+    return launch_kv_rows(true, caches, n_caches, nb_token, row_bytes, n_cells, slots, n_rows, const_cast<void *>(staging), static_cast<cudaStream_t>(stream));
 }
 
 } // extern "C"

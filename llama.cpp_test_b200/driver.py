@@ -5,10 +5,11 @@ from __future__ import annotations
 import ctypes as C
 from dataclasses import dataclass
 
-from . import (AttnDesc, KVWriteDesc, KERNEL_AUTO, TYPE_F16, TYPE_F32, TYPE_Q4_0, TYPE_Q8_0,  # noqa: F401
+from . import (AttnDesc, B200Error, KVWriteDesc, KERNEL_AUTO, STATE_ERRORS, TYPE_F16, TYPE_F32, TYPE_Q4_0, TYPE_Q8_0,  # noqa: F401
                check, lib, row_bytes)
 
 __all__ = ["KVLayout", "AttnCall", "StepCall", "kv_write_desc", "paged_attention", "dense_attention", "kv_write", "block_copy",
+           "kv_rows_gather", "kv_rows_scatter", "state_seq_pack", "state_seq_unpack", "state_seq_save", "state_seq_load",
            "BlockManager", "PagedKVCache", "current_stream"]
 
 
@@ -176,6 +177,92 @@ def block_copy(caches, block_bytes: int, n_blocks: int, pairs, stream: int | Non
                               C.c_void_p(current_stream() if stream is None else stream)), "b200_block_copy")
 
 
+def _kv_rows(fn, what, caches, layout: KVLayout, slots, staging, stream):
+    arr = (C.c_void_p * len(caches))(*[c.data_ptr() for c in caches])
+    check(fn(arr, len(caches), layout.token_bytes, layout.token_bytes, layout.n_cells, C.c_void_p(slots.data_ptr()), slots.shape[0],
+             C.c_void_p(staging.data_ptr()), C.c_void_p(current_stream() if stream is None else stream)), what)
+
+
+def kv_rows_gather(caches, layout: KVLayout, slots, staging, stream: int | None = None) -> None:
+    """staging[c][i] = token row of cell slots[i] in caches[c]; caches share one layout, slots int32 device [n],
+    staging uint8 device [len(caches), n, token_bytes]"""
+    _kv_rows(lib.b200_kv_rows_gather, "b200_kv_rows_gather", caches, layout, slots, staging, stream)
+
+
+def kv_rows_scatter(caches, layout: KVLayout, slots, staging, stream: int | None = None) -> None:
+    _kv_rows(lib.b200_kv_rows_scatter, "b200_kv_rows_scatter", caches, layout, slots, staging, stream)
+
+
+def state_seq_pack(k_rows, v_rows, type_k: int, type_v: int) -> bytes:
+    """frame token-ordered rows (uint8 numpy [n_layer, n_cells, size_row]) as the reference's single-sequence KV stream
+    (llama_kv_cache_unified::state_write, src/llama-kv-cache.cpp:848-971)"""
+    import numpy as np
+    k_rows, v_rows = np.ascontiguousarray(k_rows, dtype=np.uint8), np.ascontiguousarray(v_rows, dtype=np.uint8)
+    n_layer, n_cells, k_row = k_rows.shape
+    v_row = v_rows.shape[2]
+    size = lib.b200_kv_state_seq_size(n_cells, n_layer, k_row, v_row)
+    out = np.empty(size, dtype=np.uint8)
+    n = lib.b200_kv_state_seq_write(out.ctypes.data, size, n_cells, n_layer, type_k, k_row, type_v, v_row,
+                                    k_rows.ctypes.data, v_rows.ctypes.data)
+    if n != size:
+        raise B200Error(f"b200_kv_state_seq_write: {n}")
+    return out.tobytes()
+
+
+def state_seq_unpack(data: bytes, n_layer: int, type_k: int, k_row: int, type_v: int, v_row: int):
+    """validate a stream against the cache's shape like state_read_data (:1105-1240) -> (k_rows, v_rows) uint8 numpy
+    [n_layer, n_cells, size_row]; raises B200Error with the reference's reason on a mismatch"""
+    import numpy as np
+    buf = np.frombuffer(data, dtype=np.uint8)
+    n_cells = C.c_int64()
+    k_off, v_off = (C.c_int64 * max(n_layer, 1))(), (C.c_int64 * max(n_layer, 1))()
+    rc = lib.b200_kv_state_seq_parse(buf.ctypes.data, buf.size, n_layer, type_k, k_row, type_v, v_row, C.byref(n_cells), k_off, v_off)
+    if rc != 0:
+        raise B200Error(f"failed to restore kv cache: {STATE_ERRORS.get(rc, rc)}")
+    n = n_cells.value
+    k = np.stack([buf[k_off[l]:k_off[l] + n * k_row].reshape(n, k_row) for l in range(n_layer)]) if n_layer else np.zeros((0, n, k_row), np.uint8)
+    v = np.stack([buf[v_off[l]:v_off[l] + n * v_row].reshape(n, v_row) for l in range(n_layer)]) if n_layer else np.zeros((0, n, v_row), np.uint8)
+    return k, v
+
+
+def state_seq_save(cache: "PagedKVCache", seq: int, k_caches, v_caches, layout_k: KVLayout, layout_v: KVLayout | None = None) -> bytes:
+    """llama_state_seq_get_data for the paged layout: gather the sequence's rows of every layer on the device (two
+    launches), one D2H copy each for K and V, frame them in the reference's stream format"""
+    import torch
+    layout_v = layout_v or layout_k
+    cells = cache.slots_of(seq)
+    if cells is None:
+        cells = []
+    dev = k_caches[0].device
+    slots = torch.tensor(cells, dtype=torch.int32, device=dev)
+    n, nl = len(cells), len(k_caches)
+    ks = torch.empty((nl, n, layout_k.token_bytes), dtype=torch.uint8, device=dev)
+    vs = torch.empty((nl, n, layout_v.token_bytes), dtype=torch.uint8, device=dev)
+    if n:
+        kv_rows_gather(k_caches, layout_k, slots, ks)
+        kv_rows_gather(v_caches, layout_v, slots, vs)
+    return state_seq_pack(ks.cpu().numpy(), vs.cpu().numpy(), layout_k.type_id, layout_v.type_id)
+
+
+def state_seq_load(cache: "PagedKVCache", seq: int, data: bytes, k_caches, v_caches, layout_k: KVLayout,
+                   layout_v: KVLayout | None = None) -> int:
+    """llama_state_seq_set_data for the paged layout: validate, drop `seq`, reserve blocks, scatter the rows into
+    them.  Returns the number of restored tokens; raises B200Error("failed to restore kv cache ...") like the reference"""
+    import torch
+    layout_v = layout_v or layout_k
+    k, v = state_seq_unpack(data, len(k_caches), layout_k.type_id, layout_k.token_bytes, layout_v.type_id, layout_v.token_bytes)
+    n = k.shape[1]
+    cells = cache.restore_seq(seq, n)
+    if cells is None:
+        raise B200Error("failed to restore kv cache: failed to find available cells in kv cache")
+    if n:
+        dev = k_caches[0].device
+        slots = torch.tensor(cells, dtype=torch.int32, device=dev)
+        kv_rows_scatter(k_caches, layout_k, slots, torch.from_numpy(k.copy()).to(dev))
+        kv_rows_scatter(v_caches, layout_v, slots, torch.from_numpy(v.copy()).to(dev))
+    return n
+
+
 class BlockManager:
     """the fork's BlockManager through the C ABI (include/b200_host.h)"""
 
@@ -244,6 +331,26 @@ class PagedKVCache:
 
     def ref_count(self, block: int) -> int:
         return lib.b200_pc_ref_count(self._h, block)
+
+    def slots_of(self, seq: int):
+        """cell of every cached position, in order, or None for an unknown sequence"""
+        n = max(self.seq_len(seq), 1)
+        buf = (C.c_int32 * n)()
+        r = lib.b200_pc_slots_of(self._h, seq, buf, n)
+        return None if r < 0 else [buf[i] for i in range(r)]
+
+    def defrag(self, max_moves: int = -1):
+        """compaction plan: list of (src_block, dst_block) for block_copy; block tables are already rewritten"""
+        cap = max(self.n_blocks, 1)
+        buf = (C.c_int32 * (2 * cap))()
+        n = lib.b200_pc_defrag(self._h, buf, cap, max_moves)
+        return [(buf[2 * i], buf[2 * i + 1]) for i in range(max(n, 0))]
+
+    def restore_seq(self, seq: int, n_cells: int):
+        """drop `seq` and reserve n_cells tokens for it -> their cells, or None when the pool has no room"""
+        buf = (C.c_int32 * max(n_cells, 1))()
+        r = lib.b200_pc_restore_seq(self._h, seq, n_cells, buf)
+        return None if r < 0 else [buf[i] for i in range(r)]
 
     def export(self, seqs: list[int], stride: int):
         """-> (block_table rows as list of lists, seq_lens list) or None if stride too small"""

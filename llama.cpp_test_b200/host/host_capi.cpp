@@ -1,13 +1,9 @@
 // host_capi.cpp — C ABI wrappers (include/b200_host.h) over the host classes.
 #include "b200_host.h"
-#include "block_manager.h"
-#include "paged_kv_cache.h"
+#include "capi_types.h"
 
 #include <new>
 #include <vector>
-
-struct b200_block_manager { BlockManager impl; explicit b200_block_manager(size_t n) : impl(n) {} };
-struct b200_paged_cache   { PagedKVCache impl; b200_paged_cache(int64_t n, int bs) : impl(n, bs) {} };
 
 extern "C" {
 

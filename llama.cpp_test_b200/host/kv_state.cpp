@@ -1,0 +1,142 @@
+// kv_state.cpp — the reference's KV-cache session stream for ONE sequence, written from / read into the paged layout.
+//
+// Stream layout = llama_kv_cache_unified::state_write(io, seq_id >= 0) with flash-attention caches (v_trans = 0),
+// src/llama-kv-cache.cpp:848-971:
+//     u32 cell_count
+//     cell_count x { i32 pos, u32 n_seq_id = 0 }                               state_write_meta :905-923
+//     u32 v_trans = 0, u32 n_layer                                             state_write_data :925-971
+//     n_layer x { i32 k_type (ggml_type), u64 k_size_row, cell_count x k_size_row bytes }
+//     n_layer x { i32 v_type,             u64 v_size_row, cell_count x v_size_row bytes }
+// The unified cache writes the rows of a cell range straight out of k_l[il] (io.write_tensor); here the rows of a
+// sequence are scattered over blocks, so the device side gathers them into token order first (b200_kv_rows_gather,
+// csrc/kv_write.cu) and this file only frames them.  Reading mirrors state_read_meta / state_read_data
+// (:1008-1050, :1105-1240): every mismatch the reference rejects is rejected with its own code, nothing is modified
+// on failure of the parse, and the restore itself is seq_rm + append (= find_slot) + b200_kv_rows_scatter.
+#include "b200_host.h"
+#include "capi_types.h"
+
+#include <cstring>
+#include <vector>
+
+namespace {
+
+struct writer {
+    uint8_t *p; int64_t cap, n = 0;
+    void put(const void *src, int64_t bytes) { if (p && n + bytes <= cap) memcpy(p + n, src, (size_t) bytes); n += bytes; }
+    template <typename T> void val(T v) { put(&v, (int64_t) sizeof(T)); }
+};
+
+struct reader {
+    const uint8_t *p; int64_t size, n = 0; bool ok = true;
+    template <typename T> T val() { T v{}; if (n + (int64_t) sizeof(T) > size) { ok = false; return v; } memcpy(&v, p + n, sizeof(T)); n += (int64_t) sizeof(T); return v; }
+    bool skip(int64_t bytes) { if (bytes < 0 || n + bytes > size) { ok = false; return false; } n += bytes; return true; }
+};
+
+} // namespace
+
+extern "C" {
+
+B200_API int64_t b200_kv_state_seq_size(int64_t n_cells, int32_t n_layer, int64_t k_size_row, int64_t v_size_row) {
+    if (n_cells < 0 || n_layer < 0 || k_size_row < 0 || v_size_row < 0) return -1;
+    return 4 + n_cells*8 + 8 + (int64_t) n_layer*(2*(4 + 8) + n_cells*(k_size_row + v_size_row));
+}
+
+B200_API int64_t b200_kv_state_seq_write(uint8_t *out, int64_t cap, int64_t n_cells, int32_t n_layer,
+                                         int32_t type_k, int64_t k_size_row, int32_t type_v, int64_t v_size_row,
+                                         const uint8_t *k_rows, const uint8_t *v_rows) {
+    const int64_t need = b200_kv_state_seq_size(n_cells, n_layer, k_size_row, v_size_row);
+    if (need < 0 || n_cells > 0xffffffffLL || (n_cells > 0 && n_layer > 0 && (!k_rows || !v_rows))) return -1;
+    if (!out || cap < need) return -need;                     // caller sizes the buffer from the magnitude
+    writer w{out, cap};
+    w.val<uint32_t>((uint32_t) n_cells);
+    for (int64_t i = 0; i < n_cells; ++i) { w.val<int32_t>((int32_t) i); w.val<uint32_t>(0); }   // pos = token index
+    w.val<uint32_t>(0);                                       // v_trans: flash-attention caches are not transposed
+    w.val<uint32_t>((uint32_t) n_layer);
+    for (int32_t il = 0; il < n_layer; ++il) {
+        w.val<int32_t>(type_k); w.val<uint64_t>((uint64_t) k_size_row);
+        w.put(k_rows + (int64_t) il*n_cells*k_size_row, n_cells*k_size_row);
+    }
+    for (int32_t il = 0; il < n_layer; ++il) {
+        w.val<int32_t>(type_v); w.val<uint64_t>((uint64_t) v_size_row);
+        w.put(v_rows + (int64_t) il*n_cells*v_size_row, n_cells*v_size_row);
+    }
+    return w.n;
+}
+
+B200_API int32_t b200_kv_state_seq_parse(const uint8_t *data, int64_t size, int32_t n_layer,
+                                         int32_t type_k, int64_t k_size_row, int32_t type_v, int64_t v_size_row,
+                                         int64_t *n_cells_out, int64_t *k_off, int64_t *v_off) {
+    if (!data || size < 0 || n_layer < 0) return B200_STATE_ERR_TRUNCATED;
+    reader r{data, size};
+    const uint32_t n_cells = r.val<uint32_t>();
+    int32_t prev = -1;
+    for (uint32_t i = 0; i < n_cells && r.ok; ++i) {
+        const int32_t  pos      = r.val<int32_t>();
+        const uint32_t n_seq_id = r.val<uint32_t>();
+        if (!r.ok) break;
+        if (n_seq_id != 0) return B200_STATE_ERR_SEQ_AGNOSTIC;           // "invalid seq_id-agnostic kv cell" :1024-1027
+        // the paged cache stores position p of a sequence at table index p: a restored sequence must be 0..n-1
+        // (the unified cache accepts any positions; a shifted or holed sequence is outside the block-table model)
+        if (pos != prev + 1) return B200_STATE_ERR_POSITIONS;
+        prev = pos;
+    }
+    const uint32_t v_trans = r.val<uint32_t>();
+    const uint32_t nl      = r.val<uint32_t>();
+    if (!r.ok) return B200_STATE_ERR_TRUNCATED;
+    if (nl != (uint32_t) n_layer) return B200_STATE_ERR_LAYERS;          // "mismatched layer count" :1112-1115
+    if (v_trans != 0) return B200_STATE_ERR_VTRANS;                      // "incompatible V transposition" :1120-1123
+    for (int32_t il = 0; il < n_layer; ++il) {
+        const int32_t  t   = r.val<int32_t>();
+        const uint64_t row = r.val<uint64_t>();
+        if (!r.ok) return B200_STATE_ERR_TRUNCATED;
+        if (t != type_k) return B200_STATE_ERR_TYPE;                     // "mismatched key type" :1132-1136
+        if (row != (uint64_t) k_size_row) return B200_STATE_ERR_ROW_SIZE;// "mismatched key row size" :1141-1145
+        if (k_off) k_off[il] = r.n;
+        if (!r.skip((int64_t) n_cells*k_size_row)) return B200_STATE_ERR_TRUNCATED;
+    }
+    for (int32_t il = 0; il < n_layer; ++il) {
+        const int32_t  t   = r.val<int32_t>();
+        const uint64_t row = r.val<uint64_t>();
+        if (!r.ok) return B200_STATE_ERR_TRUNCATED;
+        if (t != type_v) return B200_STATE_ERR_TYPE;
+        if (row != (uint64_t) v_size_row) return B200_STATE_ERR_ROW_SIZE;
+        if (v_off) v_off[il] = r.n;
+        if (!r.skip((int64_t) n_cells*v_size_row)) return B200_STATE_ERR_TRUNCATED;
+    }
+    if (n_cells_out) *n_cells_out = (int64_t) n_cells;
+    return 0;
+}
+
+/* restore bookkeeping = state_read_meta's single-sequence branch (:1010-1036): seq_rm(dest, -1, -1), then find_slot
+ * for cell_count tokens.  Like the reference, the old contents of `seq` are gone even when no room is found
+ * (state_read then throws "failed to restore kv cache" after another seq_rm, :889-896). */
+B200_API int64_t b200_pc_restore_seq(b200_paged_cache *pc, int32_t seq, int64_t n_cells, int32_t *slot_mapping) {
+    if (!pc || n_cells < 0 || (n_cells > 0 && !slot_mapping)) return -1;
+    PagedKVCache &c = pc->impl;
+    c.seq_rm(seq, -1, -1);
+    std::vector<int32_t> slots;
+    std::vector<std::pair<int32_t, int32_t>> cow;
+    if (!c.append(seq, n_cells, slots, cow)) return -1;     // "failed to find available cells in kv cache" :1033-1036
+    for (size_t i = 0; i < slots.size(); ++i) slot_mapping[i] = slots[i];
+    return (int64_t) slots.size();
+}
+
+B200_API int64_t b200_pc_slots_of(const b200_paged_cache *pc, int32_t seq, int32_t *cells, int64_t cap) {
+    if (!pc) return -1;
+    std::vector<int32_t> v;
+    if (!pc->impl.slots_of(seq, v)) return -1;
+    if ((int64_t) v.size() > cap) return -(int64_t) v.size() - 1;
+    for (size_t i = 0; i < v.size(); ++i) cells[i] = v[i];
+    return (int64_t) v.size();
+}
+
+B200_API int64_t b200_pc_defrag(b200_paged_cache *pc, int32_t *moves, int64_t cap, int64_t max_moves) {
+    if (!pc || cap < 0) return -1;
+    if (max_moves < 0 || max_moves > cap) max_moves = cap;    // never plan more than the caller can receive
+    std::vector<std::pair<int32_t, int32_t>> mv;
+    const int64_t n = pc->impl.defrag(mv, max_moves);
+    for (int64_t i = 0; i < n; ++i) { moves[2*i] = mv[(size_t) i].first; moves[2*i + 1] = mv[(size_t) i].second; }
+    return n;
+}
+
+} // extern "C"

@@ -114,6 +114,41 @@ const std::vector<int32_t> * PagedKVCache::blocks_of(seq_id seq) const {
     return it == seqs_.end() ? nullptr : &it->second.blocks;
 }
 
+bool PagedKVCache::slots_of(seq_id seq, std::vector<int32_t> & cells) const {
+    auto it = seqs_.find(seq);
+    if (it == seqs_.end()) return false;
+    const Seq & s = it->second;
+    cells.reserve(cells.size() + (size_t) s.len);
+    for (int64_t p = 0; p < s.len; ++p)
+        cells.push_back((int32_t) ((int64_t) s.blocks[(size_t) (p/block_size_)]*block_size_ + p % block_size_));
+    return true;
+}
+
+int64_t PagedKVCache::defrag(std::vector<std::pair<int32_t, int32_t>> & moves, int64_t max_moves) {
+    const int64_t n_used = n_blocks() - n_free_;
+    std::vector<int32_t> remap(ref_.size(), -1);
+    int64_t n_moves = 0;
+    int32_t hole = 0;                                           // lowest free index below n_used
+    for (int32_t src = (int32_t) ref_.size() - 1; src >= n_used; --src) {
+        if (ref_[(size_t) src] == 0) continue;
+        if (max_moves >= 0 && n_moves >= max_moves) break;
+        while (hole < n_used && ref_[(size_t) hole] != 0) ++hole;
+        if (hole >= n_used) break;
+        moves.emplace_back(src, hole);
+        remap[(size_t) src] = hole;
+        ref_[(size_t) hole] = ref_[(size_t) src];
+        ref_[(size_t) src]  = 0;
+        ++n_moves;
+    }
+    if (n_moves == 0) return 0;
+    for (auto & kv : seqs_)
+        for (int32_t & b : kv.second.blocks)
+            if (remap[(size_t) b] >= 0) b = remap[(size_t) b];
+    free_ = decltype(free_)();
+    for (int32_t b = 0; b < (int32_t) ref_.size(); ++b) if (ref_[(size_t) b] == 0) free_.push(b);
+    return n_moves;
+}
+
 bool PagedKVCache::export_tables(const seq_id * seqs, int64_t n, int32_t * block_table, int64_t stride, int32_t * seq_lens) const {
     for (int64_t i = 0; i < n; ++i) {
         auto it = seqs_.find(seqs[i]);

@@ -48,6 +48,17 @@ public:
     int64_t n_seqs() const { return (int64_t) seqs_.size(); }
     const std::vector<int32_t> * blocks_of(seq_id seq) const;
 
+    // Cell index of every cached position of `seq`, in position order (the gather list of a state save).
+    bool slots_of(seq_id seq, std::vector<int32_t> & cells) const;
+
+    // Compaction (the block-granular form of llama_kv_cache_unified::defrag_prepare, src/llama-kv-cache.cpp:711-846,
+    // which moves cells from the end of the cache into holes at the front): used blocks with the highest indices move
+    // into the lowest free indices until the used blocks are [0, n_used).  Appends (src_block, dst_block) pairs for
+    // b200_block_copy — no block is both a source and a destination — and rewrites every block table that names a
+    // moved block (shared blocks move once, ref-counts travel with them).  max_moves < 0: no limit
+    // (the reference caps moves per graph, llama-kv-cache.cpp:724-729).  Returns the number of moves.
+    int64_t defrag(std::vector<std::pair<int32_t, int32_t>> & moves, int64_t max_moves = -1);
+
     // Export rows of the device block table / seq_lens for the given sequences (row i <-> seqs[i]);
     // unused entries are filled with 0 (a valid block, never dereferenced past seq_len).
     // Returns false if a row would not fit in `stride` entries.
