@@ -42,7 +42,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 TYPES = {"f16": 1, "q4_0": 2, "q8_0": 8}
 D, BS = 128, 16
 WORKLOADS = {
-    "config2": dict(n_head=32, n_head_kv=8, n_layer=32, n_seqs=64, ctx="U{512..8192} seed 7+rank", shard="sequences",
+    "config2": dict(n_head=32, n_head_kv=8, n_layer=32, n_seqs=64, ctx="U{512..8192} seed 7+rank, union LPT-sharded over the ranks", shard="sequences",
                     scaling="weak", kv_type="q8_0", steps=100),
     "config1": dict(n_head=32, n_head_kv=8, n_layer=32, n_seqs=8, ctx="1024", shard="sequences", scaling="weak",
                     kv_type="f16", steps=500),
@@ -57,10 +57,17 @@ def row_bytes(t, n):
     return {1: n * 2, 8: n // 32 * 34, 2: n // 32 * 18}[t]
 
 
-def ctx_lens(workload, rank):
+def ctx_lens(workload, rank, world=1):
     w = WORKLOADS[workload]
     if workload == "config2":
-        return np.random.default_rng(7 + rank).integers(512, 8193, size=w["n_seqs"]).astype(np.int32)
+        draw = lambda r: np.random.default_rng(7 + r).integers(512, 8193, size=w["n_seqs"]).astype(np.int32)
+        if world == 1:
+            return draw(rank)
+        # the job's batch is the union of every rank's 64 draws; sequence-batch sharding (partition A, sharding.py)
+        # hands each rank the share that balances the summed context, so no rank waits for the unluckiest draw
+        from __graft_entry__ import load
+        allc = np.concatenate([draw(r) for r in range(world)])
+        return allc[load().shard_sequences(allc, world)[rank]]
     return np.full(w["n_seqs"], int(w["ctx"].split()[0]), dtype=np.int32)
 
 
@@ -229,7 +236,8 @@ def main():
     sh = pkg.head_shard(rank if by_heads else 0, world if by_heads else 1, W["n_head"], W["n_head_kv"])
     n_head, n_head_kv = sh.n_head, sh.n_head_kv              # what THIS rank computes
     collective = by_heads and world > 1
-    lens = ctx_lens(args.workload, rank)
+    lens = ctx_lens(args.workload, rank, 1 if by_heads else world)
+    n_seqs = len(lens)
     bt_h, slot_h, n_blocks = block_tables(lens)
     total = int(lens.sum())
     lay = pkg.KVLayout(t, n_head_kv, D, BS, n_blocks + 8)

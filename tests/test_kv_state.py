@@ -1,0 +1,163 @@
+"""KV session state on the paged layout and block defrag — host side, no GPU.
+
+* the stream the product writes for one sequence equals, byte for byte, what llama_kv_cache_unified::state_write
+  produces for the same tokens held in a flat unified cache (oracle/kv_state_oracle.py restates
+  src/llama-kv-cache.cpp:848-971 over the reference's own cell layout);
+* the parser rejects exactly the streams state_read_meta / state_read_data reject (:1008-1240), for the same reason;
+* restore bookkeeping = seq_rm + find_slot; the defrag plan compacts blocks without changing what any sequence sees.
+"""
+import struct
+
+import numpy as np
+import pytest
+
+from oracle.kv_state_oracle import unified_state_read_errors, unified_state_write
+from workloads import F16, Q4_0, Q8_0, row_bytes
+
+N_EMBD_GQA = 1024          # 8 kv heads x 128 (Llama-3-8B)
+
+
+def _rows(rng, n_layer, n, size_row):
+    return rng.integers(0, 256, size=(n_layer, n, size_row), dtype=np.uint8)
+
+
+@pytest.mark.parametrize("tk,tv", [(F16, F16), (Q8_0, Q8_0), (Q4_0, Q4_0), (Q8_0, F16)])
+@pytest.mark.parametrize("placement", ["contiguous", "two_ranges", "empty"])
+def test_stream_equals_reference_writer(pkg, tk, tv, placement):
+    rng = np.random.default_rng(3)
+    n_layer, size = 3, 96
+    k_row, v_row = row_bytes(tk, N_EMBD_GQA), row_bytes(tv, N_EMBD_GQA)
+    # the reference side: a flat unified cache; sequence 5 holds n tokens, another sequence sits in between
+    if placement == "contiguous":
+        cell_of = list(range(17, 17 + 40))
+    elif placement == "two_ranges":
+        cell_of = list(range(4, 20)) + list(range(33, 60))
+    else:
+        cell_of = []
+    n = len(cell_of)
+    cells = [(-1, set()) for _ in range(size)]
+    for c in range(20, 33):
+        cells[c] = (c - 20, {9})
+    for p, c in enumerate(cell_of):
+        cells[c] = (p, {5} if p >= 8 else {5, 9})                 # a shared prefix: cells may carry several ids
+    k_flat = [rng.integers(0, 256, size=(size, k_row), dtype=np.uint8) for _ in range(n_layer)]
+    v_flat = [rng.integers(0, 256, size=(size, v_row), dtype=np.uint8) for _ in range(n_layer)]
+    want = unified_state_write(cells, 5, k_flat, v_flat, tk, tv)
+    # the product side: the same rows in token order (what b200_kv_rows_gather delivers)
+    k_tok = np.stack([k[cell_of] for k in k_flat]) if n else np.zeros((n_layer, 0, k_row), np.uint8)
+    v_tok = np.stack([v[cell_of] for v in v_flat]) if n else np.zeros((n_layer, 0, v_row), np.uint8)
+    got = pkg.state_seq_pack(k_tok, v_tok, tk, tv)
+    assert got == want
+    assert len(got) == pkg.lib.b200_kv_state_seq_size(n, n_layer, k_row, v_row)
+    k2, v2 = pkg.state_seq_unpack(got, n_layer, tk, k_row, tv, v_row)
+    assert np.array_equal(k2, k_tok) and np.array_equal(v2, v_tok)
+    assert unified_state_read_errors(got, n_layer, tk, k_row, tv, v_row) is None
+
+
+def test_parser_rejects_what_the_reference_rejects(pkg):
+    rng = np.random.default_rng(4)
+    n_layer, n = 2, 5
+    k_row, v_row = row_bytes(Q8_0, N_EMBD_GQA), row_bytes(F16, N_EMBD_GQA)
+    good = pkg.state_seq_pack(_rows(rng, n_layer, n, k_row), _rows(rng, n_layer, n, v_row), Q8_0, F16)
+    meta_end = 4 + 8*n
+    k0 = meta_end + 8                                             # first key header
+    v0 = k0 + n_layer*(12 + n*k_row)                              # first value header
+
+    def patched(off, fmt, val):
+        b = bytearray(good)
+        struct.pack_into(fmt, b, off, val)
+        return bytes(b)
+
+    cases = {
+        "invalid seq_id-agnostic kv cell": patched(4 + 8*2 + 4, "<I", 1),
+        "mismatched layer count": patched(meta_end + 4, "<I", 3),
+        "incompatible V transposition": patched(meta_end, "<I", 1),
+        "mismatched key type": patched(k0, "<i", F16),
+        "mismatched key row size": patched(k0 + 4, "<Q", k_row + 34),
+        "mismatched value type": patched(v0, "<i", Q8_0),
+        "mismatched value row size": patched(v0 + 4, "<Q", v_row - 2),
+        "truncated": good[:-7],
+    }
+    for reason, blob in cases.items():
+        assert unified_state_read_errors(blob, n_layer, Q8_0, k_row, F16, v_row) == reason   # the oracle agrees it is bad
+        with pytest.raises(pkg.B200Error) as e:
+            pkg.state_seq_unpack(blob, n_layer, Q8_0, k_row, F16, v_row)
+        msg = str(e.value)
+        assert msg.startswith("failed to restore kv cache")       # the reference's exception text, llama-kv-cache.cpp:895
+        ours = {"mismatched key type": "mismatched key/value type", "mismatched value type": "mismatched key/value type",
+                "mismatched key row size": "mismatched key/value row size", "mismatched value row size": "mismatched key/value row size",
+                "truncated": "truncated stream"}.get(reason, reason)
+        assert ours in msg
+    # shape of the cache differs from the stream's: rejected as the reference would
+    with pytest.raises(pkg.B200Error):
+        pkg.state_seq_unpack(good, n_layer, Q8_0, k_row, Q8_0, row_bytes(Q8_0, N_EMBD_GQA))
+    # positions that are not 0..n-1 cannot live in a block table
+    with pytest.raises(pkg.B200Error, match="positions"):
+        pkg.state_seq_unpack(patched(4 + 8*3, "<i", 7), n_layer, Q8_0, k_row, F16, v_row)
+
+
+def test_restore_seq_is_seq_rm_plus_find_slot(pkg):
+    c = pkg.PagedKVCache(8, 4)
+    c.append(0, 10)                      # blocks 0,1,2
+    c.append(1, 6)                       # blocks 3,4
+    assert c.seq_cp(1, 2, 0, -1)         # 2 shares blocks 3,4
+    cells = c.restore_seq(0, 7)          # old blocks of 0 come back first: lowest free indices again
+    assert cells == [0, 1, 2, 3, 4, 5, 6] and c.seq_len(0) == 7 and c.n_free() == 8 - 2 - 2
+    assert c.restore_seq(1, 3) == [8, 9, 10]                      # blocks 3,4 stay with seq 2; new block 2
+    assert c.ref_count(3) == 1 and c.ref_count(4) == 1 and c.seq_len(2) == 6
+    assert c.slots_of(2) == [12, 13, 14, 15, 16, 17]
+    # no room: like the reference, the destination sequence is gone afterwards (state_read: seq_rm, then throw)
+    assert c.restore_seq(0, 4*8) is None
+    assert c.seq_len(0) == 0 and c.slots_of(0) is None
+    assert c.restore_seq(7, 0) == [] and c.seq_len(7) == 0
+
+
+def test_defrag_compacts_and_preserves_every_sequence(pkg):
+    rng = np.random.default_rng(11)
+    bs, nb = 4, 64
+    c = pkg.PagedKVCache(nb, bs)
+    store = np.full(nb*bs, -1, dtype=np.int64)                    # what each cell holds: a unique token id
+    next_tok, live = 0, {}
+    for step in range(200):
+        op = rng.integers(0, 4)
+        seq = int(rng.integers(0, 10))
+        if op <= 1:
+            n = int(rng.integers(1, 9))
+            r = c.append(seq, n)
+            if r is None:
+                continue
+            slots, cow = r
+            for s, d in cow:
+                store[d*bs:(d + 1)*bs] = store[s*bs:(s + 1)*bs]
+            for s in slots:
+                store[s] = next_tok; next_tok += 1
+            live[seq] = True
+        elif op == 2 and live:
+            victim = int(rng.choice(list(live)))
+            c.seq_rm(victim); live.pop(victim)
+        elif op == 3 and live:
+            src = int(rng.choice(list(live)))
+            if src != seq and c.seq_cp(src, seq, 0, int(rng.integers(1, c.seq_len(src) + 1))):
+                live[seq] = True
+    assert len(live) >= 3
+    before = {s: store[c.slots_of(s)].copy() for s in live}
+    refs_before = sorted(c.ref_count(b) for b in range(nb) if c.ref_count(b) > 0)
+    n_used = nb - c.n_free()
+    assert any(c.ref_count(b) == 0 for b in range(n_used)), "the op stream left no hole to compact"
+
+    limited = c.defrag(max_moves=1)                               # the reference caps moves per graph (:724-729)
+    assert len(limited) == 1
+    moves = limited + c.defrag()
+    srcs, dsts = [m[0] for m in moves], [m[1] for m in moves]
+    assert not set(srcs) & set(dsts), "a block is both source and destination"
+    assert all(s >= n_used > d for s, d in moves)
+    for s, d in moves:                                            # what b200_block_copy does on the device
+        store[d*bs:(d + 1)*bs] = store[s*bs:(s + 1)*bs]
+    assert [c.ref_count(b) > 0 for b in range(nb)] == [b < n_used for b in range(nb)]
+    assert sorted(c.ref_count(b) for b in range(n_used)) == refs_before
+    assert c.n_free() == nb - n_used
+    for s in live:
+        assert np.array_equal(store[c.slots_of(s)], before[s]), f"sequence {s} changed"
+    assert c.defrag() == []                                       # idempotent
+    r = c.append(99, bs)                                          # the allocator still hands out the lowest free block
+    assert r is not None and r[0][0] == n_used*bs
