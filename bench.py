@@ -176,7 +176,7 @@ def workload_config(workload, kv_type, world):
     return {"workload": f"{workload}_{'llama3_70b' if w['n_head'] == 64 else 'llama3_8b'}_{kv_type}", "n_seqs": w["n_seqs"],
             "ctx": w["ctx"], "block_size": BS, "n_head": w["n_head"], "n_head_kv": w["n_head_kv"], "head_dim": D,
             "parallelism": (f"sequence-batch sharding x{world}, no collective" if w["shard"] == "sequences"
-                            else f"KV-head sharding x{world} + one NCCL all-gather of the outputs per layer")}
+                            else f"KV-head sharding x{world} + one exchange of the outputs per layer")}
 
 
 def reference_arm(args, rank, world):
@@ -206,6 +206,8 @@ def main():
     ap.add_argument("--kernel", type=int, default=0, help="0 auto, 1 generic, 2 stream-K")
     ap.add_argument("--layers", type=int, default=0)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--exchange", choices=["peer", "nccl"], default="peer",
+                    help="config4 at N>1: output exchange through the library's own NVLink peer-memory kernels (default) or NCCL all-gather")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the end-to-end leg")
     args = ap.parse_args()
@@ -266,9 +268,20 @@ def main():
                           max_seq_len=int(lens.max()), total_tokens=total, kernel=args.kernel) for l in range(n_layer)]
     torch.cuda.synchronize()
 
-    def layer_op(l):
+    peer = None
+    if collective and args.exchange == "peer":
+        peer = pkg.PeerGather((n_seqs, n_head, D), n_slots=max(2, n_layer) + 1)
+        # once, before anything is timed: the peer-memory exchange delivers exactly what NCCL's all-gather delivers
+        calls[0].run(); peer.publish(out_d[0], max(2, n_layer)); peer.wait(); peer.check()
+        ref_g = pkg.gather_head_outputs(out_d[0])
+        if not torch.equal(peer.gathered(max(2, n_layer)), ref_g):
+            raise SystemExit("peer-memory exchange differs from NCCL all_gather")
+
+    def layer_op(l, keep=False):
         calls[l].run()
-        if collective:
+        if peer is not None:
+            peer.publish(out_d[l], l if n_layer > 1 else peer.epoch & 1); peer.wait()   # slot = layer: gathered(l) is that layer's exchanged output
+        elif collective:
             pkg.gather_head_outputs(out_d[l], gathered[l])
 
     def step_resident():
@@ -277,7 +290,8 @@ def main():
 
     l0 = pkg.lib.b200_launch_count(); step_resident(); launches_per_step = pkg.lib.b200_launch_count() - l0
     graph = None
-    if not args.no_graph and not collective:
+    if not args.no_graph and (not collective or peer is not None):
+        e_before = peer.epoch if peer is not None else 0
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
@@ -286,7 +300,16 @@ def main():
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph):
             step_resident()
-    run_step = graph.replay if graph is not None else step_resident
+        if peer is not None:
+            # capture launched nothing: the host epoch must only count publishes that ran (the warm-up on `side` did)
+            peer.epoch = e_before + n_layer
+
+    def run_step():
+        if graph is None:
+            return step_resident()
+        graph.replay()
+        if peer is not None:
+            peer.note_replay(n_layer)
 
     def barrier():
         torch.cuda.synchronize()
@@ -324,7 +347,7 @@ def main():
     # layer, overlapped with compute), kv_write + attention (+ all-gather) per layer, D2H of every layer's output
     e2e = None
     if not args.no_e2e:
-        res_d = gathered if collective else out_d
+        res_d = (peer.all_slots()[:n_layer] if peer is not None else gathered) if collective else out_d
         q_h = (torch.rand((n_layer, n_seqs, n_head, D)) * 2 - 1).pin_memory()
         knew_h = (torch.rand((n_layer, n_seqs, n_head_kv * D)) * 2 - 1).pin_memory()
         vnew_h = (torch.rand((n_layer, n_seqs, n_head_kv * D)) * 2 - 1).pin_memory()
@@ -366,7 +389,7 @@ def main():
                 else:
                     for l in range(a0, a1):
                         pkg.kv_write(knew_d[l], vnew_d[l], slot_new_d, kcs[l], vcs[l], lay)
-                        layer_op(l)
+                        layer_op(l, keep=True)
                 ev_c[gi].record(cur)
                 s_out.wait_event(ev_c[gi])
                 with torch.cuda.stream(s_out):
@@ -387,6 +410,9 @@ def main():
         cfg.update({"n_layer": n_layer, "n_head_per_gpu": n_head, "n_head_kv_per_gpu": n_head_kv,
                     "kv_bytes_per_step_per_gpu": bytes_step_rank, "cuda_graph": graph is not None, "kernel": which,
                     "l2_flush": f"inputs (per-layer KV caches, {bytes_step_rank / 1e9:.1f} GB per step per GPU) are far larger than the 126 MB L2"})
+        if collective:
+            cfg["exchange"] = ("NVLink peer-memory push + epoch flags (b200_peer_publish / b200_peer_wait), verified equal to NCCL all_gather"
+                               if peer is not None else "NCCL all_gather_into_tensor")
         line = {
             "metric": "paged-attn decode KV-read GB/s", "value": round(value, 2), "unit": "GB/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4), "higher_is_better": True,

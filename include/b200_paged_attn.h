@@ -141,6 +141,31 @@ B200_API int b200_kv_rows_scatter(void *const *caches, int32_t n_caches, int64_t
  */
 B200_API int b200_decode_step(const b200_kv_write_desc *writes, const b200_attn_desc *attns, int32_t n_layers, void *stream);
 
+/*
+ * KV-head sharding (one process per GPU, rank g computes the query heads of its kv heads): the one exchange step,
+ * every rank's output slice to every rank, over NVLink peer memory with the library's own kernels instead of a
+ * library collective (the payload is ~1 MiB per layer: the cost is latency).  The reference has no counterpart
+ * (its multi-GPU path is cudaMemcpyPeerAsync row splits, ggml/src/ggml-cuda/ggml-cuda.cu:598,1592).
+ *   b200_peer_alloc / _free      cudaMalloc'ed, zero-filled device memory that can be exported
+ *   b200_peer_export / _open     CUDA IPC handle (64 bytes) of such memory / map a peer's handle into this process
+ *   b200_peer_publish            gathered_p[slot][rank] = local for every peer p (own copy included), then
+ *                                flag_p[rank] = epoch (system-scope release); epoch = ++state[0] on the device.
+ *                                Two consecutive exchanges must name different slots (e.g. slot = layer index).
+ *   b200_peer_wait               wait until flags[r] >= state[0] for every r (bounded spin; on timeout state[2] != 0)
+ * gathered buffers are [n_slots][world][bytes]; flags uint32 [world]; state uint32 [4], all from b200_peer_alloc.
+ * peer_bufs / peer_flags are HOST arrays of `world` device pointers (entry `rank` = this process's own memory).
+ * Both launches are CUDA-graph capturable.
+ */
+B200_API void *b200_peer_alloc(size_t bytes);
+B200_API int   b200_peer_free(void *p);
+B200_API int   b200_peer_export(void *p, unsigned char handle[64]);
+B200_API void *b200_peer_open(const unsigned char handle[64]);
+B200_API int   b200_peer_close(void *p);
+B200_API int   b200_peer_publish(const void *local, int64_t bytes, void *const *peer_bufs, void *const *peer_flags,
+                                 void *state, int32_t slot, int32_t rank, int32_t world, void *stream);
+B200_API int   b200_peer_wait(void *flags, void *state, int32_t world, void *stream);
+B200_API int   b200_peer_read_state(const void *state, uint32_t out[4]);   /* synchronous D2H of the 4 state words */
+
 /* diagnostics */
 B200_API const char *b200_last_error(void);
 B200_API const char *b200_version(void);

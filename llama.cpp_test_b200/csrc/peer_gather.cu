@@ -1,0 +1,102 @@
+// peer_gather.cu — the one exchange step of the KV-head-sharded path (partition B) over NVLink peer
+// memory instead of a library collective.
+//
+// Every rank g of G computes the query heads of its own kv heads, out_g [n_q][n_head/G][d] F32, and every rank needs
+// all of them (the wo matmul that follows consumes [n_q][n_head][d]).  The payload is tiny (config 4: 128 KiB per
+// rank per layer, 1 MiB in total), so the cost of an all-gather is latency: a library call costs ~25 us per layer
+// against ~82 us of attention.  Here each rank PUSHES its slice straight into every peer's gathered buffer with plain
+// 16-byte stores through peer-mapped pointers (all peers are one NVSwitch hop away), publishes an epoch flag per
+// peer with a system-scope release, and a one-warp kernel waits for the G flags with acquire loads:
+//
+//     b200_peer_publish   gathered_p[slot][rank] = local   for every peer p (its own copy included);   flag_p[rank] = epoch
+//     b200_peer_wait      spin until flag_own[r] >= epoch for every r                          (bounded: ~2 s, then error)
+//
+// Both kernels take the epoch from a device counter the publish kernel advances itself, so a whole multi-layer step
+// is CUDA-graph capturable and replays stay in step across ranks.  The caller names the destination slot (e.g. the
+// layer index) and must not use the same slot for two consecutive exchanges: a rank can only start exchange e+2 after
+// it saw every peer's flag e+1, which each peer raised after (in stream order) consuming the slot of exchange e.
+//
+// The reference has no counterpart: its multi-GPU path splits matmul rows and moves them with cudaMemcpyPeerAsync
+// (ggml/src/ggml-cuda/ggml-cuda.cu:598,1592); attention is never sharded there.
+//
+// Memory comes from cudaMalloc + CUDA IPC handles (the processes are one per GPU); handles are exchanged by the host
+// side over torch.distributed (plumbing), see llama.cpp_test_b200/sharding.py PeerGather.
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int PG_MAX_WORLD = 16;
+
+struct pg_args {
+    const uint4 *local;                  // this rank's slice
+    int64_t n16;                         // slice size in 16-byte units
+    char     *peer_buf[PG_MAX_WORLD];    // peer p's gathered buffer: [n_slots][world][slice]
+    uint32_t *peer_flag[PG_MAX_WORLD];   // peer p's flags: [world] (slot r written by rank r)
+    uint32_t *state;                     // local: [0] epoch of the last publish, [1] CTAs done, [2] wait error flag
+    int rank, world, slot;
+};
+
+__global__ void __launch_bounds__(256)
+pg_publish_kernel(const __grid_constant__ pg_args a) {
+    // blockIdx.y = destination peer; blockIdx.x strides over the slice
+    pdl_prologue();
+    const uint32_t epoch = a.state[0] + 1;                               // every CTA reads the pre-launch value
+    const int p = blockIdx.y;
+    uint4 *dst = reinterpret_cast<uint4 *>(a.peer_buf[p]) + ((int64_t) a.slot*a.world + a.rank)*a.n16;
+    for (int64_t i = (int64_t) blockIdx.x*256 + threadIdx.x; i < a.n16; i += (int64_t) gridDim.x*256) dst[i] = a.local[i];
+    __threadfence_system();                                              // this thread's peer stores are visible system-wide ...
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t total = gridDim.x*gridDim.y;
+        if (atomicAdd(&a.state[1], 1u) == total - 1) {                   // ... before the last CTA of the grid raises the flags
+            __threadfence_system();
+            a.state[1] = 0;
+            for (int q = 0; q < a.world; ++q)
+                asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(a.peer_flag[q] + a.rank), "r"(epoch) : "memory");
+            a.state[0] = epoch;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(32)
+pg_wait_kernel(uint32_t *flags, uint32_t *state, int world) {
+    const uint32_t epoch = state[0];                                     // the publish before us (stream order) set it
+    if ((int) threadIdx.x < world) {
+        const long long t0 = clock64();
+        uint32_t v;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + threadIdx.x) : "memory");
+            if ((int32_t) (v - epoch) >= 0) break;
+            if (clock64() - t0 > 4000000000LL) { state[2] = 1 + threadIdx.x; break; }      // ~2 s: a peer died; do not hang the GPU
+        } while (true);
+    }
+}
+
+int launch_peer_publish(const void *local, int64_t bytes, void *const *peer_bufs, void *const *peer_flags, void *state,
+                        int slot, int rank, int world, cudaStream_t stream) {
+    if (slot < 0 || world < 1 || world > PG_MAX_WORLD || rank < 0 || rank >= world || bytes <= 0 || (bytes & 15) || (((uintptr_t) local) & 15)) {
+        set_error("peer_publish: bad arguments (world %d, rank %d, bytes %lld)", world, rank, (long long) bytes);
+        return B200_ERR_INVALID;
+    }
+    pg_args a;
+    a.local = static_cast<const uint4 *>(local); a.n16 = bytes/16; a.state = static_cast<uint32_t *>(state); a.rank = rank; a.world = world; a.slot = slot;
+    for (int p = 0; p < world; ++p) {
+        a.peer_buf[p] = static_cast<char *>(peer_bufs[p]); a.peer_flag[p] = static_cast<uint32_t *>(peer_flags[p]);
+        if (!a.peer_buf[p] || !a.peer_flag[p] || (((uintptr_t) a.peer_buf[p]) & 15)) { set_error("peer_publish: peer %d not mapped", p); return B200_ERR_INVALID; }
+    }
+    int64_t gx = (a.n16 + 256*4 - 1)/(256*4);                            // ~4 stores per thread
+    if (gx < 1) gx = 1;
+    if (gx > 16) gx = 16;                                                // 16 x world CTAs: latency-bound, not bandwidth-bound
+    launch_pdl(pg_publish_kernel, dim3((unsigned) gx, (unsigned) world), dim3(256), 0, stream, a);
+    count_launch();
+    return check_launch("peer_publish") ? B200_OK : B200_ERR_CUDA;
+}
+
+int launch_peer_wait(void *flags, void *state, int world, cudaStream_t stream) {
+    if (world < 1 || world > PG_MAX_WORLD || !flags || !state) { set_error("peer_wait: bad arguments"); return B200_ERR_INVALID; }
+    pg_wait_kernel<<<1, 32, 0, stream>>>(static_cast<uint32_t *>(flags), static_cast<uint32_t *>(state), world);
+    count_launch();
+    return check_launch("peer_wait") ? B200_OK : B200_ERR_CUDA;
+}
+
+} // namespace b200

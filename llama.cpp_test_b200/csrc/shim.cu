@@ -36,6 +36,9 @@ int    launch_block_copy(void *const *caches, int n_caches, int64_t block_bytes,
                          const int32_t *pairs, int64_t n_pairs, cudaStream_t stream);
 int    launch_kv_rows(bool scatter, void *const *caches, int n_caches, int64_t nb_token, int64_t row_bytes, int64_t n_cells,
                       const int32_t *slots, int64_t n_rows, void *staging, cudaStream_t stream);
+int    launch_peer_publish(const void *local, int64_t bytes, void *const *peer_bufs, void *const *peer_flags, void *state,
+                           int slot, int rank, int world, cudaStream_t stream);
+int    launch_peer_wait(void *flags, void *state, int world, cudaStream_t stream);
 bool   generic_supports(const b200_attn_desc &d);
 size_t generic_workspace(const b200_attn_desc &d);
 int    launch_attn_generic(const b200_attn_desc &d, cudaStream_t st);
@@ -180,6 +183,47 @@ B200_API int b200_kv_rows_scatter(void *const *caches, int32_t n_caches, int64_t
     if (n_caches < 0 || n_rows < 0 || (n_caches > 0 && !caches) || (n_rows > 0 && (!slots || !staging))) { set_error("kv_rows_scatter: bad arguments"); return B200_ERR_INVALID; }
     if (!have_device()) return B200_ERR_CUDA;
     return launch_kv_rows(true, caches, n_caches, nb_token, row_bytes, n_cells, slots, n_rows, const_cast<void *>(staging), static_cast<cudaStream_t>(stream));
+}
+
+B200_API void *b200_peer_alloc(size_t bytes) {
+    if (!have_device() || bytes == 0) return nullptr;
+    void *p = nullptr;
+    if (cudaMalloc(&p, bytes) != cudaSuccess || cudaMemset(p, 0, bytes) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) {
+        set_error("peer_alloc: %s", cudaGetErrorString(cudaGetLastError()));
+        return nullptr;
+    }
+    return p;
+}
+B200_API int b200_peer_free(void *p) { return (!p || cudaFree(p) == cudaSuccess) ? B200_OK : B200_ERR_CUDA; }
+B200_API int b200_peer_export(void *p, unsigned char handle[64]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    cudaIpcMemHandle_t h;
+    if (!p || !handle || cudaIpcGetMemHandle(&h, p) != cudaSuccess) { set_error("peer_export: %s", cudaGetErrorString(cudaGetLastError())); return B200_ERR_CUDA; }
+    memcpy(handle, &h, 64);
+    return B200_OK;
+}
+B200_API void *b200_peer_open(const unsigned char handle[64]) {
+    if (!have_device() || !handle) return nullptr;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    void *p = nullptr;
+    if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { set_error("peer_open: %s", cudaGetErrorString(cudaGetLastError())); return nullptr; }
+    return p;
+}
+B200_API int b200_peer_close(void *p) { return (!p || cudaIpcCloseMemHandle(p) == cudaSuccess) ? B200_OK : B200_ERR_CUDA; }
+B200_API int b200_peer_publish(const void *local, int64_t bytes, void *const *peer_bufs, void *const *peer_flags,
+                               void *state, int32_t slot, int32_t rank, int32_t world, void *stream) {
+    if (!local || !peer_bufs || !peer_flags || !state) { set_error("peer_publish: bad arguments"); return B200_ERR_INVALID; }
+    if (!have_device()) return B200_ERR_CUDA;
+    return launch_peer_publish(local, bytes, peer_bufs, peer_flags, state, slot, rank, world, static_cast<cudaStream_t>(stream));
+}
+B200_API int b200_peer_wait(void *flags, void *state, int32_t world, void *stream) {
+    if (!have_device()) return B200_ERR_CUDA;
+    return launch_peer_wait(flags, state, world, static_cast<cudaStream_t>(stream));
+}
+B200_API int b200_peer_read_state(const void *state, uint32_t out[4]) {
+    if (!state || !out || !have_device()) return B200_ERR_INVALID;
+    return cudaMemcpy(out, state, 16, cudaMemcpyDeviceToHost) == cudaSuccess ? B200_OK : B200_ERR_CUDA;
 }
 
 } // extern "C"

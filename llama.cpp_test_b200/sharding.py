@@ -8,8 +8,10 @@ two partitionings and no collective inside attention:
                                manager and caches; no data-path collective at all.
   B. KV-head sharding          (70B-class GQA)  rank g holds kv heads [g*Hkv/G, (g+1)*Hkv/G) of EVERY block and
                                computes the query heads that map to them; block table / seq_lens are replicated;
-                               one all-gather of the F32 outputs afterwards (the reference has no counterpart:
-                               its multi-GPU path is cudaMemcpyPeerAsync row splits, ggml-cuda.cu:598,1592).
+                               one exchange of the F32 outputs afterwards (the reference has no counterpart:
+                               its multi-GPU path is cudaMemcpyPeerAsync row splits, ggml-cuda.cu:598,1592):
+                               PeerGather pushes the slices over NVLink peer memory with the library's own
+                               kernels (csrc/peer_gather.cu); gather_head_outputs is the NCCL/gloo form.
 
 Nothing here does arithmetic on K/V; torch.distributed is plumbing.
 """
@@ -17,7 +19,7 @@ from __future__ import annotations
 
 from dataclasses import dataclass
 
-__all__ = ["shard_sequences", "HeadShard", "head_shard", "gather_head_outputs", "merge_gathered"]
+__all__ = ["shard_sequences", "HeadShard", "head_shard", "gather_head_outputs", "merge_gathered", "PeerGather"]
 
 
 def shard_sequences(ctx_lens, world: int) -> list[list[int]]:
@@ -80,3 +82,121 @@ def merge_gathered(gathered):
     attention output — the wo matmul — can equally read the permuted view)."""
     g, n_q, hpg, d = gathered.shape
     return gathered.permute(1, 0, 2, 3).reshape(n_q, g * hpg, d)
+
+
+class _DevArray:
+    """raw device memory presented through __cuda_array_interface__ so torch can alias it without a copy"""
+
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+class PeerGather:
+    """The exchange step of partition B over NVLink peer memory (csrc/peer_gather.cu): every rank pushes its output
+    slice into every peer's gathered buffer with plain stores through CUDA-IPC-mapped pointers and raises an epoch
+    flag; `wait` spins on the local flags.  torch.distributed is used once, to exchange the 64-byte IPC handles.
+
+        pg = PeerGather(local_shape, n_slots)        # e.g. (n_q, n_head/G, d), F32; one slot per layer
+        pg.publish(local_out, slot); pg.wait()       # on the current stream; CUDA-graph capturable
+        pg.gathered(slot)                            # [G, n_q, n_head/G, d] view, valid after that wait
+    Two consecutive exchanges must use different slots (a fast rank may already be pushing exchange e+1 while a slow
+    one still reads the slot of exchange e).
+    """
+
+    def __init__(self, local_shape, n_slots: int = 2, group=None):
+        import ctypes as C
+        import torch
+        import torch.distributed as dist
+        from . import lib
+        self._lib, self._C, self._torch = lib, C, torch
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.shape = tuple(int(x) for x in local_shape)
+        n = 1
+        for x in self.shape:
+            n *= x
+        self.bytes = n*4
+        if self.bytes % 16:
+            raise ValueError("slice size must be a multiple of 16 bytes")
+        if n_slots < 2:
+            raise ValueError("n_slots must be at least 2")
+        self.n_slots = n_slots
+        self._buf = lib.b200_peer_alloc(n_slots*self.world*self.bytes)
+        self._flags = lib.b200_peer_alloc(64*4)
+        self._state = lib.b200_peer_alloc(16)
+        if not (self._buf and self._flags and self._state):
+            raise RuntimeError("b200_peer_alloc failed: " + lib.b200_last_error().decode(errors="replace"))
+        hb, hf = C.create_string_buffer(64), C.create_string_buffer(64)
+        if lib.b200_peer_export(self._buf, hb) or lib.b200_peer_export(self._flags, hf):
+            raise RuntimeError("b200_peer_export failed: " + lib.b200_last_error().decode(errors="replace"))
+        handles = [None]*self.world
+        dist.all_gather_object(handles, (hb.raw, hf.raw), group=group)          # plumbing: 128 bytes per rank, once
+        self._peer_buf, self._peer_flag, self._opened = (C.c_void_p*self.world)(), (C.c_void_p*self.world)(), []
+        for r, (b, f) in enumerate(handles):
+            if r == self.rank:
+                self._peer_buf[r], self._peer_flag[r] = self._buf, self._flags
+            else:
+                pb, pf = lib.b200_peer_open(b), lib.b200_peer_open(f)
+                if not (pb and pf):
+                    raise RuntimeError(f"b200_peer_open(rank {r}) failed: " + lib.b200_last_error().decode(errors="replace"))
+                self._peer_buf[r], self._peer_flag[r] = pb, pf
+                self._opened += [pb, pf]
+        self._all = torch.as_tensor(_DevArray(self._buf, (n_slots, self.world) + self.shape, "<f4"), device="cuda")
+        self.epoch = 0                       # host mirror of the device epoch (publishes issued so far), for check()
+        self._last_slot = -1
+        dist.barrier(group=group)                                               # nobody publishes into an unmapped peer
+
+    def publish(self, local_out, slot: int, stream=None):
+        st = self._torch.cuda.current_stream().cuda_stream if stream is None else stream
+        if tuple(local_out.shape) != self.shape or not local_out.is_contiguous():
+            raise ValueError("local_out must be contiguous with the shape given at construction")
+        if not 0 <= slot < self.n_slots or slot == self._last_slot:
+            raise ValueError("slot out of range, or the same slot as the previous exchange")
+        self._last_slot = slot
+        rc = self._lib.b200_peer_publish(local_out.data_ptr(), self.bytes, self._peer_buf, self._peer_flag, self._state,
+                                         slot, self.rank, self.world, self._C.c_void_p(st))
+        if rc:
+            raise RuntimeError("b200_peer_publish: " + self._lib.b200_last_error().decode(errors="replace"))
+        self.epoch += 1
+
+    def note_replay(self, n_publishes: int):
+        """a captured CUDA graph holding n_publishes publish launches was replayed: keep the host epoch in step"""
+        self.epoch += n_publishes
+
+    def wait(self, stream=None):
+        st = self._torch.cuda.current_stream().cuda_stream if stream is None else stream
+        rc = self._lib.b200_peer_wait(self._flags, self._state, self.world, self._C.c_void_p(st))
+        if rc:
+            raise RuntimeError("b200_peer_wait: " + self._lib.b200_last_error().decode(errors="replace"))
+
+    def state(self):
+        """(epoch, ctas_done, wait_error, _) after a device synchronise"""
+        out = (self._C.c_uint32*4)()
+        self._lib.b200_peer_read_state(self._state, out)
+        return tuple(out)
+
+    def gathered(self, slot: int):
+        """[G, *local_shape] view of a slot (valid in stream order after the wait of the exchange that filled it)"""
+        return self._all[slot]
+
+    def all_slots(self):
+        """[n_slots, G, *local_shape] view of every slot"""
+        return self._all
+
+    def check(self):
+        """synchronise and verify the device epoch matches the host's and no wait timed out"""
+        self._torch.cuda.synchronize()
+        epoch, _, err, _ = self.state()
+        if err:
+            raise RuntimeError(f"peer wait timed out on rank {err - 1}'s flag")
+        if epoch != self.epoch:
+            raise RuntimeError(f"device epoch {epoch} != host epoch {self.epoch} (graph replays not reported with note_replay?)")
+
+    def close(self):
+        for p in self._opened:
+            self._lib.b200_peer_close(p)
+        self._opened = []
+        for p in (self._buf, self._flags, self._state):
+            if p:
+                self._lib.b200_peer_free(p)
+        self._buf = self._flags = self._state = None
+        self._all = None
