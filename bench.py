@@ -50,6 +50,11 @@ WORKLOADS = {
                     scaling="weak", kv_type="f16", steps=20),
     "config4": dict(n_head=64, n_head_kv=8, n_layer=8, n_seqs=32, ctx="32768", shard="heads", scaling="strong",
                     kv_type="f16", steps=50),
+    # diagnostics, not bench lines: what ONE rank of config 4 computes at G = 8 / G = 4, without any exchange
+    "config4_shard8": dict(n_head=8, n_head_kv=1, n_layer=8, n_seqs=32, ctx="32768", shard="sequences", scaling="weak",
+                           kv_type="f16", steps=50),
+    "config4_shard4": dict(n_head=16, n_head_kv=2, n_layer=8, n_seqs=32, ctx="32768", shard="sequences", scaling="weak",
+                           kv_type="f16", steps=50),
 }
 
 
@@ -206,6 +211,7 @@ def main():
     ap.add_argument("--kernel", type=int, default=0, help="0 auto, 1 generic, 2 stream-K")
     ap.add_argument("--layers", type=int, default=0)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--plan-per-layer", action="store_true", help="A/B: every layer recomputes the schedule (no B200_ATTN_REUSE_PLAN)")
     ap.add_argument("--exchange", choices=["peer", "nccl"], default="peer",
                     help="config4 at N>1: output exchange through the library's own NVLink peer-memory kernels (default) or NCCL all-gather")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -264,8 +270,15 @@ def main():
     q_d = torch.rand((n_layer, n_seqs, n_head, D), generator=gen, device="cuda") * 2 - 1
     out_d = torch.empty_like(q_d)
     gathered = torch.empty((n_layer, world, n_seqs, n_head, D), device="cuda") if collective else None
-    calls = [pkg.AttnCall(q_d[l], kcs[l], vcs[l], lay, out_d[l], scale, block_table=bt_d, seq_lens=sl_d,
-                          max_seq_len=int(lens.max()), total_tokens=total, kernel=args.kernel) for l in range(n_layer)]
+    # the layers of a step share seq_lens / block table, hence the device-side schedule: one workspace, layer 0 plans,
+    # layers 1.. reuse it (B200_ATTN_REUSE_PLAN; b200_decode_step works that out itself, separate calls say so)
+    calls = []
+    for l in range(n_layer):
+        share = not args.plan_per_layer and l > 0
+        calls.append(pkg.AttnCall(q_d[l], kcs[l], vcs[l], lay, out_d[l], scale, block_table=bt_d, seq_lens=sl_d,
+                                  max_seq_len=int(lens.max()), total_tokens=total, kernel=args.kernel,
+                                  workspace=calls[0].workspace if share else None, reuse_plan=share and collective))
+    step_all = None if collective else pkg.StepCall(calls)
     torch.cuda.synchronize()
 
     peer = None
@@ -285,6 +298,8 @@ def main():
             pkg.gather_head_outputs(out_d[l], gathered[l])
 
     def step_resident():
+        if step_all is not None:
+            return step_all.run()                            # one b200_decode_step call over all layers
         for l in range(n_layer):
             layer_op(l)
 
@@ -410,6 +425,8 @@ def main():
         cfg.update({"n_layer": n_layer, "n_head_per_gpu": n_head, "n_head_kv_per_gpu": n_head_kv,
                     "kv_bytes_per_step_per_gpu": bytes_step_rank, "cuda_graph": graph is not None, "kernel": which,
                     "l2_flush": f"inputs (per-layer KV caches, {bytes_step_rank / 1e9:.1f} GB per step per GPU) are far larger than the 126 MB L2"})
+        cfg["schedule"] = ("every layer plans" if args.plan_per_layer else
+                           "layer 0 plans on the device, layers 1.. reuse it (B200_ATTN_REUSE_PLAN: same seq_lens within a step)")
         if collective:
             cfg["exchange"] = ("NVLink peer-memory push + epoch flags (b200_peer_publish / b200_peer_wait), verified equal to NCCL all_gather"
                                if peer is not None else "NCCL all_gather_into_tensor")

@@ -81,8 +81,18 @@ typedef struct b200_attn_desc {
 
     void   *workspace; size_t workspace_bytes;        /* device scratch, see b200_paged_attention_workspace */
     int32_t kernel;                                   /* B200_KERNEL_* */
-    int32_t reserved;
+    int32_t flags;                                    /* B200_ATTN_* */
 } b200_attn_desc;
+
+/*
+ * B200_ATTN_REUSE_PLAN: the device-side schedule (tile counts / prefix sums / row tiles, computed from seq_lens,
+ * q_seq, q_pos by a one-CTA plan kernel) of the PREVIOUS attention call on this stream with this workspace is still
+ * valid — same n_q, head counts, kernel, and unchanged seq_lens / q_seq / q_pos contents — so the plan launch is
+ * skipped.  That is the situation of layers 1..L-1 of one decode/prefill step (the reference rebuilds nothing per
+ * layer either: one mask per graph, src/llama-graph.cpp:403-477).  b200_decode_step sets it by itself where the
+ * descriptors of consecutive layers differ only in q / k / v / dst.  Kernels without a plan ignore it.
+ */
+enum { B200_ATTN_REUSE_PLAN = 1 };
 
 B200_API size_t b200_paged_attention_workspace(const b200_attn_desc *d);
 B200_API int    b200_paged_attention(const b200_attn_desc *d, void *stream);

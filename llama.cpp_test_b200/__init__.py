@@ -48,7 +48,7 @@ class AttnDesc(C.Structure):
         ("q_seq", C.c_void_p), ("q_pos", C.c_void_p),
         ("max_seq_len", C.c_int64), ("total_tokens", C.c_int64),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
-        ("kernel", C.c_int32), ("reserved", C.c_int32),
+        ("kernel", C.c_int32), ("flags", C.c_int32),
     ]
 
 

@@ -852,9 +852,11 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st) {
     if (!sk_make_map(&tmK, d.type_k, d.k, d.nbk1, d.nbk2, d.n_head_kv, d.n_kv)) return B200_ERR_CUDA;
     if (!sk_make_map(&tmV, d.type_v, d.v, d.nbv1, d.nbv2, d.n_head_kv, d.n_kv)) return B200_ERR_CUDA;
 
-    launch_pdl(sk_plan_kernel, dim3(1), dim3(1024), 0, st, a);
-    count_launch();
-    if (!check_launch("sk_plan")) return B200_ERR_CUDA;
+    if (!(d.flags & B200_ATTN_REUSE_PLAN)) {                 // layers 1.. of a step run on layer 0's schedule
+        launch_pdl(sk_plan_kernel, dim3(1), dim3(1024), 0, st, a);
+        count_launch();
+        if (!check_launch("sk_plan")) return B200_ERR_CUDA;
+    }
     const int rc = sk_dispatch(d.type_k, d.type_v, [&](auto k, auto v) { return sk_launch<decltype(k)::value, decltype(v)::value>(a, tmK, tmV, st); });
     if (rc != B200_OK) return rc;
     count_launch();

@@ -154,11 +154,28 @@ B200_API int b200_kv_write(const b200_kv_write_desc *d, void *stream) {
     return launch_kv_write(*d, static_cast<cudaStream_t>(stream));
 }
 
+// two layers of one step: everything the schedule is computed from is the same, only the tensors differ
+static bool same_plan_inputs(const b200_attn_desc &x, const b200_attn_desc &y) {
+    return x.n_q == y.n_q && x.n_head == y.n_head && x.n_head_kv == y.n_head_kv && x.head_dim == y.head_dim
+        && x.type_k == y.type_k && x.type_v == y.type_v && x.n_kv == y.n_kv
+        && x.block_table != nullptr && x.block_table == y.block_table && x.bt_stride == y.bt_stride
+        && x.seq_lens == y.seq_lens && x.n_seqs == y.n_seqs && x.block_size == y.block_size && x.q_seq == y.q_seq && x.q_pos == y.q_pos
+        && x.max_seq_len == y.max_seq_len && x.total_tokens == y.total_tokens
+        && x.workspace == y.workspace && x.workspace_bytes == y.workspace_bytes && x.kernel == y.kernel;
+}
+
 B200_API int b200_decode_step(const b200_kv_write_desc *writes, const b200_attn_desc *attns, int32_t n_layers, void *stream) {
     if (n_layers < 0 || (n_layers > 0 && !attns)) { set_error("decode_step: bad arguments"); return B200_ERR_INVALID; }
     for (int32_t l = 0; l < n_layers; ++l) {
         if (writes) { const int rc = b200_kv_write(&writes[l], stream); if (rc != B200_OK) return rc; }
-        const int rc = b200_paged_attention(&attns[l], stream);
+        int rc;
+        if (l > 0 && !(attns[l].flags & B200_ATTN_REUSE_PLAN) && same_plan_inputs(attns[l - 1], attns[l])) {
+            b200_attn_desc d = attns[l];                  // the schedule of layer l-1 stands: skip the plan launch
+            d.flags |= B200_ATTN_REUSE_PLAN;
+            rc = b200_paged_attention(&d, stream);
+        } else {
+            rc = b200_paged_attention(&attns[l], stream);
+        }
         if (rc != B200_OK) return rc;
     }
     return B200_OK;

@@ -63,7 +63,11 @@ class AttnCall:
     def __init__(self, q, k_cache, v_cache, layout_k: KVLayout, out, scale: float, *, layout_v: KVLayout | None = None,
                  block_table=None, seq_lens=None, q_seq=None, q_pos=None, mask=None, n_kv: int | None = None,
                  max_seq_len: int = 0, total_tokens: int = 0, softcap: float = 0.0, max_bias: float = 0.0,
-                 kernel: int = KERNEL_AUTO):
+                 kernel: int = KERNEL_AUTO, workspace=None, reuse_plan: bool = False):
+        """workspace: a uint8 device tensor shared with other calls on the same stream (the layers of a step; big
+        enough for each) instead of a private one.  reuse_plan: B200_ATTN_REUSE_PLAN — the caller guarantees the
+        previous call on this stream with this workspace had the same n_q / heads / kernel and unchanged seq_lens /
+        q_seq / q_pos (b200_decode_step / StepCall works that out by itself)."""
         import torch
         layout_v = layout_v or layout_k
         assert q.dtype == torch.float32 and q.dim() == 3 and q.is_contiguous()
@@ -89,9 +93,15 @@ class AttnCall:
             assert mask.dtype == torch.float16 and mask.dim() == 2 and mask.stride(1) == 1
             desc.mask, desc.nb_mask1 = mask.data_ptr(), mask.stride(0) * 2
         desc.kernel = kernel
+        desc.flags = 1 if reuse_plan else 0
         self.desc = desc
         ws = lib.b200_paged_attention_workspace(C.byref(desc))
-        self.workspace = torch.empty(max(ws, 16), dtype=torch.uint8, device=q.device)
+        if workspace is not None:
+            if workspace.numel() < ws:
+                raise ValueError(f"shared workspace of {workspace.numel()} bytes is smaller than the {ws} this call needs")
+            self.workspace = workspace
+        else:
+            self.workspace = torch.empty(max(ws, 16), dtype=torch.uint8, device=q.device)
         desc.workspace, desc.workspace_bytes = self.workspace.data_ptr(), self.workspace.numel()
         self._keep = (q, k_cache, v_cache, out, block_table, seq_lens, q_seq, q_pos, mask)
 

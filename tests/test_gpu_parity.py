@@ -317,3 +317,48 @@ def test_full_size_properties_config2(pkg, oracle, cuda, t):
     torch.cuda.synchronize()
     c = oracle.to_float(t, oracle.from_float(t, np.full((1, d), 0.5, dtype=np.float32)), d)[0, 0]
     assert np.abs(out.cpu().numpy() - c).max() <= 2e-3 * abs(c)
+
+
+# ---------------------------------------------------------------- the layers of a step share one schedule
+
+@pytest.mark.parametrize("t", [F16, Q8_0])
+def test_decode_step_reuses_the_plan_across_layers(pkg, oracle, cuda, t):
+    """b200_decode_step over L layers that share seq_lens / block table / workspace launches ONE plan kernel (layer 0)
+    and gives bit-identical results to L independent calls; an explicit B200_ATTN_REUSE_PLAN call does the same."""
+    import torch
+    L = 3
+    ws_ = [make_workload(oracle, [300, 17, 1000, 64], 32, 8, 128, t, seed=40 + l) for l in range(L)]
+    w0 = ws_[0]
+    lay = pkg.KVLayout(t, w0.n_head_kv, w0.d, w0.block_size, w0.n_blocks)
+    bt, sl = _dev(torch, w0.block_table), _dev(torch, w0.seq_lens)       # same lengths / tables for every layer
+    qs = [_dev(torch, w.q) for w in ws_]
+    kcs = [_dev(torch, w.k_cache.reshape(-1)) for w in ws_]
+    vcs = [_dev(torch, w.v_cache.reshape(-1)) for w in ws_]
+
+    def mk(l, out, **kw):
+        return pkg.AttnCall(qs[l], kcs[l], vcs[l], lay, out, w0.scale, block_table=bt, seq_lens=sl,
+                            max_seq_len=int(w0.seq_lens.max()), total_tokens=int(w0.seq_lens.sum()), kernel=2, **kw)
+
+    ref_out = [torch.full_like(qs[l], float("nan")) for l in range(L)]
+    n0 = pkg.lib.b200_launch_count()
+    for l in range(L):
+        mk(l, ref_out[l]).run()
+    assert pkg.lib.b200_launch_count() - n0 == 3*L                        # plan + main + combine each
+    out = [torch.full_like(qs[l], float("nan")) for l in range(L)]
+    first = mk(0, out[0])
+    calls = [first] + [mk(l, out[l], workspace=first.workspace) for l in range(1, L)]
+    n0 = pkg.lib.b200_launch_count()
+    pkg.StepCall(calls).run()
+    assert pkg.lib.b200_launch_count() - n0 == 1 + 2*L
+    out2 = [torch.full_like(qs[l], float("nan")) for l in range(L)]
+    first2 = mk(0, out2[0])
+    n0 = pkg.lib.b200_launch_count()
+    first2.run()
+    for l in range(1, L):
+        mk(l, out2[l], workspace=first2.workspace, reuse_plan=True).run()
+    assert pkg.lib.b200_launch_count() - n0 == 1 + 2*L
+    torch.cuda.synchronize()
+    for l in range(L):
+        assert torch.equal(out[l], ref_out[l]) and torch.equal(out2[l], ref_out[l])
+        want = oracle_attention(oracle, ws_[l])
+        assert oracle.max_rel_err(want, out[l].cpu().numpy()) <= TOL[t]
