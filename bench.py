@@ -50,6 +50,10 @@ WORKLOADS = {
                     scaling="weak", kv_type="f16", steps=20),
     "config4": dict(n_head=64, n_head_kv=8, n_layer=8, n_seqs=32, ctx="32768", shard="heads", scaling="strong",
                     kv_type="f16", steps=50),
+    # the attention share of config 5 (llama-batched-bench -npl 256 -fa -ctk q4_0 -ctv q4_0, 32 sequences per GPU at ~1k
+    # context): the model's matmuls are outside this path, so this is attention-only tok/s, not S_TG
+    "config5_attn": dict(n_head=32, n_head_kv=8, n_layer=32, n_seqs=32, ctx="1024", shard="sequences", scaling="weak",
+                         kv_type="q4_0", steps=300),
     # diagnostics, not bench lines: what ONE rank of config 4 computes at G = 8 / G = 4, without any exchange
     "config4_shard8": dict(n_head=8, n_head_kv=1, n_layer=8, n_seqs=32, ctx="32768", shard="sequences", scaling="weak",
                            kv_type="f16", steps=50),
