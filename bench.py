@@ -382,8 +382,19 @@ def main():
         s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
         # layers go through the C ABI in groups: one b200_decode_step call (kv_write + attention per layer) per group,
         # its inputs copied H2D on the copy stream while the previous group computes, its outputs D2H while the next does
-        GL = 1 if collective else 8
-        groups = [(a0, min(a0 + GL, n_layer)) for a0 in range(0, n_layer, GL)]
+        # group sizes ramp up and down (1,1,2,4,8,...,8,4,2,1,1): only the first group's H2D and the last group's D2H
+        # are exposed, everything else overlaps with compute
+        if collective:
+            sizes = [1]*n_layer
+        else:
+            ramp, sizes, left = [1, 1, 2, 4], [], n_layer
+            big = bytes_step_rank > 2e9                      # small steps are host-call bound: keep few groups
+            head = [r for r in ramp if (left := left - r) >= 0] if big and n_layer >= 2*sum(ramp) + 8 else []
+            mid = n_layer - 2*sum(head)
+            sizes = head + [8]*(mid // 8) + ([mid % 8] if mid % 8 else []) + head[::-1]
+        starts = np.cumsum([0] + sizes[:-1]).tolist()
+        groups = [(a0, a0 + n) for a0, n in zip(starts, sizes)]
+        assert groups[-1][1] == n_layer
         ev_in = [torch.cuda.Event() for _ in groups]
         ev_c = [torch.cuda.Event() for _ in groups]
         group_calls = None

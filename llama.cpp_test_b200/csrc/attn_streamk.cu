@@ -697,16 +697,30 @@ sk_combine_kernel(const __grid_constant__ sk_args a) {
     const int *FS = a.plan + 4 + (p.n_q + 1);
     const int s0 = FS[row], ns = FS[row + 1] - s0;
     if (ns == 1) return;                                              // written by the main kernel
+    // Latency matters here, not bandwidth (a row has up to ~40 segments and the whole kernel moves a few hundred KB):
+    // the segments' (m, l) are read lane-parallel, the rescale factors travel by shuffle, and the O partials of four
+    // segments are in flight at once.  (One dependent global load per segment per pass cost 9 us of a 20 us layer-op.)
+    const float2 *ML = reinterpret_cast<const float2 *>(a.part_ml) + (int64_t) s0*p.n_head + h;      // segment s at ML[s*n_head]
+    const float  *PO = a.part_o + ((int64_t) s0*p.n_head + h)*SK_D + 4*lane;                         // segment s at PO + s*n_head*SK_D
+    float M = -INFINITY;
+    for (int s = lane; s < ns; s += 32) M = fmaxf(M, ML[(int64_t) s*p.n_head].x);
+#pragma unroll
+    for (int o_ = 16; o_ > 0; o_ >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o_));
     float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
-    float M = -INFINITY, L = 0.f;
-    for (int s = 0; s < ns; ++s) M = fmaxf(M, a.part_ml[((int64_t) (s0 + s)*p.n_head + h)*2]);
-    for (int s = 0; s < ns; ++s) {
-        const float *ml = a.part_ml + ((int64_t) (s0 + s)*p.n_head + h)*2;
-        const float f = ex2(ml[0] - M);
-        const float4 v = *reinterpret_cast<const float4 *>(a.part_o + ((int64_t) (s0 + s)*p.n_head + h)*SK_D + 4*lane);
-        o.x = fmaf(v.x, f, o.x); o.y = fmaf(v.y, f, o.y); o.z = fmaf(v.z, f, o.z); o.w = fmaf(v.w, f, o.w);
-        L = fmaf(ml[1], f, L);
+    float L = 0.f;
+    for (int c = 0; c < ns; c += 32) {
+        float f = 0.f;
+        if (c + lane < ns) { const float2 ml = ML[(int64_t) (c + lane)*p.n_head]; f = ex2(ml.x - M); L = fmaf(ml.y, f, L); }
+        const int cnt = ns - c < 32 ? ns - c : 32;
+#pragma unroll 4
+        for (int j = 0; j < cnt; ++j) {
+            const float  fj = __shfl_sync(0xffffffffu, f, j);
+            const float4 v  = *reinterpret_cast<const float4 *>(PO + (int64_t) (c + j)*p.n_head*SK_D);
+            o.x = fmaf(v.x, fj, o.x); o.y = fmaf(v.y, fj, o.y); o.z = fmaf(v.z, fj, o.z); o.w = fmaf(v.w, fj, o.w);
+        }
     }
+#pragma unroll
+    for (int o_ = 16; o_ > 0; o_ >>= 1) L += __shfl_xor_sync(0xffffffffu, L, o_);
     const float inv = 1.0f/L;                                          // ns == 0: 0 * inf = NaN like the reference (ggml-cpu.c:12418)
     o.x *= inv; o.y *= inv; o.z *= inv; o.w *= inv;
     *reinterpret_cast<float4 *>(static_cast<float *>(p.dst) + ((int64_t) row*p.n_head + h)*SK_D + 4*lane) = o;
