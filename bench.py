@@ -57,6 +57,8 @@ WORKLOADS = {
     # diagnostics, not bench lines: what ONE rank of config 4 computes at G = 8 / G = 4, without any exchange
     "config4_shard8": dict(n_head=8, n_head_kv=1, n_layer=8, n_seqs=32, ctx="32768", shard="sequences", scaling="weak",
                            kv_type="f16", steps=50),
+    "config4_pair": dict(n_head=16, n_head_kv=2, n_layer=8, n_seqs=32, ctx="32768", shard="heads", scaling="strong",
+                         kv_type="f16", steps=50),          # N = 2: each rank computes what a rank of config 4 at G = 8 computes
     "config4_shard4": dict(n_head=16, n_head_kv=2, n_layer=8, n_seqs=32, ctx="32768", shard="sequences", scaling="weak",
                            kv_type="f16", steps=50),
 }
@@ -216,7 +218,7 @@ def main():
     ap.add_argument("--layers", type=int, default=0)
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--plan-per-layer", action="store_true", help="A/B: every layer recomputes the schedule (no B200_ATTN_REUSE_PLAN)")
-    ap.add_argument("--exchange", choices=["peer", "nccl"], default="peer",
+    ap.add_argument("--exchange", choices=["peer", "peer-flags", "nccl"], default="peer",
                     help="config4 at N>1: output exchange through the library's own NVLink peer-memory kernels (default) or NCCL all-gather")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the end-to-end leg")
@@ -286,10 +288,10 @@ def main():
     torch.cuda.synchronize()
 
     peer = None
-    if collective and args.exchange == "peer":
+    if collective and args.exchange != "nccl":
         peer = pkg.PeerGather((n_seqs, n_head, D), n_slots=max(2, n_layer) + 1)
         # once, before anything is timed: the peer-memory exchange delivers exactly what NCCL's all-gather delivers
-        calls[0].run(); peer.publish(out_d[0], max(2, n_layer)); peer.wait(); peer.check()
+        calls[0].run(); peer.exchange_ll(out_d[0], max(2, n_layer)); peer.check()
         ref_g = pkg.gather_head_outputs(out_d[0])
         if not torch.equal(peer.gathered(max(2, n_layer)), ref_g):
             raise SystemExit("peer-memory exchange differs from NCCL all_gather")
@@ -297,7 +299,7 @@ def main():
     def layer_op(l, keep=False):
         calls[l].run()
         if peer is not None:
-            peer.publish(out_d[l], l if n_layer > 1 else peer.epoch & 1); peer.wait()   # slot = layer: gathered(l) is that layer's exchanged output
+            (peer.exchange_ll if args.exchange == "peer" else peer.exchange)(out_d[l], l if n_layer > 1 else peer.epoch & 1)   # slot = layer: gathered(l) is that layer's exchanged output
         elif collective:
             pkg.gather_head_outputs(out_d[l], gathered[l])
 
@@ -443,7 +445,8 @@ def main():
         cfg["schedule"] = ("every layer plans" if args.plan_per_layer else
                            "layer 0 plans on the device, layers 1.. reuse it (B200_ATTN_REUSE_PLAN: same seq_lens within a step)")
         if collective:
-            cfg["exchange"] = ("NVLink peer-memory push + epoch flags (b200_peer_publish / b200_peer_wait), verified equal to NCCL all_gather"
+            cfg["exchange"] = (("NVLink peer-memory push, payload + epoch in the same 8-byte stores, one launch (b200_peer_exchange_ll)" if args.exchange == "peer"
+                                else "NVLink peer-memory push + epoch flags, one launch (b200_peer_exchange)") + ", verified equal to NCCL all_gather"
                                if peer is not None else "NCCL all_gather_into_tensor")
         line = {
             "metric": "paged-attn decode KV-read GB/s", "value": round(value, 2), "unit": "GB/s", "n_gpus": world,

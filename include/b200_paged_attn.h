@@ -162,6 +162,10 @@ B200_API int b200_decode_step(const b200_kv_write_desc *writes, const b200_attn_
  *                                flag_p[rank] = epoch (system-scope release); epoch = ++state[0] on the device.
  *                                Two consecutive exchanges must name different slots (e.g. slot = layer index).
  *   b200_peer_wait               wait until flags[r] >= state[0] for every r (bounded spin; on timeout state[2] != 0)
+ *   b200_peer_exchange           publish + wait in ONE launch (the CTA that raises the flags waits for the peers')
+ *   b200_peer_exchange_ll        lowest latency: every 8-byte store carries 4 payload bytes + the epoch (no fence, no
+ *                                separate flag); one launch pushes to every peer's LL buffer [n_slots][world][2*bytes]
+ *                                and unpacks what the peers pushed into the LOCAL gathered buffer
  * gathered buffers are [n_slots][world][bytes]; flags uint32 [world]; state uint32 [4], all from b200_peer_alloc.
  * peer_bufs / peer_flags are HOST arrays of `world` device pointers (entry `rank` = this process's own memory).
  * Both launches are CUDA-graph capturable.
@@ -174,6 +178,10 @@ B200_API int   b200_peer_close(void *p);
 B200_API int   b200_peer_publish(const void *local, int64_t bytes, void *const *peer_bufs, void *const *peer_flags,
                                  void *state, int32_t slot, int32_t rank, int32_t world, void *stream);
 B200_API int   b200_peer_wait(void *flags, void *state, int32_t world, void *stream);
+B200_API int   b200_peer_exchange(const void *local, int64_t bytes, void *const *peer_bufs, void *const *peer_flags,
+                                  void *state, int32_t slot, int32_t rank, int32_t world, void *stream);
+B200_API int   b200_peer_exchange_ll(const void *local, int64_t bytes, void *const *peer_ll, void *gathered, void *state,
+                                     int32_t slot, int32_t rank, int32_t world, void *stream);
 B200_API int   b200_peer_read_state(const void *state, uint32_t out[4]);   /* synchronous D2H of the 4 state words */
 
 /* diagnostics */

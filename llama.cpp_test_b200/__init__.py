@@ -87,7 +87,7 @@ EXPORTS = {
         "b200_paged_attention_workspace", "b200_paged_attention", "b200_supports_attention", "b200_kv_write",
         "b200_block_copy", "b200_kv_rows_gather", "b200_kv_rows_scatter", "b200_decode_step",
         "b200_peer_alloc", "b200_peer_free", "b200_peer_export", "b200_peer_open", "b200_peer_close", "b200_peer_publish",
-        "b200_peer_wait", "b200_peer_read_state", "b200_last_error", "b200_version", "b200_device_sm_count", "b200_launch_count"],
+        "b200_peer_wait", "b200_peer_exchange", "b200_peer_exchange_ll", "b200_peer_read_state", "b200_last_error", "b200_version", "b200_device_sm_count", "b200_launch_count"],
     "b200_ggml_abi.h": ["b200_flash_attn_ext_workspace", "b200_flash_attn_ext", "b200_cpy", "b200_supports_op"],
     "b200_host.h": [
         "b200_bm_create", "b200_bm_destroy", "b200_bm_allocate", "b200_bm_free", "b200_bm_evict", "b200_bm_status",
@@ -120,6 +120,10 @@ lib.b200_peer_open.argtypes = [C.c_char_p]
 lib.b200_peer_close.argtypes = [C.c_void_p]
 lib.b200_peer_publish.restype = C.c_int
 lib.b200_peer_publish.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+lib.b200_peer_exchange.restype = C.c_int
+lib.b200_peer_exchange.argtypes = lib.b200_peer_publish.argtypes
+lib.b200_peer_exchange_ll.restype = C.c_int
+lib.b200_peer_exchange_ll.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
 lib.b200_peer_wait.restype = C.c_int
 lib.b200_peer_wait.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]
 lib.b200_peer_read_state.restype = C.c_int

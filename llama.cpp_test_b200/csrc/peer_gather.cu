@@ -36,6 +36,9 @@ struct pg_args {
     int rank, world, slot;
 };
 
+// WAIT: the CTA that raises the flags also waits for the peers' flags, so publish + wait is ONE launch (a separate wait
+// kernel costs a full launch boundary, ~4 us of a ~100 us layer at G = 8)
+template <bool WAIT>
 __global__ void __launch_bounds__(256)
 pg_publish_kernel(const __grid_constant__ pg_args a) {
     // blockIdx.y = destination peer; blockIdx.x strides over the slice
@@ -44,17 +47,28 @@ pg_publish_kernel(const __grid_constant__ pg_args a) {
     const int p = blockIdx.y;
     uint4 *dst = reinterpret_cast<uint4 *>(a.peer_buf[p]) + ((int64_t) a.slot*a.world + a.rank)*a.n16;
     for (int64_t i = (int64_t) blockIdx.x*256 + threadIdx.x; i < a.n16; i += (int64_t) gridDim.x*256) dst[i] = a.local[i];
+    __shared__ int s_last;
     __threadfence_system();                                              // this thread's peer stores are visible system-wide ...
     __syncthreads();
-    if (threadIdx.x == 0) {
-        const uint32_t total = gridDim.x*gridDim.y;
-        if (atomicAdd(&a.state[1], 1u) == total - 1) {                   // ... before the last CTA of the grid raises the flags
-            __threadfence_system();
-            a.state[1] = 0;
-            for (int q = 0; q < a.world; ++q)
-                asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(a.peer_flag[q] + a.rank), "r"(epoch) : "memory");
-            a.state[0] = epoch;
-        }
+    if (threadIdx.x == 0) s_last = atomicAdd(&a.state[1], 1u) == gridDim.x*gridDim.y - 1;
+    __syncthreads();
+    if (!s_last) return;
+    // ... before the last CTA of the grid raises the flags: lane q tells peer q (fence + relaxed store = release; the
+    // eight remote stores go out in parallel instead of eight serial release stores)
+    if ((int) threadIdx.x < a.world) {
+        __threadfence_system();
+        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" :: "l"(a.peer_flag[threadIdx.x] + a.rank), "r"(epoch) : "memory");
+    }
+    if (threadIdx.x == 0) { a.state[1] = 0; a.state[0] = epoch; }
+    if (WAIT && (int) threadIdx.x < a.world) {                           // and waits for theirs
+        const uint32_t *flags = a.peer_flag[a.rank];
+        const long long t0 = clock64();
+        uint32_t v;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + threadIdx.x) : "memory");
+            if ((int32_t) (v - epoch) >= 0) break;
+            if (clock64() - t0 > 4000000000LL) { a.state[2] = 1 + threadIdx.x; break; }
+        } while (true);
     }
 }
 
@@ -73,7 +87,7 @@ pg_wait_kernel(uint32_t *flags, uint32_t *state, int world) {
 }
 
 int launch_peer_publish(const void *local, int64_t bytes, void *const *peer_bufs, void *const *peer_flags, void *state,
-                        int slot, int rank, int world, cudaStream_t stream) {
+                        int slot, int rank, int world, bool wait, cudaStream_t stream) {
     if (slot < 0 || world < 1 || world > PG_MAX_WORLD || rank < 0 || rank >= world || bytes <= 0 || (bytes & 15) || (((uintptr_t) local) & 15)) {
         set_error("peer_publish: bad arguments (world %d, rank %d, bytes %lld)", world, rank, (long long) bytes);
         return B200_ERR_INVALID;
@@ -87,9 +101,87 @@ int launch_peer_publish(const void *local, int64_t bytes, void *const *peer_bufs
     int64_t gx = (a.n16 + 256*4 - 1)/(256*4);                            // ~4 stores per thread
     if (gx < 1) gx = 1;
     if (gx > 16) gx = 16;                                                // 16 x world CTAs: latency-bound, not bandwidth-bound
-    launch_pdl(pg_publish_kernel, dim3((unsigned) gx, (unsigned) world), dim3(256), 0, stream, a);
+    if (wait) launch_pdl(pg_publish_kernel<true>,  dim3((unsigned) gx, (unsigned) world), dim3(256), 0, stream, a);
+    else      launch_pdl(pg_publish_kernel<false>, dim3((unsigned) gx, (unsigned) world), dim3(256), 0, stream, a);
     count_launch();
     return check_launch("peer_publish") ? B200_OK : B200_ERR_CUDA;
+}
+
+// ------------------------------------------------------------------------------------------------
+// low-latency form: every 8-byte store carries 4 bytes of payload and the epoch, so the receiver needs no separate
+// flag and the sender no fence — the latency is one NVLink flight plus a poll.  (8-byte aligned vector stores are
+// single transactions; the same property NCCL's LL protocol rests on.)  Twice the bytes on the wire, which for a
+// 128 KiB slice is still ~2 us.  One launch does both directions: push my slice to every peer's LL buffer, then
+// poll the peers' words in my LL buffer and unpack them into the gathered buffer (my own slice is copied directly).
+// ------------------------------------------------------------------------------------------------
+struct pg_ll_args {
+    const uint32_t *local;               // this rank's slice
+    int64_t n32;                         // slice size in 4-byte words
+    uint2    *peer_ll[PG_MAX_WORLD];     // peer p's LL buffer: [n_slots][world][n32] of (payload, epoch)
+    uint32_t *gathered;                  // local: [n_slots][world][n32]
+    uint32_t *state;                     // local: [0] epoch, [1] CTAs done, [2] wait error flag
+    int rank, world, slot;
+};
+
+__global__ void __launch_bounds__(256)
+pg_ll_kernel(const __grid_constant__ pg_ll_args a) {
+    pdl_prologue();
+    const uint32_t epoch = a.state[0] + 1;
+    const int64_t stride = (int64_t) gridDim.x*256, t = (int64_t) blockIdx.x*256 + threadIdx.x;
+    const int64_t slot_off = (int64_t) a.slot*a.world;
+    // push: word w of my slice -> LL_p[slot][rank][w] for every other rank p; my own copy goes straight to gathered
+    for (int64_t w = t; w < a.n32; w += stride) {
+        const uint32_t x = a.local[w];
+        a.gathered[(slot_off + a.rank)*a.n32 + w] = x;
+        for (int d = 1; d < a.world; ++d) {
+            const int p = (a.rank + d) % a.world;                        // stagger the destinations
+            asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" :: "l"(a.peer_ll[p] + (slot_off + a.rank)*a.n32 + w), "r"(x), "r"(epoch) : "memory");
+        }
+    }
+    // pull: poll the peers' words in my own LL buffer
+    const uint2 *mine = a.peer_ll[a.rank] + slot_off*a.n32;
+    const long long t0 = clock64();
+    bool dead = false;
+    for (int d = 1; d < a.world && !dead; ++d) {
+        const int r = (a.rank + d) % a.world;
+        for (int64_t w = t; w < a.n32; w += stride) {
+            uint32_t x, e;
+            do {
+                asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(x), "=r"(e) : "l"(mine + (int64_t) r*a.n32 + w) : "memory");
+                if (e == epoch) break;
+                if (clock64() - t0 > 4000000000LL) { a.state[2] = 1 + r; dead = true; break; }      // ~2 s: a peer died
+            } while (true);
+            if (dead) break;
+            a.gathered[(slot_off + r)*a.n32 + w] = x;
+        }
+    }
+    __shared__ int s_last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        s_last = atomicAdd(&a.state[1], 1u) == gridDim.x - 1;
+        if (s_last) { a.state[1] = 0; a.state[0] = epoch; }              // every CTA has read the old epoch by now
+    }
+}
+
+int launch_peer_exchange_ll(const void *local, int64_t bytes, void *const *peer_ll, void *gathered, void *state,
+                            int slot, int rank, int world, cudaStream_t stream) {
+    if (slot < 0 || world < 1 || world > PG_MAX_WORLD || rank < 0 || rank >= world || bytes <= 0 || (bytes & 15) || (((uintptr_t) local) & 3) || !gathered || !state) {
+        set_error("peer_exchange_ll: bad arguments (world %d, rank %d, bytes %lld)", world, rank, (long long) bytes);
+        return B200_ERR_INVALID;
+    }
+    pg_ll_args a;
+    a.local = static_cast<const uint32_t *>(local); a.n32 = bytes/4; a.gathered = static_cast<uint32_t *>(gathered);
+    a.state = static_cast<uint32_t *>(state); a.rank = rank; a.world = world; a.slot = slot;
+    for (int p = 0; p < world; ++p) {
+        a.peer_ll[p] = static_cast<uint2 *>(peer_ll[p]);
+        if (!a.peer_ll[p] || (((uintptr_t) a.peer_ll[p]) & 7)) { set_error("peer_exchange_ll: peer %d not mapped", p); return B200_ERR_INVALID; }
+    }
+    int64_t gx = (a.n32 + 256*4 - 1)/(256*4);                            // ~4 words per thread and direction
+    if (gx < 1) gx = 1;
+    if (gx > 128) gx = 128;                                              // all CTAs must be co-resident? no: nobody waits on a local CTA
+    launch_pdl(pg_ll_kernel, dim3((unsigned) gx), dim3(256), 0, stream, a);
+    count_launch();
+    return check_launch("peer_exchange_ll") ? B200_OK : B200_ERR_CUDA;
 }
 
 int launch_peer_wait(void *flags, void *state, int world, cudaStream_t stream) {

@@ -37,8 +37,10 @@ int    launch_block_copy(void *const *caches, int n_caches, int64_t block_bytes,
 int    launch_kv_rows(bool scatter, void *const *caches, int n_caches, int64_t nb_token, int64_t row_bytes, int64_t n_cells,
                       const int32_t *slots, int64_t n_rows, void *staging, cudaStream_t stream);
 int    launch_peer_publish(const void *local, int64_t bytes, void *const *peer_bufs, void *const *peer_flags, void *state,
-                           int slot, int rank, int world, cudaStream_t stream);
+                           int slot, int rank, int world, bool wait, cudaStream_t stream);
 int    launch_peer_wait(void *flags, void *state, int world, cudaStream_t stream);
+int    launch_peer_exchange_ll(const void *local, int64_t bytes, void *const *peer_ll, void *gathered, void *state,
+                               int slot, int rank, int world, cudaStream_t stream);
 bool   generic_supports(const b200_attn_desc &d);
 size_t generic_workspace(const b200_attn_desc &d);
 int    launch_attn_generic(const b200_attn_desc &d, cudaStream_t st);
@@ -232,7 +234,19 @@ B200_API int b200_peer_publish(const void *local, int64_t bytes, void *const *pe
                                void *state, int32_t slot, int32_t rank, int32_t world, void *stream) {
     if (!local || !peer_bufs || !peer_flags || !state) { set_error("peer_publish: bad arguments"); return B200_ERR_INVALID; }
     if (!have_device()) return B200_ERR_CUDA;
-    return launch_peer_publish(local, bytes, peer_bufs, peer_flags, state, slot, rank, world, static_cast<cudaStream_t>(stream));
+    return launch_peer_publish(local, bytes, peer_bufs, peer_flags, state, slot, rank, world, false, static_cast<cudaStream_t>(stream));
+}
+B200_API int b200_peer_exchange(const void *local, int64_t bytes, void *const *peer_bufs, void *const *peer_flags,
+                                void *state, int32_t slot, int32_t rank, int32_t world, void *stream) {
+    if (!local || !peer_bufs || !peer_flags || !state) { set_error("peer_exchange: bad arguments"); return B200_ERR_INVALID; }
+    if (!have_device()) return B200_ERR_CUDA;
+    return launch_peer_publish(local, bytes, peer_bufs, peer_flags, state, slot, rank, world, true, static_cast<cudaStream_t>(stream));
+}
+B200_API int b200_peer_exchange_ll(const void *local, int64_t bytes, void *const *peer_ll, void *gathered, void *state,
+                                   int32_t slot, int32_t rank, int32_t world, void *stream) {
+    if (!local || !peer_ll) { set_error("peer_exchange_ll: bad arguments"); return B200_ERR_INVALID; }
+    if (!have_device()) return B200_ERR_CUDA;
+    return launch_peer_exchange_ll(local, bytes, peer_ll, gathered, state, slot, rank, world, static_cast<cudaStream_t>(stream));
 }
 B200_API int b200_peer_wait(void *flags, void *state, int32_t world, void *stream) {
     if (!have_device()) return B200_ERR_CUDA;

@@ -123,39 +123,63 @@ class PeerGather:
         self._buf = lib.b200_peer_alloc(n_slots*self.world*self.bytes)
         self._flags = lib.b200_peer_alloc(64*4)
         self._state = lib.b200_peer_alloc(16)
-        if not (self._buf and self._flags and self._state):
+        self._ll = lib.b200_peer_alloc(n_slots*self.world*2*self.bytes)      # (payload, epoch) pairs, see exchange_ll
+        if not (self._buf and self._flags and self._state and self._ll):
             raise RuntimeError("b200_peer_alloc failed: " + lib.b200_last_error().decode(errors="replace"))
-        hb, hf = C.create_string_buffer(64), C.create_string_buffer(64)
-        if lib.b200_peer_export(self._buf, hb) or lib.b200_peer_export(self._flags, hf):
+        hb, hf, hl = C.create_string_buffer(64), C.create_string_buffer(64), C.create_string_buffer(64)
+        if lib.b200_peer_export(self._buf, hb) or lib.b200_peer_export(self._flags, hf) or lib.b200_peer_export(self._ll, hl):
             raise RuntimeError("b200_peer_export failed: " + lib.b200_last_error().decode(errors="replace"))
         handles = [None]*self.world
-        dist.all_gather_object(handles, (hb.raw, hf.raw), group=group)          # plumbing: 128 bytes per rank, once
-        self._peer_buf, self._peer_flag, self._opened = (C.c_void_p*self.world)(), (C.c_void_p*self.world)(), []
-        for r, (b, f) in enumerate(handles):
+        dist.all_gather_object(handles, (hb.raw, hf.raw, hl.raw), group=group)  # plumbing: 192 bytes per rank, once
+        self._peer_buf, self._peer_flag, self._peer_ll = (C.c_void_p*self.world)(), (C.c_void_p*self.world)(), (C.c_void_p*self.world)()
+        self._opened = []
+        for r, (b, f, l) in enumerate(handles):
             if r == self.rank:
-                self._peer_buf[r], self._peer_flag[r] = self._buf, self._flags
+                self._peer_buf[r], self._peer_flag[r], self._peer_ll[r] = self._buf, self._flags, self._ll
             else:
-                pb, pf = lib.b200_peer_open(b), lib.b200_peer_open(f)
-                if not (pb and pf):
+                pb, pf, pl = lib.b200_peer_open(b), lib.b200_peer_open(f), lib.b200_peer_open(l)
+                if not (pb and pf and pl):
                     raise RuntimeError(f"b200_peer_open(rank {r}) failed: " + lib.b200_last_error().decode(errors="replace"))
-                self._peer_buf[r], self._peer_flag[r] = pb, pf
-                self._opened += [pb, pf]
+                self._peer_buf[r], self._peer_flag[r], self._peer_ll[r] = pb, pf, pl
+                self._opened += [pb, pf, pl]
         self._all = torch.as_tensor(_DevArray(self._buf, (n_slots, self.world) + self.shape, "<f4"), device="cuda")
         self.epoch = 0                       # host mirror of the device epoch (publishes issued so far), for check()
         self._last_slot = -1
         dist.barrier(group=group)                                               # nobody publishes into an unmapped peer
 
-    def publish(self, local_out, slot: int, stream=None):
+    def exchange(self, local_out, slot: int, stream=None):
+        """publish + wait in one launch"""
+        self._push(self._lib.b200_peer_exchange, "b200_peer_exchange", local_out, slot, stream)
+
+    def exchange_ll(self, local_out, slot: int, stream=None):
+        """lowest latency: payload and epoch travel in the same 8-byte stores (no fence, no flag round trip); one
+        launch pushes to every peer and unpacks what the peers pushed into gathered(slot)"""
         st = self._torch.cuda.current_stream().cuda_stream if stream is None else stream
         if tuple(local_out.shape) != self.shape or not local_out.is_contiguous():
             raise ValueError("local_out must be contiguous with the shape given at construction")
         if not 0 <= slot < self.n_slots or slot == self._last_slot:
             raise ValueError("slot out of range, or the same slot as the previous exchange")
         self._last_slot = slot
-        rc = self._lib.b200_peer_publish(local_out.data_ptr(), self.bytes, self._peer_buf, self._peer_flag, self._state,
-                                         slot, self.rank, self.world, self._C.c_void_p(st))
+        rc = self._lib.b200_peer_exchange_ll(local_out.data_ptr(), self.bytes, self._peer_ll, self._buf, self._state,
+                                             slot, self.rank, self.world, self._C.c_void_p(st))
         if rc:
-            raise RuntimeError("b200_peer_publish: " + self._lib.b200_last_error().decode(errors="replace"))
+            raise RuntimeError("b200_peer_exchange_ll: " + self._lib.b200_last_error().decode(errors="replace"))
+        self.epoch += 1
+
+    def publish(self, local_out, slot: int, stream=None):
+        self._push(self._lib.b200_peer_publish, "b200_peer_publish", local_out, slot, stream)
+
+    def _push(self, fn, what, local_out, slot, stream):
+        st = self._torch.cuda.current_stream().cuda_stream if stream is None else stream
+        if tuple(local_out.shape) != self.shape or not local_out.is_contiguous():
+            raise ValueError("local_out must be contiguous with the shape given at construction")
+        if not 0 <= slot < self.n_slots or slot == self._last_slot:
+            raise ValueError("slot out of range, or the same slot as the previous exchange")
+        self._last_slot = slot
+        rc = fn(local_out.data_ptr(), self.bytes, self._peer_buf, self._peer_flag, self._state,
+                slot, self.rank, self.world, self._C.c_void_p(st))
+        if rc:
+            raise RuntimeError(what + ": " + self._lib.b200_last_error().decode(errors="replace"))
         self.epoch += 1
 
     def note_replay(self, n_publishes: int):
@@ -195,8 +219,8 @@ class PeerGather:
         for p in self._opened:
             self._lib.b200_peer_close(p)
         self._opened = []
-        for p in (self._buf, self._flags, self._state):
+        for p in (self._buf, self._flags, self._state, self._ll):
             if p:
                 self._lib.b200_peer_free(p)
-        self._buf = self._flags = self._state = None
+        self._buf = self._flags = self._state = self._ll = None
         self._all = None

@@ -28,9 +28,13 @@ def _worker(rank, world, port, out_dir):
         shape = (32, 8, 128)                                         # config 4 at G = 8: [n_seq, n_head/G, d]
         pg = pkg.PeerGather(shape, n_slots=3)
         gen = torch.Generator(device="cuda"); gen.manual_seed(100 + rank)
-        for it in range(7):                                          # eager, every slot, changing data
+        for it in range(7):                                          # eager, every slot, every form, changing data
             local = torch.rand(shape, device="cuda", generator=gen)
-            pg.publish(local, it % 3); pg.wait(); pg.check()
+            if it % 2:
+                pg.publish(local, it % 3); pg.wait()
+            else:
+                pg.exchange_ll(local, it % 3)
+            pg.check()
             want = pkg.gather_head_outputs(local)
             assert torch.equal(pg.gathered(it % 3), want), f"iteration {it}"
         with pytest.raises(ValueError):
@@ -42,7 +46,12 @@ def _worker(rank, world, port, out_dir):
 
         def step():
             for i in range(3):
-                pg.publish(locals_[i], (i + 1) % 3); pg.wait()
+                if i == 1:
+                    pg.publish(locals_[i], (i + 1) % 3); pg.wait()           # the two-launch form
+                elif i == 0:
+                    pg.exchange(locals_[i], (i + 1) % 3)                     # publish + wait in one launch
+                else:
+                    pg.exchange_ll(locals_[i], (i + 1) % 3)                  # payload + epoch in the same stores
                 outs[i].copy_(pg.gathered((i + 1) % 3))
         e0 = pg.epoch
         with torch.cuda.stream(side):
