@@ -10,8 +10,11 @@ python -c "import __graft_entry__ as g; g.smoke()" > $O/${TAG}_smoke.log 2>&1; t
 for T in q8_0 f16 q4_0; do
   python bench.py --kv-type $T > $O/${TAG}_bench_$T.log 2>&1; tail -c 600 $O/${TAG}_bench_$T.log; echo
 done
-for WL in config1 config3 config4; do
+for WL in config1 config3 config4 config5_attn; do
   python bench.py --workload $WL --no-cpu-baseline > $O/${TAG}_bench_$WL.log 2>&1; tail -c 400 $O/${TAG}_bench_$WL.log; echo
+done
+for T in f16 q8_0 q4_0; do   # prefill, un-capped short runs per cache type (quantised caches go through the F16 scratch)
+  python bench.py --workload config3 --kv-type $T --layers 8 --steps 10 --no-cpu-baseline > $O/${TAG}_bench_config3_${T}_8l.log 2>&1; tail -c 300 $O/${TAG}_bench_config3_${T}_8l.log; echo
 done
 python bench.py --impl reference --steps 3 --warmup 1 > $O/${TAG}_bench_reference.log 2>&1; tail -c 400 $O/${TAG}_bench_reference.log; echo
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches.csv \
