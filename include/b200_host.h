@@ -53,6 +53,20 @@ B200_API int64_t b200_pc_slots_of(const b200_paged_cache *pc, int32_t seq, int32
 B200_API int64_t b200_pc_defrag(b200_paged_cache *pc, int32_t *moves /* [cap][2] */, int64_t cap, int64_t max_moves);
 
 /*
+ * Context shift (reference callers: llama_kv_self_seq_rm(seq, p0, p1) then llama_kv_self_seq_add(seq, p1, -1, -(p1 - p0)),
+ * src/llama-kv-cache.cpp:173-242, :327-383): positions [p0, p1) of `seq` are dropped, the tokens behind them move down.
+ * On return run, in this order: b200_block_copy(cow_pairs), b200_kv_rows_gather(src cells) + b200_kv_rows_scatter(dst
+ * cells) over row_moves for K and V, b200_k_shift over shift_cells with shift[cell] = -(p1 - p0).
+ *   cow_pairs  [cow_cap][2] (src_block, dst_block)      row_moves [move_cap][2] (src_cell, dst_cell), position order
+ *   shift_cells [shift_cap] cells whose K rows need re-rotation      counts[3] receives {n_cow, n_moves, n_shift}
+ * Returns 0; -1 unknown sequence / bad interval; -2 not enough free blocks; -3 a capacity is too small (counts holds
+ * what is needed).  Nothing changes unless 0 is returned.
+ */
+B200_API int32_t b200_pc_context_shift(b200_paged_cache *pc, int32_t seq, int64_t p0, int64_t p1,
+                                       int32_t *cow_pairs, int64_t cow_cap, int32_t *row_moves, int64_t move_cap,
+                                       int32_t *shift_cells, int64_t shift_cap, int64_t counts[3]);
+
+/*
  * KV session state of ONE sequence in the reference's stream format (llama_kv_cache_unified::state_write / state_read
  * with seq_id >= 0 and flash-attention caches, src/llama-kv-cache.cpp:848-1240; users: llama_state_seq_get_data /
  * llama_state_seq_set_data, examples/save-load-state).  Rows are token-ordered: gather them from the blocks with

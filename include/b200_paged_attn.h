@@ -143,6 +143,36 @@ B200_API int b200_kv_rows_scatter(void *const *caches, int32_t n_caches, int64_t
                                   const int32_t *slots, int64_t n_rows, const void *staging, void *stream);
 
 /*
+ * K-shift: re-rotate cached K rows in place after their positions moved (context shift, llama_kv_self_seq_add /
+ * seq_div).  Replaces the graph llama_context::build_kv_self_shift builds (src/llama-context.cpp:524-571; per layer
+ * build_rope_shift :447-495: ggml_rope_ext_inplace on the F16 view [head_dim, n_head_kv, kv_size], and for a quantised
+ * cache ggml_cast -> F32, rope, ggml_cpy back) with ONE launch over all layers; arithmetic is
+ * ggml_compute_forward_rope_f32 / _f16 (ggml/src/ggml-cpu/ggml-cpu.c:10669-10853, :10855-11037; rope_yarn :10578-10593,
+ * ggml_rope_cache_init :10595-10611) and the quantisers of b200_kv_write.
+ *   caches        HOST array of n_caches device K bases (k_l[il]); cell c, head g at base + c*nb_token + g*nb_head
+ *   shift         DEVICE int32, indexed by CELL: the rope position of that cell = the delta its position moved by
+ *                 (llm_graph_input_k_shift::set_input, llama-context.cpp:507-520)
+ *   cells         DEVICE int32 [n_rows] cells to rotate, or NULL: every cell in [0, n_cells) (n_rows ignored), which
+ *                 is what the reference does (cells with shift 0 come back unchanged up to re-quantisation)
+ *   n_rot, mode   ggml_rope_ext's n_dims and mode: 0 = GGML_ROPE_TYPE_NORM (pairs 2i, 2i+1), 2 = NEOX (pairs i, i + n_rot/2)
+ *   freq_factors  DEVICE float [n_rot/2] or NULL (rope_freqs / long-short factors)
+ * Cells outside [0, n_cells) are skipped.  F32 / F16 / Q8_0 / Q4_0 caches; head_dim and n_rot even, n_rot <= head_dim,
+ * head_dim % 32 == 0 for the quantised types.
+ */
+typedef struct b200_k_shift_desc {
+    void *const *caches; int32_t n_caches;
+    int32_t type_k, n_head_kv, head_dim;
+    int64_t nb_token, nb_head, n_cells;
+    const int32_t *shift;
+    const int32_t *cells; int64_t n_rows;
+    int32_t n_rot, mode, n_ctx_orig;
+    float freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow;
+    const float *freq_factors;
+} b200_k_shift_desc;
+
+B200_API int b200_k_shift(const b200_k_shift_desc *d, void *stream);
+
+/*
  * One decode/prefill step over several layers in ONE call: for l in [0, n_layers): b200_kv_write(&writes[l]) (skipped
  * when writes == NULL) then b200_paged_attention(&attns[l]), all on `stream`.  This is the loop
  * llama_context::decode runs through ggml_backend_sched for the attention part of every layer

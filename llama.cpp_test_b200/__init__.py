@@ -65,6 +65,21 @@ class KVWriteDesc(C.Structure):
     ]
 
 
+class KShiftDesc(C.Structure):
+    """struct b200_k_shift_desc"""
+    _fields_ = [
+        ("caches", C.POINTER(C.c_void_p)), ("n_caches", C.c_int32),
+        ("type_k", C.c_int32), ("n_head_kv", C.c_int32), ("head_dim", C.c_int32),
+        ("nb_token", C.c_int64), ("nb_head", C.c_int64), ("n_cells", C.c_int64),
+        ("shift", C.c_void_p),
+        ("cells", C.c_void_p), ("n_rows", C.c_int64),
+        ("n_rot", C.c_int32), ("mode", C.c_int32), ("n_ctx_orig", C.c_int32),
+        ("freq_base", C.c_float), ("freq_scale", C.c_float), ("ext_factor", C.c_float), ("attn_factor", C.c_float),
+        ("beta_fast", C.c_float), ("beta_slow", C.c_float),
+        ("freq_factors", C.c_void_p),
+    ]
+
+
 class GgmlTensor(C.Structure):
     """struct b200_ggml_tensor == the reference's struct ggml_tensor (include/b200_ggml_abi.h)"""
     pass
@@ -85,7 +100,7 @@ GGML_OP_CPY, GGML_OP_FLASH_ATTN_EXT, GGML_TYPE_I32 = 32, 62, 26
 EXPORTS = {
     "b200_paged_attn.h": [
         "b200_paged_attention_workspace", "b200_paged_attention", "b200_supports_attention", "b200_kv_write",
-        "b200_block_copy", "b200_kv_rows_gather", "b200_kv_rows_scatter", "b200_decode_step",
+        "b200_block_copy", "b200_kv_rows_gather", "b200_kv_rows_scatter", "b200_k_shift", "b200_decode_step",
         "b200_peer_alloc", "b200_peer_free", "b200_peer_export", "b200_peer_open", "b200_peer_close", "b200_peer_publish",
         "b200_peer_wait", "b200_peer_exchange", "b200_peer_exchange_ll", "b200_peer_read_state", "b200_last_error", "b200_version", "b200_device_sm_count", "b200_launch_count"],
     "b200_ggml_abi.h": ["b200_flash_attn_ext_workspace", "b200_flash_attn_ext", "b200_cpy", "b200_supports_op"],
@@ -93,7 +108,7 @@ EXPORTS = {
         "b200_bm_create", "b200_bm_destroy", "b200_bm_allocate", "b200_bm_free", "b200_bm_evict", "b200_bm_status",
         "b200_fork_trace", "b200_pc_create", "b200_pc_destroy", "b200_pc_append", "b200_pc_seq_cp", "b200_pc_seq_rm",
         "b200_pc_seq_keep", "b200_pc_clear", "b200_pc_seq_len", "b200_pc_n_free", "b200_pc_ref_count", "b200_pc_export",
-        "b200_pc_slots_of", "b200_pc_defrag", "b200_pc_restore_seq", "b200_kv_state_seq_size", "b200_kv_state_seq_write",
+        "b200_pc_slots_of", "b200_pc_defrag", "b200_pc_restore_seq", "b200_pc_context_shift", "b200_kv_state_seq_size", "b200_kv_state_seq_write",
         "b200_kv_state_seq_parse"],
 }
 
@@ -111,6 +126,8 @@ lib.b200_kv_rows_gather.restype = C.c_int
 lib.b200_kv_rows_gather.argtypes = [C.POINTER(C.c_void_p), C.c_int32, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
 lib.b200_kv_rows_scatter.restype = C.c_int
 lib.b200_kv_rows_scatter.argtypes = lib.b200_kv_rows_gather.argtypes
+lib.b200_k_shift.restype = C.c_int
+lib.b200_k_shift.argtypes = [C.POINTER(KShiftDesc), C.c_void_p]
 lib.b200_peer_alloc.restype = C.c_void_p
 lib.b200_peer_alloc.argtypes = [C.c_size_t]
 lib.b200_peer_free.argtypes = [C.c_void_p]
@@ -179,6 +196,9 @@ lib.b200_pc_defrag.restype = C.c_int64
 lib.b200_pc_defrag.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_int64, C.c_int64]
 lib.b200_pc_restore_seq.restype = C.c_int64
 lib.b200_pc_restore_seq.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.POINTER(C.c_int32)]
+lib.b200_pc_context_shift.restype = C.c_int32
+lib.b200_pc_context_shift.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_int64, C.POINTER(C.c_int32), C.c_int64,
+                                      C.POINTER(C.c_int32), C.c_int64, C.POINTER(C.c_int32), C.c_int64, C.POINTER(C.c_int64)]
 lib.b200_kv_state_seq_size.restype = C.c_int64
 lib.b200_kv_state_seq_size.argtypes = [C.c_int64, C.c_int32, C.c_int64, C.c_int64]
 lib.b200_kv_state_seq_write.restype = C.c_int64

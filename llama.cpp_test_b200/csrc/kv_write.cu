@@ -254,4 +254,134 @@ int launch_kv_rows(bool scatter, void *const *caches, int n_caches, int64_t nb_t
     return B200_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// K-shift: cached K rows re-rotated in place after a position change (context shift / seq_add / seq_div).
+// One CTA per (cell, layer); the row is expanded to F32 in shared memory (the reference's ggml_cast of a
+// quantised cache, src/llama-context.cpp:469-471; FP16_TO_FP32 per element for F16, ggml-cpu.c:10955+), rotated
+// with the cos/sin table of its position (ggml_rope_cache_init, ggml-cpu.c:10595-10611: theta advances by repeated
+// multiplication, YaRN mix per rope_yarn :10578-10593), then written back through the KV-write path above (the
+// reference's ggml_cpy back into the cache, llama-context.cpp:487).  _rn intrinsics keep the reference's unfused
+// float sequence; cosf / sinf are CUDA's (<= 2 ulp from libm: results may differ in the last half ulp / one code).
+// ------------------------------------------------------------------------------------------------
+struct k_shift_args {
+    char *caches[BC_MAX_CACHES];
+    b200_k_shift_desc d;                     // .caches is a host pointer: not used on the device
+    float theta_scale, corr0, corr1, mscale; // powf(freq_base, -2/n_rot), ggml_rope_yarn_corr_dims, attn_factor [* YaRN magnitude]
+};
+
+template <int TYPE>
+__device__ __forceinline__ float k_shift_load(const char *head, int i) {
+    if constexpr (TYPE == B200_TYPE_F32)       return reinterpret_cast<const float *>(head)[i];
+    else if constexpr (TYPE == B200_TYPE_F16)  return __half2float(reinterpret_cast<const __half *>(head)[i]);
+    else if constexpr (TYPE == B200_TYPE_Q8_0) {       // dequantize_row_q8_0, ggml-quants.c:349-362
+        const char *blk = head + (i/QK)*Q8_BYTES;
+        return __fmul_rn((float) reinterpret_cast<const int8_t *>(blk + 2)[i % QK], __half2float(*reinterpret_cast<const __half *>(blk)));
+    } else {                                           // dequantize_row_q4_0, ggml-quants.c:255-273
+        const char *blk = head + (i/QK)*Q4_BYTES;
+        const int j = i % QK;
+        const int b = reinterpret_cast<const uint8_t *>(blk + 2)[j & 15];
+        const int q = (j < 16 ? (b & 0x0f) : (b >> 4)) - 8;
+        return __fmul_rn((float) q, __half2float(*reinterpret_cast<const __half *>(blk)));
+    }
+}
+
+template <int TYPE>
+__global__ void __launch_bounds__(KVW_THREADS)
+k_shift_kernel(const __grid_constant__ k_shift_args a) {
+    extern __shared__ __align__(16) char ks_smem[];
+    const b200_k_shift_desc &p = a.d;
+    const int hd = p.head_dim, row_elems = p.n_head_kv*hd, half_rot = p.n_rot/2;
+    float *x  = reinterpret_cast<float *>(ks_smem);
+    float *cs = x + row_elems;                                         // (cos, sin) per rotated pair
+    char  *stage = ks_smem + (((size_t) (row_elems + p.n_rot)*4 + 15) & ~(size_t) 15);
+    char  *cache = a.caches[blockIdx.y];
+    const bool neox = (p.mode & 2) != 0;
+    const int64_t n_rows = p.cells ? p.n_rows : p.n_cells;
+    for (int64_t r = blockIdx.x; r < n_rows; r += gridDim.x) {
+        const int64_t cell = p.cells ? (int64_t) p.cells[r] : r;
+        if (cell < 0 || cell >= p.n_cells) continue;                 // CTA-uniform
+        const float pos = (float) (int64_t) p.shift[cell];
+        for (int ic = threadIdx.x; ic < half_rot; ic += KVW_THREADS) {
+            float theta = pos;
+            for (int k = 0; k < ic; ++k) theta = __fmul_rn(theta, a.theta_scale);
+            const float ff = p.freq_factors ? p.freq_factors[ic] : 1.0f;
+            const float extrap = __fdiv_rn(theta, ff);
+            const float interp = __fmul_rn(p.freq_scale, extrap);
+            float th = interp;
+            if (p.ext_factor != 0.0f) {
+                const float y = __fdiv_rn(__fsub_rn((float) ic, a.corr0), fmaxf(0.001f, __fsub_rn(a.corr1, a.corr0)));
+                const float ramp_mix = __fmul_rn(__fsub_rn(1.0f, fminf(1.0f, fmaxf(0.0f, y))), p.ext_factor);
+                th = __fadd_rn(__fmul_rn(interp, __fsub_rn(1.0f, ramp_mix)), __fmul_rn(extrap, ramp_mix));
+            }
+            cs[2*ic]     = __fmul_rn(cosf(th), a.mscale);
+            cs[2*ic + 1] = __fmul_rn(sinf(th), a.mscale);
+        }
+        const char *row = cache + cell*p.nb_token;
+        for (int e = threadIdx.x; e < row_elems; e += KVW_THREADS) {
+            const int h = e/hd;
+            x[e] = k_shift_load<TYPE>(row + h*p.nb_head, e - h*hd);
+        }
+        __syncthreads();
+        for (int pr = threadIdx.x; pr < p.n_head_kv*half_rot; pr += KVW_THREADS) {
+            const int h = pr/half_rot, ic = pr - h*half_rot;
+            float *xh = x + h*hd;
+            const int i0 = neox ? ic : 2*ic, i1 = neox ? ic + half_rot : 2*ic + 1;
+            const float c = cs[2*ic], sn = cs[2*ic + 1], x0 = xh[i0], x1 = xh[i1];
+            xh[i0] = __fsub_rn(__fmul_rn(x0, c),  __fmul_rn(x1, sn));
+            xh[i1] = __fadd_rn(__fmul_rn(x0, sn), __fmul_rn(x1, c));
+        }
+        __syncthreads();
+        write_row<TYPE>(x, cache, cell, p.n_head_kv, hd, p.nb_token, p.nb_head, stage);
+        __syncthreads();
+    }
+}
+
+// ggml_rope_yarn_corr_dims, ggml/src/ggml.c:3735-3750 (host side, the same libm calls as the reference)
+static void k_shift_corr_dims(int n_dims, int n_ctx_orig, float freq_base, float beta_fast, float beta_slow, float dims[2]) {
+    const float pi = 3.14159265358979323846f;
+    auto corr_dim = [&](float n_rot) { return n_dims*logf(n_ctx_orig/(n_rot*2*pi))/(2*logf(freq_base)); };
+    const float start = floorf(corr_dim(beta_fast)), end = ceilf(corr_dim(beta_slow));
+    dims[0] = start > 0 ? start : 0;
+    dims[1] = end < n_dims - 1 ? end : (float) (n_dims - 1);
+}
+
+int launch_k_shift(const b200_k_shift_desc &d, cudaStream_t stream) {
+    const int64_t n_rows = d.cells ? d.n_rows : d.n_cells;
+    if (n_rows <= 0 || d.n_caches <= 0) return B200_OK;
+    const bool quant = d.type_k == B200_TYPE_Q8_0 || d.type_k == B200_TYPE_Q4_0;
+    if (!(quant || d.type_k == B200_TYPE_F16 || d.type_k == B200_TYPE_F32)) { set_error("k_shift: unsupported cache type %d", d.type_k); return B200_ERR_UNSUPPORTED; }
+    if (d.mode & ~2) { set_error("k_shift: rope mode %d (only NORM = 0 and NEOX = 2)", d.mode); return B200_ERR_UNSUPPORTED; }
+    if (!d.caches || !d.shift || d.n_head_kv <= 0 || d.head_dim <= 0 || (d.head_dim & 1) || d.n_rot <= 0 || (d.n_rot & 1) || d.n_rot > d.head_dim
+        || (quant && d.head_dim % QK)) {
+        set_error("k_shift: bad arguments (head_dim %d, n_rot %d)", d.head_dim, d.n_rot);
+        return B200_ERR_INVALID;
+    }
+    const int64_t row_elems = (int64_t) d.n_head_kv*d.head_dim;
+    const size_t smem = (((size_t) (row_elems + d.n_rot)*4 + 15) & ~(size_t) 15) + (size_t) row_bytes(d.type_k, row_elems);
+    if (smem > 48*1024) { set_error("k_shift: token row needs %zu bytes of shared memory (limit 48 KiB)", smem); return B200_ERR_UNSUPPORTED; }
+    k_shift_args a;
+    a.d = d;
+    a.theta_scale = powf(d.freq_base, -2.0f/d.n_rot);
+    float corr[2];
+    k_shift_corr_dims(d.n_rot, d.n_ctx_orig, d.freq_base, d.beta_fast, d.beta_slow, corr);
+    a.corr0 = corr[0]; a.corr1 = corr[1];
+    a.mscale = d.attn_factor;
+    if (d.ext_factor != 0.0f) a.mscale *= 1.0f + 0.1f*logf(1.0f/d.freq_scale);
+    const unsigned gx = (unsigned) (n_rows < 148*64 ? n_rows : 148*64);
+    for (int c0 = 0; c0 < d.n_caches; c0 += BC_MAX_CACHES) {
+        const int n = d.n_caches - c0 < BC_MAX_CACHES ? d.n_caches - c0 : BC_MAX_CACHES;
+        for (int i = 0; i < n; ++i) a.caches[i] = static_cast<char *>(d.caches[c0 + i]);
+        const dim3 grid(gx, (unsigned) n);
+        switch (d.type_k) {
+            case B200_TYPE_F32:  k_shift_kernel<B200_TYPE_F32 ><<<grid, KVW_THREADS, smem, stream>>>(a); break;
+            case B200_TYPE_F16:  k_shift_kernel<B200_TYPE_F16 ><<<grid, KVW_THREADS, smem, stream>>>(a); break;
+            case B200_TYPE_Q8_0: k_shift_kernel<B200_TYPE_Q8_0><<<grid, KVW_THREADS, smem, stream>>>(a); break;
+            default:             k_shift_kernel<B200_TYPE_Q4_0><<<grid, KVW_THREADS, smem, stream>>>(a); break;
+        }
+        count_launch();
+        if (!check_launch("k_shift")) return B200_ERR_CUDA;
+    }
+    return B200_OK;
+}
+
 } // namespace b200

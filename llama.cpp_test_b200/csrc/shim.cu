@@ -36,6 +36,7 @@ int    launch_block_copy(void *const *caches, int n_caches, int64_t block_bytes,
                          const int32_t *pairs, int64_t n_pairs, cudaStream_t stream);
 int    launch_kv_rows(bool scatter, void *const *caches, int n_caches, int64_t nb_token, int64_t row_bytes, int64_t n_cells,
                       const int32_t *slots, int64_t n_rows, void *staging, cudaStream_t stream);
+int    launch_k_shift(const b200_k_shift_desc &d, cudaStream_t stream);
 int    launch_peer_publish(const void *local, int64_t bytes, void *const *peer_bufs, void *const *peer_flags, void *state,
                            int slot, int rank, int world, bool wait, cudaStream_t stream);
 int    launch_peer_wait(void *flags, void *state, int world, cudaStream_t stream);
@@ -202,6 +203,13 @@ B200_API int b200_kv_rows_scatter(void *const *caches, int32_t n_caches, int64_t
     if (n_caches < 0 || n_rows < 0 || (n_caches > 0 && !caches) || (n_rows > 0 && (!slots || !staging))) { set_error("kv_rows_scatter: bad arguments"); return B200_ERR_INVALID; }
     if (!have_device()) return B200_ERR_CUDA;
     return launch_kv_rows(true, caches, n_caches, nb_token, row_bytes, n_cells, slots, n_rows, const_cast<void *>(staging), static_cast<cudaStream_t>(stream));
+}
+
+B200_API int b200_k_shift(const b200_k_shift_desc *d, void *stream) {
+    if (!d) { set_error("k_shift: null descriptor"); return B200_ERR_INVALID; }
+    if (d->n_caches < 0 || d->n_cells < 0 || (d->cells && d->n_rows < 0)) { set_error("k_shift: bad arguments"); return B200_ERR_INVALID; }
+    if (!have_device()) return B200_ERR_CUDA;
+    return launch_k_shift(*d, static_cast<cudaStream_t>(stream));
 }
 
 B200_API void *b200_peer_alloc(size_t bytes) {

@@ -5,11 +5,11 @@ from __future__ import annotations
 import ctypes as C
 from dataclasses import dataclass
 
-from . import (AttnDesc, B200Error, KVWriteDesc, KERNEL_AUTO, STATE_ERRORS, TYPE_F16, TYPE_F32, TYPE_Q4_0, TYPE_Q8_0,  # noqa: F401
+from . import (AttnDesc, B200Error, KShiftDesc, KVWriteDesc, KERNEL_AUTO, STATE_ERRORS, TYPE_F16, TYPE_F32, TYPE_Q4_0, TYPE_Q8_0,  # noqa: F401
                check, lib, row_bytes)
 
 __all__ = ["KVLayout", "AttnCall", "StepCall", "kv_write_desc", "paged_attention", "dense_attention", "kv_write", "block_copy",
-           "kv_rows_gather", "kv_rows_scatter", "state_seq_pack", "state_seq_unpack", "state_seq_save", "state_seq_load",
+           "kv_rows_gather", "kv_rows_scatter", "k_shift", "context_shift", "state_seq_pack", "state_seq_unpack", "state_seq_save", "state_seq_load",
            "BlockManager", "PagedKVCache", "current_stream"]
 
 
@@ -203,6 +203,57 @@ def kv_rows_scatter(caches, layout: KVLayout, slots, staging, stream: int | None
     _kv_rows(lib.b200_kv_rows_scatter, "b200_kv_rows_scatter", caches, layout, slots, staging, stream)
 
 
+def k_shift(k_caches, layout: KVLayout, shift, cells=None, *, n_rot: int | None = None, mode: int = 0, n_ctx_orig: int = 8192,
+            freq_base: float = 500000.0, freq_scale: float = 1.0, ext_factor: float = 0.0, attn_factor: float = 1.0,
+            beta_fast: float = 32.0, beta_slow: float = 1.0, freq_factors=None, stream: int | None = None) -> None:
+    """re-rotate K rows in place (the reference's K-shift graph, src/llama-context.cpp:524-571) for every layer in one
+    launch.  shift int32 device [n_cells] indexed by cell; cells int32 device list of cells to visit (None: all);
+    the rope parameters are ggml_rope_ext's (defaults: Llama-3)."""
+    d = KShiftDesc()
+    arr = (C.c_void_p * len(k_caches))(*[c.data_ptr() for c in k_caches])
+    d.caches, d.n_caches = arr, len(k_caches)
+    d.type_k, d.n_head_kv, d.head_dim = layout.type_id, layout.n_head_kv, layout.head_dim
+    d.nb_token, d.nb_head, d.n_cells = layout.token_bytes, layout.head_bytes, layout.n_cells
+    d.shift = _ptr(shift)
+    d.cells, d.n_rows = _ptr(cells), (0 if cells is None else cells.shape[0])
+    d.n_rot, d.mode, d.n_ctx_orig = (n_rot or layout.head_dim), mode, n_ctx_orig
+    d.freq_base, d.freq_scale, d.ext_factor, d.attn_factor = freq_base, freq_scale, ext_factor, attn_factor
+    d.beta_fast, d.beta_slow = beta_fast, beta_slow
+    d.freq_factors = _ptr(freq_factors)
+    check(lib.b200_k_shift(C.byref(d), C.c_void_p(current_stream() if stream is None else stream)), "b200_k_shift")
+
+
+def context_shift(cache: "PagedKVCache", seq: int, p0: int, p1: int, k_caches, v_caches, layout_k: KVLayout,
+                  layout_v: KVLayout | None = None, **rope) -> bool:
+    """llama_kv_self_seq_rm(seq, p0, p1) + llama_kv_self_seq_add(seq, p1, -1, p0 - p1) + the K-shift of the next
+    kv_self_update (src/llama-context.cpp:719-790) on the paged layout: block-table edit on the host, then at most four
+    launches (copy-on-write copies, row gather, row scatter, K rotation) over all layers.  False: refused, nothing changed."""
+    import torch
+    layout_v = layout_v or layout_k
+    plan = cache.context_shift(seq, p0, p1)
+    if plan is None:
+        return False
+    cow, moves, cells = plan
+    dev = k_caches[0].device
+    if cow:
+        pairs = torch.tensor(cow, dtype=torch.int32, device=dev)
+        block_copy(list(k_caches), layout_k.block_bytes, layout_k.n_blocks, pairs)
+        block_copy(list(v_caches), layout_v.block_bytes, layout_v.n_blocks, pairs)
+    if moves:
+        src = torch.tensor([m[0] for m in moves], dtype=torch.int32, device=dev)
+        dst = torch.tensor([m[1] for m in moves], dtype=torch.int32, device=dev)
+        for caches, lay in ((k_caches, layout_k), (v_caches, layout_v)):
+            st = torch.empty((len(caches), len(moves), lay.token_bytes), dtype=torch.uint8, device=dev)
+            kv_rows_gather(list(caches), lay, src, st)
+            kv_rows_scatter(list(caches), lay, dst, st)
+    if cells:
+        cl = torch.tensor(cells, dtype=torch.int32, device=dev)
+        shift = torch.zeros(layout_k.n_cells, dtype=torch.int32, device=dev)
+        shift[cl.long()] = p0 - p1
+        k_shift(list(k_caches), layout_k, shift, cl, **rope)
+    return True
+
+
 def state_seq_pack(k_rows, v_rows, type_k: int, type_v: int) -> bytes:
     """frame token-ordered rows (uint8 numpy [n_layer, n_cells, size_row]) as the reference's single-sequence KV stream
     (llama_kv_cache_unified::state_write, src/llama-kv-cache.cpp:848-971)"""
@@ -355,6 +406,22 @@ class PagedKVCache:
         buf = (C.c_int32 * (2 * cap))()
         n = lib.b200_pc_defrag(self._h, buf, cap, max_moves)
         return [(buf[2 * i], buf[2 * i + 1]) for i in range(max(n, 0))]
+
+    def context_shift(self, seq: int, p0: int, p1: int):
+        """drop positions [p0, p1) of `seq`, later tokens move down -> (cow_pairs, row_moves, shift_cells) or None when refused"""
+        counts = (C.c_int64 * 3)()
+        rc = lib.b200_pc_context_shift(self._h, seq, p0, p1, None, 0, None, 0, None, 0, counts)
+        if rc == 0:
+            return [], [], []
+        if rc != -3:
+            return None
+        nc, nm, ns = counts[0], counts[1], counts[2]
+        cow, mv, cells = (C.c_int32 * max(2 * nc, 1))(), (C.c_int32 * max(2 * nm, 1))(), (C.c_int32 * max(ns, 1))()
+        rc = lib.b200_pc_context_shift(self._h, seq, p0, p1, cow, nc, mv, nm, cells, ns, counts)
+        if rc != 0:
+            return None
+        return ([(cow[2 * i], cow[2 * i + 1]) for i in range(counts[0])], [(mv[2 * i], mv[2 * i + 1]) for i in range(counts[1])],
+                [cells[i] for i in range(counts[2])])
 
     def restore_seq(self, seq: int, n_cells: int):
         """drop `seq` and reserve n_cells tokens for it -> their cells, or None when the pool has no room"""

@@ -139,4 +139,27 @@ B200_API int64_t b200_pc_defrag(b200_paged_cache *pc, int32_t *moves, int64_t ca
     return n;
 }
 
+B200_API int32_t b200_pc_context_shift(b200_paged_cache *pc, int32_t seq, int64_t p0, int64_t p1,
+                                       int32_t *cow_pairs, int64_t cow_cap, int32_t *row_moves, int64_t move_cap,
+                                       int32_t *shift_cells, int64_t shift_cap, int64_t counts[3]) {
+    if (!pc || !counts) return -1;
+    PagedKVCache &c = pc->impl;
+    int64_t n_cow = 0, n_moves = 0, n_shift = 0;
+    if (!c.context_shift_sizes(seq, p0, p1, n_cow, n_moves, n_shift)) {
+        // tell "no room for the copy-on-write copies" from a bad request
+        return (c.has_seq(seq) && p0 >= 0 && p1 > p0 && p1 <= c.seq_len(seq)) ? -2 : -1;
+    }
+    counts[0] = n_cow; counts[1] = n_moves; counts[2] = n_shift;
+    if (n_cow > cow_cap || n_moves > move_cap || n_shift > shift_cap
+        || (n_cow > 0 && !cow_pairs) || (n_moves > 0 && !row_moves) || (n_shift > 0 && !shift_cells)) return -3;
+    std::vector<std::pair<int32_t, int32_t>> cow, mv;
+    std::vector<int32_t> cells;
+    if (!c.context_shift(seq, p0, p1, cow, mv, cells)) return -1;
+    for (size_t i = 0; i < cow.size(); ++i) { cow_pairs[2*i] = cow[i].first; cow_pairs[2*i + 1] = cow[i].second; }
+    for (size_t i = 0; i < mv.size(); ++i)  { row_moves[2*i] = mv[i].first;  row_moves[2*i + 1] = mv[i].second; }
+    for (size_t i = 0; i < cells.size(); ++i) shift_cells[i] = cells[i];
+    counts[0] = (int64_t) cow.size(); counts[1] = (int64_t) mv.size(); counts[2] = (int64_t) cells.size();
+    return 0;
+}
+
 } // extern "C"

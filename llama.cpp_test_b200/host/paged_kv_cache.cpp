@@ -90,6 +90,55 @@ bool PagedKVCache::seq_rm(seq_id seq, int64_t p0, int64_t p1) {
     return true;
 }
 
+bool PagedKVCache::context_shift_sizes(seq_id seq, int64_t p0, int64_t p1, int64_t & n_cow, int64_t & n_moves, int64_t & n_shift) const {
+    auto it = seqs_.find(seq);
+    if (it == seqs_.end()) return false;
+    const Seq & s = it->second;
+    if (p0 < 0 || p1 <= p0 || p1 > s.len) return false;
+    const int64_t nd = p1 - p0, new_len = s.len - nd, bs = block_size_;
+    const bool aligned = p0 % bs == 0 && nd % bs == 0;
+    n_shift = new_len - p0;
+    n_moves = aligned ? 0 : n_shift;
+    n_cow = 0;
+    if (n_shift > 0) {
+        // blocks that will be written: aligned -> the survivors behind the gap (old indices); else -> those covering [p0, new_len)
+        const int64_t b0 = aligned ? p1/bs : p0/bs, b1 = aligned ? (int64_t) s.blocks.size() : (new_len + bs - 1)/bs;
+        for (int64_t b = b0; b < b1; ++b) if (ref_[(size_t) s.blocks[(size_t) b]] > 1) ++n_cow;
+    }
+    return n_cow <= n_free_;
+}
+
+bool PagedKVCache::context_shift(seq_id seq, int64_t p0, int64_t p1, std::vector<std::pair<int32_t, int32_t>> & cow_pairs,
+                                 std::vector<std::pair<int32_t, int32_t>> & row_moves, std::vector<int32_t> & shift_cells) {
+    int64_t n_cow, n_moves, n_shift;
+    if (!context_shift_sizes(seq, p0, p1, n_cow, n_moves, n_shift)) return false;
+    Seq & s = seqs_[seq];
+    const int64_t nd = p1 - p0, new_len = s.len - nd, bs = block_size_;
+    const bool aligned = p0 % bs == 0 && nd % bs == 0;
+    auto cell_of = [&](const std::vector<int32_t> & blocks, int64_t p) { return (int32_t) ((int64_t) blocks[(size_t) (p/bs)]*bs + p % bs); };
+    auto cow = [&](int64_t b) {                                 // private copy of table entry b (allocated before anything is freed)
+        const int32_t old = s.blocks[(size_t) b];
+        if (ref_[(size_t) old] <= 1) return;
+        const int32_t nb = alloc_block();
+        cow_pairs.emplace_back(old, nb);
+        s.blocks[(size_t) b] = nb;
+        unref(old);
+    };
+    if (aligned) {
+        if (n_shift > 0) for (int64_t b = p1/bs; b < (int64_t) s.blocks.size(); ++b) cow(b);
+        for (int64_t b = p0/bs; b < p1/bs; ++b) unref(s.blocks[(size_t) b]);
+        s.blocks.erase(s.blocks.begin() + p0/bs, s.blocks.begin() + p1/bs);
+        s.len = new_len;
+    } else {
+        if (n_shift > 0) for (int64_t b = p0/bs; b < (new_len + bs - 1)/bs; ++b) cow(b);
+        for (int64_t q = p0; q < new_len; ++q) row_moves.emplace_back(cell_of(s.blocks, q + nd), cell_of(s.blocks, q));
+        release(s, new_len);
+    }
+    for (int64_t q = p0; q < new_len; ++q) shift_cells.push_back(cell_of(s.blocks, q));
+    if (s.len == 0) seqs_.erase(seq);
+    return true;
+}
+
 void PagedKVCache::seq_keep(seq_id seq) {
     std::vector<seq_id> ids;
     for (auto & kv : seqs_) if (kv.first != seq) ids.push_back(kv.first);

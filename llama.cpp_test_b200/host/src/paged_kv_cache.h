@@ -43,6 +43,22 @@ public:
     void seq_keep(seq_id seq);
     void clear();
 
+    // Context shift: the reference callers' pair llama_kv_self_seq_rm(seq, p0, p1) + llama_kv_self_seq_add(seq, p1, -1,
+    // -(p1 - p0)) (examples/main/main.cpp context shift; seq_rm src/llama-kv-cache.cpp:173-242, seq_add :327-383) as ONE
+    // operation on the block table: positions [p0, p1) are dropped and the tokens behind them move down by p1 - p0.
+    //   * p0 and p1 - p0 multiples of the block size: the dropped blocks leave the table, no row moves;
+    //   * otherwise the surviving rows move: row_moves gets (src_cell, dst_cell) pairs in position order — gather all
+    //     sources, then scatter (b200_kv_rows_gather / _scatter, K and V), after the copy-on-write copies;
+    //   * every block that gets written (row moves, K rotation) and is shared is copied first: cow_pairs (src, dst) for
+    //     b200_block_copy; its allocation happens before any block is freed, so no source is overwritten;
+    //   * shift_cells gets the cell of every token whose position changed, in position order: their K rows need the
+    //     rotation by -(p1 - p0) (b200_k_shift with shift[cell] = -(p1 - p0); the reference's cell delta, .h:31).
+    // Returns false (nothing changes) for an unknown sequence, an empty / out-of-range interval, or too few free blocks.
+    bool context_shift(seq_id seq, int64_t p0, int64_t p1, std::vector<std::pair<int32_t, int32_t>> & cow_pairs,
+                       std::vector<std::pair<int32_t, int32_t>> & row_moves, std::vector<int32_t> & shift_cells);
+    // upper bounds of what context_shift would append (for fixed-size callers); false when it would refuse
+    bool context_shift_sizes(seq_id seq, int64_t p0, int64_t p1, int64_t & n_cow, int64_t & n_moves, int64_t & n_shift) const;
+
     bool    has_seq(seq_id seq) const { return seqs_.count(seq) != 0; }
     int64_t seq_len(seq_id seq) const;                 // tokens cached (seq_pos_max + 1), 0 if absent
     int64_t n_seqs() const { return (int64_t) seqs_.size(); }

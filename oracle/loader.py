@@ -54,6 +54,8 @@ class Oracle:
                                    C.c_size_t, C.c_size_t, C.c_int64]
         L.orc_block_copy.argtypes = [C.c_void_p, C.c_size_t, C.c_int64, C.c_void_p, C.c_int64]
         L.orc_attention.argtypes = [C.POINTER(_AttnParams)]
+        L.orc_k_shift.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_size_t, C.c_int64, C.c_void_p, C.c_void_p,
+                                  C.c_int64, C.c_int, C.c_int, C.c_int] + [C.c_float]*6 + [C.c_void_p]
         L.orc_nmse.restype = C.c_double
         L.orc_nmse.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
         L.orc_max_rel_err.restype = C.c_double
@@ -88,6 +90,21 @@ class Oracle:
         rc = self.lib.orc_kv_write(_p(src), src.strides[0], src.shape[0], _p(sm), _p(cache), t, n_head_kv, head_dim,
                                    nb_token, nb_head, n_cells)
         assert rc == 0
+
+    def k_shift(self, cache, t, n_head_kv, head_dim, shift, cells=None, *, n_rot=None, mode=0, n_ctx_orig=8192,
+                freq_base=500000.0, freq_scale=1.0, ext_factor=0.0, attn_factor=1.0, beta_fast=32.0, beta_slow=1.0,
+                freq_factors=None):
+        """in place on a flat token-major cache (uint8 [n_cells * row_bytes])"""
+        assert cache.dtype == np.uint8 and cache.flags.c_contiguous
+        hb = row_bytes(t, head_dim)
+        n_cells = cache.size // (hb * n_head_kv)
+        sh = np.ascontiguousarray(shift, dtype=np.int32); assert sh.size == n_cells
+        cl = None if cells is None else np.ascontiguousarray(cells, dtype=np.int32)
+        ff = None if freq_factors is None else np.ascontiguousarray(freq_factors, dtype=np.float32)
+        rc = self.lib.orc_k_shift(_p(cache), t, n_head_kv, head_dim, hb * n_head_kv, hb, n_cells, _p(sh), _p(cl),
+                                  0 if cl is None else cl.size, n_rot or head_dim, mode, n_ctx_orig, freq_base, freq_scale,
+                                  ext_factor, attn_factor, beta_fast, beta_slow, _p(ff))
+        assert rc == 0, rc
 
     def block_copy(self, cache, block_bytes, n_blocks, pairs):
         pairs = np.ascontiguousarray(pairs, dtype=np.int32)
@@ -183,6 +200,8 @@ class Ref:
         L.ref_attention.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int,
                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float,
                                     C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double)]
+        L.ref_k_shift.argtypes = [C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_float]*6 \
+                                 + [C.c_void_p, C.c_int]
         self.n_threads = L.ref_n_threads_default()
 
     def features(self) -> str:
@@ -203,6 +222,17 @@ class Ref:
         out = np.empty((rows.shape[0], k), dtype=np.float32)
         assert self.lib.ref_to_float(t, _p(rows), _p(out), out.size) == 0
         return out.reshape(b.shape[:-1] + (k,))
+
+    def k_shift(self, cache, t, n_head_kv, head_dim, shift, *, n_rot=None, mode=0, n_ctx_orig=8192, freq_base=500000.0,
+                freq_scale=1.0, ext_factor=0.0, attn_factor=1.0, beta_fast=32.0, beta_slow=1.0, freq_factors=None, n_threads=2):
+        """the reference's K-shift graph (build_kv_self_shift) on the CPU backend, in place, every cell"""
+        assert cache.dtype == np.uint8 and cache.flags.c_contiguous
+        n_cells = cache.size // (row_bytes(t, head_dim) * n_head_kv)
+        sh = np.ascontiguousarray(shift, dtype=np.int32); assert sh.size == n_cells
+        ff = None if freq_factors is None else np.ascontiguousarray(freq_factors, dtype=np.float32)
+        rc = self.lib.ref_k_shift(t, _p(cache), n_cells, n_head_kv, head_dim, _p(sh), n_rot or head_dim, mode, n_ctx_orig,
+                                  freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow, _p(ff), n_threads)
+        assert rc == 0, rc
 
     def cpy_f32(self, t: int, src: np.ndarray, n_threads: int = 1) -> np.ndarray:
         src = np.ascontiguousarray(src, dtype=np.float32)

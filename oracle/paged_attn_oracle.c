@@ -74,6 +74,9 @@ void orc_fp32_to_fp16_row(const float *x, uint16_t *y, int64_t n) {
 /* ggml/src/ggml-common.h:161-166 block_q4_0 = {half d; uint8 qs[16]} (18 B / 32 elems)
  * ggml/src/ggml-common.h:203-208 block_q8_0 = {half d; int8  qs[32]} (34 B / 32 elems) */
 #define QK 32
+#ifndef M_PI
+#define M_PI 3.14159265358979323846
+#endif
 #define Q4_BYTES 18
 #define Q8_BYTES 34
 
@@ -220,6 +223,76 @@ int orc_block_copy(void *cache, size_t block_bytes, int64_t n_blocks,
         if (s == d) continue;
         memcpy((char *)cache + (size_t)d*block_bytes, (const char *)cache + (size_t)s*block_bytes, block_bytes);
     }
+    return 0;
+}
+
+/* ---------------------------------------------------------------- K-shift (rope on cached K rows) */
+
+/* ggml/src/ggml.c:3735-3750 */
+static float rope_yarn_corr_dim(int n_dims, int n_ctx_orig, float n_rot, float base) {
+    return n_dims * logf(n_ctx_orig / (n_rot * 2 * (float)M_PI)) / (2 * logf(base));
+}
+static void rope_yarn_corr_dims(int n_dims, int n_ctx_orig, float freq_base, float beta_fast, float beta_slow, float dims[2]) {
+    const float start = floorf(rope_yarn_corr_dim(n_dims, n_ctx_orig, beta_fast, freq_base));
+    const float end   =  ceilf(rope_yarn_corr_dim(n_dims, n_ctx_orig, beta_slow, freq_base));
+    dims[0] = start > 0 ? start : 0;
+    dims[1] = end < n_dims - 1 ? end : n_dims - 1;
+}
+
+/* ggml-cpu.c:10571-10611: cache[i0] = cos, cache[i0+1] = sin for the pair starting at i0 (forward: sin_sign = 1) */
+static void rope_cache_init(float theta_base, float freq_scale, const float *freq_factors, const float corr_dims[2],
+                            int64_t ne0, float ext_factor, float mscale0, float *cache, float theta_scale) {
+    float theta = theta_base;
+    for (int64_t i0 = 0; i0 < ne0; i0 += 2) {
+        const float ff = freq_factors ? freq_factors[i0/2] : 1.0f;
+        const float theta_extrap = theta/ff;
+        const float theta_interp = freq_scale * theta_extrap;
+        float th = theta_interp, mscale = mscale0;
+        if (ext_factor != 0.0f) {
+            const float hl = corr_dims[1] - corr_dims[0];
+            const float y = (i0 / 2 - corr_dims[0]) / (0.001f > hl ? 0.001f : hl);
+            const float cl = y < 0 ? 0 : y;
+            const float ramp_mix = (1 - (1 < cl ? 1 : cl)) * ext_factor;
+            th = theta_interp * (1 - ramp_mix) + theta_extrap * ramp_mix;
+            mscale *= 1.0f + 0.1f * logf(1.0f / freq_scale);
+        }
+        cache[i0 + 0] = cosf(th) * mscale;
+        cache[i0 + 1] = sinf(th) * mscale;
+        theta *= theta_scale;
+    }
+}
+
+int orc_k_shift(void *cache, int type, int n_head_kv, int head_dim, size_t nb_token, size_t nb_head, int64_t n_cells,
+                const int32_t *shift, const int32_t *cells, int64_t n_rows,
+                int n_rot, int mode, int n_ctx_orig, float freq_base, float freq_scale, float ext_factor,
+                float attn_factor, float beta_fast, float beta_slow, const float *freq_factors) {
+    if (orc_row_size(type, head_dim) == 0 || (mode & ~2) || n_rot <= 0 || (n_rot & 1) || n_rot > head_dim || (head_dim & 1)) return -1;
+    if ((type == ORC_TYPE_Q8_0 || type == ORC_TYPE_Q4_0) && head_dim % QK) return -1;
+    const float theta_scale = powf(freq_base, -2.0f/n_rot);                       /* ggml-cpu.c:10720 */
+    float corr_dims[2];
+    rope_yarn_corr_dims(n_rot, n_ctx_orig, freq_base, beta_fast, beta_slow, corr_dims);
+    const int neox = (mode & 2) != 0;
+    float *x = (float *)malloc(sizeof(float)*(size_t)head_dim), *cs = (float *)malloc(sizeof(float)*(size_t)head_dim);
+    if (!x || !cs) { free(x); free(cs); return -1; }
+    const int64_t n = cells ? n_rows : n_cells;
+    for (int64_t r = 0; r < n; ++r) {
+        const int64_t c = cells ? cells[r] : r;
+        if (c < 0 || c >= n_cells) continue;
+        rope_cache_init((float)(int64_t)shift[c], freq_scale, freq_factors, corr_dims, head_dim, ext_factor, attn_factor, cs, theta_scale);
+        for (int h = 0; h < n_head_kv; ++h) {
+            void *row = (char *)cache + (size_t)c*nb_token + (size_t)h*nb_head;
+            if (orc_to_float(type, row, x, head_dim)) { free(x); free(cs); return -1; }   /* ggml_cast / FP16_TO_FP32 */
+            for (int i0 = 0; i0 < n_rot; i0 += 2) {                                        /* ggml-cpu.c:10800-10830 */
+                const float cos_theta = cs[i0], sin_theta = cs[i0 + 1];
+                const int a = neox ? i0/2 : i0, b = neox ? i0/2 + n_rot/2 : i0 + 1;
+                const float x0 = x[a], x1 = x[b];
+                x[a] = x0*cos_theta - x1*sin_theta;
+                x[b] = x0*sin_theta + x1*cos_theta;
+            }
+            if (orc_from_float(type, x, row, head_dim)) { free(x); free(cs); return -1; }   /* ggml_cpy back / FP32_TO_FP16 */
+        }
+    }
+    free(x); free(cs);
     return 0;
 }
 

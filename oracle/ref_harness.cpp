@@ -190,4 +190,33 @@ int ref_attention(int mode, int n_q, int n_head, int n_head_kv, int d, int64_t n
     return 0;
 }
 
+// K-shift exactly as llama_context::build_kv_self_shift / build_rope_shift emit it (src/llama-context.cpp:524-571,
+// :447-495): view [head_dim, n_head_kv, n_cells] of the flat K cache; F16/F32: ggml_rope_ext_inplace on the view;
+// quantised: ggml_cast -> F32, ggml_rope_ext_inplace, ggml_cpy back into the view.  shift = I32 [n_cells].  In place.
+int ref_k_shift(int type, void * k_cache, int64_t n_cells, int n_head_kv, int d, const int32_t * shift,
+                int n_rot, int mode, int n_ctx_orig, float freq_base, float freq_scale, float ext_factor,
+                float attn_factor, float beta_fast, float beta_slow, const float * freq_factors, int n_threads) {
+    ref_init_once();
+    const int64_t row = (int64_t) d*n_head_kv;
+    ctx_guard g((size_t) 64*1024*1024 + (size_t) n_cells*row*8);
+    ggml_context * ctx = g.ctx;
+    if (!ctx) return -1;
+    ggml_tensor * kc = wrap(ctx, (ggml_type) type, row*n_cells, 1, 1, k_cache);          // k_l[il]: flat 1-D (llama-kv-cache.cpp:100)
+    ggml_tensor * sh = wrap(ctx, GGML_TYPE_I32, n_cells, 1, 1, (void *) shift);
+    ggml_tensor * ff = freq_factors ? wrap(ctx, GGML_TYPE_F32, n_rot/2, 1, 1, (void *) freq_factors) : nullptr;
+    ggml_tensor * cur = ggml_view_3d(ctx, kc, d, n_head_kv, n_cells, ggml_row_size(kc->type, d), ggml_row_size(kc->type, row), 0);
+    ggml_tensor * tmp;
+    if (ggml_is_quantized(cur->type)) {
+        tmp = ggml_cast(ctx, cur, GGML_TYPE_F32);
+        tmp = ggml_rope_ext_inplace(ctx, tmp, sh, ff, n_rot, mode, n_ctx_orig, freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow);
+        tmp = ggml_cpy(ctx, tmp, cur);
+    } else {
+        tmp = ggml_rope_ext_inplace(ctx, cur, sh, ff, n_rot, mode, n_ctx_orig, freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow);
+    }
+    ggml_cgraph * gf = ggml_new_graph(ctx);
+    ggml_build_forward_expand(gf, tmp);
+    run_graph(gf, n_threads, 1);
+    return 0;
+}
+
 } // extern "C"

@@ -140,6 +140,22 @@ def test_paged_decode(pkg, oracle, cuda, case, t, kernel):
 
 
 @pytest.mark.parametrize("kernel", [1, 2], ids=["generic", "streamk"])
+@pytest.mark.parametrize("t", [F16, Q4_0])
+def test_paged_decode_empty_sequences(pkg, oracle, cuda, t, kernel):
+    """a row whose sequence holds no token: the reference divides 0 by a zero row sum (ggml-cpu.c:12418) -> NaN row;
+    its neighbours are untouched by it (stream-K: such rows own no segment; the combine kernel writes them)"""
+    import torch
+    w = make_workload(oracle, [0, 33, 0, 700, 0], 32, 8, 128, t, seed=5)
+    got = _run_paged(pkg, torch, w, kernel)
+    want = oracle_attention(oracle, w)
+    for r in (0, 2, 4):
+        assert np.isnan(got[r]).all() and np.isnan(want[r]).all()
+    live = [1, 3]
+    assert not np.isnan(got[live]).any()
+    assert oracle.max_rel_err(want[live], got[live]) <= TOL[t]
+
+
+@pytest.mark.parametrize("kernel", [1, 2], ids=["generic", "streamk"])
 @pytest.mark.parametrize("dist", ["uniform", "normal"])
 def test_paged_decode_mixed_types_and_normal_inputs(pkg, oracle, cuda, dist, kernel):
     import torch
