@@ -482,8 +482,15 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
     const int g1 = min(g0 + chunk, total);
 
     // row containing global tile g0: last r with P[r] <= g0 (rows without tiles share P with their successor)
+    // 32-ary search: each level is ONE coalesced load + ballot (a binary search is log2(n_q) DEPENDENT global loads
+    // in front of the first TMA issue; on an 8 x 1024 problem the whole op lasts ~10 us)
     int lo = 0, hi = p.n_q;                                  // invariant: P[lo] <= g0 < P[hi]
-    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (P[mid] <= g0) lo = mid; else hi = mid; }
+    while (hi - lo > 1) {
+        const int step = (hi - lo + 31) >> 5, idx = lo + step*(lane + 1);
+        const int k = __popc(__ballot_sync(0xffffffffu, idx < hi && P[idx] <= g0));   // P is non-decreasing: a prefix of lanes
+        hi = min(hi, lo + step*(k + 1));
+        lo += step*k;
+    }
     int row = lo;
 
     uint32_t smem0 = smem_u32(sk_dyn) + SM::BAR_BYTES + warp*SM::WARP;
@@ -698,25 +705,33 @@ sk_combine_kernel(const __grid_constant__ sk_args a) {
     const int s0 = FS[row], ns = FS[row + 1] - s0;
     if (ns == 1) return;                                              // written by the main kernel
     // Latency matters here, not bandwidth (a row has up to ~40 segments and the whole kernel moves a few hundred KB):
-    // the segments' (m, l) are read lane-parallel, the rescale factors travel by shuffle, and the O partials of four
-    // segments are in flight at once.  (One dependent global load per segment per pass cost 9 us of a 20 us layer-op.)
+    // the segments' (m, l) are read lane-parallel (once for rows of up to 32 segments), the rescale factors travel by
+    // shuffle, and the O partials of sixteen segments are in flight at once: FS -> (m, l) -> O is three dependent
+    // round trips.  (One dependent global load per segment per pass cost 9 us of a 20 us layer-op.)
     const float2 *ML = reinterpret_cast<const float2 *>(a.part_ml) + (int64_t) s0*p.n_head + h;      // segment s at ML[s*n_head]
     const float  *PO = a.part_o + ((int64_t) s0*p.n_head + h)*SK_D + 4*lane;                         // segment s at PO + s*n_head*SK_D
-    float M = -INFINITY;
-    for (int s = lane; s < ns; s += 32) M = fmaxf(M, ML[(int64_t) s*p.n_head].x);
+    const float2 ml0 = lane < ns ? ML[(int64_t) lane*p.n_head] : make_float2(-INFINITY, 0.f);       // kept for the first batch
+    float M = ml0.x;
+    for (int s = lane + 32; s < ns; s += 32) M = fmaxf(M, ML[(int64_t) s*p.n_head].x);
 #pragma unroll
     for (int o_ = 16; o_ > 0; o_ >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o_));
     float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
     float L = 0.f;
     for (int c = 0; c < ns; c += 32) {
         float f = 0.f;
-        if (c + lane < ns) { const float2 ml = ML[(int64_t) (c + lane)*p.n_head]; f = ex2(ml.x - M); L = fmaf(ml.y, f, L); }
+        if (c + lane < ns) { const float2 ml = c ? ML[(int64_t) (c + lane)*p.n_head] : ml0; f = ex2(ml.x - M); L = fmaf(ml.y, f, L); }
         const int cnt = ns - c < 32 ? ns - c : 32;
-#pragma unroll 4
-        for (int j = 0; j < cnt; ++j) {
-            const float  fj = __shfl_sync(0xffffffffu, f, j);
-            const float4 v  = *reinterpret_cast<const float4 *>(PO + (int64_t) (c + j)*p.n_head*SK_D);
-            o.x = fmaf(v.x, fj, o.x); o.y = fmaf(v.y, fj, o.y); o.z = fmaf(v.z, fj, o.z); o.w = fmaf(v.w, fj, o.w);
+        // branch-free batches of 16 partials in flight (one L2 round trip for a row of up to 16 segments): segments
+        // past the end are clamped to a valid address and enter with the zero factor of their lane
+        for (int j0 = 0; j0 < cnt; j0 += 16) {
+            float4 v[16];
+#pragma unroll
+            for (int u = 0; u < 16; ++u) v[u] = *reinterpret_cast<const float4 *>(PO + (int64_t) min(c + j0 + u, ns - 1)*p.n_head*SK_D);
+#pragma unroll
+            for (int u = 0; u < 16; ++u) {
+                const float fj = __shfl_sync(0xffffffffu, f, j0 + u);       // lanes >= cnt hold f == 0
+                o.x = fmaf(v[u].x, fj, o.x); o.y = fmaf(v[u].y, fj, o.y); o.z = fmaf(v[u].z, fj, o.z); o.w = fmaf(v[u].w, fj, o.w);
+            }
         }
     }
 #pragma unroll
