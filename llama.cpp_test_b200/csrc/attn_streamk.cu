@@ -475,16 +475,20 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
 
     const int wid  = blockIdx.x*SK_WARPS + warp;
     const int item = wid / p.n_head_kv, kvh = wid - item*p.n_head_kv;
-    const int total = a.plan[0], chunk = a.plan[1];
+    // the first 128 bytes of the plan in ONE coalesced load: the header {total, chunk} and P[0..27]
     const int *P = a.plan + 4, *FS = P + (p.n_q + 1);
+    const int head = lane < 4 + p.n_q + 1 ? a.plan[lane] : INT_MAX;
+    const int total = __shfl_sync(0xffffffffu, head, 0), chunk = __shfl_sync(0xffffffffu, head, 1);
     int g0 = item*chunk;
     if (g0 >= total) return;
     const int g1 = min(g0 + chunk, total);
 
     // row containing global tile g0: last r with P[r] <= g0 (rows without tiles share P with their successor)
     // 32-ary search: each level is ONE coalesced load + ballot (a binary search is log2(n_q) DEPENDENT global loads
-    // in front of the first TMA issue; on an 8 x 1024 problem the whole op lasts ~10 us)
-    int lo = 0, hi = p.n_q;                                  // invariant: P[lo] <= g0 < P[hi]
+    // in front of the first TMA issue; on an 8 x 1024 problem the whole op lasts ~10 us).  Up to 27 rows are settled
+    // by the header load itself: P is non-decreasing, so the lanes with P[r] <= g0 form a prefix.
+    int lo = __popc(__ballot_sync(0xffffffffu, lane >= 4 && head <= g0)) - 1, hi = p.n_q;   // invariant: P[lo] <= g0 < P[hi]
+    if (lo < 27) hi = min(hi, lo + 1);
     while (hi - lo > 1) {
         const int step = (hi - lo + 31) >> 5, idx = lo + step*(lane + 1);
         const int k = __popc(__ballot_sync(0xffffffffu, idx < hi && P[idx] <= g0));   // P is non-decreasing: a prefix of lanes
