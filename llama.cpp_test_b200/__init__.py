@@ -20,7 +20,7 @@ LIB_PATH = os.path.join(_HERE, "libb200attn.so")
 
 TYPE_F32, TYPE_F16, TYPE_Q4_0, TYPE_Q8_0 = 0, 1, 2, 8
 TYPE_NAMES = {TYPE_F32: "f32", TYPE_F16: "f16", TYPE_Q4_0: "q4_0", TYPE_Q8_0: "q8_0"}
-KERNEL_AUTO, KERNEL_GENERIC, KERNEL_STREAMK, KERNEL_PREFILL = 0, 1, 2, 3
+KERNEL_AUTO, KERNEL_GENERIC, KERNEL_STREAMK, KERNEL_PREFILL, KERNEL_STREAMK_DQ = 0, 1, 2, 3, 4
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(
