@@ -19,7 +19,8 @@
 // once (what the reference's CUDA path does before its F16 MMA kernel, ggml/src/ggml-cuda/fattn-common.cuh:723-749);
 // scores, softmax and the accumulators are FP32.
 
-constexpr int DQ_THREADS = 256;                      // 8 warps: warp w owns tokens 32*(w&3).. and half (w>>2) of the row / of the heads
+constexpr int DQ_WORKERS = 256;                      // 8 worker warps: warp w owns tokens 32*(w&3).. and half (w>>2) of the row / of the heads
+constexpr int DQ_THREADS = DQ_WORKERS + 32;          // + the control warp: TMA gathers and tcgen05.mma issue
 constexpr int DQ_TOK     = 128;                       // tokens per super-tile
 constexpr int DQ_WIN     = 144;                       // staged bytes per token row (136-byte head row + alignment slack)
 constexpr int DQ_SLOT    = DQ_TOK*DQ_WIN;             // 18432
@@ -29,7 +30,7 @@ constexpr int DQ_OFF_Q   = 32768;                     // Q16 [2 d-halves][16 row
 constexpr int DQ_OFF_P   = 36864;                     // P^T [2 token-halves][16 rows][128 B]
 constexpr int DQ_OFF_KS  = 40960;                     // staged K rows, DQ_NSLOT slots
 constexpr int DQ_OFF_VS  = DQ_OFF_KS + DQ_NSLOT*DQ_SLOT;
-constexpr int DQ_OFF_BAR = DQ_OFF_VS + DQ_NSLOT*DQ_SLOT;   // kfull[2], vfull[2], sbar, pvbar, tmem slot, reduction scratch
+constexpr int DQ_OFF_BAR = DQ_OFF_VS + DQ_NSLOT*DQ_SLOT;   // kfull[2], vfull[2], S, PV, K-ready, P-ready, tmem slot, reduction scratch
 constexpr int DQ_SMEM    = DQ_OFF_BAR + 256;          // 114944: two CTAs per SM
 // TMEM columns (128 allocated): S^T 0..15, O^T 16..31, K16 32..95 (the A operand of S^T = K16 . Q16^T: lane = token, two
 // halves per column; it never touches shared memory)
@@ -149,6 +150,9 @@ __device__ __forceinline__ void dq_store_half(uint32_t dst_tile, int tk, int hf,
     for (int c = 0; c < 8; ++c) dq_sts128(rowbase + (((uint32_t) c << 4) ^ x7), r[4*c], r[4*c + 1], r[4*c + 2], r[4*c + 3]);
 }
 
+__device__ __forceinline__ void dq_mbar_arrive(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory"); }
+__device__ __forceinline__ void dq_workers_sync() { asm volatile("bar.sync 1, %0;" :: "n"(DQ_WORKERS) : "memory"); }
+
 __global__ void __launch_bounds__(DQ_THREADS, 2)
 dq_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV) {
     extern __shared__ __align__(1024) char dq_dyn[];
@@ -156,19 +160,23 @@ dq_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
     const uint32_t sbase = smem_u32(dq_dyn);
     const uint32_t sVf = sbase + DQ_OFF_VF, sQ = sbase + DQ_OFF_Q, sP = sbase + DQ_OFF_P;
     const uint32_t sKs = sbase + DQ_OFF_KS, sVs = sbase + DQ_OFF_VS, sBar = sbase + DQ_OFF_BAR;
-    const uint32_t bKfull = sBar, bVfull = sBar + 16, bS = sBar + 32, bPV = sBar + 40;   // kfull / vfull: one per slot
-    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(dq_dyn + DQ_OFF_BAR + 48);
-    float *red = reinterpret_cast<float *>(dq_dyn + DQ_OFF_BAR + 64);           // [2 halves][4 quadrants][4 heads]
+    // kfull / vfull: TMA -> workers, one per slot.  S / PV: tcgen05.commit -> workers.  KR / PR: the 256 workers -> the control
+    // warp ("K16 (and Q16) are in place", "V16 and P are in place"): an arrive, so no worker ever waits for the control warp.
+    const uint32_t bKfull = sBar, bVfull = sBar + 16, bS = sBar + 32, bPV = sBar + 40, bKR = sBar + 48, bPR = sBar + 56;
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(dq_dyn + DQ_OFF_BAR + 64);
+    float *red = reinterpret_cast<float *>(dq_dyn + DQ_OFF_BAR + 96);           // [2 halves][4 quadrants][4 heads]
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-    const int hf = warp >> 2, tk = 32*(warp & 3) + lane;                        // this thread: token tk of the super-tile, half hf
+    const bool control = warp == DQ_WORKERS/32;
+    const int hf = (warp >> 2) & 1, tk = 32*(warp & 3) + lane;                  // worker: token tk of the super-tile, half hf
     pdl_prologue();
 
     if (t == 0) {
         mbar_init(bKfull, 1); mbar_init(bKfull + 8, 1); mbar_init(bVfull, 1); mbar_init(bVfull + 8, 1); mbar_init(bS, 1); mbar_init(bPV, 1);
+        mbar_init(bKR, DQ_WORKERS); mbar_init(bPR, DQ_WORKERS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 128;" :: "r"(sBar + 48) : "memory");
+    if (control) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 128;" :: "r"(sBar + 64) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     // Q16 rows >= gqa and P rows 8..15 stay zero for the whole kernel
@@ -203,180 +211,198 @@ dq_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
         const int pb = P[row], pe = P[row + 1];
         if (pe <= g0) { ++row; continue; }
         const int t0 = g0 - pb, t1 = min(g1, pe) - pb;        // 16-token tiles [t0, t1) of this row
-        const int seq = p.q_seq ? p.q_seq[row] : row;
-        const int n_vis = sk_row_nvis(p, row);
-        const int32_t *bt = p.block_table + (int64_t) seq*p.bt_stride;
-        const int seg = FS[row] + (item - pb/chunk);
-        const bool single = (FS[row + 1] - FS[row]) == 1;
         const int nst = (t1 - t0 + 7) >> 3;                   // super-tiles of this segment
 
-        // the 8 boxes of super-tile j (one warp, lanes 0..7: one box each), K or V; g: its CTA-wide index (slot = g & 1)
-        auto issue = [&](int j, uint32_t g, bool is_v) {
-            const int tile0 = t0 + 8*j, nb = min(8, t1 - tile0);
-            const uint32_t bar = (is_v ? bVfull : bKfull) + 8*(g & 1), dst = (is_v ? sVs : sKs) + (g & 1)*DQ_SLOT;
-            if (lane == 0) mbar_expect_tx(bar, (uint32_t) (nb*SK_TILE*DQ_WIN));
-            __syncwarp();
-            if (lane < nb) {
-                const int ti = tile0 + lane, b = ti/tpb;
-                const int blk = b < n_blk ? bt[b] : 0;
-                const int cell = blk*bs + (ti - b*tpb)*SK_TILE;
-                tma_load_2d(dst + (uint32_t) (lane*SK_TILE*DQ_WIN), is_v ? &tmV : &tmK, is_v ? vc : kc, cell, bar);
-            }
-        };
-        if (warp == 1) {                                      // warp 1 gathers, warp 0 issues the MMAs
+        if (control) {
+            // ================= control warp: gathers through the block table, issues the MMAs =================
+            const int seq = p.q_seq ? p.q_seq[row] : row;
+            const int32_t *bt = p.block_table + (int64_t) seq*p.bt_stride;
+            // block-table entries come from a register window (lane l: entry win_base + l, the next 32 one window ahead)
+            int win_base = t0/tpb;
+            int win      = win_base + lane      < n_blk ? bt[win_base + lane]      : 0;
+            int win_next = win_base + 32 + lane < n_blk ? bt[win_base + 32 + lane] : 0;
+            // the 8 boxes of super-tile j (lanes 0..7: one box each), K or V; g: its CTA-wide index (slot = g & 1)
+            auto issue = [&](int j, uint32_t g, bool is_v) {
+                const int tile0 = t0 + 8*j, nb = min(8, t1 - tile0);
+                const uint32_t bar = (is_v ? bVfull : bKfull) + 8*(g & 1), dst = (is_v ? sVs : sKs) + (g & 1)*DQ_SLOT;
+                if (tile0/tpb - win_base >= 32) {             // K and V of a super-tile, and super-tiles, come in order
+                    win_base += 32; win = win_next;
+                    win_next = win_base + 32 + lane < n_blk ? bt[win_base + 32 + lane] : 0;
+                }
+                if (lane == 0) mbar_expect_tx(bar, (uint32_t) (nb*SK_TILE*DQ_WIN));
+                const int ti = tile0 + (lane & 7), b = ti/tpb, idx = b - win_base;
+                const int e0 = __shfl_sync(0xffffffffu, win, idx & 31), e1 = __shfl_sync(0xffffffffu, win_next, idx & 31);
+                const int blk = idx < 32 ? e0 : e1;
+                if (lane < nb) {
+                    const int cell = blk*bs + (ti - b*tpb)*SK_TILE;
+                    tma_load_2d(dst + (uint32_t) (lane*SK_TILE*DQ_WIN), is_v ? &tmV : &tmK, is_v ? vc : kc, cell, bar);
+                }
+            };
             issue(0, G, false); issue(0, G, true);
             if (nst > 1) { issue(1, G + 1, false); issue(1, G + 1, true); }
-        }
-
-        // ---- Q16: thread t fills positions [8*(t&15), +8) of row t>>4 (rows >= gqa stay zero)
-        {
-            const int h = t >> 4, p0 = 8*(t & 15);
-            if (h < a.gqa) {
-                const float *qrow = reinterpret_cast<const float *>(static_cast<const char *>(p.q) + (int64_t) row*p.nbq1
-                                                                     + (int64_t) (kvh*a.gqa + h)*p.nbq2);
-                uint32_t r[4];
+            for (int j = 0; j < nst; ++j, ++G) {
+                mbar_wait(bKR, G & 1);                        // K16 in TMEM, Q16 in shared memory, staged K rows free
+                if (lane == 0) {
+                    dq_tc_fence_after();
+                    const uint64_t b0 = dq_desc(sQ, 16, 1024);
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    r[k] = pack_h2(qrow[dq_pos_to_d(p0 + 2*k)]*a.qscale, qrow[dq_pos_to_d(p0 + 2*k + 1)]*a.qscale);
-                const int c = (p0 & 63) >> 3;
-                dq_sts128(sQ + (uint32_t) ((p0 >> 6)*2048 + (h >> 3)*1024 + (h & 7)*128 + ((c ^ (h & 7)) << 4)), r[0], r[1], r[2], r[3]);
+                    for (int ks = 0; ks < 8; ++ks)
+                        dq_mma_ts(tmem + DQ_TM_S, tmem + DQ_TM_K + 8*ks, b0 + (uint64_t) ((ks >> 2)*128 + (ks & 3)*2), ID_QK, ks > 0);
+                    dq_commit(bS);
+                }
+                __syncwarp();
+                if (j + 2 < nst) issue(j + 2, G + 2, false);
+                mbar_wait(bPR, G & 1);                        // V16 and P in shared memory, O rescaled, staged V rows free
+                if (lane == 0) {
+                    dq_tc_fence_after();
+                    const uint64_t a0 = dq_desc(sVf, 16384, 1024), b0 = dq_desc(sP, 16, 1024);
+#pragma unroll
+                    for (int ks = 0; ks < 8; ++ks)
+                        dq_mma(tmem + DQ_TM_O, a0 + (uint64_t) (ks*128), b0 + (uint64_t) ((ks >> 2)*128 + (ks & 3)*2), ID_PV, (j > 0 || ks > 0) ? 1u : 0u);
+                    dq_commit(bPV);
+                }
+                __syncwarp();
+                if (j + 2 < nst) issue(j + 2, G + 2, true);
             }
-        }
-
-        float ref[4], lsum[4];                                // heads 4hf .. 4hf+3
-#pragma unroll
-        for (int h = 0; h < 4; ++h) { ref[h] = -INFINITY; lsum[h] = 0.f; }
-
-        for (int j = 0; j < nst; ++j, ++G) {
-            const int tok0 = (t0 + 8*j)*SK_TILE;              // first token of the super-tile within the row
-            const bool dead = tok0 + tk >= n_vis || tk >= min(8, t1 - (t0 + 8*j))*SK_TILE;
-            const uint32_t slot = G & 1, par = (G >> 1) & 1;
-            // ---- K: expand into TMEM, then S^T = K16 . Q16^T  (QK of the previous super-tile retired: bS was waited on)
-            mbar_wait(bKfull + 8*slot, par);
+        } else {
+            // ================= worker warps =================
+            const int n_vis = sk_row_nvis(p, row);
+            const int seg = FS[row] + (item - pb/chunk);
+            const bool single = (FS[row + 1] - FS[row]) == 1;
+            // ---- Q16: thread t fills positions [8*(t&15), +8) of row t>>4 (rows >= gqa stay zero).  Its previous readers
+            //      (the QK MMAs of the last segment) retired before the epilogue's PV wait.
             {
-                uint32_t r[32];
-                const uint32_t src = sKs + slot*DQ_SLOT + (uint32_t) (tk*DQ_WIN);
-                if (hf) dq_expand<1>(src, kmis, r, false); else dq_expand<0>(src, kmis, r, false);
-                dq_tmem_st32(tK, r);
+                const int h = t >> 4, p0 = 8*(t & 15);
+                if (h < a.gqa) {
+                    const float *qrow = reinterpret_cast<const float *>(static_cast<const char *>(p.q) + (int64_t) row*p.nbq1
+                                                                         + (int64_t) (kvh*a.gqa + h)*p.nbq2);
+                    uint32_t r[4];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        r[k] = pack_h2(qrow[dq_pos_to_d(p0 + 2*k)]*a.qscale, qrow[dq_pos_to_d(p0 + 2*k + 1)]*a.qscale);
+                    const int c = (p0 & 63) >> 3;
+                    dq_sts128(sQ + (uint32_t) ((p0 >> 6)*2048 + (h >> 3)*1024 + (h & 7)*128 + ((c ^ (h & 7)) << 4)), r[0], r[1], r[2], r[3]);
+                }
             }
-            dq_fence_async_smem();                            // Q16 (first super-tile of a segment)
-            dq_tc_fence_before();
-            __syncthreads();                                  // K16 (and Q16) complete, staged K rows free
-            if (warp == 1 && j + 2 < nst) issue(j + 2, G + 2, false);
-            if (t == 0) {
+            float ref[4], lsum[4];                            // heads 4hf .. 4hf+3
+#pragma unroll
+            for (int h = 0; h < 4; ++h) { ref[h] = -INFINITY; lsum[h] = 0.f; }
+
+            for (int j = 0; j < nst; ++j, ++G) {
+                const int tok0 = (t0 + 8*j)*SK_TILE;          // first token of the super-tile within the row
+                const bool dead = tok0 + tk >= n_vis || tk >= min(8, t1 - (t0 + 8*j))*SK_TILE;
+                const uint32_t slot = G & 1, par = (G >> 1) & 1;
+                // ---- K: expand into TMEM (QK of the previous super-tile retired: bS was waited on)
+                mbar_wait(bKfull + 8*slot, par);
+                {
+                    uint32_t r[32];
+                    const uint32_t src = sKs + slot*DQ_SLOT + (uint32_t) (tk*DQ_WIN);
+                    if (hf) dq_expand<1>(src, kmis, r, false); else dq_expand<0>(src, kmis, r, false);
+                    dq_tmem_st32(tK, r);
+                }
+                dq_fence_async_smem();                        // Q16 (first super-tile of a segment)
+                dq_tc_fence_before();
+                dq_mbar_arrive(bKR);
+                // ---- V: expand into shared memory (the previous P.V must have retired: it reads V16 and P)
+                if (G > 0) mbar_wait(bPV, (G - 1) & 1);
+                mbar_wait(bVfull + 8*slot, par);
+                {
+                    uint32_t r[32];
+                    const uint32_t src = sVs + slot*DQ_SLOT + (uint32_t) (tk*DQ_WIN);
+                    if (hf) dq_expand<1>(src, vmis, r, dead); else dq_expand<0>(src, vmis, r, dead);
+                    dq_store_half(sVf, tk, hf, r);
+                }
+                // ---- softmax: this thread's token, its 4 head columns
+                mbar_wait(bS, G & 1);
                 dq_tc_fence_after();
-                const uint64_t b0 = dq_desc(sQ, 16, 1024);
+                float s[4];
+                dq_tmem_ld4(tS, s);
+                float mx[4];
 #pragma unroll
-                for (int ks = 0; ks < 8; ++ks)
-                    dq_mma_ts(tmem + DQ_TM_S, tmem + DQ_TM_K + 8*ks, b0 + (uint64_t) ((ks >> 2)*128 + (ks & 3)*2), ID_QK, ks > 0);
-                dq_commit(bS);
+                for (int h = 0; h < 4; ++h) { if (dead) s[h] = -INFINITY; mx[h] = s[h]; }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+                    for (int h = 0; h < 4; ++h) mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], o));
+                }
+                // `red` is free: its readers of the previous super-tile arrived on PR before PV was issued, and bS of this
+                // one completed after every worker arrived on KR
+                if (lane == 0) *reinterpret_cast<float4 *>(red + 4*warp) = make_float4(mx[0], mx[1], mx[2], mx[3]);
+                dq_workers_sync();
+                bool move = false;                            // uniform over the 4 warps of this half
+                float alpha[4];
+                {
+                    const float4 m0 = *reinterpret_cast<const float4 *>(red + 16*hf),     m1 = *reinterpret_cast<const float4 *>(red + 16*hf + 4);
+                    const float4 m2 = *reinterpret_cast<const float4 *>(red + 16*hf + 8), m3 = *reinterpret_cast<const float4 *>(red + 16*hf + 12);
+                    const float m[4] = {fmaxf(fmaxf(m0.x, m1.x), fmaxf(m2.x, m3.x)), fmaxf(fmaxf(m0.y, m1.y), fmaxf(m2.y, m3.y)),
+                                        fmaxf(fmaxf(m0.z, m1.z), fmaxf(m2.z, m3.z)), fmaxf(fmaxf(m0.w, m1.w), fmaxf(m2.w, m3.w))};
+#pragma unroll
+                    for (int h = 0; h < 4; ++h) {
+                        alpha[h] = 1.0f;
+                        // lazy reference: it only moves when the maximum outgrows it by 2^8 (P stays below 256: exact enough in F16)
+                        if (m[h] > ref[h] + 8.0f) { alpha[h] = ex2(ref[h] - m[h]); ref[h] = m[h]; move = true; }   // ref = -inf: alpha = 0
+                    }
+                }
+                if (move) {
+#pragma unroll
+                    for (int h = 0; h < 4; ++h) lsum[h] *= alpha[h];
+                    if (j > 0) {                              // O holds earlier tiles of this segment: rescale this lane's 4 columns (PV retired above)
+                        float o4[4];
+                        dq_tmem_ld4(tO, o4);
+#pragma unroll
+                        for (int h = 0; h < 4; ++h) o4[h] *= alpha[h];
+                        dq_tmem_st4(tO, o4);
+                    }
+                }
+                {
+                    const uint32_t pbase = sP + (uint32_t) ((tk >> 6)*2048 + (tk & 7)*2), c = (uint32_t) ((tk & 63) >> 3);
+#pragma unroll
+                    for (int h = 0; h < 4; ++h) {
+                        const float pv = dead ? 0.0f : ex2(s[h] - ref[h]);
+                        lsum[h] += pv;
+                        const uint32_t hh = (uint32_t) (4*hf + h);
+                        dq_sts16(pbase + hh*128 + ((c ^ hh) << 4), (uint32_t) __half_as_ushort(__float2half_rn(pv)));
+                    }
+                }
+                dq_fence_async_smem();
+                dq_tc_fence_before();
+                dq_mbar_arrive(bPR);
             }
-            // ---- V: expand into shared memory (the previous P.V must have retired: it reads V16 and P)
-            if (G > 0) mbar_wait(bPV, (G - 1) & 1);
-            mbar_wait(bVfull + 8*slot, par);
-            {
-                uint32_t r[32];
-                const uint32_t src = sVs + slot*DQ_SLOT + (uint32_t) (tk*DQ_WIN);
-                if (hf) dq_expand<1>(src, vmis, r, dead); else dq_expand<0>(src, vmis, r, dead);
-                dq_store_half(sVf, tk, hf, r);
-            }
-            // ---- softmax: this thread's token, its 4 head columns
-            mbar_wait(bS, G & 1);
+
+            // ---- segment epilogue: O^T row tk = position tk of this half's heads; row sums over the 128 token lanes
+            mbar_wait(bPV, (G - 1) & 1);
             dq_tc_fence_after();
-            float s[4];
-            dq_tmem_ld4(tS, s);
-            float mx[4];
-#pragma unroll
-            for (int h = 0; h < 4; ++h) { if (dead) s[h] = -INFINITY; mx[h] = s[h]; }
+            float o4[4];
+            dq_tmem_ld4(tO, o4);
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
 #pragma unroll
-                for (int h = 0; h < 4; ++h) mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], o));
+                for (int h = 0; h < 4; ++h) lsum[h] += __shfl_xor_sync(0xffffffffu, lsum[h], o);
             }
-            if (lane == 0) *reinterpret_cast<float4 *>(red + 4*warp) = make_float4(mx[0], mx[1], mx[2], mx[3]);   // `red` is free: its last readers passed a barrier since
-            __syncthreads();
-            bool move = false;                                // uniform over the 4 warps of this half
-            float alpha[4];
-            {
-                const float4 m0 = *reinterpret_cast<const float4 *>(red + 16*hf),     m1 = *reinterpret_cast<const float4 *>(red + 16*hf + 4);
-                const float4 m2 = *reinterpret_cast<const float4 *>(red + 16*hf + 8), m3 = *reinterpret_cast<const float4 *>(red + 16*hf + 12);
-                const float m[4] = {fmaxf(fmaxf(m0.x, m1.x), fmaxf(m2.x, m3.x)), fmaxf(fmaxf(m0.y, m1.y), fmaxf(m2.y, m3.y)),
-                                    fmaxf(fmaxf(m0.z, m1.z), fmaxf(m2.z, m3.z)), fmaxf(fmaxf(m0.w, m1.w), fmaxf(m2.w, m3.w))};
+            dq_workers_sync();                                // the last readers of `red` (this segment's last maxima) are done
+            if (lane == 0) *reinterpret_cast<float4 *>(red + 4*warp) = make_float4(lsum[0], lsum[1], lsum[2], lsum[3]);
+            dq_workers_sync();
+            const int dd = dq_pos_to_d(tk);
 #pragma unroll
-                for (int h = 0; h < 4; ++h) {
-                    alpha[h] = 1.0f;
-                    // lazy reference: it only moves when the maximum outgrows it by 2^8 (P stays below 256: exact enough in F16)
-                    if (m[h] > ref[h] + 8.0f) { alpha[h] = ex2(ref[h] - m[h]); ref[h] = m[h]; move = true; }   // ref = -inf: alpha = 0
+            for (int h = 0; h < 4; ++h) {
+                if (4*hf + h < a.gqa) {
+                    const float l = (red[16*hf + h] + red[16*hf + 4 + h]) + (red[16*hf + 8 + h] + red[16*hf + 12 + h]);
+                    const int head = kvh*a.gqa + 4*hf + h;
+                    if (single) static_cast<float *>(p.dst)[((int64_t) row*p.n_head + head)*SK_D + dd] = o4[h]*(1.0f/l);
+                    else {
+                        a.part_o[((int64_t) seg*p.n_head + head)*SK_D + dd] = o4[h];
+                        if (tk == 0) { float *ml = a.part_ml + ((int64_t) seg*p.n_head + head)*2; ml[0] = ref[h]; ml[1] = l; }
+                    }
                 }
             }
-            if (move) {
-#pragma unroll
-                for (int h = 0; h < 4; ++h) lsum[h] *= alpha[h];
-                if (j > 0) {                                  // O holds earlier tiles of this segment: rescale this lane's 4 columns (PV retired above)
-                    float o4[4];
-                    dq_tmem_ld4(tO, o4);
-#pragma unroll
-                    for (int h = 0; h < 4; ++h) o4[h] *= alpha[h];
-                    dq_tmem_st4(tO, o4);
-                }
-            }
-            {
-                const uint32_t pbase = sP + (uint32_t) ((tk >> 6)*2048 + (tk & 7)*2), c = (uint32_t) ((tk & 63) >> 3);
-#pragma unroll
-                for (int h = 0; h < 4; ++h) {
-                    const float pv = dead ? 0.0f : ex2(s[h] - ref[h]);
-                    lsum[h] += pv;
-                    const uint32_t hh = (uint32_t) (4*hf + h);
-                    dq_sts16(pbase + hh*128 + ((c ^ hh) << 4), (uint32_t) __half_as_ushort(__float2half_rn(pv)));
-                }
-            }
-            dq_fence_async_smem();
             dq_tc_fence_before();
-            __syncthreads();                                  // V16 and P complete, staged V rows free, O rescaled
-            if (warp == 1 && j + 2 < nst) issue(j + 2, G + 2, true);
-            if (t == 0) {
-                dq_tc_fence_after();
-                const uint64_t a0 = dq_desc(sVf, 16384, 1024), b0 = dq_desc(sP, 16, 1024);
-#pragma unroll
-                for (int ks = 0; ks < 8; ++ks)
-                    dq_mma(tmem + DQ_TM_O, a0 + (uint64_t) (ks*128), b0 + (uint64_t) ((ks >> 2)*128 + (ks & 3)*2), ID_PV, (j > 0 || ks > 0) ? 1u : 0u);
-                dq_commit(bPV);
-            }
+            dq_workers_sync();                                // `red` and the TMEM columns are free for the next segment
         }
-
-        // ---- segment epilogue: O^T row tk = position tk of this half's heads; row sums over the 128 token lanes
-        mbar_wait(bPV, (G - 1) & 1);
-        dq_tc_fence_after();
-        float o4[4];
-        dq_tmem_ld4(tO, o4);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-            for (int h = 0; h < 4; ++h) lsum[h] += __shfl_xor_sync(0xffffffffu, lsum[h], o);
-        }
-        __syncthreads();
-        if (lane == 0) *reinterpret_cast<float4 *>(red + 4*warp) = make_float4(lsum[0], lsum[1], lsum[2], lsum[3]);
-        __syncthreads();
-        const int dd = dq_pos_to_d(tk);
-#pragma unroll
-        for (int h = 0; h < 4; ++h) {
-            if (4*hf + h < a.gqa) {
-                const float l = (red[16*hf + h] + red[16*hf + 4 + h]) + (red[16*hf + 8 + h] + red[16*hf + 12 + h]);
-                const int head = kvh*a.gqa + 4*hf + h;
-                if (single) static_cast<float *>(p.dst)[((int64_t) row*p.n_head + head)*SK_D + dd] = o4[h]*(1.0f/l);
-                else {
-                    a.part_o[((int64_t) seg*p.n_head + head)*SK_D + dd] = o4[h];
-                    if (tk == 0) { float *ml = a.part_ml + ((int64_t) seg*p.n_head + head)*2; ml[0] = ref[h]; ml[1] = l; }
-                }
-            }
-        }
-        dq_tc_fence_before();
-        __syncthreads();                                      // red, Q16 and the TMEM columns are free for the next segment
         g0 = pb + t1;
         ++row;
     }
 
     dq_tc_fence_before();
     __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 128;" :: "r"(tmem) : "memory");
+    if (control) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 128;" :: "r"(tmem) : "memory");
 }
