@@ -71,6 +71,37 @@ __device__ __forceinline__ void dq_tmem_st32(uint32_t taddr, const uint32_t (&v)
 __device__ __forceinline__ void dq_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
 }
+// The 8 K16 steps of S^T = K16 . Q16^T and the commit in ONE elected block of a converged warp: with elect.sync ptxas
+// emits the uniform-datapath instructions directly (an `if (lane == 0)` costs a vote loop per MMA), and the step
+// descriptors are the step-0 ones plus constants: K16 8 TMEM columns per step; Q16 32 B per step, +2 KB for the second d-half.
+__device__ __forceinline__ void dq_qk_block(uint32_t d_tmem, uint32_t a_tmem, uint64_t b0, uint32_t idesc, uint32_t bar) {
+    asm volatile("{\n .reg .pred e, z;\n .reg .b64 b;\n .reg .b32 t;\n elect.sync _|e, 0xffffffff;\n setp.ne.b32 z, 0, 0;\n"
+                 " @e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, z;\n setp.eq.b32 z, 0, 0;\n"
+                 " add.u32 t, %1, 8;\n  add.u64 b, %2, 2;\n   @e tcgen05.mma.cta_group::1.kind::f16 [%0], [t], b, %3, z;\n"
+                 " add.u32 t, %1, 16;\n add.u64 b, %2, 4;\n   @e tcgen05.mma.cta_group::1.kind::f16 [%0], [t], b, %3, z;\n"
+                 " add.u32 t, %1, 24;\n add.u64 b, %2, 6;\n   @e tcgen05.mma.cta_group::1.kind::f16 [%0], [t], b, %3, z;\n"
+                 " add.u32 t, %1, 32;\n add.u64 b, %2, 128;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], [t], b, %3, z;\n"
+                 " add.u32 t, %1, 40;\n add.u64 b, %2, 130;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], [t], b, %3, z;\n"
+                 " add.u32 t, %1, 48;\n add.u64 b, %2, 132;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], [t], b, %3, z;\n"
+                 " add.u32 t, %1, 56;\n add.u64 b, %2, 134;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], [t], b, %3, z;\n"
+                 " @e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%4];\n}"
+                 :: "r"(d_tmem), "r"(a_tmem), "l"(b0), "r"(idesc), "r"(bar) : "memory");
+}
+// The 8 K16 steps (16 tokens each) of O^T += V16^T . P and the commit: V16 +2 KB per step; P^T 32 B per step, +2 KB for the
+// second token half.  acc_first = 0 overwrites O^T (first super-tile of a segment).
+__device__ __forceinline__ void dq_pv_block(uint32_t d_tmem, uint64_t a0, uint64_t b0, uint32_t idesc, uint32_t acc_first, uint32_t bar) {
+    asm volatile("{\n .reg .pred e, z;\n .reg .b64 a, b;\n elect.sync _|e, 0xffffffff;\n setp.ne.b32 z, %4, 0;\n"
+                 " @e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, z;\n setp.eq.b32 z, 0, 0;\n"
+                 " add.u64 a, %1, 128;\n add.u64 b, %2, 2;\n   @e tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, z;\n"
+                 " add.u64 a, %1, 256;\n add.u64 b, %2, 4;\n   @e tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, z;\n"
+                 " add.u64 a, %1, 384;\n add.u64 b, %2, 6;\n   @e tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, z;\n"
+                 " add.u64 a, %1, 512;\n add.u64 b, %2, 128;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, z;\n"
+                 " add.u64 a, %1, 640;\n add.u64 b, %2, 130;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, z;\n"
+                 " add.u64 a, %1, 768;\n add.u64 b, %2, 132;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, z;\n"
+                 " add.u64 a, %1, 896;\n add.u64 b, %2, 134;\n @e tcgen05.mma.cta_group::1.kind::f16 [%0], a, b, %3, z;\n"
+                 " @e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%5];\n}"
+                 :: "r"(d_tmem), "l"(a0), "l"(b0), "r"(idesc), "r"(acc_first), "r"(bar) : "memory");
+}
 __device__ __forceinline__ void dq_tmem_ld8(uint32_t taddr, float (&v)[8]) {
     uint32_t r[8];
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
@@ -240,28 +271,15 @@ dq_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
             };
             issue(0, G, false); issue(0, G, true);
             if (nst > 1) { issue(1, G + 1, false); issue(1, G + 1, true); }
+            const uint64_t bQ = dq_desc(sQ, 16, 1024), aV = dq_desc(sVf, 16384, 1024), bP = dq_desc(sP, 16, 1024);
             for (int j = 0; j < nst; ++j, ++G) {
                 mbar_wait(bKR, G & 1);                        // K16 in TMEM, Q16 in shared memory, staged K rows free
-                if (lane == 0) {
-                    dq_tc_fence_after();
-                    const uint64_t b0 = dq_desc(sQ, 16, 1024);
-#pragma unroll
-                    for (int ks = 0; ks < 8; ++ks)
-                        dq_mma_ts(tmem + DQ_TM_S, tmem + DQ_TM_K + 8*ks, b0 + (uint64_t) ((ks >> 2)*128 + (ks & 3)*2), ID_QK, ks > 0);
-                    dq_commit(bS);
-                }
-                __syncwarp();
+                dq_tc_fence_after();
+                dq_qk_block(tmem + DQ_TM_S, tmem + DQ_TM_K, bQ, ID_QK, bS);
                 if (j + 2 < nst) issue(j + 2, G + 2, false);
                 mbar_wait(bPR, G & 1);                        // V16 and P in shared memory, O rescaled, staged V rows free
-                if (lane == 0) {
-                    dq_tc_fence_after();
-                    const uint64_t a0 = dq_desc(sVf, 16384, 1024), b0 = dq_desc(sP, 16, 1024);
-#pragma unroll
-                    for (int ks = 0; ks < 8; ++ks)
-                        dq_mma(tmem + DQ_TM_O, a0 + (uint64_t) (ks*128), b0 + (uint64_t) ((ks >> 2)*128 + (ks & 3)*2), ID_PV, (j > 0 || ks > 0) ? 1u : 0u);
-                    dq_commit(bPV);
-                }
-                __syncwarp();
+                dq_tc_fence_after();
+                dq_pv_block(tmem + DQ_TM_O, aV, bP, ID_PV, j > 0 ? 1u : 0u, bPV);
                 if (j + 2 < nst) issue(j + 2, G + 2, true);
             }
         } else {
