@@ -256,7 +256,9 @@ int launch_kv_rows(bool scatter, void *const *caches, int n_caches, int64_t nb_t
 
 // ------------------------------------------------------------------------------------------------
 // K-shift: cached K rows re-rotated in place after a position change (context shift / seq_add / seq_div).
-// One CTA per (cell, layer); the row is expanded to F32 in shared memory (the reference's ggml_cast of a
+// One CTA per cell and group of layers (the cos/sin table of a cell is the same for every layer and costs more than a
+// row: up to 63 dependent multiplications plus a large-argument sincos; built once, it serves the whole group); each row is
+// expanded to F32 in shared memory (the reference's ggml_cast of a
 // quantised cache, src/llama-context.cpp:469-471; FP16_TO_FP32 per element for F16, ggml-cpu.c:10955+), rotated
 // with the cos/sin table of its position (ggml_rope_cache_init, ggml-cpu.c:10595-10611: theta advances by repeated
 // multiplication, YaRN mix per rope_yarn :10578-10593), then written back through the KV-write path above (the
@@ -267,6 +269,7 @@ struct k_shift_args {
     char *caches[BC_MAX_CACHES];
     b200_k_shift_desc d;                     // .caches is a host pointer: not used on the device
     float theta_scale, corr0, corr1, mscale; // powf(freq_base, -2/n_rot), ggml_rope_yarn_corr_dims, attn_factor [* YaRN magnitude]
+    int   n;                                 // caches in this launch; CTA (x, y) serves caches y, y + gridDim.y, ... of row x
 };
 
 template <int TYPE>
@@ -294,7 +297,6 @@ k_shift_kernel(const __grid_constant__ k_shift_args a) {
     float *x  = reinterpret_cast<float *>(ks_smem);
     float *cs = x + row_elems;                                         // (cos, sin) per rotated pair
     char  *stage = ks_smem + (((size_t) (row_elems + p.n_rot)*4 + 15) & ~(size_t) 15);
-    char  *cache = a.caches[blockIdx.y];
     const bool neox = (p.mode & 2) != 0;
     const int64_t n_rows = p.cells ? p.n_rows : p.n_cells;
     for (int64_t r = blockIdx.x; r < n_rows; r += gridDim.x) {
@@ -316,23 +318,26 @@ k_shift_kernel(const __grid_constant__ k_shift_args a) {
             cs[2*ic]     = __fmul_rn(cosf(th), a.mscale);
             cs[2*ic + 1] = __fmul_rn(sinf(th), a.mscale);
         }
-        const char *row = cache + cell*p.nb_token;
-        for (int e = threadIdx.x; e < row_elems; e += KVW_THREADS) {
-            const int h = e/hd;
-            x[e] = k_shift_load<TYPE>(row + h*p.nb_head, e - h*hd);
+        for (int ci = blockIdx.y; ci < a.n; ci += gridDim.y) {
+            char *cache = a.caches[ci];
+            const char *row = cache + cell*p.nb_token;
+            for (int e = threadIdx.x; e < row_elems; e += KVW_THREADS) {
+                const int h = e/hd;
+                x[e] = k_shift_load<TYPE>(row + h*p.nb_head, e - h*hd);
+            }
+            __syncthreads();                                             // also: the cos/sin table is complete
+            for (int pr = threadIdx.x; pr < p.n_head_kv*half_rot; pr += KVW_THREADS) {
+                const int h = pr/half_rot, ic = pr - h*half_rot;
+                float *xh = x + h*hd;
+                const int i0 = neox ? ic : 2*ic, i1 = neox ? ic + half_rot : 2*ic + 1;
+                const float c = cs[2*ic], sn = cs[2*ic + 1], x0 = xh[i0], x1 = xh[i1];
+                xh[i0] = __fsub_rn(__fmul_rn(x0, c),  __fmul_rn(x1, sn));
+                xh[i1] = __fadd_rn(__fmul_rn(x0, sn), __fmul_rn(x1, c));
+            }
+            __syncthreads();
+            write_row<TYPE>(x, cache, cell, p.n_head_kv, hd, p.nb_token, p.nb_head, stage);
+            __syncthreads();
         }
-        __syncthreads();
-        for (int pr = threadIdx.x; pr < p.n_head_kv*half_rot; pr += KVW_THREADS) {
-            const int h = pr/half_rot, ic = pr - h*half_rot;
-            float *xh = x + h*hd;
-            const int i0 = neox ? ic : 2*ic, i1 = neox ? ic + half_rot : 2*ic + 1;
-            const float c = cs[2*ic], sn = cs[2*ic + 1], x0 = xh[i0], x1 = xh[i1];
-            xh[i0] = __fsub_rn(__fmul_rn(x0, c),  __fmul_rn(x1, sn));
-            xh[i1] = __fadd_rn(__fmul_rn(x0, sn), __fmul_rn(x1, c));
-        }
-        __syncthreads();
-        write_row<TYPE>(x, cache, cell, p.n_head_kv, hd, p.nb_token, p.nb_head, stage);
-        __syncthreads();
     }
 }
 
@@ -371,7 +376,12 @@ int launch_k_shift(const b200_k_shift_desc &d, cudaStream_t stream) {
     for (int c0 = 0; c0 < d.n_caches; c0 += BC_MAX_CACHES) {
         const int n = d.n_caches - c0 < BC_MAX_CACHES ? d.n_caches - c0 : BC_MAX_CACHES;
         for (int i = 0; i < n; ++i) a.caches[i] = static_cast<char *>(d.caches[c0 + i]);
-        const dim3 grid(gx, (unsigned) n);
+        a.n = n;
+        // enough CTAs to fill the GPU (~16 per SM), as few layer groups as that allows: the table is rebuilt per group
+        int gy = (int) ((148*16 + (int64_t) gx - 1)/gx);
+        if (gy > n) gy = n;
+        if (gy < 1) gy = 1;
+        const dim3 grid(gx, (unsigned) gy);
         switch (d.type_k) {
             case B200_TYPE_F32:  k_shift_kernel<B200_TYPE_F32 ><<<grid, KVW_THREADS, smem, stream>>>(a); break;
             case B200_TYPE_F16:  k_shift_kernel<B200_TYPE_F16 ><<<grid, KVW_THREADS, smem, stream>>>(a); break;
