@@ -1,0 +1,82 @@
+// llama_kv_cache_paged.h — the reference's llama_kv_cache interface (src/llama-kv-cache.h:17-26 over llama_memory_i,
+// src/llama-memory.h:8-23; the unified implementation's methods, llama-kv-cache.h:93-111) implemented on PagedKVCache.
+//
+// A maintainer derives it from the real llama_kv_cache (the method names, argument order and return types are the
+// reference's; llama_pos / llama_seq_id are int32_t as in include/llama.h:60-63) and hands `update()`'s work lists to the
+// C ABI the way llama_context::kv_self_update turns has_shift / do_defrag into graphs (src/llama-context.cpp:719-790).
+//
+// What maps and what does not:
+//   clear / seq_cp / seq_keep / seq_pos_max / get_n_tokens / get_used_cells / defrag      exact (block granularity for defrag)
+//   seq_rm(seq, p0, p1)   tail and whole-sequence removal: immediate.  A middle range is remembered: the reference's callers
+//                         follow it with seq_add(seq, p1, end, p0 - p1) (context shift, examples/main/main.cpp) and the
+//                         pair becomes ONE PagedKVCache::context_shift; a pending range that is not closed that way by
+//                         the next update() / find_slot() fails there (positions with a hole cannot be a block table)
+//   seq_add               only as the closing half of a context shift (delta == p0 - p1 of the pending range, range to
+//                         the end of the sequence), once per sequence between two update() calls; anything else sets
+//                         `unsupported` (update() then fails, the caller falls back as for get_can_shift() == false)
+//   seq_div               outside the block-table model: sets `unsupported`
+//   find_slot(ubatch)     -> find_slot(seq, n_tokens): slot mapping + copy-on-write pairs (llama_decode's "no KV slot": false)
+#pragma once
+#include "paged_kv_cache.h"
+
+#include <cstdint>
+#include <limits>
+#include <map>
+#include <set>
+#include <utility>
+#include <vector>
+
+typedef int32_t llama_pos;
+typedef int32_t llama_seq_id;
+
+class llama_kv_cache_paged {
+public:
+    // device work a call to update() hands out, in execution order
+    struct pending_work {
+        std::vector<std::pair<int32_t, int32_t>> cow_pairs;    // b200_block_copy
+        std::vector<std::pair<int32_t, int32_t>> row_moves;    // b200_kv_rows_gather (first) / _scatter (second), K and V
+        std::vector<int32_t>                     shift_cells;  // b200_k_shift: cells ...
+        std::vector<int32_t>                     shift_delta;  // ... and the delta of each (the reference's cell.delta)
+        std::vector<std::pair<int32_t, int32_t>> defrag_moves; // b200_block_copy, after everything above
+        bool empty() const { return cow_pairs.empty() && row_moves.empty() && shift_cells.empty() && defrag_moves.empty(); }
+    };
+
+    llama_kv_cache_paged(int64_t n_blocks, int block_size) : cache_(n_blocks, block_size) {}
+
+    // ---- llama_kv_cache
+    int32_t  get_n_tokens()   const;                          // sum over sequences (shared prefixes count per sequence, as in the reference)
+    uint32_t get_used_cells() const;                          // cells of allocated blocks
+    bool     get_can_shift()  const { return true; }
+    bool     get_can_edit()   const { return get_can_shift(); }
+
+    // ---- llama_memory_i
+    void clear();
+    void defrag() { do_defrag_ = true; }                      // deferred, like llama_kv_cache_unified::defrag (.cpp:149-153)
+    bool seq_rm  (llama_seq_id seq_id,                              llama_pos p0, llama_pos p1);
+    void seq_cp  (llama_seq_id seq_id_src, llama_seq_id seq_id_dst, llama_pos p0, llama_pos p1);
+    void seq_keep(llama_seq_id seq_id);
+    void seq_add (llama_seq_id seq_id,                              llama_pos p0, llama_pos p1, llama_pos delta);
+    void seq_div (llama_seq_id seq_id,                              llama_pos p0, llama_pos p1, int d);
+    llama_pos seq_pos_max(llama_seq_id seq_id);
+
+    // ---- the decode loop
+    // reserve n_tokens at the end of seq_id: their cells (slot mapping) and the copy-on-write pairs to run first.
+    // false: no room (llama_decode returns 1) or an open middle removal (a request the block table cannot express)
+    bool find_slot(llama_seq_id seq_id, int32_t n_tokens, std::vector<int32_t> & slot_mapping,
+                   std::vector<std::pair<int32_t, int32_t>> & cow_pairs);
+    // kv_self_update: everything deferred since the last call.  false: a pending request could not be expressed
+    // (`unsupported()` tells which kind) — the work lists are then empty and the cache is unchanged by this call.
+    bool update(pending_work & out);
+    bool has_pending() const { return !work_.empty() || do_defrag_ || !open_.empty(); }
+    bool unsupported() const { return unsupported_; }
+
+    PagedKVCache       & blocks()       { return cache_; }
+    const PagedKVCache & blocks() const { return cache_; }
+
+private:
+    PagedKVCache cache_;
+    pending_work work_;                                       // accumulated by closed context shifts
+    std::map<llama_seq_id, std::pair<llama_pos, llama_pos>> open_;   // middle removals waiting for their seq_add
+    std::set<llama_seq_id> shifted_;                          // sequences with a context shift in work_
+    bool do_defrag_ = false, unsupported_ = false;
+};

@@ -62,6 +62,7 @@ public:
     bool    has_seq(seq_id seq) const { return seqs_.count(seq) != 0; }
     int64_t seq_len(seq_id seq) const;                 // tokens cached (seq_pos_max + 1), 0 if absent
     int64_t n_seqs() const { return (int64_t) seqs_.size(); }
+    std::vector<seq_id> seq_ids() const { std::vector<seq_id> v; for (const auto & kv : seqs_) v.push_back(kv.first); return v; }
     const std::vector<int32_t> * blocks_of(seq_id seq) const;
 
     // Cell index of every cached position of `seq`, in position order (the gather list of a state save).
