@@ -16,7 +16,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200attn.so")
+LIB_PATH = os.environ.get("B200_LIB") or os.path.join(_HERE, "libb200attn.so")     # B200_LIB: A/B builds of the same ABI
 
 TYPE_F32, TYPE_F16, TYPE_Q4_0, TYPE_Q8_0 = 0, 1, 2, 8
 TYPE_NAMES = {TYPE_F32: "f32", TYPE_F16: "f16", TYPE_Q4_0: "q4_0", TYPE_Q8_0: "q8_0"}

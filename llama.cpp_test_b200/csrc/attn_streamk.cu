@@ -584,12 +584,15 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
         auto body = [&](auto full_c, int i) {
             constexpr bool FULL = decltype(full_c)::value;
             const int nsub = FULL ? NSUB : min(NSUB, nt - i);        // tiles of this iteration (warp-uniform)
-            uint32_t kbs[NSUB], vbs[NSUB];
+            // FULL iterations wait for their first tile only; the later ones were requested last and are waited for
+            // right before their own Q.K^T, behind the first tile's
+            uint32_t kbs[NSUB], vbs[NSUB], tbar[NSUB], tph[NSUB];
 #pragma unroll
             for (int u = 0; u < NSUB; ++u) {
-                kbs[u] = vbs[u] = 0;
+                kbs[u] = vbs[u] = tbar[u] = tph[u] = 0;
                 if (FULL || u < nsub) {
-                    mbar_wait(bar0 + 8*cs, cph);
+                    if (!FULL || u == 0) mbar_wait(bar0 + 8*cs, cph);
+                    tbar[u] = bar0 + 8*cs; tph[u] = cph;
                     const uint32_t sb = smem0 + cs*SM::STAGE;
                     kbs[u] = sb + SM::KOFF; vbs[u] = sb + SM::VOFF;
                     if (++cs == STAGES) { cs = 0; cph ^= 1; }
@@ -616,6 +619,7 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
                 S[u][0] = S[u][1] = S[u][2] = S[u][3] = FULL ? 0.f : -INFINITY;
                 if (FULL || u < nsub) {
                     float A[4] = {0.f, 0.f, 0.f, 0.f};
+                    if (FULL && u > 0) mbar_wait(tbar[u], tph[u]);
                     if constexpr (TK == B200_TYPE_F16) sk_qk_f16(A, kbs[u], qf, lane);
                     else                               sk_qk_quant<TK>(A, kbs[u], kmis, qf, kcon, lane);
                     if constexpr (!FULL) {
