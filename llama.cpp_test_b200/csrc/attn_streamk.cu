@@ -43,6 +43,9 @@
 namespace b200 {
 
 constexpr int SK_WARPS = 8;
+#ifndef SK_Q8_WARPS
+#define SK_Q8_WARPS 8                                         // warps per CTA of the Q8_0/Q8_0 kernel (8 = the three-stage form)
+#endif
 constexpr int SK_D     = 128;
 constexpr int SK_TILE  = 16;           // tokens per tile
 
@@ -78,10 +81,15 @@ struct sk_smem {
     // quantised K and V: TWO tiles per loop iteration share one softmax step (the loop is instruction-issue
     // bound, profiles/r1f_*), so the ring must hold the 2 being consumed + at least 1 in flight
     static constexpr int NSUB = ANY16 ? 1 : 2;
-    static constexpr int STAGES = ANY16 ? (STAGE <= 2560 ? 4 : 3) : (STAGE <= 2560 ? 5 : 3);
+    // With 3 stages the second tile of an iteration is requested at the top of the iteration that consumes it
+    // (29 % of the warp's time in that wait, profiles/r1q_sk_q8_0_ncu_full.txt).  Tiles up to 3584 bytes take a fourth
+    // stage at 8 warps.  Q8_0 K with Q8_0 V (4608) only fits four stages with 6 warps per CTA (SK_Q8_WARPS=6, register
+    // cap 168): measured equal to 8 warps x 3 stages (5229 vs 5256 GB/s), so 8 stays the default
+    static constexpr int WARPS = ANY16 || STAGE <= 3584 ? SK_WARPS : SK_Q8_WARPS;
+    static constexpr int STAGES = ANY16 ? (STAGE <= 2560 ? 4 : 3) : (STAGE <= 2560 ? 5 : (WARPS == SK_WARPS && STAGE > 3584 ? 3 : 4));
     static constexpr int WARP = STAGE*STAGES;
-    static constexpr int BAR_BYTES = 1024;                                        // mbarriers, keeps tiles 1024-aligned
-    static constexpr int CTA = BAR_BYTES + WARP*SK_WARPS + 16;                    // +16: funnel loads may touch 4 bytes past a row
+    static constexpr int BAR_BYTES = ANY16 ? 1024 : 512;                          // mbarriers; F16 tiles must stay 1024-aligned
+    static constexpr int CTA = BAR_BYTES + WARP*WARPS + 16;                       // +16: funnel loads may touch 4 bytes past a row
     static constexpr int CTAS_PER_SM = 2*(CTA + 1024) <= 233472 ? 2 : 1;
 };
 
@@ -464,7 +472,7 @@ __device__ __forceinline__ int sk_row_d(int mt, int h, int g) {
 // main kernel
 // ------------------------------------------------------------------------------------------------
 template <int TK, int TV>
-__global__ void __launch_bounds__(32*SK_WARPS, sk_smem<TK, TV>::CTAS_PER_SM)
+__global__ void __launch_bounds__(32*sk_smem<TK, TV>::WARPS, sk_smem<TK, TV>::CTAS_PER_SM)
 sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV) {
     extern __shared__ __align__(1024) char sk_dyn[];
     using SM = sk_smem<TK, TV>;
@@ -476,7 +484,7 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
     const int g = lane >> 2, t = lane & 3;
     pdl_prologue();
 
-    const int wid  = blockIdx.x*SK_WARPS + warp;
+    const int wid  = blockIdx.x*SM::WARPS + warp;
     const int item = wid / p.n_head_kv, kvh = wid - item*p.n_head_kv;
     // the first 128 bytes of the plan in ONE coalesced load: the header {total, chunk} and P[0..27]
     const int *P = a.plan + 4, *FS = P + (p.n_q + 1);
@@ -791,8 +799,9 @@ template <typename F> static auto sk_dispatch(int tk, int tv, F &&f) {
 }
 
 static int sk_items(const b200_attn_desc &d) {
-    const int cps = sk_dispatch(d.type_k, d.type_v, [](auto k, auto v) { return sk_smem<decltype(k)::value, decltype(v)::value>::CTAS_PER_SM; });
-    const int64_t warps = (int64_t) sk_sm_count()*cps*SK_WARPS;
+    const int wps = sk_dispatch(d.type_k, d.type_v, [](auto k, auto v) {         // resident warps per SM
+        using SM = sk_smem<decltype(k)::value, decltype(v)::value>; return SM::CTAS_PER_SM*SM::WARPS; });
+    const int64_t warps = (int64_t) sk_sm_count()*wps;
     int64_t items = warps/d.n_head_kv;
     if (items < 1) items = 1;
     // no more items than 4-tile pieces of the (host-estimated) work: tiny problems stay in few warps
@@ -891,8 +900,8 @@ static int sk_launch(const sk_args &a, const CUtensorMap &tmK, const CUtensorMap
         configured = true;
     }
     const int64_t warps = (int64_t) a.n_items*a.d.n_head_kv;
-    const unsigned grid = (unsigned) ((warps + SK_WARPS - 1)/SK_WARPS);
-    launch_pdl(sk_main_kernel<TK, TV>, dim3(grid), dim3(32*SK_WARPS), SM::CTA, st, a, tmK, tmV);
+    const unsigned grid = (unsigned) ((warps + SM::WARPS - 1)/SM::WARPS);
+    launch_pdl(sk_main_kernel<TK, TV>, dim3(grid), dim3(32*SM::WARPS), SM::CTA, st, a, tmK, tmV);
     return B200_OK;
 }
 
