@@ -536,7 +536,11 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
     const uint32_t k64k = a.k65536;
 
     while (g0 < g1) {
-        const int pb = P[row], pe = P[row + 1];
+        // P[row], P[row + 1]: the header load holds P[0..27]; a shuffle keeps one global round trip out of the chain
+        // plan -> block table -> first TMA box that every row-segment starts with
+        int pb, pe;
+        if (row < 27) { pb = __shfl_sync(0xffffffffu, head, 4 + row); pe = __shfl_sync(0xffffffffu, head, 5 + row); }
+        else          { pb = P[row]; pe = P[row + 1]; }
         if (pe <= g0) { ++row; continue; }                  // row without tiles
         const int t0 = g0 - pb, t1 = min(g1, pe) - pb;       // tiles [t0, t1) of this row
         const int seq = p.q_seq ? p.q_seq[row] : row;
@@ -544,15 +548,6 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
         const int32_t *bt = p.block_table + (int64_t) seq*p.bt_stride;
         const int seg = FS[row] + (item - pb/chunk);
         const bool single = (FS[row + 1] - FS[row]) == 1;
-
-        // ---- Q fragments (this kv head's query heads in the 8 mma columns)
-        sk_qfrag<TK> qf;
-        {
-            const bool live = g < a.gqa;
-            const float *qrow = reinterpret_cast<const float *>(static_cast<const char *>(p.q) + (int64_t) row*p.nbq1
-                                                                 + (int64_t) (kvh*a.gqa + (live ? g : 0))*p.nbq2);
-            qf.load(qrow, live, a.qscale, lane);
-        }
 
         float O[8][4];
 #pragma unroll
@@ -585,6 +580,16 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
         int issued = 0;
 #pragma unroll
         for (int s = 0; s < STAGES - NSUB; ++s) { if (issued < nt) { issue(); ++issued; } }
+
+        // ---- Q fragments (this kv head's query heads in the 8 mma columns); after the first boxes are on their way,
+        // so the Q round trip runs under theirs instead of in front of it
+        sk_qfrag<TK> qf;
+        {
+            const bool live = g < a.gqa;
+            const float *qrow = reinterpret_cast<const float *>(static_cast<const char *>(p.q) + (int64_t) row*p.nbq1
+                                                                 + (int64_t) (kvh*a.gqa + (live ? g : 0))*p.nbq2);
+            qf.load(qrow, live, a.qscale, lane);
+        }
 
         // One loop iteration = NSUB tiles sharing one softmax step.  FULL iterations (all tiles complete and inside the
         // row's visible range, no softcap) run branch-free between the barrier waits and the rescale vote, so the

@@ -165,6 +165,20 @@ def test_paged_decode_mixed_types_and_normal_inputs(pkg, oracle, cuda, dist, ker
     assert oracle.max_rel_err(want, got) <= 1e-2
 
 
+MIXED = [(F16, Q8_0), (F16, Q4_0), (Q8_0, Q4_0), (Q4_0, Q8_0), (Q4_0, F16)]
+
+
+@pytest.mark.parametrize("tk,tv", MIXED, ids=lambda x: str(x))
+def test_paged_decode_every_mixed_type_pair(pkg, oracle, cuda, tk, tv):
+    """-ctk / -ctv chosen independently (common/arg.cpp cache-type-k / cache-type-v): every pair has its own tile ring
+    (stage size, stage count); long and short rows so the ring wraps and rows split across warps"""
+    import torch
+    w = make_workload(oracle, [2500, 17, 640, 1, 333], 32, 8, 128, tk, tv, seed=101)
+    got = _run_paged(pkg, torch, w, 2)
+    want = oracle_attention(oracle, w)
+    assert oracle.max_rel_err(want, got) <= 1e-2
+
+
 @pytest.mark.parametrize("kernel", [1, 2], ids=["generic", "streamk"])
 @pytest.mark.parametrize("t", TYPES)
 def test_chunked_prefill_rows(pkg, oracle, cuda, t, kernel):
