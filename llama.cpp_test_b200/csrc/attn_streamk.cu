@@ -43,6 +43,7 @@
 namespace b200 {
 
 constexpr int SK_WARPS = 8;
+constexpr int SK_MIN_CHUNK = 4;                              // tiles: a warp's share is never shorter (its prologue costs about two)
 #ifndef SK_Q8_WARPS
 #define SK_Q8_WARPS 8                                         // warps per CTA of the Q8_0/Q8_0 kernel (8 = the three-stage form)
 #endif
@@ -54,6 +55,7 @@ struct sk_args {
     int    gqa;
     int    n_items;                     // upper bound on items per kv head
     int    chunk_align;                 // chunk is rounded up to a multiple of this many tiles (8: the tcgen05 kernel's super-tile)
+    int    chunk_min;                   // and is at least this many tiles
     int   *plan;                        // [4] {total_tiles, chunk, -, -} then P[n_q+1], FS[n_q+1]
     float *part_ml;                     // [max_segs][n_head][2]
     float *part_o;                      // [max_segs][n_head][D]
@@ -249,7 +251,21 @@ sk_plan_kernel(const __grid_constant__ sk_args a) {
     const int total = carry;
     int chunk = (total + a.n_items - 1)/a.n_items;
     if (chunk < 1) chunk = 1;
+    if (chunk < a.chunk_min) chunk = a.chunk_min;
     chunk = (chunk + a.chunk_align - 1)/a.chunk_align*a.chunk_align;
+    // Row-aligned chunks: when some chunk up to a third longer divides every row's first tile index (equal-length
+    // batches, the llama-batched-bench shape), no warp straddles two rows and pays two prologues, two partial
+    // stores: 32 x 1024 Q4_0, 7 -> 8 tiles per warp, 1880 -> 2024 GB/s.  Only for short chunks, where that overhead counts.
+    if (chunk <= 32 && a.chunk_align == 1) {
+        __syncthreads();                                     // P[] of the whole CTA
+        int best = 0;
+        for (int c = chunk; c <= chunk + (chunk + 2)/3 && !best; ++c) {
+            int ok = 1;
+            for (int r = threadIdx.x; r < p.n_q; r += 1024) ok &= (P[r] % c == 0);
+            if (__syncthreads_and(ok)) best = c;
+        }
+        if (best) chunk = best;
+    }
     if (threadIdx.x == 0) { P[p.n_q] = total; a.plan[0] = total; a.plan[1] = chunk; a.plan[2] = (total + chunk - 1)/chunk; a.plan[3] = 0; }
     __syncthreads();
     carry = 0;
@@ -809,12 +825,9 @@ static int sk_items(const b200_attn_desc &d) {
     const int64_t warps = (int64_t) sk_sm_count()*wps;
     int64_t items = warps/d.n_head_kv;
     if (items < 1) items = 1;
-    // no more items than 4-tile pieces of the (host-estimated) work: tiny problems stay in few warps
-    int64_t tok = d.total_tokens > 0 ? d.total_tokens
-                : (int64_t) d.n_q*(d.max_seq_len > 0 ? d.max_seq_len : d.bt_stride*d.block_size);
-    int64_t cap = tok/(4*SK_TILE) + 1;
-    if (cap < d.n_q) cap = d.n_q;
-    if (items > cap) items = cap;
+    // always the whole machine: small problems are kept in few warps by the plan's minimum chunk (SK_MIN_CHUNK tiles),
+    // the surplus CTAs leave after the header load.  (A grid cut to the work, 129 CTAs for 8 x 1024, measured 4 % slower
+    // than 148 with the same 128 active: profiles/r1v_plan_ab.txt.)
     return (int) items;
 }
 
@@ -934,6 +947,7 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st) {
     const bool dq = dq_wanted(d);
     a.n_items = dq ? dq_items(d) : sk_items(d);
     a.chunk_align = dq ? DQ_TOK/SK_TILE : 1;
+    a.chunk_min = dq ? 1 : SK_MIN_CHUNK;
     const size_t max_segs = (size_t) sk_items(d) + d.n_q;    // the layout streamk_workspace() promised
     char *ws = static_cast<char *>(d.workspace);
     a.plan = reinterpret_cast<int *>(ws);
