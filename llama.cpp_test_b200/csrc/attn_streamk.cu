@@ -42,6 +42,9 @@
 
 namespace b200 {
 
+#ifndef SK_BIAS_MMA
+#define SK_BIAS_MMA 0                                         // 1: remove the V expansion bias with a constant-A MMA per m-tile
+#endif
 constexpr int SK_WARPS = 8;
 constexpr int SK_MIN_CHUNK = 4;                              // tiles: a warp's share is never shorter (its prologue costs about two)
 #ifndef SK_Q8_WARPS
@@ -405,14 +408,15 @@ __device__ __forceinline__ void sk_qk_quant(float (&S)[4], uint32_t kb, int mis,
 
 // ------------------------------------------------------------------------------------------------
 // O^T += V^T . P^T ; 8 m-tiles of 16 d-rows.
-// Quantised V costs NO per-element arithmetic beyond the byte/nibble -> half expansion:
+// Quantised V costs one HADD2 per operand register (two elements) beyond the byte/nibble -> half expansion:
 //   * the block scale d[token][blk] is folded into the B operand: b = P * d (one HMUL2 per register and block, the
 //     16 rows of an m-tile all belong to ONE 32-element block, so the scale depends on (token, block) only);
-//   * the bias of the exponent trick (1152 + q for Q8_0; (1024 + 16 n)/16 = 64 + n for Q4_0, whose b carries an
-//     extra 1/16) is removed on the tensor core: one more MMA per m-tile with A = -1152 everywhere adds
-//     -1152 * sum_tok b = -(bias) * sum_tok P d to the accumulator BEFORE the data MMA, so the accumulator only
-//     ever strays from the true value by one tile's bias (FP32 error ~1e-7 relative; the tensor pipe was 18 %
-//     busy, profiles/r1f_sk_q4_0_ncu_full.txt).  Result: sum_tok (q | n - 8) * d * P, i.e. dequantize_row_*
+//   * the bias of the exponent trick (1152 + q for Q8_0; 1024 + n and 1024 + 16 n for Q4_0's low / high nibbles, whose b
+//     carries an extra 1/16 for the high ones) leaves the A operand by one exact HADD2 per register: (1152 + q) - 1152,
+//     (1024 + n) - 1032 = n - 8, (1024 + 16 n) - 1152 = 16 (n - 8) are all representable.  (SK_BIAS_MMA=1 is the earlier
+//     form: one more MMA per m-tile with A = -bias everywhere.  ptxas rebuilt that constant 4-register operand with
+//     3 MOVs per MMA under the 128-register cap, 9 % of the loop's instructions; r1v: Q4_0 3650 -> 3895 GB/s without it.)
+//     Result: sum_tok (q | n - 8) * d * P, i.e. dequantize_row_*
 //     (ggml/src/ggml-quants.c:255-273, :349-362) times P with P*d rounded to half once.
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void sk_pv_f16(float (&O)[8][4], uint32_t vb, uint32_t p0, uint32_t p1, int lane) {
@@ -456,8 +460,13 @@ __device__ __forceinline__ void sk_pv_quant(float (&O)[8][4], uint32_t vb, int m
             const uint32_t x23l = q8_bias(prmt(W2, W3, 0x5410)), x23h = q8_bias(prmt(W2, W3, 0x7632));
             a[0] = q8_e02(x01l, kc.x); a[1] = q8_e13(x01l, kc.x); a[2] = q8_e02(x23l, kc.x); a[3] = q8_e13(x23l, kc.x);
             c[0] = q8_e02(x01h, kc.x); c[1] = q8_e13(x01h, kc.x); c[2] = q8_e02(x23h, kc.x); c[3] = q8_e13(x23h, kc.x);
-            mma_16816(O[2*blk],     neg, b0, b1);
-            mma_16816(O[2*blk + 1], neg, b0, b1);
+            if constexpr (SK_BIAS_MMA) {
+                mma_16816(O[2*blk],     neg, b0, b1);
+                mma_16816(O[2*blk + 1], neg, b0, b1);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { a[j] = hadd2_u(a[j], NEG); c[j] = hadd2_u(c[j], NEG); }     // (1152 + q) - 1152, exact
+            }
             mma_16816(O[2*blk],     a,   b0, b1);
             mma_16816(O[2*blk + 1], c,   b0, b1);
         } else {                                             // lane g: bytes 2g, 2g+1 -> d = 32 blk + 2g + {0,1} (low), + 16 (high nibbles)
@@ -469,8 +478,13 @@ __device__ __forceinline__ void sk_pv_quant(float (&O)[8][4], uint32_t vb, int m
             const uint32_t NEGLO = 0xE408E408u;              // half2(-1032)
             const uint32_t neglo[4] = {NEGLO, NEGLO, NEGLO, NEGLO};
             const uint32_t h0 = hmul2_u(b0, 0x2C002C00u), h1 = hmul2_u(b1, 0x2C002C00u);      // * 1/16 (exact)
-            mma_16816(O[2*blk],     neglo, b0, b1);
-            mma_16816(O[2*blk + 1], neg,   h0, h1);
+            if constexpr (SK_BIAS_MMA) {
+                mma_16816(O[2*blk],     neglo, b0, b1);
+                mma_16816(O[2*blk + 1], neg,   h0, h1);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { a[j] = hadd2_u(a[j], NEGLO); c[j] = hadd2_u(c[j], NEG); }   // n - 8 and 16 (n - 8), exact
+            }
             mma_16816(O[2*blk],     a,     b0, b1);
             mma_16816(O[2*blk + 1], c,     h0, h1);
         }
