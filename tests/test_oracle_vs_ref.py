@@ -110,3 +110,34 @@ def test_attention_softcap_and_alibi_dense(oracle, ref):
         fa, _ = ref.attention(0, q, k, v, F16, F16, n_head_kv, n_kv, mask, 0.088, max_bias, softcap, n_threads=2)
         assert oracle.max_rel_err(f32, got) < 2e-5, (max_bias, softcap)
         assert oracle.nmse(fa, got) < 5e-4
+
+
+@pytest.mark.parametrize("t", TYPES)
+@pytest.mark.parametrize("hs", [64, 128])
+def test_oracle_vs_reference_over_the_reference_test_grid(oracle, ref, hs, t):
+    """The whole test_flash_attn_ext loop nest of tests/test-backend-ops.cpp:4367-4391 (the grid the GPU path is run over
+    in tests/test_gpu_ggml_entry.py), oracle against the reference CPU backend: F32 formulation to 2e-5 (3e-5 with
+    softcap: tanhf), the FLASH_ATTN_EXT op to its own NMSE bar"""
+    from test_gpu_ggml_entry import _grid
+    worst = [0.0, 0.0]
+    for i, c in enumerate(_grid(hs)):
+        if c["permuted"]:
+            continue                                         # same values, other strides: the harness takes token-major caches
+        rng = np.random.default_rng(4321 + i)
+        nh, n_head, kv, nb = 4, 4 * c["nr"], c["kv"], c["nb"]
+        q = rng.uniform(-1, 1, (nb, n_head, hs)).astype(np.float32)
+        k = oracle.from_float(t, rng.uniform(-1, 1, (kv * nh, hs)).astype(np.float32)).reshape(kv, -1)
+        v = oracle.from_float(t, rng.uniform(-1, 1, (kv * nh, hs)).astype(np.float32)).reshape(kv, -1)
+        m = None
+        if c["mask"]:
+            m = rng.uniform(-1, 1, ((nb + 63) // 64 * 64, kv)).astype(np.float16)
+            m[0, kv // 3: kv // 2] = -np.inf
+        scale = 1.0 / np.sqrt(hs)
+        got = oracle.attention(q, k, v, t, t, nh, scale, mask=m, n_kv=kv, max_bias=c["max_bias"], softcap=c["softcap"])
+        f32, _ = ref.attention(1, q, k, v, t, t, nh, kv, m, scale, c["max_bias"], c["softcap"], n_threads=2)
+        fa, _ = ref.attention(0, q, k, v, t, t, nh, kv, m, scale, c["max_bias"], c["softcap"], n_threads=2)
+        e1, e2 = oracle.max_rel_err(f32, got), oracle.nmse(fa, got)
+        worst = [max(worst[0], e1), max(worst[1], e2)]
+        assert e1 < (3e-5 if c["softcap"] else 2e-5), (c, e1)
+        assert e2 < 5e-4, (c, e2)
+    assert worst[0] > 0.0                                    # the loop ran
