@@ -143,3 +143,31 @@ def test_supports_op_mirrors_reference_rules(pkg):
     dstc = tensor(pkg.TYPE_Q8_0, [1024, 16], op=pkg.GGML_OP_CPY)
     dstc.src[0] = C.pointer(odd); dstc.src[1] = C.pointer(dstc)
     assert pkg.lib.b200_supports_op(C.byref(dstc)) == 0
+
+
+def test_sass_of_the_hot_kernels_is_sm100a_tma_and_tcgen05(pkg, tmp_path):
+    """The built library carries sm_100a SASS only, the decode kernel gathers with TMA (UTMALDG) and computes with HMMA,
+    the prefill and the Q8_0 tile kernels issue tcgen05 MMAs (UTCHMMA) with TMEM loads (the mnemonics
+    /opt/skills/guides/B200_PROFILING.md names as proof) — a build-level guard against a silent fallback path"""
+    import shutil
+    import subprocess
+    exe = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(exe):
+        pytest.skip("cuobjdump not available")
+    elf = subprocess.run([exe, "-lelf", pkg.LIB_PATH], capture_output=True, text=True).stdout
+    assert "sm_100a" in elf and not any(a in elf for a in ("sm_90", "sm_80", "sm_100.")), elf
+    sass = subprocess.run([exe, "-sass", pkg.LIB_PATH], capture_output=True, text=True).stdout
+    funcs, cur = {}, None
+    for line in sass.splitlines():
+        if "Function :" in line:
+            cur = line.split("Function :")[1].strip()
+            funcs[cur] = set()
+        elif cur:
+            for m in ("UTMALDG", "UTCHMMA", "HMMA.16816", "LDTM", "STTM", "SYNCS"):
+                if m in line:
+                    funcs[cur].add(m)
+    sk = [f for f in funcs if "sk_main_kernel" in f]
+    assert len(sk) == 9 and all({"UTMALDG", "HMMA.16816", "SYNCS"} <= funcs[f] for f in sk), {f: funcs[f] for f in sk}
+    for name in ("pf_main_kernel", "dq_main_kernel"):
+        fs = [f for f in funcs if name in f]
+        assert fs and all({"UTMALDG", "UTCHMMA", "LDTM"} <= funcs[f] for f in fs), {f: funcs[f] for f in fs}
