@@ -34,6 +34,16 @@ B200_API void    b200_pc_destroy(b200_paged_cache *pc);
  * slot_mapping receives n_new cells; cow_pairs receives [n][2] = (src_block, dst_block). */
 B200_API int64_t b200_pc_append(b200_paged_cache *pc, int32_t seq, int64_t n_new, int32_t *slot_mapping,
                                 int32_t *cow_pairs, int64_t cow_cap);
+/* One ubatch of llama_context::decode's KV section in the paged form (src/llama-context.cpp:1291-1353 find_slot +
+ * src/llama-graph.cpp:403-477 mask fill): token i of sequence seq[i] at position pos[i] (pos NULL: positions continue
+ * each sequence) gets slot_mapping[i] (its cell, for b200_kv_write), q_seq[i] (row of its sequence in seqs[], the
+ * order of first appearance: export those rows with b200_pc_export) and q_pos[i].  seqs[] needs room for one entry
+ * per distinct sequence (n_tokens always suffices), cow_pairs for one (src, dst) pair per distinct sequence.
+ * 0 ok; 1 not enough free blocks (llama_decode's "no KV slot"); -1 positions do not continue their sequence or bad
+ * arguments; -3 cow_cap too small.  Nothing changes unless 0 is returned. */
+B200_API int32_t b200_pc_prepare_batch(b200_paged_cache *pc, int64_t n_tokens, const int32_t *seq, const int32_t *pos,
+                                       int32_t *slot_mapping, int32_t *q_seq, int32_t *q_pos, int32_t *seqs, int64_t *n_seqs,
+                                       int32_t *cow_pairs, int64_t cow_cap, int64_t *n_cow);
 B200_API int32_t b200_pc_seq_cp(b200_paged_cache *pc, int32_t src, int32_t dst, int64_t p0, int64_t p1);   /* 1 ok / 0 refused */
 B200_API int32_t b200_pc_seq_rm(b200_paged_cache *pc, int32_t seq, int64_t p0, int64_t p1);
 B200_API void    b200_pc_seq_keep(b200_paged_cache *pc, int32_t seq);

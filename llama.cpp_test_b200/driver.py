@@ -372,6 +372,22 @@ class PagedKVCache:
             return None
         return [slots[i] for i in range(n_new)], [(cow[2 * i], cow[2 * i + 1]) for i in range(n)]
 
+    def prepare_batch(self, seq, pos=None):
+        """one ubatch (llama_context::decode's find_slot + mask fill, paged form): -> dict(slot_mapping, q_seq, q_pos, seqs,
+        cow_pairs), or the status 1 (no room) / -1 (positions do not continue their sequence); see include/b200_host.h"""
+        n = len(seq)
+        arr = lambda v: (C.c_int32 * max(n, 1))(*v)
+        s_in, p_in = arr(seq), (arr(pos) if pos is not None else None)
+        slots, q_seq, q_pos, seqs, cow = (C.c_int32 * max(n, 1))(), (C.c_int32 * max(n, 1))(), (C.c_int32 * max(n, 1))(), \
+            (C.c_int32 * max(n, 1))(), (C.c_int32 * (2 * max(n, 1)))()
+        n_seqs, n_cow = C.c_int64(0), C.c_int64(0)
+        rc = lib.b200_pc_prepare_batch(self._h, n, s_in, p_in, slots, q_seq, q_pos, seqs, C.byref(n_seqs), cow, max(n, 1),
+                                       C.byref(n_cow))
+        if rc != 0:
+            return rc
+        return dict(slot_mapping=list(slots[:n]), q_seq=list(q_seq[:n]), q_pos=list(q_pos[:n]), seqs=list(seqs[:n_seqs.value]),
+                    cow_pairs=[(cow[2 * i], cow[2 * i + 1]) for i in range(n_cow.value)])
+
     def seq_cp(self, src: int, dst: int, p0: int = 0, p1: int = -1) -> bool:
         return bool(lib.b200_pc_seq_cp(self._h, src, dst, p0, p1))
 

@@ -2,6 +2,7 @@
 #include "b200_host.h"
 #include "capi_types.h"
 
+#include <algorithm>
 #include <new>
 #include <vector>
 
@@ -33,6 +34,27 @@ B200_API int64_t b200_pc_append(b200_paged_cache *pc, int32_t seq, int64_t n_new
     for (size_t i = 0; i < slots.size(); ++i) slot_mapping[i] = slots[i];
     for (size_t i = 0; i < cow.size(); ++i) { cow_pairs[2*i] = cow[i].first; cow_pairs[2*i + 1] = cow[i].second; }
     return (int64_t) cow.size();
+}
+B200_API int32_t b200_pc_prepare_batch(b200_paged_cache *pc, int64_t n_tokens, const int32_t *seq, const int32_t *pos,
+                                       int32_t *slot_mapping, int32_t *q_seq, int32_t *q_pos, int32_t *seqs, int64_t *n_seqs,
+                                       int32_t *cow_pairs, int64_t cow_cap, int64_t *n_cow) {
+    if (!pc || n_tokens < 0 || (n_tokens > 0 && (!seq || !slot_mapping || !q_seq || !q_pos || !seqs))) return -1;
+    // at most one copy-on-write pair per sequence, at most one sequence per token: refuse before changing anything
+    {
+        std::vector<int32_t> distinct(seq, seq + n_tokens);
+        std::sort(distinct.begin(), distinct.end());
+        const int64_t n_distinct = (int64_t) (std::unique(distinct.begin(), distinct.end()) - distinct.begin());
+        if (cow_cap < n_distinct) return -3;
+    }
+    PagedKVCache::BatchInputs in;
+    const int rc = pc->impl.prepare_batch(n_tokens, seq, pos, in);
+    if (rc != 0) return rc;
+    for (int64_t i = 0; i < n_tokens; ++i) { slot_mapping[i] = in.slot_mapping[(size_t) i]; q_seq[i] = in.q_seq[(size_t) i]; q_pos[i] = in.q_pos[(size_t) i]; }
+    for (size_t r = 0; r < in.seqs.size(); ++r) seqs[r] = in.seqs[r];
+    if (n_seqs) *n_seqs = (int64_t) in.seqs.size();
+    for (size_t i = 0; i < in.cow_pairs.size(); ++i) { cow_pairs[2*i] = in.cow_pairs[i].first; cow_pairs[2*i + 1] = in.cow_pairs[i].second; }
+    if (n_cow) *n_cow = (int64_t) in.cow_pairs.size();
+    return 0;
 }
 B200_API int32_t b200_pc_seq_cp(b200_paged_cache *pc, int32_t s, int32_t d, int64_t p0, int64_t p1) { return pc->impl.seq_cp(s, d, p0, p1) ? 1 : 0; }
 B200_API int32_t b200_pc_seq_rm(b200_paged_cache *pc, int32_t s, int64_t p0, int64_t p1) { return pc->impl.seq_rm(s, p0, p1) ? 1 : 0; }

@@ -55,6 +55,42 @@ bool PagedKVCache::append(seq_id seq, int64_t n_new, std::vector<int32_t> & slot
     return true;
 }
 
+int PagedKVCache::prepare_batch(int64_t n_tokens, const seq_id * seq, const int32_t * pos, BatchInputs & out) {
+    out = BatchInputs();
+    if (n_tokens < 0 || (n_tokens > 0 && !seq)) return -1;
+    std::map<seq_id, int32_t> row;                       // sequence -> row, in order of first appearance
+    std::vector<int64_t> n_new;
+    for (int64_t i = 0; i < n_tokens; ++i) {
+        auto it = row.find(seq[i]);
+        if (it == row.end()) { it = row.emplace(seq[i], (int32_t) out.seqs.size()).first; out.seqs.push_back(seq[i]); n_new.push_back(0); }
+        const int64_t want = seq_len(seq[i]) + n_new[(size_t) it->second];
+        if (seq[i] < 0 || (pos && pos[i] != want)) { out = BatchInputs(); return -1; }
+        out.q_seq.push_back(it->second);
+        out.q_pos.push_back((int32_t) want);
+        ++n_new[(size_t) it->second];
+    }
+    // the appends are sequential and each is all-or-nothing; undo the earlier ones when a later one fails
+    const std::vector<int32_t> ref0 = ref_;
+    const auto free0 = free_;
+    const int64_t n_free0 = n_free_;
+    const std::map<seq_id, Seq> seqs0 = seqs_;
+    std::vector<std::vector<int32_t>> slots(out.seqs.size());
+    for (size_t r = 0; r < out.seqs.size(); ++r) {
+        if (!append(out.seqs[r], n_new[r], slots[r], out.cow_pairs)) {
+            ref_ = ref0; free_ = free0; n_free_ = n_free0; seqs_ = seqs0;
+            out = BatchInputs();
+            return 1;
+        }
+    }
+    std::vector<size_t> next(out.seqs.size(), 0);
+    out.slot_mapping.resize((size_t) n_tokens);
+    for (int64_t i = 0; i < n_tokens; ++i) {
+        const size_t r = (size_t) out.q_seq[(size_t) i];
+        out.slot_mapping[(size_t) i] = slots[r][next[r]++];
+    }
+    return 0;
+}
+
 bool PagedKVCache::seq_cp(seq_id src, seq_id dst, int64_t p0, int64_t p1) {
     if (p0 > 0) return false;
     auto it = seqs_.find(src);

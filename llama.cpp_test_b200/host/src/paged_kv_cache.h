@@ -34,6 +34,22 @@ public:
     bool append(seq_id seq, int64_t n_new, std::vector<int32_t> & slot_mapping,
                 std::vector<std::pair<int32_t, int32_t>> & cow_pairs);
 
+    // One ubatch of llama_context::decode's KV section (src/llama-context.cpp:1291-1353: find_slot for the whole ubatch,
+    // then llm_graph_input_attn_kv_unified::set_input, src/llama-graph.cpp:403-477, fills the [n_kv, n_tokens] mask with
+    // 0 where the cell holds the token's sequence at a position <= the token's, -inf elsewhere) in the paged form:
+    // token i of sequence seq[i] at position pos[i] gets its cell slot_mapping[i] and the query-row inputs q_seq[i] (the
+    // row of its sequence in `seqs`, the order of first appearance = the row order of export_tables(seqs)) and
+    // q_pos[i] = pos[i]; a row then sees positions [0, q_pos] of its own block-table row, which is exactly the set the
+    // mask marks.  Sequences may interleave in the batch.  pos == nullptr: positions continue each sequence.
+    // Returns 0; 1 when the blocks do not suffice (llama_decode's "could not find a KV slot", nothing changes);
+    // -1 for positions that do not continue their sequence (a paged sequence has no holes), nothing changes.
+    struct BatchInputs {
+        std::vector<int32_t> slot_mapping, q_seq, q_pos;
+        std::vector<seq_id>  seqs;
+        std::vector<std::pair<int32_t, int32_t>> cow_pairs;
+    };
+    int prepare_batch(int64_t n_tokens, const seq_id * seq, const int32_t * pos, BatchInputs & out);
+
     // llama_kv_self_seq_cp semantics restricted to prefixes (p0 <= 0): dst becomes positions [0, p1) of src,
     // sharing blocks.  p1 < 0 means "to the end".  Returns false for p0 > 0 or unknown src.
     bool seq_cp(seq_id src, seq_id dst, int64_t p0, int64_t p1);

@@ -162,3 +162,79 @@ def test_equivalent_to_unified_cache_visibility(pkg, seed):
             refs[bt[0]] += 1
     assert refs.tolist() == [pc.ref_count(b) for b in range(nb)]
     assert pc.n_free() == int((refs == 0).sum())
+
+
+def test_prepare_batch_interleaved_sequences(pkg):
+    """one ubatch with interleaved sequences: cells, query rows and positions, and the row order of the exported table"""
+    pc = pkg.PagedKVCache(16, 4)
+    pc.append(7, 6)                                           # seq 7 holds 6 tokens: blocks 0, 1
+    r = pc.prepare_batch([7, 3, 7, 3, 9], pos=[6, 0, 7, 1, 0])
+    assert r["seqs"] == [7, 3, 9] and r["q_seq"] == [0, 1, 0, 1, 2] and r["q_pos"] == [6, 0, 7, 1, 0]
+    assert r["slot_mapping"] == [6, 8, 7, 9, 12] and r["cow_pairs"] == []     # seq 7 fills block 1; seq 3 -> block 2; seq 9 -> block 3
+    bt, lens = pc.export(r["seqs"], 3)
+    assert lens == [8, 2, 1] and bt == [[0, 1, 0], [2, 0, 0], [3, 0, 0]]
+    assert pc.prepare_batch([3, 3], pos=[2, 4]) == -1 and pc.seq_len(3) == 2  # a hole: refused, nothing changed
+    assert pc.prepare_batch([3], pos=[1]) == -1                               # position already cached
+    r = pc.prepare_batch([9, 9, 3])                                           # pos None: positions continue
+    assert r["q_pos"] == [1, 2, 2] and r["seqs"] == [9, 3]
+
+
+def test_prepare_batch_is_all_or_nothing(pkg):
+    pc = pkg.PagedKVCache(4, 4)
+    pc.append(0, 6)                                           # blocks 0, 1 (1 is half full)
+    pc.seq_cp(0, 1)
+    before = (pc.n_free(), pc.seq_len(0), pc.seq_len(1), [pc.ref_count(b) for b in range(4)])
+    # seq 1 needs a copy-on-write block, seq 2 needs 2 blocks: 3 > 2 free -> "no KV slot", nothing may change
+    assert pc.prepare_batch([1, 2, 2, 2, 2, 2]) == 1
+    assert before == (pc.n_free(), pc.seq_len(0), pc.seq_len(1), [pc.ref_count(b) for b in range(4)]) and pc.seq_len(2) == 0
+    r = pc.prepare_batch([1, 2, 2])                           # CoW (block 1 -> 2) + one block for seq 2
+    assert r["cow_pairs"] == [(1, 2)] and r["slot_mapping"] == [2 * 4 + 2, 12, 13] and pc.n_free() == 0
+
+
+@pytest.mark.parametrize("seed", range(5))
+def test_prepare_batch_equals_the_reference_mask(pkg, seed):
+    """llm_graph_input_attn_kv_unified::set_input (src/llama-graph.cpp:428-460) lets token (seq s, pos p) see the cells whose
+    seq set holds s and whose pos <= p.  The paged inputs must name exactly those cells, in position order."""
+    rng = np.random.default_rng(100 + seed)
+    bs, nb = int(rng.choice([1, 4, 16])), 96
+    pc, um = pkg.PagedKVCache(nb, bs), UnifiedModel()
+    content = np.full(nb * bs, -1, dtype=np.int64)
+    next_tok = 0
+    for _ in range(120):
+        op = rng.choice(["batch", "batch", "batch", "cp", "trunc", "rm"])
+        seqs = [s for s in range(5) if pc.seq_len(s) > 0]
+        if op == "batch":
+            n = int(rng.integers(1, 3 * bs + 3))
+            seq = [int(s) for s in rng.integers(0, 5, n)]                    # interleaved
+            r = pc.prepare_batch(seq)
+            if r == 1:
+                continue
+            for a, b in r["cow_pairs"]:
+                content[b * bs:(b + 1) * bs] = content[a * bs:(a + 1) * bs]
+            toks = list(range(next_tok, next_tok + n)); next_tok += n
+            content[r["slot_mapping"]] = toks
+            for s, t in zip(seq, toks):
+                um.append(s, [t])
+            stride = max((pc.seq_len(s) + bs - 1) // bs for s in r["seqs"])
+            bt, lens = pc.export(r["seqs"], stride)
+            for i in range(n):                                               # every query row of the batch
+                s, p = seq[i], r["q_pos"][i]
+                want = [c[2] for c in sorted((c for c in um.cells if s in c[1] and c[0] <= p), key=lambda c: c[0])]
+                row = np.asarray(bt[r["q_seq"][i]])
+                n_vis = min(lens[r["q_seq"][i]], p + 1)
+                pos = np.arange(n_vis)
+                assert content[row[pos // bs] * bs + pos % bs].tolist() == want
+                assert want[-1] == toks[i]                                   # it sees itself last
+        elif op == "cp" and seqs:
+            src, dst = int(rng.choice(seqs)), int(rng.integers(0, 5))
+            p1 = int(rng.integers(1, pc.seq_len(src) + 1))
+            assert pc.seq_cp(src, dst, 0, p1)
+            um.seq_cp(src, dst, p1)
+        elif op == "trunc" and seqs:
+            s = int(rng.choice(seqs)); p0 = int(rng.integers(0, pc.seq_len(s) + 1))
+            assert pc.seq_rm(s, p0, -1)
+            um.seq_rm(s, p0)
+        elif op == "rm" and seqs:
+            s = int(rng.choice(seqs))
+            assert pc.seq_rm(s)
+            um.seq_rm(s)
