@@ -88,6 +88,14 @@ bool llama_kv_cache_paged::find_slot(llama_seq_id seq_id, int32_t n_tokens, std:
     return cache_.append(seq_id, n_tokens, slot_mapping, cow_pairs);
 }
 
+int llama_kv_cache_paged::find_slot(int32_t n_tokens, const llama_seq_id * seq_id, const llama_pos * pos,
+                                    PagedKVCache::BatchInputs & out) {
+    out = PagedKVCache::BatchInputs();
+    if (!work_.empty()) { unsupported_ = true; return 1; }
+    for (int32_t i = 0; i < n_tokens; ++i) { if (open_.count(seq_id[i])) { unsupported_ = true; return 1; } }
+    return cache_.prepare_batch(n_tokens, seq_id, pos, out);
+}
+
 bool llama_kv_cache_paged::update(pending_work & out) {
     out = pending_work();
     if (!open_.empty() || unsupported_) { unsupported_ = true; return false; }

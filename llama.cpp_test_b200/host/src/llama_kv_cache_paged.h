@@ -64,6 +64,10 @@ public:
     // false: no room (llama_decode returns 1) or an open middle removal (a request the block table cannot express)
     bool find_slot(llama_seq_id seq_id, int32_t n_tokens, std::vector<int32_t> & slot_mapping,
                    std::vector<std::pair<int32_t, int32_t>> & cow_pairs);
+    // the reference's own shape, find_slot(const llama_ubatch &) (src/llama-kv-cache.cpp:453-672): every token of the ubatch,
+    // sequences interleaved; also yields the op's per-row inputs.  Same statuses as PagedKVCache::prepare_batch (0 / 1 /
+    // -1); 1 as well while deferred work is pending.
+    int find_slot(int32_t n_tokens, const llama_seq_id * seq_id, const llama_pos * pos, PagedKVCache::BatchInputs & out);
     // kv_self_update: everything deferred since the last call.  false: a pending request could not be expressed
     // (`unsupported()` tells which kind) — the work lists are then empty and the cache is unchanged by this call.
     bool update(pending_work & out);

@@ -78,6 +78,17 @@ static void scenario_basic() {
     kv2.clear();
     CHECK(kv2.find_slot(3, 9, slots, cow) && kv2.seq_rm(3, 1, 3));
     CHECK(!kv2.update(w));                                   // open removal never closed
+    // the ubatch form: interleaved sequences, per-row inputs, refused while a context shift is pending
+    llama_kv_cache_paged kv3(8, 4);
+    PagedKVCache::BatchInputs in;
+    const llama_seq_id sq[5] = {2, 5, 2, 5, 2}; const llama_pos ps[5] = {0, 0, 1, 1, 2};
+    CHECK(kv3.find_slot(5, sq, ps, in) == 0 && in.seqs == std::vector<int32_t>({2, 5}));
+    CHECK(in.q_seq == std::vector<int32_t>({0, 1, 0, 1, 0}) && in.q_pos == std::vector<int32_t>({0, 0, 1, 1, 2}));
+    CHECK(in.slot_mapping == std::vector<int32_t>({0, 4, 1, 5, 2}) && kv3.seq_pos_max(2) == 2 && kv3.seq_pos_max(5) == 1);
+    const llama_pos hole[1] = {7};
+    CHECK(kv3.find_slot(1, sq, hole, in) == -1 && kv3.seq_pos_max(2) == 2);
+    CHECK(kv3.seq_rm(2, 0, 1)); kv3.seq_add(2, 1, -1, -1);   // context shift of sequence 2, not applied yet
+    CHECK(kv3.find_slot(1, sq + 1, nullptr, in) == 1 && kv3.unsupported());
 }
 
 static void scenario_random(unsigned seed) {
