@@ -141,3 +141,18 @@ def test_oracle_vs_reference_over_the_reference_test_grid(oracle, ref, hs, t):
         assert e1 < (3e-5 if c["softcap"] else 2e-5), (c, e1)
         assert e2 < 5e-4, (c, e2)
     assert worst[0] > 0.0                                    # the loop ran
+
+
+@pytest.mark.parametrize("t", [F16, Q8_0, Q4_0])
+def test_quantize_fns_thresholds_on_the_reference_test_data(oracle, ref, t):
+    """tests/test-quantize-fns.cpp on the cache types: its synthetic vector 0.1 + 2 cos(i + offset) (:32-36, test_size
+    32 * 128 :119), total quantisation error array_rmse(x, dequant(quant(x))) < 0.002 (:18, :134-141) and the quantiser
+    against from_float_ref < 0.0001 (:17, :143-147) — here the second is byte equality with the reference's bytes"""
+    n = 32 * 128
+    x = (0.1 + 2.0 * np.cos(np.arange(n, dtype=np.float32) + np.float32(0.0))).astype(np.float32).reshape(-1, 128)
+    b = oracle.from_float(t, x)
+    assert np.array_equal(b, ref.quantize(t, x))
+    back = oracle.to_float(t, b, 128)
+    assert np.array_equal(back, ref.to_float(t, b, 128))
+    rmse = float(np.sqrt(np.sum((x.astype(np.float64) - back) ** 2)) / n)          # array_rmse divides by n, not sqrt(n)
+    assert rmse < 0.002, rmse
