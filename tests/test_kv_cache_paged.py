@@ -31,3 +31,21 @@ def test_library_exports_the_adapter():
     out = subprocess.run(["nm", "-DC", "--defined-only", lib], capture_output=True, text=True).stdout
     for m in ("llama_kv_cache_paged::seq_rm", "llama_kv_cache_paged::seq_add", "llama_kv_cache_paged::update", "llama_kv_cache_paged::find_slot"):
         assert m in out, m
+
+
+def test_paged_cache_stress_under_sanitizers(tmp_path):
+    """tests/cpp/paged_cache_stress.cpp: 12 seeded streams of 1500 calls over PagedKVCache (append, prepare_batch, seq_cp, seq_rm,
+    seq_keep, context_shift, defrag) in small pools, built with AddressSanitizer + UBSan where the toolchain has them; after
+    every call the reference counts are recomputed from the block tables and the free count must close the books"""
+    exe = str(tmp_path / "paged_cache_stress")
+    base = ["g++", "-std=c++17", "-g", "-O1", "-Wall", "-Wextra", "-I", os.path.join(HOST, "src"),
+            os.path.join(ROOT, "tests", "cpp", "paged_cache_stress.cpp"), os.path.join(HOST, "paged_kv_cache.cpp"), "-o", exe]
+    r = subprocess.run(base + ["-fsanitize=address,undefined", "-fno-omit-frame-pointer"], capture_output=True, text=True)
+    if r.returncode != 0:                                   # no sanitizer runtime on this machine: the invariants still run
+        r = subprocess.run(base, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    run = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert run.returncode == 0, (run.stdout[-1500:], run.stderr[-3000:])
+    lines = run.stdout.strip().splitlines()
+    assert lines[-1] == "OK" and len(lines) == 13
+    assert sum(int(l.split(",")[2].split()[0]) for l in lines[:-1]) > 500         # the refusal paths ran
