@@ -161,3 +161,24 @@ def test_defrag_compacts_and_preserves_every_sequence(pkg):
     assert c.defrag() == []                                       # idempotent
     r = c.append(99, bs)                                          # the allocator still hands out the lowest free block
     assert r is not None and r[0][0] == n_used*bs
+
+
+def test_parser_on_damaged_streams_under_address_sanitizer(tmp_path):
+    """tests/cpp/kv_state_fuzz.cpp: every truncation and 4000 seeded corruptions of a valid stream, each in a heap buffer of
+    exactly its own length (a read past the end faults under ASan); the parser answers 0 or a B200_STATE_ERR_* and the
+    offsets it hands out stay inside the buffer — the reference throws on the same conditions (llama-kv-cache.cpp:1005-1240)"""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    host = os.path.join(root, "llama.cpp_test_b200", "host")
+    exe = str(tmp_path / "kv_state_fuzz")
+    base = ["g++", "-std=c++17", "-g", "-O1", "-Wall", "-Wextra", "-I", os.path.join(root, "include"), "-I", os.path.join(host, "src"),
+            os.path.join(root, "tests", "cpp", "kv_state_fuzz.cpp"), os.path.join(host, "kv_state.cpp"),
+            os.path.join(host, "paged_kv_cache.cpp"), "-o", exe]
+    r = subprocess.run(base + ["-fsanitize=address,undefined", "-fno-omit-frame-pointer"], capture_output=True, text=True)
+    if r.returncode != 0:
+        r = subprocess.run(base, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    run = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert run.returncode == 0 and run.stdout.strip().endswith("OK"), (run.stdout[-1500:], run.stderr[-3000:])
+    assert "runtime error" not in run.stderr, run.stderr[-3000:]
