@@ -91,7 +91,9 @@ enum {
     B200_STATE_ERR_LAYERS       = -4,   /* mismatched layer count                                               :1112 */
     B200_STATE_ERR_VTRANS       = -5,   /* incompatible V transposition                                         :1120 */
     B200_STATE_ERR_TYPE         = -6,   /* mismatched key / value type                                     :1132,:1160 */
-    B200_STATE_ERR_ROW_SIZE     = -7    /* mismatched key / value row size                                 :1141,:1169 */
+    B200_STATE_ERR_ROW_SIZE     = -7,   /* mismatched key / value row size                                 :1141,:1169 */
+    B200_STATE_ERR_NO_ROOM      = -8,   /* not enough cells in kv cache (whole-cache restore)                    :1043 */
+    B200_STATE_ERR_SEQ_ID       = -9    /* invalid seq_id in a cell (whole-cache stream)                         :1067 */
 };
 B200_API int64_t b200_kv_state_seq_size(int64_t n_cells, int32_t n_layer, int64_t k_size_row, int64_t v_size_row);
 /* returns bytes written; -(bytes needed) when out is NULL or cap too small; -1 on bad arguments */
@@ -103,6 +105,31 @@ B200_API int64_t b200_kv_state_seq_write(uint8_t *out, int64_t cap, int64_t n_ce
 B200_API int32_t b200_kv_state_seq_parse(const uint8_t *data, int64_t size, int32_t n_layer,
                                          int32_t type_k, int64_t k_size_row, int32_t type_v, int64_t v_size_row,
                                          int64_t *n_cells, int64_t *k_off, int64_t *v_off);
+/*
+ * The whole-cache stream: llama_kv_cache_unified::state_write(io, -1) / state_read(io, -1) (llama_state_get_data /
+ * llama_state_set_data; src/llama-kv-cache.cpp:848-903, meta with sequence ids :905-923 and :1038-1087).  Every cell some
+ * sequence holds is written once, in ascending cell order, with its position and the ids of all sequences that see it.
+ *   b200_pc_used_cells   those cells in stream order: gather their rows with b200_kv_rows_gather; returns the count,
+ *                        -(count)-1 when cap is too small
+ *   b200_kv_state_all_write   frames the gathered rows ([n_layer][n_cells][size_row]); returns bytes written, -(bytes
+ *                        needed) when out is NULL or cap too small, -1 on bad arguments
+ *   b200_kv_state_all_restore validates the stream (same codes as the sequence parser, plus SEQ_ID / NO_ROOM), then
+ *                        clears the cache and rebuilds every sequence: src_rows[i] (row index inside each layer's rows
+ *                        of the stream) must be copied to cell dst_cells[i] (b200_kv_rows_scatter).  Whole blocks of a
+ *                        prefix that two sequences hold in the same stream cells stay shared (ref-counted); other shared
+ *                        cells are written once per sequence.  Returns the number of pairs; a B200_STATE_ERR_*;
+ *                        -(pairs needed)-100 when cap is too small (nothing changed).  Nothing changes on a parse
+ *                        error; on NO_ROOM the cache is left cleared, as in the reference.
+ */
+B200_API int64_t b200_pc_used_cells(const b200_paged_cache *pc, int32_t *cells, int64_t cap);
+B200_API int64_t b200_kv_state_all_write(uint8_t *out, int64_t cap, const b200_paged_cache *pc, int32_t n_layer,
+                                         int32_t type_k, int64_t k_size_row, int32_t type_v, int64_t v_size_row,
+                                         const uint8_t *k_rows, const uint8_t *v_rows);
+B200_API int64_t b200_kv_state_all_restore(b200_paged_cache *pc, const uint8_t *data, int64_t size, int32_t n_layer,
+                                           int32_t type_k, int64_t k_size_row, int32_t type_v, int64_t v_size_row,
+                                           int32_t *src_rows, int32_t *dst_cells, int64_t cap,
+                                           int64_t *n_cells, int64_t *k_off, int64_t *v_off);
+
 /* state_read_meta for one sequence: drop `seq`, reserve n_cells tokens, slot_mapping[n_cells] = their cells.
  * Returns n_cells, or -1 when the pool has no room (the sequence is gone either way, as in the reference). */
 B200_API int64_t b200_pc_restore_seq(b200_paged_cache *pc, int32_t seq, int64_t n_cells, int32_t *slot_mapping);

@@ -109,7 +109,7 @@ EXPORTS = {
         "b200_fork_trace", "b200_pc_create", "b200_pc_destroy", "b200_pc_append", "b200_pc_prepare_batch", "b200_pc_seq_cp", "b200_pc_seq_rm",
         "b200_pc_seq_keep", "b200_pc_clear", "b200_pc_seq_len", "b200_pc_n_free", "b200_pc_ref_count", "b200_pc_export",
         "b200_pc_slots_of", "b200_pc_defrag", "b200_pc_restore_seq", "b200_pc_context_shift", "b200_kv_state_seq_size", "b200_kv_state_seq_write",
-        "b200_kv_state_seq_parse"],
+        "b200_kv_state_seq_parse", "b200_pc_used_cells", "b200_kv_state_all_write", "b200_kv_state_all_restore"],
 }
 
 lib.b200_paged_attention_workspace.restype = C.c_size_t
@@ -211,9 +211,18 @@ lib.b200_kv_state_seq_write.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_in
 lib.b200_kv_state_seq_parse.restype = C.c_int32
 lib.b200_kv_state_seq_parse.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_int64,
                                         C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+lib.b200_pc_used_cells.restype = C.c_int64
+lib.b200_pc_used_cells.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_int64]
+lib.b200_kv_state_all_write.restype = C.c_int64
+lib.b200_kv_state_all_write.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_int64,
+                                        C.c_void_p, C.c_void_p]
+lib.b200_kv_state_all_restore.restype = C.c_int64
+lib.b200_kv_state_all_restore.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_int64,
+                                          C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int64,
+                                          C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
 STATE_ERRORS = {-1: "truncated stream", -2: "invalid seq_id-agnostic kv cell", -3: "positions are not 0..n-1",
                 -4: "mismatched layer count", -5: "incompatible V transposition", -6: "mismatched key/value type",
-                -7: "mismatched key/value row size"}
+                -7: "mismatched key/value row size", -8: "not enough cells in kv cache", -9: "invalid seq_id"}
 
 
 class B200Error(RuntimeError):

@@ -9,7 +9,7 @@ from . import (AttnDesc, B200Error, KShiftDesc, KVWriteDesc, KERNEL_AUTO, STATE_
                check, lib, row_bytes)
 
 __all__ = ["KVLayout", "AttnCall", "StepCall", "kv_write_desc", "paged_attention", "dense_attention", "kv_write", "block_copy",
-           "kv_rows_gather", "kv_rows_scatter", "k_shift", "context_shift", "state_seq_pack", "state_seq_unpack", "state_seq_save", "state_seq_load",
+           "kv_rows_gather", "kv_rows_scatter", "k_shift", "context_shift", "state_seq_pack", "state_seq_unpack", "state_seq_save", "state_seq_load", "state_all_pack", "state_all_restore",
            "BlockManager", "PagedKVCache", "current_stream"]
 
 
@@ -286,6 +286,46 @@ def state_seq_unpack(data: bytes, n_layer: int, type_k: int, k_row: int, type_v:
     return k, v
 
 
+def state_all_pack(cache: "PagedKVCache", k_rows, v_rows, type_k: int, type_v: int) -> bytes:
+    """the whole-cache stream (llama_state_get_data's KV section) from rows gathered in cache.used_cells() order:
+    k_rows / v_rows uint8 [n_layer, n_cells, size_row]"""
+    import numpy as np
+    k_rows = np.ascontiguousarray(k_rows, dtype=np.uint8); v_rows = np.ascontiguousarray(v_rows, dtype=np.uint8)
+    n_layer, _, k_row = k_rows.shape
+    v_row = v_rows.shape[2]
+    need = -lib.b200_kv_state_all_write(None, 0, cache._h, n_layer, type_k, k_row, type_v, v_row, None, None)
+    out = np.empty(need, dtype=np.uint8)
+    n = lib.b200_kv_state_all_write(out.ctypes.data, need, cache._h, n_layer, type_k, k_row, type_v, v_row,
+                                    k_rows.ctypes.data, v_rows.ctypes.data)
+    if n != need:
+        raise B200Error(f"b200_kv_state_all_write: {n}")
+    return out.tobytes()
+
+
+def state_all_restore(cache: "PagedKVCache", data: bytes, n_layer: int, type_k: int, k_row: int, type_v: int, v_row: int):
+    """llama_state_set_data's KV section: validates, clears the cache, rebuilds every sequence.
+    -> (src_rows, dst_cells, k_rows, v_rows): copy row src_rows[i] of each layer's rows to cell dst_cells[i]"""
+    import numpy as np
+    buf = np.frombuffer(data, dtype=np.uint8)
+    n_cells = C.c_int64(0)
+    k_off, v_off = (C.c_int64 * max(n_layer, 1))(), (C.c_int64 * max(n_layer, 1))()
+    cap = 16
+    while True:
+        src, dst = (C.c_int32 * cap)(), (C.c_int32 * cap)()
+        rc = lib.b200_kv_state_all_restore(cache._h, buf.ctypes.data, buf.size, n_layer, type_k, k_row, type_v, v_row,
+                                           src, dst, cap, C.byref(n_cells), k_off, v_off)
+        if rc <= -100:
+            cap = -rc - 100
+            continue
+        break
+    if rc < 0:
+        raise B200Error(f"kv state: {STATE_ERRORS.get(int(rc), rc)}")
+    n = n_cells.value
+    k_rows = np.stack([buf[k_off[l]:k_off[l] + n * k_row].reshape(n, k_row) for l in range(n_layer)]) if n_layer else np.zeros((0, n, k_row), np.uint8)
+    v_rows = np.stack([buf[v_off[l]:v_off[l] + n * v_row].reshape(n, v_row) for l in range(n_layer)]) if n_layer else np.zeros((0, n, v_row), np.uint8)
+    return list(src[:rc]), list(dst[:rc]), k_rows, v_rows
+
+
 def state_seq_save(cache: "PagedKVCache", seq: int, k_caches, v_caches, layout_k: KVLayout, layout_v: KVLayout | None = None) -> bytes:
     """llama_state_seq_get_data for the paged layout: gather the sequence's rows of every layer on the device (two
     launches), one D2H copy each for K and V, frame them in the reference's stream format"""
@@ -408,6 +448,13 @@ class PagedKVCache:
 
     def ref_count(self, block: int) -> int:
         return lib.b200_pc_ref_count(self._h, block)
+
+    def used_cells(self):
+        """every cell some sequence holds, ascending: the row order of the whole-cache stream"""
+        n = -lib.b200_pc_used_cells(self._h, None, 0) - 1
+        buf = (C.c_int32 * max(n, 1))()
+        n = lib.b200_pc_used_cells(self._h, buf, max(n, 1))
+        return list(buf[:n])
 
     def slots_of(self, seq: int):
         """cell of every cached position, in order, or None for an unknown sequence"""

@@ -15,7 +15,9 @@
 #include "b200_host.h"
 #include "capi_types.h"
 
+#include <algorithm>
 #include <cstring>
+#include <map>
 #include <vector>
 
 namespace {
@@ -105,6 +107,132 @@ B200_API int32_t b200_kv_state_seq_parse(const uint8_t *data, int64_t size, int3
     }
     if (n_cells_out) *n_cells_out = (int64_t) n_cells;
     return 0;
+}
+
+// ---- the whole-cache stream: state_write(io, -1) / state_read(io, -1), i.e. llama_state_get_data / llama_state_set_data
+// (src/llama-kv-cache.cpp:848-903; meta with sequence ids :905-923, :1038-1087).  Same framing as the single-sequence
+// stream, but every used cell is written once, in cell order, with the ids of all sequences that see it.
+
+static int32_t parse_layers(reader & r, int64_t n_cells, int32_t n_layer, int32_t type_k, int64_t k_size_row,
+                            int32_t type_v, int64_t v_size_row, int64_t *k_off, int64_t *v_off) {
+    const uint32_t v_trans = r.val<uint32_t>();
+    const uint32_t nl      = r.val<uint32_t>();
+    if (!r.ok) return B200_STATE_ERR_TRUNCATED;
+    if (nl != (uint32_t) n_layer) return B200_STATE_ERR_LAYERS;
+    if (v_trans != 0) return B200_STATE_ERR_VTRANS;
+    for (int pass = 0; pass < 2; ++pass) {
+        const int32_t t_want = pass ? type_v : type_k;
+        const int64_t row_want = pass ? v_size_row : k_size_row;
+        int64_t *off = pass ? v_off : k_off;
+        for (int32_t il = 0; il < n_layer; ++il) {
+            const int32_t  t   = r.val<int32_t>();
+            const uint64_t row = r.val<uint64_t>();
+            if (!r.ok) return B200_STATE_ERR_TRUNCATED;
+            if (t != t_want) return B200_STATE_ERR_TYPE;
+            if (row != (uint64_t) row_want) return B200_STATE_ERR_ROW_SIZE;
+            if (off) off[il] = r.n;
+            if (!r.skip(n_cells*row_want)) return B200_STATE_ERR_TRUNCATED;
+        }
+    }
+    return 0;
+}
+
+B200_API int64_t b200_pc_used_cells(const b200_paged_cache *pc, int32_t *cells, int64_t cap) {
+    if (!pc) return -1;
+    std::vector<PagedKVCache::UsedCell> u;
+    pc->impl.used_cells(u);
+    if ((int64_t) u.size() > cap) return -(int64_t) u.size() - 1;
+    for (size_t i = 0; i < u.size(); ++i) cells[i] = u[i].cell;
+    return (int64_t) u.size();
+}
+
+B200_API int64_t b200_kv_state_all_write(uint8_t *out, int64_t cap, const b200_paged_cache *pc, int32_t n_layer,
+                                         int32_t type_k, int64_t k_size_row, int32_t type_v, int64_t v_size_row,
+                                         const uint8_t *k_rows, const uint8_t *v_rows) {
+    if (!pc || n_layer < 0 || k_size_row < 0 || v_size_row < 0) return -1;
+    std::vector<PagedKVCache::UsedCell> u;
+    pc->impl.used_cells(u);
+    const int64_t n_cells = (int64_t) u.size();
+    int64_t need = 4 + 8 + (int64_t) n_layer*(2*(4 + 8) + n_cells*(k_size_row + v_size_row));
+    for (const auto & c : u) need += 8 + 4*(int64_t) c.ids.size();
+    if (n_cells > 0 && n_layer > 0 && out && (!k_rows || !v_rows)) return -1;
+    if (!out || cap < need) return -need;
+    writer w{out, cap};
+    w.val<uint32_t>((uint32_t) n_cells);
+    for (const auto & c : u) {
+        w.val<int32_t>(c.pos); w.val<uint32_t>((uint32_t) c.ids.size());
+        for (int32_t id : c.ids) w.val<int32_t>(id);                     // std::set order in the reference: ascending
+    }
+    w.val<uint32_t>(0);
+    w.val<uint32_t>((uint32_t) n_layer);
+    for (int32_t il = 0; il < n_layer; ++il) {
+        w.val<int32_t>(type_k); w.val<uint64_t>((uint64_t) k_size_row);
+        w.put(k_rows + (int64_t) il*n_cells*k_size_row, n_cells*k_size_row);
+    }
+    for (int32_t il = 0; il < n_layer; ++il) {
+        w.val<int32_t>(type_v); w.val<uint64_t>((uint64_t) v_size_row);
+        w.put(v_rows + (int64_t) il*n_cells*v_size_row, n_cells*v_size_row);
+    }
+    return w.n;
+}
+
+B200_API int64_t b200_kv_state_all_restore(b200_paged_cache *pc, const uint8_t *data, int64_t size, int32_t n_layer,
+                                           int32_t type_k, int64_t k_size_row, int32_t type_v, int64_t v_size_row,
+                                           int32_t *src_rows, int32_t *dst_cells, int64_t cap,
+                                           int64_t *n_cells_out, int64_t *k_off, int64_t *v_off) {
+    if (!pc || !data || size < 0 || n_layer < 0) return B200_STATE_ERR_TRUNCATED;
+    reader r{data, size};
+    const uint32_t n_cells = r.val<uint32_t>();
+    if (!r.ok) return B200_STATE_ERR_TRUNCATED;
+    std::map<int32_t, std::vector<std::pair<int32_t, int32_t>>> seqs;    // seq -> (pos, stream row)
+    for (uint32_t i = 0; i < n_cells; ++i) {
+        const int32_t  pos      = r.val<int32_t>();
+        const uint32_t n_seq_id = r.val<uint32_t>();
+        if (!r.ok || (int64_t) n_seq_id*4 > size - r.n) return B200_STATE_ERR_TRUNCATED;
+        for (uint32_t j = 0; j < n_seq_id; ++j) {
+            const int32_t id = r.val<int32_t>();
+            if (id < 0) return B200_STATE_ERR_SEQ_ID;                    // "invalid seq_id ... out of range" :1067-1071
+            seqs[id].emplace_back(pos, (int32_t) i);
+        }
+    }
+    const int32_t rc = parse_layers(r, (int64_t) n_cells, n_layer, type_k, k_size_row, type_v, v_size_row, k_off, v_off);
+    if (rc != 0) return rc;
+    int64_t n_pairs = 0;
+    for (auto & kv : seqs) {                                              // a paged sequence is positions 0..n-1, each once
+        std::sort(kv.second.begin(), kv.second.end());
+        for (size_t p = 0; p < kv.second.size(); ++p) if (kv.second[p].first != (int32_t) p) return B200_STATE_ERR_POSITIONS;
+        n_pairs += (int64_t) kv.second.size();
+    }
+    if (n_cells_out) *n_cells_out = (int64_t) n_cells;
+    if (n_pairs > cap || (n_pairs > 0 && (!src_rows || !dst_cells))) return -n_pairs - 100;
+    // everything checked: from here the cache changes (the reference clears first and clears again on failure, :1047, :889-893)
+    PagedKVCache & c = pc->impl;
+    c.clear();
+    const int64_t bs = c.block_size();
+    std::vector<int32_t> done;                                            // restored sequences, candidates for sharing
+    int64_t n = 0;
+    for (auto & kv : seqs) {
+        const auto & mine = kv.second;
+        // whole blocks of the longest prefix that an already restored sequence holds in the same stream rows are shared
+        // (the stream says so: one cell, several ids); the rest gets cells of its own and a copy of the rows
+        int32_t best = -1; int64_t best_len = 0;
+        for (int32_t other : done) {
+            const auto & theirs = seqs[other];
+            int64_t m = 0;
+            while (m < (int64_t) mine.size() && m < (int64_t) theirs.size() && mine[(size_t) m].second == theirs[(size_t) m].second) ++m;
+            m = m/bs*bs;
+            if (m > best_len) { best_len = m; best = other; }
+        }
+        if (best >= 0) c.seq_cp(best, kv.first, 0, best_len);
+        std::vector<int32_t> slots; std::vector<std::pair<int32_t, int32_t>> cow;
+        if (!c.append(kv.first, (int64_t) mine.size() - best_len, slots, cow) || !cow.empty()) {
+            c.clear();
+            return B200_STATE_ERR_NO_ROOM;                                // "not enough cells in kv cache" :1043-1046
+        }
+        for (size_t p = 0; p < slots.size(); ++p) { src_rows[n] = mine[(size_t) best_len + p].second; dst_cells[n] = slots[p]; ++n; }
+        done.push_back(kv.first);
+    }
+    return n;
 }
 
 /* restore bookkeeping = state_read_meta's single-sequence branch (:1010-1036): seq_rm(dest, -1, -1), then find_slot

@@ -55,6 +55,21 @@ bool PagedKVCache::append(seq_id seq, int64_t n_new, std::vector<int32_t> & slot
     return true;
 }
 
+void PagedKVCache::used_cells(std::vector<UsedCell> & out) const {
+    std::map<int32_t, UsedCell> by_cell;
+    for (const auto & kv : seqs_) {                            // seqs_ is ordered: ids come out ascending
+        const Seq & s = kv.second;
+        for (int64_t p = 0; p < s.len; ++p) {
+            const int32_t cell = (int32_t) ((int64_t) s.blocks[(size_t) (p/block_size_)]*block_size_ + p % block_size_);
+            UsedCell & u = by_cell[cell];
+            u.cell = cell; u.pos = (int32_t) p;
+            u.ids.push_back(kv.first);
+        }
+    }
+    out.clear();
+    for (auto & kv : by_cell) out.push_back(std::move(kv.second));
+}
+
 int PagedKVCache::prepare_batch(int64_t n_tokens, const seq_id * seq, const int32_t * pos, BatchInputs & out) {
     out = BatchInputs();
     if (n_tokens < 0 || (n_tokens > 0 && !seq)) return -1;

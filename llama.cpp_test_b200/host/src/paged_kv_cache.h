@@ -84,6 +84,12 @@ public:
     // Cell index of every cached position of `seq`, in position order (the gather list of a state save).
     bool slots_of(seq_id seq, std::vector<int32_t> & cells) const;
 
+    // Every cell some sequence holds, in ascending cell order (the order llama_kv_cache_unified::state_write(io, -1) walks its
+    // cells, src/llama-kv-cache.cpp:856-872), with its position and the sorted ids of the sequences that see it (a cell of a
+    // shared block carries several; sharers agree on the position because K rows are rotated by it).
+    struct UsedCell { int32_t cell; int32_t pos; std::vector<seq_id> ids; };
+    void used_cells(std::vector<UsedCell> & out) const;
+
     // Compaction (the block-granular form of llama_kv_cache_unified::defrag_prepare, src/llama-kv-cache.cpp:711-846,
     // which moves cells from the end of the cache into holes at the front): used blocks with the highest indices move
     // into the lowest free indices until the used blocks are [0, n_used).  Appends (src_block, dst_block) pairs for

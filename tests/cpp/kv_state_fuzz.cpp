@@ -66,6 +66,53 @@ int main() {
                 CHECK(ko[(size_t) l] >= 0 && ko[(size_t) l] + nc*k_row <= (int64_t) bad.size() && vo[(size_t) l] >= 0 && vo[(size_t) l] + nc*v_row <= (int64_t) bad.size());
         } else ++rejected;
     }
-    std::printf("rejected %ld, accepted %ld (flips inside row data)\nOK\n", rejected, accepted);
+    std::printf("rejected %ld, accepted %ld (flips inside row data)\n", rejected, accepted);
+
+    // ---- the whole-cache stream (state_write / state_read with seq_id == -1): same treatment, through the restore entry
+    b200_paged_cache * pc = b200_pc_create(64, 4);
+    std::vector<int32_t> slots(64); int32_t cow[2];
+    CHECK(b200_pc_append(pc, 2, 21, slots.data(), cow, 1) == 0 && b200_pc_seq_cp(pc, 2, 5, 0, 13) == 1);
+    CHECK(b200_pc_append(pc, 5, 6, slots.data(), cow, 1) >= 0 && b200_pc_append(pc, 0, 9, slots.data(), cow, 1) == 0);
+    std::vector<int32_t> used(256);
+    const int64_t n_used = b200_pc_used_cells(pc, used.data(), 256);
+    CHECK(n_used == 21 + 6 + 1 + 9);                          // seq 5 shares 12 cells, copies the 13th on write, adds 6
+    std::vector<uint8_t> ka((size_t) (n_layer*n_used*k_row)), va((size_t) (n_layer*n_used*v_row));
+    for (auto & b : ka) b = (uint8_t) rng();
+    const int64_t all_size = -b200_kv_state_all_write(nullptr, 0, pc, n_layer, type_k, k_row, type_v, v_row, nullptr, nullptr);
+    std::vector<uint8_t> all((size_t) all_size);
+    CHECK(b200_kv_state_all_write(all.data(), all_size, pc, n_layer, type_k, k_row, type_v, v_row, ka.data(), va.data()) == all_size);
+    auto restore = [&](const std::vector<uint8_t> & buf, b200_paged_cache * into) {
+        uint8_t * exact = (uint8_t *) std::malloc(buf.size() ? buf.size() : 1);
+        if (!buf.empty()) std::memcpy(exact, buf.data(), buf.size());
+        std::vector<int32_t> src(256), dst(256);
+        ko.assign((size_t) n_layer, -1); vo.assign((size_t) n_layer, -1);
+        const int64_t rc = b200_kv_state_all_restore(into, exact, (int64_t) buf.size(), n_layer, type_k, k_row, type_v, v_row,
+                                                     src.data(), dst.data(), 256, &nc, ko.data(), vo.data());
+        if (rc >= 0) {
+            for (int64_t i = 0; i < rc; ++i) CHECK(src[(size_t) i] >= 0 && src[(size_t) i] < nc && dst[(size_t) i] >= 0 && dst[(size_t) i] < 64*4);
+            for (int l = 0; l < n_layer; ++l) CHECK(ko[(size_t) l] >= 0 && ko[(size_t) l] + nc*k_row <= (int64_t) buf.size());
+        }
+        std::free(exact);
+        return rc;
+    };
+    b200_paged_cache * into = b200_pc_create(64, 4);
+    CHECK(restore(all, into) == 21 + (6 + 1 + 12 - 12) + 9 && b200_pc_seq_len(into, 5) == 19 && b200_pc_ref_count(into, 3) == 2);   // ids ascend: seq 0 took blocks 0..2
+    long rej2 = 0, acc2 = 0;
+    for (int64_t len = 0; len < all_size; len += (len < 1024 ? 1 : 389)) {
+        std::vector<uint8_t> cut(all.begin(), all.begin() + len);
+        CHECK(restore(cut, into) == B200_STATE_ERR_TRUNCATED);
+        ++rej2;
+    }
+    const int64_t meta2 = 4 + n_used*12 + 64;
+    for (int it = 0; it < 4000; ++it) {
+        std::vector<uint8_t> bad = all;
+        for (int f = 1 + (int) (rng() % 3); f > 0; --f) bad[(size_t) (rng() % (uint64_t) meta2)] = (uint8_t) rng();
+        if (rng() % 6 == 0) bad.resize((size_t) (rng() % (uint64_t) all_size));
+        const int64_t rc = restore(bad, into);
+        CHECK(rc >= 0 || (rc <= B200_STATE_ERR_TRUNCATED && rc >= B200_STATE_ERR_SEQ_ID));
+        (rc >= 0 ? acc2 : rej2) += 1;
+    }
+    b200_pc_destroy(pc); b200_pc_destroy(into);
+    std::printf("whole-cache stream: rejected %ld, accepted %ld\nOK\n", rej2, acc2);
     return 0;
 }

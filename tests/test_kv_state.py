@@ -174,7 +174,8 @@ def test_parser_on_damaged_streams_under_address_sanitizer(tmp_path):
     exe = str(tmp_path / "kv_state_fuzz")
     base = ["g++", "-std=c++17", "-g", "-O1", "-Wall", "-Wextra", "-I", os.path.join(root, "include"), "-I", os.path.join(host, "src"),
             os.path.join(root, "tests", "cpp", "kv_state_fuzz.cpp"), os.path.join(host, "kv_state.cpp"),
-            os.path.join(host, "paged_kv_cache.cpp"), "-o", exe]
+            os.path.join(host, "paged_kv_cache.cpp"), os.path.join(host, "host_capi.cpp"), os.path.join(host, "fork_compat.cpp"),
+            os.path.join(host, "llama_kv_cache_paged.cpp"), "-o", exe]
     r = subprocess.run(base + ["-fsanitize=address,undefined", "-fno-omit-frame-pointer"], capture_output=True, text=True)
     if r.returncode != 0:
         r = subprocess.run(base, capture_output=True, text=True)
@@ -182,3 +183,133 @@ def test_parser_on_damaged_streams_under_address_sanitizer(tmp_path):
     run = subprocess.run([exe], capture_output=True, text=True, timeout=300)
     assert run.returncode == 0 and run.stdout.strip().endswith("OK"), (run.stdout[-1500:], run.stderr[-3000:])
     assert "runtime error" not in run.stderr, run.stderr[-3000:]
+
+
+# ---- the whole-cache stream: llama_state_get_data / llama_state_set_data (state_write / state_read with seq_id == -1)
+
+def _unified_read_all(data, n_layer, k_row, v_row):
+    """state_read_meta's whole-cache branch (src/llama-kv-cache.cpp:1038-1087) + state_read_data, restated: the cells
+    (pos, ids) in stream order and each layer's rows"""
+    off = 0
+    (count,) = struct.unpack_from("<I", data, off); off += 4
+    cells = []
+    for _ in range(count):
+        pos, n = struct.unpack_from("<iI", data, off); off += 8
+        ids = set(struct.unpack_from(f"<{n}i", data, off)); off += 4 * n
+        cells.append((pos, ids))
+    off += 8
+    k, v = [], []
+    for rows, size_row in ((k, k_row), (v, v_row)):
+        for _ in range(n_layer):
+            off += 12
+            rows.append(np.frombuffer(data, np.uint8, count * size_row, off).reshape(count, size_row)); off += count * size_row
+    assert off == len(data)
+    return cells, k, v
+
+
+def _visible_rows(cells, rows, seq):
+    """what sequence `seq` sees, in position order"""
+    idx = sorted((pos, i) for i, (pos, ids) in enumerate(cells) if seq in ids)
+    assert [p for p, _ in idx] == list(range(len(idx)))
+    return rows[[i for _, i in idx]] if idx else rows[:0]
+
+
+@pytest.mark.parametrize("bs", [1, 4, 16])
+def test_whole_cache_stream_equals_reference_writer(pkg, bs):
+    """a paged cache with forks (shared blocks), a truncated and a removed sequence: its stream is byte for byte what
+    state_write(io, -1) writes for a unified cache whose cells are the paged cells"""
+    rng = np.random.default_rng(bs)
+    n_layer, nb = 2, 96
+    k_row, v_row = row_bytes(Q8_0, N_EMBD_GQA), row_bytes(F16, N_EMBD_GQA)
+    pc = pkg.PagedKVCache(nb, bs)
+    pc.append(3, 37); pc.append(0, 5); pc.seq_cp(3, 7, 0, 22); pc.append(7, 9); pc.append(1, 12); pc.seq_rm(1)
+    pc.append(3, 2); pc.seq_cp(0, 2); pc.seq_rm(3, 30, -1)
+    size = nb * bs
+    k_flat = [rng.integers(0, 256, size=(size, k_row), dtype=np.uint8) for _ in range(n_layer)]
+    v_flat = [rng.integers(0, 256, size=(size, v_row), dtype=np.uint8) for _ in range(n_layer)]
+    cells = [(-1, set()) for _ in range(size)]                 # the unified view of the same cache
+    for s in (0, 2, 3, 7):
+        for p, c in enumerate(pc.slots_of(s)):
+            assert cells[c][0] in (-1, p)
+            cells[c] = (p, cells[c][1] | {s})
+    want = unified_state_write(cells, -1, k_flat, v_flat, Q8_0, F16)
+    used = pc.used_cells()
+    assert used == [c for c in range(size) if cells[c][1]]
+    got = pkg.state_all_pack(pc, np.stack([k[used] for k in k_flat]), np.stack([v[used] for v in v_flat]), Q8_0, F16)
+    assert got == want
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_whole_cache_restore_from_a_unified_layout(pkg, seed):
+    """a stream the reference would write from its own layout — sequences interleaved cell by cell (batched decode),
+    a prompt prefix shared by three sequences — restored into blocks: every sequence sees the same rows in the same
+    order, whole blocks of the common prefix stay shared"""
+    rng = np.random.default_rng(40 + seed)
+    bs = int(rng.choice([1, 4, 16]))
+    n_layer, size = 2, 400
+    k_row, v_row = row_bytes(F16, N_EMBD_GQA), row_bytes(Q4_0, N_EMBD_GQA)
+    cells = [(-1, set()) for _ in range(size)]
+    prefix = int(rng.integers(20, 50))
+    for p in range(prefix):
+        cells[10 + p] = (p, {0, 4, 6})                         # shared prompt (llama-batched-bench -pps)
+    c, lens = 10 + prefix + int(rng.integers(0, 5)), {0: prefix, 4: prefix, 6: prefix, 9: 0}
+    for _ in range(int(rng.integers(30, 60))):                 # decode steps: one cell per sequence per step, interleaved
+        for s in (6, 0, 9, 4):
+            if rng.random() < 0.8:
+                cells[c] = (lens[s], {s}); lens[s] += 1; c += 1
+    k_flat = [rng.integers(0, 256, size=(size, k_row), dtype=np.uint8) for _ in range(n_layer)]
+    v_flat = [rng.integers(0, 256, size=(size, v_row), dtype=np.uint8) for _ in range(n_layer)]
+    data = unified_state_write(cells, -1, k_flat, v_flat, F16, Q4_0)
+    st_cells, st_k, st_v = _unified_read_all(data, n_layer, k_row, v_row)
+    pc = pkg.PagedKVCache(64 * 16 // bs, bs)
+    pc.append(11, 3)                                           # state_read clears whatever was there
+    src, dst, k_rows, v_rows = pkg.state_all_restore(pc, data, n_layer, F16, k_row, Q4_0, v_row)
+    assert pc.seq_len(11) == 0 and len(set(dst)) == len(dst)
+    k_new = [np.zeros((pc.n_blocks * bs, k_row), np.uint8) for _ in range(n_layer)]
+    for l in range(n_layer):
+        assert np.array_equal(k_rows[l], st_k[l]) and np.array_equal(v_rows[l], st_v[l])
+        k_new[l][dst] = k_rows[l][src]                         # what b200_kv_rows_scatter does
+    for s, n in lens.items():
+        assert pc.seq_len(s) == n
+        if n:
+            for l in range(n_layer):
+                assert np.array_equal(k_new[l][pc.slots_of(s)], _visible_rows(st_cells, st_k[l], s))
+    shared = prefix // bs                                      # whole blocks of the prompt are held by all three
+    assert sum(pc.ref_count(b) == 3 for b in range(pc.n_blocks)) == shared
+    # and the stream written back from the blocks restores to the same thing (round trip through the product's own writer)
+    used = pc.used_cells()
+    again = pkg.state_all_pack(pc, np.stack([k[used] for k in k_new]), np.stack([np.zeros((len(used), v_row), np.uint8)] * n_layer), F16, Q4_0)
+    c2, k2, _ = _unified_read_all(again, n_layer, k_row, v_row)
+    for s, n in lens.items():
+        if n:
+            assert np.array_equal(_visible_rows(c2, k2[0], s), _visible_rows(st_cells, st_k[0], s))
+
+
+def test_whole_cache_restore_rejects_like_the_reference(pkg):
+    n_layer, k_row, v_row = 1, row_bytes(F16, N_EMBD_GQA), row_bytes(F16, N_EMBD_GQA)
+    rows = [np.zeros((6, k_row), np.uint8)]
+
+    def stream(cells):
+        return unified_state_write(cells + [(-1, set())], -1, rows[:1], rows[:1], F16, F16) if len(cells) == 5 else None
+
+    pc = pkg.PagedKVCache(4, 2)
+    pc.append(1, 3)
+    ok = [(0, {2}), (1, {2}), (2, {2}), (0, {5}), (1, {5})]
+    for bad, msg in (([(0, {2}), (2, {2}), (3, {2}), (0, {5}), (1, {5})], "positions are not 0..n-1"),      # a hole
+                     ([(0, {2}), (1, {2}), (1, {2}), (0, {5}), (1, {5})], "positions are not 0..n-1"),      # twice
+                     ([(0, {2}), (1, {2}), (2, {2}), (0, {-3}), (1, {5})], "invalid seq_id")):
+        with pytest.raises(pkg.B200Error, match=msg):
+            pkg.state_all_restore(pc, stream(bad), n_layer, F16, k_row, F16, v_row)
+        assert pc.seq_len(1) == 3                              # a parse error changes nothing
+    good = stream(ok)
+    with pytest.raises(pkg.B200Error, match="truncated"):
+        pkg.state_all_restore(pc, good[:-5], n_layer, F16, k_row, F16, v_row)
+    with pytest.raises(pkg.B200Error, match="mismatched key/value type"):
+        pkg.state_all_restore(pc, good, n_layer, Q8_0, k_row, F16, v_row)
+    src, dst, _, _ = pkg.state_all_restore(pc, good, n_layer, F16, k_row, F16, v_row)
+    assert pc.seq_len(1) == 0 and pc.seq_len(2) == 3 and pc.seq_len(5) == 2 and src == [0, 1, 2, 3, 4]
+    small = pkg.PagedKVCache(2, 2)                             # 3 + 2 tokens need 2 + 1 blocks
+    small.append(0, 1)
+    with pytest.raises(pkg.B200Error, match="not enough cells"):
+        pkg.state_all_restore(small, good, n_layer, F16, k_row, F16, v_row)
+    assert small.n_free() == 2                                 # cleared, as the reference leaves it
