@@ -14,6 +14,19 @@ uint32_t llama_kv_cache_paged::get_used_cells() const {
     return (uint32_t) ((cache_.n_blocks() - cache_.n_free())*cache_.block_size());
 }
 
+bool llama_kv_cache_paged::defrag_if_fragmented(float defrag_thold, uint32_t padding) {
+    if (!(defrag_thold > 0.0f)) return false;
+    int64_t top = -1;
+    for (int64_t b = cache_.n_blocks() - 1; b >= 0 && top < 0; --b) if (cache_.ref_count(b) > 0) top = b;
+    if (padding == 0) padding = 1;
+    uint32_t n = (uint32_t) ((top + 1)*cache_.block_size());
+    n = (n + padding - 1)/padding*padding;                                // kv_self->n = GGML_PAD(cell_max(), padding), llama-context.cpp:1311
+    const float frag = n >= 2048 ? 1.0f - float(get_used_cells() + padding)/float(n) : 0.0f;
+    if (!((frag > 0.0f ? frag : 0.0f) > defrag_thold)) return false;
+    defrag();
+    return true;
+}
+
 void llama_kv_cache_paged::clear() {
     cache_.clear();
     work_ = pending_work();

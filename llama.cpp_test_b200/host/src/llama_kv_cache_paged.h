@@ -51,6 +51,11 @@ public:
 
     // ---- llama_memory_i
     void clear();
+    // llama_context::decode's closing check (src/llama-context.cpp:1468-1480): fragmentation = 1 - (used + padding)/n with
+    // n = the padded extent of the used cells (cell_max, .cpp:679-689; get_padding 256 with flash attention, :674-677),
+    // contexts below 2048 cells never defragment; above the threshold a defrag is queued for the next update().  In blocks:
+    // n = cells up to the highest block in use, used = cells of the blocks in use.  Returns whether it queued one.
+    bool defrag_if_fragmented(float defrag_thold, uint32_t padding = 256);
     void defrag() { do_defrag_ = true; }                      // deferred, like llama_kv_cache_unified::defrag (.cpp:149-153)
     bool seq_rm  (llama_seq_id seq_id,                              llama_pos p0, llama_pos p1);
     void seq_cp  (llama_seq_id seq_id_src, llama_seq_id seq_id_dst, llama_pos p0, llama_pos p1);

@@ -78,6 +78,18 @@ static void scenario_basic() {
     kv2.clear();
     CHECK(kv2.find_slot(3, 9, slots, cow) && kv2.seq_rm(3, 1, 3));
     CHECK(!kv2.update(w));                                   // open removal never closed
+    // the decode loop's fragmentation check: small contexts never defragment; a hole under a high block does above the threshold
+    {
+        llama_kv_cache_paged big(512, 16);                   // 8192 cells
+        std::vector<int32_t> sl; std::vector<std::pair<int32_t, int32_t>> cw;
+        CHECK(big.find_slot(0, 100, sl, cw) && !big.defrag_if_fragmented(0.1f));          // n = 256 < 2048
+        CHECK(big.find_slot(1, 6000, sl, cw) && big.find_slot(2, 160, sl, cw));
+        CHECK(!big.defrag_if_fragmented(0.1f));                                            // dense: nothing to gain
+        CHECK(big.seq_rm(1, -1, -1) && !big.defrag_if_fragmented(-1.0f));                  // disabled (the default, llama-context.cpp:2250)
+        CHECK(big.defrag_if_fragmented(0.1f) && big.has_pending());                        // 272 used cells under block 391
+        llama_kv_cache_paged::pending_work pw;
+        CHECK(big.update(pw) && pw.defrag_moves.size() == 10 && !big.defrag_if_fragmented(0.1f));
+    }
     // the ubatch form: interleaved sequences, per-row inputs, refused while a context shift is pending
     llama_kv_cache_paged kv3(8, 4);
     PagedKVCache::BatchInputs in;
