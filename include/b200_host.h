@@ -44,6 +44,9 @@ B200_API int64_t b200_pc_append(b200_paged_cache *pc, int32_t seq, int64_t n_new
 B200_API int32_t b200_pc_prepare_batch(b200_paged_cache *pc, int64_t n_tokens, const int32_t *seq, const int32_t *pos,
                                        int32_t *slot_mapping, int32_t *q_seq, int32_t *q_pos, int32_t *seqs, int64_t *n_seqs,
                                        int32_t *cow_pairs, int64_t cow_cap, int64_t *n_cow);
+/* llama_kv_slot_restorer::restore (src/llama-kv-cache.h:192-237): drop the tokens a successful b200_pc_prepare_batch placed
+ * (seq[] as passed to it, q_pos[] as it returned) when the ubatch's graph failed (src/llama-context.cpp:1322-1343) */
+B200_API void    b200_pc_undo_batch(b200_paged_cache *pc, int64_t n_tokens, const int32_t *seq, const int32_t *q_pos);
 B200_API int32_t b200_pc_seq_cp(b200_paged_cache *pc, int32_t src, int32_t dst, int64_t p0, int64_t p1);   /* 1 ok / 0 refused */
 B200_API int32_t b200_pc_seq_rm(b200_paged_cache *pc, int32_t seq, int64_t p0, int64_t p1);
 B200_API void    b200_pc_seq_keep(b200_paged_cache *pc, int32_t seq);

@@ -106,7 +106,7 @@ EXPORTS = {
     "b200_ggml_abi.h": ["b200_flash_attn_ext_workspace", "b200_flash_attn_ext", "b200_cpy", "b200_supports_op"],
     "b200_host.h": [
         "b200_bm_create", "b200_bm_destroy", "b200_bm_allocate", "b200_bm_free", "b200_bm_evict", "b200_bm_status",
-        "b200_fork_trace", "b200_pc_create", "b200_pc_destroy", "b200_pc_append", "b200_pc_prepare_batch", "b200_pc_seq_cp", "b200_pc_seq_rm",
+        "b200_fork_trace", "b200_pc_create", "b200_pc_destroy", "b200_pc_append", "b200_pc_prepare_batch", "b200_pc_undo_batch", "b200_pc_seq_cp", "b200_pc_seq_rm",
         "b200_pc_seq_keep", "b200_pc_clear", "b200_pc_seq_len", "b200_pc_n_free", "b200_pc_ref_count", "b200_pc_export",
         "b200_pc_slots_of", "b200_pc_defrag", "b200_pc_restore_seq", "b200_pc_context_shift", "b200_kv_state_seq_size", "b200_kv_state_seq_write",
         "b200_kv_state_seq_parse", "b200_pc_used_cells", "b200_kv_state_all_write", "b200_kv_state_all_restore"],
@@ -192,6 +192,8 @@ lib.b200_pc_prepare_batch.restype = C.c_int32
 lib.b200_pc_prepare_batch.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                       C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int64),
                                       C.POINTER(C.c_int32), C.c_int64, C.POINTER(C.c_int64)]
+lib.b200_pc_undo_batch.restype = None
+lib.b200_pc_undo_batch.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
 lib.b200_pc_export.restype = C.c_int32
 lib.b200_pc_export.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_int64, C.POINTER(C.c_int32), C.c_int64, C.POINTER(C.c_int32)]
 lib.b200_pc_slots_of.restype = C.c_int64

@@ -428,6 +428,11 @@ class PagedKVCache:
         return dict(slot_mapping=list(slots[:n]), q_seq=list(q_seq[:n]), q_pos=list(q_pos[:n]), seqs=list(seqs[:n_seqs.value]),
                     cow_pairs=[(cow[2 * i], cow[2 * i + 1]) for i in range(n_cow.value)])
 
+    def undo_batch(self, seq, q_pos) -> None:
+        """llama_kv_slot_restorer::restore for a batch prepare_batch placed (its seq list, the q_pos it returned)"""
+        n = len(seq)
+        lib.b200_pc_undo_batch(self._h, n, (C.c_int32 * max(n, 1))(*seq), (C.c_int32 * max(n, 1))(*q_pos))
+
     def seq_cp(self, src: int, dst: int, p0: int = 0, p1: int = -1) -> bool:
         return bool(lib.b200_pc_seq_cp(self._h, src, dst, p0, p1))
 

@@ -56,6 +56,18 @@ B200_API int32_t b200_pc_prepare_batch(b200_paged_cache *pc, int64_t n_tokens, c
     if (n_cow) *n_cow = (int64_t) in.cow_pairs.size();
     return 0;
 }
+B200_API void b200_pc_undo_batch(b200_paged_cache *pc, int64_t n_tokens, const int32_t *seq, const int32_t *q_pos) {
+    if (!pc || n_tokens <= 0 || !seq || !q_pos) return;
+    PagedKVCache::BatchInputs in;
+    for (int64_t i = 0; i < n_tokens; ++i) {
+        size_t r = 0;
+        while (r < in.seqs.size() && in.seqs[r] != seq[i]) ++r;
+        if (r == in.seqs.size()) in.seqs.push_back(seq[i]);
+        in.q_seq.push_back((int32_t) r);
+        in.q_pos.push_back(q_pos[i]);
+    }
+    pc->impl.undo_batch(in);
+}
 B200_API int32_t b200_pc_seq_cp(b200_paged_cache *pc, int32_t s, int32_t d, int64_t p0, int64_t p1) { return pc->impl.seq_cp(s, d, p0, p1) ? 1 : 0; }
 B200_API int32_t b200_pc_seq_rm(b200_paged_cache *pc, int32_t s, int64_t p0, int64_t p1) { return pc->impl.seq_rm(s, p0, p1) ? 1 : 0; }
 B200_API void    b200_pc_seq_keep(b200_paged_cache *pc, int32_t s) { pc->impl.seq_keep(s); }

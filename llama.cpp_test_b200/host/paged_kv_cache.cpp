@@ -106,6 +106,18 @@ int PagedKVCache::prepare_batch(int64_t n_tokens, const seq_id * seq, const int3
     return 0;
 }
 
+void PagedKVCache::undo_batch(const BatchInputs & in) {
+    std::vector<int64_t> first(in.seqs.size(), -1);
+    for (size_t i = 0; i < in.q_seq.size(); ++i) {
+        int64_t & f = first[(size_t) in.q_seq[i]];
+        if (f < 0 || in.q_pos[i] < f) f = in.q_pos[i];
+    }
+    for (size_t r = 0; r < in.seqs.size(); ++r) {
+        if (first[r] < 0) continue;
+        if (first[r] == 0) seq_rm(in.seqs[r], -1, -1); else seq_rm(in.seqs[r], first[r], -1);
+    }
+}
+
 bool PagedKVCache::seq_cp(seq_id src, seq_id dst, int64_t p0, int64_t p1) {
     if (p0 > 0) return false;
     auto it = seqs_.find(src);

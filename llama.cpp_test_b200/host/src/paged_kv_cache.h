@@ -49,6 +49,11 @@ public:
         std::vector<std::pair<int32_t, int32_t>> cow_pairs;
     };
     int prepare_batch(int64_t n_tokens, const seq_id * seq, const int32_t * pos, BatchInputs & out);
+    // llama_kv_slot_restorer::restore (src/llama-kv-cache.h:192-237; llama_context::decode calls it when the graph of a ubatch
+    // fails, src/llama-context.cpp:1322-1343): the tokens a prepare_batch placed are dropped again — every sequence of the
+    // batch is cut back to the position of its first token in the batch.  Blocks that a copy-on-write gave the sequence stay
+    // its own (their content equals the shared block's; nothing has to be copied back).
+    void undo_batch(const BatchInputs & in);
 
     // llama_kv_self_seq_cp semantics restricted to prefixes (p0 <= 0): dst becomes positions [0, p1) of src,
     // sharing blocks.  p1 < 0 means "to the end".  Returns false for p0 > 0 or unknown src.

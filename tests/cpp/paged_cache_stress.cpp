@@ -46,7 +46,13 @@ int main() {
                 if (bad_pos) { pos.assign((size_t) n, 0); for (int i = 0; i < n; ++i) pos[(size_t) i] = (int32_t) pc.seq_len(seq[(size_t) i]) + 1 + R(3); }
                 const int rc = pc.prepare_batch(n, seq.data(), bad_pos ? pos.data() : nullptr, in);
                 CHECK(bad_pos ? rc == -1 : (rc == 0 || rc == 1));
-                if (rc == 0) {
+                if (rc == 0 && R(5) == 0) {                               // the graph failed: llama_kv_slot_restorer::restore
+                    std::vector<int64_t> before(6);
+                    for (int q = 0; q < 6; ++q) before[(size_t) q] = pc.seq_len(q);
+                    for (int i = 0; i < n; ++i) --before[(size_t) seq[(size_t) i]];
+                    pc.undo_batch(in);
+                    for (int q = 0; q < 6; ++q) CHECK(pc.seq_len(q) == before[(size_t) q]);
+                } else if (rc == 0) {
                     CHECK((int) in.slot_mapping.size() == n && in.q_seq.size() == in.q_pos.size());
                     for (int i = 0; i < n; ++i) {                         // the cell of token i is the cell of its position in its row
                         const std::vector<int32_t> * b = pc.blocks_of(seq[(size_t) i]);

@@ -191,6 +191,20 @@ def test_prepare_batch_is_all_or_nothing(pkg):
     assert r["cow_pairs"] == [(1, 2)] and r["slot_mapping"] == [2 * 4 + 2, 12, 13] and pc.n_free() == 0
 
 
+def test_undo_batch_is_the_slot_restorer(pkg):
+    """llama_context::decode restores the cache when a ubatch's graph fails (llama_kv_slot_restorer, src/llama-kv-cache.h:
+    192-237): the sequences are back to their lengths, new sequences are gone, the blocks are free again"""
+    pc = pkg.PagedKVCache(16, 4)
+    pc.append(7, 6)
+    free0 = pc.n_free()
+    seq = [7, 3, 7, 3, 9, 7, 7]
+    r = pc.prepare_batch(seq)
+    assert pc.seq_len(7) == 10 and pc.seq_len(3) == 2 and pc.seq_len(9) == 1
+    pc.undo_batch(seq, r["q_pos"])
+    assert pc.seq_len(7) == 6 and pc.seq_len(3) == 0 and pc.seq_len(9) == 0 and pc.n_free() == free0
+    assert pc.prepare_batch(seq)["slot_mapping"] == r["slot_mapping"]          # and the same cells come out again
+
+
 @pytest.mark.parametrize("seed", range(5))
 def test_prepare_batch_equals_the_reference_mask(pkg, seed):
     """llm_graph_input_attn_kv_unified::set_input (src/llama-graph.cpp:428-460) lets token (seq s, pos p) see the cells whose
