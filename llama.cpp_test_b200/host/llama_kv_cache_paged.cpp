@@ -91,7 +91,10 @@ void llama_kv_cache_paged::seq_div(llama_seq_id, llama_pos p0, llama_pos p1, int
 }
 
 llama_pos llama_kv_cache_paged::seq_pos_max(llama_seq_id seq_id) {
-    return (llama_pos) cache_.seq_len(seq_id) - 1;           // -1 for an absent sequence, like the reference (:437-447)
+    // the reference starts its maximum at 0 (src/llama-kv-cache.cpp:431-441), so an absent or empty sequence answers 0, the
+    // same as a sequence holding position 0 only — pinned against the reference itself in tests/test_ref_kv_cache.py
+    const int64_t len = cache_.seq_len(seq_id);
+    return len > 0 ? (llama_pos) (len - 1) : 0;
 }
 
 bool llama_kv_cache_paged::find_slot(llama_seq_id seq_id, int32_t n_tokens, std::vector<int32_t> & slot_mapping,

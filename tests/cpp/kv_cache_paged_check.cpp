@@ -44,7 +44,7 @@ static void apply(const llama_kv_cache_paged::pending_work & w, std::vector<long
 static void scenario_basic() {
     llama_kv_cache_paged kv(8, 4);
     std::vector<int32_t> slots; std::vector<std::pair<int32_t, int32_t>> cow;
-    CHECK(kv.get_can_shift() && kv.seq_pos_max(0) == -1 && kv.get_n_tokens() == 0);
+    CHECK(kv.get_can_shift() && kv.seq_pos_max(0) == 0 && kv.get_n_tokens() == 0);
     CHECK(kv.find_slot(0, 10, slots, cow) && slots.size() == 10 && cow.empty());
     CHECK(kv.seq_pos_max(0) == 9 && kv.get_n_tokens() == 10 && kv.get_used_cells() == 12);
     kv.seq_cp(0, 1, 0, 6);
@@ -160,7 +160,7 @@ static void scenario_random(unsigned seed) {
         }
         // bookkeeping agrees with the model at every step (seq_pos_max, token count)
         CHECK(kv.get_n_tokens() == model.n_tokens());
-        for (int s = 0; s < 5; ++s) CHECK(kv.seq_pos_max(s) == (model.seqs.count(s) ? (int) model.seqs[s].size() - 1 : -1));
+        for (int s = 0; s < 5; ++s) CHECK(kv.seq_pos_max(s) == (model.seqs.count(s) && !model.seqs[s].empty() ? (int) model.seqs[s].size() - 1 : 0));
     }
     llama_kv_cache_paged::pending_work w;
     CHECK(kv.update(w));

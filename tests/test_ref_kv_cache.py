@@ -1,0 +1,179 @@
+"""Pins the restatements of the reference's KV-cache bookkeeping to the reference itself.
+
+oracle/_ref/refkv is the reference's OWN llama_kv_cache_unified (src/llama-kv-cache.cpp, compiled where it lies with the rest
+of libllama's sources by `make -C oracle refkv`; oracle/ref_kv_harness.cpp only constructs it and relays calls).  The same
+seeded call stream goes to it, to the cell-per-token model the host-class tests use (tests/test_paged_cache.py::UnifiedModel),
+to the product's PagedKVCache, and its session streams are compared byte for byte with oracle/kv_state_oracle.py and with the
+product's writers.  Skipped where the binary is absent (no reference tree when the checker was built)."""
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle.kv_state_oracle import unified_state_write
+from test_paged_cache import UnifiedModel
+from workloads import F16, row_bytes
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(ROOT, "oracle", "_ref", "refkv")
+
+
+class RefKV:
+    def __init__(self, n_layer, head_dim, n_head_kv, size, tk=F16, tv=F16):
+        if not os.path.exists(EXE):
+            pytest.skip("oracle/_ref/refkv not built (reference tree absent when the checker was built)")
+        self.p = subprocess.Popen([EXE], stdin=subprocess.PIPE, stdout=subprocess.PIPE, text=True)
+        assert self.cmd(f"I {n_layer} {head_dim} {n_head_kv} {size} {tk} {tv}") == "ok"
+
+    def cmd(self, line):
+        self.p.stdin.write(line + "\n"); self.p.stdin.flush()
+        return self.p.stdout.readline().strip()
+
+    def visible(self, seq):
+        return [tuple(map(int, e.split(":"))) for e in self.cmd(f"V {seq}").split()[1:]]
+
+    def close(self):
+        self.p.stdin.close(); self.p.wait(timeout=10)
+
+
+def test_seq_pos_max_of_an_empty_sequence_is_zero(pkg):
+    """src/llama-kv-cache.cpp:431-441 starts its maximum at 0: the adapter answers the same (found by this pin)"""
+    r = RefKV(1, 16, 2, 32)
+    assert r.cmd("P 3") == "0"
+    r.cmd("A 3 1"); assert r.cmd("P 3") == "0"
+    r.cmd("A 3 2"); assert r.cmd("P 3") == "2"
+    r.close()
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_cell_model_and_paged_cache_against_the_reference_cache(pkg, seed):
+    """random append (single sequence and interleaved ubatches) / fork / truncate / remove / keep streams: what every sequence
+    sees — token ids in position order — is the same in the reference's cache, in the cell model and in the block tables;
+    the reference's get_n_tokens equals the sum of the sequence lengths"""
+    rng = np.random.default_rng(700 + seed)
+    bs = int(rng.choice([1, 4, 16]))
+    size, n_seq = 512, 5
+    r, um, pc = RefKV(1, 16, 2, size), UnifiedModel(), pkg.PagedKVCache(size // bs + 64, bs)
+    content = np.full((size // bs + 64) * bs, -1, dtype=np.int64)
+    next_tok = 0
+    for step in range(150):
+        op = rng.choice(["append", "append", "batch", "batch", "cp", "trunc", "rm", "keep"])
+        live = [s for s in range(n_seq) if pc.seq_len(s) > 0]
+        if op in ("append", "batch"):
+            seq = [int(rng.integers(0, n_seq))] * int(rng.integers(1, 20)) if op == "append" else \
+                  [int(s) for s in rng.integers(0, n_seq, int(rng.integers(1, 24)))]
+            ans = r.cmd("B %d %s" % (len(seq), " ".join(map(str, seq))))
+            if ans == "noslot":                                # the flat cache fragments; the paged one need not follow
+                continue
+            got = pc.prepare_batch(seq)
+            assert isinstance(got, dict)
+            for a, b in got["cow_pairs"]:
+                content[b * bs:(b + 1) * bs] = content[a * bs:(a + 1) * bs]
+            toks = list(range(next_tok, next_tok + len(seq))); next_tok += len(seq)
+            content[got["slot_mapping"]] = toks
+            for s, t in zip(seq, toks):
+                um.append(s, [t])
+        elif op == "cp" and live:
+            src, dst = int(rng.choice(live)), int(rng.integers(0, n_seq))
+            if dst == src:
+                continue
+            p1 = int(rng.integers(1, pc.seq_len(src) + 1))
+            r.cmd(f"R {dst} -1 -1")                            # the paged seq_cp replaces dst: give the reference the same request
+            r.cmd(f"C {src} {dst} 0 {p1}")
+            assert pc.seq_cp(src, dst, 0, p1)
+            um.seq_cp(src, dst, p1)
+        elif op == "trunc" and live:
+            s = int(rng.choice(live)); p0 = int(rng.integers(0, pc.seq_len(s) + 1))
+            assert r.cmd(f"R {s} {p0} -1") == "1" and pc.seq_rm(s, p0, -1)
+            um.seq_rm(s, p0)
+        elif op == "rm" and live:
+            s = int(rng.choice(live))
+            assert r.cmd(f"R {s} -1 -1") == "1" and pc.seq_rm(s)
+            um.seq_rm(s)
+        elif op == "keep" and live and rng.random() < 0.3:
+            s = int(rng.choice(live))
+            r.cmd(f"K {s}"); pc.seq_keep(s)
+            for o in range(n_seq):
+                if o != s:
+                    um.seq_rm(o)
+        n_tokens = 0
+        for s in range(n_seq):
+            vis = r.visible(s)
+            assert [p for p, _ in vis] == list(range(len(vis)))
+            ids = [t for _, t in vis]
+            assert ids == um.visible(s)
+            n = pc.seq_len(s)
+            assert n == len(ids)
+            if n:
+                assert content[pc.slots_of(s)].tolist() == ids
+            n_tokens += n
+        assert int(r.cmd("N").split()[0]) == n_tokens
+    r.close()
+
+
+@pytest.mark.parametrize("whole", [False, True])
+def test_session_streams_against_the_reference_writer(pkg, whole):
+    """state_write(io, seq) / state_write(io, -1) of the reference on a cache with a shared prefix and interleaved decode
+    cells == oracle/kv_state_oracle.py on the same cells (this pins the restatement) == the product's writers fed the same rows
+    in their own order; and the reference's state_read accepts the product's single-sequence stream"""
+    n_layer, hd, nkv, size = 2, 16, 2, 96
+    k_row = row_bytes(F16, hd * nkv)
+    r = RefKV(n_layer, hd, nkv, size)
+    cells = [(-1, set()) for _ in range(size)]
+    k0 = np.zeros((size, k_row), np.uint8)
+    tok, lens = 0, {}
+
+    def batch(seq):
+        nonlocal tok
+        head = int(r.cmd("B %d %s" % (len(seq), " ".join(map(str, seq)))).split()[1])
+        for i, s in enumerate(seq):
+            cells[head + i] = (lens.get(s, 0), {s}); lens[s] = lens.get(s, 0) + 1
+            k0[head + i, :4] = np.frombuffer(struct.pack("<i", tok), np.uint8); tok += 1
+
+    batch([0] * 21)
+    r.cmd("C 0 4 0 13")
+    for c in range(13):
+        cells[c] = (cells[c][0], {0, 4})
+    lens[4] = 13
+    for _ in range(9):
+        batch([4, 0, 7])
+    k_l = [k0, np.zeros_like(k0)]
+    v_l = [np.zeros_like(k0), np.zeros_like(k0)]
+    seq = -1 if whole else 4
+    got = bytes.fromhex(r.cmd(f"S {seq}").split()[1])
+    assert got == unified_state_write(cells, seq, k_l, v_l, F16, F16)
+    # the product: the same contents in a paged cache
+    pc = pkg.PagedKVCache(64, 4)
+    pc.append(0, 21); pc.seq_cp(0, 4, 0, 13)
+    where = {}                                                  # (seq, pos) -> flat cell of the reference
+    for c, (pos, ids) in enumerate(cells):
+        for s in ids:
+            where[(s, pos)] = c
+    for _ in range(9):
+        pc.prepare_batch([4, 0, 7])
+    if whole:
+        # the paged cache numbers its cells differently (and copies the shared tail block on write): compare what each
+        # sequence sees after reading the product's stream back with the reference's reader
+        used = pc.used_cells()
+        owner = {}
+        for s in (0, 4, 7):
+            for p, c in enumerate(pc.slots_of(s)):
+                owner[c] = (s, p)
+        rows = np.stack([np.stack([kl[where[owner[c]]] for c in used]) for kl in k_l])
+        mine = pkg.state_all_pack(pc, rows, np.zeros_like(rows), F16, F16)
+        r2 = RefKV(n_layer, hd, nkv, size)
+        assert r2.cmd(f"L -1 {mine.hex()}") == "ok"
+        for s in (0, 4, 7):
+            assert r2.visible(s) == r.visible(s)
+        r2.close()
+    else:
+        rows = np.stack([np.stack([kl[where[(4, p)]] for p in range(lens[4])]) for kl in k_l])
+        mine = pkg.state_seq_pack(rows, np.zeros_like(rows), F16, F16)
+        assert mine == got                                      # byte for byte the reference's stream
+        r2 = RefKV(n_layer, hd, nkv, size)
+        assert r2.cmd(f"L 9 {mine.hex()}") == "ok"              # and the reference restores it as sequence 9
+        assert [t for _, t in r2.visible(9)] == [t for _, t in r.visible(4)]
+        r2.close()
+    r.close()
