@@ -9,8 +9,8 @@ a flat unified cache of `size` cells where the sequence occupies arbitrary cells
                                           every range; first all K layers, then all V layers (v_trans == 0)
   state_read_meta / _data      :1008-1240 the checks and their messages
 
-Parity is UNPINNED against a running libllama (it is not built here): this file follows the source
-line by line instead, and the tests compare the product's stream with it byte for byte.
+Pinned: tests/test_ref_kv_cache.py compares this writer byte for byte with the reference's own state_write (single-sequence
+and whole-cache form) run through oracle/_ref/refkv, the reference's llama_kv_cache_unified compiled where it lies.
 """
 from __future__ import annotations
 
