@@ -12,6 +12,8 @@
 //                                                                                       -> "slot h" | "noslot"
 //   B n s0 s1 ...      one ubatch of n tokens, token i for sequence s_i (interleaved), as above  -> "slot h" | "noslot"
 //   C src dst p0 p1 / R seq p0 p1 / K seq / X                  seq_cp / seq_rm / seq_keep / clear -> "ok" | "0"/"1" for R
+//   T seq p0 p1 delta  seq_add                                                                 -> "ok"
+//   E seq              has_shift and, per cell of seq with a pending K rotation, pos:delta      -> "e 0|1 pos:delta ..."
 //   P seq              seq_pos_max                                                             -> number
 //   N                  get_n_tokens get_used_cells                                             -> "n used"
 //   V seq              token ids seq sees, in position order (cells whose set holds seq)       -> "v id id ..."
@@ -100,6 +102,16 @@ int main() {
             }
         } else if (op == 'C') { int a, b, p0, p1; in >> a >> b >> p0 >> p1; kv->seq_cp(a, b, p0, p1); std::printf("ok\n"); }
         else if (op == 'R') { int s, p0, p1; in >> s >> p0 >> p1; std::printf("%d\n", kv->seq_rm(s, p0, p1) ? 1 : 0); }
+        else if (op == 'T') { int s, p0, p1, d; in >> s >> p0 >> p1 >> d; kv->seq_add(s, p0, p1, d); std::printf("ok\n"); }
+        else if (op == 'E') {                                      // the cells with a pending K rotation and their delta (has_shift)
+            int s; in >> s;
+            std::vector<std::pair<llama_pos, llama_pos>> v;
+            for (uint32_t i = 0; i < kv->size; ++i) if (kv->cells[i].has_seq_id(s) && kv->cells[i].delta != 0) v.emplace_back(kv->cells[i].pos, kv->cells[i].delta);
+            std::sort(v.begin(), v.end());
+            std::printf("e %d", kv->has_shift ? 1 : 0);
+            for (auto & e : v) std::printf(" %d:%d", e.first, e.second);
+            std::printf("\n");
+        }
         else if (op == 'K') { int s; in >> s; kv->seq_keep(s); std::printf("ok\n"); }
         else if (op == 'X') { kv->clear(); std::printf("ok\n"); }
         else if (op == 'P') { int s; in >> s; std::printf("%d\n", kv->seq_pos_max(s)); }

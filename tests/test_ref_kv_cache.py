@@ -168,6 +168,15 @@ def test_session_streams_against_the_reference_writer(pkg, whole):
         for s in (0, 4, 7):
             assert r2.visible(s) == r.visible(s)
         r2.close()
+        # the other direction: the reference's own whole-cache stream restored into blocks
+        pc2 = pkg.PagedKVCache(64, 4)
+        src, dst, k_rows, _ = pkg.state_all_restore(pc2, got, n_layer, F16, k_row, F16, k_row)
+        flat = np.zeros((64 * 4, k_row), np.uint8)
+        flat[dst] = k_rows[0][src]
+        for s in (0, 4, 7):
+            ids = [int(np.frombuffer(flat[c, :4].tobytes(), "<i4")[0]) for c in pc2.slots_of(s)]
+            assert ids == [t for _, t in r.visible(s)]
+        assert sum(pc2.ref_count(b) == 2 for b in range(64)) == 13 // 4         # the shared prompt's whole blocks stay shared
     else:
         rows = np.stack([np.stack([kl[where[(4, p)]] for p in range(lens[4])]) for kl in k_l])
         mine = pkg.state_seq_pack(rows, np.zeros_like(rows), F16, F16)
@@ -176,4 +185,47 @@ def test_session_streams_against_the_reference_writer(pkg, whole):
         assert r2.cmd(f"L 9 {mine.hex()}") == "ok"              # and the reference restores it as sequence 9
         assert [t for _, t in r2.visible(9)] == [t for _, t in r.visible(4)]
         r2.close()
+    r.close()
+
+
+@pytest.mark.parametrize("seed", range(5))
+def test_context_shift_against_the_reference_pair_of_calls(pkg, seed):
+    """llama_kv_self_seq_rm(seq, p0, p1) + llama_kv_self_seq_add(seq, p1, -1, -(p1 - p0)) on the reference's cache (what
+    examples/main does on context overflow) against PagedKVCache.context_shift: the surviving tokens and their new positions,
+    and the set of cells whose K rows need re-rotation with the delta the reference records (cell.delta, has_shift)"""
+    rng = np.random.default_rng(900 + seed)
+    bs = int(rng.choice([1, 4, 16]))
+    size = 256
+    r, pc = RefKV(1, 16, 2, size), pkg.PagedKVCache(size // bs + 16, bs)
+    content = np.full((size // bs + 16) * bs, -1, dtype=np.int64)
+    n = int(rng.integers(40, 120))
+    assert r.cmd(f"A 0 {n}").startswith("slot")
+    slots, _ = pc.append(0, n)
+    content[slots] = np.arange(n)
+    if rng.random() < 0.5:                                    # a fork first: shared blocks must be copied before they are written
+        p1 = int(rng.integers(1, n + 1))
+        r.cmd(f"C 0 1 0 {p1}"); assert pc.seq_cp(0, 1, 0, p1)
+    p0 = int(rng.integers(0, n - 2)); p1 = int(rng.integers(p0 + 1, n))
+    assert r.cmd(f"R 0 {p0} {p1}") == "1"
+    r.cmd(f"T 0 {p1} -1 {-(p1 - p0)}")
+    got = pc.context_shift(0, p0, p1)
+    assert got is not None
+    cow, moves, shift_cells = got
+    for a, b in cow:
+        content[b * bs:(b + 1) * bs] = content[a * bs:(a + 1) * bs]
+    if moves:
+        src, dst = [m[0] for m in moves], [m[1] for m in moves]
+        content[dst] = content[src].copy()                     # gather all, then scatter all
+    vis = r.visible(0)
+    assert [p for p, _ in vis] == list(range(n - (p1 - p0)))
+    assert content[pc.slots_of(0)].tolist() == [t for _, t in vis]
+    # the rotation work: the reference marks every moved cell with delta = -(p1 - p0)
+    e = r.cmd("E 0").split()
+    assert e[1] == "1"
+    marked = [tuple(map(int, x.split(":"))) for x in e[2:]]
+    assert marked == [(p, -(p1 - p0)) for p in range(p0, n - (p1 - p0))]
+    cell_of = pc.slots_of(0)
+    assert sorted(shift_cells) == sorted(cell_of[p] for p, _ in marked)
+    if pc.seq_len(1):                                          # the fork still sees what it saw
+        assert content[pc.slots_of(1)].tolist() == [t for _, t in r.visible(1)]
     r.close()
