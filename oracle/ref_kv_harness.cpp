@@ -11,6 +11,8 @@
 //                      placed cell is stamped with a running token id, head += n (llama-context.cpp:1291-1353)
 //                                                                                       -> "slot h" | "noslot"
 //   B n s0 s1 ...      one ubatch of n tokens, token i for sequence s_i (interleaved), as above  -> "slot h" | "noslot"
+//   M n s0 s1 ...      as B, then kv_self->n and the reference's mask fill for the ubatch: per token row, the token ids its
+//                      mask row leaves visible, by position                         -> "m n_kv ids ids ..." | "noslot"
 //   C src dst p0 p1 / R seq p0 p1 / K seq / X                  seq_cp / seq_rm / seq_keep / clear -> "ok" | "0"/"1" for R
 //   T seq p0 p1 delta  seq_add                                                                 -> "ok"
 //   E seq              has_shift and, per cell of seq with a pending K rotation, pos:delta      -> "e 0|1 pos:delta ..."
@@ -24,6 +26,7 @@
 #include "llama-cparams.h"
 #include "llama-batch.h"
 #include "llama-io.h"
+#include "llama-graph.h"
 
 #include <algorithm>
 #include <cstdio>
@@ -52,7 +55,8 @@ int main() {
     llama_model model(llama_model_default_params());
     model.arch = LLM_ARCH_LLAMA;
     llama_cparams cparams = {};
-    cparams.flash_attn = true;                                   // v_trans = 0, like -fa runs (the paged path's layout)
+    cparams.flash_attn = true;
+    cparams.causal_attn = true;                                   // v_trans = 0, like -fa runs (the paged path's layout)
     std::unique_ptr<llama_kv_cache_unified> kv;
     int32_t next_tok = 0;
     size_t k_row = 0;
@@ -100,6 +104,48 @@ int main() {
                 kv->head += n;
                 if (kv->head >= kv->size) kv->head = 0;
             }
+        } else if (op == 'M') {
+            // one decode step's KV section with the reference's own mask fill: find_slot, kv_self->n as llama_context::decode
+            // sets it (src/llama-context.cpp:1304-1312), llm_graph_input_attn_kv_unified::set_input (src/llama-graph.cpp:403-477)
+            int n0; in >> n0;
+            std::vector<llama_seq_id> seq((size_t) n0); for (auto & q : seq) in >> q;
+            const uint32_t n = (uint32_t) n0;
+            std::vector<llama_pos> pos(n); std::vector<int32_t> n_seq_id(n, 1); std::vector<llama_seq_id *> seq_ptr(n);
+            std::vector<llama_pos> nxt(64, -2);
+            for (uint32_t i = 0; i < n; ++i) {
+                llama_pos & p = nxt[(size_t) seq[i]];
+                if (p == -2) { p = 0; for (uint32_t c = 0; c < kv->size; ++c) if (kv->cells[c].has_seq_id(seq[i])) p = std::max(p, kv->cells[c].pos + 1); }
+                pos[i] = p++; seq_ptr[i] = &seq[i];
+            }
+            llama_ubatch ub = {};
+            ub.equal_seqs = false; ub.n_tokens = n; ub.n_seq_tokens = 1; ub.n_seqs = n;
+            ub.pos = pos.data(); ub.n_seq_id = n_seq_id.data(); ub.seq_id = seq_ptr.data();
+            if (!kv->find_slot(ub)) { std::printf("noslot\n"); std::fflush(stdout); continue; }
+            for (uint32_t i = 0; i < n; ++i) { int32_t tok = next_tok++; memcpy((char *) kv->k_l[0]->data + (size_t) (kv->head + i)*k_row, &tok, 4); }
+            const uint32_t pad = kv->get_padding(cparams);
+            kv->n = std::min(kv->size, std::max(pad, GGML_PAD(kv->cell_max(), pad)));
+            ggml_init_params ip = { ggml_tensor_overhead()*4, nullptr, true };
+            ggml_context * ctx = ggml_init(ip);
+            llm_graph_input_attn_kv_unified inp(model.hparams, cparams, kv.get());
+            inp.self_kq_mask = ggml_new_tensor_2d(ctx, GGML_TYPE_F32, kv->n, GGML_PAD(n, GGML_KQ_MASK_PAD));
+            ggml_backend_buffer_t buf = ggml_backend_alloc_ctx_tensors_from_buft(ctx, ggml_backend_cpu_buffer_type());
+            inp.set_input(&ub);
+            const float * m = (const float *) inp.self_kq_mask->data;
+            std::printf("m %u", kv->n);
+            for (uint32_t i = 0; i < n; ++i) {                     // row i: token ids of the cells its mask row leaves visible, by position
+                std::vector<std::pair<llama_pos, int32_t>> v;
+                for (uint32_t c = 0; c < kv->n; ++c) if (m[(size_t) i*kv->n + c] == 0.0f) {
+                    int32_t tok; memcpy(&tok, (const char *) kv->k_l[0]->data + (size_t) c*k_row, 4);
+                    v.emplace_back(kv->cells[c].pos, tok);
+                }
+                std::sort(v.begin(), v.end());
+                std::printf(" ");
+                for (size_t k = 0; k < v.size(); ++k) std::printf(k ? ",%d" : "%d", v[k].second);
+            }
+            std::printf("\n");
+            ggml_backend_buffer_free(buf); ggml_free(ctx);
+            kv->head += n;
+            if (kv->head >= kv->size) kv->head = 0;
         } else if (op == 'C') { int a, b, p0, p1; in >> a >> b >> p0 >> p1; kv->seq_cp(a, b, p0, p1); std::printf("ok\n"); }
         else if (op == 'R') { int s, p0, p1; in >> s >> p0 >> p1; std::printf("%d\n", kv->seq_rm(s, p0, p1) ? 1 : 0); }
         else if (op == 'T') { int s, p0, p1, d; in >> s >> p0 >> p1 >> d; kv->seq_add(s, p0, p1, d); std::printf("ok\n"); }

@@ -229,3 +229,54 @@ def test_context_shift_against_the_reference_pair_of_calls(pkg, seed):
     if pc.seq_len(1):                                          # the fork still sees what it saw
         assert content[pc.slots_of(1)].tolist() == [t for _, t in r.visible(1)]
     r.close()
+
+
+@pytest.mark.parametrize("seed", range(5))
+def test_prepare_batch_against_the_reference_mask_fill(pkg, seed):
+    """The equivalence the whole paged path rests on, against the reference's own code: for every token row of a ubatch the
+    cells that llm_graph_input_attn_kv_unified::set_input (src/llama-graph.cpp:403-477) leaves unmasked — after the reference's
+    find_slot placed the ubatch and llama_context::decode's kv_self->n was set — hold exactly the tokens that the block-table
+    row + q_pos of PagedKVCache::prepare_batch name, in the same order.  Interleaved sequences, forks, truncations."""
+    rng = np.random.default_rng(1300 + seed)
+    bs = int(rng.choice([1, 4, 16]))
+    size, n_seq = 768, 5
+    r, pc = RefKV(1, 16, 2, size), pkg.PagedKVCache(size // bs + 64, bs)
+    content = np.full((size // bs + 64) * bs, -1, dtype=np.int64)
+    next_tok, rows = 0, 0
+    for _ in range(60):
+        op = rng.choice(["batch", "batch", "batch", "cp", "trunc", "rm"])
+        live = [s for s in range(n_seq) if pc.seq_len(s) > 0]
+        if op == "batch":
+            n = int(rng.integers(1, 40))
+            seq = [int(s) for s in rng.integers(0, n_seq, n)] if rng.random() < 0.7 else [int(rng.integers(0, n_seq))] * n
+            ans = r.cmd("M %d %s" % (n, " ".join(map(str, seq)))).split(" ")
+            if ans[0] == "noslot":
+                continue
+            got = pc.prepare_batch(seq)
+            assert isinstance(got, dict)
+            for a, b in got["cow_pairs"]:
+                content[b * bs:(b + 1) * bs] = content[a * bs:(a + 1) * bs]
+            content[got["slot_mapping"]] = np.arange(next_tok, next_tok + n); next_tok += n
+            stride = max((pc.seq_len(s) + bs - 1) // bs for s in got["seqs"])
+            bt, lens = pc.export(got["seqs"], stride)
+            assert len(ans) == 2 + n
+            for i in range(n):
+                want = [int(t) for t in ans[2 + i].split(",")]
+                row = np.asarray(bt[got["q_seq"][i]])
+                pos = np.arange(min(lens[got["q_seq"][i]], got["q_pos"][i] + 1))
+                assert content[row[pos // bs] * bs + pos % bs].tolist() == want
+                rows += 1
+        elif op == "cp" and live:
+            src, dst = int(rng.choice(live)), int(rng.integers(0, n_seq))
+            if dst != src:
+                p1 = int(rng.integers(1, pc.seq_len(src) + 1))
+                r.cmd(f"R {dst} -1 -1"); r.cmd(f"C {src} {dst} 0 {p1}")
+                assert pc.seq_cp(src, dst, 0, p1)
+        elif op == "trunc" and live:
+            s = int(rng.choice(live)); p0 = int(rng.integers(0, pc.seq_len(s) + 1))
+            assert r.cmd(f"R {s} {p0} -1") == "1" and pc.seq_rm(s, p0, -1)
+        elif op == "rm" and live:
+            s = int(rng.choice(live))
+            assert r.cmd(f"R {s} -1 -1") == "1" and pc.seq_rm(s)
+    assert rows > 200
+    r.close()
