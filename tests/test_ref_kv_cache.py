@@ -280,3 +280,39 @@ def test_prepare_batch_against_the_reference_mask_fill(pkg, seed):
             assert r.cmd(f"R {s} -1 -1") == "1" and pc.seq_rm(s)
     assert rows > 200
     r.close()
+
+
+def test_stream_rejections_against_the_reference_reader(pkg):
+    """every malformed single-sequence stream the product's parser rejects (by code) is rejected by the reference's own
+    state_read ("failed to restore kv cache", src/llama-kv-cache.cpp:886-903), and the well-formed one is accepted by both"""
+    from workloads import Q8_0
+    rng = np.random.default_rng(4)
+    n_layer, hd, nkv, n = 2, 16, 2, 5
+    k_row, v_row = row_bytes(Q8_0, hd * nkv), row_bytes(F16, hd * nkv)
+    rows = lambda w: rng.integers(0, 256, size=(n_layer, n, w), dtype=np.uint8)
+    good = pkg.state_seq_pack(rows(k_row), rows(v_row), Q8_0, F16)
+    meta_end = 4 + 8 * n
+    k0 = meta_end + 8
+    v0 = k0 + n_layer * (12 + n * k_row)
+
+    def patched(off, fmt, val):
+        b = bytearray(good)
+        struct.pack_into(fmt, b, off, val)
+        return bytes(b)
+
+    cases = {
+        "invalid seq_id-agnostic kv cell": patched(4 + 8 * 2 + 4, "<I", 1),
+        "mismatched layer count": patched(meta_end + 4, "<I", 3),
+        "incompatible V transposition": patched(meta_end, "<I", 1),
+        "mismatched key/value type": patched(k0, "<i", F16),
+        "mismatched key/value row size": patched(v0 + 4, "<Q", v_row - 2),
+        "truncated stream": good[:-7],
+    }
+    r = RefKV(n_layer, hd, nkv, 64, Q8_0, F16)
+    assert r.cmd(f"L 3 {good.hex()}") == "ok" and r.cmd("P 3") == str(n - 1)
+    pkg.state_seq_unpack(good, n_layer, Q8_0, k_row, F16, v_row)
+    for reason, blob in cases.items():
+        assert r.cmd(f"L 3 {blob.hex()}").startswith("fail"), reason
+        with pytest.raises(pkg.B200Error, match=reason):
+            pkg.state_seq_unpack(blob, n_layer, Q8_0, k_row, F16, v_row)
+    r.close()
