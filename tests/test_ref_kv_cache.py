@@ -202,9 +202,10 @@ def test_context_shift_against_the_reference_pair_of_calls(pkg, seed):
     assert r.cmd(f"A 0 {n}").startswith("slot")
     slots, _ = pc.append(0, n)
     content[slots] = np.arange(n)
+    fork = 0
     if rng.random() < 0.5:                                    # a fork first: shared blocks must be copied before they are written
-        p1 = int(rng.integers(1, n + 1))
-        r.cmd(f"C 0 1 0 {p1}"); assert pc.seq_cp(0, 1, 0, p1)
+        fork = int(rng.integers(1, n + 1))
+        r.cmd(f"C 0 1 0 {fork}"); assert pc.seq_cp(0, 1, 0, fork)
     p0 = int(rng.integers(0, n - 2)); p1 = int(rng.integers(p0 + 1, n))
     assert r.cmd(f"R 0 {p0} {p1}") == "1"
     r.cmd(f"T 0 {p1} -1 {-(p1 - p0)}")
@@ -226,8 +227,13 @@ def test_context_shift_against_the_reference_pair_of_calls(pkg, seed):
     assert marked == [(p, -(p1 - p0)) for p in range(p0, n - (p1 - p0))]
     cell_of = pc.slots_of(0)
     assert sorted(shift_cells) == sorted(cell_of[p] for p, _ in marked)
-    if pc.seq_len(1):                                          # the fork still sees what it saw
-        assert content[pc.slots_of(1)].tolist() == [t for _, t in r.visible(1)]
+    if fork:
+        # the fork keeps its own view in the block tables (shared blocks were copied before they were written)
+        assert content[pc.slots_of(1)].tolist() == list(range(fork))
+        if fork <= p1:                                         # none of its cells was moved: the reference agrees
+            assert [t for _, t in r.visible(1)] == list(range(fork))
+        # (fork > p1: the unified cache has ONE position per cell, so seq_add moves the shared cells under the fork as well,
+        #  src/llama-kv-cache.cpp:347-366 — a side effect the block tables do not reproduce)
     r.close()
 
 
