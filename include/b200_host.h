@@ -137,6 +137,40 @@ B200_API int64_t b200_kv_state_all_restore(b200_paged_cache *pc, const uint8_t *
  * Returns n_cells, or -1 when the pool has no room (the sequence is gone either way, as in the reference). */
 B200_API int64_t b200_pc_restore_seq(b200_paged_cache *pc, int32_t seq, int64_t n_cells, int32_t *slot_mapping);
 
+/*
+ * The reference's llama_kv_cache method surface (struct llama_kv_cache : llama_memory_i, src/llama-kv-cache.h:17-26,
+ * src/llama-memory.h:8-23; callers llama_kv_self_* in src/llama-context.cpp) on the block manager, for FFI hosts — the C++
+ * class is llama_kv_cache_paged (llama.cpp_test_b200/host/src/llama_kv_cache_paged.h), same names and argument order.
+ * seq_rm of a middle range stays open until the matching seq_add(seq, p1, -1, -(p1 - p0)) closes it into a context shift;
+ * the device work of shifts and defrags is handed out by b200_kvc_update (= kv_self_update) in execution order:
+ * b200_block_copy(cow_pairs), rows gather/scatter over row_moves, b200_k_shift(shift_cells, shift_delta),
+ * b200_block_copy(defrag_moves).  Requests the block tables cannot express (seq_div, a shift without a removal, a removal
+ * never closed) set b200_kvc_unsupported and make update / find_slot refuse.
+ */
+typedef struct b200_kv_cache b200_kv_cache;
+B200_API b200_kv_cache *b200_kvc_create(int64_t n_blocks, int32_t block_size);
+B200_API void    b200_kvc_destroy(b200_kv_cache *kv);
+B200_API void    b200_kvc_clear(b200_kv_cache *kv);
+B200_API void    b200_kvc_defrag(b200_kv_cache *kv);
+B200_API int32_t b200_kvc_seq_rm(b200_kv_cache *kv, int32_t seq, int32_t p0, int32_t p1);
+B200_API void    b200_kvc_seq_cp(b200_kv_cache *kv, int32_t src, int32_t dst, int32_t p0, int32_t p1);
+B200_API void    b200_kvc_seq_keep(b200_kv_cache *kv, int32_t seq);
+B200_API void    b200_kvc_seq_add(b200_kv_cache *kv, int32_t seq, int32_t p0, int32_t p1, int32_t delta);
+B200_API void    b200_kvc_seq_div(b200_kv_cache *kv, int32_t seq, int32_t p0, int32_t p1, int32_t d);
+B200_API int32_t b200_kvc_seq_pos_max(b200_kv_cache *kv, int32_t seq);
+B200_API int32_t b200_kvc_n_tokens(const b200_kv_cache *kv);
+B200_API int32_t b200_kvc_used_cells(const b200_kv_cache *kv);
+B200_API int32_t b200_kvc_unsupported(const b200_kv_cache *kv);
+B200_API int64_t b200_kvc_slots_of(const b200_kv_cache *kv, int32_t seq, int32_t *cells, int64_t cap);
+/* find_slot(ubatch): as b200_pc_prepare_batch; 1 also while deferred work is pending (decode runs kv_self_update first) */
+B200_API int32_t b200_kvc_find_slot(b200_kv_cache *kv, int32_t n_tokens, const int32_t *seq, const int32_t *pos,
+                                    int32_t *slot_mapping, int32_t *q_seq, int32_t *q_pos, int32_t *seqs, int64_t *n_seqs,
+                                    int32_t *cow_pairs, int64_t cow_cap, int64_t *n_cow);
+/* kv_self_update.  caps[4] / counts[5] = {cow pairs, row moves, shift cells, defrag moves}: call with caps == NULL to
+ * learn the counts (returns -3 if there is work, 1 if none), then with arrays that fit.  1 done, 0 unsupported request. */
+B200_API int32_t b200_kvc_update(b200_kv_cache *kv, int32_t *cow_pairs, int32_t *row_moves, int32_t *shift_cells, int32_t *shift_delta,
+                                 int32_t *defrag_moves, const int64_t caps[4], int64_t counts[5]);
+
 #ifdef __cplusplus
 }
 #endif

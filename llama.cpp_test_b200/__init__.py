@@ -109,7 +109,10 @@ EXPORTS = {
         "b200_fork_trace", "b200_pc_create", "b200_pc_destroy", "b200_pc_append", "b200_pc_prepare_batch", "b200_pc_undo_batch", "b200_pc_seq_cp", "b200_pc_seq_rm",
         "b200_pc_seq_keep", "b200_pc_clear", "b200_pc_seq_len", "b200_pc_n_free", "b200_pc_ref_count", "b200_pc_export",
         "b200_pc_slots_of", "b200_pc_defrag", "b200_pc_restore_seq", "b200_pc_context_shift", "b200_kv_state_seq_size", "b200_kv_state_seq_write",
-        "b200_kv_state_seq_parse", "b200_pc_used_cells", "b200_kv_state_all_write", "b200_kv_state_all_restore"],
+        "b200_kv_state_seq_parse", "b200_pc_used_cells", "b200_kv_state_all_write", "b200_kv_state_all_restore",
+        "b200_kvc_create", "b200_kvc_destroy", "b200_kvc_clear", "b200_kvc_defrag", "b200_kvc_seq_rm", "b200_kvc_seq_cp", "b200_kvc_seq_keep",
+        "b200_kvc_seq_add", "b200_kvc_seq_div", "b200_kvc_seq_pos_max", "b200_kvc_n_tokens", "b200_kvc_used_cells", "b200_kvc_unsupported",
+        "b200_kvc_slots_of", "b200_kvc_find_slot", "b200_kvc_update"],
 }
 
 lib.b200_paged_attention_workspace.restype = C.c_size_t
@@ -222,6 +225,37 @@ lib.b200_kv_state_all_restore.restype = C.c_int64
 lib.b200_kv_state_all_restore.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_int64,
                                           C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int64,
                                           C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+lib.b200_kvc_create.restype = C.c_void_p
+lib.b200_kvc_create.argtypes = [C.c_int64, C.c_int32]
+lib.b200_kvc_destroy.restype = None
+lib.b200_kvc_destroy.argtypes = [C.c_void_p]
+for _n in ("clear", "defrag"):
+    getattr(lib, "b200_kvc_" + _n).restype = None
+    getattr(lib, "b200_kvc_" + _n).argtypes = [C.c_void_p]
+lib.b200_kvc_seq_rm.restype = C.c_int32
+lib.b200_kvc_seq_rm.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32]
+lib.b200_kvc_seq_cp.restype = None
+lib.b200_kvc_seq_cp.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32]
+lib.b200_kvc_seq_keep.restype = None
+lib.b200_kvc_seq_keep.argtypes = [C.c_void_p, C.c_int32]
+lib.b200_kvc_seq_add.restype = None
+lib.b200_kvc_seq_add.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32]
+lib.b200_kvc_seq_div.restype = None
+lib.b200_kvc_seq_div.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32]
+lib.b200_kvc_seq_pos_max.restype = C.c_int32
+lib.b200_kvc_seq_pos_max.argtypes = [C.c_void_p, C.c_int32]
+for _n in ("n_tokens", "used_cells", "unsupported"):
+    getattr(lib, "b200_kvc_" + _n).restype = C.c_int32
+    getattr(lib, "b200_kvc_" + _n).argtypes = [C.c_void_p]
+lib.b200_kvc_slots_of.restype = C.c_int64
+lib.b200_kvc_slots_of.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.c_int64]
+lib.b200_kvc_find_slot.restype = C.c_int32
+lib.b200_kvc_find_slot.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
+                                   C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int64),
+                                   C.POINTER(C.c_int32), C.c_int64, C.POINTER(C.c_int64)]
+lib.b200_kvc_update.restype = C.c_int32
+lib.b200_kvc_update.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
+                                C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
 STATE_ERRORS = {-1: "truncated stream", -2: "invalid seq_id-agnostic kv cell", -3: "positions are not 0..n-1",
                 -4: "mismatched layer count", -5: "incompatible V transposition", -6: "mismatched key/value type",
                 -7: "mismatched key/value row size", -8: "not enough cells in kv cache", -9: "invalid seq_id"}

@@ -10,7 +10,7 @@ from . import (AttnDesc, B200Error, KShiftDesc, KVWriteDesc, KERNEL_AUTO, STATE_
 
 __all__ = ["KVLayout", "AttnCall", "StepCall", "kv_write_desc", "paged_attention", "dense_attention", "kv_write", "block_copy",
            "kv_rows_gather", "kv_rows_scatter", "k_shift", "context_shift", "state_seq_pack", "state_seq_unpack", "state_seq_save", "state_seq_load", "state_all_pack", "state_all_restore",
-           "BlockManager", "PagedKVCache", "current_stream"]
+           "BlockManager", "PagedKVCache", "LlamaKVCachePaged", "current_stream"]
 
 
 def current_stream() -> int:
@@ -506,3 +506,68 @@ class PagedKVCache:
         if not lib.b200_pc_export(self._h, ids, n, bt, stride, lens):
             return None
         return [[bt[i * stride + j] for j in range(stride)] for i in range(n)], [lens[i] for i in range(n)]
+
+
+class LlamaKVCachePaged:
+    """llama_kv_cache_paged through the C ABI (b200_kvc_*): the reference's llama_kv_cache method surface on the block manager"""
+
+    def __init__(self, n_blocks: int, block_size: int):
+        self._h = lib.b200_kvc_create(n_blocks, block_size)
+        self.n_blocks, self.block_size = n_blocks, block_size
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib.b200_kvc_destroy(self._h)
+            self._h = None
+
+    def clear(self): lib.b200_kvc_clear(self._h)
+    def defrag(self): lib.b200_kvc_defrag(self._h)
+    def seq_rm(self, seq, p0, p1): return bool(lib.b200_kvc_seq_rm(self._h, seq, p0, p1))
+    def seq_cp(self, src, dst, p0, p1): lib.b200_kvc_seq_cp(self._h, src, dst, p0, p1)
+    def seq_keep(self, seq): lib.b200_kvc_seq_keep(self._h, seq)
+    def seq_add(self, seq, p0, p1, delta): lib.b200_kvc_seq_add(self._h, seq, p0, p1, delta)
+    def seq_div(self, seq, p0, p1, d): lib.b200_kvc_seq_div(self._h, seq, p0, p1, d)
+    def seq_pos_max(self, seq): return lib.b200_kvc_seq_pos_max(self._h, seq)
+    def get_n_tokens(self): return lib.b200_kvc_n_tokens(self._h)
+    def get_used_cells(self): return lib.b200_kvc_used_cells(self._h)
+    def unsupported(self): return bool(lib.b200_kvc_unsupported(self._h))
+
+    def slots_of(self, seq):
+        n = lib.b200_kvc_slots_of(self._h, seq, None, 0)
+        if n == -1:
+            return None
+        n = max(-n - 1, 0) if n < 0 else n
+        buf = (C.c_int32 * max(n, 1))()
+        n = lib.b200_kvc_slots_of(self._h, seq, buf, max(n, 1))
+        return list(buf[:n])
+
+    def find_slot(self, seq, pos=None):
+        """find_slot(ubatch) -> dict like PagedKVCache.prepare_batch, or the status"""
+        n = len(seq)
+        arr = lambda v: (C.c_int32 * max(n, 1))(*v)
+        out = [(C.c_int32 * max(n, 1))() for _ in range(4)]
+        cow, n_seqs, n_cow = (C.c_int32 * (2 * max(n, 1)))(), C.c_int64(0), C.c_int64(0)
+        rc = lib.b200_kvc_find_slot(self._h, n, arr(seq), arr(pos) if pos is not None else None, out[0], out[1], out[2], out[3],
+                                    C.byref(n_seqs), cow, max(n, 1), C.byref(n_cow))
+        if rc != 0:
+            return rc
+        return dict(slot_mapping=list(out[0][:n]), q_seq=list(out[1][:n]), q_pos=list(out[2][:n]), seqs=list(out[3][:n_seqs.value]),
+                    cow_pairs=[(cow[2 * i], cow[2 * i + 1]) for i in range(n_cow.value)])
+
+    def update(self):
+        """kv_self_update -> dict(cow_pairs, row_moves, shift_cells, shift_delta, defrag_moves), or None when unsupported"""
+        counts = (C.c_int64 * 5)()
+        rc = lib.b200_kvc_update(self._h, None, None, None, None, None, None, counts)
+        if rc == 0:
+            return None
+        c = [int(x) for x in counts[:4]]
+        bufs = [(C.c_int32 * max(2 * c[0], 1))(), (C.c_int32 * max(2 * c[1], 1))(), (C.c_int32 * max(c[2], 1))(),
+                (C.c_int32 * max(c[2], 1))(), (C.c_int32 * max(2 * c[3], 1))()]
+        if rc == -3:
+            caps = (C.c_int64 * 4)(*c)
+            rc = lib.b200_kvc_update(self._h, bufs[0], bufs[1], bufs[2], bufs[3], bufs[4], caps, counts)
+        if rc != 1:
+            return None
+        pairs = lambda b, k: [(b[2 * i], b[2 * i + 1]) for i in range(k)]
+        return dict(cow_pairs=pairs(bufs[0], c[0]), row_moves=pairs(bufs[1], c[1]), shift_cells=list(bufs[2][:c[2]]),
+                    shift_delta=list(bufs[3][:c[2]]), defrag_moves=pairs(bufs[4], c[3]))

@@ -1,6 +1,8 @@
 // llama_kv_cache_paged.cpp — see src/llama_kv_cache_paged.h
 #include "llama_kv_cache_paged.h"
 
+#include <new>
+
 #include <algorithm>
 
 int32_t llama_kv_cache_paged::get_n_tokens() const {
@@ -121,3 +123,78 @@ bool llama_kv_cache_paged::update(pending_work & out) {
     if (do_defrag_) { cache_.defrag(out.defrag_moves); do_defrag_ = false; }
     return true;
 }
+
+// ---- C ABI (include/b200_host.h): the llama_kv_cache method surface for hosts that bind the library over FFI
+#include "b200_host.h"
+
+struct b200_kv_cache {
+    llama_kv_cache_paged impl;
+    llama_kv_cache_paged::pending_work held;                  // taken from impl.update() by the sizing call, handed out by the next
+    bool holding = false;
+    b200_kv_cache(int64_t n, int bs) : impl(n, bs) {}
+};
+
+extern "C" {
+
+B200_API b200_kv_cache *b200_kvc_create(int64_t n_blocks, int32_t block_size) {
+    return (n_blocks <= 0 || block_size <= 0) ? nullptr : new (std::nothrow) b200_kv_cache(n_blocks, block_size);
+}
+B200_API void    b200_kvc_destroy(b200_kv_cache *kv) { delete kv; }
+B200_API void    b200_kvc_clear(b200_kv_cache *kv) { kv->impl.clear(); kv->held = llama_kv_cache_paged::pending_work(); kv->holding = false; }
+B200_API void    b200_kvc_defrag(b200_kv_cache *kv) { kv->impl.defrag(); }
+B200_API int32_t b200_kvc_seq_rm(b200_kv_cache *kv, int32_t seq, int32_t p0, int32_t p1) { return kv->impl.seq_rm(seq, p0, p1) ? 1 : 0; }
+B200_API void    b200_kvc_seq_cp(b200_kv_cache *kv, int32_t src, int32_t dst, int32_t p0, int32_t p1) { kv->impl.seq_cp(src, dst, p0, p1); }
+B200_API void    b200_kvc_seq_keep(b200_kv_cache *kv, int32_t seq) { kv->impl.seq_keep(seq); }
+B200_API void    b200_kvc_seq_add(b200_kv_cache *kv, int32_t seq, int32_t p0, int32_t p1, int32_t delta) { kv->impl.seq_add(seq, p0, p1, delta); }
+B200_API void    b200_kvc_seq_div(b200_kv_cache *kv, int32_t seq, int32_t p0, int32_t p1, int32_t d) { kv->impl.seq_div(seq, p0, p1, d); }
+B200_API int32_t b200_kvc_seq_pos_max(b200_kv_cache *kv, int32_t seq) { return kv->impl.seq_pos_max(seq); }
+B200_API int32_t b200_kvc_n_tokens(const b200_kv_cache *kv) { return kv->impl.get_n_tokens(); }
+B200_API int32_t b200_kvc_used_cells(const b200_kv_cache *kv) { return (int32_t) kv->impl.get_used_cells(); }
+B200_API int32_t b200_kvc_unsupported(const b200_kv_cache *kv) { return kv->impl.unsupported() ? 1 : 0; }
+B200_API int64_t b200_kvc_slots_of(const b200_kv_cache *kv, int32_t seq, int32_t *cells, int64_t cap) {
+    std::vector<int32_t> v;
+    if (!kv->impl.blocks().slots_of(seq, v)) return -1;
+    if ((int64_t) v.size() > cap) return -(int64_t) v.size() - 1;
+    for (size_t i = 0; i < v.size(); ++i) cells[i] = v[i];
+    return (int64_t) v.size();
+}
+B200_API int32_t b200_kvc_find_slot(b200_kv_cache *kv, int32_t n_tokens, const int32_t *seq, const int32_t *pos,
+                                    int32_t *slot_mapping, int32_t *q_seq, int32_t *q_pos, int32_t *seqs, int64_t *n_seqs,
+                                    int32_t *cow_pairs, int64_t cow_cap, int64_t *n_cow) {
+    if (!kv || n_tokens < 0 || (n_tokens > 0 && (!seq || !slot_mapping || !q_seq || !q_pos || !seqs))) return -1;
+    if (cow_cap < n_tokens) return -3;
+    PagedKVCache::BatchInputs in;
+    const int rc = kv->impl.find_slot(n_tokens, seq, pos, in);
+    if (rc != 0) return rc;
+    for (int32_t i = 0; i < n_tokens; ++i) { slot_mapping[i] = in.slot_mapping[(size_t) i]; q_seq[i] = in.q_seq[(size_t) i]; q_pos[i] = in.q_pos[(size_t) i]; }
+    for (size_t r = 0; r < in.seqs.size(); ++r) seqs[r] = in.seqs[r];
+    if (n_seqs) *n_seqs = (int64_t) in.seqs.size();
+    for (size_t i = 0; i < in.cow_pairs.size(); ++i) { cow_pairs[2*i] = in.cow_pairs[i].first; cow_pairs[2*i + 1] = in.cow_pairs[i].second; }
+    if (n_cow) *n_cow = (int64_t) in.cow_pairs.size();
+    return 0;
+}
+// kv_self_update: counts[5] = {cow pairs, row moves, shift cells, defrag moves, 0}.  Call with NULL arrays to learn the counts
+// (nothing is consumed), then with arrays of at least that size.  Returns 1, 0 when a pending request cannot be expressed
+// (b200_kvc_unsupported), -3 when a capacity is too small.
+B200_API int32_t b200_kvc_update(b200_kv_cache *kv, int32_t *cow_pairs, int32_t *row_moves, int32_t *shift_cells, int32_t *shift_delta,
+                                 int32_t *defrag_moves, const int64_t caps[4], int64_t counts[5]) {
+    if (!kv || !counts) return -1;
+    llama_kv_cache_paged::pending_work & held = kv->held;
+    if (!kv->holding) {
+        if (!kv->impl.update(held)) { held = llama_kv_cache_paged::pending_work(); return 0; }
+        kv->holding = true;
+    }
+    counts[0] = (int64_t) held.cow_pairs.size(); counts[1] = (int64_t) held.row_moves.size();
+    counts[2] = (int64_t) held.shift_cells.size(); counts[3] = (int64_t) held.defrag_moves.size(); counts[4] = 0;
+    const bool fits = caps && caps[0] >= counts[0] && caps[1] >= counts[1] && caps[2] >= counts[2] && caps[3] >= counts[3];
+    if (!fits) { if ((counts[0] | counts[1] | counts[2] | counts[3]) == 0) { kv->holding = false; return 1; } return -3; }
+    for (size_t i = 0; i < held.cow_pairs.size(); ++i) { cow_pairs[2*i] = held.cow_pairs[i].first; cow_pairs[2*i + 1] = held.cow_pairs[i].second; }
+    for (size_t i = 0; i < held.row_moves.size(); ++i) { row_moves[2*i] = held.row_moves[i].first; row_moves[2*i + 1] = held.row_moves[i].second; }
+    for (size_t i = 0; i < held.shift_cells.size(); ++i) { shift_cells[i] = held.shift_cells[i]; shift_delta[i] = held.shift_delta[i]; }
+    for (size_t i = 0; i < held.defrag_moves.size(); ++i) { defrag_moves[2*i] = held.defrag_moves[i].first; defrag_moves[2*i + 1] = held.defrag_moves[i].second; }
+    held = llama_kv_cache_paged::pending_work();
+    kv->holding = false;
+    return 1;
+}
+
+} // extern "C"

@@ -322,3 +322,88 @@ def test_stream_rejections_against_the_reference_reader(pkg):
         with pytest.raises(pkg.B200Error, match=reason):
             pkg.state_seq_unpack(blob, n_layer, Q8_0, k_row, F16, v_row)
     r.close()
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_llama_kv_cache_adapter_against_the_reference_call_for_call(pkg, seed):
+    """llama_kv_cache_paged (through b200_kvc_*) and the reference's llama_kv_cache_unified receive the same llama_kv_self_*
+    calls, name for name — decode ubatches, seq_cp, tail seq_rm, seq_keep, and the context shift as the reference's callers
+    issue it (seq_rm of a middle range, then seq_add of the tail by the negative length) — with kv_self_update (b200_kvc_update)
+    before every decode as llama_context::decode runs it.  After every call every sequence must show the same token ids in
+    position order; get_n_tokens and seq_pos_max must agree.  (Shifts are only issued on sequences that share no cell: the
+    unified cache moves a shared cell for every owner, see the context-shift pin above.)"""
+    rng = np.random.default_rng(2100 + seed)
+    bs = int(rng.choice([1, 4, 16]))
+    size, n_seq = 768, 4
+    r, kv = RefKV(1, 16, 2, size), pkg.LlamaKVCachePaged(size // bs + 64, bs)
+    content = np.full((size // bs + 64) * bs, -1, dtype=np.int64)
+    next_tok, shifts = 0, 0
+    shared = set()                                            # sequences that took part in a seq_cp and still hold tokens
+
+    def run_update():
+        w = kv.update()
+        assert w is not None
+        for a, b in w["cow_pairs"]:
+            content[b * bs:(b + 1) * bs] = content[a * bs:(a + 1) * bs]
+        if w["row_moves"]:
+            content[[m[1] for m in w["row_moves"]]] = content[[m[0] for m in w["row_moves"]]].copy()
+        if w["defrag_moves"]:
+            snap = content.copy()
+            for a, b in w["defrag_moves"]:
+                content[b * bs:(b + 1) * bs] = snap[a * bs:(a + 1) * bs]
+
+    for _ in range(120):
+        run_update()                                          # kv_self_update before the decode
+        lens = {s: len(kv.slots_of(s) or []) for s in range(n_seq)}
+        live = [s for s in range(n_seq) if lens[s] > 0]
+        op = rng.choice(["decode", "decode", "decode", "cp", "shift", "shift", "trunc", "keep", "defrag"])
+        if op == "decode":
+            n = int(rng.integers(1, 30))
+            seq = [int(s) for s in rng.integers(0, n_seq, n)]
+            ans = r.cmd("B %d %s" % (n, " ".join(map(str, seq))))
+            if ans == "noslot":
+                continue
+            got = kv.find_slot(seq)
+            assert isinstance(got, dict)
+            for a, b in got["cow_pairs"]:
+                content[b * bs:(b + 1) * bs] = content[a * bs:(a + 1) * bs]
+            content[got["slot_mapping"]] = np.arange(next_tok, next_tok + n); next_tok += n
+        elif op == "cp" and live:
+            src, dst = int(rng.choice(live)), int(rng.integers(0, n_seq))
+            if dst == src:
+                continue
+            p1 = int(rng.integers(1, lens[src] + 1))
+            r.cmd(f"R {dst} -1 -1"); r.cmd(f"C {src} {dst} 0 {p1}")
+            kv.seq_cp(src, dst, 0, p1)
+            shared |= {src, dst}
+        elif op == "shift" and [s for s in live if s not in shared and lens[s] > 3]:
+            s = int(rng.choice([s for s in live if s not in shared and lens[s] > 3]))
+            p0 = int(rng.integers(0, lens[s] - 2)); p1 = int(rng.integers(p0 + 1, lens[s]))
+            assert r.cmd(f"R {s} {p0} {p1}") == "1" and kv.seq_rm(s, p0, p1)
+            r.cmd(f"T {s} {p1} -1 {p0 - p1}"); kv.seq_add(s, p1, -1, p0 - p1)
+            assert not kv.unsupported()
+            shifts += 1
+            run_update()
+        elif op == "trunc" and live:
+            s = int(rng.choice(live)); p0 = int(rng.integers(0, lens[s] + 1))
+            assert r.cmd(f"R {s} {p0} -1") == "1" and kv.seq_rm(s, p0, -1)
+            if p0 == 0:
+                shared.discard(s)
+        elif op == "keep" and live and rng.random() < 0.25:
+            s = int(rng.choice(live))
+            r.cmd(f"K {s}"); kv.seq_keep(s)
+            shared &= {s}
+        elif op == "defrag":
+            kv.defrag()                                       # the reference's defrag needs its graph: visibility must not change
+            run_update()
+        n_tokens = 0
+        for s in range(n_seq):
+            vis = r.visible(s)
+            cells = kv.slots_of(s) or []
+            assert [p for p, _ in vis] == list(range(len(vis))) and len(cells) == len(vis)
+            assert content[cells].tolist() == [t for _, t in vis]
+            assert kv.seq_pos_max(s) == int(r.cmd(f"P {s}"))
+            n_tokens += len(cells)
+        assert kv.get_n_tokens() == n_tokens == int(r.cmd("N").split()[0])
+    assert shifts >= 5                                        # the pair of calls really ran
+    r.close()
