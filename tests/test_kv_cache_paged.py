@@ -12,7 +12,7 @@ HOST = os.path.join(ROOT, "llama.cpp_test_b200", "host")
 
 def test_llama_kv_cache_paged_against_the_cell_model(tmp_path):
     exe = str(tmp_path / "kv_cache_paged_check")
-    cmd = ["g++", "-std=c++17", "-O1", "-Wall", "-Wextra", "-I", os.path.join(HOST, "src"),
+    cmd = ["g++", "-std=c++17", "-O1", "-Wall", "-Wextra", "-I", os.path.join(HOST, "src"), "-I", os.path.join(ROOT, "include"),
            os.path.join(ROOT, "tests", "cpp", "kv_cache_paged_check.cpp"),
            os.path.join(HOST, "llama_kv_cache_paged.cpp"), os.path.join(HOST, "paged_kv_cache.cpp"), "-o", exe]
     r = subprocess.run(cmd, capture_output=True, text=True)
