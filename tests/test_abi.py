@@ -171,3 +171,27 @@ def test_sass_of_the_hot_kernels_is_sm100a_tma_and_tcgen05(pkg, tmp_path):
     for name in ("pf_main_kernel", "dq_main_kernel"):
         fs = [f for f in funcs if name in f]
         assert fs and all({"UTMALDG", "UTCHMMA", "LDTM"} <= funcs[f] for f in fs), {f: funcs[f] for f in fs}
+
+
+def test_product_sources_never_reach_into_the_oracle():
+    """oracle/ is the checker: nothing under llama.cpp_test_b200/ or include/ may import, include, dlopen or exec it (only tests/,
+    __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs do)"""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    bad = []
+    for base in ("llama.cpp_test_b200", "include"):
+        for dirpath, dirnames, files in os.walk(os.path.join(root, base)):
+            dirnames[:] = [d for d in dirnames if d not in ("build", "__pycache__")]
+            for f in files:
+                if not f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".c", "Makefile")):
+                    continue
+                text = open(os.path.join(dirpath, f), errors="replace").read()
+                for m in re.finditer(r"(import\s+oracle|from\s+oracle|oracle/|liboracle|libref_|refkv)", text):
+                    line = text[text.rfind("\n", 0, m.start()) + 1:text.find("\n", m.end())]
+                    if not line.lstrip().startswith(("//", "#", "*", "/*")) and '"""' not in line:
+                        bad.append((f, line.strip()))
+    assert not bad, bad
+    # and bench.py only touches it in the two CPU legs
+    bench = open(os.path.join(root, "bench.py")).read()
+    for m in re.finditer(r"from oracle|import oracle", bench):
+        ctx = bench[max(0, bench.rfind("\ndef ", 0, m.start())):m.start()]
+        assert re.search(r"def \w*(cpu|reference)\w*\(", ctx), ctx[:80]         # cpu_layer_op & co: the CPU-baseline / reference legs
