@@ -215,6 +215,22 @@ B200_API int   b200_peer_exchange_ll(const void *local, int64_t bytes, void *con
                                      int32_t slot, int32_t rank, int32_t world, void *stream);
 B200_API int   b200_peer_read_state(const void *state, uint32_t out[4]);   /* synchronous D2H of the 4 state words */
 
+/*
+ * b200_paged_attention_static_ws — no counterpart in the reference.
+ * b200_paged_attention's stream-K decode path for callers that cannot call cudaMalloc (code under CUDA-graph capture,
+ * tight serving loops, harnesses that forbid it): d->workspace / d->workspace_bytes are IGNORED and the kernels' scratch
+ * (device-side plan + partials of split rows) is a file-scope __device__ array of B200_STATIC_WS_BYTES that every GPU
+ * loading the library holds until exit.  The call allocates nothing (no cudaMalloc / cudaFree / allocating library
+ * routine).  Paged mode on the stream-K kernel only (d->kernel AUTO or STREAMK; whatever b200_supports_attention
+ * accepts with kernel = B200_KERNEL_STREAMK); a call whose b200_paged_attention_workspace() exceeds
+ * B200_STATIC_WS_BYTES returns B200_ERR_ALLOC with the two sizes in b200_last_error().  All calls on one device share
+ * the one array (it keeps the last call's contents; nothing in it needs to start at zero): calls that overlap on the
+ * GPU — two streams, two host threads — race, so order them on one stream or with events.
+ */
+#define B200_STATIC_WS_BYTES (16u << 20)     /* 16 MiB: config 2 (64 rows x 32 heads) needs 5.9 MiB, config 4 (32 x 64) 10.7 MiB */
+B200_API size_t b200_static_workspace_bytes(void);
+B200_API int    b200_paged_attention_static_ws(const b200_attn_desc *d, void *stream);
+
 /* diagnostics */
 B200_API const char *b200_last_error(void);
 B200_API const char *b200_version(void);

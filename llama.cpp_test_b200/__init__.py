@@ -102,7 +102,8 @@ EXPORTS = {
         "b200_paged_attention_workspace", "b200_paged_attention", "b200_supports_attention", "b200_kv_write",
         "b200_block_copy", "b200_kv_rows_gather", "b200_kv_rows_scatter", "b200_k_shift", "b200_decode_step",
         "b200_peer_alloc", "b200_peer_free", "b200_peer_export", "b200_peer_open", "b200_peer_close", "b200_peer_publish",
-        "b200_peer_wait", "b200_peer_exchange", "b200_peer_exchange_ll", "b200_peer_read_state", "b200_last_error", "b200_version", "b200_device_sm_count", "b200_launch_count"],
+        "b200_peer_wait", "b200_peer_exchange", "b200_peer_exchange_ll", "b200_peer_read_state",
+        "b200_static_workspace_bytes", "b200_paged_attention_static_ws", "b200_last_error", "b200_version", "b200_device_sm_count", "b200_launch_count"],
     "b200_ggml_abi.h": ["b200_flash_attn_ext_workspace", "b200_flash_attn_ext", "b200_cpy", "b200_supports_op"],
     "b200_host.h": [
         "b200_bm_create", "b200_bm_destroy", "b200_bm_allocate", "b200_bm_free", "b200_bm_evict", "b200_bm_status",
@@ -119,6 +120,9 @@ lib.b200_paged_attention_workspace.restype = C.c_size_t
 lib.b200_paged_attention_workspace.argtypes = [C.POINTER(AttnDesc)]
 lib.b200_paged_attention.restype = C.c_int
 lib.b200_paged_attention.argtypes = [C.POINTER(AttnDesc), C.c_void_p]
+lib.b200_paged_attention_static_ws.restype = C.c_int
+lib.b200_paged_attention_static_ws.argtypes = [C.POINTER(AttnDesc), C.c_void_p]
+lib.b200_static_workspace_bytes.restype = C.c_size_t
 lib.b200_supports_attention.restype = C.c_int
 lib.b200_supports_attention.argtypes = [C.POINTER(AttnDesc)]
 lib.b200_kv_write.restype = C.c_int
