@@ -142,9 +142,11 @@ B200_API int64_t b200_pc_restore_seq(b200_paged_cache *pc, int32_t seq, int64_t 
  * src/llama-memory.h:8-23; callers llama_kv_self_* in src/llama-context.cpp) on the block manager, for FFI hosts — the C++
  * class is llama_kv_cache_paged (llama.cpp_test_b200/host/src/llama_kv_cache_paged.h), same names and argument order.
  * seq_rm of a middle range stays open until the matching seq_add(seq, p1, -1, -(p1 - p0)) closes it into a context shift;
- * the device work of shifts and defrags is handed out by b200_kvc_update (= kv_self_update) in execution order:
- * b200_block_copy(cow_pairs), rows gather/scatter over row_moves, b200_k_shift(shift_cells, shift_delta),
- * b200_block_copy(defrag_moves).  Requests the block tables cannot express (seq_div, a shift without a removal, a removal
+ * the device work of shifts and defrags is handed out by b200_kvc_update (= kv_self_update) in execution order, one GROUP
+ * per context shift closed since the last update (b200_kvc_update_groups gives each group's end in the three lists): for
+ * every group in turn b200_block_copy(its cow_pairs), rows gather/scatter over its row_moves, b200_k_shift(its shift_cells,
+ * shift_delta) — a group is finished before the next starts, because a later shift may reuse blocks an earlier one freed
+ * or read rows it wrote — and after the last group b200_block_copy(defrag_moves).  Requests the block tables cannot express (seq_div, a shift without a removal, a removal
  * never closed) set b200_kvc_unsupported and make update / find_slot refuse.
  */
 typedef struct b200_kv_cache b200_kv_cache;
@@ -166,10 +168,14 @@ B200_API int64_t b200_kvc_slots_of(const b200_kv_cache *kv, int32_t seq, int32_t
 B200_API int32_t b200_kvc_find_slot(b200_kv_cache *kv, int32_t n_tokens, const int32_t *seq, const int32_t *pos,
                                     int32_t *slot_mapping, int32_t *q_seq, int32_t *q_pos, int32_t *seqs, int64_t *n_seqs,
                                     int32_t *cow_pairs, int64_t cow_cap, int64_t *n_cow);
-/* kv_self_update.  caps[4] / counts[5] = {cow pairs, row moves, shift cells, defrag moves}: call with caps == NULL to
- * learn the counts (returns -3 if there is work, 1 if none), then with arrays that fit.  1 done, 0 unsupported request. */
+/* kv_self_update.  caps[4] / counts[5] = {cow pairs, row moves, shift cells, defrag moves, (counts only) groups}: call with
+ * caps == NULL to learn the counts (returns -3 if there is work, 1 if none), then with arrays that fit.  1 done, 0
+ * unsupported request. */
 B200_API int32_t b200_kvc_update(b200_kv_cache *kv, int32_t *cow_pairs, int32_t *row_moves, int32_t *shift_cells, int32_t *shift_delta,
                                  int32_t *defrag_moves, const int64_t caps[4], int64_t counts[5]);
+/* between the sizing call and the consuming call of b200_kvc_update: ends[g][3] = the cumulative {cow pairs, row moves,
+ * shift cells} at the end of group g.  Returns the number of groups, or -(n_groups) - 1 when cap is too small. */
+B200_API int64_t b200_kvc_update_groups(const b200_kv_cache *kv, int64_t *ends, int64_t cap);
 
 #ifdef __cplusplus
 }

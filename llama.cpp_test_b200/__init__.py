@@ -113,7 +113,7 @@ EXPORTS = {
         "b200_kv_state_seq_parse", "b200_pc_used_cells", "b200_kv_state_all_write", "b200_kv_state_all_restore",
         "b200_kvc_create", "b200_kvc_destroy", "b200_kvc_clear", "b200_kvc_defrag", "b200_kvc_seq_rm", "b200_kvc_seq_cp", "b200_kvc_seq_keep",
         "b200_kvc_seq_add", "b200_kvc_seq_div", "b200_kvc_seq_pos_max", "b200_kvc_n_tokens", "b200_kvc_used_cells", "b200_kvc_unsupported",
-        "b200_kvc_slots_of", "b200_kvc_find_slot", "b200_kvc_update"],
+        "b200_kvc_slots_of", "b200_kvc_find_slot", "b200_kvc_update", "b200_kvc_update_groups"],
 }
 
 lib.b200_paged_attention_workspace.restype = C.c_size_t
@@ -260,6 +260,8 @@ lib.b200_kvc_find_slot.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), 
 lib.b200_kvc_update.restype = C.c_int32
 lib.b200_kvc_update.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                 C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+lib.b200_kvc_update_groups.restype = C.c_int64
+lib.b200_kvc_update_groups.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.c_int64]
 STATE_ERRORS = {-1: "truncated stream", -2: "invalid seq_id-agnostic kv cell", -3: "positions are not 0..n-1",
                 -4: "mismatched layer count", -5: "incompatible V transposition", -6: "mismatched key/value type",
                 -7: "mismatched key/value row size", -8: "not enough cells in kv cache", -9: "invalid seq_id"}

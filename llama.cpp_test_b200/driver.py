@@ -555,12 +555,16 @@ class LlamaKVCachePaged:
                     cow_pairs=[(cow[2 * i], cow[2 * i + 1]) for i in range(n_cow.value)])
 
     def update(self):
-        """kv_self_update -> dict(cow_pairs, row_moves, shift_cells, shift_delta, defrag_moves), or None when unsupported"""
+        """kv_self_update -> dict(cow_pairs, row_moves, shift_cells, shift_delta, groups, defrag_moves), or None when
+        unsupported.  groups = [(cow_end, move_end, shift_end)] per context shift, to be executed one after another."""
         counts = (C.c_int64 * 5)()
         rc = lib.b200_kvc_update(self._h, None, None, None, None, None, None, counts)
         if rc == 0:
             return None
         c = [int(x) for x in counts[:4]]
+        ends = (C.c_int64 * max(3 * int(counts[4]), 1))()
+        n_groups = lib.b200_kvc_update_groups(self._h, ends, int(counts[4])) if rc == -3 else 0
+        groups = [(int(ends[3 * g]), int(ends[3 * g + 1]), int(ends[3 * g + 2])) for g in range(max(n_groups, 0))]
         bufs = [(C.c_int32 * max(2 * c[0], 1))(), (C.c_int32 * max(2 * c[1], 1))(), (C.c_int32 * max(c[2], 1))(),
                 (C.c_int32 * max(c[2], 1))(), (C.c_int32 * max(2 * c[3], 1))()]
         if rc == -3:
@@ -570,4 +574,4 @@ class LlamaKVCachePaged:
             return None
         pairs = lambda b, k: [(b[2 * i], b[2 * i + 1]) for i in range(k)]
         return dict(cow_pairs=pairs(bufs[0], c[0]), row_moves=pairs(bufs[1], c[1]), shift_cells=list(bufs[2][:c[2]]),
-                    shift_delta=list(bufs[3][:c[2]]), defrag_moves=pairs(bufs[4], c[3]))
+                    shift_delta=list(bufs[3][:c[2]]), groups=groups, defrag_moves=pairs(bufs[4], c[3]))

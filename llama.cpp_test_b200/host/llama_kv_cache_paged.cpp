@@ -33,7 +33,6 @@ void llama_kv_cache_paged::clear() {
     cache_.clear();
     work_ = pending_work();
     open_.clear();
-    shifted_.clear();
     do_defrag_ = false;
     unsupported_ = false;
 }
@@ -49,7 +48,7 @@ bool llama_kv_cache_paged::seq_rm(llama_seq_id seq_id, llama_pos p0, llama_pos p
     const int64_t e = (p1 < 0 || p1 > len) ? len : p1;
     if (p0 < e && e < len) {
         // tokens survive behind the removed range: remember it, the seq_add that follows closes the context shift
-        if (open_.count(seq_id) || shifted_.count(seq_id)) { unsupported_ = true; return false; }
+        if (open_.count(seq_id)) { unsupported_ = true; return false; }
         open_[seq_id] = std::make_pair(p0, (llama_pos) e);
         return true;
     }
@@ -82,9 +81,9 @@ void llama_kv_cache_paged::seq_add(llama_seq_id seq_id, llama_pos p0, llama_pos 
     open_.erase(it);
     if (!cache_.context_shift(seq_id, g0, g1, work_.cow_pairs, work_.row_moves, work_.shift_cells)) { unsupported_ = true; return; }
     work_.shift_delta.resize(work_.shift_cells.size(), delta);   // the reference's cells[i].delta (:360)
-    // one shift per sequence between two updates: the row moves of a second one would read what the first one has not
-    // written yet (the lists are executed as one batch: copies, gathers, scatters, rotation)
-    shifted_.insert(seq_id);
+    // this shift's share of the lists is one group; the consumer finishes a group before it starts the next, so a later
+    // shift (of this or another sequence) may reuse the blocks this one freed and read the rows this one wrote
+    work_.groups.push_back({work_.cow_pairs.size(), work_.row_moves.size(), work_.shift_cells.size()});
 }
 
 void llama_kv_cache_paged::seq_div(llama_seq_id, llama_pos p0, llama_pos p1, int d) {
@@ -119,7 +118,6 @@ bool llama_kv_cache_paged::update(pending_work & out) {
     if (!open_.empty() || unsupported_) { unsupported_ = true; return false; }
     out = std::move(work_);
     work_ = pending_work();
-    shifted_.clear();
     if (do_defrag_) { cache_.defrag(out.defrag_moves); do_defrag_ = false; }
     return true;
 }
@@ -173,7 +171,7 @@ B200_API int32_t b200_kvc_find_slot(b200_kv_cache *kv, int32_t n_tokens, const i
     if (n_cow) *n_cow = (int64_t) in.cow_pairs.size();
     return 0;
 }
-// kv_self_update: counts[5] = {cow pairs, row moves, shift cells, defrag moves, 0}.  Call with NULL arrays to learn the counts
+// kv_self_update: counts[5] = {cow pairs, row moves, shift cells, defrag moves, groups}.  Call with NULL arrays to learn the counts
 // (nothing is consumed), then with arrays of at least that size.  Returns 1, 0 when a pending request cannot be expressed
 // (b200_kvc_unsupported), -3 when a capacity is too small.
 B200_API int32_t b200_kvc_update(b200_kv_cache *kv, int32_t *cow_pairs, int32_t *row_moves, int32_t *shift_cells, int32_t *shift_delta,
@@ -185,7 +183,7 @@ B200_API int32_t b200_kvc_update(b200_kv_cache *kv, int32_t *cow_pairs, int32_t 
         kv->holding = true;
     }
     counts[0] = (int64_t) held.cow_pairs.size(); counts[1] = (int64_t) held.row_moves.size();
-    counts[2] = (int64_t) held.shift_cells.size(); counts[3] = (int64_t) held.defrag_moves.size(); counts[4] = 0;
+    counts[2] = (int64_t) held.shift_cells.size(); counts[3] = (int64_t) held.defrag_moves.size(); counts[4] = (int64_t) held.groups.size();
     const bool fits = caps && caps[0] >= counts[0] && caps[1] >= counts[1] && caps[2] >= counts[2] && caps[3] >= counts[3];
     if (!fits) { if ((counts[0] | counts[1] | counts[2] | counts[3]) == 0) { kv->holding = false; return 1; } return -3; }
     for (size_t i = 0; i < held.cow_pairs.size(); ++i) { cow_pairs[2*i] = held.cow_pairs[i].first; cow_pairs[2*i + 1] = held.cow_pairs[i].second; }
@@ -195,6 +193,15 @@ B200_API int32_t b200_kvc_update(b200_kv_cache *kv, int32_t *cow_pairs, int32_t 
     held = llama_kv_cache_paged::pending_work();
     kv->holding = false;
     return 1;
+}
+
+// the group boundaries of the work the sizing call of b200_kvc_update is holding: ends[g] = {cow_end, move_end, shift_end}
+B200_API int64_t b200_kvc_update_groups(const b200_kv_cache *kv, int64_t *ends, int64_t cap) {
+    if (!kv || !kv->holding) return 0;
+    const auto & g = kv->held.groups;
+    if ((int64_t) g.size() > cap || (!g.empty() && !ends)) return -(int64_t) g.size() - 1;
+    for (size_t i = 0; i < g.size(); ++i) { ends[3*i] = (int64_t) g[i].cow_end; ends[3*i + 1] = (int64_t) g[i].move_end; ends[3*i + 2] = (int64_t) g[i].shift_end; }
+    return (int64_t) g.size();
 }
 
 } // extern "C"

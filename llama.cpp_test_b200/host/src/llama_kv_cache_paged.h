@@ -12,8 +12,10 @@
 //                         pair becomes ONE PagedKVCache::context_shift; a pending range that is not closed that way by
 //                         the next update() / find_slot() fails there (positions with a hole cannot be a block table)
 //   seq_add               only as the closing half of a context shift (delta == p0 - p1 of the pending range, range to
-//                         the end of the sequence), once per sequence between two update() calls; anything else sets
-//                         `unsupported` (update() then fails, the caller falls back as for get_can_shift() == false)
+//                         the end of the sequence); anything else sets `unsupported` (update() then fails, the caller
+//                         falls back as for get_can_shift() == false).  Several shifts may close between two update()
+//                         calls (llama-server shifts several slots before one decode), of one sequence or of many: each
+//                         is its own GROUP of device work and the groups are executed one after another (see pending_work)
 //   seq_div               outside the block-table model: sets `unsupported`
 //   find_slot(ubatch)     -> find_slot(seq, n_tokens): slot mapping + copy-on-write pairs (llama_decode's "no KV slot": false)
 #pragma once
@@ -31,13 +33,21 @@ typedef int32_t llama_seq_id;
 
 class llama_kv_cache_paged {
 public:
-    // device work a call to update() hands out, in execution order
+    // device work a call to update() hands out, in execution order.
+    // One GROUP per context shift, in the order the shifts were closed: group g owns cow_pairs[groups[g-1].cow_end,
+    // groups[g].cow_end), row_moves[.. move_end) and shift_cells[.. shift_end), and the consumer runs a group to the end
+    // (copies, gather-all, scatter-all, rotation) before it starts the next one.  The order matters: a block one shift
+    // frees may be the copy-on-write destination of the next while it is still the source of the first one's row moves,
+    // and a sequence forked between two shifts shares blocks the first shift has yet to write.  (Running the flat lists
+    // phase by phase is only right when there is a single group.)
     struct pending_work {
+        struct group { size_t cow_end, move_end, shift_end; };
         std::vector<std::pair<int32_t, int32_t>> cow_pairs;    // b200_block_copy
         std::vector<std::pair<int32_t, int32_t>> row_moves;    // b200_kv_rows_gather (first) / _scatter (second), K and V
         std::vector<int32_t>                     shift_cells;  // b200_k_shift: cells ...
         std::vector<int32_t>                     shift_delta;  // ... and the delta of each (the reference's cell.delta)
-        std::vector<std::pair<int32_t, int32_t>> defrag_moves; // b200_block_copy, after everything above
+        std::vector<group>                       groups;       // cumulative ends of each shift's share of the three lists above
+        std::vector<std::pair<int32_t, int32_t>> defrag_moves; // b200_block_copy, after every group
         bool empty() const { return cow_pairs.empty() && row_moves.empty() && shift_cells.empty() && defrag_moves.empty(); }
     };
 
@@ -86,6 +96,5 @@ private:
     PagedKVCache cache_;
     pending_work work_;                                       // accumulated by closed context shifts
     std::map<llama_seq_id, std::pair<llama_pos, llama_pos>> open_;   // middle removals waiting for their seq_add
-    std::set<llama_seq_id> shifted_;                          // sequences with a context shift in work_
     bool do_defrag_ = false, unsupported_ = false;
 };

@@ -24,21 +24,91 @@ struct Model {                                               // seq -> tokens in
 };
 
 static void apply(const llama_kv_cache_paged::pending_work & w, std::vector<long> & store, int bs, std::vector<int> & rotated) {
-    for (auto & c : w.cow_pairs) for (int i = 0; i < bs; ++i) {
-        store[(size_t) c.second*bs + i] = store[(size_t) c.first*bs + i];
-        rotated[(size_t) c.second*bs + i] = rotated[(size_t) c.first*bs + i];
-    }
-    std::vector<long> staged; std::vector<int> staged_rot;   // gather every source, then scatter
-    for (auto & m : w.row_moves) { staged.push_back(store[(size_t) m.first]); staged_rot.push_back(rotated[(size_t) m.first]); }
-    for (size_t i = 0; i < w.row_moves.size(); ++i) { store[(size_t) w.row_moves[i].second] = staged[i]; rotated[(size_t) w.row_moves[i].second] = staged_rot[i]; }
+    // group by group, each to its end, as the device runs them (pending_work): copies, gather-all, scatter-all, rotation
     CHECK(w.shift_cells.size() == w.shift_delta.size());
-    for (size_t i = 0; i < w.shift_cells.size(); ++i) rotated[(size_t) w.shift_cells[i]] += w.shift_delta[i];
+    CHECK(w.groups.empty() ? (w.cow_pairs.empty() && w.row_moves.empty() && w.shift_cells.empty())
+                           : (w.groups.back().cow_end == w.cow_pairs.size() && w.groups.back().move_end == w.row_moves.size()
+                              && w.groups.back().shift_end == w.shift_cells.size()));
+    size_t c0 = 0, m0 = 0, s0 = 0;
+    for (auto & g : w.groups) {
+        CHECK(g.cow_end >= c0 && g.move_end >= m0 && g.shift_end >= s0);
+        for (size_t k = c0; k < g.cow_end; ++k) for (int i = 0; i < bs; ++i) {
+            store[(size_t) w.cow_pairs[k].second*bs + i] = store[(size_t) w.cow_pairs[k].first*bs + i];
+            rotated[(size_t) w.cow_pairs[k].second*bs + i] = rotated[(size_t) w.cow_pairs[k].first*bs + i];
+        }
+        std::vector<long> staged; std::vector<int> staged_rot;   // gather every source, then scatter
+        for (size_t k = m0; k < g.move_end; ++k) { staged.push_back(store[(size_t) w.row_moves[k].first]); staged_rot.push_back(rotated[(size_t) w.row_moves[k].first]); }
+        for (size_t k = m0; k < g.move_end; ++k) { store[(size_t) w.row_moves[k].second] = staged[k - m0]; rotated[(size_t) w.row_moves[k].second] = staged_rot[k - m0]; }
+        for (size_t k = s0; k < g.shift_end; ++k) rotated[(size_t) w.shift_cells[k]] += w.shift_delta[k];
+        c0 = g.cow_end; m0 = g.move_end; s0 = g.shift_end;
+    }
     std::vector<long> s2 = store; std::vector<int> r2 = rotated;
     for (auto & d : w.defrag_moves) for (int i = 0; i < bs; ++i) {
         s2[(size_t) d.second*bs + i] = store[(size_t) d.first*bs + i];
         r2[(size_t) d.second*bs + i] = rotated[(size_t) d.first*bs + i];
     }
     store.swap(s2); rotated.swap(r2);
+}
+
+// Several context shifts closed between two update() calls (llama-server shifts several slots before one decode).  Both
+// cases used to corrupt rows silently when the lists of all shifts were executed phase by phase.
+static void scenario_shifts_between_updates() {
+    auto read_back = [](llama_kv_cache_paged & kv, int seq, const std::vector<long> & store) {
+        std::vector<int32_t> cells; std::vector<long> out;
+        CHECK(kv.blocks().slots_of(seq, cells));
+        for (int32_t c : cells) out.push_back(store[(size_t) c]);
+        return out;
+    };
+    {   // 1: a block the first shift frees is the copy-on-write destination of the second while still a source of the first's moves
+        llama_kv_cache_paged kv(8, 4);
+        std::vector<long> store(32, -1); std::vector<int> rot(32, 0);
+        std::vector<int32_t> sl; std::vector<std::pair<int32_t, int32_t>> cw;
+        CHECK(kv.find_slot(0, 10, sl, cw)); for (size_t i = 0; i < sl.size(); ++i) store[(size_t) sl[i]] = (long) i;
+        sl.clear(); CHECK(kv.find_slot(1, 8, sl, cw));  for (size_t i = 0; i < sl.size(); ++i) store[(size_t) sl[i]] = 100 + (long) i;
+        kv.seq_cp(1, 2, 0, 8);
+        CHECK(kv.seq_rm(0, 1, 4)); kv.seq_add(0, 4, -1, -3);
+        CHECK(kv.seq_rm(1, 1, 2)); kv.seq_add(1, 2, -1, -1);
+        CHECK(!kv.unsupported());
+        llama_kv_cache_paged::pending_work w;
+        CHECK(kv.update(w) && w.groups.size() == 2);
+        apply(w, store, 4, rot);
+        CHECK(read_back(kv, 0, store) == std::vector<long>({0, 4, 5, 6, 7, 8, 9}));
+        CHECK(read_back(kv, 1, store) == std::vector<long>({100, 102, 103, 104, 105, 106, 107}));
+        CHECK(read_back(kv, 2, store) == std::vector<long>({100, 101, 102, 103, 104, 105, 106, 107}));
+    }
+    {   // 2: a fork between two shifts shares blocks the first shift has yet to write
+        llama_kv_cache_paged kv(8, 4);
+        std::vector<long> store(32, -1); std::vector<int> rot(32, 0);
+        std::vector<int32_t> sl; std::vector<std::pair<int32_t, int32_t>> cw;
+        CHECK(kv.find_slot(0, 10, sl, cw)); for (size_t i = 0; i < sl.size(); ++i) store[(size_t) sl[i]] = (long) i;
+        CHECK(kv.seq_rm(0, 1, 3)); kv.seq_add(0, 3, -1, -2);                 // 0 3 4 5 6 7 8 9
+        kv.seq_cp(0, 1, 0, -1);
+        CHECK(kv.seq_rm(1, 1, 2)); kv.seq_add(1, 2, -1, -1);                 // 0 4 5 6 7 8 9
+        CHECK(kv.seq_rm(0, 0, 1)); kv.seq_add(0, 1, -1, -1);                 // the same sequence a second time: 3 4 5 6 7 8 9
+        CHECK(!kv.unsupported());
+        llama_kv_cache_paged::pending_work w;
+        CHECK(kv.update(w) && w.groups.size() == 3);
+        apply(w, store, 4, rot);
+        CHECK(read_back(kv, 0, store) == std::vector<long>({3, 4, 5, 6, 7, 8, 9}));
+        CHECK(read_back(kv, 1, store) == std::vector<long>({0, 4, 5, 6, 7, 8, 9}));
+    }
+    {   // 3: a sequence dropped while its shift is pending: the stale scatters must land before a later copy reuses the block
+        llama_kv_cache_paged kv(6, 4);
+        std::vector<long> store(24, -1); std::vector<int> rot(24, 0);
+        std::vector<int32_t> sl; std::vector<std::pair<int32_t, int32_t>> cw;
+        CHECK(kv.find_slot(0, 7, sl, cw));  for (size_t i = 0; i < sl.size(); ++i) store[(size_t) sl[i]] = (long) i;
+        sl.clear(); CHECK(kv.find_slot(1, 8, sl, cw));  for (size_t i = 0; i < sl.size(); ++i) store[(size_t) sl[i]] = 100 + (long) i;
+        kv.seq_cp(1, 2, 0, 8);
+        CHECK(kv.seq_rm(0, 1, 2)); kv.seq_add(0, 2, -1, -1);
+        CHECK(kv.seq_rm(0, -1, -1));                                         // sequence 0 goes away, its blocks are free again
+        CHECK(kv.seq_rm(1, 2, 3)); kv.seq_add(1, 3, -1, -1);                 // copy-on-write into the freed blocks
+        CHECK(!kv.unsupported());
+        llama_kv_cache_paged::pending_work w;
+        CHECK(kv.update(w));
+        apply(w, store, 4, rot);
+        CHECK(read_back(kv, 1, store) == std::vector<long>({100, 101, 103, 104, 105, 106, 107}));
+        CHECK(read_back(kv, 2, store) == std::vector<long>({100, 101, 102, 103, 104, 105, 106, 107}));
+    }
 }
 
 static void scenario_basic() {
@@ -112,14 +182,19 @@ static void scenario_random(unsigned seed) {
     std::vector<int> rotated((size_t) n_blocks*bs, 0);       // accumulated K rotation per cell
     long next_tok = 0;
     auto R = [&](int n) { return (int) (rng() % (unsigned) n); };
-    int shifts = 0, defrags = 0;
+    int shifts = 0, defrags = 0, multi = 0;
     for (int step = 0; step < 200; ++step) {
-        // kv_self_update before every decode, as llama_context::decode does
-        llama_kv_cache_paged::pending_work w;
-        CHECK(kv.update(w));
-        apply(w, store, bs, rotated);
-        defrags += !w.defrag_moves.empty();
+        // kv_self_update before every decode, as llama_context::decode does; between two decodes any number of
+        // shifts, forks, removals and defrag requests may pile up (llama-server edits several slots, then decodes once)
         const int op = R(10);
+        std::vector<int> live0; for (auto & s : model.seqs) live0.push_back(s.first);
+        if (op < 4 || live0.empty() || R(3) == 0) {
+            llama_kv_cache_paged::pending_work w;
+            CHECK(kv.update(w));
+            apply(w, store, bs, rotated);
+            defrags += !w.defrag_moves.empty();
+            multi += w.groups.size() > 1;
+        }
         std::vector<int> live; for (auto & s : model.seqs) live.push_back(s.first);
         if (op < 4 || live.empty()) {                        // decode: append tokens
             const int seq = R(5), n = 1 + R(24);
@@ -186,11 +261,12 @@ static void scenario_random(unsigned seed) {
     int64_t free_blocks = 0;
     for (int b = 0; b < n_blocks; ++b) { CHECK(kv.blocks().ref_count(b) == refs[(size_t) b]); free_blocks += refs[(size_t) b] == 0; }
     CHECK(kv.blocks().n_free() == free_blocks);
-    std::printf("seed %u: block %d, %d context shifts, %d defrags, %d tokens cached\n", seed, bs, shifts, defrags, model.n_tokens());
+    std::printf("seed %u: block %d, %d context shifts, %d updates with several shift groups, %d defrags, %d tokens cached\n", seed, bs, shifts, multi, defrags, model.n_tokens());
 }
 
 int main() {
     scenario_basic();
+    scenario_shifts_between_updates();
     for (unsigned seed = 1; seed <= 24; ++seed) scenario_random(seed);
     std::printf("OK\n");
     return 0;
