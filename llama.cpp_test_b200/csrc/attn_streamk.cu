@@ -65,7 +65,14 @@ struct sk_args {
     float  qscale;                      // scale*log2(e), or scale/softcap when softcap != 0
     float  cap_log2e;                   // softcap*log2(e)
     uint32_t k65536;                    // 65536, read from the constant bank so ptxas keeps pack16 an IMAD (FMA pipe)
+    // dense-mask mode (an unmodified ggml graph: flat cache + F16 mask): d.block_table / seq_lens / q_seq are the tile
+    // lists sk_dense_scan_kernel wrote into the workspace; the mask is consulted again only on tiles it marked MIXED
+    const char *mask; int64_t nb_mask1; // F16 [n_kv, >= n_q] or NULL
+    float  alibi_m0, alibi_m1; int n_head_log2;   // ALiBi slopes (ggml-cpu.c:12294-12298); max_bias in d
+    int   *dense_len, *dense_bt, *dense_qseq;     // scan outputs: [n_q] visible cells (16 x listed tiles), [n_q][n_kv/16] tile ids, [n_q] zeros
+    int    n_tiles;                     // n_kv / 16
 };
+constexpr int SK_MIXED = 1 << 30;       // tile-list entry flag: some cell of the tile is hidden or carries a bias
 
 // ------------------------------------------------------------------------------------------------
 // per-type tile geometry for D = 128.  WIN = bytes of one token row of the shared-memory tile.
@@ -94,6 +101,8 @@ struct sk_smem {
     static constexpr int STAGES = ANY16 ? (STAGE <= 2560 ? 4 : 3) : (STAGE <= 2560 ? 5 : (WARPS == SK_WARPS && STAGE > 3584 ? 3 : 4));
     static constexpr int WARP = STAGE*STAGES;
     static constexpr int BAR_BYTES = ANY16 ? 1024 : 512;                          // mbarriers; F16 tiles must stay 1024-aligned
+    static constexpr int META_OFF = WARPS*STAGES*8;                               // dense mode: one tile-list entry per ring slot, behind the barriers
+    static_assert(META_OFF + WARPS*STAGES*4 <= BAR_BYTES, "barrier area too small for the dense-mode slot words");
     static constexpr int CTA = BAR_BYTES + WARP*WARPS + 16;                       // +16: funnel loads may touch 4 bytes past a row
     static constexpr int CTAS_PER_SM = 2*(CTA + 1024) <= 233472 ? 2 : 1;
 };
@@ -285,6 +294,54 @@ sk_plan_kernel(const __grid_constant__ sk_args a) {
         carry += tot;
     }
     if (threadIdx.x == 0) FS[p.n_q] = carry;
+}
+
+// ------------------------------------------------------------------------------------------------
+// dense-mask mode: the mask of an unmodified ggml graph -> per-row lists of 16-cell tiles
+// ------------------------------------------------------------------------------------------------
+// The reference's kernels add the mask after the dot product (fattn-vec-f32.cuh:197, fattn-mma-f16.cuh), so every query
+// row streams all n_kv cells of all sequences.  Here the mask (F16 [n_kv, >= n_q], filled by
+// llm_graph_input_attn_kv_unified::set_input, src/llama-graph.cpp:403-477) is read ONCE: row r gets the ascending list of
+// tiles holding at least one cell it may see (entry = tile id, | SK_MIXED when some cell of the tile is hidden or carries a
+// non-zero bias), and the stream-K plan runs over those lists exactly as over a block table with 16-cell blocks
+// (sequence = row, seq_lens[r] = 16 x listed tiles).  One CTA per row; a thread classifies 4 consecutive tiles (128
+// contiguous mask bytes) per step.
+__global__ void __launch_bounds__(1024)
+sk_dense_scan_kernel(const __grid_constant__ sk_args a) {
+    __shared__ int s_warp[32];
+    pdl_prologue();
+    const int row = blockIdx.x, n_tiles = a.n_tiles;
+    int *out = a.dense_bt + (int64_t) row*n_tiles;
+    if (a.mask == nullptr) {                                  // no mask (grid of one CTA): every row sees every cell, one identity list serves all
+        for (int t = threadIdx.x; t < n_tiles; t += 1024) out[t] = t;
+        for (int r = threadIdx.x; r < a.d.n_q; r += 1024) { a.dense_qseq[r] = 0; a.dense_len[r] = r == 0 ? n_tiles*SK_TILE : 0; }
+        return;
+    }
+    if (threadIdx.x == 0) a.dense_qseq[row] = row;
+    const uint4 *m = reinterpret_cast<const uint4 *>(a.mask + (int64_t) row*a.nb_mask1);
+    int base = 0;
+    for (int t0 = 0; t0 < n_tiles; t0 += 4096) {
+        const int tile0 = t0 + 4*threadIdx.x;
+        uint4 x[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) x[j] = tile0 + j/2 < n_tiles ? m[2*tile0 + j] : make_uint4(0xFC00FC00u, 0xFC00FC00u, 0xFC00FC00u, 0xFC00FC00u);
+        int ent[4], cnt = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint4 u = x[2*j], v = x[2*j + 1];
+            const bool hidden = u.x == 0xFC00FC00u && u.y == 0xFC00FC00u && u.z == 0xFC00FC00u && u.w == 0xFC00FC00u
+                             && v.x == 0xFC00FC00u && v.y == 0xFC00FC00u && v.z == 0xFC00FC00u && v.w == 0xFC00FC00u;     // sixteen times -inf
+            const bool clean = ((u.x | u.y | u.z | u.w | v.x | v.y | v.z | v.w) & 0x7FFF7FFFu) == 0;                       // sixteen times +-0
+            ent[j] = hidden ? -1 : ((tile0 + j) | (clean ? 0 : SK_MIXED));
+            cnt += hidden ? 0 : 1;
+        }
+        int tot;
+        int o = base + sk_block_scan(cnt, s_warp, &tot);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { if (ent[j] >= 0) out[o++] = ent[j]; }
+        base += tot;
+    }
+    if (threadIdx.x == 0) a.dense_len[row] = base*SK_TILE;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -501,7 +558,7 @@ __device__ __forceinline__ int sk_row_d(int mt, int h, int g) {
 // ------------------------------------------------------------------------------------------------
 // main kernel
 // ------------------------------------------------------------------------------------------------
-template <int TK, int TV>
+template <int TK, int TV, bool DENSE>
 __global__ void __launch_bounds__(32*sk_smem<TK, TV>::WARPS, sk_smem<TK, TV>::CTAS_PER_SM)
 sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV) {
     extern __shared__ __align__(1024) char sk_dyn[];
@@ -540,6 +597,7 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
 
     uint32_t smem0 = smem_u32(sk_dyn) + SM::BAR_BYTES + warp*SM::WARP;
     uint32_t bar0  = smem_u32(sk_dyn) + warp*STAGES*8;
+    const uint32_t meta0 = smem_u32(sk_dyn) + SM::META_OFF + warp*STAGES*4;      // DENSE: the tile-list entry of each ring slot
     asm volatile("mov.b32 %0, %0;" : "+r"(smem0));
     asm volatile("mov.b32 %0, %0;" : "+r"(bar0));
     if (lane == 0) {
@@ -578,6 +636,17 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
         const int32_t *bt = p.block_table + (int64_t) seq*p.bt_stride;
         const int seg = FS[row] + (item - pb/chunk);
         const bool single = (FS[row + 1] - FS[row]) == 1;
+        // DENSE: this row's mask line and the ALiBi slopes of the lane's two query heads, in the log2 domain
+        const __half *mrow = nullptr;
+        float sl0 = 1.4426950408889634f, sl1 = 1.4426950408889634f;
+        if constexpr (DENSE) {
+            mrow = reinterpret_cast<const __half *>(a.mask + (int64_t) row*a.nb_mask1);
+            if (p.max_bias > 0.0f) {
+                const int hh = kvh*a.gqa + 2*t;
+                sl0 *= hh     < a.n_head_log2 ? powf(a.alibi_m0, (float) (hh + 1)) : powf(a.alibi_m1, (float) (2*(hh     - a.n_head_log2) + 1));
+                sl1 *= hh + 1 < a.n_head_log2 ? powf(a.alibi_m0, (float) (hh + 2)) : powf(a.alibi_m1, (float) (2*(hh + 1 - a.n_head_log2) + 1));
+            }
+        }
 
         float O[8][4];
 #pragma unroll
@@ -596,8 +665,9 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
                 win_next = win_base + 32 + lane < n_blk ? bt[win_base + 32 + lane] : 0;
             }
             const int blk = __shfl_sync(0xffffffffu, win, b_cur - win_base);
-            const int cell = blk*bs + o_cur*SK_TILE;
+            const int cell = (DENSE ? (blk & (SK_MIXED - 1)) : blk)*bs + o_cur*SK_TILE;
             if (++o_cur == tpb) { o_cur = 0; ++b_cur; }
+            if constexpr (DENSE) { if (lane == 0) asm volatile("st.shared.b32 [%0], %1;" :: "r"(meta0 + 4*is), "r"(blk) : "memory"); }
             {
                 const uint32_t bar = bar0 + 8*is, sb = smem0 + is*SM::STAGE;
                 sk_issue_elect<TK == B200_TYPE_F16, TV == B200_TYPE_F16>(bar, SM::KT + SM::VT, sb + SM::KOFF, &tmK, kc,
@@ -629,11 +699,12 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
             const int nsub = FULL ? NSUB : min(NSUB, nt - i);        // tiles of this iteration (warp-uniform)
             // FULL iterations wait for their first tile only; the later ones were requested last and are waited for
             // right before their own Q.K^T, behind the first tile's
-            uint32_t kbs[NSUB], vbs[NSUB], tbar[NSUB], tph[NSUB];
+            uint32_t kbs[NSUB], vbs[NSUB], tbar[NSUB], tph[NSUB], ment[NSUB];
 #pragma unroll
             for (int u = 0; u < NSUB; ++u) {
-                kbs[u] = vbs[u] = tbar[u] = tph[u] = 0;
+                kbs[u] = vbs[u] = tbar[u] = tph[u] = ment[u] = 0;
                 if (FULL || u < nsub) {
+                    if constexpr (DENSE && !FULL) ment[u] = lds32(meta0 + 4*cs);
                     if (!FULL || u == 0) mbar_wait(bar0 + 8*cs, cph);
                     tbar[u] = bar0 + 8*cs; tph[u] = cph;
                     const uint32_t sb = smem0 + cs*SM::STAGE;
@@ -670,6 +741,11 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
 #pragma unroll
                             for (int j = 0; j < 4; ++j) A[j] = a.cap_log2e*tanhf(A[j]);
                         }
+                    }
+                    if constexpr (DENSE && !FULL) {               // mask values of the tile's cells: -inf hides, anything else is a bias
+                        const int c0 = (int) (ment[u] & (SK_MIXED - 1))*SK_TILE + g;
+                        const float mv0 = __half2float(mrow[c0]), mv1 = __half2float(mrow[c0 + 8]);
+                        A[0] = fmaf(sl0, mv0, A[0]); A[1] = fmaf(sl1, mv0, A[1]); A[2] = fmaf(sl0, mv1, A[2]); A[3] = fmaf(sl1, mv1, A[3]);
                     }
                     S[u][0] = A[0]; S[u][1] = A[1]; S[u][2] = A[2]; S[u][3] = A[3];
                     if constexpr (!FULL) {
@@ -715,8 +791,17 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
             __syncwarp();                                    // every lane is done with the slots about to be refilled
 #pragma unroll
             for (int u = 0; u < NSUB; ++u) { if (issued < nt) { issue(); ++issued; } }
-            if (no_cap && i + NSUB <= nt && (t0 + i + NSUB)*SK_TILE <= n_vis) body(std::true_type{}, i);
-            else                                                              body(std::false_type{}, i);
+            bool fast = no_cap && i + NSUB <= nt && (t0 + i + NSUB)*SK_TILE <= n_vis;
+            if constexpr (DENSE) {                           // and no tile of the iteration is marked MIXED
+                if (fast) {
+                    uint32_t any = 0;
+#pragma unroll
+                    for (int u = 0; u < NSUB; ++u) any |= lds32(meta0 + 4*((cs + u) % STAGES));
+                    fast = !(any & SK_MIXED);
+                }
+            }
+            if (fast) body(std::true_type{}, i);
+            else      body(std::false_type{}, i);
         }
 
         // ---- segment epilogue
@@ -808,17 +893,36 @@ static int sk_sm_count() {
 
 static bool sk_type_ok(int t) { return t == B200_TYPE_F16 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_0; }
 
+// dense-mask mode (block_table == NULL): the flat cache of an unmodified ggml graph, scanned into tile lists first
+static bool sk_dense(const b200_attn_desc &d) { return d.block_table == nullptr; }
+
 bool streamk_supports(const b200_attn_desc &d) {
-    if (!d.block_table || d.head_dim != SK_D || d.max_bias != 0.0f) return false;
+    if (d.head_dim != SK_D) return false;
     if (!sk_type_ok(d.type_k) || !sk_type_ok(d.type_v)) return false;
     const int gqa = d.n_head/d.n_head_kv;
     if (gqa < 1 || gqa > 8) return false;
-    if (d.block_size % SK_TILE || d.n_kv < SK_TILE) return false;                          // one TMA box = 16 consecutive cells
+    if (sk_dense(d)) {
+        if (d.n_kv % SK_TILE || d.n_kv < SK_TILE || d.n_q < 1) return false;                // whole 16-cell tiles
+        if (d.mask) {
+            if (d.type_k != d.type_v) return false;                                         // the DENSE kernels exist for equal K/V types
+            if (((uintptr_t) d.mask | (uint64_t) d.nb_mask1) & 15) return false;            // 16-byte loads of the mask rows
+        }
+        if ((int64_t) d.n_q*(d.n_kv/SK_TILE) > (1LL << 28)) return false;                    // tile lists: n_q x n_kv/16 ints of workspace
+    } else {
+        if (d.max_bias != 0.0f) return false;                                               // ALiBi needs the mask's positions
+        if (d.block_size % SK_TILE || d.n_kv < SK_TILE) return false;                       // one TMA box = 16 consecutive cells
+    }
     if (((uintptr_t) d.k | (uintptr_t) d.v | (uint64_t) d.nbk1 | (uint64_t) d.nbv1) & 15) return false;
     if ((d.nbk2 & (d.type_k == B200_TYPE_F16 ? 127 : 7)) || (d.nbv2 & (d.type_v == B200_TYPE_F16 ? 127 : 7))) return false;
     if (d.nbk1 <= 0 || d.nbv1 <= 0 || d.nbk2 <= 0 || d.nbv2 <= 0) return false;
-    if ((int64_t) d.n_head_kv*d.nbk2 > d.nbk1 || (int64_t) d.n_head_kv*d.nbv2 > d.nbv1) return false;   // heads inside the token row
-    if (d.n_kv*(d.nbk1 > d.nbv1 ? d.nbk1 : d.nbv1) >= (1LL << 40) || d.n_kv >= (1LL << 31)) return false;
+    // heads inside the token row (the llama.cpp cache, cell-major).  An F16 tensor may also be head-major ([d, n_kv, n_head]
+    // contiguous, as tests/test-backend-ops.cpp builds K and V): its 3-D map addresses 128-byte pieces by (cell, piece) with
+    // strides (nb1, 128), which is indifferent to the order of the two.  Quantised head-major rows are 136 / 72 bytes apart
+    // (not a legal TMA stride) and stay with the CUDA-core kernel.
+    if ((int64_t) d.n_head_kv*d.nbk2 > d.nbk1 && d.type_k != B200_TYPE_F16) return false;
+    if ((int64_t) d.n_head_kv*d.nbv2 > d.nbv1 && d.type_v != B200_TYPE_F16) return false;
+    const int64_t span_k = d.n_kv*d.nbk1 + (int64_t) d.n_head_kv*d.nbk2, span_v = d.n_kv*d.nbv1 + (int64_t) d.n_head_kv*d.nbv2;
+    if ((span_k > span_v ? span_k : span_v) >= (1LL << 40) || d.n_kv >= (1LL << 31)) return false;
     if (((uintptr_t) d.q | (uint64_t) d.nbq1 | (uint64_t) d.nbq2) & 15) return false;      // float4 loads of Q
     if ((uintptr_t) d.dst & 15) return false;
     return true;
@@ -848,7 +952,7 @@ static int sk_items(const b200_attn_desc &d) {
 // the tcgen05 formulation (attn_decode_dq.cuh): Q8_0 K and V, big enough that 128-token super-tiles fill the GPU.
 // B200_DECODE_DQ=0 / 1 forces it off / on wherever it is legal (A/B runs); kernel id B200_KERNEL_STREAMK_DQ asks for it.
 static bool dq_legal(const b200_attn_desc &d) {
-    return d.type_k == B200_TYPE_Q8_0 && d.type_v == B200_TYPE_Q8_0 && d.logit_softcap == 0.0f;
+    return d.block_table && d.type_k == B200_TYPE_Q8_0 && d.type_v == B200_TYPE_Q8_0 && d.logit_softcap == 0.0f;
 }
 bool streamk_dq_supports(const b200_attn_desc &d) { return dq_legal(d); }
 constexpr bool DQ_AUTO = false;                              // AUTO keeps the mma.sync kernel until the A/B says otherwise
@@ -875,9 +979,14 @@ static bool dq_wanted(const b200_attn_desc &d) {
 
 static size_t sk_align(size_t x) { return (x + 255) & ~(size_t) 255; }
 
+// dense mode: [n_q] visible cells per row, [n_q] q_seq, [n_q][n_kv/16] tile lists, in front of the usual layout
+static size_t sk_dense_bytes(const b200_attn_desc &d) {
+    return sk_dense(d) ? sk_align((2*(size_t) d.n_q + (size_t) d.n_q*(size_t) (d.n_kv/SK_TILE))*sizeof(int)) : 0;
+}
+
 size_t streamk_workspace(const b200_attn_desc &d) {
     const size_t max_segs = (size_t) sk_items(d) + d.n_q;
-    return sk_align((4 + 2*((size_t) d.n_q + 1))*sizeof(int)) + sk_align(max_segs*d.n_head*2*sizeof(float))
+    return sk_dense_bytes(d) + sk_align((4 + 2*((size_t) d.n_q + 1))*sizeof(int)) + sk_align(max_segs*d.n_head*2*sizeof(float))
          + max_segs*d.n_head*SK_D*sizeof(float);
 }
 
@@ -922,18 +1031,18 @@ static bool sk_make_map(CUtensorMap *tm, int type, const void *base, int64_t nb1
     return true;
 }
 
-template <int TK, int TV>
+template <int TK, int TV, bool DENSE = false>
 static int sk_launch(const sk_args &a, const CUtensorMap &tmK, const CUtensorMap &tmV, cudaStream_t st) {
     using SM = sk_smem<TK, TV>;
     static bool configured = false;
     if (!configured) {
-        const cudaError_t e = cudaFuncSetAttribute(sk_main_kernel<TK, TV>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::CTA);
+        const cudaError_t e = cudaFuncSetAttribute(sk_main_kernel<TK, TV, DENSE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::CTA);
         if (e != cudaSuccess) { set_error("stream-K: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return B200_ERR_CUDA; }
         configured = true;
     }
     const int64_t warps = (int64_t) a.n_items*a.d.n_head_kv;
     const unsigned grid = (unsigned) ((warps + SM::WARPS - 1)/SM::WARPS);
-    launch_pdl(sk_main_kernel<TK, TV>, dim3(grid), dim3(32*SM::WARPS), SM::CTA, st, a, tmK, tmV);
+    launch_pdl(sk_main_kernel<TK, TV, DENSE>, dim3(grid), dim3(32*SM::WARPS), SM::CTA, st, a, tmK, tmV);
     return B200_OK;
 }
 
@@ -964,6 +1073,23 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st) {
     a.chunk_min = dq ? 1 : SK_MIN_CHUNK;
     const size_t max_segs = (size_t) sk_items(d) + d.n_q;    // the layout streamk_workspace() promised
     char *ws = static_cast<char *>(d.workspace);
+    const bool dense = sk_dense(d);
+    a.mask = nullptr; a.nb_mask1 = 0; a.alibi_m0 = a.alibi_m1 = 1.0f; a.n_head_log2 = 1;
+    a.dense_len = a.dense_bt = a.dense_qseq = nullptr; a.n_tiles = 0;
+    if (dense) {                                             // the tile lists stand in for block table / seq_lens / q_seq
+        a.n_tiles    = (int) (d.n_kv/SK_TILE);
+        a.dense_len  = reinterpret_cast<int *>(ws);
+        a.dense_qseq = a.dense_len + d.n_q;
+        a.dense_bt   = a.dense_qseq + d.n_q;
+        ws += sk_dense_bytes(d);
+        a.mask = static_cast<const char *>(d.mask); a.nb_mask1 = d.nb_mask1;
+        a.n_head_log2 = 1 << (int) floor(log2((double) d.n_head));                       // ggml-cpu.c:12294-12298
+        a.alibi_m0 = powf(2.0f, -(d.max_bias       )/a.n_head_log2);
+        a.alibi_m1 = powf(2.0f, -(d.max_bias / 2.0f)/a.n_head_log2);
+        a.d.block_table = a.dense_bt; a.d.bt_stride = a.n_tiles; a.d.block_size = SK_TILE;
+        a.d.seq_lens = a.dense_len; a.d.n_seqs = d.n_q;
+        a.d.q_seq = a.dense_qseq; a.d.q_pos = nullptr;
+    }
     a.plan = reinterpret_cast<int *>(ws);
     ws += sk_align((4 + 2*((size_t) d.n_q + 1))*sizeof(int));
     a.part_ml = reinterpret_cast<float *>(ws);
@@ -977,13 +1103,25 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st) {
     if (!sk_make_map(&tmK, d.type_k, d.k, d.nbk1, d.nbk2, d.n_head_kv, d.n_kv)) return B200_ERR_CUDA;
     if (!sk_make_map(&tmV, d.type_v, d.v, d.nbv1, d.nbv2, d.n_head_kv, d.n_kv)) return B200_ERR_CUDA;
 
-    if (!(d.flags & B200_ATTN_REUSE_PLAN)) {                 // layers 1.. of a step run on layer 0's schedule
+    if (dense) {
+        launch_pdl(sk_dense_scan_kernel, dim3(d.mask ? (unsigned) d.n_q : 1u), dim3(1024), 0, st, a);
+        count_launch();
+        if (!check_launch("sk_dense_scan")) return B200_ERR_CUDA;
+    }
+    if (dense || !(d.flags & B200_ATTN_REUSE_PLAN)) {        // layers 1.. of a step run on layer 0's schedule
         launch_pdl(sk_plan_kernel, dim3(1), dim3(1024), 0, st, a);
         count_launch();
         if (!check_launch("sk_plan")) return B200_ERR_CUDA;
     }
-    const int rc = dq ? dq_launch(a, tmK, tmV, st)
-                      : sk_dispatch(d.type_k, d.type_v, [&](auto k, auto v) { return sk_launch<decltype(k)::value, decltype(v)::value>(a, tmK, tmV, st); });
+    int rc;
+    if (dq) rc = dq_launch(a, tmK, tmV, st);
+    else if (dense && d.mask) {                              // equal K/V types (streamk_supports)
+        rc = d.type_k == B200_TYPE_F16  ? sk_launch<B200_TYPE_F16,  B200_TYPE_F16,  true>(a, tmK, tmV, st)
+           : d.type_k == B200_TYPE_Q8_0 ? sk_launch<B200_TYPE_Q8_0, B200_TYPE_Q8_0, true>(a, tmK, tmV, st)
+                                        : sk_launch<B200_TYPE_Q4_0, B200_TYPE_Q4_0, true>(a, tmK, tmV, st);
+    } else {
+        rc = sk_dispatch(d.type_k, d.type_v, [&](auto k, auto v) { return sk_launch<decltype(k)::value, decltype(v)::value>(a, tmK, tmV, st); });
+    }
     if (rc != B200_OK) return rc;
     count_launch();
     if (!check_launch("sk_main")) return B200_ERR_CUDA;

@@ -56,6 +56,9 @@ static bool node_to_desc(const b200_ggml_tensor *dst, b200_attn_desc &d) {
         const b200_ggml_tensor *SL = dst->src[5], *QS = dst->src[6], *QP = dst->src[7];
         if (BT->type != B200_GGML_TYPE_I32 || !SL || SL->type != B200_GGML_TYPE_I32) { set_error("flash_attn_ext: block_table/seq_lens must be I32"); return false; }
         if ((QS && QS->type != B200_GGML_TYPE_I32) || (QP && QP->type != B200_GGML_TYPE_I32)) { set_error("flash_attn_ext: q_seq/q_pos must be I32"); return false; }
+        // a block table says "row t sees positions [0, min(seq_len, q_pos + 1)) of its sequence" and nothing else: a node that also
+        // carries a mask (non-causal, sliding window, ALiBi) would silently lose it
+        if (M) { set_error("flash_attn_ext: a paged node (src[4] block table) must not carry a mask (src[3])"); return false; }
         d.block_table = static_cast<const int32_t *>(BT->data);
         d.bt_stride   = (int64_t) (BT->nb[1]/4);
         d.n_seqs      = (int32_t) BT->ne[1];

@@ -167,7 +167,7 @@ def test_sass_of_the_hot_kernels_is_sm100a_tma_and_tcgen05(pkg, tmp_path):
                 if m in line:
                     funcs[cur].add(m)
     sk = [f for f in funcs if "sk_main_kernel" in f]
-    assert len(sk) == 9 and all({"UTMALDG", "HMMA.16816", "SYNCS"} <= funcs[f] for f in sk), {f: funcs[f] for f in sk}
+    assert len(sk) == 12 and all({"UTMALDG", "HMMA.16816", "SYNCS"} <= funcs[f] for f in sk), {f: funcs[f] for f in sk}   # 9 K/V type pairs + 3 dense-mask forms
     for name in ("pf_main_kernel", "dq_main_kernel"):
         fs = [f for f in funcs if name in f]
         assert fs and all({"UTMALDG", "UTCHMMA", "LDTM"} <= funcs[f] for f in fs), {f: funcs[f] for f in fs}

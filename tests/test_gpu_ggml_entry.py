@@ -170,6 +170,13 @@ def test_flash_attn_ext_node_paged_extension(pkg, oracle, cuda):
     assert pkg.lib.b200_flash_attn_ext(C.byref(dst), ws.data_ptr(), need, None) == 0, pkg.lib.b200_last_error().decode()
     torch.cuda.synchronize()
     assert oracle.max_rel_err(want, out.cpu().numpy()) <= 1e-2
+    # a paged node must not also carry a mask: it would be dropped silently (the block table only says "causal prefix")
+    mbuf = torch.zeros(64 * w.n_cells, dtype=torch.float16, device=dev)
+    m = _node(pkg, F16, (w.n_cells, 64, 1, 1), (2, w.n_cells * 2), mbuf.data_ptr())
+    dst.src[3] = C.pointer(m)
+    assert pkg.lib.b200_supports_op(C.byref(dst)) == 0
+    assert pkg.lib.b200_flash_attn_ext(C.byref(dst), ws.data_ptr(), need, None) != 0
+    assert "must not carry a mask" in pkg.lib.b200_last_error().decode()
 
 
 @pytest.mark.parametrize("t", [F32, F16, Q8_0, Q4_0])

@@ -238,6 +238,66 @@ def test_dense_alibi(pkg, oracle, cuda):
     assert oracle.max_rel_err(want, got) <= 2e-3
 
 
+@pytest.mark.parametrize("t", TYPES)
+def test_dense_mask_on_the_tensor_core_kernel_equals_paged(pkg, oracle, cuda, t):
+    """An unmodified ggml graph (flat cache + the dense F16 mask libllama fills) runs on the stream-K kernel through
+    per-row tile lists scanned from the mask: same cache bytes, same rows as the block-table form -> same result as
+    the oracle, and as the CUDA-core kernel; the launch count shows which kernels ran (scan + plan + main + combine)."""
+    import torch
+    w = make_workload(oracle, [1, 15, 16, 17, 100, 333, 2049, 700], 32, 8, 128, t, seed=31)
+    mask = w.dense_mask()                                   # [pad64(n_q), n_cells]: 0 on the row's own cells, -inf elsewhere
+    lay = pkg.KVLayout(t, w.n_head_kv, w.d, w.block_size, w.n_blocks)
+    q, kc, vc, m = _dev(torch, w.q), _dev(torch, w.k_cache.reshape(-1)), _dev(torch, w.v_cache.reshape(-1)), _dev(torch, mask)
+    want = oracle_attention(oracle, w)
+    outs = {}
+    for kernel, n_launch in ((pkg.KERNEL_AUTO, 4), (pkg.KERNEL_STREAMK, 4), (pkg.KERNEL_GENERIC, None)):
+        out = torch.full_like(q, float("nan"))
+        call = pkg.AttnCall(q, kc, vc, lay, out, w.scale, mask=m, n_kv=w.n_cells, kernel=kernel)
+        assert call.supported()
+        before = pkg.lib.b200_launch_count()
+        call.run()
+        torch.cuda.synchronize()
+        if n_launch is not None:
+            assert pkg.lib.b200_launch_count() - before == n_launch, "the dense-mask call did not run on the stream-K kernels"
+        outs[kernel] = out.cpu().numpy()
+        assert oracle.max_rel_err(want, outs[kernel]) <= TOL[t], f"kernel {kernel}"
+    assert np.array_equal(outs[pkg.KERNEL_AUTO], outs[pkg.KERNEL_STREAMK])
+
+
+def test_dense_mask_edge_rows(pkg, oracle, cuda):
+    """a row whose mask hides every cell gives NaN like the reference (1/0 * 0, ggml-cpu.c:12418); no mask at all: every
+    row sees every cell; cells hidden inside a visible tile and biases (finite mask values) are honoured"""
+    import torch
+    rng = np.random.default_rng(33)
+    n_q, n_head, n_head_kv, d, n_kv = 6, 32, 8, 128, 1024
+    q = rng.uniform(-1, 1, (n_q, n_head, d)).astype(np.float32)
+    k = oracle.from_float(Q8_0, rng.uniform(-1, 1, (n_kv * n_head_kv, d)).astype(np.float32)).reshape(-1)
+    v = oracle.from_float(Q8_0, rng.uniform(-1, 1, (n_kv * n_head_kv, d)).astype(np.float32)).reshape(-1)
+    lay = pkg.KVLayout(Q8_0, n_head_kv, d, 16, n_kv // 16)
+    mask = np.full((64, n_kv), -np.inf, dtype=np.float16)
+    mask[0, 5:6] = 0.0                                       # one cell
+    mask[1, ::3] = 0.0                                       # every tile mixed
+    mask[2, 100:900] = rng.uniform(-2, 0, 800).astype(np.float16)   # biases
+    mask[3, :] = 0.0                                         # everything, all tiles clean
+    mask[4, 16:32] = 0.0; mask[4, 512:1024] = 0.0            # clean tiles only, with a gap
+    # row 5 stays hidden entirely
+    got = pkg.dense_attention(_dev(torch, q), _dev(torch, k), _dev(torch, v), lay, n_kv, _dev(torch, mask), 0.0884,
+                              kernel=pkg.KERNEL_STREAMK).cpu().numpy()
+    want = oracle.attention(q, k, v, Q8_0, Q8_0, n_head_kv, 0.0884, mask=mask, n_kv=n_kv)
+    assert np.isnan(got[5]).all() and np.isfinite(got[:5]).all()
+    assert oracle.max_rel_err(want[:5], got[:5]) <= 1e-2
+    # no mask: mixed K/V types are allowed too
+    vf = oracle.from_float(F16, rng.uniform(-1, 1, (n_kv * n_head_kv, d)).astype(np.float32)).reshape(-1)
+    out = torch.empty((n_q, n_head, d), dtype=torch.float32, device="cuda")
+    call = pkg.AttnCall(_dev(torch, q), _dev(torch, k), _dev(torch, vf), lay, out, 0.0884, layout_v=pkg.KVLayout(F16, n_head_kv, d, 16, n_kv // 16),
+                        n_kv=n_kv, kernel=pkg.KERNEL_STREAMK)
+    assert call.supported()
+    call.run()
+    torch.cuda.synchronize()
+    want = oracle.attention(q, k, vf, Q8_0, F16, n_head_kv, 0.0884, n_kv=n_kv)
+    assert oracle.max_rel_err(want, out.cpu().numpy()) <= 1e-2
+
+
 # ---------------------------------------------------------------- end to end: write -> fork/CoW -> attend
 
 @pytest.mark.parametrize("t", TYPES)
