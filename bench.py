@@ -165,11 +165,11 @@ def cpu_layer_op(workload, t, steps, warmup):
     kv_bytes = w.kv_bytes()
     if ref is not None:
         mask = w.dense_mask()
-        n_iter = max(1, warmup + steps)
+        n_iter = max(3, 1 + steps)                           # one warm-up run + the timed ones (the harness discards the first)
         _, us = ref.attention(0, w.q, w.k_cache, w.v_cache, t, t, n_head_kv, w.n_cells, mask, w.scale, n_iter=n_iter)
         kind, cores = "reference", ref.n_threads
         sample = (f"{what}: ggml CPU GGML_OP_FLASH_ATTN_EXT, flat cache of {w.n_cells} cells + dense F16 mask, "
-                  f"{cores} threads, isa {ref.isa}, best of {n_iter}")
+                  f"{cores} threads, isa {ref.isa}, median of {n_iter - 1} runs after 1 warm-up run")
     else:
         t0 = time.perf_counter()
         rows = np.argsort(lens)[:4]
@@ -198,7 +198,9 @@ def reference_arm(args, rank, world):
     t = TYPES[args.kv_type]
     sample, value, cores, kind, ms = cpu_layer_op(args.workload, t, args.steps, args.warmup)
     line = {"impl": "reference", "metric": "paged-attn decode KV-read GB/s", "value": value, "unit": "GB/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "ms_per_layer_op": ms,
+            "step": "ONE layer-op of the workload (the b200 arm's step is the attention op of all its layers); both values are GB/s over the same algorithmic bytes",
+            "higher_is_better": True,
             "scaling": WORKLOADS[args.workload]["scaling"], "vs_baseline": None, "dtype": args.kv_type, "data": "synthetic",
             "config": workload_config(args.workload, args.kv_type, world),
             "cpu_baseline": {"value": value, "unit": "GB/s", "cores": cores, "kind": kind, "sample": sample},
@@ -222,19 +224,20 @@ def main():
                     help="config4 at N>1: output exchange through the library's own NVLink peer-memory kernels (default) or NCCL all-gather")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the end-to-end leg")
+    ap.add_argument("--no-head-sharded", action="store_true", help="default workload only: skip the config-4 KV-head-sharded sub-record")
     args = ap.parse_args()
     W = WORKLOADS[args.workload]
     args.kv_type = args.kv_type or W["kv_type"]
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
     if args.impl == "reference":
-        args.steps = args.steps or 3
+        args.steps = args.steps or 5
         return reference_arm(args, rank, world)
     if args.workload == "config3":
         return run_config3(args, rank, world, local)
-    args.steps = args.steps or W["steps"]
     args.warmup = max(args.warmup, 3)
 
+    import copy
     import torch
     import torch.distributed as dist
     from __graft_entry__ import load
@@ -243,6 +246,39 @@ def main():
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    a = copy.copy(args)
+    a.steps = args.steps or W["steps"]
+    line = run_decode(a, rank, world, local, pkg)
+    # The driver's scaling run launches the DEFAULT workload at N = 1, 2, 4, 8: config 2, sequence-sharded, no collective.
+    # The path's other partitioning (BASELINE config 4: 70B heads, 32 x 32k, KV heads sharded over the
+    # ranks + one exchange of the outputs per layer) rides along as a sub-record of the same JSON line, so that record
+    # carries its strong-scaling curve too (N = 1: the whole problem on one GPU, the curve's baseline).
+    if args.workload == "config2" and not args.no_head_sharded and not args.layers and args.kv_type == W["kv_type"] and not args.no_e2e:
+        del a
+        import gc
+        gc.collect(); torch.cuda.empty_cache()
+        b = copy.copy(args)
+        b.workload, b.kv_type, b.layers, b.kernel, b.plan_per_layer = "config4", "f16", 0, 0, False
+        b.steps = 30
+        b.no_cpu_baseline = True
+        sub = run_decode(b, rank, world, local, pkg)
+        if rank == 0:
+            keep = ("value", "unit", "ms_per_step", "scaling", "dtype", "decode_tok_s", "gpu_launches", "roofline", "clocks", "e2e",
+                    "exchange", "steps", "warmup")
+            line["kv_head_sharded"] = {"workload": sub["config"]["workload"], "parallelism": sub["config"]["parallelism"],
+                                       "n_layer": sub["config"]["n_layer"], **{k: sub[k] for k in keep if k in sub}}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def run_decode(args, rank, world, local, pkg):
+    """one decode workload (args.workload) on this process group; returns the JSON line on rank 0"""
+    import torch
+    import torch.distributed as dist
+    W = WORKLOADS[args.workload]
     t = TYPES[args.kv_type]
     n_layer = args.layers or W["n_layer"]
     n_seqs = W["n_seqs"]
@@ -357,6 +393,23 @@ def main():
     ms_total = timed(run_step, args.steps, args.warmup)
     ms_step = ms_total / args.steps
     bytes_step_rank = kv_bytes_op * n_layer
+    exchange_us = None
+    if collective:
+        # what the exchange adds per layer: the same step without it (this rank's attention only), same replay form
+        def attn_only():
+            for c in calls:
+                c.run()
+        g2 = None
+        if graph is not None:
+            side = torch.cuda.Stream(); side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                attn_only()
+            torch.cuda.current_stream().wait_stream(side)
+            g2 = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g2):
+                attn_only()
+        ms_attn = timed(g2.replay if g2 is not None else attn_only, args.steps, args.warmup) / args.steps
+        exchange_us = round((ms_step - ms_attn) * 1e3 / n_layer, 2)
     # whole-job bytes = sum over ranks (weak: every rank holds its own sequences; strong: its own kv heads)
     tot = torch.tensor([float(bytes_step_rank), float(n_seqs)], device="cuda", dtype=torch.float64)
     if world > 1:
@@ -387,7 +440,10 @@ def main():
         # group sizes ramp up and down (1,1,2,4,8,...,8,4,2,1,1): only the first group's H2D and the last group's D2H
         # are exposed, everything else overlaps with compute
         if collective:
-            sizes = [1]*n_layer
+            # the step's inputs are small here (Q and one new K/V row per sequence: ~1 MB): the compute of each half of the
+            # layers (kv_write + attention + exchange per layer) is ONE captured graph, the first half's outputs go D2H
+            # while the second half computes
+            sizes = [n_layer - n_layer // 2, n_layer // 2] if n_layer >= 2 and peer is not None else [1]*n_layer
         else:
             ramp, sizes, left = [1, 1, 2, 4], [], n_layer
             big = bytes_step_rank > 2e9                      # small steps are host-call bound: keep few groups
@@ -403,6 +459,27 @@ def main():
         if not collective:
             group_calls = [pkg.StepCall(calls[a0:a1], [pkg.kv_write_desc(knew_d[l], vnew_d[l], slot_new_d, kcs[l], vcs[l], lay)
                                                         for l in range(a0, a1)]) for a0, a1 in groups]
+        group_graphs = None
+        if collective and peer is not None and not args.no_graph and len(groups) == 2:
+            def group_body(a0, a1):
+                for l in range(a0, a1):
+                    pkg.kv_write(knew_d[l], vnew_d[l], slot_new_d, kcs[l], vcs[l], lay)
+                    layer_op(l, keep=True)
+            group_graphs = []
+            for a0, a1 in groups:
+                e_before = peer.epoch
+                side = torch.cuda.Stream(); side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):
+                    group_body(a0, a1)                      # warm-up outside capture (really runs: the epoch advances)
+                torch.cuda.current_stream().wait_stream(side)
+                torch.cuda.synchronize()
+                if world > 1:
+                    dist.barrier()
+                gg = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gg):
+                    group_body(a0, a1)
+                peer.epoch = e_before + (a1 - a0)           # capture launched nothing
+                group_graphs.append(gg)
 
         def step_e2e():
             cur = torch.cuda.current_stream()
@@ -418,6 +495,8 @@ def main():
                 cur.wait_event(ev_in[gi])
                 if group_calls is not None:
                     group_calls[gi].run()
+                elif group_graphs is not None:
+                    group_graphs[gi].replay(); peer.note_replay(a1 - a0)
                 else:
                     for l in range(a0, a1):
                         pkg.kv_write(knew_d[l], vnew_d[l], slot_new_d, kcs[l], vcs[l], lay)
@@ -428,12 +507,30 @@ def main():
                     out_h[a0:a1].copy_(res_d[a0:a1], non_blocking=True)
             s_out.synchronize()                              # the host holds the step's result
 
+        def step_copies():                                   # the step's host<->device traffic alone, same streams and sizes
+            cur = torch.cuda.current_stream()
+            s_in.wait_stream(cur)
+            with torch.cuda.stream(s_in):
+                bt_d.copy_(bt_hp, non_blocking=True); sl_d.copy_(sl_hp, non_blocking=True)
+                slot_new_d.copy_(slot_new_h, non_blocking=True)
+                q_d.copy_(q_h, non_blocking=True); knew_d.copy_(knew_h, non_blocking=True); vnew_d.copy_(vnew_h, non_blocking=True)
+            s_out.wait_stream(cur)
+            with torch.cuda.stream(s_out):
+                out_h.copy_(res_d, non_blocking=True)
+            s_in.synchronize(); s_out.synchronize()
+
         e2e_steps = max(3, args.steps // 2)
         ms_e2e = timed(step_e2e, e2e_steps, 3) / e2e_steps
+        ms_copies = timed(step_copies, e2e_steps, 3) / e2e_steps
         e2e = {"value": round(tot[0].item() / (ms_e2e * 1e-3) / 1e9, 2), "unit": "GB/s", "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(d2h), "ms_per_step": round(ms_e2e, 4)}
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": round(ms_e2e, 4),
+               # where an e2e step's time can go besides the kernels: both directions of the step's copies run alone (max over
+               # ranks; H2D and D2H concurrently, as in the step) and the GB/s that is per rank
+               "copies_only_ms_per_step": round(ms_copies, 4),
+               "copies_only_gbs_per_rank": round((h2d + d2h) / (ms_copies * 1e-3) / 1e9, 1)}
     clocks = sampler.summary()
 
+    line = None
     if rank == 0:
         peak, peak_src = peaks()
         achieved = kv_bytes_op / (ms_step / n_layer * 1e-3) / 1e9         # per GPU, per layer-op
@@ -460,15 +557,20 @@ def main():
                          "algorithmic_bytes_per_launch": kv_bytes_op},
             "clocks": clocks,
         }
+        if collective:
+            line["exchange"] = {"us_per_layer": exchange_us, "form": cfg["exchange"], "equals_nccl": peer is not None,
+                                "what": "step time with the exchange minus the same ranks' attention-only step, per layer"}
         if e2e is not None:
             line["e2e"] = e2e
         if not args.no_cpu_baseline:
-            sample, v, cores, kind, _ = cpu_layer_op(args.workload, t, 3, 1)
+            sample, v, cores, kind, _ = cpu_layer_op(args.workload, t, 4, 1)
             line["cpu_baseline"] = {"value": round(v, 3), "unit": "GB/s", "cores": cores, "kind": kind, "sample": sample}
-        print(json.dumps(line))
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    if peer is not None:
+        peer.check()
+        if world > 1:
+            dist.barrier()
+        peer.close()
+    return line if rank == 0 else None
 
 
 def run_config3(args, rank, world, local):

@@ -21,6 +21,12 @@
  *   dst->src[6] I32 [n_q]                q_seq   (optional)
  *   dst->src[7] I32 [n_q]                q_pos   (optional)
  *   dst->op_params[4] = block_size (int32), op_params[5..6] = max_seq_len (int64, 0 = unknown)
+ *   a paged node carries no mask (rejected: the block table only says "causal prefix of the row's own sequence"); its
+ *   src[3] may instead hold the fused KV store of the step, which replaces build_attn's two ggml_cpy nodes
+ *   (src/llama-graph.cpp:1375-1397) and runs before the attention reads the cache:
+ *   dst->src[3] I32 [n_tokens]           slot mapping: destination cell of each new row (out of range: skipped)
+ *   dst->src[8] F32 [n_head_kv*d, n_tokens]  this step's K rows (k_cur), contiguous   } either may be absent
+ *   dst->src[9] F32 [n_head_kv*d, n_tokens]  this step's V rows (v_cur), contiguous   }
  */
 #ifndef B200_GGML_ABI_H
 #define B200_GGML_ABI_H

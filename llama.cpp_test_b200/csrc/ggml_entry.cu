@@ -29,7 +29,8 @@ static bool is_contiguous(const b200_ggml_tensor *t) {
     return true;
 }
 
-static bool node_to_desc(const b200_ggml_tensor *dst, b200_attn_desc &d) {
+static bool node_to_desc(const b200_ggml_tensor *dst, b200_attn_desc &d, b200_kv_write_desc *store = nullptr) {
+    if (store) memset(store, 0, sizeof(*store));
     if (!dst || dst->op != B200_GGML_OP_FLASH_ATTN_EXT) { set_error("flash_attn_ext: not a FLASH_ATTN_EXT node"); return false; }
     const b200_ggml_tensor *Q = dst->src[0], *K = dst->src[1], *V = dst->src[2], *M = dst->src[3];
     if (!Q || !K || !V) { set_error("flash_attn_ext: missing q/k/v source"); return false; }
@@ -57,8 +58,33 @@ static bool node_to_desc(const b200_ggml_tensor *dst, b200_attn_desc &d) {
         if (BT->type != B200_GGML_TYPE_I32 || !SL || SL->type != B200_GGML_TYPE_I32) { set_error("flash_attn_ext: block_table/seq_lens must be I32"); return false; }
         if ((QS && QS->type != B200_GGML_TYPE_I32) || (QP && QP->type != B200_GGML_TYPE_I32)) { set_error("flash_attn_ext: q_seq/q_pos must be I32"); return false; }
         // a block table says "row t sees positions [0, min(seq_len, q_pos + 1)) of its sequence" and nothing else: a node that also
-        // carries a mask (non-causal, sliding window, ALiBi) would silently lose it
-        if (M) { set_error("flash_attn_ext: a paged node (src[4] block table) must not carry a mask (src[3])"); return false; }
+        // carries a mask (non-causal, sliding window, ALiBi) would silently lose it.  In a paged node src[3] is instead the
+        // I32 slot mapping of the fused KV store: src[8] / src[9] = this step's new K / V rows (F32 [n_head_kv*d, n_tokens],
+        // contiguous), written to cell slot_mapping[i] of the caches src[1] / src[2] view BEFORE the attention reads them —
+        // build_attn's two ggml_cpy nodes (src/llama-graph.cpp:1375-1397) and the op in one node, as b200_decode_step does
+        if (M && M->type != B200_GGML_TYPE_I32) { set_error("flash_attn_ext: a paged node (src[4] block table) must not carry a mask (src[3])"); return false; }
+        const b200_ggml_tensor *KN = dst->src[8], *VN = dst->src[9];
+        if ((KN || VN) && !M) { set_error("flash_attn_ext: new K/V rows (src[8], src[9]) need the I32 slot mapping in src[3]"); return false; }
+        if (M) {
+            if (!KN && !VN) { set_error("flash_attn_ext: a slot mapping (src[3]) without new K/V rows (src[8], src[9])"); return false; }
+            const int64_t n_tok = M->ne[0], row = (int64_t) d.n_head_kv*d.head_dim;
+            for (const b200_ggml_tensor *X : {KN, VN}) {
+                if (X && (X->type != B200_TYPE_F32 || !is_contiguous(X) || nelements(X) != n_tok*row)) {
+                    set_error("flash_attn_ext: new K/V rows must be contiguous F32 with n_tokens x n_head_kv x head_dim elements"); return false;
+                }
+            }
+            if (store) {
+                store->k_src = KN ? static_cast<const float *>(KN->data) : nullptr;
+                store->v_src = VN ? static_cast<const float *>(VN->data) : nullptr;
+                store->src_nb1 = row*4;
+                store->n_tokens = n_tok;
+                store->slot_mapping = static_cast<const int32_t *>(M->data);
+                store->k_cache = const_cast<void *>(d.k); store->v_cache = const_cast<void *>(d.v);
+                store->type_k = d.type_k; store->type_v = d.type_v; store->n_head_kv = d.n_head_kv; store->head_dim = d.head_dim;
+                store->nbk_token = d.nbk1; store->nbk_head = d.nbk2; store->nbv_token = d.nbv1; store->nbv_head = d.nbv2;
+                store->n_cells = d.n_kv;
+            }
+        }
         d.block_table = static_cast<const int32_t *>(BT->data);
         d.bt_stride   = (int64_t) (BT->nb[1]/4);
         d.n_seqs      = (int32_t) BT->ne[1];
@@ -94,8 +120,14 @@ B200_API size_t b200_flash_attn_ext_workspace(const struct b200_ggml_tensor *dst
 
 B200_API int b200_flash_attn_ext(const struct b200_ggml_tensor *dst, void *workspace, size_t workspace_bytes, void *stream) {
     b200_attn_desc d;
-    if (!node_to_desc(dst, d)) return B200_ERR_INVALID;
+    b200_kv_write_desc store;
+    if (!node_to_desc(dst, d, &store)) return B200_ERR_INVALID;
     d.workspace = workspace; d.workspace_bytes = workspace_bytes;
+    if (store.slot_mapping) {                                     // the fused KV store of a paged node, first
+        if (!b200_supports_attention(&d)) { set_error("flash_attn_ext: unsupported shape/type"); return B200_ERR_UNSUPPORTED; }   // nothing is written for a node that cannot run
+        const int rc = b200_kv_write(&store, stream);
+        if (rc != B200_OK) return rc;
+    }
     return b200_paged_attention(&d, stream);
 }
 

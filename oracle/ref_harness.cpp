@@ -9,6 +9,7 @@
 #include "ggml.h"
 #include "ggml-cpu.h"
 
+#include <algorithm>
 #include <chrono>
 #include <thread>
 #include <cmath>
@@ -37,20 +38,25 @@ ggml_tensor * wrap(ggml_context * ctx, ggml_type type, int64_t ne0, int64_t ne1,
     return t;
 }
 
+// n_iter >= 3: one warm-up run, then the MEDIAN of the other n_iter - 1 (SURVEY.md 8d "CPU baseline timing": median of
+// >= 5 runs after 1 warm-up); fewer: the best of them
 double run_graph(ggml_cgraph * gf, int n_threads, int n_iter) {
     ggml_cplan plan = ggml_graph_plan(gf, n_threads, nullptr);
     std::vector<uint8_t> work(plan.work_size + 64);
     plan.work_data = work.data();
-    double best = 1e300, total = 0;
+    std::vector<double> us_all;
     for (int it = 0; it < (n_iter < 1 ? 1 : n_iter); ++it) {
         auto t0 = std::chrono::steady_clock::now();
         ggml_graph_compute(gf, &plan);
         auto t1 = std::chrono::steady_clock::now();
-        const double us = std::chrono::duration<double, std::micro>(t1 - t0).count();
-        total += us; if (us < best) best = us;
+        us_all.push_back(std::chrono::duration<double, std::micro>(t1 - t0).count());
     }
-    (void) total;
-    return best;
+    if (us_all.size() >= 3) {
+        us_all.erase(us_all.begin());
+        std::sort(us_all.begin(), us_all.end());
+        return us_all[us_all.size()/2];
+    }
+    return *std::min_element(us_all.begin(), us_all.end());
 }
 
 } // namespace
@@ -131,7 +137,8 @@ int ref_cpy_f32(int type, const float * src, int64_t row_elems, int64_t n_rows, 
 //   dst  F32  [n_q][n_head][d]
 // mode 0: GGML_OP_FLASH_ATTN_EXT, prec F32           (src/llama-graph.cpp:1187-1199)
 // mode 1: "F32 CPU result": K/V -> F32 by to_float, mul_mat -> soft_max_ext -> mul_mat (:1201-1239)
-// returns best-of-n_iter wall time in us through *us (graph compute only)
+// returns through *us the wall time of one graph compute in us: the median of n_iter - 1 runs after one warm-up run
+// when n_iter >= 3, else the best of n_iter
 int ref_attention(int mode, int n_q, int n_head, int n_head_kv, int d, int64_t n_kv,
                   int type_k, int type_v,
                   const float * q, const void * k, const void * v, const uint16_t * mask,

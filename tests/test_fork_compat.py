@@ -66,6 +66,22 @@ def test_reference_test_program_output_matches_reference_binary(name, tmp_path):
         assert run.stderr.splitlines() == gold_err
 
 
+def test_apply_attention_matches_the_reference_binary(tmp_path):
+    """F6 (blockKVAttentionRealFwd / applyAttention): the reference ships ./test_apply_attention without its source; its
+    main() is restated in tests/cpp/apply_attention_main.cpp from the binary's output, linked with fork_compat.cpp, and
+    stdout must equal what the reference binary printed (tests/golden/fork/test_apply_attention.stdout) — both the
+    usePaged = true branch (chunked dummy attention) and the 4-key scalar softmax."""
+    exe = str(tmp_path / "apply_attention")
+    cmd = ["g++", "-std=c++17", "-O1", "-w", "-I", os.path.join(HOST, "src"), os.path.join(ROOT, "tests", "cpp", "apply_attention_main.cpp"),
+           os.path.join(HOST, "fork_compat.cpp"), "-o", exe]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
+    run = subprocess.run([exe], capture_output=True, text=True, timeout=60)
+    assert run.returncode == 0
+    with open(os.path.join(GOLD, "test_apply_attention.stdout")) as f:
+        assert run.stdout == f.read()
+
+
 def test_block_manager_trace_3_blocks(pkg):
     """tests/test_block_manager.cpp:8-26: alloc 0,1,2; 4th alloc evicts the LOWEST allocated index (0) and
     re-allocates it; free(1); alloc -> 1; all allocated at the end"""

@@ -349,7 +349,7 @@ def test_write_fork_cow_attend(pkg, oracle, cuda, t):
 
 # ---------------------------------------------------------------- full-size properties (no oracle needed)
 
-@pytest.mark.parametrize("t", [Q8_0, Q4_0])
+@pytest.mark.parametrize("t", [F16, Q8_0, Q4_0])
 def test_full_size_properties_config2(pkg, oracle, cuda, t):
     """BASELINE config 2 at full size (64 seqs x U{512..8192}): (a) output is invariant under a re-permutation
     of physical blocks, (b) the two kernels agree, (c) sampled rows meet the oracle tolerance,
@@ -407,6 +407,74 @@ def test_full_size_properties_config2(pkg, oracle, cuda, t):
     torch.cuda.synchronize()
     c = oracle.to_float(t, oracle.from_float(t, np.full((1, d), 0.5, dtype=np.float32)), d)[0, 0]
     assert np.abs(out.cpu().numpy() - c).max() <= 2e-3 * abs(c)
+
+
+def test_full_size_properties_config4(pkg, oracle, cuda):
+    """BASELINE config 4 at its real shape on one GPU: Llama-3-70B heads (64 q / 8 kv, d 128), 32 sequences x 32 768
+    tokens, F16 (2 x 2 GiB of cache per layer).  Every row splits into dozens of stream-K segments per kv head here, so
+    this is where the combine's numerics matter most: (a) bit-identical output under a re-permutation of the physical
+    blocks, (b) agreement with the FP32 CUDA-core kernel (unsplit rows), (c) sampled rows against the oracle,
+    (d) V == const gives that const."""
+    import torch
+    n_seq, ctx, n_head, n_head_kv, d, bs = 32, 32768, 64, 8, 128, 16
+    bps = ctx // bs
+    nb = n_seq * bps
+    lay = pkg.KVLayout(F16, n_head_kv, d, bs, nb)
+    kc, vc = lay.alloc(), lay.alloc()
+    lens = np.full(n_seq, ctx, dtype=np.int32)
+    sl = _dev(torch, lens)
+    gen = torch.Generator(device="cuda"); gen.manual_seed(44)
+    q = torch.rand((n_seq, n_head, d), generator=gen, device=cuda) * 2 - 1
+    scale = 1.0 / np.sqrt(d)
+
+    def fill(perm_seed, const_v=None):
+        ids = np.random.default_rng(perm_seed).permutation(nb).astype(np.int32).reshape(n_seq, bps)
+        g = torch.Generator(device="cuda")
+        pos = np.arange(ctx)
+        for s in range(n_seq):                                # one sequence at a time: 2 x 128 MiB of F32 rows
+            g.manual_seed(1000 + s)                           # the same rows whatever the permutation
+            ks = torch.rand((ctx, n_head_kv * d), generator=g, device=cuda) * 2 - 1
+            vs = torch.rand((ctx, n_head_kv * d), generator=g, device=cuda) * 2 - 1
+            if const_v is not None:
+                vs.fill_(const_v)
+            slot = ids[s, pos // bs].astype(np.int64) * bs + pos % bs
+            pkg.kv_write(ks, vs, _dev(torch, slot.astype(np.int32)), kc, vc, lay)
+        return ids
+
+    outs = {}
+    for seed in (1, 2):
+        bt = fill(seed)
+        for kernel in ((pkg.KERNEL_STREAMK, pkg.KERNEL_GENERIC) if seed == 2 else (pkg.KERNEL_STREAMK,)):
+            out = torch.full_like(q, float("nan"))
+            call = pkg.AttnCall(q, kc, vc, lay, out, scale, block_table=_dev(torch, bt), seq_lens=sl, max_seq_len=ctx,
+                                total_tokens=n_seq * ctx, kernel=kernel)
+            assert call.supported()
+            call.run(); torch.cuda.synchronize()
+            outs[(seed, kernel)] = out.cpu().numpy()
+    a, b, gnr = outs[(1, pkg.KERNEL_STREAMK)], outs[(2, pkg.KERNEL_STREAMK)], outs[(2, pkg.KERNEL_GENERIC)]
+    assert np.isfinite(a).all() and np.array_equal(a, b), "stream-K output depends on the physical block placement"
+    assert oracle.max_rel_err(gnr, b) <= 2e-3, "split rows (stream-K + combine) disagree with unsplit rows (CUDA cores)"
+    # sampled rows against the oracle: that sequence's cells gathered into a compact cache with an identity table
+    for row in (0, 17):
+        cells = (torch.from_numpy(bt[row].astype(np.int64)).to(cuda)[:, None] * bs + torch.arange(bs, device=cuda)[None, :]).reshape(-1)
+        hk = kc.view(lay.n_cells, -1)[cells].cpu().numpy(); hv = vc.view(lay.n_cells, -1)[cells].cpu().numpy()
+        want = oracle.attention(q[row:row + 1].cpu().numpy(), hk, hv, F16, F16, n_head_kv, scale,
+                                block_table=np.arange(bps, dtype=np.int32)[None, :], seq_lens=np.array([ctx], dtype=np.int32), block_size=bs)
+        assert oracle.max_rel_err(want, b[row:row + 1]) <= TOL[F16]
+    fill(2, const_v=0.5)
+    out = pkg.paged_attention(q, kc, vc, lay, _dev(torch, bt), sl, scale, max_seq_len=ctx, total_tokens=n_seq * ctx)
+    torch.cuda.synchronize()
+    assert np.abs(out.cpu().numpy() - 0.5).max() <= 2e-3 * 0.5
+
+
+@pytest.mark.parametrize("t", [Q8_0, Q4_0])
+def test_one_32k_sequence_quantised_70b_heads(pkg, oracle, cuda, t):
+    """one sequence of 32 768 tokens at the 70B head shape with a quantised cache: a single row spread over the whole
+    machine (hundreds of segments merged by the combine kernel) against the oracle"""
+    import torch
+    w = make_workload(oracle, [32768], 64, 8, 128, t, seed=45)
+    got = _run_paged(pkg, torch, w, pkg.KERNEL_STREAMK)
+    assert oracle.max_rel_err(oracle_attention(oracle, w), got) <= TOL[t]
 
 
 # ---------------------------------------------------------------- stream-K with the tcgen05 main kernel (Q8_0 caches)
