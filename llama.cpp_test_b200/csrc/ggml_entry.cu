@@ -38,7 +38,7 @@ static bool node_to_desc(const b200_ggml_tensor *dst, b200_attn_desc &d, b200_kv
     if (Q->type != B200_TYPE_F32 || dst->type != B200_TYPE_F32) { set_error("flash_attn_ext: q and dst must be F32"); return false; }
     if (Q->ne[3] != 1 || K->ne[3] != 1 || V->ne[3] != 1) { set_error("flash_attn_ext: batch dim (ne3) must be 1"); return false; }
     if (Q->nb[0] != 4 || K->ne[0] != Q->ne[0] || V->ne[0] != Q->ne[0]) { set_error("flash_attn_ext: head size mismatch / q rows not contiguous"); return false; }
-    if (M && (M->type != B200_TYPE_F16 || M->ne[1] < Q->ne[1] || M->ne[0] != K->ne[1])) { set_error("flash_attn_ext: mask must be F16 [n_kv, >= n_q]"); return false; }
+    if (M && !dst->src[4] && (M->type != B200_TYPE_F16 || M->ne[1] < Q->ne[1] || M->ne[0] != K->ne[1])) { set_error("flash_attn_ext: mask must be F16 [n_kv, >= n_q]"); return false; }
     if (dst->ne[0] != Q->ne[0] || dst->ne[1] != Q->ne[2] || dst->ne[2] != Q->ne[1] || !is_contiguous(dst)) { set_error("flash_attn_ext: dst must be contiguous [d, n_head, n_q]"); return false; }
     memset(&d, 0, sizeof(d));
     d.head_dim = (int32_t) Q->ne[0]; d.n_q = (int32_t) Q->ne[1]; d.n_head = (int32_t) Q->ne[2];

@@ -83,7 +83,10 @@ static int pick_kernel(const b200_attn_desc &d) {
     if (d.kernel == B200_KERNEL_STREAMK || d.kernel == B200_KERNEL_STREAMK_DQ) return B200_KERNEL_STREAMK;
     if (d.kernel == B200_KERNEL_PREFILL) return B200_KERNEL_PREFILL;
     // many causal query rows per sequence: the tcgen05 tile kernel reads K/V once per 128/gqa rows instead of once per row
-    if (d.q_pos && d.n_q >= 128 && prefill_supports(d)) return B200_KERNEL_PREFILL;
+    // ... when a sequence brings enough rows to fill a tile: a ubatch interleaved position by position over many sequences
+    // (llama-batched-bench's prompt order: 512 rows = 2 positions x 256 sequences) has a few rows per sequence, which the
+    // per-row kernel serves better (measured through libllama, profiles/r2g_*: 464 vs 555 ms of attention per prompt)
+    if (d.q_pos && d.n_q >= 128 && (int64_t) d.n_q >= 8*(int64_t) d.n_seqs && prefill_supports(d)) return B200_KERNEL_PREFILL;
     return streamk_supports(d) ? B200_KERNEL_STREAMK : B200_KERNEL_GENERIC;
 }
 

@@ -12,13 +12,17 @@
 // Nothing of the reference is modified or copied; the same effect is the ~40-line patch of INTEGRATION.md.
 //
 // B200_GLUE=0 in the environment sends everything to the reference's kernels (A/B runs with one binary);
-// B200_GLUE_STATS=1 prints, at exit, how many nodes each side computed.
+// B200_GLUE_STATS=1 prints, at exit, how many nodes each side computed; B200_GLUE_TIMING=1 brackets every FLASH_ATTN_EXT
+// node (either side) with CUDA events and prints, at exit, the GPU time they took per ubatch size — the attention share
+// of a llama-batched-bench run (SURVEY 8d config 5 asks for it "from cb_eval / nsys"; neither is needed this way).
 #include "common.cuh"                  // the reference's ggml/src/ggml-cuda/common.cuh
 #include "b200_ggml_abi.h"
 
 #include <atomic>
 #include <cstdio>
 #include <cstdlib>
+#include <map>
+#include <vector>
 
 // the reference's own entry points (ggml/src/ggml-cuda/fattn.cu:244, cpy.cu:510, :586, :591)
 void   ggml_cuda_flash_attn_ext(ggml_backend_cuda_context & ctx, ggml_tensor * dst);
@@ -31,6 +35,27 @@ static_assert(sizeof(ggml_tensor) == sizeof(b200_ggml_tensor), "b200_ggml_tensor
 namespace {
 
 std::atomic<long long> n_fa_b200{0}, n_fa_ref{0}, n_cpy_b200{0}, n_cpy_ref{0};
+
+struct fa_span { cudaEvent_t e0, e1; int64_t n_tokens; };
+std::vector<fa_span> g_spans;
+
+bool timing_on() {
+    static const bool on = [] {
+        const char * e = getenv("B200_GLUE_TIMING");
+        const bool v = e && e[0] == '1';
+        if (v) {
+            atexit([] {
+                cudaDeviceSynchronize();
+                std::map<int64_t, std::pair<long long, double>> by;
+                for (auto & sp : g_spans) { float ms = 0; if (cudaEventElapsedTime(&ms, sp.e0, sp.e1) == cudaSuccess) { by[sp.n_tokens].first++; by[sp.n_tokens].second += ms; } }
+                for (auto & kv : by) fprintf(stderr, "b200 glue timing: FLASH_ATTN_EXT nodes with %lld query rows: %lld nodes, %.3f ms of GPU time\n",
+                                             (long long) kv.first, kv.second.first, kv.second.second);
+            });
+        }
+        return v;
+    }();
+    return on;
+}
 
 bool glue_on() {
     static const bool on = [] {
@@ -61,8 +86,23 @@ bool b200_takes_cpy(const ggml_tensor * src0, const ggml_tensor * src1) {
 
 } // namespace
 
+static void fa_dispatch(ggml_backend_cuda_context & ctx, ggml_tensor * dst);
+
 void b200_glue_flash_attn_ext(ggml_backend_cuda_context & ctx, ggml_tensor * dst) {
+    if (!timing_on()) return fa_dispatch(ctx, dst);
+    fa_span sp; sp.n_tokens = dst->src[0]->ne[1];
+    cudaEventCreate(&sp.e0); cudaEventCreate(&sp.e1);
+    cudaEventRecord(sp.e0, ctx.stream());
+    fa_dispatch(ctx, dst);
+    cudaEventRecord(sp.e1, ctx.stream());
+    g_spans.push_back(sp);
+}
+
+static void fa_dispatch(ggml_backend_cuda_context & ctx, ggml_tensor * dst) {
     const b200_ggml_tensor * node = reinterpret_cast<const b200_ggml_tensor *>(dst);
+    if (dst->src[4] != nullptr && !(glue_on() && b200_supports_op(node))) {
+        GGML_ABORT("a paged FLASH_ATTN_EXT node (src[4] block table) needs libb200attn: %s", glue_on() ? b200_last_error() : "B200_GLUE=0");
+    }
     if (glue_on() && b200_supports_op(node)) {
         const size_t ws = b200_flash_attn_ext_workspace(node);
         ggml_cuda_pool_alloc<char> scratch(ctx.pool(), ws > 0 ? ws : 1);       // the backend's pool, as launch_fattn does (fattn-common.cuh:708-711)

@@ -179,6 +179,55 @@ def test_flash_attn_ext_node_paged_extension(pkg, oracle, cuda):
     assert "must not carry a mask" in pkg.lib.b200_last_error().decode()
 
 
+@pytest.mark.parametrize("t", [F16, Q8_0, Q4_0])
+def test_flash_attn_ext_node_paged_with_fused_kv_store(pkg, oracle, cuda, t):
+    """the paged node as the libllama patch emits it (llama.cpp_test_b200/host/libllama_paged.patch): src[3] = I32 slot
+    mapping, src[8] / src[9] = this step's K / V rows; the store runs first, then the attention sees the new token.  The
+    cache starts WITHOUT the last token of every sequence; afterwards its bytes equal the oracle's full cache and the
+    output equals the oracle's attention over it."""
+    import torch
+    from workloads import make_workload, oracle_attention
+    w = make_workload(oracle, [130, 7, 64, 33], 32, 8, 128, t, seed=19)
+    want = oracle_attention(oracle, w)
+    dev = cuda
+    n_q, n_head, d = w.q.shape
+    rb = pkg.row_bytes(t, d)
+    last = np.cumsum(w.seq_lens.astype(np.int64)) - 1                     # row of each sequence's last token in k_f32 / slot_mapping
+    slots_last = w.slot_mapping[last].astype(np.int32)
+    k_cache, v_cache = w.k_cache.copy(), w.v_cache.copy()
+    k_cache[slots_last] = 0; v_cache[slots_last] = 0                      # the step's tokens are not in the cache yet
+    up = lambda a: torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).to(dev)
+    bq, bk, bv = up(w.q), up(k_cache), up(v_cache)
+    bbt, bsl, bslot = up(w.block_table.astype(np.int32)), up(w.seq_lens.astype(np.int32)), up(slots_last)
+    bkn, bvn = up(w.k_f32[last]), up(w.v_f32[last])
+    out = torch.full((n_q, n_head, d), float("nan"), dtype=torch.float32, device=dev)
+    nb0 = {F16: 2, Q8_0: 34, Q4_0: 18}[t]
+    q = _node(pkg, F32, (d, n_q, n_head, 1), (4, n_head * d * 4, d * 4), bq.data_ptr())
+    k = _node(pkg, t, (d, w.n_cells, 8, 1), (nb0, 8 * rb, rb), bk.data_ptr())
+    v = _node(pkg, t, (d, w.n_cells, 8, 1), (nb0, 8 * rb, rb), bv.data_ptr())
+    bt = _node(pkg, pkg.GGML_TYPE_I32, (w.block_table.shape[1], w.block_table.shape[0], 1, 1), (4, w.block_table.shape[1] * 4), bbt.data_ptr())
+    sl = _node(pkg, pkg.GGML_TYPE_I32, (len(w.seq_lens), 1, 1, 1), (4,), bsl.data_ptr())
+    sm = _node(pkg, pkg.GGML_TYPE_I32, (n_q, 1, 1, 1), (4,), bslot.data_ptr())
+    kn = _node(pkg, F32, (8 * d, n_q, 1, 1), (4, 8 * d * 4), bkn.data_ptr())
+    vn = _node(pkg, F32, (8 * d, n_q, 1, 1), (4, 8 * d * 4), bvn.data_ptr())
+    dst = _node(pkg, F32, (d, n_head, n_q, 1), (4, d * 4, n_head * d * 4), out.data_ptr(), op=pkg.GGML_OP_FLASH_ATTN_EXT)
+    for i, s_ in ((0, q), (1, k), (2, v), (3, sm), (4, bt), (5, sl), (8, kn), (9, vn)):
+        dst.src[i] = C.pointer(s_)
+    dst.op_params[0] = _f32bits(w.scale)
+    dst.op_params[4] = w.block_size
+    assert pkg.lib.b200_supports_op(C.byref(dst)) == 1, pkg.lib.b200_last_error().decode()
+    need = pkg.lib.b200_flash_attn_ext_workspace(C.byref(dst))
+    ws = torch.empty(max(need, 16), dtype=torch.uint8, device=dev)
+    assert pkg.lib.b200_flash_attn_ext(C.byref(dst), ws.data_ptr(), need, None) == 0, pkg.lib.b200_last_error().decode()
+    torch.cuda.synchronize()
+    assert np.array_equal(bk.cpu().numpy().reshape(w.k_cache.shape), w.k_cache), "the fused store did not write the oracle's K bytes"
+    assert np.array_equal(bv.cpu().numpy().reshape(w.v_cache.shape), w.v_cache)
+    assert oracle.max_rel_err(want, out.cpu().numpy()) <= TOL[t]
+    # a slot mapping without rows, or rows without a slot mapping, is malformed
+    dst.src[8] = dst.src[9] = None
+    assert pkg.lib.b200_supports_op(C.byref(dst)) == 0
+
+
 @pytest.mark.parametrize("t", [F32, F16, Q8_0, Q4_0])
 @pytest.mark.parametrize("ne", [(256, 4, 4, 4), (1024, 37, 1, 1), (128, 2, 3, 1)])
 def test_cpy_node_f32_to_cache_types(pkg, oracle, cuda, t, ne):
