@@ -45,8 +45,11 @@ B200_API int32_t b200_pc_prepare_batch(b200_paged_cache *pc, int64_t n_tokens, c
                                        int32_t *slot_mapping, int32_t *q_seq, int32_t *q_pos, int32_t *seqs, int64_t *n_seqs,
                                        int32_t *cow_pairs, int64_t cow_cap, int64_t *n_cow);
 /* llama_kv_slot_restorer::restore (src/llama-kv-cache.h:192-237): drop the tokens a successful b200_pc_prepare_batch placed
- * (seq[] as passed to it, q_pos[] as it returned) when the ubatch's graph failed (src/llama-context.cpp:1322-1343) */
-B200_API void    b200_pc_undo_batch(b200_paged_cache *pc, int64_t n_tokens, const int32_t *seq, const int32_t *q_pos);
+ * (seq[] as passed to it, q_pos[] and cow_pairs[n_cow][2] as it returned) when the ubatch's graph failed
+ * (src/llama-context.cpp:1322-1343).  A block a copy-on-write of that batch gave a sequence is swapped back for the shared
+ * original and released: the device copy may never have run.  cow_pairs may be NULL when n_cow is 0. */
+B200_API void    b200_pc_undo_batch(b200_paged_cache *pc, int64_t n_tokens, const int32_t *seq, const int32_t *q_pos,
+                                    const int32_t *cow_pairs, int64_t n_cow);
 B200_API int32_t b200_pc_seq_cp(b200_paged_cache *pc, int32_t src, int32_t dst, int64_t p0, int64_t p1);   /* 1 ok / 0 refused */
 B200_API int32_t b200_pc_seq_rm(b200_paged_cache *pc, int32_t seq, int64_t p0, int64_t p1);
 B200_API void    b200_pc_seq_keep(b200_paged_cache *pc, int32_t seq);
@@ -104,7 +107,10 @@ B200_API int64_t b200_kv_state_seq_write(uint8_t *out, int64_t cap, int64_t n_ce
                                          int32_t type_k, int64_t k_size_row, int32_t type_v, int64_t v_size_row,
                                          const uint8_t *k_rows, const uint8_t *v_rows);
 /* validates a stream against the cache's shape; returns 0 or a B200_STATE_ERR_*; k_off/v_off [n_layer] receive the
- * byte offsets of each layer's rows inside `data` (either may be NULL) */
+ * byte offsets of each layer's rows inside `data` (either may be NULL).  The stream's rows must hold exactly the positions
+ * 0..n-1, in any order (the reference writes cells in cell-index order): b200_kv_state_seq_positions gives the position of
+ * every stream row, and the restore scatters row i to the cell of position pos[i]. */
+B200_API int64_t b200_kv_state_seq_positions(const uint8_t *data, int64_t size, int32_t *pos_out, int64_t cap);   /* n_cells; -(n)-1: cap too small */
 B200_API int32_t b200_kv_state_seq_parse(const uint8_t *data, int64_t size, int32_t n_layer,
                                          int32_t type_k, int64_t k_size_row, int32_t type_v, int64_t v_size_row,
                                          int64_t *n_cells, int64_t *k_off, int64_t *v_off);
@@ -176,6 +182,20 @@ B200_API int32_t b200_kvc_update(b200_kv_cache *kv, int32_t *cow_pairs, int32_t 
 /* between the sizing call and the consuming call of b200_kvc_update: ends[g][3] = the cumulative {cow pairs, row moves,
  * shift cells} at the end of group g.  Returns the number of groups, or -(n_groups) - 1 when cap is too small. */
 B200_API int64_t b200_kvc_update_groups(const b200_kv_cache *kv, int64_t *ends, int64_t cap);
+
+/*
+ * Multi-GPU partitioning of the path (one process per GPU; no reference counterpart — its multi-GPU path splits matmul rows,
+ * ggml/src/ggml-cuda/ggml-cuda.cu:598,1592).  Deterministic integer policy, so every rank computes the same answer alone.
+ *   b200_shard_sequences   partition A (configs 1-3, 5): sequences -> ranks balanced by context length (longest first to
+ *                          the lightest rank); rank_of[i] = owner of sequence i.  No data-path collective afterwards.
+ *   b200_head_shard        partition B (config 4, 70B GQA): rank g holds kv heads [out[0], out[0] + out[1]) of every block
+ *                          and computes query heads [out[2], out[2] + out[3]); the block table is replicated; the one
+ *                          exchange of the outputs is b200_peer_exchange_ll (b200_paged_attn.h).  -2 / -3: heads do not divide.
+ * The peer buffers of that exchange are set up with b200_peer_alloc / _export (64-byte handle) / _open; carrying the handles
+ * between the processes is the host's own IPC (the Python driver uses one torch.distributed.all_gather_object).
+ */
+B200_API int32_t b200_shard_sequences(const int32_t *ctx_lens, int64_t n_seqs, int32_t world, int32_t *rank_of);
+B200_API int32_t b200_head_shard(int32_t rank, int32_t world, int32_t n_head, int32_t n_head_kv, int32_t out[4]);
 
 #ifdef __cplusplus
 }

@@ -110,10 +110,10 @@ EXPORTS = {
         "b200_fork_trace", "b200_pc_create", "b200_pc_destroy", "b200_pc_append", "b200_pc_prepare_batch", "b200_pc_undo_batch", "b200_pc_seq_cp", "b200_pc_seq_rm",
         "b200_pc_seq_keep", "b200_pc_clear", "b200_pc_seq_len", "b200_pc_n_free", "b200_pc_ref_count", "b200_pc_export",
         "b200_pc_slots_of", "b200_pc_defrag", "b200_pc_restore_seq", "b200_pc_context_shift", "b200_kv_state_seq_size", "b200_kv_state_seq_write",
-        "b200_kv_state_seq_parse", "b200_pc_used_cells", "b200_kv_state_all_write", "b200_kv_state_all_restore",
+        "b200_kv_state_seq_parse", "b200_kv_state_seq_positions", "b200_pc_used_cells", "b200_kv_state_all_write", "b200_kv_state_all_restore",
         "b200_kvc_create", "b200_kvc_destroy", "b200_kvc_clear", "b200_kvc_defrag", "b200_kvc_seq_rm", "b200_kvc_seq_cp", "b200_kvc_seq_keep",
         "b200_kvc_seq_add", "b200_kvc_seq_div", "b200_kvc_seq_pos_max", "b200_kvc_n_tokens", "b200_kvc_used_cells", "b200_kvc_unsupported",
-        "b200_kvc_slots_of", "b200_kvc_find_slot", "b200_kvc_update", "b200_kvc_update_groups"],
+        "b200_kvc_slots_of", "b200_kvc_find_slot", "b200_kvc_update", "b200_kvc_update_groups", "b200_shard_sequences", "b200_head_shard"],
 }
 
 lib.b200_paged_attention_workspace.restype = C.c_size_t
@@ -200,7 +200,7 @@ lib.b200_pc_prepare_batch.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int32
                                       C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int64),
                                       C.POINTER(C.c_int32), C.c_int64, C.POINTER(C.c_int64)]
 lib.b200_pc_undo_batch.restype = None
-lib.b200_pc_undo_batch.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+lib.b200_pc_undo_batch.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int64]
 lib.b200_pc_export.restype = C.c_int32
 lib.b200_pc_export.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_int64, C.POINTER(C.c_int32), C.c_int64, C.POINTER(C.c_int32)]
 lib.b200_pc_slots_of.restype = C.c_int64
@@ -220,6 +220,8 @@ lib.b200_kv_state_seq_write.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_in
 lib.b200_kv_state_seq_parse.restype = C.c_int32
 lib.b200_kv_state_seq_parse.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_int64,
                                         C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+lib.b200_kv_state_seq_positions.restype = C.c_int64
+lib.b200_kv_state_seq_positions.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int32), C.c_int64]
 lib.b200_pc_used_cells.restype = C.c_int64
 lib.b200_pc_used_cells.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_int64]
 lib.b200_kv_state_all_write.restype = C.c_int64
@@ -262,6 +264,10 @@ lib.b200_kvc_update.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_
                                 C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
 lib.b200_kvc_update_groups.restype = C.c_int64
 lib.b200_kvc_update_groups.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.c_int64]
+lib.b200_shard_sequences.restype = C.c_int32
+lib.b200_shard_sequences.argtypes = [C.POINTER(C.c_int32), C.c_int64, C.c_int32, C.POINTER(C.c_int32)]
+lib.b200_head_shard.restype = C.c_int32
+lib.b200_head_shard.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32)]
 STATE_ERRORS = {-1: "truncated stream", -2: "invalid seq_id-agnostic kv cell", -3: "positions are not 0..n-1",
                 -4: "mismatched layer count", -5: "incompatible V transposition", -6: "mismatched key/value type",
                 -7: "mismatched key/value row size", -8: "not enough cells in kv cache", -9: "invalid seq_id"}

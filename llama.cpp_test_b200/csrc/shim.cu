@@ -179,7 +179,12 @@ B200_API int b200_decode_step(const b200_kv_write_desc *writes, const b200_attn_
     for (int32_t l = 0; l < n_layers; ++l) {
         if (writes) { const int rc = b200_kv_write(&writes[l], stream); if (rc != B200_OK) return rc; }
         int rc;
-        if (l > 0 && !(attns[l].flags & B200_ATTN_REUSE_PLAN) && same_plan_inputs(attns[l - 1], attns[l])) {
+        // the schedule of layer l-1 stands only if layer l-1 really ran the stream-K plan kernel and layer l runs stream-K too:
+        // pick_kernel also looks at pointers and strides (alignment), which same_plan_inputs does not compare
+        if (l > 0 && !(attns[l].flags & B200_ATTN_REUSE_PLAN) && same_plan_inputs(attns[l - 1], attns[l])
+            && attns[l - 1].logit_softcap == attns[l].logit_softcap
+            && validate_attn(&attns[l - 1]) == B200_OK && pick_kernel(attns[l - 1]) == B200_KERNEL_STREAMK
+            && validate_attn(&attns[l]) == B200_OK && pick_kernel(attns[l]) == B200_KERNEL_STREAMK) {
             b200_attn_desc d = attns[l];                  // the schedule of layer l-1 stands: skip the plan launch
             d.flags |= B200_ATTN_REUSE_PLAN;
             rc = b200_paged_attention(&d, stream);

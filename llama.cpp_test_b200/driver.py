@@ -283,6 +283,13 @@ def state_seq_unpack(data: bytes, n_layer: int, type_k: int, k_row: int, type_v:
     n = n_cells.value
     k = np.stack([buf[k_off[l]:k_off[l] + n * k_row].reshape(n, k_row) for l in range(n_layer)]) if n_layer else np.zeros((0, n, k_row), np.uint8)
     v = np.stack([buf[v_off[l]:v_off[l] + n * v_row].reshape(n, v_row) for l in range(n_layer)]) if n_layer else np.zeros((0, n, v_row), np.uint8)
+    # the stream's rows come in the writer's cell order, which need not be position order: hand them out by position
+    pos = (C.c_int32 * max(n, 1))()
+    if lib.b200_kv_state_seq_positions(buf.ctypes.data, buf.size, pos, n) != n:
+        raise B200Error("failed to restore kv cache: truncated stream")
+    order = np.argsort(np.frombuffer(pos, dtype=np.int32, count=n), kind="stable")
+    if not np.array_equal(order, np.arange(n)):
+        k, v = k[:, order], v[:, order]
     return k, v
 
 
@@ -428,10 +435,12 @@ class PagedKVCache:
         return dict(slot_mapping=list(slots[:n]), q_seq=list(q_seq[:n]), q_pos=list(q_pos[:n]), seqs=list(seqs[:n_seqs.value]),
                     cow_pairs=[(cow[2 * i], cow[2 * i + 1]) for i in range(n_cow.value)])
 
-    def undo_batch(self, seq, q_pos) -> None:
-        """llama_kv_slot_restorer::restore for a batch prepare_batch placed (its seq list, the q_pos it returned)"""
+    def undo_batch(self, seq, q_pos, cow_pairs=()) -> None:
+        """llama_kv_slot_restorer::restore for a batch prepare_batch placed (its seq list, the q_pos and cow_pairs it returned)"""
         n = len(seq)
-        lib.b200_pc_undo_batch(self._h, n, (C.c_int32 * max(n, 1))(*seq), (C.c_int32 * max(n, 1))(*q_pos))
+        flat = [x for pr in cow_pairs for x in pr]
+        lib.b200_pc_undo_batch(self._h, n, (C.c_int32 * max(n, 1))(*seq), (C.c_int32 * max(n, 1))(*q_pos),
+                               (C.c_int32 * max(len(flat), 1))(*flat), len(flat) // 2)
 
     def seq_cp(self, src: int, dst: int, p0: int = 0, p1: int = -1) -> bool:
         return bool(lib.b200_pc_seq_cp(self._h, src, dst, p0, p1))

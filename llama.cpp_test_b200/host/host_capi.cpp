@@ -56,9 +56,11 @@ B200_API int32_t b200_pc_prepare_batch(b200_paged_cache *pc, int64_t n_tokens, c
     if (n_cow) *n_cow = (int64_t) in.cow_pairs.size();
     return 0;
 }
-B200_API void b200_pc_undo_batch(b200_paged_cache *pc, int64_t n_tokens, const int32_t *seq, const int32_t *q_pos) {
+B200_API void b200_pc_undo_batch(b200_paged_cache *pc, int64_t n_tokens, const int32_t *seq, const int32_t *q_pos,
+                                 const int32_t *cow_pairs, int64_t n_cow) {
     if (!pc || n_tokens <= 0 || !seq || !q_pos) return;
     PagedKVCache::BatchInputs in;
+    for (int64_t i = 0; cow_pairs && i < n_cow; ++i) in.cow_pairs.emplace_back(cow_pairs[2*i], cow_pairs[2*i + 1]);
     for (int64_t i = 0; i < n_tokens; ++i) {
         size_t r = 0;
         while (r < in.seqs.size() && in.seqs[r] != seq[i]) ++r;

@@ -71,16 +71,23 @@ B200_API int32_t b200_kv_state_seq_parse(const uint8_t *data, int64_t size, int3
     if (!data || size < 0 || n_layer < 0) return B200_STATE_ERR_TRUNCATED;
     reader r{data, size};
     const uint32_t n_cells = r.val<uint32_t>();
-    int32_t prev = -1;
+    // the paged cache stores position p of a sequence at table index p, so a restored sequence must hold exactly the
+    // positions 0..n-1 (the unified cache accepts any positions; a shifted or holed sequence is outside the block-table
+    // model) — in ANY stream order: state_write(seq_id) walks cells in cell-index order, which need not be position order
+    // (find_slot's head wraps, cells are reused after seq_rm, defrag moves them); b200_kv_state_seq_positions hands out the
+    // order so that the restore scatters stream row i to the cell of position pos[i]
+    std::vector<bool> seen;
     for (uint32_t i = 0; i < n_cells && r.ok; ++i) {
         const int32_t  pos      = r.val<int32_t>();
         const uint32_t n_seq_id = r.val<uint32_t>();
         if (!r.ok) break;
         if (n_seq_id != 0) return B200_STATE_ERR_SEQ_AGNOSTIC;           // "invalid seq_id-agnostic kv cell" :1024-1027
-        // the paged cache stores position p of a sequence at table index p: a restored sequence must be 0..n-1
-        // (the unified cache accepts any positions; a shifted or holed sequence is outside the block-table model)
-        if (pos != prev + 1) return B200_STATE_ERR_POSITIONS;
-        prev = pos;
+        if (seen.empty()) {
+            if ((int64_t) n_cells*8 > size) return B200_STATE_ERR_TRUNCATED;     // a corrupt count must not size the bitmap
+            seen.assign(n_cells, false);
+        }
+        if (pos < 0 || (uint32_t) pos >= n_cells || seen[(size_t) pos]) return B200_STATE_ERR_POSITIONS;
+        seen[(size_t) pos] = true;
     }
     const uint32_t v_trans = r.val<uint32_t>();
     const uint32_t nl      = r.val<uint32_t>();
@@ -107,6 +114,19 @@ B200_API int32_t b200_kv_state_seq_parse(const uint8_t *data, int64_t size, int3
     }
     if (n_cells_out) *n_cells_out = (int64_t) n_cells;
     return 0;
+}
+
+B200_API int64_t b200_kv_state_seq_positions(const uint8_t *data, int64_t size, int32_t *pos_out, int64_t cap) {
+    if (!data || size < 4) return -1;
+    reader r{data, size};
+    const uint32_t n_cells = r.val<uint32_t>();
+    if ((int64_t) n_cells*8 > size - 4) return -1;
+    if ((int64_t) n_cells > cap || (n_cells > 0 && !pos_out)) return -(int64_t) n_cells - 1;
+    for (uint32_t i = 0; i < n_cells; ++i) {
+        pos_out[i] = r.val<int32_t>();
+        (void) r.val<uint32_t>();
+    }
+    return r.ok ? (int64_t) n_cells : -1;
 }
 
 // ---- the whole-cache stream: state_write(io, -1) / state_read(io, -1), i.e. llama_state_get_data / llama_state_set_data

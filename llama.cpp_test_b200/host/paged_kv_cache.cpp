@@ -116,6 +116,20 @@ void PagedKVCache::undo_batch(const BatchInputs & in) {
         if (first[r] < 0) continue;
         if (first[r] == 0) seq_rm(in.seqs[r], -1, -1); else seq_rm(in.seqs[r], first[r], -1);
     }
+    // A copy-on-write gave a sequence its own block `dst` for the partly filled, shared block `src` it was about to append
+    // into.  Whether the device copy src -> dst ever ran is unknown here (the ubatch may have failed before it), so the table
+    // entry goes back to the shared block, whose rows are certainly valid, and dst is released.  src is still allocated: it
+    // was shared (ref > 1) when the pair was made and nothing but this batch has touched the cache since.
+    for (const auto & pr : in.cow_pairs) {
+        if (pr.first < 0 || pr.first >= (int32_t) ref_.size() || ref_[(size_t) pr.first] <= 0) continue;
+        for (seq_id id : in.seqs) {
+            auto it = seqs_.find(id);
+            if (it == seqs_.end()) continue;
+            for (int32_t & b : it->second.blocks) {
+                if (b == pr.second) { b = pr.first; ++ref_[(size_t) pr.first]; unref(pr.second); }
+            }
+        }
+    }
 }
 
 bool PagedKVCache::seq_cp(seq_id src, seq_id dst, int64_t p0, int64_t p1) {

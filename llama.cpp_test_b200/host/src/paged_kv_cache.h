@@ -51,8 +51,8 @@ public:
     int prepare_batch(int64_t n_tokens, const seq_id * seq, const int32_t * pos, BatchInputs & out);
     // llama_kv_slot_restorer::restore (src/llama-kv-cache.h:192-237; llama_context::decode calls it when the graph of a ubatch
     // fails, src/llama-context.cpp:1322-1343): the tokens a prepare_batch placed are dropped again — every sequence of the
-    // batch is cut back to the position of its first token in the batch.  Blocks that a copy-on-write gave the sequence stay
-    // its own (their content equals the shared block's; nothing has to be copied back).
+    // batch is cut back to the position of its first token in the batch, and a block that a copy-on-write of the batch gave a
+    // sequence is swapped back for the shared original (the copy may never have run) and released.
     void undo_batch(const BatchInputs & in);
 
     // llama_kv_self_seq_cp semantics restricted to prefixes (p0 <= 0): dst becomes positions [0, p1) of src,

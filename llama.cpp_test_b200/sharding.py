@@ -25,17 +25,21 @@ __all__ = ["shard_sequences", "HeadShard", "head_shard", "gather_head_outputs", 
 def shard_sequences(ctx_lens, world: int) -> list[list[int]]:
     """Partition A.  Longest-processing-time greedy: sequences sorted by context length (descending, index as
     tie-break) go to the currently lightest rank.  Deterministic, so every rank computes the same assignment
-    without communicating.  Returns, per rank, the ascending list of sequence indices it owns."""
+    without communicating.  Returns, per rank, the ascending list of sequence indices it owns.
+    The policy itself is the library's (b200_shard_sequences, host/sharding.cpp): a C host gets the same answer."""
+    import ctypes as C
+    from . import lib
     if world <= 0:
         raise ValueError("world must be positive")
-    order = sorted(range(len(ctx_lens)), key=lambda i: (-int(ctx_lens[i]), i))
-    load = [0] * world
+    n = len(ctx_lens)
+    lens = (C.c_int32 * max(n, 1))(*[int(x) for x in ctx_lens])
+    rank_of = (C.c_int32 * max(n, 1))()
+    if lib.b200_shard_sequences(lens, n, world, rank_of) != 0:
+        raise ValueError("b200_shard_sequences: bad arguments")
     owned: list[list[int]] = [[] for _ in range(world)]
-    for i in order:
-        r = min(range(world), key=lambda j: (load[j], len(owned[j]), j))
-        owned[r].append(i)
-        load[r] += int(ctx_lens[i])
-    return [sorted(o) for o in owned]
+    for i in range(n):
+        owned[rank_of[i]].append(i)
+    return owned
 
 
 @dataclass(frozen=True)
@@ -52,15 +56,17 @@ class HeadShard:
 def head_shard(rank: int, world: int, n_head: int, n_head_kv: int) -> HeadShard:
     """GQA maps query head h to kv head h // (n_head / n_head_kv) (ggml-cpu.c:12264), so a contiguous range of
     kv heads owns a contiguous range of query heads."""
-    if n_head % n_head_kv:
+    import ctypes as C
+    from . import lib
+    out = (C.c_int32 * 4)()
+    rc = lib.b200_head_shard(rank, world, n_head, n_head_kv, out)     # the library's policy (host/sharding.cpp)
+    if rc == -2:
         raise ValueError("n_head must be a multiple of n_head_kv")
-    if n_head_kv % world:
+    if rc == -3:
         raise ValueError(f"{n_head_kv} kv heads do not split over {world} ranks")
-    if not 0 <= rank < world:
+    if rc != 0:
         raise ValueError("rank out of range")
-    per = n_head_kv // world
-    gqa = n_head // n_head_kv
-    return HeadShard(rank, world, rank * per, per, rank * per * gqa, per * gqa)
+    return HeadShard(rank, world, out[0], out[1], out[2], out[3])
 
 
 def gather_head_outputs(local_out, gathered=None, group=None, async_op: bool = False):

@@ -94,6 +94,25 @@ def test_parser_rejects_what_the_reference_rejects(pkg):
     # positions that are not 0..n-1 cannot live in a block table
     with pytest.raises(pkg.B200Error, match="positions"):
         pkg.state_seq_unpack(patched(4 + 8*3, "<i", 7), n_layer, Q8_0, k_row, F16, v_row)
+    with pytest.raises(pkg.B200Error, match="positions"):
+        pkg.state_seq_unpack(patched(4 + 8*3, "<i", 2), n_layer, Q8_0, k_row, F16, v_row)      # position 2 twice, 3 missing
+
+
+def test_stream_rows_in_cell_order_not_position_order(pkg):
+    """llama_kv_cache_unified::state_write(seq_id) walks the cells in cell-index order (src/llama-kv-cache.cpp:856-872), which
+    is not position order once find_slot's head has wrapped, cells were reused after a seq_rm or a defrag moved them.  Such a
+    stream — the positions 0..n-1 in any row order — restores to the same rows, by position."""
+    rng = np.random.default_rng(12)
+    n, n_layer = 9, 2
+    k_row, v_row = row_bytes(Q4_0, N_EMBD_GQA), row_bytes(Q8_0, N_EMBD_GQA)
+    k, v = _rows(rng, n_layer, n, k_row), _rows(rng, n_layer, n, v_row)
+    perm = rng.permutation(n)                                   # stream row i holds position perm[i]
+    blob = bytearray(pkg.state_seq_pack(k[:, perm], v[:, perm], Q4_0, Q8_0))
+    for i in range(n):
+        struct.pack_into("<i", blob, 4 + 8*i, int(perm[i]))
+    assert unified_state_read_errors(bytes(blob), n_layer, Q4_0, k_row, Q8_0, v_row) is None    # a stream the reference reads
+    k2, v2 = pkg.state_seq_unpack(bytes(blob), n_layer, Q4_0, k_row, Q8_0, v_row)
+    assert np.array_equal(k2, k) and np.array_equal(v2, v)
 
 
 def test_restore_seq_is_seq_rm_plus_find_slot(pkg):

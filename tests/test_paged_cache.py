@@ -203,6 +203,17 @@ def test_undo_batch_is_the_slot_restorer(pkg):
     pc.undo_batch(seq, r["q_pos"])
     assert pc.seq_len(7) == 6 and pc.seq_len(3) == 0 and pc.seq_len(9) == 0 and pc.n_free() == free0
     assert pc.prepare_batch(seq)["slot_mapping"] == r["slot_mapping"]          # and the same cells come out again
+    # a batch that forced a copy-on-write: the device copy may never have run, so the undo hands the sequence its shared
+    # block back and frees the copy — the cache is exactly what it was before the batch
+    pc = pkg.PagedKVCache(8, 4)
+    pc.append(0, 6)
+    pc.seq_cp(0, 1)
+    state = lambda: (pc.n_free(), pc.seq_len(0), pc.seq_len(1), [pc.ref_count(b) for b in range(8)], pc.export([0, 1], 4))
+    before = state()
+    r = pc.prepare_batch([1, 1, 1])
+    assert r["cow_pairs"] == [(1, 2)] and pc.ref_count(1) == 1 and pc.ref_count(2) == 1
+    pc.undo_batch([1, 1, 1], r["q_pos"], r["cow_pairs"])
+    assert state() == before
 
 
 @pytest.mark.parametrize("seed", range(5))
