@@ -46,7 +46,8 @@ enum { B200_TYPE_F32 = 0, B200_TYPE_F16 = 1, B200_TYPE_Q4_0 = 2, B200_TYPE_Q8_0 
 
 /* kernel selection, for tests and ablation; AUTO in production */
 enum { B200_KERNEL_AUTO = 0, B200_KERNEL_GENERIC = 1, B200_KERNEL_STREAMK = 2, B200_KERNEL_PREFILL = 3,
-       B200_KERNEL_STREAMK_DQ = 4 /* stream-K with the tcgen05 main kernel (Q8_0 K and V only) */ };
+       B200_KERNEL_STREAMK_DQ = 4 /* REMOVED in round 2 (a tcgen05 formulation of Q8_0 decode, 20-25 % slower than the
+                                     mma.sync kernel and never chosen by AUTO): asking for it is B200_ERR_UNSUPPORTED */ };
 
 /*
  * Attention descriptor.  Tensor meaning follows ggml_flash_attn_ext (ggml/include/ggml.h:1794-1807):

@@ -57,7 +57,7 @@ struct sk_args {
     b200_attn_desc d;
     int    gqa;
     int    n_items;                     // upper bound on items per kv head
-    int    chunk_align;                 // chunk is rounded up to a multiple of this many tiles (8: the tcgen05 kernel's super-tile)
+    int    chunk_align;                 // chunk is rounded up to a multiple of this many tiles (1)
     int    chunk_min;                   // and is at least this many tiles
     int   *plan;                        // [4] {total_tiles, chunk, -, -} then P[n_q+1], FS[n_q+1]
     float *part_ml;                     // [max_segs][n_head][2]
@@ -880,8 +880,6 @@ sk_combine_kernel(const __grid_constant__ sk_args a) {
     *reinterpret_cast<float4 *>(static_cast<float *>(p.dst) + ((int64_t) row*p.n_head + h)*SK_D + 4*lane) = o;
 }
 
-#include "attn_decode_dq.cuh"
-
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
@@ -947,34 +945,6 @@ static int sk_items(const b200_attn_desc &d) {
     // the surplus CTAs leave after the header load.  (A grid cut to the work, 129 CTAs for 8 x 1024, measured 4 % slower
     // than 148 with the same 128 active: profiles/r1v_plan_ab.txt.)
     return (int) items;
-}
-
-// the tcgen05 formulation (attn_decode_dq.cuh): Q8_0 K and V, big enough that 128-token super-tiles fill the GPU.
-// B200_DECODE_DQ=0 / 1 forces it off / on wherever it is legal (A/B runs); kernel id B200_KERNEL_STREAMK_DQ asks for it.
-static bool dq_legal(const b200_attn_desc &d) {
-    return d.block_table && d.type_k == B200_TYPE_Q8_0 && d.type_v == B200_TYPE_Q8_0 && d.logit_softcap == 0.0f;
-}
-bool streamk_dq_supports(const b200_attn_desc &d) { return dq_legal(d); }
-constexpr bool DQ_AUTO = false;                              // AUTO keeps the mma.sync kernel until the A/B says otherwise
-static int dq_items(const b200_attn_desc &d) {
-    int64_t items = (int64_t) sk_sm_count()*2/d.n_head_kv;
-    if (items < 1) items = 1;
-    int64_t tok = d.total_tokens > 0 ? d.total_tokens
-                : (int64_t) d.n_q*(d.max_seq_len > 0 ? d.max_seq_len : d.bt_stride*d.block_size);
-    int64_t cap = tok/(2*DQ_TOK) + 1;                        // no more items than 256-token pieces of the work
-    if (cap < d.n_q) cap = d.n_q;
-    if (items > cap) items = cap;
-    const int64_t sk = sk_items(d);                          // the workspace is sized for the mma.sync kernel's items
-    return (int) (items < sk ? items : sk);
-}
-static bool dq_wanted(const b200_attn_desc &d) {
-    if (!dq_legal(d)) return false;
-    if (d.kernel == B200_KERNEL_STREAMK_DQ) return true;
-    static const int env = [] { const char *e = getenv("B200_DECODE_DQ"); return e ? atoi(e) : -1; }();
-    if (env == 0) return false;
-    if (env == 1) return true;
-    const int64_t tok = d.total_tokens > 0 ? d.total_tokens : (int64_t) d.n_q*(d.max_seq_len > 0 ? d.max_seq_len : 0);
-    return DQ_AUTO && tok >= (int64_t) sk_sm_count()*2*4*DQ_TOK/d.n_head_kv;   // >= 4 super-tiles per CTA
 }
 
 static size_t sk_align(size_t x) { return (x + 255) & ~(size_t) 255; }
@@ -1046,17 +1016,6 @@ static int sk_launch(const sk_args &a, const CUtensorMap &tmK, const CUtensorMap
     return B200_OK;
 }
 
-static int dq_launch(const sk_args &a, const CUtensorMap &tmK, const CUtensorMap &tmV, cudaStream_t st) {
-    static bool configured = false;
-    if (!configured) {
-        const cudaError_t e = cudaFuncSetAttribute(dq_main_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DQ_SMEM);
-        if (e != cudaSuccess) { set_error("stream-K (tcgen05): cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return B200_ERR_CUDA; }
-        configured = true;
-    }
-    launch_pdl(dq_main_kernel, dim3((unsigned) (a.n_items*a.d.n_head_kv)), dim3(DQ_THREADS), DQ_SMEM, st, a, tmK, tmV);
-    return B200_OK;
-}
-
 int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st) {
     const size_t need = streamk_workspace(d);
     if (d.workspace == nullptr || d.workspace_bytes < need) {
@@ -1067,10 +1026,9 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st) {
     a.d = d;
     a.gqa = d.n_head/d.n_head_kv;
     a.k65536 = 65536u;
-    const bool dq = dq_wanted(d);
-    a.n_items = dq ? dq_items(d) : sk_items(d);
-    a.chunk_align = dq ? DQ_TOK/SK_TILE : 1;
-    a.chunk_min = dq ? 1 : SK_MIN_CHUNK;
+    a.n_items = sk_items(d);
+    a.chunk_align = 1;
+    a.chunk_min = SK_MIN_CHUNK;
     const size_t max_segs = (size_t) sk_items(d) + d.n_q;    // the layout streamk_workspace() promised
     char *ws = static_cast<char *>(d.workspace);
     const bool dense = sk_dense(d);
@@ -1114,8 +1072,7 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st) {
         if (!check_launch("sk_plan")) return B200_ERR_CUDA;
     }
     int rc;
-    if (dq) rc = dq_launch(a, tmK, tmV, st);
-    else if (dense && d.mask) {                              // equal K/V types (streamk_supports)
+    if (dense && d.mask) {                              // equal K/V types (streamk_supports)
         rc = d.type_k == B200_TYPE_F16  ? sk_launch<B200_TYPE_F16,  B200_TYPE_F16,  true>(a, tmK, tmV, st)
            : d.type_k == B200_TYPE_Q8_0 ? sk_launch<B200_TYPE_Q8_0, B200_TYPE_Q8_0, true>(a, tmK, tmV, st)
                                         : sk_launch<B200_TYPE_Q4_0, B200_TYPE_Q4_0, true>(a, tmK, tmV, st);

@@ -43,7 +43,6 @@ int    launch_peer_wait(void *flags, void *state, int world, cudaStream_t stream
 int    launch_peer_exchange_ll(const void *local, int64_t bytes, void *const *peer_ll, void *gathered, void *state,
                                int slot, int rank, int world, cudaStream_t stream);
 bool   generic_supports(const b200_attn_desc &d);
-bool   streamk_dq_supports(const b200_attn_desc &d);
 size_t generic_workspace(const b200_attn_desc &d);
 int    launch_attn_generic(const b200_attn_desc &d, cudaStream_t st);
 bool   streamk_supports(const b200_attn_desc &d);
@@ -80,7 +79,7 @@ static int validate_attn(const b200_attn_desc *d) {
 
 static int pick_kernel(const b200_attn_desc &d) {
     if (d.kernel == B200_KERNEL_GENERIC) return B200_KERNEL_GENERIC;
-    if (d.kernel == B200_KERNEL_STREAMK || d.kernel == B200_KERNEL_STREAMK_DQ) return B200_KERNEL_STREAMK;
+    if (d.kernel == B200_KERNEL_STREAMK) return B200_KERNEL_STREAMK;
     if (d.kernel == B200_KERNEL_PREFILL) return B200_KERNEL_PREFILL;
     // many causal query rows per sequence: the tcgen05 tile kernel reads K/V once per 128/gqa rows instead of once per row
     // ... when a sequence brings enough rows to fill a tile: a ubatch interleaved position by position over many sequences
@@ -111,7 +110,7 @@ B200_API int b200_device_sm_count(void) {
 B200_API int b200_supports_attention(const b200_attn_desc *d) {
     if (validate_attn(d) != B200_OK) return 0;
     if (d->kernel == B200_KERNEL_STREAMK) return streamk_supports(*d) ? 1 : 0;
-    if (d->kernel == B200_KERNEL_STREAMK_DQ) return (streamk_supports(*d) && streamk_dq_supports(*d)) ? 1 : 0;
+    if (d->kernel == B200_KERNEL_STREAMK_DQ) return 0;                                   // removed in round 2 (include/b200_paged_attn.h)
     if (d->kernel == B200_KERNEL_PREFILL) return prefill_supports(*d) ? 1 : 0;
     if (d->kernel == B200_KERNEL_GENERIC) return generic_supports(*d) ? 1 : 0;
     return (generic_supports(*d) || streamk_supports(*d) || prefill_supports(*d)) ? 1 : 0;
@@ -123,7 +122,7 @@ B200_API size_t b200_paged_attention_workspace(const b200_attn_desc *d) {
     size_t b = streamk_supports(*d) ? streamk_workspace(*d) : 0;
     size_t c = prefill_supports(*d) ? prefill_workspace(*d) : 0;
     if (d->kernel == B200_KERNEL_GENERIC) b = c = 0;
-    if (d->kernel == B200_KERNEL_STREAMK || d->kernel == B200_KERNEL_STREAMK_DQ) a = c = 0;
+    if (d->kernel == B200_KERNEL_STREAMK) a = c = 0;
     if (d->kernel == B200_KERNEL_PREFILL) a = b = 0;
     if (b > a) a = b;
     return a > c ? a : c;
@@ -134,13 +133,14 @@ B200_API int b200_paged_attention(const b200_attn_desc *d, void *stream) {
     if (rc != B200_OK) return rc;
     if (!have_device()) return B200_ERR_CUDA;
     if (d->n_q == 0) return B200_OK;
+    if (d->kernel == B200_KERNEL_STREAMK_DQ) { set_error("attention: kernel id 4 (tcgen05 decode formulation) was removed; use AUTO or STREAMK"); return B200_ERR_UNSUPPORTED; }
     const int k = pick_kernel(*d);
     if (k == B200_KERNEL_PREFILL) {
         if (!prefill_supports(*d)) { set_error("attention: prefill tile kernel does not take this shape"); return B200_ERR_UNSUPPORTED; }
         return launch_attn_prefill(*d, static_cast<cudaStream_t>(stream));
     }
     if (k == B200_KERNEL_STREAMK) {
-        if (!streamk_supports(*d) || (d->kernel == B200_KERNEL_STREAMK_DQ && !streamk_dq_supports(*d))) {
+        if (!streamk_supports(*d)) {
             set_error("attention: stream-K kernel does not take this shape"); return B200_ERR_UNSUPPORTED;
         }
         return launch_attn_streamk(*d, static_cast<cudaStream_t>(stream));

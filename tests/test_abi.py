@@ -147,7 +147,7 @@ def test_supports_op_mirrors_reference_rules(pkg):
 
 def test_sass_of_the_hot_kernels_is_sm100a_tma_and_tcgen05(pkg, tmp_path):
     """The built library carries sm_100a SASS only, the decode kernel gathers with TMA (UTMALDG) and computes with HMMA,
-    the prefill and the Q8_0 tile kernels issue tcgen05 MMAs (UTCHMMA) with TMEM loads (the mnemonics
+    the prefill tile kernel issues tcgen05 MMAs (UTCHMMA) with TMEM loads (the mnemonics
     /opt/skills/guides/B200_PROFILING.md names as proof) — a build-level guard against a silent fallback path"""
     import shutil
     import subprocess
@@ -168,7 +168,7 @@ def test_sass_of_the_hot_kernels_is_sm100a_tma_and_tcgen05(pkg, tmp_path):
                     funcs[cur].add(m)
     sk = [f for f in funcs if "sk_main_kernel" in f]
     assert len(sk) == 12 and all({"UTMALDG", "HMMA.16816", "SYNCS"} <= funcs[f] for f in sk), {f: funcs[f] for f in sk}   # 9 K/V type pairs + 3 dense-mask forms
-    for name in ("pf_main_kernel", "dq_main_kernel"):
+    for name in ("pf_main_kernel",):
         fs = [f for f in funcs if name in f]
         assert fs and all({"UTMALDG", "UTCHMMA", "LDTM"} <= funcs[f] for f in fs), {f: funcs[f] for f in fs}
 

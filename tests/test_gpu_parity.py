@@ -477,42 +477,17 @@ def test_one_32k_sequence_quantised_70b_heads(pkg, oracle, cuda, t):
     assert oracle.max_rel_err(oracle_attention(oracle, w), got) <= TOL[t]
 
 
-# ---------------------------------------------------------------- stream-K with the tcgen05 main kernel (Q8_0 caches)
-
-DQ_CASES = [
-    ([128], 32, 8, 128),                             # exactly one super-tile
-    ([1024] * 8, 32, 8, 128),                        # config 1 shape
-    ([130, 17, 512, 64, 1, 16, 129, 255], 32, 8, 128),   # ragged: partial super-tiles, partial 16-token tiles
-    ([700, 64, 2049], 64, 8, 128),                   # 70B GQA ratio 8
-    ([5000, 300, 2600], 32, 8, 128),                 # rows split across CTAs (combine), lazy reference moves
-    ([333, 40], 8, 8, 128),                          # MHA
-    ([0, 200, 0], 16, 4, 128),                       # empty rows
-]
-
-
-@pytest.mark.parametrize("dist", ["uniform", "normal"])
-@pytest.mark.parametrize("case", DQ_CASES, ids=lambda c: f"{len(c[0])}x{max(c[0])}_h{c[1]}_{c[2]}")
-def test_paged_decode_tcgen05_q8_0(pkg, oracle, cuda, case, dist):
+def test_removed_kernel_id_is_refused(pkg, oracle, cuda):
+    """kernel id 4 (the tcgen05 formulation of Q8_0 decode, removed in round 2) is refused, not silently re-routed"""
     import torch
-    seq_lens, n_head, n_head_kv, d = case
-    w = make_workload(oracle, seq_lens, n_head, n_head_kv, d, Q8_0, seed=4321, dist=dist)
-    got = _run_paged(pkg, torch, w, pkg.KERNEL_STREAMK_DQ)
-    want = oracle_attention(oracle, w)
-    live = [i for i, n in enumerate(seq_lens) if n > 0]
-    for i, n in enumerate(seq_lens):
-        if n == 0:
-            assert np.isnan(got[i]).all()
-    assert not np.isnan(got[live]).any()
-    err, nm = oracle.max_rel_err(want[live], got[live]), oracle.nmse(want[live], got[live])
-    assert err <= TOL[Q8_0], f"max rel err {err:.3e} (nmse {nm:.3e})"
-    assert nm <= 5e-4
-
-
-def test_paged_decode_tcgen05_refuses_other_types(pkg, oracle, cuda):
-    import torch
-    w = make_workload(oracle, [64, 64], 32, 8, 128, Q4_0, seed=1)
-    with pytest.raises(pytest.skip.Exception):
-        _run_paged(pkg, torch, w, pkg.KERNEL_STREAMK_DQ)
+    w = make_workload(oracle, [128], 32, 8, 128, Q8_0, seed=2)
+    lay = pkg.KVLayout(Q8_0, 8, 128, 16, w.n_blocks)
+    q = _dev(torch, w.q)
+    call = pkg.AttnCall(q, _dev(torch, w.k_cache.reshape(-1)), _dev(torch, w.v_cache.reshape(-1)), lay, torch.empty_like(q), w.scale,
+                        block_table=_dev(torch, w.block_table), seq_lens=_dev(torch, w.seq_lens), kernel=pkg.KERNEL_STREAMK_DQ)
+    assert not call.supported()
+    with pytest.raises(pkg.B200Error):
+        call.run()
 
 
 # ---------------------------------------------------------------- the layers of a step share one schedule
