@@ -124,6 +124,8 @@ class ClockSampler(threading.Thread):
         self.index, self.rows, self.stop_flag = index, [], False
 
     def run(self):
+        if self.index < 0:
+            return
         while not self.stop_flag:
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
@@ -259,7 +261,8 @@ def main():
         gc.collect(); torch.cuda.empty_cache()
         b = copy.copy(args)
         b.workload, b.kv_type, b.layers, b.kernel, b.plan_per_layer = "config4", "f16", 0, 0, False
-        b.steps = 30
+        # long enough for the clock sampler: ~0.8 s of timed steps whatever the N (5 ms per step on one GPU, 0.87 ms on eight)
+        b.steps = {1: 160, 2: 300, 4: 500}.get(world, 900)
         b.no_cpu_baseline = True
         sub = run_decode(b, rank, world, local, pkg)
         if rank == 0:
@@ -389,7 +392,7 @@ def run_decode(args, rank, world, local, pkg):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
-    sampler = ClockSampler(local); sampler.start()
+    sampler = ClockSampler(local if rank == 0 else -1); sampler.start()   # rank 0's GPU: eight concurrent nvidia-smi loops starve each other
     ms_total = timed(run_step, args.steps, args.warmup)
     ms_step = ms_total / args.steps
     bytes_step_rank = kv_bytes_op * n_layer
@@ -421,7 +424,10 @@ def run_decode(args, rank, world, local, pkg):
     # layer, overlapped with compute), kv_write + attention (+ all-gather) per layer, D2H of every layer's output
     e2e = None
     if not args.no_e2e:
-        res_d = (peer.all_slots()[:n_layer] if peer is not None else gathered) if collective else out_d
+        # head-sharded: the exchanged result [n_layer, world, ...] is on every GPU; each rank brings ITS slice to its host
+        # process — the union over the ranks is the whole result and every byte crosses a host link once (eight ranks each
+        # downloading all of it would move it eight times through one host's memory)
+        res_d = ((peer.all_slots()[:n_layer] if peer is not None else gathered)[:, rank:rank + 1]) if collective else out_d
         q_h = (torch.rand((n_layer, n_seqs, n_head, D)) * 2 - 1).pin_memory()
         knew_h = (torch.rand((n_layer, n_seqs, n_head_kv * D)) * 2 - 1).pin_memory()
         vnew_h = (torch.rand((n_layer, n_seqs, n_head_kv * D)) * 2 - 1).pin_memory()
@@ -460,6 +466,21 @@ def run_decode(args, rank, world, local, pkg):
             group_calls = [pkg.StepCall(calls[a0:a1], [pkg.kv_write_desc(knew_d[l], vnew_d[l], slot_new_d, kcs[l], vcs[l], lay)
                                                         for l in range(a0, a1)]) for a0, a1 in groups]
         group_graphs = None
+        if not collective and not args.no_graph:
+            # each group's b200_decode_step call (kv_write + plan/main/combine per layer) captured once and replayed per step,
+            # like the resident path: the host-side launch gaps between ~100 kernels per step go away, the copies stay
+            # ordinary stream operations around the replays
+            group_graphs = []
+            for gc in group_calls:
+                side = torch.cuda.Stream(); side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):
+                    gc.run()
+                torch.cuda.current_stream().wait_stream(side)
+                torch.cuda.synchronize()
+                gg = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gg):
+                    gc.run()
+                group_graphs.append(gg)
         if collective and peer is not None and not args.no_graph and len(groups) == 2:
             def group_body(a0, a1):
                 for l in range(a0, a1):
@@ -493,7 +514,9 @@ def run_decode(args, rank, world, local, pkg):
                     ev_in[gi].record(s_in)
             for gi, (a0, a1) in enumerate(groups):
                 cur.wait_event(ev_in[gi])
-                if group_calls is not None:
+                if group_graphs is not None and group_calls is not None:
+                    group_graphs[gi].replay()
+                elif group_calls is not None:
                     group_calls[gi].run()
                 elif group_graphs is not None:
                     group_graphs[gi].replay(); peer.note_replay(a1 - a0)
