@@ -72,8 +72,12 @@ struct b200_ggml_tensor {
 B200_API size_t b200_flash_attn_ext_workspace(const struct b200_ggml_tensor *dst);
 B200_API int    b200_flash_attn_ext(const struct b200_ggml_tensor *dst, void *workspace, size_t workspace_bytes, void *stream);
 
-/* GGML_OP_CPY: src0 -> src1 (src1 is the destination view, as in ggml_cuda_cpy).  Handles the two uses on the
- * hot path: F32 -> {F32,F16,Q8_0,Q4_0} contiguous rows (KV store) and same-type contiguous copies (block moves). */
+/* GGML_OP_CPY: src0 -> src1 (src1 is the destination view, as in ggml_cuda_cpy).  The two uses on the hot path — F32 ->
+ * {F32,F16,Q8_0,Q4_0} contiguous rows (KV store) and same-type contiguous copies (block moves) — have their own kernels; beyond
+ * them, row by row: F32 / F16 sources with any strides (permuted, not contiguous along dim 0) to F32 / F16 / Q8_0 / Q4_0, and
+ * Q8_0 / Q4_0 rows to F32 (the cast of build_rope_shift), for rows of a multiple of 4 (32 with a quantised side) up to 8192
+ * elements, into a destination that is contiguous or has the source's shape with contiguous rows.  Everything else
+ * (other types, odd row lengths) is declined by b200_supports_op and stays with the backend's own kernel. */
 B200_API int    b200_cpy(const struct b200_ggml_tensor *src0, struct b200_ggml_tensor *src1, void *stream);
 
 /* 1 if b200_flash_attn_ext / b200_cpy will take this node, else 0 (the backend keeps its own kernel). */

@@ -12,6 +12,8 @@ namespace b200 {
 static_assert(sizeof(b200_ggml_tensor) == 336, "ggml_tensor mirror out of sync with ggml/include/ggml.h:578-610");
 
 int launch_kv_write(const b200_kv_write_desc &d, cudaStream_t stream);
+int launch_cpy_rows(const void *src, void *dst, int type_src, int type_dst, const int64_t ne[4], const int64_t snb[4],
+                    const int64_t dnb[4], cudaStream_t stream);
 
 static int64_t nelements(const b200_ggml_tensor *t) { return t->ne[0]*t->ne[1]*t->ne[2]*t->ne[3]; }
 
@@ -99,6 +101,43 @@ static bool node_to_desc(const b200_ggml_tensor *dst, b200_attn_desc &d, b200_kv
     return true;
 }
 
+// element-wise strided copy between F32 / F16 tensors of any strides (test_cpy "not contiguous", ggml_cont of a permuted
+// tensor): element i of the source in its logical order -> element i of the destination in its own
+struct cpy_elem_args {
+    const char *src; char *dst; int type_src, type_dst;
+    int64_t n, sne[4], snb[4], dne[4], dnb[4];
+};
+__global__ void __launch_bounds__(256) cpy_elem_kernel(const __grid_constant__ cpy_elem_args a) {
+    for (int64_t i = (int64_t) blockIdx.x*256 + threadIdx.x; i < a.n; i += (int64_t) gridDim.x*256) {
+        int64_t r = i, so = 0, d_ = i, doff = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { so += (r % a.sne[k])*a.snb[k]; r /= a.sne[k]; doff += (d_ % a.dne[k])*a.dnb[k]; d_ /= a.dne[k]; }
+        const float v = a.type_src == B200_TYPE_F32 ? *reinterpret_cast<const float *>(a.src + so)
+                                                    : __half2float(*reinterpret_cast<const __half *>(a.src + so));
+        if (a.type_dst == B200_TYPE_F32) *reinterpret_cast<float *>(a.dst + doff) = v;
+        else                             *reinterpret_cast<__half *>(a.dst + doff) = __float2half_rn(v);
+    }
+}
+static bool cpy_elem_ok(const b200_ggml_tensor *s0, const b200_ggml_tensor *s1) {
+    const auto fp = [](int t) { return t == B200_TYPE_F32 || t == B200_TYPE_F16; };
+    return fp(s0->type) && fp(s1->type) && nelements(s0) == nelements(s1) && nelements(s0) > 0;
+}
+
+// the row-wise general copy (cpy_rows_kernel, kv_write.cu): which (src0, src1) pairs it takes
+static bool cpy_rows_ok(const b200_ggml_tensor *s0, const b200_ggml_tensor *s1) {
+    const auto kv_type = [](int t) { return t == B200_TYPE_F32 || t == B200_TYPE_F16 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_0; };
+    const auto quant = [](int t) { return t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_0; };
+    if (!kv_type(s0->type) || !kv_type(s1->type)) return false;
+    if (nelements(s0) != nelements(s1) || nelements(s0) == 0) return false;
+    const int64_t ne0 = s0->ne[0];
+    if (ne0 % 4 || ne0 > 8192 || ((quant(s0->type) || quant(s1->type)) && ne0 % QK)) return false;
+    if (quant(s0->type) && (s1->type != B200_TYPE_F32 || s0->nb[0] != (size_t) row_bytes(s0->type, QK))) return false;   // cpy.cu takes Q -> F32 only
+    if (is_contiguous(s1)) return true;                            // row r of the source = the r-th run of ne0 elements
+    if (s1->nb[0] != (size_t) (quant(s1->type) ? row_bytes(s1->type, QK) : row_bytes(s1->type, 1))) return false;
+    for (int i = 0; i < B200_GGML_MAX_DIMS; ++i) if (s0->ne[i] != s1->ne[i]) return false;    // same shape, own strides
+    return true;
+}
+
 __global__ void __launch_bounds__(256) copy16_kernel(const uint4 *src, uint4 *dst, int64_t n16) {
     for (int64_t i = (int64_t) blockIdx.x*256 + threadIdx.x; i < n16; i += (int64_t) gridDim.x*256) dst[i] = src[i];
 }
@@ -134,10 +173,30 @@ B200_API int b200_flash_attn_ext(const struct b200_ggml_tensor *dst, void *works
 B200_API int b200_cpy(const struct b200_ggml_tensor *src0, struct b200_ggml_tensor *src1, void *stream) {
     if (!src0 || !src1) { set_error("cpy: NULL tensor"); return B200_ERR_INVALID; }
     if (nelements(src0) != nelements(src1)) { set_error("cpy: element counts differ"); return B200_ERR_INVALID; }   // ggml.c:2953
-    if (!is_contiguous(src0) || !is_contiguous(src1)) { set_error("cpy: only contiguous tensors are taken"); return B200_ERR_UNSUPPORTED; }
     const int64_t n = nelements(src0);
     if (n == 0) return B200_OK;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const bool fast = is_contiguous(src0) && is_contiguous(src1) && (src0->type == src1->type || src0->type == B200_TYPE_F32);
+    if (!fast) {                                                   // strided / permuted source, F16 or quantised source: row by row
+        if (cpy_elem_ok(src0, src1)) {
+            cpy_elem_args e;
+            e.src = static_cast<const char *>(src0->data); e.dst = static_cast<char *>(src1->data);
+            e.type_src = src0->type; e.type_dst = src1->type; e.n = n;
+            for (int i = 0; i < 4; ++i) { e.sne[i] = src0->ne[i]; e.snb[i] = (int64_t) src0->nb[i]; e.dne[i] = src1->ne[i]; e.dnb[i] = (int64_t) src1->nb[i]; }
+            const int64_t blocks = (n + 255)/256;
+            cpy_elem_kernel<<<(unsigned) (blocks < 148*16 ? blocks : 148*16), 256, 0, st>>>(e);
+            count_launch();
+            return check_launch("cpy_elem") ? B200_OK : B200_ERR_CUDA;
+        }
+        if (!cpy_rows_ok(src0, src1)) { set_error("cpy: this pair of tensors is not taken (types %d -> %d)", src0->type, src1->type); return B200_ERR_UNSUPPORTED; }
+        int64_t ne[4], snb[4], dnb[4];
+        for (int i = 0; i < 4; ++i) { ne[i] = src0->ne[i]; snb[i] = (int64_t) src0->nb[i]; dnb[i] = (int64_t) src1->nb[i]; }
+        if (is_contiguous(src1)) {                                 // destination rows one after the other, whatever its own shape
+            const int64_t rb = row_bytes(src1->type, ne[0]);
+            dnb[1] = rb; dnb[2] = rb*ne[1]; dnb[3] = rb*ne[1]*ne[2];
+        }
+        return launch_cpy_rows(src0->data, src1->data, src0->type, src1->type, ne, snb, dnb, st);
+    }
     if (src0->type == src1->type) {                                // block move: bytes
         const int64_t bytes = row_bytes(src0->type, n);
         const int grid = (int) ((bytes/16 + 255)/256 < 148*8 ? ((bytes/16 + 255)/256 > 0 ? (bytes/16 + 255)/256 : 1) : 148*8);
@@ -172,9 +231,12 @@ B200_API int b200_supports_op(const struct b200_ggml_tensor *op) {
     }
     if (op->op == B200_GGML_OP_CPY || op->op == B200_GGML_OP_DUP || op->op == B200_GGML_OP_CONT) {
         const b200_ggml_tensor *s0 = op->src[0], *s1 = op->op == B200_GGML_OP_CPY ? op->src[1] : op;
-        if (!s0 || !s1 || !is_contiguous(s0) || !is_contiguous(s1)) return 0;
-        if (s0->type == s1->type) return 1;
-        return s0->type == B200_TYPE_F32 && s0->ne[0] % QK == 0 && s0->ne[0] <= 8192 ? 1 : 0;
+        if (!s0 || !s1) return 0;
+        if (is_contiguous(s0) && is_contiguous(s1)) {
+            if (s0->type == s1->type) return 1;
+            if (s0->type == B200_TYPE_F32) return s0->ne[0] % QK == 0 && s0->ne[0] <= 8192 ? 1 : 0;
+        }
+        return (cpy_elem_ok(s0, s1) || cpy_rows_ok(s0, s1)) ? 1 : 0;   // permuted / strided / F16 / quantised sources
     }
     return 0;
 }

@@ -318,6 +318,8 @@ k_shift_kernel(const __grid_constant__ k_shift_args a) {
             cs[2*ic]     = __fmul_rn(cosf(th), a.mscale);
             cs[2*ic + 1] = __fmul_rn(sinf(th), a.mscale);
         }
+        // (round 2: fetching the NEXT layer's row into registers while this one is rotated and written back was measured and
+        // made the launch slower, 0.42 -> 0.54 ms for F16, profiles/r2l_kshift.jsonl; the plain form stays)
         for (int ci = blockIdx.y; ci < a.n; ci += gridDim.y) {
             char *cache = a.caches[ci];
             const char *row = cache + cell*p.nb_token;
@@ -392,6 +394,66 @@ int launch_k_shift(const b200_k_shift_desc &d, cudaStream_t stream) {
         if (!check_launch("k_shift")) return B200_ERR_CUDA;
     }
     return B200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// GGML_OP_CPY in general (ggml_cuda_cpy, ggml/src/ggml-cuda/cpy.cu:510-584; cases of tests/test-backend-ops.cpp:3992-4009):
+// strided / permuted sources, F16 sources, quantised sources to F32.  One CTA per row of ne0 elements: the row is brought
+// to F32 in shared memory (element-wise through the source strides, so a source that is not contiguous along dim 0 works
+// too), then leaves through the KV-write path (same converters, staged, 16-byte stores).  Row r of the source, in its
+// logical order (i1, i2, i3), goes to row r of the destination: contiguous, or with the source's shape and its own strides.
+// ---------------------------------------------------------------------------------------------
+struct cpy_rows_args {
+    const char *src; char *dst;
+    int type_src, type_dst;
+    int64_t ne0, ne1, ne2, ne3;
+    int64_t snb0, snb1, snb2, snb3;          // source strides in bytes (snb0 == element size: the row is contiguous)
+    int64_t dnb1, dnb2, dnb3;                // destination row strides in bytes (rows themselves are contiguous)
+};
+
+__global__ void __launch_bounds__(KVW_THREADS)
+cpy_rows_kernel(const __grid_constant__ cpy_rows_args a) {
+    extern __shared__ __align__(16) char cr_smem[];
+    float *x = reinterpret_cast<float *>(cr_smem);
+    char *stage = cr_smem + a.ne0*4;
+    const int64_t r = blockIdx.x;
+    const int64_t i3 = r/(a.ne1*a.ne2), i2 = (r - i3*a.ne1*a.ne2)/a.ne1, i1 = r - i3*a.ne1*a.ne2 - i2*a.ne1;
+    const char *srow = a.src + i1*a.snb1 + i2*a.snb2 + i3*a.snb3;
+    for (int e = threadIdx.x; e < a.ne0; e += KVW_THREADS) {
+        float v;
+        switch (a.type_src) {
+            case B200_TYPE_F32:  v = *reinterpret_cast<const float *>(srow + e*a.snb0); break;
+            case B200_TYPE_F16:  v = __half2float(*reinterpret_cast<const __half *>(srow + e*a.snb0)); break;
+            case B200_TYPE_Q8_0: v = k_shift_load<B200_TYPE_Q8_0>(srow, e); break;
+            default:             v = k_shift_load<B200_TYPE_Q4_0>(srow, e); break;
+        }
+        x[e] = v;
+    }
+    __syncthreads();
+    char *drow = a.dst + i1*a.dnb1 + i2*a.dnb2 + i3*a.dnb3;
+    const int hd = (int) a.ne0;
+    switch (a.type_dst) {
+        case B200_TYPE_F32:  write_row<B200_TYPE_F32 >(x, drow, 0, 1, hd, 0, row_bytes(B200_TYPE_F32,  hd), stage); break;
+        case B200_TYPE_F16:  write_row<B200_TYPE_F16 >(x, drow, 0, 1, hd, 0, row_bytes(B200_TYPE_F16,  hd), stage); break;
+        case B200_TYPE_Q8_0: write_row<B200_TYPE_Q8_0>(x, drow, 0, 1, hd, 0, row_bytes(B200_TYPE_Q8_0, hd), stage); break;
+        default:             write_row<B200_TYPE_Q4_0>(x, drow, 0, 1, hd, 0, row_bytes(B200_TYPE_Q4_0, hd), stage); break;
+    }
+}
+
+int launch_cpy_rows(const void *src, void *dst, int type_src, int type_dst, const int64_t ne[4], const int64_t snb[4],
+                    const int64_t dnb[4], cudaStream_t stream) {
+    cpy_rows_args a;
+    a.src = static_cast<const char *>(src); a.dst = static_cast<char *>(dst); a.type_src = type_src; a.type_dst = type_dst;
+    a.ne0 = ne[0]; a.ne1 = ne[1]; a.ne2 = ne[2]; a.ne3 = ne[3];
+    a.snb0 = snb[0]; a.snb1 = snb[1]; a.snb2 = snb[2]; a.snb3 = snb[3];
+    a.dnb1 = dnb[1]; a.dnb2 = dnb[2]; a.dnb3 = dnb[3];
+    const int64_t rows = ne[1]*ne[2]*ne[3];
+    if (rows <= 0 || ne[0] <= 0) return B200_OK;
+    const size_t smem = (size_t) ne[0]*4 + (size_t) row_bytes(type_dst, ne[0]);
+    if (smem > 48*1024 || rows >= (1LL << 31)) { set_error("cpy: row of %lld elements / %lld rows not supported", (long long) ne[0], (long long) rows); return B200_ERR_UNSUPPORTED; }
+    cpy_rows_kernel<<<(unsigned) rows, KVW_THREADS, smem, stream>>>(a);
+    count_launch();
+    return check_launch("cpy_rows") ? B200_OK : B200_ERR_CUDA;
 }
 
 } // namespace b200

@@ -254,6 +254,65 @@ def test_cpy_node_f32_to_cache_types(pkg, oracle, cuda, t, ne):
     assert np.array_equal(dst_b.cpu().numpy(), want)
 
 
+@pytest.mark.parametrize("perm", [(0, 2, 1, 3), (1, 0, 2, 3)], ids=["by_rows", "not_contiguous"])
+@pytest.mark.parametrize("ts,td", [(F32, F32), (F32, F16), (F16, F16), (F16, F32), (F32, Q8_0), (F32, Q4_0), (F16, Q8_0)])
+def test_cpy_node_permuted_sources(pkg, oracle, cuda, ts, td, perm):
+    """test_cpy(type_src, type_dst, {256, 2, 3, 4}, permute) of tests/test-backend-ops.cpp:3992-4009: a permuted view of a
+    contiguous F32 / F16 tensor copied into a contiguous destination of the view's shape; the bytes must equal the CPU
+    semantics (element i of the view in its own order -> element i of the destination, converted with the _ref quantisers)"""
+    import torch
+    ne = (256, 2, 3, 4)
+    rng = np.random.default_rng(7)
+    base = rng.uniform(-1, 1, ne[::-1]).astype(np.float32 if ts == F32 else np.float16)     # numpy axes are (3, 2, 1, 0)
+    esz = base.itemsize
+    nb = (esz, ne[0] * esz, ne[0] * ne[1] * esz, ne[0] * ne[1] * ne[2] * esz)
+    # ggml_permute(a, p0..p3): axis i of a becomes axis p_i of the result
+    vne, vnb = [0] * 4, [0] * 4
+    for i in range(4):
+        vne[perm[i]], vnb[perm[i]] = ne[i], nb[i]
+    if td in (Q8_0, Q4_0) and vne[0] % 32:
+        pytest.skip("row length of the view is not a multiple of the quant block")
+    view = np.lib.stride_tricks.as_strided(base, shape=tuple(vne[::-1]), strides=tuple(vnb[::-1]))
+    flat = np.ascontiguousarray(view).astype(np.float32).reshape(-1, vne[0])
+    if td == F32:
+        want = flat.view(np.uint8).reshape(-1)
+    elif td == F16:
+        want = flat.astype(np.float16).view(np.uint8).reshape(-1)
+    else:
+        want = oracle.from_float(td, flat).reshape(-1)
+    src_b = torch.from_numpy(base.view(np.uint8).reshape(-1)).to(cuda)
+    dst_b = torch.zeros(want.size, dtype=torch.uint8, device=cuda)
+    src = _node(pkg, ts, tuple(vne), tuple(vnb), src_b.data_ptr())
+    dsz = {F32: 4, F16: 2, Q8_0: 34, Q4_0: 18}[td]
+    rb = pkg.row_bytes(td, vne[0])
+    dst = _node(pkg, td, tuple(vne), (dsz, rb, rb * vne[1], rb * vne[1] * vne[2]), dst_b.data_ptr(), op=pkg.GGML_OP_CPY)
+    dst.src[0], dst.src[1] = C.pointer(src), C.pointer(dst)
+    assert pkg.lib.b200_supports_op(C.byref(dst)) == 1, pkg.lib.b200_last_error().decode()
+    assert pkg.lib.b200_cpy(C.byref(src), C.byref(dst), None) == 0, pkg.lib.b200_last_error().decode()
+    torch.cuda.synchronize()
+    assert np.array_equal(dst_b.cpu().numpy(), want)
+
+
+@pytest.mark.parametrize("ts", [Q8_0, Q4_0])
+def test_cpy_node_quantised_to_f32(pkg, oracle, cuda, ts):
+    """the cast of build_rope_shift (src/llama-context.cpp:476-480): Q8_0 / Q4_0 rows -> F32 = dequantize_row_*"""
+    import torch
+    rng = np.random.default_rng(8)
+    x = rng.uniform(-1, 1, (24, 256)).astype(np.float32)
+    q = oracle.from_float(ts, x)
+    want = oracle.to_float(ts, q, 256).astype(np.float32)
+    src_b = torch.from_numpy(q.reshape(-1)).to(cuda)
+    dst_b = torch.zeros(want.size * 4, dtype=torch.uint8, device=cuda)
+    rb = pkg.row_bytes(ts, 256)
+    src = _node(pkg, ts, (256, 4, 3, 2), ({Q8_0: 34, Q4_0: 18}[ts], rb, rb * 4, rb * 12), src_b.data_ptr())
+    dst = _node(pkg, F32, (256, 4, 3, 2), (4, 1024, 4096, 12288), dst_b.data_ptr(), op=pkg.GGML_OP_CPY)
+    dst.src[0], dst.src[1] = C.pointer(src), C.pointer(dst)
+    assert pkg.lib.b200_supports_op(C.byref(dst)) == 1
+    assert pkg.lib.b200_cpy(C.byref(src), C.byref(dst), None) == 0, pkg.lib.b200_last_error().decode()
+    torch.cuda.synchronize()
+    assert np.array_equal(dst_b.cpu().numpy().view(np.float32).reshape(want.shape), want)
+
+
 @pytest.mark.parametrize("t", [F16, Q8_0, Q4_0])
 def test_cpy_node_same_type_block_move(pkg, oracle, cuda, t):
     """build_kv_self_defrag's moves (llama-context.cpp:670-707): same-type 2-D row views, bytes copied"""
