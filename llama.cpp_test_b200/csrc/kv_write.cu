@@ -12,6 +12,7 @@
 // (ggml/src/ggml-quants.c:194-216, :31-66) with explicit _rn intrinsics so nvcc cannot contract
 // x*id + 8.5f into an FMA; half conversion is RNE like ggml_fp32_to_fp16_row (ggml/src/ggml.c:387).
 #include "common.cuh"
+#include <cstdlib>
 
 namespace b200 {
 
@@ -98,19 +99,10 @@ __device__ __forceinline__ void convert4(const float4 x, int e0, char *stage, in
     }
 }
 
+// the staged (converted, heads packed) row -> cache + cell*nb_token; the whole CTA takes part, after a barrier behind the staging
 template <int TYPE>
-__device__ void write_row(const float *src, char *cache, int64_t cell, int n_head_kv, int head_dim,
-                          int64_t nb_token, int64_t nb_head, char *stage) {
-    const int row_elems = n_head_kv*head_dim;
-    const int lane = threadIdx.x & 31;
-    // uniform trip count for the whole CTA: lanes past the row still take part in the shuffles
-    for (int base = 0; base < row_elems; base += 4*KVW_THREADS) {
-        const int e0 = base + 4*threadIdx.x;
-        const bool active = e0 < row_elems;
-        const float4 x = active ? *reinterpret_cast<const float4 *>(src + e0) : make_float4(0.f, 0.f, 0.f, 0.f);
-        convert4<TYPE>(x, e0, stage, lane, active);
-    }
-    __syncthreads();
+__device__ __forceinline__ void store_staged_row(const char *stage, char *cache, int64_t cell, int n_head_kv, int head_dim,
+                                                 int64_t nb_token, int64_t nb_head) {
     const int64_t head_bytes = row_bytes(TYPE, head_dim);
     char *dst = cache + cell*nb_token;
     if (nb_head == head_bytes && (((uintptr_t) dst | (uintptr_t) (head_bytes*n_head_kv)) & 15) == 0) {
@@ -124,6 +116,22 @@ __device__ void write_row(const float *src, char *cache, int64_t cell, int n_hea
             reinterpret_cast<uint16_t *>(dst + h*nb_head)[o] = reinterpret_cast<const uint16_t *>(stage)[i];
         }
     }
+}
+
+template <int TYPE>
+__device__ void write_row(const float *src, char *cache, int64_t cell, int n_head_kv, int head_dim,
+                          int64_t nb_token, int64_t nb_head, char *stage) {
+    const int row_elems = n_head_kv*head_dim;
+    const int lane = threadIdx.x & 31;
+    // uniform trip count for the whole CTA: lanes past the row still take part in the shuffles
+    for (int base = 0; base < row_elems; base += 4*KVW_THREADS) {
+        const int e0 = base + 4*threadIdx.x;
+        const bool active = e0 < row_elems;
+        const float4 x = active ? *reinterpret_cast<const float4 *>(src + e0) : make_float4(0.f, 0.f, 0.f, 0.f);
+        convert4<TYPE>(x, e0, stage, lane, active);
+    }
+    __syncthreads();
+    store_staged_row<TYPE>(stage, cache, cell, n_head_kv, head_dim, nb_token, nb_head);
 }
 
 // grid (n_tokens, 2): y == 0 writes K, y == 1 writes V
@@ -343,6 +351,109 @@ k_shift_kernel(const __grid_constant__ k_shift_args a) {
     }
 }
 
+// Fast form for head_dim 128 (one warp = one head row, a lane = 4 consecutive elements): the general kernel above is
+// instruction-bound, not latency- or byte-bound — per element it pays an integer division for the head, a 2-byte load, a
+// shared-memory round trip and two more divisions in the rotation loop, ~300 instructions per thread and layer, which at 8
+// CTAs per SM is the whole 0.42 ms of a 32-layer shift (round 1: 0.19 of HBM for F16, the same time for every type).  Here
+// a lane loads its 4 elements with one or two vector loads, rotates them in registers (NORM pairs live inside the lane; NEOX
+// partners are 64 elements = 16 lanes away: one shuffle each) with its cos / sin kept in registers across the layers, and
+// hands them straight to convert4: no F32 row in shared memory, two barriers per layer instead of three, ~60 instructions.
+// Same arithmetic sequence as the general kernel (and ggml_compute_forward_rope_f32 / _f16): results are bit-identical.
+template <int TYPE>
+__device__ __forceinline__ float4 k_shift_load4(const char *head, int i) {          // elements i..i+3 of one head row, i % 4 == 0
+    if constexpr (TYPE == B200_TYPE_F32) return *reinterpret_cast<const float4 *>(head + 4*i);
+    else if constexpr (TYPE == B200_TYPE_F16) {
+        const uint2 w = *reinterpret_cast<const uint2 *>(head + 2*i);
+        const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&w.x)), b = __half22float2(*reinterpret_cast<const __half2 *>(&w.y));
+        return make_float4(a.x, a.y, b.x, b.y);
+    } else if constexpr (TYPE == B200_TYPE_Q8_0) {
+        const char *blk = head + (i/QK)*Q8_BYTES;
+        const float d = __half2float(*reinterpret_cast<const __half *>(blk));
+        const uint32_t lo = ld_u16(blk + 2 + (i % QK)), hi = ld_u16(blk + 4 + (i % QK));
+        return make_float4(__fmul_rn((float) (int8_t) (lo & 0xff), d), __fmul_rn((float) (int8_t) (lo >> 8), d),
+                           __fmul_rn((float) (int8_t) (hi & 0xff), d), __fmul_rn((float) (int8_t) (hi >> 8), d));
+    } else {
+        const char *blk = head + (i/QK)*Q4_BYTES;
+        const float d = __half2float(*reinterpret_cast<const __half *>(blk));
+        const int j = i % QK, sh = j < 16 ? 0 : 4;
+        const uint32_t lo = ld_u16(blk + 2 + (j & 15)), hi = ld_u16(blk + 4 + (j & 15));
+        auto deq = [&](uint32_t b) { return __fmul_rn((float) ((int) ((b >> sh) & 0xf) - 8), d); };
+        return make_float4(deq(lo & 0xff), deq(lo >> 8), deq(hi & 0xff), deq(hi >> 8));
+    }
+}
+
+template <int TYPE, bool NEOX>
+__global__ void __launch_bounds__(KVW_THREADS)
+k_shift_fast_kernel(const __grid_constant__ k_shift_args a) {
+    extern __shared__ __align__(16) char ks_smem[];
+    const b200_k_shift_desc &p = a.d;
+    constexpr int HD = 128;
+    const int half_rot = p.n_rot/2, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float *cs = reinterpret_cast<float *>(ks_smem);                   // (cos, sin) per rotated pair
+    char  *stage = ks_smem + (((size_t) p.n_rot*4 + 15) & ~(size_t) 15);
+    const int64_t n_rows = p.cells ? p.n_rows : p.n_cells;
+    for (int64_t r = blockIdx.x; r < n_rows; r += gridDim.x) {
+        const int64_t cell = p.cells ? (int64_t) p.cells[r] : r;
+        if (cell < 0 || cell >= p.n_cells) continue;                 // CTA-uniform
+        const float pos = (float) (int64_t) p.shift[cell];
+        __syncthreads();                                             // the previous row's readers of cs are done
+        for (int ic = threadIdx.x; ic < half_rot; ic += KVW_THREADS) {
+            float theta = pos;
+            for (int k = 0; k < ic; ++k) theta = __fmul_rn(theta, a.theta_scale);
+            const float ff = p.freq_factors ? p.freq_factors[ic] : 1.0f;
+            const float extrap = __fdiv_rn(theta, ff);
+            const float interp = __fmul_rn(p.freq_scale, extrap);
+            float th = interp;
+            if (p.ext_factor != 0.0f) {
+                const float y = __fdiv_rn(__fsub_rn((float) ic, a.corr0), fmaxf(0.001f, __fsub_rn(a.corr1, a.corr0)));
+                const float ramp_mix = __fmul_rn(__fsub_rn(1.0f, fminf(1.0f, fmaxf(0.0f, y))), p.ext_factor);
+                th = __fadd_rn(__fmul_rn(interp, __fsub_rn(1.0f, ramp_mix)), __fmul_rn(extrap, ramp_mix));
+            }
+            cs[2*ic]     = __fmul_rn(cosf(th), a.mscale);
+            cs[2*ic + 1] = __fmul_rn(sinf(th), a.mscale);
+        }
+        __syncthreads();
+        // this lane's cos / sin, kept across the layers.  NORM: pairs (4l, 4l+1), (4l+2, 4l+3) -> ic = 2l, 2l+1.
+        // NEOX (n_rot == 128): element 4(l%16)+k pairs with the one 64 further on -> ic = 4(l%16)+k for both partners.
+        float c[4], sn[4];
+        bool rot[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int ic = NEOX ? 4*(lane & 15) + k : 2*lane + (k >> 1);
+            rot[k] = ic < half_rot;
+            c[k]  = rot[k] ? cs[2*ic] : 1.0f;
+            sn[k] = rot[k] ? cs[2*ic + 1] : 0.0f;
+        }
+        for (int ci = blockIdx.y; ci < a.n; ci += gridDim.y) {
+            char *cache = a.caches[ci];
+            const char *row = cache + cell*p.nb_token;
+            for (int h = warp; h < p.n_head_kv; h += KVW_THREADS/32) {
+                float4 x = k_shift_load4<TYPE>(row + h*p.nb_head, 4*lane);
+                if constexpr (NEOX) {
+                    const float4 y = make_float4(__shfl_xor_sync(0xffffffffu, x.x, 16), __shfl_xor_sync(0xffffffffu, x.y, 16),
+                                                 __shfl_xor_sync(0xffffffffu, x.z, 16), __shfl_xor_sync(0xffffffffu, x.w, 16));
+                    float xv[4] = {x.x, x.y, x.z, x.w};
+                    const float yv[4] = {y.x, y.y, y.z, y.w};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        if (!rot[k]) continue;
+                        xv[k] = lane < 16 ? __fsub_rn(__fmul_rn(xv[k], c[k]), __fmul_rn(yv[k], sn[k]))      // x0' = x0 c - x1 s
+                                          : __fadd_rn(__fmul_rn(yv[k], sn[k]), __fmul_rn(xv[k], c[k]));     // x1' = x0 s + x1 c
+                    }
+                    x = make_float4(xv[0], xv[1], xv[2], xv[3]);
+                } else {
+                    if (rot[0]) { const float x0 = x.x, x1 = x.y; x.x = __fsub_rn(__fmul_rn(x0, c[0]), __fmul_rn(x1, sn[0])); x.y = __fadd_rn(__fmul_rn(x0, sn[0]), __fmul_rn(x1, c[0])); }
+                    if (rot[2]) { const float x0 = x.z, x1 = x.w; x.z = __fsub_rn(__fmul_rn(x0, c[2]), __fmul_rn(x1, sn[2])); x.w = __fadd_rn(__fmul_rn(x0, sn[2]), __fmul_rn(x1, c[2])); }
+                }
+                convert4<TYPE>(x, HD*h + 4*lane, stage, lane, true);
+            }
+            __syncthreads();
+            store_staged_row<TYPE>(stage, cache, cell, p.n_head_kv, HD, p.nb_token, p.nb_head);
+            __syncthreads();                                             // the stage is free again
+        }
+    }
+}
+
 // ggml_rope_yarn_corr_dims, ggml/src/ggml.c:3735-3750 (host side, the same libm calls as the reference)
 static void k_shift_corr_dims(int n_dims, int n_ctx_orig, float freq_base, float beta_fast, float beta_slow, float dims[2]) {
     const float pi = 3.14159265358979323846f;
@@ -384,6 +495,29 @@ int launch_k_shift(const b200_k_shift_desc &d, cudaStream_t stream) {
         if (gy > n) gy = n;
         if (gy < 1) gy = 1;
         const dim3 grid(gx, (unsigned) gy);
+        // head_dim 128 with aligned heads: the register form (NEOX needs its partners 16 lanes away: n_rot == 128)
+        const bool neox = (d.mode & 2) != 0;
+        const int64_t hb = row_bytes(d.type_k, 128);
+        const bool aligned = d.type_k == B200_TYPE_F32 ? ((d.nb_head | d.nb_token) % 16 == 0 && ((uintptr_t) a.caches[0] & 15) == 0)
+                           : d.type_k == B200_TYPE_F16 ? ((d.nb_head | d.nb_token) % 8 == 0 && ((uintptr_t) a.caches[0] & 7) == 0)
+                                                       : ((d.nb_head | d.nb_token) % 2 == 0 && ((uintptr_t) a.caches[0] & 1) == 0);
+        bool all_aligned = aligned;
+        for (int i = 0; i < n && all_aligned; ++i) all_aligned = ((uintptr_t) a.caches[i] & 15) == 0;
+        if (d.head_dim == 128 && d.nb_head >= hb && all_aligned && d.n_rot % 4 == 0 && (!neox || d.n_rot == 128) && !getenv("B200_KSHIFT_GENERAL")) {
+            const size_t smem_fast = (((size_t) d.n_rot*4 + 15) & ~(size_t) 15) + (size_t) row_bytes(d.type_k, row_elems);
+#define KS_FAST(T) do { if (neox) k_shift_fast_kernel<T, true><<<grid, KVW_THREADS, smem_fast, stream>>>(a); \
+                        else      k_shift_fast_kernel<T, false><<<grid, KVW_THREADS, smem_fast, stream>>>(a); } while (0)
+            switch (d.type_k) {
+                case B200_TYPE_F32:  KS_FAST(B200_TYPE_F32);  break;
+                case B200_TYPE_F16:  KS_FAST(B200_TYPE_F16);  break;
+                case B200_TYPE_Q8_0: KS_FAST(B200_TYPE_Q8_0); break;
+                default:             KS_FAST(B200_TYPE_Q4_0); break;
+            }
+#undef KS_FAST
+            count_launch();
+            if (!check_launch("k_shift")) return B200_ERR_CUDA;
+            continue;
+        }
         switch (d.type_k) {
             case B200_TYPE_F32:  k_shift_kernel<B200_TYPE_F32 ><<<grid, KVW_THREADS, smem, stream>>>(a); break;
             case B200_TYPE_F16:  k_shift_kernel<B200_TYPE_F16 ><<<grid, KVW_THREADS, smem, stream>>>(a); break;

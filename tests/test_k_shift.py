@@ -280,6 +280,37 @@ def test_gpu_k_shift_matches_oracle_and_reference_vectors(pkg, oracle, cuda, gol
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("mode", [0, 2], ids=["norm", "neox"])
+@pytest.mark.parametrize("t", [F16, Q8_0, Q4_0])
+def test_gpu_k_shift_register_form_equals_general_form(pkg, oracle, cuda, t, mode):
+    """head_dim 128 runs on the register form (a lane = 4 elements, NEOX partners by shuffle, no F32 row in shared memory);
+    B200_KSHIFT_GENERAL=1 forces the general kernel: same arithmetic sequence, so the cache bytes must be identical"""
+    import os
+    import torch
+    rng = np.random.default_rng(50 + t)
+    n_cells, hkv, d, L = 96, 8, 128, 3
+    lay = pkg.KVLayout(t, hkv, d, 16, n_cells // 16)
+    base = [oracle.from_float(t, rng.uniform(-1, 1, (n_cells, hkv, d)).astype(np.float32)).reshape(-1) for _ in range(L)]
+    shift = rng.integers(-4000, 1, n_cells).astype(np.int32)
+    outs = []
+    for general in ("", "1"):
+        if general:
+            os.environ["B200_KSHIFT_GENERAL"] = general
+        else:
+            os.environ.pop("B200_KSHIFT_GENERAL", None)
+        try:
+            layers = [_dev(torch, b) for b in base]
+            pkg.k_shift(layers, lay, _dev(torch, shift), mode=mode, freq_base=500000.0)
+            torch.cuda.synchronize()
+            outs.append([c.cpu().numpy() for c in layers])
+        finally:
+            os.environ.pop("B200_KSHIFT_GENERAL", None)
+    for a, b, b0 in zip(outs[0], outs[1], base):
+        assert np.array_equal(a, b), "register form and general form disagree"
+        assert not np.array_equal(a, b0)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("t", [F16, Q8_0, Q4_0])
 def test_gpu_k_shift_cell_list_and_strided_heads(pkg, oracle, cuda, t):
     """only the listed cells change; zero shift leaves the bytes alone; Llama-3-8B row shape (8 kv heads)"""
