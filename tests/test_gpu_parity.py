@@ -139,6 +139,35 @@ def test_paged_decode(pkg, oracle, cuda, case, t, kernel):
     assert nm <= 5e-4
 
 
+KV_SHARD_CASES = [
+    # a KV-head shard of a GQA model (config 4 sharded over 8 / 4 / 2 GPUs): 1, 2 or 4 kv heads in the call
+    ([700, 64, 2049, 0, 33, 1], 8, 1, 128),          # one kv head, gqa 8: the 8 warps of a CTA are 8 stream-K items
+    ([9000, 300, 5000], 8, 2, 128),                  # two kv heads, gqa 4; rows long enough to span several CTAs
+    ([129, 4097, 16, 777], 32, 4, 128),              # four kv heads, gqa 8
+    ([40000], 8, 1, 128),                            # one long row over the whole machine
+]
+
+
+@pytest.mark.parametrize("t", TYPES)
+@pytest.mark.parametrize("case", KV_SHARD_CASES, ids=lambda c: f"{len(c[0])}x{max(c[0])}_h{c[1]}_{c[2]}")
+def test_paged_decode_kv_head_shard(pkg, oracle, cuda, case, t):
+    """fewer than 8 kv heads in the call (what one rank of the KV-head-sharded config 4 computes): the warps of a CTA are then
+    several stream-K items instead of the 8 heads of one; same bars as every other decode case, and agreement with the
+    CUDA-core kernel"""
+    import torch
+    seq_lens, n_head, n_head_kv, d = case
+    w = make_workload(oracle, seq_lens, n_head, n_head_kv, d, t, seed=77 + t)
+    got = _run_paged(pkg, torch, w, pkg.KERNEL_STREAMK)
+    want = oracle_attention(oracle, w)
+    live = np.array(seq_lens) > 0
+    assert np.isnan(got[~live]).all() and not np.isnan(got[live]).any()
+    err, nm = oracle.max_rel_err(want[live], got[live]), oracle.nmse(want[live], got[live])
+    assert err <= TOL[t], f"max rel err {err:.3e} (nmse {nm:.3e})"
+    assert nm <= 5e-4
+    gen = _run_paged(pkg, torch, w, pkg.KERNEL_GENERIC)
+    assert oracle.max_rel_err(gen[live], got[live]) <= 2e-3
+
+
 @pytest.mark.parametrize("kernel", [1, 2], ids=["generic", "streamk"])
 @pytest.mark.parametrize("t", [F16, Q4_0])
 def test_paged_decode_empty_sequences(pkg, oracle, cuda, t, kernel):
