@@ -27,4 +27,8 @@ ncu --set full --clock-control none --import-source on -k regex:pf_main -s 2 -c 
     python bench.py --workload config3 --layers 2 --steps 2 --no-graph > $O/${TAG}_ncu_pf.log 2>&1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $O/${TAG}_launches_config3.csv \
     python bench.py --workload config3 --layers 2 --steps 2 --no-graph > $O/${TAG}_ncu_list3.log 2>&1
+for WL in config1 config4_shard8; do   # the latency-bound ops: where the ~10 us of launch chain around 5 / 80 us of bytes go
+  ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $O/${TAG}_launches_$WL.csv \
+      python bench.py --workload $WL --layers 4 --steps 2 --warmup 3 --no-graph --no-cpu-baseline --no-e2e > $O/${TAG}_ncu_list_$WL.log 2>&1
+done
 ls -la $O | tail -15
