@@ -100,7 +100,7 @@ GGML_OP_CPY, GGML_OP_FLASH_ATTN_EXT, GGML_TYPE_I32 = 32, 62, 26
 EXPORTS = {
     "b200_paged_attn.h": [
         "b200_paged_attention_workspace", "b200_paged_attention", "b200_supports_attention", "b200_kv_write",
-        "b200_block_copy", "b200_kv_rows_gather", "b200_kv_rows_scatter", "b200_k_shift", "b200_decode_step",
+        "b200_block_copy", "b200_kv_rows_gather", "b200_kv_rows_scatter", "b200_k_shift", "b200_decode_step", "b200_store_attention",
         "b200_peer_alloc", "b200_peer_free", "b200_peer_export", "b200_peer_open", "b200_peer_close", "b200_peer_publish",
         "b200_peer_wait", "b200_peer_exchange", "b200_peer_exchange_ll", "b200_peer_read_state",
         "b200_static_workspace_bytes", "b200_paged_attention_static_ws", "b200_last_error", "b200_version", "b200_device_sm_count", "b200_launch_count"],
@@ -154,6 +154,8 @@ lib.b200_peer_read_state.restype = C.c_int
 lib.b200_peer_read_state.argtypes = [C.c_void_p, C.POINTER(C.c_uint32)]
 lib.b200_decode_step.restype = C.c_int
 lib.b200_decode_step.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]
+lib.b200_store_attention.restype = C.c_int
+lib.b200_store_attention.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
 lib.b200_last_error.restype = C.c_char_p
 lib.b200_version.restype = C.c_char_p
 lib.b200_device_sm_count.restype = C.c_int

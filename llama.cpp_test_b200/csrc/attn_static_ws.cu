@@ -23,7 +23,7 @@ namespace b200 {
 
 bool   streamk_supports(const b200_attn_desc &d);
 size_t streamk_workspace(const b200_attn_desc &d);
-int    launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st);
+int    launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st, const b200_kv_write_desc *store, bool store_checked, bool chained);
 
 static __device__ __align__(256) unsigned char g_static_ws[B200_STATIC_WS_BYTES];
 
@@ -96,7 +96,7 @@ B200_API int b200_paged_attention_static_ws(const b200_attn_desc *d, void *strea
     x.kernel = B200_KERNEL_STREAMK;
     x.workspace = ws;
     x.workspace_bytes = (size_t) B200_STATIC_WS_BYTES;
-    return launch_attn_streamk(x, static_cast<cudaStream_t>(stream));
+    return launch_attn_streamk(x, static_cast<cudaStream_t>(stream), nullptr, false, false);
 }
 
 } // extern "C"

@@ -47,6 +47,10 @@ namespace b200 {
 #endif
 constexpr int SK_WARPS = 8;
 constexpr int SK_MIN_CHUNK = 4;                              // tiles: a warp's share is never shorter (its prologue costs about two)
+#ifndef SK_F16_WARPS
+#define SK_F16_WARPS 8                                        // warps per CTA / ring stages of the kernels with an F16 operand
+#define SK_F16_STAGES 3
+#endif
 #ifndef SK_Q8_WARPS
 #define SK_Q8_WARPS 8                                         // warps per CTA of the Q8_0/Q8_0 kernel (8 = the three-stage form)
 #endif
@@ -59,7 +63,7 @@ struct sk_args {
     int    n_items;                     // upper bound on items per kv head
     int    chunk_align;                 // chunk is rounded up to a multiple of this many tiles (1)
     int    chunk_min;                   // and is at least this many tiles
-    int   *plan;                        // [4] {total_tiles, chunk, -, -} then P[n_q+1], FS[n_q+1]
+    int   *plan;                        // [4] {total_tiles, chunk, items, store slots checked} then P[n_q+1], FS[n_q+1]
     float *part_ml;                     // [max_segs][n_head][2]
     float *part_o;                      // [max_segs][n_head][D]
     float  qscale;                      // scale*log2(e), or scale/softcap when softcap != 0
@@ -71,6 +75,17 @@ struct sk_args {
     float  alibi_m0, alibi_m1; int n_head_log2;   // ALiBi slopes (ggml-cpu.c:12294-12298); max_bias in d
     int   *dense_len, *dense_bt, *dense_qseq;     // scan outputs: [n_q] visible cells (16 x listed tiles), [n_q][n_kv/16] tile ids, [n_q] zeros
     int    n_tiles;                     // n_kv / 16
+    // store overlap (launch_attn_streamk): the launch in front of the main kernel is this layer's kv_write of ONE new
+    // token per sequence.  The plan kernel checks that slot r is the cell of sequence r's last position (plan[3]);
+    // the main kernel then starts before that store has finished and waits for it only in front of a row's last tile.
+    int    after_store;
+    const int32_t *store_slots; int64_t store_cells;
+    // early prologue (decode_step, layers 1..): plan and block table were read by the previous layer's launch already, so
+    // this one reads them BEFORE it waits for its predecessor
+    int    early;
+    // arrivals: [n_q][n_head_kv] segment counters.  A main-kernel warp bumps its row's counter after its stores; the
+    // combine CTA of (row, kv head) spins on it instead of waiting for the whole main grid to drain, and zeroes it again
+    int   *arrive;
 };
 constexpr int SK_MIXED = 1 << 30;       // tile-list entry flag: some cell of the tile is hidden or carries a bias
 
@@ -97,8 +112,8 @@ struct sk_smem {
     // (29 % of the warp's time in that wait, profiles/r1q_sk_q8_0_ncu_full.txt).  Tiles up to 3584 bytes take a fourth
     // stage at 8 warps.  Q8_0 K with Q8_0 V (4608) only fits four stages with 6 warps per CTA (SK_Q8_WARPS=6, register
     // cap 168): measured equal to 8 warps x 3 stages (5229 vs 5256 GB/s), so 8 stays the default
-    static constexpr int WARPS = ANY16 || STAGE <= 3584 ? SK_WARPS : SK_Q8_WARPS;
-    static constexpr int STAGES = ANY16 ? (STAGE <= 2560 ? 4 : 3) : (STAGE <= 2560 ? 5 : (WARPS == SK_WARPS && STAGE > 3584 ? 3 : 4));
+    static constexpr int WARPS = ANY16 ? SK_F16_WARPS : STAGE <= 3584 ? SK_WARPS : SK_Q8_WARPS;
+    static constexpr int STAGES = ANY16 ? (STAGE <= 2560 ? 4 : SK_F16_STAGES) : (STAGE <= 2560 ? 5 : (WARPS == SK_WARPS && STAGE > 3584 ? 3 : 4));
     static constexpr int WARP = STAGE*STAGES;
     static constexpr int BAR_BYTES = ANY16 ? 1024 : 512;                          // mbarriers; F16 tiles must stay 1024-aligned
     static constexpr int META_OFF = WARPS*STAGES*8;                               // dense mode: one tile-list entry per ring slot, behind the barriers
@@ -251,6 +266,7 @@ sk_plan_kernel(const __grid_constant__ sk_args a) {
     pdl_prologue();
     const b200_attn_desc &p = a.d;
     int *P = a.plan + 4, *FS = P + (p.n_q + 1);
+    for (int64_t i = threadIdx.x; i < (int64_t) p.n_q*p.n_head_kv; i += 1024) a.arrive[i] = 0;
     int carry = 0;
     for (int r0 = 0; r0 < p.n_q; r0 += 1024) {
         const int r = r0 + threadIdx.x;
@@ -278,7 +294,19 @@ sk_plan_kernel(const __grid_constant__ sk_args a) {
         }
         if (best) chunk = best;
     }
-    if (threadIdx.x == 0) { P[p.n_q] = total; a.plan[0] = total; a.plan[1] = chunk; a.plan[2] = (total + chunk - 1)/chunk; a.plan[3] = 0; }
+    // store overlap: every stored row must land on the LAST visible cell of its own sequence (or be skipped by kv_write)
+    int slots_ok = 0;
+    if (a.after_store) {                                     // uniform; pure decode (row == sequence) by construction
+        int ok = 1;
+        for (int r = threadIdx.x; r < p.n_q; r += 1024) {
+            const int64_t slot = a.store_slots ? (int64_t) a.store_slots[r] : r;
+            if (slot < 0 || slot >= a.store_cells) continue;            // kv_write skips it
+            const int n = sk_row_nvis(p, r);
+            ok &= n > 0 && slot == (int64_t) p.block_table[(int64_t) r*p.bt_stride + (n - 1)/p.block_size]*p.block_size + (n - 1) % p.block_size;
+        }
+        slots_ok = __syncthreads_and(ok);
+    }
+    if (threadIdx.x == 0) { P[p.n_q] = total; a.plan[0] = total; a.plan[1] = chunk; a.plan[2] = (total + chunk - 1)/chunk; a.plan[3] = slots_ok; }
     __syncthreads();
     carry = 0;
     for (int r0 = 0; r0 < p.n_q; r0 += 1024) {
@@ -569,7 +597,17 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
     asm volatile("mov.b32 %0, %0;" : "+r"(lane));             // pin in a register: ptxas otherwise re-reads SR_TID in the loop
     const int warp = threadIdx.x >> 5;
     const int g = lane >> 2, t = lane & 3;
-    pdl_prologue();
+    TL_BEGIN(3, threadIdx.x == 0);        // s2 first TMA issue, s3 past the wait for the predecessor, s4 first tile consumed, s5 first row's loop end
+    // Where this grid waits for its predecessor, and when it lets the combine grid in (which spins on a.arrive and may
+    // only start once the PREVIOUS combine on this workspace has completed):
+    //   default      wait, then trigger, at the top
+    //   early        plan / block-table reads first, then wait + trigger in front of the first TMA issue
+    //   after_store  trigger at the top (the kv_write in front let this grid start only after its own predecessor had
+    //                completed: pdl_prologue_strict); nothing read before a row's last tile was written by that store,
+    //                so the wait stands in front of that tile only
+    bool waited = false;
+    if (!a.after_store && !a.early) { pdl_wait(); waited = true; TL_STAMP(3); }
+    if (waited || a.after_store) pdl_trigger();
 
     const int wid  = blockIdx.x*SM::WARPS + warp;
     const int item = wid / p.n_head_kv, kvh = wid - item*p.n_head_kv;
@@ -577,8 +615,9 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
     const int *P = a.plan + 4, *FS = P + (p.n_q + 1);
     const int head = lane < 4 + p.n_q + 1 ? a.plan[lane] : INT_MAX;
     const int total = __shfl_sync(0xffffffffu, head, 0), chunk = __shfl_sync(0xffffffffu, head, 1);
+    if (a.after_store && !waited && __shfl_sync(0xffffffffu, head, 3) == 0) { pdl_wait(); waited = true; TL_STAMP(3); }   // the plan could not vouch for the slots
     int g0 = item*chunk;
-    if (g0 >= total) return;
+    if (g0 >= total) { if (!waited) pdl_wait(); TL_END(); return; }
     const int g1 = min(g0 + chunk, total);
 
     // row containing global tile g0: last r with P[r] <= g0 (rows without tiles share P with their successor)
@@ -659,7 +698,11 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
         int win      = win_base + lane      < n_blk ? bt[win_base + lane]      : 0;
         int win_next = win_base + 32 + lane < n_blk ? bt[win_base + 32 + lane] : 0;
 
+        const int nt = t1 - t0;
+        int issued = 0;
+        const int t_new = (n_vis - 1)/SK_TILE - t0;         // the tile holding the row's newest cell, relative to t0
         auto issue = [&]() {                                // all lanes (shuffle); lane 0 talks to the TMA unit
+            if (!waited && issued >= t_new) { pdl_wait(); waited = true; TL_STAMP_ONCE(3); }   // the one tile the store in front of this launch wrote into
             if (b_cur - win_base >= 32) {
                 win_base += 32; win = win_next;
                 win_next = win_base + 32 + lane < n_blk ? bt[win_base + 32 + lane] : 0;
@@ -676,8 +719,8 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
             if (++is == STAGES) is = 0;
         };
 
-        const int nt = t1 - t0;
-        int issued = 0;
+        if (!waited && !a.after_store) { pdl_wait(); pdl_trigger(); waited = true; TL_STAMP(3); }      // early: the tables are here already
+        TL_STAMP_ONCE(2);
 #pragma unroll
         for (int s = 0; s < STAGES - NSUB; ++s) { if (issued < nt) { issue(); ++issued; } }
 
@@ -802,7 +845,10 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
             }
             if (fast) body(std::true_type{}, i);
             else      body(std::false_type{}, i);
+            TL_STAMP_ONCE(4);
         }
+        TL_STAMP_ONCE(5);
+        TL_EXTRA(nt);
 
         // ---- segment epilogue
 #pragma unroll
@@ -826,46 +872,60 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
             if (w0) { ml[0] = m0; ml[1] = l0; }
             if (w1) { ml[2] = m1; ml[3] = l1; }
         }
+        __threadfence();                                     // every lane's stores, device-wide, before the arrival
+        __syncwarp();
+        if (lane == 0) atomicAdd(a.arrive + (int64_t) row*p.n_head_kv + kvh, 1);
         g0 = pb + t1;
         ++row;
     }
+    if (!waited) pdl_wait();             // this grid's completion must imply the store's: the successor only waits for this grid
+    TL_END();
 }
 
-// merge the segments of split rows; one warp per (row, query head), log2-domain maxima
-__global__ void __launch_bounds__(128)
-sk_combine_kernel(const __grid_constant__ sk_args a) {
+// merge the segments of split rows; one CTA per (row, kv head), one warp per query head of it, log2-domain maxima.
+// The grid is let in while the main kernel runs (its trigger) and does not wait for that grid to drain: warp by warp it
+// spins on the row's arrival counter, which the main kernel's warps bump after their partials are stored and fenced
+// (the boundary "main grid complete -> griddepcontrol.wait returns" is ~1.4 us on a 10 us layer-op,
+// profiles/r2q_timeline_*).  No deadlock: the main grid triggers only from running CTAs, so all of them are resident
+// or done before this grid's first CTA starts.  Rows with one segment were written by the main kernel; their CTA
+// still sees the arrival, so this grid's completion implies every store of the main grid.
+__device__ __forceinline__ int sk_ld_acquire(const int *p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// one warp: the segments [s0, s0 + ns) of (row, head h) -> dst
+__device__ __forceinline__ void sk_merge_segments(const sk_args &a, int row, int h, int s0, int ns, int lane) {
     const b200_attn_desc &p = a.d;
-    pdl_prologue();
-    const int lane = threadIdx.x & 31;
-    const int64_t idx = (int64_t) blockIdx.x*4 + (threadIdx.x >> 5);
-    if (idx >= (int64_t) p.n_q*p.n_head) return;
-    const int row = (int) (idx / p.n_head), h = (int) (idx - (int64_t) row*p.n_head);
-    const int *FS = a.plan + 4 + (p.n_q + 1);
-    const int s0 = FS[row], ns = FS[row + 1] - s0;
-    if (ns == 1) return;                                              // written by the main kernel
     // Latency matters here, not bandwidth (a row has up to ~40 segments and the whole kernel moves a few hundred KB):
     // the segments' (m, l) are read lane-parallel (once for rows of up to 32 segments), the rescale factors travel by
-    // shuffle, and the O partials of sixteen segments are in flight at once: FS -> (m, l) -> O is three dependent
-    // round trips.  (One dependent global load per segment per pass cost 9 us of a 20 us layer-op.)
+    // shuffle, and the O partials of sixteen segments are in flight at once — the first sixteen requested together with
+    // the (m, l), in front of the first use of either: ONE L2 round trip for a row of up to 16 segments.  (One dependent
+    // global load per segment per pass cost 9 us of a 20 us layer-op.)
     const float2 *ML = reinterpret_cast<const float2 *>(a.part_ml) + (int64_t) s0*p.n_head + h;      // segment s at ML[s*n_head]
     const float  *PO = a.part_o + ((int64_t) s0*p.n_head + h)*SK_D + 4*lane;                         // segment s at PO + s*n_head*SK_D
-    const float2 ml0 = lane < ns ? ML[(int64_t) lane*p.n_head] : make_float2(-INFINITY, 0.f);       // kept for the first batch
+    const float2 ml0 = lane < ns ? __ldcg(ML + (int64_t) lane*p.n_head) : make_float2(-INFINITY, 0.f);   // kept for the first batch; .cg: written by other SMs during this grid
+    float4 v[16];
+#pragma unroll
+    for (int u = 0; u < 16; ++u) v[u] = ns > 0 ? __ldcg(reinterpret_cast<const float4 *>(PO + (int64_t) min(u, ns - 1)*p.n_head*SK_D)) : make_float4(0.f, 0.f, 0.f, 0.f);
     float M = ml0.x;
-    for (int s = lane + 32; s < ns; s += 32) M = fmaxf(M, ML[(int64_t) s*p.n_head].x);
+    for (int s = lane + 32; s < ns; s += 32) M = fmaxf(M, __ldcg(ML + (int64_t) s*p.n_head).x);
 #pragma unroll
     for (int o_ = 16; o_ > 0; o_ >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o_));
     float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
     float L = 0.f;
     for (int c = 0; c < ns; c += 32) {
         float f = 0.f;
-        if (c + lane < ns) { const float2 ml = c ? ML[(int64_t) (c + lane)*p.n_head] : ml0; f = ex2(ml.x - M); L = fmaf(ml.y, f, L); }
+        if (c + lane < ns) { const float2 ml = c ? __ldcg(ML + (int64_t) (c + lane)*p.n_head) : ml0; f = ex2(ml.x - M); L = fmaf(ml.y, f, L); }
         const int cnt = ns - c < 32 ? ns - c : 32;
         // branch-free batches of 16 partials in flight (one L2 round trip for a row of up to 16 segments): segments
         // past the end are clamped to a valid address and enter with the zero factor of their lane
         for (int j0 = 0; j0 < cnt; j0 += 16) {
-            float4 v[16];
+            if (c + j0 > 0) {
 #pragma unroll
-            for (int u = 0; u < 16; ++u) v[u] = *reinterpret_cast<const float4 *>(PO + (int64_t) min(c + j0 + u, ns - 1)*p.n_head*SK_D);
+                for (int u = 0; u < 16; ++u) v[u] = __ldcg(reinterpret_cast<const float4 *>(PO + (int64_t) min(c + j0 + u, ns - 1)*p.n_head*SK_D));
+            }
 #pragma unroll
             for (int u = 0; u < 16; ++u) {
                 const float fj = __shfl_sync(0xffffffffu, f, j0 + u);       // lanes >= cnt hold f == 0
@@ -878,6 +938,33 @@ sk_combine_kernel(const __grid_constant__ sk_args a) {
     const float inv = 1.0f/L;                                          // ns == 0: 0 * inf = NaN like the reference (ggml-cpu.c:12418)
     o.x *= inv; o.y *= inv; o.z *= inv; o.w *= inv;
     *reinterpret_cast<float4 *>(static_cast<float *>(p.dst) + ((int64_t) row*p.n_head + h)*SK_D + 4*lane) = o;
+}
+
+__global__ void __launch_bounds__(256)
+sk_combine_kernel(const __grid_constant__ sk_args a) {
+    const b200_attn_desc &p = a.d;
+    TL_BEGIN(4, threadIdx.x == 0);
+    pdl_trigger();
+    const int lane = threadIdx.x & 31;
+    const int row = (int) (blockIdx.x / p.n_head_kv), h = (int) (blockIdx.x - (unsigned) row*p.n_head_kv)*a.gqa + (threadIdx.x >> 5);
+    const int *FS = a.plan + 4 + (p.n_q + 1);
+    const int s0 = FS[row], ns = FS[row + 1] - s0;
+    int *arrived = a.arrive + blockIdx.x;
+    if (lane == 0) {
+        unsigned long long t0 = 0;
+        while (sk_ld_acquire(arrived) < ns) {
+            __nanosleep(32);
+            unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t0 == 0) t0 = t;
+            else if (t - t0 > 4000000000ull) __trap();                // 4 s: a lost arrival must fail loudly, not hang the device
+        }
+    }
+    __syncwarp();
+    TL_STAMP(2);
+    if (ns != 1) sk_merge_segments(a, row, h, s0, ns, lane);             // one segment: written by the main kernel
+    __syncthreads();                                                   // every warp of the CTA has seen the count
+    if (threadIdx.x == 0) *arrived = 0;                                  // ready for the next launch on this plan
+    TL_END();
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -956,8 +1043,8 @@ static size_t sk_dense_bytes(const b200_attn_desc &d) {
 
 size_t streamk_workspace(const b200_attn_desc &d) {
     const size_t max_segs = (size_t) sk_items(d) + d.n_q;
-    return sk_dense_bytes(d) + sk_align((4 + 2*((size_t) d.n_q + 1))*sizeof(int)) + sk_align(max_segs*d.n_head*2*sizeof(float))
-         + max_segs*d.n_head*SK_D*sizeof(float);
+    return sk_dense_bytes(d) + sk_align((4 + 2*((size_t) d.n_q + 1))*sizeof(int)) + sk_align((size_t) d.n_q*d.n_head_kv*sizeof(int))
+         + sk_align(max_segs*d.n_head*2*sizeof(float)) + max_segs*d.n_head*SK_D*sizeof(float);
 }
 
 typedef CUresult (*sk_encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
@@ -1016,12 +1103,19 @@ static int sk_launch(const sk_args &a, const CUtensorMap &tmK, const CUtensorMap
     return B200_OK;
 }
 
-int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st) {
+int launch_kv_write(const b200_kv_write_desc &d, cudaStream_t stream);          // kv_write.cu
+
+// store != NULL: this layer's kv_write, launched between the plan and the main kernel (the schedule does not depend on
+// it).  store_checked: with B200_ATTN_REUSE_PLAN, the plan in the workspace was computed with these very slots.
+// chained: b200_decode_step set B200_ATTN_REUSE_PLAN itself — the previous launch on this stream was the previous layer of
+// the same call, with this plan and these tables (sk_args::early).
+int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st, const b200_kv_write_desc *store, bool store_checked, bool chained) {
     const size_t need = streamk_workspace(d);
     if (d.workspace == nullptr || d.workspace_bytes < need) {
         set_error("attention: workspace of %zu bytes needed, %zu given", need, d.workspace_bytes);
         return B200_ERR_ALLOC;
     }
+    TL_ARM();
     sk_args a;
     a.d = d;
     a.gqa = d.n_head/d.n_head_kv;
@@ -1034,6 +1128,13 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st) {
     const bool dense = sk_dense(d);
     a.mask = nullptr; a.nb_mask1 = 0; a.alibi_m0 = a.alibi_m1 = 1.0f; a.n_head_log2 = 1;
     a.dense_len = a.dense_bt = a.dense_qseq = nullptr; a.n_tiles = 0;
+    const bool reuse = !dense && (d.flags & B200_ATTN_REUSE_PLAN);
+    // store overlap: ONE new token per sequence, row r == sequence r == stored row r (pure decode), launches chained by PDL
+    a.after_store = store && store->n_tokens > 0 && store->n_tokens == d.n_q && !dense && !d.q_seq && !d.q_pos
+                 && pdl_enabled() && (!reuse || store_checked) ? 1 : 0;
+    a.store_slots = a.after_store ? store->slot_mapping : nullptr;
+    a.store_cells = a.after_store ? store->n_cells : 0;
+    a.early = reuse && chained && pdl_enabled() ? 1 : 0;
     if (dense) {                                             // the tile lists stand in for block table / seq_lens / q_seq
         a.n_tiles    = (int) (d.n_kv/SK_TILE);
         a.dense_len  = reinterpret_cast<int *>(ws);
@@ -1050,6 +1151,8 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st) {
     }
     a.plan = reinterpret_cast<int *>(ws);
     ws += sk_align((4 + 2*((size_t) d.n_q + 1))*sizeof(int));
+    a.arrive = reinterpret_cast<int *>(ws);
+    ws += sk_align((size_t) d.n_q*d.n_head_kv*sizeof(int));
     a.part_ml = reinterpret_cast<float *>(ws);
     ws += sk_align(max_segs*d.n_head*2*sizeof(float));
     a.part_o = reinterpret_cast<float *>(ws);
@@ -1066,11 +1169,12 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st) {
         count_launch();
         if (!check_launch("sk_dense_scan")) return B200_ERR_CUDA;
     }
-    if (dense || !(d.flags & B200_ATTN_REUSE_PLAN)) {        // layers 1.. of a step run on layer 0's schedule
+    if (!reuse) {                                            // layers 1.. of a step run on layer 0's schedule
         launch_pdl(sk_plan_kernel, dim3(1), dim3(1024), 0, st, a);
         count_launch();
         if (!check_launch("sk_plan")) return B200_ERR_CUDA;
     }
+    if (store) { const int rc = launch_kv_write(*store, st); if (rc != B200_OK) return rc; }
     int rc;
     if (dense && d.mask) {                              // equal K/V types (streamk_supports)
         rc = d.type_k == B200_TYPE_F16  ? sk_launch<B200_TYPE_F16,  B200_TYPE_F16,  true>(a, tmK, tmV, st)
@@ -1082,8 +1186,7 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st) {
     if (rc != B200_OK) return rc;
     count_launch();
     if (!check_launch("sk_main")) return B200_ERR_CUDA;
-    const int64_t pairs = (int64_t) d.n_q*d.n_head;
-    launch_pdl(sk_combine_kernel, dim3((unsigned) ((pairs + 3)/4)), dim3(128), 0, st, a);
+    launch_pdl(sk_combine_kernel, dim3((unsigned) ((int64_t) d.n_q*d.n_head_kv)), dim3(32*a.gqa), 0, st, a);
     count_launch();
     if (!check_launch("sk_combine")) return B200_ERR_CUDA;
     return B200_OK;

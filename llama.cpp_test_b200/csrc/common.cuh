@@ -83,9 +83,19 @@ __device__ __forceinline__ void load_row_elems(const char *row, int e0, float (&
 // kv_write ...) lets its successor be scheduled at once (launch_dependents) and waits for its predecessor's memory
 // before touching global memory (wait), so launch latency and CTA ramp-up hide under the predecessor's tail instead of
 // adding ~1-2 us per kernel boundary to a 20 us layer-op (config 1).  Without the launch attribute both are no-ops.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait()    { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_prologue() {
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    asm volatile("griddepcontrol.wait;" ::: "memory");
+    pdl_trigger();
+    pdl_wait();
+}
+// The other order, for a kernel whose SUCCESSOR starts work before its own wait (kv_write in front of the stream-K
+// main kernel, attn_streamk.cu "store overlap"): the successor is scheduled only once this kernel's predecessor has
+// completed, so everything two or more launches back is finished and visible by the time the successor's first
+// instruction runs.
+__device__ __forceinline__ void pdl_prologue_strict() {
+    pdl_wait();
+    pdl_trigger();
 }
 
 bool pdl_enabled();                       // shim.cu: false when B200_NO_PDL=1
@@ -100,6 +110,50 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
     cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(std::forward<Args>(args))...);
 }
+
+// -DB200_TIMELINE (diagnosis builds only, profiles/run_timeline.sh; never the product library): thread 0 of the first
+// and last CTA of every kernel of the decode chain appends one record of %globaltimer stamps to a device buffer that
+// shim.cu writes out at exit.  Record: {kernel id | block << 8, entry, s2, s3, s4, s5, end, extra}.
+#ifdef B200_TIMELINE
+unsigned long long *timeline_buffer();                        // shim.cu: [0] = records so far, records from [8]
+constexpr unsigned long long TL_MAX = 1u << 16;
+static __device__ unsigned long long *tl_buf;                 // one per translation unit, armed by tl_arm()
+static inline void tl_arm() {
+    static bool done = false;
+    if (!done) { unsigned long long *p = timeline_buffer(); cudaMemcpyToSymbol(tl_buf, &p, sizeof p); done = true; }
+}
+struct tl_rec {
+    unsigned long long v[8]; bool on;
+    __device__ tl_rec(int id, bool thread_on) {
+        on = thread_on && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1) && blockIdx.y == 0;
+        for (int i = 0; i < 8; ++i) v[i] = 0;
+        v[0] = (unsigned long long) id | ((unsigned long long) blockIdx.x << 8);
+        stamp(1);
+    }
+    __device__ void stamp(int i) { if (on) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); v[i] = t; } }
+    __device__ void stamp_once(int i) { if (on && v[i] == 0) stamp(i); }
+    __device__ void flush() {
+        if (!on) return;
+        stamp(6);
+        const unsigned long long k = atomicAdd(tl_buf, 1ULL);
+        if (k < TL_MAX) for (int i = 0; i < 8; ++i) tl_buf[8 + 8*k + i] = v[i];
+        on = false;
+    }
+};
+#define TL_BEGIN(id, thread_on) tl_rec tl_((id), (thread_on))
+#define TL_STAMP(i)      tl_.stamp(i)
+#define TL_STAMP_ONCE(i) tl_.stamp_once(i)
+#define TL_EXTRA(x)      (tl_.v[7] = (unsigned long long) (x))
+#define TL_END()         tl_.flush()
+#define TL_ARM()         tl_arm()
+#else
+#define TL_BEGIN(id, thread_on) do { } while (0)
+#define TL_STAMP(i)      do { } while (0)
+#define TL_STAMP_ONCE(i) do { } while (0)
+#define TL_EXTRA(x)      do { } while (0)
+#define TL_END()         do { } while (0)
+#define TL_ARM()         do { } while (0)
+#endif
 
 // process-wide bookkeeping (defined in shim.cu)
 void set_error(const char *fmt, ...);

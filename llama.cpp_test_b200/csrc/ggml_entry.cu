@@ -164,8 +164,7 @@ B200_API int b200_flash_attn_ext(const struct b200_ggml_tensor *dst, void *works
     d.workspace = workspace; d.workspace_bytes = workspace_bytes;
     if (store.slot_mapping) {                                     // the fused KV store of a paged node, first
         if (!b200_supports_attention(&d)) { set_error("flash_attn_ext: unsupported shape/type"); return B200_ERR_UNSUPPORTED; }   // nothing is written for a node that cannot run
-        const int rc = b200_kv_write(&store, stream);
-        if (rc != B200_OK) return rc;
+        return b200_store_attention(&store, &d, stream);
     }
     return b200_paged_attention(&d, stream);
 }

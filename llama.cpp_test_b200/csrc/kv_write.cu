@@ -138,13 +138,15 @@ __device__ void write_row(const float *src, char *cache, int64_t cell, int n_hea
 __global__ void __launch_bounds__(KVW_THREADS)
 kv_write_kernel(const b200_kv_write_desc p) {
     extern __shared__ __align__(16) char stage[];
-    pdl_prologue();
+    TL_BEGIN(1, threadIdx.x == 0);
+    pdl_prologue_strict();                                            // the attention behind this store may start early (attn_streamk.cu)
+    TL_STAMP(2);
     const int64_t t = blockIdx.x;
     const int64_t cell = p.slot_mapping ? (int64_t) p.slot_mapping[t] : t;
-    if (cell < 0 || cell >= p.n_cells) return;                       // writeToCache skips invalid slots
+    if (cell < 0 || cell >= p.n_cells) { TL_END(); return; }         // writeToCache skips invalid slots
     const bool is_v = blockIdx.y == 1;
     const float *src = is_v ? p.v_src : p.k_src;
-    if (src == nullptr) return;
+    if (src == nullptr) { TL_END(); return; }
     src = reinterpret_cast<const float *>(reinterpret_cast<const char *>(src) + t*p.src_nb1);
     char *cache = static_cast<char *>(is_v ? p.v_cache : p.k_cache);
     const int type = is_v ? p.type_v : p.type_k;
@@ -155,6 +157,7 @@ kv_write_kernel(const b200_kv_write_desc p) {
         case B200_TYPE_Q8_0: write_row<B200_TYPE_Q8_0>(src, cache, cell, p.n_head_kv, p.head_dim, nbt, nbh, stage); break;
         default:             write_row<B200_TYPE_Q4_0>(src, cache, cell, p.n_head_kv, p.head_dim, nbt, nbh, stage); break;
     }
+    TL_END();
 }
 
 int launch_kv_write(const b200_kv_write_desc &d, cudaStream_t stream) {
@@ -164,6 +167,7 @@ int launch_kv_write(const b200_kv_write_desc &d, cudaStream_t stream) {
     const size_t smem = (size_t) (sk > sv ? sk : sv);
     if (smem > 48*1024) { set_error("kv_write: token row of %lld bytes exceeds 48 KiB staging", (long long) smem); return B200_ERR_UNSUPPORTED; }
     const dim3 grid((unsigned) d.n_tokens, 2);
+    TL_ARM();
     launch_pdl(kv_write_kernel, grid, dim3(KVW_THREADS), smem, stream, d);
     count_launch();
     return check_launch("kv_write") ? B200_OK : B200_ERR_CUDA;

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
+#include <vector>
 
 namespace b200 {
 
@@ -47,7 +48,7 @@ size_t generic_workspace(const b200_attn_desc &d);
 int    launch_attn_generic(const b200_attn_desc &d, cudaStream_t st);
 bool   streamk_supports(const b200_attn_desc &d);
 size_t streamk_workspace(const b200_attn_desc &d);
-int    launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st);
+int    launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st, const b200_kv_write_desc *store, bool store_checked, bool chained);
 bool   prefill_supports(const b200_attn_desc &d);
 size_t prefill_workspace(const b200_attn_desc &d);
 int    launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st);
@@ -89,6 +90,32 @@ static int pick_kernel(const b200_attn_desc &d) {
     return streamk_supports(d) ? B200_KERNEL_STREAMK : B200_KERNEL_GENERIC;
 }
 
+#ifdef B200_TIMELINE
+unsigned long long *timeline_buffer() {
+    static unsigned long long *buf = nullptr;
+    if (!buf) {
+        cudaMalloc(&buf, (8 + 8*TL_MAX)*sizeof(unsigned long long));
+        cudaMemset(buf, 0, (8 + 8*TL_MAX)*sizeof(unsigned long long));
+        atexit([] {
+            cudaDeviceSynchronize();
+            std::vector<unsigned long long> h(8 + 8*TL_MAX);
+            if (cudaMemcpy(h.data(), buf, h.size()*sizeof(unsigned long long), cudaMemcpyDeviceToHost) != cudaSuccess) return;
+            const char *path = getenv("B200_TIMELINE_OUT");
+            FILE *f = path ? fopen(path, "w") : stderr;
+            if (!f) return;
+            const unsigned long long n = h[0] < TL_MAX ? h[0] : TL_MAX;
+            fprintf(f, "# %llu records: kernel(1 kv_write 2 plan 3 main 4 combine) block entry s2 s3 s4 s5 end extra  (ns, absolute)\n", n);
+            for (unsigned long long k = 0; k < n; ++k) {
+                const unsigned long long *v = &h[8 + 8*k];
+                fprintf(f, "%llu %llu %llu %llu %llu %llu %llu %llu %llu\n", v[0] & 255, v[0] >> 8, v[1], v[2], v[3], v[4], v[5], v[6], v[7]);
+            }
+            if (path) fclose(f);
+        });
+    }
+    return buf;
+}
+#endif
+
 } // namespace b200
 
 using namespace b200;
@@ -128,10 +155,20 @@ B200_API size_t b200_paged_attention_workspace(const b200_attn_desc *d) {
     return a > c ? a : c;
 }
 
-B200_API int b200_paged_attention(const b200_attn_desc *d, void *stream) {
+static int validate_kv_write(const b200_kv_write_desc *d);
+
+// The attention of one layer, with that layer's KV store (or NULL) in front of it.  The stream-K path places the store
+// between its plan and main kernels and lets the main kernel start under it (attn_streamk.cu, "store overlap"); every
+// other kernel runs store, then attention.  store_checked, chained: see launch_attn_streamk.
+static int attention_with_store(const b200_attn_desc *d, const b200_kv_write_desc *store, bool store_checked, bool chained, void *stream) {
     const int rc = validate_attn(d);
     if (rc != B200_OK) return rc;
+    if (store) { const int rs = validate_kv_write(store); if (rs != B200_OK) return rs; }
     if (!have_device()) return B200_ERR_CUDA;
+    if (d->n_q == 0 || pick_kernel(*d) != B200_KERNEL_STREAMK || !streamk_supports(*d) || d->kernel == B200_KERNEL_STREAMK_DQ) {
+        if (store) { const int rs = launch_kv_write(*store, static_cast<cudaStream_t>(stream)); if (rs != B200_OK) return rs; }
+        store = nullptr;
+    }
     if (d->n_q == 0) return B200_OK;
     if (d->kernel == B200_KERNEL_STREAMK_DQ) { set_error("attention: kernel id 4 (tcgen05 decode formulation) was removed; use AUTO or STREAMK"); return B200_ERR_UNSUPPORTED; }
     const int k = pick_kernel(*d);
@@ -143,7 +180,7 @@ B200_API int b200_paged_attention(const b200_attn_desc *d, void *stream) {
         if (!streamk_supports(*d)) {
             set_error("attention: stream-K kernel does not take this shape"); return B200_ERR_UNSUPPORTED;
         }
-        return launch_attn_streamk(*d, static_cast<cudaStream_t>(stream));
+        return launch_attn_streamk(*d, static_cast<cudaStream_t>(stream), store, store_checked, chained);
     }
     if (!generic_supports(*d)) {
         set_error("attention: unsupported shape/type (head_dim %d, type_k %d, type_v %d)", d->head_dim, d->type_k, d->type_v);
@@ -152,7 +189,13 @@ B200_API int b200_paged_attention(const b200_attn_desc *d, void *stream) {
     return launch_attn_generic(*d, static_cast<cudaStream_t>(stream));
 }
 
-B200_API int b200_kv_write(const b200_kv_write_desc *d, void *stream) {
+B200_API int b200_paged_attention(const b200_attn_desc *d, void *stream) { return attention_with_store(d, nullptr, false, false, stream); }
+
+B200_API int b200_store_attention(const b200_kv_write_desc *store, const b200_attn_desc *d, void *stream) {
+    return attention_with_store(d, store, false, false, stream);
+}
+
+static int validate_kv_write(const b200_kv_write_desc *d) {
     if (!d) { set_error("kv_write: NULL descriptor"); return B200_ERR_INVALID; }
     if (d->n_tokens < 0 || d->n_head_kv <= 0 || d->head_dim <= 0) { set_error("kv_write: bad shape"); return B200_ERR_INVALID; }
     if ((d->k_src && !d->k_cache) || (d->v_src && !d->v_cache)) { set_error("kv_write: source without cache"); return B200_ERR_INVALID; }
@@ -160,6 +203,12 @@ B200_API int b200_kv_write(const b200_kv_write_desc *d, void *stream) {
     if (d->head_dim % QK) { set_error("kv_write: head_dim %d not a multiple of 32", d->head_dim); return B200_ERR_UNSUPPORTED; }
     if ((d->src_nb1 & 15) || ((uintptr_t) d->k_src & 15) || ((uintptr_t) d->v_src & 15)) { set_error("kv_write: source rows must be 16-byte aligned"); return B200_ERR_INVALID; }
     if ((d->nbk_token | d->nbk_head | d->nbv_token | d->nbv_head | (int64_t) (uintptr_t) d->k_cache | (int64_t) (uintptr_t) d->v_cache) & 1) { set_error("kv_write: cache strides must be even"); return B200_ERR_INVALID; }
+    return B200_OK;
+}
+
+B200_API int b200_kv_write(const b200_kv_write_desc *d, void *stream) {
+    const int rc = validate_kv_write(d);
+    if (rc != B200_OK) return rc;
     if (!have_device()) return B200_ERR_CUDA;
     return launch_kv_write(*d, static_cast<cudaStream_t>(stream));
 }
@@ -176,8 +225,9 @@ static bool same_plan_inputs(const b200_attn_desc &x, const b200_attn_desc &y) {
 
 B200_API int b200_decode_step(const b200_kv_write_desc *writes, const b200_attn_desc *attns, int32_t n_layers, void *stream) {
     if (n_layers < 0 || (n_layers > 0 && !attns)) { set_error("decode_step: bad arguments"); return B200_ERR_INVALID; }
+    const int32_t *planned_slots = nullptr; int64_t planned_tokens = -1, planned_cells = -1;   // the store the standing plan was checked against
     for (int32_t l = 0; l < n_layers; ++l) {
-        if (writes) { const int rc = b200_kv_write(&writes[l], stream); if (rc != B200_OK) return rc; }
+        const b200_kv_write_desc *w = writes ? &writes[l] : nullptr;
         int rc;
         // the schedule of layer l-1 stands only if layer l-1 really ran the stream-K plan kernel and layer l runs stream-K too:
         // pick_kernel also looks at pointers and strides (alignment), which same_plan_inputs does not compare
@@ -187,9 +237,11 @@ B200_API int b200_decode_step(const b200_kv_write_desc *writes, const b200_attn_
             && validate_attn(&attns[l]) == B200_OK && pick_kernel(attns[l]) == B200_KERNEL_STREAMK) {
             b200_attn_desc d = attns[l];                  // the schedule of layer l-1 stands: skip the plan launch
             d.flags |= B200_ATTN_REUSE_PLAN;
-            rc = b200_paged_attention(&d, stream);
+            rc = attention_with_store(&d, w, w && planned_tokens >= 0 && w->slot_mapping == planned_slots && w->n_tokens == planned_tokens && w->n_cells == planned_cells, true, stream);
         } else {
-            rc = b200_paged_attention(&attns[l], stream);
+            rc = attention_with_store(&attns[l], w, false, false, stream);
+            const bool planned = w && !(attns[l].flags & B200_ATTN_REUSE_PLAN);       // this call ran the plan kernel, with w's slots
+            planned_slots = planned ? w->slot_mapping : nullptr; planned_tokens = planned ? w->n_tokens : -1; planned_cells = planned ? w->n_cells : -1;
         }
         if (rc != B200_OK) return rc;
     }
