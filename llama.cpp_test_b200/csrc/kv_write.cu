@@ -134,28 +134,67 @@ __device__ void write_row(const float *src, char *cache, int64_t cell, int n_hea
     store_staged_row<TYPE>(stage, cache, cell, n_head_kv, head_dim, nb_token, nb_head);
 }
 
-// grid (n_tokens, 2): y == 0 writes K, y == 1 writes V
+// KVW_ROWS token rows of one CTA, every row's source loads (and slots) requested before the first is used: a CTA that
+// takes one row has one 4 KB load in flight, 8 CTAs per SM cover a third of the bytes HBM latency asks for
+// (config 3's 4096-token store ran at 0.59 of HBM that way).  Rows of up to 4*KVW_THREADS elements only.
+constexpr int KVW_ROWS = 4;
+
+template <int TYPE>
+__device__ __forceinline__ void write_rows(const b200_kv_write_desc &p, const float *src0, char *cache, int64_t t0, int64_t nbt, int64_t nbh, char *stage) {
+    const int row_elems = p.n_head_kv*p.head_dim;
+    const int lane = threadIdx.x & 31, e0 = 4*threadIdx.x;
+    const bool active = e0 < row_elems;
+    const int stage_row = (int) row_bytes(TYPE, row_elems);
+    float4 x[KVW_ROWS];
+    int64_t cell[KVW_ROWS];
+#pragma unroll
+    for (int r = 0; r < KVW_ROWS; ++r) {
+        const int64_t t = t0 + r;
+        const bool live = t < p.n_tokens;
+        x[r] = live && active ? *reinterpret_cast<const float4 *>(reinterpret_cast<const char *>(src0) + t*p.src_nb1 + 4*e0) : make_float4(0.f, 0.f, 0.f, 0.f);
+        cell[r] = !live ? -1 : p.slot_mapping ? (int64_t) p.slot_mapping[t] : t;
+    }
+#pragma unroll
+    for (int r = 0; r < KVW_ROWS; ++r) convert4<TYPE>(x[r], e0, stage + r*stage_row, lane, active);
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < KVW_ROWS; ++r)
+        if (cell[r] >= 0 && cell[r] < p.n_cells) store_staged_row<TYPE>(stage + r*stage_row, cache, cell[r], p.n_head_kv, p.head_dim, nbt, nbh);
+}
+
+// grid (ceil(n_tokens / rows), 2): y == 0 writes K, y == 1 writes V; ROWS == 1: one token per CTA, rows of any length
+template <int ROWS>
 __global__ void __launch_bounds__(KVW_THREADS)
 kv_write_kernel(const b200_kv_write_desc p) {
     extern __shared__ __align__(16) char stage[];
     TL_BEGIN(1, threadIdx.x == 0);
     pdl_prologue_strict();                                            // the attention behind this store may start early (attn_streamk.cu)
     TL_STAMP(2);
-    const int64_t t = blockIdx.x;
-    const int64_t cell = p.slot_mapping ? (int64_t) p.slot_mapping[t] : t;
-    if (cell < 0 || cell >= p.n_cells) { TL_END(); return; }         // writeToCache skips invalid slots
     const bool is_v = blockIdx.y == 1;
     const float *src = is_v ? p.v_src : p.k_src;
     if (src == nullptr) { TL_END(); return; }
-    src = reinterpret_cast<const float *>(reinterpret_cast<const char *>(src) + t*p.src_nb1);
     char *cache = static_cast<char *>(is_v ? p.v_cache : p.k_cache);
     const int type = is_v ? p.type_v : p.type_k;
     const int64_t nbt = is_v ? p.nbv_token : p.nbk_token, nbh = is_v ? p.nbv_head : p.nbk_head;
-    switch (type) {
-        case B200_TYPE_F32:  write_row<B200_TYPE_F32 >(src, cache, cell, p.n_head_kv, p.head_dim, nbt, nbh, stage); break;
-        case B200_TYPE_F16:  write_row<B200_TYPE_F16 >(src, cache, cell, p.n_head_kv, p.head_dim, nbt, nbh, stage); break;
-        case B200_TYPE_Q8_0: write_row<B200_TYPE_Q8_0>(src, cache, cell, p.n_head_kv, p.head_dim, nbt, nbh, stage); break;
-        default:             write_row<B200_TYPE_Q4_0>(src, cache, cell, p.n_head_kv, p.head_dim, nbt, nbh, stage); break;
+    if constexpr (ROWS > 1) {
+        const int64_t t0 = (int64_t) blockIdx.x*ROWS;
+        switch (type) {
+            case B200_TYPE_F32:  write_rows<B200_TYPE_F32 >(p, src, cache, t0, nbt, nbh, stage); break;
+            case B200_TYPE_F16:  write_rows<B200_TYPE_F16 >(p, src, cache, t0, nbt, nbh, stage); break;
+            case B200_TYPE_Q8_0: write_rows<B200_TYPE_Q8_0>(p, src, cache, t0, nbt, nbh, stage); break;
+            default:             write_rows<B200_TYPE_Q4_0>(p, src, cache, t0, nbt, nbh, stage); break;
+        }
+    } else {
+        const int64_t t = blockIdx.x;
+        const int64_t cell = p.slot_mapping ? (int64_t) p.slot_mapping[t] : t;
+        if (cell < 0 || cell >= p.n_cells) { TL_END(); return; }     // writeToCache skips invalid slots
+        src = reinterpret_cast<const float *>(reinterpret_cast<const char *>(src) + t*p.src_nb1);
+        switch (type) {
+            case B200_TYPE_F32:  write_row<B200_TYPE_F32 >(src, cache, cell, p.n_head_kv, p.head_dim, nbt, nbh, stage); break;
+            case B200_TYPE_F16:  write_row<B200_TYPE_F16 >(src, cache, cell, p.n_head_kv, p.head_dim, nbt, nbh, stage); break;
+            case B200_TYPE_Q8_0: write_row<B200_TYPE_Q8_0>(src, cache, cell, p.n_head_kv, p.head_dim, nbt, nbh, stage); break;
+            default:             write_row<B200_TYPE_Q4_0>(src, cache, cell, p.n_head_kv, p.head_dim, nbt, nbh, stage); break;
+        }
     }
     TL_END();
 }
@@ -166,9 +205,17 @@ int launch_kv_write(const b200_kv_write_desc &d, cudaStream_t stream) {
     const int64_t sk = row_bytes(d.type_k, row_elems), sv = row_bytes(d.type_v, row_elems);
     const size_t smem = (size_t) (sk > sv ? sk : sv);
     if (smem > 48*1024) { set_error("kv_write: token row of %lld bytes exceeds 48 KiB staging", (long long) smem); return B200_ERR_UNSUPPORTED; }
-    const dim3 grid((unsigned) d.n_tokens, 2);
     TL_ARM();
-    launch_pdl(kv_write_kernel, grid, dim3(KVW_THREADS), smem, stream, d);
+    // several rows per CTA once one-row CTAs would no longer be resident all at once (8 per SM); decode-sized stores keep one
+    static int sms = 0;
+    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
+    if (row_elems <= 4*KVW_THREADS && 2*d.n_tokens > 8*(int64_t) sms && smem*KVW_ROWS <= 48*1024) {
+        const dim3 grid((unsigned) ((d.n_tokens + KVW_ROWS - 1)/KVW_ROWS), 2);
+        launch_pdl(kv_write_kernel<KVW_ROWS>, grid, dim3(KVW_THREADS), smem*KVW_ROWS, stream, d);
+    } else {
+        const dim3 grid((unsigned) d.n_tokens, 2);
+        launch_pdl(kv_write_kernel<1>, grid, dim3(KVW_THREADS), smem, stream, d);
+    }
     count_launch();
     return check_launch("kv_write") ? B200_OK : B200_ERR_CUDA;
 }

@@ -70,6 +70,35 @@ def test_kv_write_bit_exact(pkg, oracle, cuda, t, shape):
         assert np.array_equal(got, want), f"{int((got != want).sum())} bytes differ"
 
 
+@pytest.mark.parametrize("t", [F32, F16, Q8_0, Q4_0])
+@pytest.mark.parametrize("shape", [(8, 128), (4, 64)])
+def test_kv_write_many_rows_bit_exact(pkg, oracle, cuda, t, shape):
+    """a prefill-sized store (more one-row CTAs than fit the machine at once) takes the several-rows-per-CTA form of the
+    kernel: a token count that is not a multiple of its row group, skipped slots inside a group"""
+    import torch
+    n_head_kv, d = shape
+    rng = np.random.default_rng(300 + t)
+    n_tokens, n_cells = 1501, 2048
+    src_k = rng.uniform(-1, 1, (n_tokens, n_head_kv * d)).astype(np.float32)
+    src_v = rng.standard_normal((n_tokens, n_head_kv * d)).astype(np.float32) * 3
+    src_k[4, :32] = 0.0
+    src_k[5, 7] = 6.0e4
+    slot = rng.permutation(n_cells)[:n_tokens].astype(np.int32)
+    slot[6] = -1
+    slot[1499] = n_cells + 9
+    slot[1500] = 3 if 3 not in slot[:1500] else slot[1500]
+    lay = pkg.KVLayout(t, n_head_kv, d, 16, n_cells // 16)
+    kc = torch.full((lay.total_bytes,), 0x5a, dtype=torch.uint8, device=cuda)
+    vc = torch.full((lay.total_bytes,), 0x5a, dtype=torch.uint8, device=cuda)
+    pkg.kv_write(_dev(torch, src_k), _dev(torch, src_v), _dev(torch, slot), kc, vc, lay)
+    torch.cuda.synchronize()
+    for src, dev in ((src_k, kc), (src_v, vc)):
+        want = np.full((n_cells, lay.token_bytes), 0x5a, dtype=np.uint8)
+        oracle.kv_write(src, slot, want, t, n_head_kv, d, lay.token_bytes, lay.head_bytes, n_cells)
+        got = dev.cpu().numpy().reshape(n_cells, lay.token_bytes)
+        assert np.array_equal(got, want), f"{int((got != want).sum())} bytes differ"
+
+
 def test_kv_write_mixed_types_and_strided_heads(pkg, oracle, cuda):
     """type_k != type_v (-ctk q8_0 -ctv f16) and a head stride wider than the row (generic store path)"""
     import torch
