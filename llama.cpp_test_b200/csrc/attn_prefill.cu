@@ -46,6 +46,14 @@ constexpr int PF_SK      = 65536;        // after Q [2 groups][2 d-halves][128 r
 constexpr int PF_SV      = PF_SK + PF_KST*16384;   // V stage s at + s*16384, same layout
 constexpr int PF_SBAR    = PF_SV + PF_VST*16384;
 constexpr int PF_SMEM    = PF_SBAR + 256;
+// KV split of the tail: when the work items do not fill the last wave of the persistent grid (n_work % grid != 0, or
+// fewer items than SMs: ONE sequence's 512-token chunk is 16 items), each of the leftover items is cut into up to
+// PF_MAX_SPLIT pieces of consecutive kv tiles so that the pieces fill the machine; a piece leaves (m, l, unnormalised O)
+// per row in the workspace and pf_combine_kernel merges them.  Pieces are never shorter than PF_MIN_PIECE tiles.
+#ifndef PF_SPLIT_MAX
+#define PF_SPLIT_MAX 8
+#endif
+constexpr int PF_MAX_SPLIT = PF_SPLIT_MAX, PF_MIN_PIECE = 4;
 
 // mbarriers: SFULL[group][S buffer], PFULL[group][P buffer] (128 arrivals; the softmax may be a tile ahead of the MMA warp), ODONE[group]
 enum { PF_FULLK = 0, PF_FULLV = 4, PF_EMPTYK = 7, PF_EMPTYV = 11, PF_SFULL = 14, PF_PFULL = 18, PF_ODONE = 22, PF_NBAR = 24 };
@@ -61,6 +69,8 @@ struct pf_args {
     __half *k16, *v16;                   // [scratch_cells][n_head_kv][128]
     int64_t scratch_cells;
     int64_t cap;                         // upper bound applied to every seq_lens entry (block-table capacity, or max_seq_len)
+    float  *part_o, *part_ml;            // KV-split pieces: [grid_main][256 rows][128], [grid_main][256 rows][2] {m (log2 domain), l}
+    int     grid_main;                   // CTAs of pf_main_kernel (the combine kernel derives the same split from it)
 #ifdef PF_TIMELINE
     long long *dbg;                      // debug builds only: clock64 stamps of CTA 0's first work item, [3 warps][64 tiles][8]
 #endif
@@ -334,6 +344,24 @@ pf_dequant_kernel(const __grid_constant__ pf_args a) {
     }
 }
 
+// which work items are split, and how: everything follows from the item count and the grid, so the main and the
+// combine kernel agree without a table.  Units [0, full) are whole items; unit full + j is piece j % k of item full + j / k.
+struct pf_split { int full, rem, k, n_units; };
+__device__ __forceinline__ pf_split pf_split_of(int n_work, int grid) {
+    pf_split sp;
+    sp.rem = n_work % grid; sp.full = n_work - sp.rem;
+    sp.k = sp.rem ? grid/sp.rem : 1;
+    if (sp.k > PF_MAX_SPLIT) sp.k = PF_MAX_SPLIT;
+    sp.n_units = sp.full + sp.rem*sp.k;
+    return sp;
+}
+// tiles [ta, tb) of piece `piece` of an item with nkt kv tiles
+__device__ __forceinline__ void pf_piece_range(int nkt, int k, int piece, int &ta, int &tb) {
+    int ke = nkt/PF_MIN_PIECE; ke = ke < 1 ? 1 : (ke > k ? k : ke);      // pieces this item really has
+    if (piece >= ke) { ta = tb = 0; return; }
+    ta = (int) ((int64_t) nkt*piece/ke); tb = (int) ((int64_t) nkt*(piece + 1)/ke);
+}
+
 // ------------------------------------------------------------------------------------------------
 // main kernel: one CTA per SM, TWO 128-row groups (A = rows 0..127, B = 128..255 of a 256-row work item) share every
 // K/V tile, so K/V cross L2 -> shared memory once per 256 rows, and the tensor pipe works on one group while the
@@ -348,6 +376,7 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
     volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(pf_dyn + PF_SBAR + 208);
     volatile int      *work_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 212);
     volatile int      *nvis_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 216);   // [8] per-warp max n_vis
+    volatile int      *part_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 248);   // piece slot of the current unit or -1 (kept out of the softmax warps' registers)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     pdl_prologue();
 
@@ -374,9 +403,14 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
     for (;;) {
         if (threadIdx.x == 0) *work_slot = atomicAdd(&a.plan[1], 1);
         __syncthreads();
-        const int w = *work_slot;
+        const int unit = *work_slot;
         const int n_tiles = a.plan[0];
-        if (w >= n_tiles*p.n_head_kv) break;
+        const pf_split sp = pf_split_of(n_tiles*p.n_head_kv, (int) gridDim.x);
+        if (unit >= sp.n_units) break;
+        const int pidx = unit - sp.full;                     // >= 0: a piece (slot in the partial buffers)
+        const int w = pidx < 0 ? unit : sp.full + pidx/sp.k, piece = pidx < 0 ? 0 : pidx % sp.k;
+        const bool split = pidx >= 0 && sp.k > 1;
+        if (threadIdx.x == 0) *part_slot = split ? pidx : -1;       // read back in the epilogue, behind the __syncthreads below
         const int tile = n_tiles - 1 - w/p.n_head_kv, kvh = w % p.n_head_kv;      // later rows (longer contexts) first
         const int row0 = tile_row0[tile], nrows = tile_rows[tile];
         const bool useB = nrows > tokA;                      // group B has live rows
@@ -418,7 +452,9 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
         int nvis_max = 0;
 #pragma unroll
         for (int i = 0; i < 8; ++i) nvis_max = max(nvis_max, nvis_slot[i]);
-        const int nkt = (nvis_max + PF_BN - 1)/PF_BN;
+        // kv tiles [ta, ta + nkt) of this unit: all of the item's, or one piece of them
+        int ta = 0, nkt = (nvis_max + PF_BN - 1)/PF_BN;
+        if (split) { int tb; pf_piece_range(nkt, sp.k, piece, ta, tb); nkt = tb - ta; }
 
         if (warp == PF_TMA_WARP) {
             // ================= TMA producer =================
@@ -428,11 +464,11 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
             // (the whole warp takes part, one elected lane talks to the TMA unit).
             const int dense_base = a.seq_off ? a.seq_off[seq] : -1;       // F16 scratch of a quantised cache: cells are sequence-local
             const int kc0 = a.seq_off ? kvh*PF_D : (int) ((int64_t) kvh*p.nbk2/2), vc0 = a.seq_off ? kvh*PF_D : (int) ((int64_t) kvh*p.nbv2/2);
-            int win_base = 0;
-            int win      = lane < n_blk ? bt[lane] : 0;
-            int win_next = 32 + lane < n_blk ? bt[32 + lane] : 0;
             const int tpb = bs/16;                           // 16-cell boxes per block
-            int b_cur = 0, o_cur = 0;
+            int b_cur = ta*(PF_BN/16)/tpb, o_cur = ta*(PF_BN/16) - b_cur*tpb;
+            int win_base = b_cur;
+            int win      = win_base + lane < n_blk ? bt[win_base + lane] : 0;
+            int win_next = win_base + 32 + lane < n_blk ? bt[win_base + 32 + lane] : 0;
             int cell[4], vcell[4] = {0, 0, 0, 0};
             for (int t = 0; t <= nkt; ++t) {
                 if (t < nkt) {
@@ -444,7 +480,7 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                         }
                         cell[i] = __shfl_sync(0xffffffffu, win, b_cur - win_base)*bs + o_cur*16;
                         if (++o_cur == tpb) { o_cur = 0; ++b_cur; }
-                        if (dense_base >= 0) cell[i] = dense_base + t*PF_BN + 16*i;
+                        if (dense_base >= 0) cell[i] = dense_base + (ta + t)*PF_BN + 16*i;
                     }
                     const uint32_t g = G + t, st = g % PF_KST, sk = sK + st*16384, bk = sBar + 8*(PF_FULLK + st);
                     if (lane == 0) {
@@ -529,7 +565,7 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                 pf_tmem_ld32(tS + (g & 1)*64 + lane_base + 32, v, 32);
                 pf_tmem_wait_ld();
                 PF_T(grp, j, 2);
-                const int tok0 = j*PF_BN;
+                const int tok0 = (ta + j)*PF_BN;
                 float mx = -INFINITY, mx2 = -INFINITY;
                 if (tok0 + PF_BN > nvis_min) {               // warp-uniform: only tiles that cross some row's limit mask
 #pragma unroll
@@ -589,13 +625,17 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                 pf_mbar_arrive(sBar + 8*(PF_PFULL + 2*grp + (g & 1)));
                 PF_T(grp, j, 6);
             }
-            // ---- epilogue: O / l -> dst[row][head][d]
+            // ---- epilogue: O / l -> dst[row][head][d]; a piece: (m, l) and the unnormalised O -> its slot of the partial buffers
             const bool live = tl < nrows;
-            float *out = static_cast<float *>(p.dst) + ((int64_t) (row0 + (live ? tl : 0))*p.n_head + kvh*gqa + hg)*PF_D;
+            const int pslot = *part_slot;
+            const bool is_piece = pslot >= 0;
+            float *out = is_piece ? a.part_o + ((int64_t) pslot*2*PF_ROWS + R)*PF_D
+                                  : static_cast<float *>(p.dst) + ((int64_t) (row0 + (live ? tl : 0))*p.n_head + kvh*gqa + hg)*PF_D;
+            if (is_piece) *reinterpret_cast<float2 *>(a.part_ml + ((int64_t) pslot*2*PF_ROWS + R)*2) = make_float2(nkt > 0 ? m_run : -INFINITY, nkt > 0 ? l_run : 0.f);
             if (nkt > 0) {
                 pf_mbar_wait(sBar + 8*(PF_ODONE + grp), (Gg + nkt - 1) & 1);
                 pf_tc_fence_after();
-                const float inv = 1.0f/l_run;
+                const float inv = is_piece ? 1.0f : 1.0f/l_run;
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     pf_tmem_ld32(tO + lane_base + 64*h,      v, 0);
@@ -608,7 +648,7 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                                                                                       __uint_as_float(v[c + 2])*inv, __uint_as_float(v[c + 3])*inv);
                     }
                 }
-            } else if (live) {
+            } else if (live && !is_piece) {
                 const float nan = __int_as_float(0x7fc00000);                     // no visible cell: 0/0 like the reference (ggml-cpu.c:12418)
                 for (int c = 0; c < PF_D; c += 4) *reinterpret_cast<float4 *>(out + c) = make_float4(nan, nan, nan, nan);
             }
@@ -622,6 +662,50 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
     pf_tc_fence_before();
     __syncthreads();
     if (warp == PF_MMA_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(tmem) : "memory");
+}
+
+// merge the pieces of the split items: CTA (b, y) = rows 8y .. 8y+7 of split item b (the b-th of the last `rem` work
+// items), one warp per row, a lane per 4 of the 128 output dims: every row's (m, l) and O loads are one round trip, all
+// rows in flight at once (32 rows per warp in sequence made this kernel ~55 us of an 83 us op).  Exits at once when
+// nothing was split.
+__global__ void __launch_bounds__(256)
+pf_combine_kernel(const __grid_constant__ pf_args a) {
+    const b200_attn_desc &p = a.d;
+    const int n_tiles = a.plan[0];
+    const pf_split sp = pf_split_of(n_tiles*p.n_head_kv, a.grid_main);
+    if (sp.k <= 1 || (int) blockIdx.x >= sp.rem) return;
+    const int w = sp.full + blockIdx.x;
+    const int tile = n_tiles - 1 - w/p.n_head_kv, kvh = w % p.n_head_kv;
+    const int *tile_row0 = a.plan + 2, *tile_rows = tile_row0 + p.n_q;
+    const int row0 = tile_row0[tile], nrows = tile_rows[tile];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t slot0 = (int64_t) blockIdx.x*sp.k;        // first piece slot of this item
+    {
+        const int R = blockIdx.y*8 + warp;
+        const int tl = R/a.gqa, hg = R - tl*a.gqa;
+        if (tl >= nrows) return;
+        const float2 ml = lane < sp.k ? *reinterpret_cast<const float2 *>(a.part_ml + ((slot0 + lane)*2*PF_ROWS + R)*2) : make_float2(-INFINITY, 0.f);
+        float4 v[PF_MAX_SPLIT];
+#pragma unroll
+        for (int i = 0; i < PF_MAX_SPLIT; ++i)
+            v[i] = i < sp.k ? *reinterpret_cast<const float4 *>(a.part_o + ((slot0 + i)*2*PF_ROWS + R)*PF_D + 4*lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+        float M = ml.x;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
+        const float f = ml.x == -INFINITY ? 0.f : pf_ex2(ml.x - M);      // empty pieces (and their unwritten O) drop out
+        float L = ml.y*f;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) L += __shfl_xor_sync(0xffffffffu, L, o);
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int i = 0; i < PF_MAX_SPLIT; ++i) {
+            const float fi = __shfl_sync(0xffffffffu, f, i);
+            if (fi != 0.f) { acc.x = fmaf(v[i].x, fi, acc.x); acc.y = fmaf(v[i].y, fi, acc.y); acc.z = fmaf(v[i].z, fi, acc.z); acc.w = fmaf(v[i].w, fi, acc.w); }
+        }
+        const float inv = 1.0f/L;                             // no visible cell at all: 0 * inf = NaN like the reference (ggml-cpu.c:12418)
+        acc.x *= inv; acc.y *= inv; acc.z *= inv; acc.w *= inv;
+        *reinterpret_cast<float4 *>(static_cast<float *>(p.dst) + ((int64_t) (row0 + tl)*p.n_head + kvh*a.gqa + hg)*PF_D + 4*lane) = acc;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -678,8 +762,20 @@ bool prefill_supports(const b200_attn_desc &d) {
 static size_t pf_align(size_t x) { return (x + 1023) & ~(size_t) 1023; }
 static size_t pf_plan_bytes(const b200_attn_desc &d) { return pf_align((2 + 2*(size_t) d.n_q + (size_t) d.n_seqs + 1)*sizeof(int)); }
 
+static int pf_sm_count() {
+    static int sms = 0;
+    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
+    return sms;
+}
+static int64_t pf_grid(const b200_attn_desc &d) {             // persistent grid: one CTA per SM, never more than work items can exist
+    const int64_t items = (int64_t) d.n_q*d.n_head_kv;        // upper bound (one row per tile)
+    return items < pf_sm_count() ? items : pf_sm_count();
+}
+static size_t pf_part_o_bytes(const b200_attn_desc &d)  { return pf_align((size_t) pf_grid(d)*2*PF_ROWS*PF_D*sizeof(float)); }   // pieces <= grid
+static size_t pf_part_ml_bytes(const b200_attn_desc &d) { return pf_align((size_t) pf_grid(d)*2*PF_ROWS*2*sizeof(float)); }
+
 size_t prefill_workspace(const b200_attn_desc &d) {
-    size_t n = pf_plan_bytes(d);
+    size_t n = pf_plan_bytes(d) + pf_part_o_bytes(d) + pf_part_ml_bytes(d);
     if (pf_needs_scratch(d)) n += 2*pf_align((size_t) pf_scratch_cells(d)*d.n_head_kv*PF_D*2);
     return n;
 }
@@ -720,13 +816,16 @@ int launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st) {
     a.cap = d.bt_stride*d.block_size;
     if (scratch && d.max_seq_len > 0 && d.max_seq_len < a.cap) a.cap = d.max_seq_len;
     a.seq_off = nullptr; a.k16 = a.v16 = nullptr; a.scratch_cells = 0;
+    char *ws = static_cast<char *>(d.workspace) + pf_plan_bytes(d);
+    a.part_o = reinterpret_cast<float *>(ws);  ws += pf_part_o_bytes(d);
+    a.part_ml = reinterpret_cast<float *>(ws); ws += pf_part_ml_bytes(d);
+    a.grid_main = (int) pf_grid(d);
     if (scratch) {
-        char *ws = static_cast<char *>(d.workspace);
         a.seq_off = a.plan + 2 + 2*(size_t) d.n_q;
         a.scratch_cells = pf_scratch_cells(d);
         const size_t tb = pf_align((size_t) a.scratch_cells*d.n_head_kv*PF_D*2);
-        a.k16 = reinterpret_cast<__half *>(ws + pf_plan_bytes(d));
-        a.v16 = reinterpret_cast<__half *>(ws + pf_plan_bytes(d) + tb);
+        a.k16 = reinterpret_cast<__half *>(ws);
+        a.v16 = reinterpret_cast<__half *>(ws + tb);
     }
     alignas(64) CUtensorMap tmK, tmV;
     if (scratch) {
@@ -740,10 +839,7 @@ int launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st) {
     pf_plan_kernel<<<1, 1024, 0, st>>>(a);
     count_launch();
     if (!check_launch("pf_plan")) return B200_ERR_CUDA;
-    int dev = 0, sms = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (sms <= 0) sms = 148;
+    const int sms = pf_sm_count();
     if (scratch) {
         int64_t g = a.scratch_cells/16;
         if (g > 8*sms) g = 8*sms;
@@ -752,8 +848,7 @@ int launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st) {
         count_launch();
         if (!check_launch("pf_dequant")) return B200_ERR_CUDA;
     }
-    int64_t grid = (int64_t) d.n_q*d.n_head_kv;              // upper bound on work items (one row per tile)
-    if (grid > sms) grid = sms;
+    const int64_t grid = a.grid_main;
 #ifdef PF_TIMELINE
     cudaMalloc(&a.dbg, 3*64*8*sizeof(long long)); cudaMemset(a.dbg, 0, 3*64*8*sizeof(long long));
 #endif
@@ -778,6 +873,9 @@ int launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st) {
 #endif
     count_launch();
     if (!check_launch("pf_main")) return B200_ERR_CUDA;
+    pf_combine_kernel<<<dim3((unsigned) grid, 2*PF_ROWS/8), 256, 0, st>>>(a);   // the split items' pieces -> dst (returns at once when nothing was split)
+    count_launch();
+    if (!check_launch("pf_combine")) return B200_ERR_CUDA;
     return B200_OK;
 }
 

@@ -27,6 +27,12 @@ CASES = {
     "block32":            ([513, 64], 8, 2, _chunk(0, 385, 513) + _chunk(1, 0, 64), 32),
     "chunk512_ctx2k":     ([2048, 700], 32, 8, _chunk(0, 1536, 2048) + _chunk(1, 188, 700), 16),   # config-3 shape, 2 sequences
     "not_causal_limit":   ([150], 8, 2, [(0, 149)] * 40, 16),                          # q_pos beyond: every row sees all 150
+    # KV split of the tail items (fewer work items than SMs, or a last wave that is not full): pieces + pf_combine_kernel
+    "one_seq_chunk512_ctx4k": ([4096], 32, 8, _chunk(0, 3584, 4096), 16),             # 16 items -> 8 pieces of 8 kv tiles each
+    "one_seq_first_chunk512": ([512], 32, 8, _chunk(0, 0, 512), 16),                  # early rows see nothing of the later pieces
+    # 80 one-row tiles x 2 kv heads = 160 items: 148 whole ones + the 12 of the six long sequences (first in row order = last
+    # in work order), each cut into 4 pieces
+    "tail_wave_160_items":    ([1200]*6 + [40 + 3*i for i in range(74)], 8, 2, [(s, 1199) for s in range(6)] + [(6 + i, 39 + 3*i) for i in range(74)], 16),
 }
 
 
@@ -44,7 +50,7 @@ def test_prefill_tile_kernel(pkg, oracle, cuda, name):
 
 
 @pytest.mark.parametrize("tk,tv", [(Q8_0, Q8_0), (Q4_0, Q4_0), (Q8_0, F16), (F16, Q4_0)], ids=["q8", "q4", "q8k_f16v", "f16k_q4v"])
-@pytest.mark.parametrize("name", ["two_seqs_ragged", "chunk512_ctx2k", "block32", "gqa8_70b"])
+@pytest.mark.parametrize("name", ["two_seqs_ragged", "chunk512_ctx2k", "block32", "gqa8_70b", "one_seq_chunk512_ctx4k"])
 def test_prefill_quantised_cache(pkg, oracle, cuda, name, tk, tv):
     """quantised caches: sequences expanded once to the F16 scratch, then the same tile kernel"""
     import torch
@@ -69,11 +75,12 @@ def test_prefill_matches_streamk_rows(pkg, oracle, cuda):
 
 
 def test_auto_picks_prefill_for_chunks(pkg, oracle, cuda):
-    """AUTO routes a 512-row causal chunk to the tile kernel (2 launches: plan + main) and still matches the oracle"""
+    """AUTO routes a 512-row causal chunk to the tile kernel (3 launches: plan + main + combine of the split items) and
+    still matches the oracle"""
     import torch
     rows = _chunk(0, 512, 1024)
     w = make_workload(oracle, [1024], 32, 8, 128, F16, seed=6, q_rows=rows)
     n0 = pkg.lib.b200_launch_count()
     got = _run_paged(pkg, torch, w, 0)
-    assert pkg.lib.b200_launch_count() - n0 == 2
+    assert pkg.lib.b200_launch_count() - n0 == 3
     assert oracle.max_rel_err(oracle_attention(oracle, w), got) <= TOL[F16]
