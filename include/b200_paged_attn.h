@@ -182,11 +182,12 @@ B200_API int b200_k_shift(const b200_k_shift_desc *d, void *stream);
  * Stops at the first failing layer and returns its status.
  *
  * Each layer is b200_store_attention(&writes[l], &attns[l]) below, which the results are identical to "store, then
- * attention" of: when the layer is a pure decode step on the stream-K kernel (q_seq == q_pos == NULL, n_q ==
- * writes[l].n_tokens, ONE new token per sequence) the attention kernel is started UNDER the store and waits for it only
- * in front of the one tile per sequence the store writes into.  The device checks first (plan kernel) that stored row r
- * goes to the cell of sequence r's last visible position — what build_attn's k_cur / v_cur copies do for a decode ubatch,
- * src/llama-graph.cpp:1375-1397 — and falls back to waiting in front of everything when any row does not.
+ * attention" of: when the layer is a decode step on the stream-K kernel (n_q == writes[l].n_tokens <= n_seqs, ONE new
+ * token per sequence) the attention kernel is started UNDER the store and waits for it only in front of the one tile per
+ * sequence the store writes into.  The device checks first (plan kernel) that row r is the row of sequence r (q_seq NULL
+ * or the identity) and that stored row r goes to the cell of that row's last visible position — what build_attn's
+ * k_cur / v_cur copies do for a decode ubatch, src/llama-graph.cpp:1375-1397 — and falls back to waiting in front of
+ * everything when any row does not.
  */
 B200_API int b200_decode_step(const b200_kv_write_desc *writes, const b200_attn_desc *attns, int32_t n_layers, void *stream);
 B200_API int b200_store_attention(const b200_kv_write_desc *store /* or NULL */, const b200_attn_desc *d, void *stream);

@@ -296,12 +296,13 @@ sk_plan_kernel(const __grid_constant__ sk_args a) {
     }
     // store overlap: every stored row must land on the LAST visible cell of its own sequence (or be skipped by kv_write)
     int slots_ok = 0;
-    if (a.after_store) {                                     // uniform; pure decode (row == sequence) by construction
-        int ok = 1;
+    if (a.after_store) {                                     // uniform.  Row r must be THE row of sequence r (q_seq absent or the identity):
+        int ok = 1;                                          // no other row then reads the cell row r's store writes
         for (int r = threadIdx.x; r < p.n_q; r += 1024) {
+            if (p.q_seq && p.q_seq[r] != r) ok = 0;
             const int64_t slot = a.store_slots ? (int64_t) a.store_slots[r] : r;
             if (slot < 0 || slot >= a.store_cells) continue;            // kv_write skips it
-            const int n = sk_row_nvis(p, r);
+            const int n = sk_row_nvis(p, r);                            // with q_pos: the row's own position + 1
             ok &= n > 0 && slot == (int64_t) p.block_table[(int64_t) r*p.bt_stride + (n - 1)/p.block_size]*p.block_size + (n - 1) % p.block_size;
         }
         slots_ok = __syncthreads_and(ok);
@@ -1129,8 +1130,9 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st, const b200_kv_
     a.mask = nullptr; a.nb_mask1 = 0; a.alibi_m0 = a.alibi_m1 = 1.0f; a.n_head_log2 = 1;
     a.dense_len = a.dense_bt = a.dense_qseq = nullptr; a.n_tiles = 0;
     const bool reuse = !dense && (d.flags & B200_ATTN_REUSE_PLAN);
-    // store overlap: ONE new token per sequence, row r == sequence r == stored row r (pure decode), launches chained by PDL
-    a.after_store = store && store->n_tokens > 0 && store->n_tokens == d.n_q && !dense && !d.q_seq && !d.q_pos
+    // store overlap: ONE new token per sequence, row r == sequence r == stored row r (a decode ubatch; with q_seq / q_pos
+    // given the plan kernel checks that they say so), launches chained by PDL
+    a.after_store = store && store->n_tokens > 0 && store->n_tokens == d.n_q && d.n_q <= d.n_seqs && !dense
                  && pdl_enabled() && (!reuse || store_checked) ? 1 : 0;
     a.store_slots = a.after_store ? store->slot_mapping : nullptr;
     a.store_cells = a.after_store ? store->n_cells : 0;

@@ -49,13 +49,13 @@ class _Layers:
             self.kc[l].copy_(self.full_k[l]); self.vc[l].copy_(self.full_v[l])
             self.kc[l][self.poison_idx] = 0x7b; self.vc[l][self.poison_idx] = 0x7b
 
-    def calls(self, outs):
+    def calls(self, outs, q_seq=None, q_pos=None):
         pkg, w0 = self.pkg, self.w0
         first = None
         calls, writes = [], []
         for l in range(self.L):
             c = pkg.AttnCall(self.qs[l], self.kc[l].view(-1), self.vc[l].view(-1), self.lay, outs[l], w0.scale, block_table=self.bt,
-                             seq_lens=self.sl, max_seq_len=int(w0.seq_lens.max()), total_tokens=int(w0.seq_lens.sum()),
+                             seq_lens=self.sl, q_seq=q_seq, q_pos=q_pos, max_seq_len=int(w0.seq_lens.max()), total_tokens=int(w0.seq_lens.sum()),
                              kernel=pkg.KERNEL_STREAMK, workspace=None if first is None else first.workspace)
             first = first or c
             calls.append(c)
@@ -146,3 +146,41 @@ def test_store_into_other_cells_switches_the_overlap_off(pkg, oracle, cuda):
         want = oracle.attention(wl.q, hk, hv, t, t, wl.n_head_kv, wl.scale, block_table=wl.block_table, seq_lens=wl.seq_lens,
                                 block_size=wl.block_size)
         assert oracle.max_rel_err(want, outs[l].cpu().numpy()) <= TOL[t]
+
+
+@pytest.mark.parametrize("identity", [True, False], ids=["q_seq_identity", "q_seq_permuted"])
+def test_decode_ubatch_with_q_seq_and_q_pos(pkg, oracle, cuda, identity):
+    """the form a llama_kv_cache host emits for a decode ubatch: q_seq and q_pos given.  With q_seq the identity and every
+    row at its sequence's newest position the overlap runs; with the rows in another order of sequences the plan kernel
+    must refuse it (another row could read the cell under the store) — and both give store-then-attend's results"""
+    import torch
+    t = Q8_0
+    lens = [300, 170, 1000, 64, 33, 2049]
+    n = len(lens)
+    perm = np.arange(n) if identity else np.array([1, 0, 2, 3, 5, 4])
+    rows = [(int(s), lens[int(s)] - 1) for s in perm]
+    ws_ = [make_workload(oracle, lens, 32, 8, 128, t, seed=120 + l, q_rows=rows) for l in range(2)]
+    w0 = ws_[0]
+    lay = pkg.KVLayout(t, 8, 128, 16, w0.n_blocks)
+    last = np.cumsum(w0.seq_lens.astype(np.int64)) - 1
+    slots = w0.slot_mapping[last][perm].astype(np.int32)                          # stored row r = query row r
+    bt, sl = _dev(torch, w0.block_table), _dev(torch, w0.seq_lens)
+    q_seq, q_pos = _dev(torch, w0.q_seq), _dev(torch, w0.q_pos)
+    slots_d, poison = _dev(torch, slots), _dev(torch, slots.astype(np.int64))
+    outs, calls, writes, caches = [], [], [], []
+    for l, w in enumerate(ws_):
+        kc, vc = _dev(torch, w.k_cache), _dev(torch, w.v_cache)
+        kc[poison] = 0x7b; vc[poison] = 0x7b
+        out = torch.full((n, 32, 128), float("nan"), device=cuda)
+        c = pkg.AttnCall(_dev(torch, w.q), kc.view(-1), vc.view(-1), lay, out, w0.scale, block_table=bt, seq_lens=sl, q_seq=q_seq, q_pos=q_pos,
+                         max_seq_len=max(lens), total_tokens=sum(lens), kernel=pkg.KERNEL_STREAMK, workspace=calls[0].workspace if calls else None)
+        calls.append(c); outs.append(out); caches.append((kc, vc))
+        src = (_dev(torch, w.k_f32[last][perm]), _dev(torch, w.v_f32[last][perm]))   # the descriptor holds raw pointers: keep the rows alive
+        caches[-1] += src
+        writes.append(pkg.kv_write_desc(src[0], src[1], slots_d, kc.view(-1), vc.view(-1), lay))
+    pkg.StepCall(calls, writes).run()
+    torch.cuda.synchronize()
+    assert calls[0].workspace.view(torch.int32)[3].item() == (1 if identity else 0)
+    for l, w in enumerate(ws_):
+        assert np.array_equal(caches[l][0].cpu().numpy(), w.k_cache) and np.array_equal(caches[l][1].cpu().numpy(), w.v_cache)
+        assert oracle.max_rel_err(oracle_attention(oracle, w), outs[l].cpu().numpy()) <= TOL[t]
