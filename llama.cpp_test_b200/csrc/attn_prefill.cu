@@ -436,7 +436,7 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
             if (grp == 0 || useB) {
                 const float *qrow = reinterpret_cast<const float *>(static_cast<const char *>(p.q) + (int64_t) (row0 + (live ? tl : 0))*p.nbq1
                                                                      + (int64_t) (kvh*gqa + hg)*p.nbq2);
-#pragma unroll 4
+#pragma unroll 8
                 for (int c = 0; c < 16; ++c) {
                     float4 x = make_float4(0.f, 0.f, 0.f, 0.f), y = x;
                     if (live) { x = *reinterpret_cast<const float4 *>(qrow + 8*c); y = *reinterpret_cast<const float4 *>(qrow + 8*c + 4); }

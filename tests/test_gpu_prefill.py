@@ -28,7 +28,7 @@ CASES = {
     "chunk512_ctx2k":     ([2048, 700], 32, 8, _chunk(0, 1536, 2048) + _chunk(1, 188, 700), 16),   # config-3 shape, 2 sequences
     "not_causal_limit":   ([150], 8, 2, [(0, 149)] * 40, 16),                          # q_pos beyond: every row sees all 150
     # KV split of the tail items (fewer work items than SMs, or a last wave that is not full): pieces + pf_combine_kernel
-    "one_seq_chunk512_ctx4k": ([4096], 32, 8, _chunk(0, 3584, 4096), 16),             # 16 items -> 8 pieces of 8 kv tiles each
+    "one_seq_chunk256_ctx2k": ([2048], 8, 2, _chunk(0, 1792, 2048), 16),              # 8 items -> 8 pieces of 4 kv tiles each
     "one_seq_first_chunk512": ([512], 32, 8, _chunk(0, 0, 512), 16),                  # early rows see nothing of the later pieces
     # 80 one-row tiles x 2 kv heads = 160 items: 148 whole ones + the 12 of the six long sequences (first in row order = last
     # in work order), each cut into 4 pieces
@@ -50,7 +50,7 @@ def test_prefill_tile_kernel(pkg, oracle, cuda, name):
 
 
 @pytest.mark.parametrize("tk,tv", [(Q8_0, Q8_0), (Q4_0, Q4_0), (Q8_0, F16), (F16, Q4_0)], ids=["q8", "q4", "q8k_f16v", "f16k_q4v"])
-@pytest.mark.parametrize("name", ["two_seqs_ragged", "chunk512_ctx2k", "block32", "gqa8_70b", "one_seq_chunk512_ctx4k"])
+@pytest.mark.parametrize("name", ["two_seqs_ragged", "chunk512_ctx2k", "block32", "gqa8_70b", "one_seq_chunk256_ctx2k"])
 def test_prefill_quantised_cache(pkg, oracle, cuda, name, tk, tv):
     """quantised caches: sequences expanded once to the F16 scratch, then the same tile kernel"""
     import torch
