@@ -234,6 +234,7 @@ __global__ void __launch_bounds__(1024)
 pf_plan_kernel(const __grid_constant__ pf_args a) {
     __shared__ int s_warp[32];
     const b200_attn_desc &p = a.d;
+    pdl_prologue();                                          // the plan of the previous call on this workspace may still be in use
     int *row0 = a.plan + 2, *rows = row0 + p.n_q;
     int carry_start = 0, carry_tiles = 0;                    // run start of the last row seen, tiles so far
     for (int r0 = 0; r0 < p.n_q; r0 += 1024) {
@@ -316,6 +317,7 @@ __device__ __forceinline__ void pf_dequant_block(int type, const char *row, int 
 __global__ void __launch_bounds__(256)
 pf_dequant_kernel(const __grid_constant__ pf_args a) {
     const b200_attn_desc &p = a.d;
+    pdl_prologue();
     const int total = a.seq_off[p.n_seqs];
     for (int64_t c0 = (int64_t) blockIdx.x*16; c0 < total; c0 += (int64_t) gridDim.x*16) {
         int lo = 0, hi = p.n_seqs;                           // sequence owning scratch cell c0: last s with seq_off[s] <= c0
@@ -378,7 +380,7 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
     volatile int      *nvis_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 216);   // [8] per-warp max n_vis
     volatile int      *part_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 248);   // piece slot of the current unit or -1 (kept out of the softmax warps' registers)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    pdl_prologue();
+    pdl_trigger();                                           // the CTA set-up below (barriers, TMEM) runs under the plan / expansion kernels
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < PF_NBAR; ++i) pf_mbar_init(sBar + 8*i, (i >= PF_PFULL && i < PF_PFULL + 4) ? 128 : 1);
@@ -392,6 +394,7 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
     __syncthreads();
     pf_tc_fence_after();
     const uint32_t tmem = *tmem_slot;
+    pdl_wait();                                              // plan, F16 scratch, the caller's tensors
 
     const int gqa = a.gqa, bs = p.block_size;
     const int n_blk = p.bt_stride < INT32_MAX ? (int) p.bt_stride : INT32_MAX;
@@ -671,6 +674,7 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
 __global__ void __launch_bounds__(256)
 pf_combine_kernel(const __grid_constant__ pf_args a) {
     const b200_attn_desc &p = a.d;
+    pdl_prologue();
     const int n_tiles = a.plan[0];
     const pf_split sp = pf_split_of(n_tiles*p.n_head_kv, a.grid_main);
     if (sp.k <= 1 || (int) blockIdx.x >= sp.rem) return;
@@ -836,7 +840,7 @@ int launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st) {
         if (!pf_make_map(&tmV, d.v, d.nbv1, d.nbv2, d.n_head_kv, d.n_kv)) return B200_ERR_CUDA;
     }
 
-    pf_plan_kernel<<<1, 1024, 0, st>>>(a);
+    launch_pdl(pf_plan_kernel, dim3(1), dim3(1024), 0, st, a);
     count_launch();
     if (!check_launch("pf_plan")) return B200_ERR_CUDA;
     const int sms = pf_sm_count();
@@ -844,7 +848,7 @@ int launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st) {
         int64_t g = a.scratch_cells/16;
         if (g > 8*sms) g = 8*sms;
         if (g < 1) g = 1;
-        pf_dequant_kernel<<<(unsigned) g, 256, 0, st>>>(a);
+        launch_pdl(pf_dequant_kernel, dim3((unsigned) g), dim3(256), 0, st, a);
         count_launch();
         if (!check_launch("pf_dequant")) return B200_ERR_CUDA;
     }
@@ -852,7 +856,7 @@ int launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st) {
 #ifdef PF_TIMELINE
     cudaMalloc(&a.dbg, 3*64*8*sizeof(long long)); cudaMemset(a.dbg, 0, 3*64*8*sizeof(long long));
 #endif
-    pf_main_kernel<<<(unsigned) grid, PF_THREADS, PF_SMEM, st>>>(a, tmK, tmV);
+    launch_pdl(pf_main_kernel, dim3((unsigned) grid), dim3(PF_THREADS), PF_SMEM, st, a, tmK, tmV);
 #ifdef PF_TIMELINE
     {
         static int dumped = 0;
@@ -873,7 +877,7 @@ int launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st) {
 #endif
     count_launch();
     if (!check_launch("pf_main")) return B200_ERR_CUDA;
-    pf_combine_kernel<<<dim3((unsigned) grid, 2*PF_ROWS/8), 256, 0, st>>>(a);   // the split items' pieces -> dst (returns at once when nothing was split)
+    launch_pdl(pf_combine_kernel, dim3((unsigned) grid, 2*PF_ROWS/8), dim3(256), 0, st, a);   // the split items' pieces -> dst (returns at once when nothing was split)
     count_launch();
     if (!check_launch("pf_combine")) return B200_ERR_CUDA;
     return B200_OK;
