@@ -31,4 +31,6 @@ for WL in config1 config4_shard8; do   # the latency-bound ops: where the ~10 us
   ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $O/${TAG}_launches_$WL.csv \
       python bench.py --workload $WL --layers 4 --steps 2 --warmup 3 --no-graph --no-cpu-baseline --no-e2e > $O/${TAG}_ncu_list_$WL.log 2>&1
 done
+python profiles/bench_prefill_single.py > $O/${TAG}_prefill_single.jsonl 2>&1; cat $O/${TAG}_prefill_single.jsonl   # one sequence's chunk: the KV split of the tail
+bash profiles/run_timeline.sh $TAG config1 config5_attn > $O/${TAG}_timeline.log 2>&1; grep -A3 "^==" $O/${TAG}_timeline.log   # needs gpurun_variants/tl (make timeline)
 ls -la $O | tail -15
