@@ -502,7 +502,47 @@ def run_decode(args, rank, world, local, pkg):
                 peer.epoch = e_before + (a1 - a0)           # capture launched nothing
                 group_graphs.append(gg)
 
+        # One sequence-sharded step as ONE CUDA graph: the H2D copies (copy stream), every group's b200_decode_step call and
+        # the D2H copies (second copy stream) captured with their cross-stream dependencies, so a step is one graph launch —
+        # the ten group replays of the form below each ended in a full drain of the GPU, and the programmatic launch chain
+        # of the kernels broke at every group boundary.  The copies are still the step's own, from / to pinned host memory.
+        step_graph = None
+        # (small steps — config 1, config 5: ~0.5 ms — measured 2 % slower this way and keep the per-group form)
+        if group_calls is not None and group_graphs is not None and bytes_step_rank > 2e9 and os.environ.get("B200_E2E_STEP_GRAPH", "1") != "0":
+            def step_body():
+                cur = torch.cuda.current_stream()
+                s_in.wait_stream(cur); s_out.wait_stream(cur)
+                with torch.cuda.stream(s_in):
+                    bt_d.copy_(bt_hp, non_blocking=True); sl_d.copy_(sl_hp, non_blocking=True)
+                    slot_new_d.copy_(slot_new_h, non_blocking=True)
+                    for gi, (a0, a1) in enumerate(groups):
+                        q_d[a0:a1].copy_(q_h[a0:a1], non_blocking=True)
+                        knew_d[a0:a1].copy_(knew_h[a0:a1], non_blocking=True); vnew_d[a0:a1].copy_(vnew_h[a0:a1], non_blocking=True)
+                        ev_in[gi].record(s_in)
+                for gi, (a0, a1) in enumerate(groups):
+                    cur.wait_event(ev_in[gi])
+                    group_calls[gi].run()
+                    ev_c[gi].record(cur)
+                    s_out.wait_event(ev_c[gi])
+                    with torch.cuda.stream(s_out):
+                        out_h[a0:a1].copy_(res_d[a0:a1], non_blocking=True)
+                cur.wait_stream(s_in); cur.wait_stream(s_out)
+            try:
+                torch.cuda.synchronize()
+                gg = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gg):
+                    step_body()
+                step_graph = gg
+            except Exception as e:                           # keep the per-group form
+                print(f"bench: whole-step graph capture failed ({type(e).__name__}: {e}); per-group graphs stay", file=sys.stderr)
+                torch.cuda.synchronize()
+                step_graph = None
+
         def step_e2e():
+            if step_graph is not None:
+                step_graph.replay()
+                torch.cuda.current_stream().synchronize()    # the host holds the step's result
+                return
             cur = torch.cuda.current_stream()
             s_in.wait_stream(cur)
             with torch.cuda.stream(s_in):
@@ -549,6 +589,8 @@ def run_decode(args, rank, world, local, pkg):
                "d2h_bytes_per_step": int(d2h), "ms_per_step": round(ms_e2e, 4),
                # where an e2e step's time can go besides the kernels: both directions of the step's copies run alone (max over
                # ranks; H2D and D2H concurrently, as in the step) and the GB/s that is per rank
+               "form": ("one CUDA graph per step: H2D copies, b200_decode_step per layer group, D2H copies" if step_graph is not None
+                        else "copies on two copy streams around one b200_decode_step call (captured graph) per layer group"),
                "copies_only_ms_per_step": round(ms_copies, 4),
                "copies_only_gbs_per_rank": round((h2d + d2h) / (ms_copies * 1e-3) / 1e9, 1)}
     clocks = sampler.summary()
