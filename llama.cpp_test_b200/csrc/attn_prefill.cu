@@ -49,11 +49,17 @@ constexpr int PF_SMEM    = PF_SBAR + 256;
 // KV split of the tail: when the work items do not fill the last wave of the persistent grid (n_work % grid != 0, or
 // fewer items than SMs: ONE sequence's 512-token chunk is 16 items), each of the leftover items is cut into up to
 // PF_MAX_SPLIT pieces of consecutive kv tiles so that the pieces fill the machine; a piece leaves (m, l, unnormalised O)
-// per row in the workspace and pf_combine_kernel merges them.  Pieces are never shorter than PF_MIN_PIECE tiles.
+// per row in the workspace and pf_combine_kernel merges them.  Pieces are never shorter than PF_MIN_PIECE tiles (a piece
+// pays its own Q load, partial store and share of the merge, ~10 us: with 4-tile pieces the 512-row prompt chunks of
+// llama-batched-bench at ctx <= 1k got 6 % slower); an item too short for two pieces runs whole and writes dst itself,
+// the units of its other piece slots find no tiles and write nothing.
 #ifndef PF_SPLIT_MAX
 #define PF_SPLIT_MAX 8
 #endif
-constexpr int PF_MAX_SPLIT = PF_SPLIT_MAX, PF_MIN_PIECE = 4;
+#ifndef PF_PIECE_MIN
+#define PF_PIECE_MIN 16
+#endif
+constexpr int PF_MAX_SPLIT = PF_SPLIT_MAX, PF_MIN_PIECE = PF_PIECE_MIN;
 
 // mbarriers: SFULL[group][S buffer], PFULL[group][P buffer] (128 arrivals; the softmax may be a tile ahead of the MMA warp), ODONE[group]
 enum { PF_FULLK = 0, PF_FULLV = 4, PF_EMPTYK = 7, PF_EMPTYV = 11, PF_SFULL = 14, PF_PFULL = 18, PF_ODONE = 22, PF_NBAR = 24 };
@@ -71,6 +77,7 @@ struct pf_args {
     int64_t cap;                         // upper bound applied to every seq_lens entry (block-table capacity, or max_seq_len)
     float  *part_o, *part_ml;            // KV-split pieces: [grid_main][256 rows][128], [grid_main][256 rows][2] {m (log2 domain), l}
     int     grid_main;                   // CTAs of pf_main_kernel (the combine kernel derives the same split from it)
+    int     split_max;                   // PF_MAX_SPLIT, or 1 when the host knows no sequence is long enough for two pieces (no combine launch)
 #ifdef PF_TIMELINE
     long long *dbg;                      // debug builds only: clock64 stamps of CTA 0's first work item, [3 warps][64 tiles][8]
 #endif
@@ -349,19 +356,20 @@ pf_dequant_kernel(const __grid_constant__ pf_args a) {
 // which work items are split, and how: everything follows from the item count and the grid, so the main and the
 // combine kernel agree without a table.  Units [0, full) are whole items; unit full + j is piece j % k of item full + j / k.
 struct pf_split { int full, rem, k, n_units; };
-__device__ __forceinline__ pf_split pf_split_of(int n_work, int grid) {
+__device__ __forceinline__ pf_split pf_split_of(int n_work, int grid, int k_max) {
     pf_split sp;
     sp.rem = n_work % grid; sp.full = n_work - sp.rem;
     sp.k = sp.rem ? grid/sp.rem : 1;
-    if (sp.k > PF_MAX_SPLIT) sp.k = PF_MAX_SPLIT;
+    if (sp.k > k_max) sp.k = k_max;
     sp.n_units = sp.full + sp.rem*sp.k;
     return sp;
 }
-// tiles [ta, tb) of piece `piece` of an item with nkt kv tiles
-__device__ __forceinline__ void pf_piece_range(int nkt, int k, int piece, int &ta, int &tb) {
-    int ke = nkt/PF_MIN_PIECE; ke = ke < 1 ? 1 : (ke > k ? k : ke);      // pieces this item really has
-    if (piece >= ke) { ta = tb = 0; return; }
+// tiles [ta, tb) of piece `piece` of an item with nkt kv tiles; returns the number of pieces the item really has
+__device__ __forceinline__ int pf_piece_range(int nkt, int k, int piece, int &ta, int &tb) {
+    int ke = nkt/PF_MIN_PIECE; ke = ke < 1 ? 1 : (ke > k ? k : ke);
+    if (piece >= ke) { ta = tb = 0; return ke; }
     ta = (int) ((int64_t) nkt*piece/ke); tb = (int) ((int64_t) nkt*(piece + 1)/ke);
+    return ke;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -378,7 +386,6 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
     volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(pf_dyn + PF_SBAR + 208);
     volatile int      *work_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 212);
     volatile int      *nvis_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 216);   // [8] per-warp max n_vis
-    volatile int      *part_slot = reinterpret_cast<volatile int *>(pf_dyn + PF_SBAR + 248);   // piece slot of the current unit or -1 (kept out of the softmax warps' registers)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     pdl_trigger();                                           // the CTA set-up below (barriers, TMEM) runs under the plan / expansion kernels
 
@@ -408,12 +415,11 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
         __syncthreads();
         const int unit = *work_slot;
         const int n_tiles = a.plan[0];
-        const pf_split sp = pf_split_of(n_tiles*p.n_head_kv, (int) gridDim.x);
+        const pf_split sp = pf_split_of(n_tiles*p.n_head_kv, (int) gridDim.x, a.split_max);
         if (unit >= sp.n_units) break;
         const int pidx = unit - sp.full;                     // >= 0: a piece (slot in the partial buffers)
         const int w = pidx < 0 ? unit : sp.full + pidx/sp.k, piece = pidx < 0 ? 0 : pidx % sp.k;
         const bool split = pidx >= 0 && sp.k > 1;
-        if (threadIdx.x == 0) *part_slot = split ? pidx : -1;       // read back in the epilogue, behind the __syncthreads below
         const int tile = n_tiles - 1 - w/p.n_head_kv, kvh = w % p.n_head_kv;      // later rows (longer contexts) first
         const int row0 = tile_row0[tile], nrows = tile_rows[tile];
         const bool useB = nrows > tokA;                      // group B has live rows
@@ -630,11 +636,27 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
             }
             // ---- epilogue: O / l -> dst[row][head][d]; a piece: (m, l) and the unnormalised O -> its slot of the partial buffers
             const bool live = tl < nrows;
-            const int pslot = *part_slot;
+            // what kind of unit this was, worked out again from the shared slots (kept out of the tile loop's registers):
+            // pslot >= 0: a piece (partial buffers); dead: a piece slot of an item that runs whole — nothing to write
+            int pslot = -1;
+            bool dead = false;
+            {
+                const pf_split sp_e = pf_split_of(a.plan[0]*p.n_head_kv, (int) gridDim.x, a.split_max);
+                const int pidx_e = *work_slot - sp_e.full;
+                if (pidx_e >= 0 && sp_e.k > 1) {
+                    int nv = 0;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) nv = max(nv, nvis_slot[i]);
+                    int ta_e, tb_e;
+                    const int ke = pf_piece_range((nv + PF_BN - 1)/PF_BN, sp_e.k, pidx_e % sp_e.k, ta_e, tb_e);
+                    if (ke > 1) pslot = pidx_e;
+                    dead = pidx_e % sp_e.k >= ke;
+                }
+            }
             const bool is_piece = pslot >= 0;
             float *out = is_piece ? a.part_o + ((int64_t) pslot*2*PF_ROWS + R)*PF_D
                                   : static_cast<float *>(p.dst) + ((int64_t) (row0 + (live ? tl : 0))*p.n_head + kvh*gqa + hg)*PF_D;
-            if (is_piece) *reinterpret_cast<float2 *>(a.part_ml + ((int64_t) pslot*2*PF_ROWS + R)*2) = make_float2(nkt > 0 ? m_run : -INFINITY, nkt > 0 ? l_run : 0.f);
+            if (is_piece && !dead) *reinterpret_cast<float2 *>(a.part_ml + ((int64_t) pslot*2*PF_ROWS + R)*2) = make_float2(nkt > 0 ? m_run : -INFINITY, nkt > 0 ? l_run : 0.f);
             if (nkt > 0) {
                 pf_mbar_wait(sBar + 8*(PF_ODONE + grp), (Gg + nkt - 1) & 1);
                 pf_tc_fence_after();
@@ -651,7 +673,7 @@ pf_main_kernel(const __grid_constant__ pf_args a, const __grid_constant__ CUtens
                                                                                       __uint_as_float(v[c + 2])*inv, __uint_as_float(v[c + 3])*inv);
                     }
                 }
-            } else if (live && !is_piece) {
+            } else if (live && !is_piece && !dead) {
                 const float nan = __int_as_float(0x7fc00000);                     // no visible cell: 0/0 like the reference (ggml-cpu.c:12418)
                 for (int c = 0; c < PF_D; c += 4) *reinterpret_cast<float4 *>(out + c) = make_float4(nan, nan, nan, nan);
             }
@@ -676,23 +698,45 @@ pf_combine_kernel(const __grid_constant__ pf_args a) {
     const b200_attn_desc &p = a.d;
     pdl_prologue();
     const int n_tiles = a.plan[0];
-    const pf_split sp = pf_split_of(n_tiles*p.n_head_kv, a.grid_main);
+    const pf_split sp = pf_split_of(n_tiles*p.n_head_kv, a.grid_main, a.split_max);
     if (sp.k <= 1 || (int) blockIdx.x >= sp.rem) return;
     const int w = sp.full + blockIdx.x;
     const int tile = n_tiles - 1 - w/p.n_head_kv, kvh = w % p.n_head_kv;
     const int *tile_row0 = a.plan + 2, *tile_rows = tile_row0 + p.n_q;
     const int row0 = tile_row0[tile], nrows = tile_rows[tile];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // the item's kv tiles, as the main kernel counted them: from the largest visible length of its tokens
+    __shared__ int s_nvis[8];
+    {
+        int n_vis = 0;
+        if ((int) threadIdx.x < nrows) {
+            const int seq = p.q_seq ? p.q_seq[row0] : row0;
+            int seq_len = p.seq_lens[seq];
+            if (seq_len > a.cap) seq_len = (int) a.cap;
+            n_vis = seq_len < 0 ? 0 : seq_len;
+            if (p.q_pos) { const int lim = p.q_pos[row0 + threadIdx.x] + 1; n_vis = lim < n_vis ? lim : n_vis; }
+            if (n_vis < 0) n_vis = 0;
+        }
+        const int wmax = __reduce_max_sync(0xffffffffu, n_vis);
+        if (lane == 0) s_nvis[warp] = wmax;
+        __syncthreads();
+    }
+    int nvis_max = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) nvis_max = max(nvis_max, s_nvis[i]);
+    int ta, tb;
+    const int ke = pf_piece_range((nvis_max + PF_BN - 1)/PF_BN, sp.k, 0, ta, tb);
+    if (ke <= 1) return;                                     // ran whole: the main kernel wrote dst
     const int64_t slot0 = (int64_t) blockIdx.x*sp.k;        // first piece slot of this item
     {
         const int R = blockIdx.y*8 + warp;
         const int tl = R/a.gqa, hg = R - tl*a.gqa;
         if (tl >= nrows) return;
-        const float2 ml = lane < sp.k ? *reinterpret_cast<const float2 *>(a.part_ml + ((slot0 + lane)*2*PF_ROWS + R)*2) : make_float2(-INFINITY, 0.f);
+        const float2 ml = lane < ke ? *reinterpret_cast<const float2 *>(a.part_ml + ((slot0 + lane)*2*PF_ROWS + R)*2) : make_float2(-INFINITY, 0.f);
         float4 v[PF_MAX_SPLIT];
 #pragma unroll
         for (int i = 0; i < PF_MAX_SPLIT; ++i)
-            v[i] = i < sp.k ? *reinterpret_cast<const float4 *>(a.part_o + ((slot0 + i)*2*PF_ROWS + R)*PF_D + 4*lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+            v[i] = i < ke ? *reinterpret_cast<const float4 *>(a.part_o + ((slot0 + i)*2*PF_ROWS + R)*PF_D + 4*lane) : make_float4(0.f, 0.f, 0.f, 0.f);
         float M = ml.x;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
@@ -824,6 +868,11 @@ int launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st) {
     a.part_o = reinterpret_cast<float *>(ws);  ws += pf_part_o_bytes(d);
     a.part_ml = reinterpret_cast<float *>(ws); ws += pf_part_ml_bytes(d);
     a.grid_main = (int) pf_grid(d);
+    {                                                        // contexts the host knows to be short never split: no pieces, no combine launch
+        int64_t bound = d.bt_stride*d.block_size;
+        if (d.max_seq_len > 0 && d.max_seq_len < bound) bound = d.max_seq_len;
+        a.split_max = bound < 2*PF_MIN_PIECE*PF_BN ? 1 : PF_MAX_SPLIT;
+    }
     if (scratch) {
         a.seq_off = a.plan + 2 + 2*(size_t) d.n_q;
         a.scratch_cells = pf_scratch_cells(d);
@@ -877,9 +926,11 @@ int launch_attn_prefill(const b200_attn_desc &d, cudaStream_t st) {
 #endif
     count_launch();
     if (!check_launch("pf_main")) return B200_ERR_CUDA;
-    launch_pdl(pf_combine_kernel, dim3((unsigned) grid, 2*PF_ROWS/8), dim3(256), 0, st, a);   // the split items' pieces -> dst (returns at once when nothing was split)
-    count_launch();
-    if (!check_launch("pf_combine")) return B200_ERR_CUDA;
+    if (a.split_max > 1) {
+        launch_pdl(pf_combine_kernel, dim3((unsigned) grid, 2*PF_ROWS/8), dim3(256), 0, st, a);   // the split items' pieces -> dst (returns at once when nothing was split)
+        count_launch();
+        if (!check_launch("pf_combine")) return B200_ERR_CUDA;
+    }
     return B200_OK;
 }
 

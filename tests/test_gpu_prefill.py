@@ -28,11 +28,13 @@ CASES = {
     "chunk512_ctx2k":     ([2048, 700], 32, 8, _chunk(0, 1536, 2048) + _chunk(1, 188, 700), 16),   # config-3 shape, 2 sequences
     "not_causal_limit":   ([150], 8, 2, [(0, 149)] * 40, 16),                          # q_pos beyond: every row sees all 150
     # KV split of the tail items (fewer work items than SMs, or a last wave that is not full): pieces + pf_combine_kernel
-    "one_seq_chunk256_ctx2k": ([2048], 8, 2, _chunk(0, 1792, 2048), 16),              # 8 items -> 8 pieces of 4 kv tiles each
+    "one_seq_chunk256_ctx2k": ([2048], 8, 2, _chunk(0, 1792, 2048), 16),              # 8 items of 32 kv tiles -> 2 pieces each (a piece is >= 16 tiles)
+    "one_seq_chunk128_ctx8k": ([8192], 8, 2, _chunk(0, 8064, 8192), 16),              # 4 items of 128 kv tiles -> 8 pieces each
     "one_seq_first_chunk512": ([512], 32, 8, _chunk(0, 0, 512), 16),                  # early rows see nothing of the later pieces
     # 80 one-row tiles x 2 kv heads = 160 items: 148 whole ones + the 12 of the six long sequences (first in row order = last
-    # in work order), each cut into 4 pieces
-    "tail_wave_160_items":    ([1200]*6 + [40 + 3*i for i in range(74)], 8, 2, [(s, 1199) for s in range(6)] + [(6 + i, 39 + 3*i) for i in range(74)], 16),
+    # in work order): 3 pieces for the 3300-cell ones, 2 for the 2100-cell ones, the 900-cell one runs whole
+    "tail_wave_160_items":    ([3300, 3300, 2100, 2100, 2100, 900] + [40 + 3*i for i in range(74)], 8, 2,
+                               [(s, n - 1) for s, n in enumerate([3300, 3300, 2100, 2100, 2100, 900])] + [(6 + i, 39 + 3*i) for i in range(74)], 16),
 }
 
 
@@ -41,7 +43,10 @@ def test_prefill_tile_kernel(pkg, oracle, cuda, name):
     import torch
     seq_lens, n_head, n_head_kv, rows, bs = CASES[name]
     w = make_workload(oracle, seq_lens, n_head, n_head_kv, 128, F16, seed=31, q_rows=rows, block_size=bs)
+    n0 = pkg.lib.b200_launch_count()
     got = _run_paged(pkg, torch, w, PREFILL)
+    # plan + main, and the merge of split items only when some sequence is long enough for two pieces (2 x 16 kv tiles)
+    assert pkg.lib.b200_launch_count() - n0 == (3 if max(seq_lens) >= 2048 else 2)
     want = oracle_attention(oracle, w)
     assert not np.isnan(got).any()
     err, nm = oracle.max_rel_err(want, got), oracle.nmse(want, got)
@@ -75,12 +80,12 @@ def test_prefill_matches_streamk_rows(pkg, oracle, cuda):
 
 
 def test_auto_picks_prefill_for_chunks(pkg, oracle, cuda):
-    """AUTO routes a 512-row causal chunk to the tile kernel (3 launches: plan + main + combine of the split items) and
-    still matches the oracle"""
+    """AUTO routes a 512-row causal chunk to the tile kernel (2 launches: plan + main; the context is too short for
+    KV-split pieces, so no merge launch) and still matches the oracle"""
     import torch
     rows = _chunk(0, 512, 1024)
     w = make_workload(oracle, [1024], 32, 8, 128, F16, seed=6, q_rows=rows)
     n0 = pkg.lib.b200_launch_count()
     got = _run_paged(pkg, torch, w, 0)
-    assert pkg.lib.b200_launch_count() - n0 == 3
+    assert pkg.lib.b200_launch_count() - n0 == 2
     assert oracle.max_rel_err(oracle_attention(oracle, w), got) <= TOL[F16]
