@@ -25,6 +25,9 @@
 //              (128-byte swizzle), 8 boxes per 64-token stage; K ring 4 stages, V ring 3
 // TMEM: all 512 columns (per group S0 64, S1 64, O 128).  Shared: Q 2 x 32 KB + K 4 x 16 KB + V 3 x 16 KB = 176 KB.
 // What bounds it is measured in profiles/r1p_microbench.txt (QK^T from shared memory: 384 cycles per block).
+// Work items that do not fill the persistent grid's last wave are cut into pieces of consecutive kv tiles whose
+// partial (m, l, O) pf_combine_kernel merges (PF_MAX_SPLIT below); the plan / expansion / main / merge kernels are
+// chained by programmatic dependent launch, the CTA set-up of the main kernel running under its predecessors.
 #ifdef PF_TIMELINE
 #include <cstdio>
 #endif

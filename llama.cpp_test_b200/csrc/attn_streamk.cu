@@ -32,7 +32,13 @@
 //                      max/sum).  The 8 warps of a CTA take the 8 kv heads of the same tokens, so a CTA consumes
 //                      whole contiguous token rows of the flat llama.cpp cache.
 //   * sk_combine_kernel merges the segments of rows that were split (rows with one segment are written
-//                      directly by the main kernel).
+//                      directly by the main kernel).  One CTA per (row, kv head), started while the main kernel
+//                      runs; it does not wait for that grid to drain but spins on the row's arrival counter,
+//                      which the main kernel's warps bump after their partials are stored (sk_args::arrive).
+//   Launch chain (programmatic dependent launch, common.cuh): layers 1.. of a b200_decode_step call read plan and block
+//   table before they wait for their predecessor (sk_args::early); with the layer's kv_write in front
+//   (b200_store_attention) the main kernel starts under the store and waits for it only in front of each row's last
+//   tile, after the plan kernel has checked the slot mapping on the device (sk_args::after_store).  DESIGN.md 3.1.
 #include "common.cuh"
 #include <cuda.h>
 #include <math.h>

@@ -6,7 +6,8 @@
 // (src/llama-graph.cpp:1375-1397), and the per-move cudaMemcpyAsync of defrag (cpy.cu:544-547,
 // src/llama-context.cpp:653-711).  The reference launches ONE single-thread CTA per 32-element quant
 // block (cpy.cu:372-381); here one CTA owns one token row, 8 lanes cooperate on each quant block with
-// shuffles, the converted row is staged in shared memory and leaves the SM as coalesced 16-byte stores.
+// shuffles, the converted row is staged in shared memory and leaves the SM as coalesced 16-byte stores
+// (prefill-sized stores: four token rows per CTA, all their source loads in flight before the first use).
 //
 // Bit-exactness: arithmetic is the IEEE sequence of quantize_row_q8_0_ref / quantize_row_q4_0_ref
 // (ggml/src/ggml-quants.c:194-216, :31-66) with explicit _rn intrinsics so nvcc cannot contract
