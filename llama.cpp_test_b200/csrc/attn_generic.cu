@@ -182,7 +182,7 @@ static void launch_g(const attn_generic_args &a, int G, dim3 grid, cudaStream_t 
 }
 
 bool generic_supports(const b200_attn_desc &d) {
-    return (d.head_dim == 64 || d.head_dim == 128) && type_ok(d.type_k) && type_ok(d.type_v) &&
+    return (d.head_dim == 64 || d.head_dim == 128 || d.head_dim == 256) && type_ok(d.type_k) && type_ok(d.type_v) &&
            d.n_head_kv > 0 && d.n_head % d.n_head_kv == 0;
 }
 
@@ -223,12 +223,13 @@ int launch_attn_generic(const b200_attn_desc &d, cudaStream_t st) {
     a.m0 = powf(2.0f, -(d.max_bias       )/a.n_head_log2);
     a.m1 = powf(2.0f, -(d.max_bias / 2.0f)/a.n_head_log2);
     const dim3 grid((unsigned) d.n_q, (unsigned) (d.n_head/G), (unsigned) a.n_splits);
-    if (d.head_dim == 128) launch_g<128>(a, G, grid, st); else launch_g<64>(a, G, grid, st);
+    if (d.head_dim == 128) launch_g<128>(a, G, grid, st); else if (d.head_dim == 256) launch_g<256>(a, G, grid, st); else launch_g<64>(a, G, grid, st);
     count_launch();
     if (!check_launch("attn_generic")) return B200_ERR_CUDA;
     if (a.n_splits > 1) {
         const unsigned rows = (unsigned) d.n_q*d.n_head;
         if (d.head_dim == 128) attn_combine_kernel<128><<<rows, 128, 0, st>>>(a.partial, static_cast<float *>(d.dst), a.n_splits);
+        else if (d.head_dim == 256) attn_combine_kernel<256><<<rows, 256, 0, st>>>(a.partial, static_cast<float *>(d.dst), a.n_splits);
         else                   attn_combine_kernel<64 ><<<rows, 64,  0, st>>>(a.partial, static_cast<float *>(d.dst), a.n_splits);
         count_launch();
         if (!check_launch("attn_combine")) return B200_ERR_CUDA;

@@ -113,7 +113,7 @@ def _grid(hs):
 
 
 @pytest.mark.parametrize("t", TYPES)
-@pytest.mark.parametrize("hs", [64, 128])
+@pytest.mark.parametrize("hs", [64, 128, 256])
 def test_flash_attn_ext_node_reference_grid(pkg, oracle, cuda, hs, t):
     import torch
     bad, n = [], 0
@@ -131,7 +131,7 @@ def test_flash_attn_ext_node_reference_grid(pkg, oracle, cuda, hs, t):
     assert n == (108 if hs == 128 else 44)                   # every case of the grid ran
 
 
-@pytest.mark.parametrize("hs", [80, 256])
+@pytest.mark.parametrize("hs", [80, 96, 112])
 def test_flash_attn_ext_node_unsupported_head_sizes_are_declined(pkg, oracle, cuda, hs):
     """supports_op says no and the entry returns a status instead of computing: the backend keeps its own kernel"""
     import torch
