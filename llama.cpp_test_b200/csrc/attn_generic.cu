@@ -35,12 +35,16 @@ __device__ __forceinline__ float alibi_slope(const attn_generic_args &a, int h) 
 template <int D, int G, int TK, int TV>
 __global__ void __launch_bounds__(32*AG_WARPS)
 attn_generic_kernel(const __grid_constant__ attn_generic_args a) {
-    constexpr int EPL = D/32;                       // elements per lane
+    // elements per lane; head sizes 80 / 96 / 112 put 4 on each of the first D/4 lanes (never across a quant block), the
+    // other lanes carry zeros through the dot products.  80 and 112 are no multiple of the quant block: F16 / F32 rows only
+    constexpr int EPL = (D == 64 || D == 128 || D == 256) ? D/32 : 4;
+    constexpr int LANES = D/EPL;
     const b200_attn_desc &p = a.d;
     const int iq = blockIdx.x, h0 = blockIdx.y*G, split = blockIdx.z;
     const int kvh = h0/a.rk2;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool paged = p.block_table != nullptr;
+    const bool active = lane < LANES;
 
     // visible range of this row
     int64_t n_vis; int seq = 0;
@@ -64,7 +68,7 @@ attn_generic_kernel(const __grid_constant__ attn_generic_args a) {
     for (int g = 0; g < G; ++g) {
         const float *qp = reinterpret_cast<const float *>(static_cast<const char *>(p.q) + (int64_t) iq*p.nbq1 + (int64_t) (h0 + g)*p.nbq2);
 #pragma unroll
-        for (int e = 0; e < EPL; ++e) { q[g][e] = qp[lane*EPL + e]*scale; acc[g][e] = 0.0f; }
+        for (int e = 0; e < EPL; ++e) { q[g][e] = active ? qp[lane*EPL + e]*scale : 0.0f; acc[g][e] = 0.0f; }
         m[g] = -INFINITY; l[g] = 0.0f;
         slope[g] = alibi_slope(a, h0 + g);
     }
@@ -85,8 +89,13 @@ attn_generic_kernel(const __grid_constant__ attn_generic_args a) {
             }
         }
         float kf[EPL], vf[EPL];
-        load_row_elems<TK, EPL>(kbase + cell*p.nbk1, lane*EPL, kf);
-        load_row_elems<TV, EPL>(vbase + cell*p.nbv1, lane*EPL, vf);
+        if (LANES == 32 || active) {
+            load_row_elems<TK, EPL>(kbase + cell*p.nbk1, lane*EPL, kf);
+            load_row_elems<TV, EPL>(vbase + cell*p.nbv1, lane*EPL, vf);
+        } else {
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) kf[e] = vf[e] = 0.0f;
+        }
 #pragma unroll
         for (int g = 0; g < G; ++g) {
             float s = 0.0f;
@@ -111,7 +120,7 @@ attn_generic_kernel(const __grid_constant__ attn_generic_args a) {
 #pragma unroll
     for (int g = 0; g < G; ++g) {
 #pragma unroll
-        for (int e = 0; e < EPL; ++e) s_acc[warp][g][lane*EPL + e] = acc[g][e];
+        for (int e = 0; e < EPL; ++e) if (LANES == 32 || active) s_acc[warp][g][lane*EPL + e] = acc[g][e];
         if (lane == 0) { s_m[warp][g] = m[g]; s_l[warp][g] = l[g]; }
     }
     __syncthreads();
@@ -158,20 +167,30 @@ attn_combine_kernel(const float *partial, float *dst, int n_splits) {
 
 template <int D, int G, int TK>
 static void launch_tv(const attn_generic_args &a, dim3 grid, cudaStream_t st) {
-    switch (a.d.type_v) {
-        case B200_TYPE_F32:  attn_generic_kernel<D, G, TK, B200_TYPE_F32 ><<<grid, 32*AG_WARPS, 0, st>>>(a); break;
-        case B200_TYPE_F16:  attn_generic_kernel<D, G, TK, B200_TYPE_F16 ><<<grid, 32*AG_WARPS, 0, st>>>(a); break;
-        case B200_TYPE_Q8_0: attn_generic_kernel<D, G, TK, B200_TYPE_Q8_0><<<grid, 32*AG_WARPS, 0, st>>>(a); break;
-        default:             attn_generic_kernel<D, G, TK, B200_TYPE_Q4_0><<<grid, 32*AG_WARPS, 0, st>>>(a); break;
+    if constexpr (D % 32 != 0) {                     // no quantised rows of these lengths exist (generic_supports)
+        if (a.d.type_v == B200_TYPE_F32) attn_generic_kernel<D, G, TK, B200_TYPE_F32><<<grid, 32*AG_WARPS, 0, st>>>(a);
+        else                             attn_generic_kernel<D, G, TK, B200_TYPE_F16><<<grid, 32*AG_WARPS, 0, st>>>(a);
+    } else {
+        switch (a.d.type_v) {
+            case B200_TYPE_F32:  attn_generic_kernel<D, G, TK, B200_TYPE_F32 ><<<grid, 32*AG_WARPS, 0, st>>>(a); break;
+            case B200_TYPE_F16:  attn_generic_kernel<D, G, TK, B200_TYPE_F16 ><<<grid, 32*AG_WARPS, 0, st>>>(a); break;
+            case B200_TYPE_Q8_0: attn_generic_kernel<D, G, TK, B200_TYPE_Q8_0><<<grid, 32*AG_WARPS, 0, st>>>(a); break;
+            default:             attn_generic_kernel<D, G, TK, B200_TYPE_Q4_0><<<grid, 32*AG_WARPS, 0, st>>>(a); break;
+        }
     }
 }
 template <int D, int G>
 static void launch_tk(const attn_generic_args &a, dim3 grid, cudaStream_t st) {
-    switch (a.d.type_k) {
-        case B200_TYPE_F32:  launch_tv<D, G, B200_TYPE_F32 >(a, grid, st); break;
-        case B200_TYPE_F16:  launch_tv<D, G, B200_TYPE_F16 >(a, grid, st); break;
-        case B200_TYPE_Q8_0: launch_tv<D, G, B200_TYPE_Q8_0>(a, grid, st); break;
-        default:             launch_tv<D, G, B200_TYPE_Q4_0>(a, grid, st); break;
+    if constexpr (D % 32 != 0) {
+        if (a.d.type_k == B200_TYPE_F32) launch_tv<D, G, B200_TYPE_F32>(a, grid, st);
+        else                             launch_tv<D, G, B200_TYPE_F16>(a, grid, st);
+    } else {
+        switch (a.d.type_k) {
+            case B200_TYPE_F32:  launch_tv<D, G, B200_TYPE_F32 >(a, grid, st); break;
+            case B200_TYPE_F16:  launch_tv<D, G, B200_TYPE_F16 >(a, grid, st); break;
+            case B200_TYPE_Q8_0: launch_tv<D, G, B200_TYPE_Q8_0>(a, grid, st); break;
+            default:             launch_tv<D, G, B200_TYPE_Q4_0>(a, grid, st); break;
+        }
     }
 }
 template <int D>
@@ -182,8 +201,10 @@ static void launch_g(const attn_generic_args &a, int G, dim3 grid, cudaStream_t 
 }
 
 bool generic_supports(const b200_attn_desc &d) {
-    return (d.head_dim == 64 || d.head_dim == 128 || d.head_dim == 256) && type_ok(d.type_k) && type_ok(d.type_v) &&
-           d.n_head_kv > 0 && d.n_head % d.n_head_kv == 0;
+    const bool plain = (d.type_k == B200_TYPE_F16 || d.type_k == B200_TYPE_F32) && (d.type_v == B200_TYPE_F16 || d.type_v == B200_TYPE_F32);
+    const bool hs_ok = d.head_dim == 64 || d.head_dim == 96 || d.head_dim == 128 || d.head_dim == 256
+                    || ((d.head_dim == 80 || d.head_dim == 112) && plain);
+    return hs_ok && type_ok(d.type_k) && type_ok(d.type_v) && d.n_head_kv > 0 && d.n_head % d.n_head_kv == 0;
 }
 
 static int generic_splits(const b200_attn_desc &d, int G) {
@@ -223,14 +244,27 @@ int launch_attn_generic(const b200_attn_desc &d, cudaStream_t st) {
     a.m0 = powf(2.0f, -(d.max_bias       )/a.n_head_log2);
     a.m1 = powf(2.0f, -(d.max_bias / 2.0f)/a.n_head_log2);
     const dim3 grid((unsigned) d.n_q, (unsigned) (d.n_head/G), (unsigned) a.n_splits);
-    if (d.head_dim == 128) launch_g<128>(a, G, grid, st); else if (d.head_dim == 256) launch_g<256>(a, G, grid, st); else launch_g<64>(a, G, grid, st);
+    switch (d.head_dim) {
+        case 128: launch_g<128>(a, G, grid, st); break;
+        case 256: launch_g<256>(a, G, grid, st); break;
+        case 80:  launch_g<80 >(a, G, grid, st); break;
+        case 96:  launch_g<96 >(a, G, grid, st); break;
+        case 112: launch_g<112>(a, G, grid, st); break;
+        default:  launch_g<64 >(a, G, grid, st); break;
+    }
     count_launch();
     if (!check_launch("attn_generic")) return B200_ERR_CUDA;
     if (a.n_splits > 1) {
         const unsigned rows = (unsigned) d.n_q*d.n_head;
-        if (d.head_dim == 128) attn_combine_kernel<128><<<rows, 128, 0, st>>>(a.partial, static_cast<float *>(d.dst), a.n_splits);
-        else if (d.head_dim == 256) attn_combine_kernel<256><<<rows, 256, 0, st>>>(a.partial, static_cast<float *>(d.dst), a.n_splits);
-        else                   attn_combine_kernel<64 ><<<rows, 64,  0, st>>>(a.partial, static_cast<float *>(d.dst), a.n_splits);
+        float *dst = static_cast<float *>(d.dst);
+        switch (d.head_dim) {
+            case 128: attn_combine_kernel<128><<<rows, 128, 0, st>>>(a.partial, dst, a.n_splits); break;
+            case 256: attn_combine_kernel<256><<<rows, 256, 0, st>>>(a.partial, dst, a.n_splits); break;
+            case 80:  attn_combine_kernel<80 ><<<rows, 80,  0, st>>>(a.partial, dst, a.n_splits); break;
+            case 96:  attn_combine_kernel<96 ><<<rows, 96,  0, st>>>(a.partial, dst, a.n_splits); break;
+            case 112: attn_combine_kernel<112><<<rows, 112, 0, st>>>(a.partial, dst, a.n_splits); break;
+            default:  attn_combine_kernel<64 ><<<rows, 64,  0, st>>>(a.partial, dst, a.n_splits); break;
+        }
         count_launch();
         if (!check_launch("attn_combine")) return B200_ERR_CUDA;
     }

@@ -113,9 +113,11 @@ def _grid(hs):
 
 
 @pytest.mark.parametrize("t", TYPES)
-@pytest.mark.parametrize("hs", [64, 128, 256])
+@pytest.mark.parametrize("hs", [64, 80, 128, 256])
 def test_flash_attn_ext_node_reference_grid(pkg, oracle, cuda, hs, t):
     import torch
+    if hs % 32 and t != F16:
+        hs = 96                  # GGML_PAD(hs, block size): what the reference's grid builds for a quantised type (test-backend-ops.cpp:3233)
     bad, n = [], 0
     for i, c in enumerate(_grid(hs)):
         case = FlashAttnCase(pkg, oracle, torch, cuda, hs, 4, c["nr"], c["kv"], c["nb"], c["mask"], c["max_bias"],
@@ -131,7 +133,7 @@ def test_flash_attn_ext_node_reference_grid(pkg, oracle, cuda, hs, t):
     assert n == (108 if hs == 128 else 44)                   # every case of the grid ran
 
 
-@pytest.mark.parametrize("hs", [80, 96, 112])
+@pytest.mark.parametrize("hs", [72, 160])
 def test_flash_attn_ext_node_unsupported_head_sizes_are_declined(pkg, oracle, cuda, hs):
     """supports_op says no and the entry returns a status instead of computing: the backend keeps its own kernel"""
     import torch
