@@ -89,6 +89,10 @@ struct sk_args {
     // early prologue (decode_step, layers 1..): plan and block table were read by the previous layer's launch already, so
     // this one reads them BEFORE it waits for its predecessor
     int    early;
+    // more than 8 query heads per kv head (a multiple of 8): every 8 of them are a VIRTUAL kv head — d.n_head_kv and gqa
+    // below are the virtual counts (gqa = 8), and vsplit virtual heads share one row of the cache (read once per virtual
+    // head: twice the L2 traffic for gqa 16, still the tensor-core kernel instead of the CUDA-core catch-all)
+    int    vsplit;
     // arrivals: [n_q][n_head_kv] segment counters.  A main-kernel warp bumps its row's counter after its stores; the
     // combine CTA of (row, kv head) spins on it instead of waiting for the whole main grid to drain, and zeroes it again
     int   *arrive;
@@ -654,7 +658,7 @@ sk_main_kernel(const __grid_constant__ sk_args a, const __grid_constant__ CUtens
     __syncwarp();
 
     // head-row placement: quantised rows are only 8-byte aligned, the TMA box starts `mis` bytes earlier
-    const int64_t koff = (int64_t) kvh*p.nbk2, voff = (int64_t) kvh*p.nbv2;
+    const int64_t koff = (int64_t) (kvh/a.vsplit)*p.nbk2, voff = (int64_t) (kvh/a.vsplit)*p.nbv2;
     const int kmis = TK == B200_TYPE_F16 ? 0 : (int) (koff & 15), vmis = TV == B200_TYPE_F16 ? 0 : (int) (voff & 15);
     const int kc = TK == B200_TYPE_F16 ? (int) (koff >> 7) : (int) (koff - kmis);     // TMA coordinate of the head row
     const int vc = TV == B200_TYPE_F16 ? (int) (voff >> 7) : (int) (voff - vmis);
@@ -992,7 +996,7 @@ bool streamk_supports(const b200_attn_desc &d) {
     if (d.head_dim != SK_D) return false;
     if (!sk_type_ok(d.type_k) || !sk_type_ok(d.type_v)) return false;
     const int gqa = d.n_head/d.n_head_kv;
-    if (gqa < 1 || gqa > 8) return false;
+    if (gqa < 1 || gqa*d.n_head_kv != d.n_head || (gqa > 8 && (gqa % 8 || gqa > 64))) return false;   // > 8: virtual kv heads of 8 (sk_args::vsplit)
     if (sk_dense(d)) {
         if (d.n_kv % SK_TILE || d.n_kv < SK_TILE || d.n_q < 1) return false;                // whole 16-cell tiles
         if (d.mask) {
@@ -1029,11 +1033,14 @@ template <typename F> static auto sk_dispatch(int tk, int tv, F &&f) {
     return f(std::integral_constant<int, B200_TYPE_Q4_0>{}, std::integral_constant<int, B200_TYPE_Q4_0>{});
 }
 
+static int sk_vsplit(const b200_attn_desc &d) { const int gqa = d.n_head/d.n_head_kv; return gqa > 8 ? gqa/8 : 1; }
+static int sk_nkv(const b200_attn_desc &d)    { return d.n_head_kv*sk_vsplit(d); }                   // virtual kv heads
+
 static int sk_items(const b200_attn_desc &d) {
     const int wps = sk_dispatch(d.type_k, d.type_v, [](auto k, auto v) {         // resident warps per SM
         using SM = sk_smem<decltype(k)::value, decltype(v)::value>; return SM::CTAS_PER_SM*SM::WARPS; });
     const int64_t warps = (int64_t) sk_sm_count()*wps;
-    int64_t items = warps/d.n_head_kv;
+    int64_t items = warps/sk_nkv(d);
     if (items < 1) items = 1;
     // always the whole machine: small problems are kept in few warps by the plan's minimum chunk (SK_MIN_CHUNK tiles),
     // the surplus CTAs leave after the header load.  (A grid cut to the work, 129 CTAs for 8 x 1024, measured 4 % slower
@@ -1050,7 +1057,7 @@ static size_t sk_dense_bytes(const b200_attn_desc &d) {
 
 size_t streamk_workspace(const b200_attn_desc &d) {
     const size_t max_segs = (size_t) sk_items(d) + d.n_q;
-    return sk_dense_bytes(d) + sk_align((4 + 2*((size_t) d.n_q + 1))*sizeof(int)) + sk_align((size_t) d.n_q*d.n_head_kv*sizeof(int))
+    return sk_dense_bytes(d) + sk_align((4 + 2*((size_t) d.n_q + 1))*sizeof(int)) + sk_align((size_t) d.n_q*sk_nkv(d)*sizeof(int))
          + sk_align(max_segs*d.n_head*2*sizeof(float)) + max_segs*d.n_head*SK_D*sizeof(float);
 }
 
@@ -1125,7 +1132,9 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st, const b200_kv_
     TL_ARM();
     sk_args a;
     a.d = d;
-    a.gqa = d.n_head/d.n_head_kv;
+    a.vsplit = sk_vsplit(d);
+    a.d.n_head_kv = sk_nkv(d);                               // virtual kv heads from here on (the tensor maps keep the real count)
+    a.gqa = d.n_head/a.d.n_head_kv;
     a.k65536 = 65536u;
     a.n_items = sk_items(d);
     a.chunk_align = 1;
@@ -1160,7 +1169,7 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st, const b200_kv_
     a.plan = reinterpret_cast<int *>(ws);
     ws += sk_align((4 + 2*((size_t) d.n_q + 1))*sizeof(int));
     a.arrive = reinterpret_cast<int *>(ws);
-    ws += sk_align((size_t) d.n_q*d.n_head_kv*sizeof(int));
+    ws += sk_align((size_t) d.n_q*sk_nkv(d)*sizeof(int));
     a.part_ml = reinterpret_cast<float *>(ws);
     ws += sk_align(max_segs*d.n_head*2*sizeof(float));
     a.part_o = reinterpret_cast<float *>(ws);
@@ -1194,7 +1203,7 @@ int launch_attn_streamk(const b200_attn_desc &d, cudaStream_t st, const b200_kv_
     if (rc != B200_OK) return rc;
     count_launch();
     if (!check_launch("sk_main")) return B200_ERR_CUDA;
-    launch_pdl(sk_combine_kernel, dim3((unsigned) ((int64_t) d.n_q*d.n_head_kv)), dim3(32*a.gqa), 0, st, a);
+    launch_pdl(sk_combine_kernel, dim3((unsigned) ((int64_t) d.n_q*a.d.n_head_kv)), dim3(32*a.gqa), 0, st, a);
     count_launch();
     if (!check_launch("sk_combine")) return B200_ERR_CUDA;
     return B200_OK;

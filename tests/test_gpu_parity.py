@@ -150,6 +150,8 @@ DECODE_CASES = [
     ([700, 64, 2049], 64, 8, 128),                   # 70B GQA ratio 8
     ([129, 40], 8, 8, 128),                          # MHA (ratio 1): CUDA-core single-query path
     ([77, 300], 12, 4, 64),                          # d = 64, ratio 3
+    ([600, 17, 2100], 64, 4, 128),                   # ratio 16 (405B-class): two virtual kv heads of 8 per cache head on stream-K
+    ([333, 1500], 48, 2, 128),                       # ratio 24: three virtual kv heads
 ]
 
 
