@@ -72,6 +72,11 @@ attn_generic_kernel(const __grid_constant__ attn_generic_args a) {
         m[g] = -INFINITY; l[g] = 0.0f;
         slope[g] = alibi_slope(a, h0 + g);
     }
+    // ALiBi through a block table: the bias the reference's mask would carry for this row, -|pos(cell) - pos(query)| rounded to
+    // half (llm_graph_input_attn_kv_unified::set_input, src/llama-graph.cpp:403-477, fills an F16 mask); cell i of a sequence
+    // holds position i, the query sits at q_pos or at the sequence's newest position
+    const bool alibi_paged = paged && p.max_bias > 0.0f;
+    const int64_t qpos = p.q_pos ? (int64_t) p.q_pos[iq] : n_vis - 1;
     const __half *mrow = (!paged && p.mask) ? reinterpret_cast<const __half *>(static_cast<const char *>(p.mask) + (int64_t) iq*p.nb_mask1) : nullptr;
     const int32_t *bt = paged ? p.block_table + (int64_t) seq*p.bt_stride : nullptr;
     const char *kbase = static_cast<const char *>(p.k) + (int64_t) kvh*p.nbk2;
@@ -81,6 +86,7 @@ attn_generic_kernel(const __grid_constant__ attn_generic_args a) {
         int64_t cell; float mval = 0.0f;
         if (paged) {
             cell = (int64_t) bt[i/p.block_size]*p.block_size + i % p.block_size;
+            if (alibi_paged) mval = __half2float(__float2half_rn(-fabsf((float) (i - qpos))));
         } else {
             cell = i;
             if (mrow) {

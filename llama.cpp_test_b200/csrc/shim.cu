@@ -73,7 +73,6 @@ static int validate_attn(const b200_attn_desc *d) {
     if (d->block_table) {
         if (!d->seq_lens || d->n_seqs <= 0 || d->block_size <= 0 || d->bt_stride <= 0) { set_error("attention: paged mode needs seq_lens, n_seqs, block_size, bt_stride"); return B200_ERR_INVALID; }
         if (!d->q_seq && d->n_q > d->n_seqs) { set_error("attention: n_q %d > n_seqs %d without q_seq", d->n_q, d->n_seqs); return B200_ERR_INVALID; }
-        if (d->max_bias != 0.0f) { set_error("attention: ALiBi needs the dense mask (paged mode carries no positions bias)"); return B200_ERR_UNSUPPORTED; }
     } else if (d->n_kv < 0) { set_error("attention: negative n_kv"); return B200_ERR_INVALID; }
     return B200_OK;
 }

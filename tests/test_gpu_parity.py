@@ -170,6 +170,34 @@ def test_paged_decode(pkg, oracle, cuda, case, t, kernel):
     assert nm <= 5e-4
 
 
+@pytest.mark.parametrize("t", TYPES)
+def test_paged_alibi_equals_the_dense_mask_form(pkg, oracle, cuda, t):
+    """ALiBi through a block table (max_bias > 0 without a mask): the kernel derives the bias the reference's F16 mask
+    carries, -|pos(cell) - pos(query)| (src/llama-graph.cpp:403-477), from the cell's index in its sequence.  Checked
+    against the oracle's dense-mask form fed with exactly that mask; decode rows and rows in the middle of a sequence."""
+    import torch
+    lens = [300, 17, 2600, 64]
+    rows = [(0, 299), (1, 16), (2, 2599), (3, 63), (2, 1000), (0, 5)]
+    w = make_workload(oracle, lens, 16, 4, 128, t, seed=310 + t, q_rows=rows)
+    mask = w.dense_mask().astype(np.float32)
+    for i, (s_, pos) in enumerate(rows):
+        p = np.arange(pos + 1)
+        cells = w.block_table[s_, p // w.block_size].astype(np.int64) * w.block_size + p % w.block_size
+        mask[i, cells] = -np.abs(p - pos)
+    want = oracle.attention(w.q, w.k_cache, w.v_cache, t, t, w.n_head_kv, w.scale, mask=mask.astype(np.float16), n_kv=w.n_cells, max_bias=8.0)
+    lay = pkg.KVLayout(t, w.n_head_kv, w.d, w.block_size, w.n_blocks)
+    q = _dev(torch, w.q)
+    out = torch.full_like(q, float("nan"))
+    call = pkg.AttnCall(q, _dev(torch, w.k_cache.reshape(-1)), _dev(torch, w.v_cache.reshape(-1)), lay, out, w.scale,
+                        block_table=_dev(torch, w.block_table), seq_lens=_dev(torch, w.seq_lens), q_seq=_dev(torch, w.q_seq),
+                        q_pos=_dev(torch, w.q_pos), max_bias=8.0)
+    assert call.supported()
+    call.run(); torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    assert not np.isnan(got).any()
+    assert oracle.max_rel_err(want, got) <= TOL[t] and oracle.nmse(want, got) <= 5e-4
+
+
 KV_SHARD_CASES = [
     # a KV-head shard of a GQA model (config 4 sharded over 8 / 4 / 2 GPUs): 1, 2 or 4 kv heads in the call
     ([700, 64, 2049, 0, 33, 1], 8, 1, 128),          # one kv head, gqa 8: the 8 warps of a CTA are 8 stream-K items
