@@ -59,7 +59,12 @@ enum { B200_KERNEL_AUTO = 0, B200_KERNEL_GENERIC = 1, B200_KERNEL_STREAMK = 2, B
  *          with -inf hiding cells — identical semantics to the reference op.
  *   paged  (block_table != NULL): query row t belongs to sequence q_seq[t] (or t when NULL) and sees
  *          positions [0, min(seq_lens[s], q_pos[t]+1)); position p lives in cell
- *          block_table[s*bt_stride + p/block_size]*block_size + p%block_size.  No mask is read.
+ *          block_table[s*bt_stride + p/block_size]*block_size + p%block_size.  No mask is read; with max_bias > 0
+ *          the ALiBi bias the reference's F16 mask would carry, -|p - pos(query)|, is derived from p.
+ * Shapes: head_dim 128 runs on the tensor-core kernels (stream-K decode for any GQA ratio up to 8 or a multiple of 8,
+ * the tcgen05 tile kernel for prefill chunks); head_dim 64 / 80 / 96 / 112 / 256, other GQA ratios and ALiBi through a
+ * block table run on the CUDA-core kernel (80 and 112: F16 / F32 rows only).  b200_supports_attention() says whether
+ * a descriptor is taken at all.
  */
 typedef struct b200_attn_desc {
     int32_t n_q, n_head, n_head_kv, head_dim;
